@@ -1,0 +1,97 @@
+"""ctypes binding of libhpe_b200.so (the C ABI declared in include/hpe_b200.h).
+
+There is deliberately no fallback: if the shared library is missing or a call fails, a
+``RuntimeError`` is raised.  PyTorch is only used by callers for device memory and streams.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "lib", "libhpe_b200.so")
+
+HPE_F32, HPE_BF16 = 0, 1
+ACT_NONE, ACT_RELU, ACT_SILU = 0, 1, 2
+CONV_1x1, CONV_3x3, CONV_STEM7x7, CONV_DECONV4, CONV_FINAL = 0, 1, 2, 3, 4
+
+
+class ConvDesc(C.Structure):
+    _fields_ = [("kind", C.c_int), ("B", C.c_int), ("H", C.c_int), ("W", C.c_int), ("Cin", C.c_int),
+                ("Cout", C.c_int), ("stride", C.c_int), ("act", C.c_int), ("has_residual", C.c_int)]
+
+
+_vp, _i, _f, _sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
+
+# name -> (restype, argtypes); must list every symbol include/hpe_b200.h declares
+SIGNATURES = {
+    "hpe_abi_version": (_i, []),
+    "hpe_last_error": (C.c_char_p, []),
+    "hpe_check_device": (_i, []),
+    "hpe_decode_heatmaps": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _i, _vp, _vp, _vp, _vp]),
+    "hpe_decode_host_scratch_bytes": (_sz, [_i, _i, _i, _i, _i]),
+    "hpe_decode_heatmaps_host": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "hpe_joints_mse_fused": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _f, _f, _f, _vp, _vp, _vp, _f, _vp, _vp]),
+    "hpe_joints_mse_dense": (_i, [_vp, _i, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _f, _vp]),
+    "hpe_generate_target": (_i, [_vp, _i, _i, _i, _i, _f, _f, _f, _vp, _vp, _vp]),
+    "hpe_conv_plan_create": (_i, [C.POINTER(ConvDesc), C.POINTER(_vp)]),
+    "hpe_conv_plan_destroy": (None, [_vp]),
+    "hpe_conv_packed_weight_elems": (_sz, [C.POINTER(ConvDesc)]),
+    "hpe_conv_pack_weight": (_i, [C.POINTER(ConvDesc), _vp, _vp, _vp]),
+    "hpe_conv_run": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "hpe_conv_out_hw": (_i, [C.POINTER(ConvDesc), C.POINTER(_i), C.POINTER(_i)]),
+    "hpe_preprocess_out_elems": (_sz, [_i, _i, _i]),
+    "hpe_preprocess": (_i, [_vp, _i, _i, _i, _vp, _vp]),
+    "hpe_maxpool3x3s2": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
+}
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Load (once) and return the shared library; raises loudly when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python 2d-human-pose-estimation_b200/build.py` "
+                "(or __graft_entry__.build()).  There is no CPU / PyTorch fallback for this path.")
+        handle = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(handle, name)          # AttributeError if a declared symbol is not exported
+            fn.restype = res
+            fn.argtypes = args
+        _lib = handle
+    return _lib
+
+
+def check(rc: int, what: str = "libhpe_b200") -> None:
+    if rc != 0:
+        msg = lib().hpe_last_error()
+        raise RuntimeError(f"{what} failed (code {rc}): {msg.decode() if msg else '?'}")
+
+
+def dtype_code(t) -> int:
+    import torch
+    if t.dtype == torch.float32:
+        return HPE_F32
+    if t.dtype == torch.bfloat16:
+        return HPE_BF16
+    raise TypeError(f"unsupported dtype {t.dtype}: the sm_100a kernels take float32 or bfloat16")
+
+
+def ptr(t) -> int:
+    return 0 if t is None else t.data_ptr()
+
+
+def stream_ptr() -> int:
+    import torch
+    return torch.cuda.current_stream().cuda_stream
+
+
+def require_cuda(*tensors) -> None:
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("libhpe_b200 has no CPU path: tensors must live on a CUDA (sm_100a) device")
+        if t is not None and not t.is_contiguous():
+            raise RuntimeError("libhpe_b200 needs contiguous tensors")

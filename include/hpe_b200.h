@@ -1,0 +1,153 @@
+/*
+ * hpe_b200.h -- C ABI of libhpe_b200.so: the B200 (sm_100a) device path for the top-down heatmap
+ * pose hot path of AI-sangbeom/2D-Human-Pose-Estimation.
+ *
+ * The reference is pure Python/PyTorch and defines no FFI ("the plugin API is Python
+ * duck-typing").  Each entry point below therefore cites the reference *call site* (file:line under
+ * /root/reference) whose device work it replaces, or -- for the stages the reference does not
+ * implement -- the paragraph of SURVEY.md Appendix A that specifies it.
+ *
+ * Conventions (all entry points):
+ *   - return 0 on success, a negative HPE_E* code otherwise; hpe_last_error() returns a thread-local
+ *     human-readable message for the last failure on the calling thread;
+ *   - stream-ordered on the caller's cudaStream_t (passed as void*; NULL = legacy default stream);
+ *     no allocation, no host synchronisation, no host<->device copy inside unless the name ends in
+ *     `_host` (those take HOST pointers and do the copies on `stream`, then synchronise it);
+ *   - every buffer is caller-owned device memory (plain pointers + sizes; no torch types);
+ *   - one host thread per stream; different streams may be driven from different threads.
+ */
+#ifndef HPE_B200_H_
+#define HPE_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HPE_OK            0
+#define HPE_EINVAL       -1   /* bad argument (null pointer, non-positive size, bad dtype, misalignment) */
+#define HPE_ECUDA        -2   /* a CUDA runtime/driver call or kernel launch failed                   */
+#define HPE_EUNSUPPORTED -3   /* shape outside what the sm_100a kernels cover                          */
+#define HPE_EARCH        -4   /* device is not compute capability 10.x                                 */
+
+#define HPE_F32  0
+#define HPE_BF16 1
+
+/* activation codes of the fused conv epilogue */
+#define HPE_ACT_NONE 0
+#define HPE_ACT_RELU 1        /* timm Bottleneck act (resnet.py:244-270)                               */
+#define HPE_ACT_SILU 2        /* first-party ConvBlock default act (HPE/models/nn/modules/block.py:20-45) */
+
+int         hpe_abi_version(void);
+const char* hpe_last_error(void);
+/* 0 if the current device can run the sm_100a kernels, HPE_EARCH otherwise. */
+int         hpe_check_device(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * Heatmap decode.  Replaces the decode the reference's metric/test loop would run on the output of
+ * `output = model(data)` (HPE/engine/trainer.py:90, :110-113; HPE/test.py:335-361 is the reference's
+ * regression analogue).  Semantics: SURVEY.md App. A.2 (first-max argmax, coords zeroed when
+ * maxval <= 0), A.3 (quarter-pixel, strictly interior peaks) and A.4 (per-sample 2x3 inverse affine),
+ * one pass over the heatmaps.
+ *   hm      [B,K,H,W] dtype HPE_F32|HPE_BF16, contiguous
+ *   affine  [B,2,3] f32 or NULL (identity: heatmap coordinates are returned)
+ *   refine  0 = A.2 only (get_max_preds), 1 = A.2+A.3
+ *   coords  [B,K,2] f32 out; maxvals [B,K] f32 out; idx [B,K] i32 out or NULL
+ * ---------------------------------------------------------------------------------------------- */
+int hpe_decode_heatmaps(const void* hm, int dtype, int B, int K, int H, int W,
+                        const float* affine, int refine,
+                        float* coords, float* maxvals, int32_t* idx, void* stream);
+
+/* Same call with HOST buffers (pageable or pinned): H2D of hm/affine, kernel, D2H of the results on
+ * `stream`, then a stream synchronise.  `d_scratch` is caller-owned DEVICE scratch of at least
+ * hpe_decode_host_scratch_bytes(...) bytes. */
+size_t hpe_decode_host_scratch_bytes(int dtype, int B, int K, int H, int W);
+int hpe_decode_heatmaps_host(const void* h_hm, int dtype, int B, int K, int H, int W,
+                             const float* h_affine, int refine,
+                             float* h_coords, float* h_maxvals, int32_t* h_idx,
+                             void* d_scratch, size_t scratch_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Target generation + target-weighted joints MSE.  Replaces `loss = criterion(output, target,
+ * target_weight[B,K,1])` (HPE/engine/trainer.py:92) and the dataloader-side target rasterisation.
+ * Semantics: SURVEY.md App. A.5 (Gaussian targets) and A.6 (JointsMSELoss, use_target_weight=True).
+ *
+ * Fused mode (targets never materialised):
+ *   pred     [B,K,H,W] f32|bf16          joints [B,K,3] f32 (x, y in input px, visibility)
+ *   partials [B*K] f32 scratch (per-map sum of w^2 (p-g)^2, fixed reduction order)
+ *   loss     [1] f32 out = 0.5/(K*B*H*W) * sum(partials)   (second, single-CTA, fixed-order stage)
+ *   grad     [B,K,H,W] in pred's dtype or NULL; when non-NULL also writes
+ *            dL/dpred = grad_scale * w^2 (p-g)/(K*B*H*W) in the same pass
+ *   weight_out [B,K] f32 or NULL: the effective target weight (A.5, incl. the out-of-map rule)
+ * ---------------------------------------------------------------------------------------------- */
+int hpe_joints_mse_fused(const void* pred, int dtype, const float* joints,
+                         int B, int K, int H, int W, float sigma, float stride_x, float stride_y,
+                         float* partials, float* loss, void* grad, float grad_scale,
+                         float* weight_out, void* stream);
+
+/* Drop-in mode: materialised target [B,K,H,W] f32 and weight [B,K] f32 (the trainer's call shape). */
+int hpe_joints_mse_dense(const void* pred, int dtype, const float* target, const float* weight,
+                         int B, int K, int H, int W,
+                         float* partials, float* loss, void* grad, float grad_scale, void* stream);
+
+/* A.5 alone: rasterise target [B,K,H,W] f32 and weight [B,K] f32 from joints. */
+int hpe_generate_target(const float* joints, int B, int K, int H, int W,
+                        float sigma, float stride_x, float stride_y,
+                        float* target, float* weight, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Convolution stack (NHWC bf16 activations, fp32 accumulation on tcgen05/TMEM, operands by TMA).
+ * Replaces the cuDNN conv + BatchNorm2d + activation (+ residual add) launches behind
+ * `output = model(data)` (HPE/engine/trainer.py:90) for the config-default backbone:
+ * timm ResNet-50 stem/Bottleneck/forward_features (HPE/thirdparty/pytorch-image-models/timm/models/
+ * resnet.py:554-576, 244-270, 742-756), and -- for the first-party conv unit -- ConvBlock.forward_fuse
+ * (HPE/models/nn/modules/block.py:44-45).  The deconv head and final 1x1 follow SURVEY.md App. A.1.
+ *
+ * A plan owns the TMA descriptors and launch geometry for ONE layer at ONE shape; create once, run
+ * every step.  Tensors (device, caller-owned):
+ *   x        [B,H,W,Cin]     bf16 NHWC         w  packed bf16, see hpe_conv_pack_weight_elems()
+ *   scale,shift [Cout] f32   folded BN (y = acc*scale + shift), shift doubles as conv bias
+ *   residual [B,Ho,Wo,Cout]  bf16 or NULL      y  [B,Ho,Wo,Cout] bf16 NHWC
+ *                                              (HPE_CONV_FINAL: y = heatmaps [B,Cout,Ho,Wo] f32 NCHW)
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct hpe_conv_plan hpe_conv_plan;
+
+#define HPE_CONV_1x1      0   /* 1x1, stride 1|2, pad 0                                         */
+#define HPE_CONV_3x3      1   /* 3x3, stride 1|2, pad 1                                         */
+#define HPE_CONV_STEM7x7  2   /* 7x7 s2 p3 on the space-to-depth image written by hpe_preprocess */
+#define HPE_CONV_DECONV4  3   /* ConvTranspose2d k4 s2 p1 as four 2x2 sub-pixel convolutions    */
+#define HPE_CONV_FINAL    4   /* 1x1 -> K joints (+bias), writes fp32 NCHW heatmaps             */
+
+typedef struct hpe_conv_desc {
+  int kind;                 /* HPE_CONV_*                                         */
+  int B, H, W, Cin, Cout;   /* input geometry (H,W = input height/width)          */
+  int stride;               /* 1 or 2 (ignored for STEM/DECONV/FINAL)             */
+  int act;                  /* HPE_ACT_*                                          */
+  int has_residual;         /* epilogue adds `residual` before the activation     */
+} hpe_conv_desc;
+
+int  hpe_conv_plan_create(const hpe_conv_desc* desc, hpe_conv_plan** out);
+void hpe_conv_plan_destroy(hpe_conv_plan* plan);
+/* number of bf16 elements of the packed weight buffer for this layer */
+size_t hpe_conv_packed_weight_elems(const hpe_conv_desc* desc);
+/* Pack a PyTorch-layout fp32 weight (Conv2d [Cout,Cin,kh,kw]; ConvTranspose2d [Cin,Cout,4,4]) that
+ * lives on the DEVICE into the kernel's bf16 GEMM-B layout (device).  Stream-ordered. */
+int  hpe_conv_pack_weight(const hpe_conv_desc* desc, const float* w_torch, void* w_packed, void* stream);
+int  hpe_conv_run(hpe_conv_plan* plan, const void* x, const void* w_packed,
+                  const float* scale, const float* shift, const void* residual, void* y, void* stream);
+/* output spatial size of the layer */
+int  hpe_conv_out_hw(const hpe_conv_desc* desc, int* Ho, int* Wo);
+
+/* fp32 NCHW image [B,3,H,W] -> bf16 space-to-depth NHWC staging the stem conv reads
+ * (replaces `data.float()` + cuDNN's layout transform, HPE/engine/trainer.py:88-90). */
+size_t hpe_preprocess_out_elems(int B, int H, int W);
+int  hpe_preprocess(const float* img_nchw, int B, int H, int W, void* s2d_out, void* stream);
+/* MaxPool 3x3 s2 p1 on NHWC bf16 (timm resnet.py:574-576). */
+int  hpe_maxpool3x3s2(const void* x, int B, int H, int W, int C, void* y, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HPE_B200_H_ */

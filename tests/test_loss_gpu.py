@@ -1,0 +1,77 @@
+"""GPU parity: fused Gaussian-target + joints MSE (through the C ABI) vs the App.-A oracle.
+Bar: loss within 1e-4 relative (north_star); gradient and rasterised targets elementwise."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import heatmap_ref as hr
+
+pytestmark = pytest.mark.gpu
+LOSS_RTOL = 1e-4
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("B,K,H,W,sigma", [(16, 17, 64, 48, 2.0), (4, 17, 96, 72, 3.0), (2, 133, 64, 48, 2.0),
+                                           (3, 5, 10, 7, 1.0)])
+def test_fused_loss_and_grad(hpe, cuda_dev, B, K, H, W, sigma, dtype):
+    pred = hr.synth_heatmaps(B, K, H, W, seed=3, adversarial=False)
+    joints = hr.synth_joints(B, K, (H * 4, W * 4), seed=5)
+    p = torch.from_numpy(pred).to(cuda_dev).to(dtype).requires_grad_(True)
+    crit = hpe.JointsMSELoss(sigma=sigma)
+    loss = crit(p, torch.from_numpy(joints).to(cuda_dev), None)
+    loss.backward()
+    lo, go = hr.joints_mse_loss_from_joints(p.detach().float().cpu().numpy(), joints, sigma)
+    assert loss.dim() == 0 and abs(loss.item() - float(lo)) <= LOSS_RTOL * abs(float(lo))
+    g = p.grad.float().cpu().numpy()
+    tol = 1e-9 if dtype == torch.float32 else np.abs(go).max() * 2 ** -8
+    assert np.abs(g - go).max() <= tol + 1e-6 * np.abs(go).max()
+
+
+def test_generate_target_matches_oracle(hpe, cuda_dev):
+    for (H, W, sigma) in [(64, 48, 2.0), (96, 72, 3.0), (9, 7, 1.0)]:
+        joints = hr.synth_joints(8, 17, (H * 4, W * 4), seed=5)
+        # add exact half-integer and negative coordinates (rounding / truncation rules)
+        joints[0, 0] = [10.0, 10.0, 1.0]; joints[0, 1] = [-3.0, 20.0, 2.0]; joints[0, 2] = [-40.0, 10.0, 1.0]
+        joints[0, 3] = [1e9, 5.0, 1.0]; joints[0, 4] = [float(W * 4 + 11), 5.0, 1.0]
+        t, w = hpe.generate_target(torch.from_numpy(joints).to(cuda_dev), (H, W), sigma)
+        to, wo = hr.generate_target(joints, (H, W), sigma)
+        np.testing.assert_array_equal(w.cpu().numpy(), wo)
+        assert np.abs(t.cpu().numpy() - to).max() <= 2e-7
+        assert np.array_equal(t.cpu().numpy() == 0, to == 0)        # support is identical
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_dense_drop_in_mode(hpe, cuda_dev, dtype):
+    B, K, H, W = 8, 17, 64, 48
+    pred = hr.synth_heatmaps(B, K, H, W, seed=3, adversarial=False)
+    joints = hr.synth_joints(B, K, (256, 192), seed=5)
+    target, tw = hr.generate_target(joints, (H, W), 2.0)
+    tw = tw * np.random.default_rng(0).uniform(0.5, 1.5, tw.shape).astype(np.float32)   # non-binary weights
+    p = torch.from_numpy(pred).to(cuda_dev).to(dtype).requires_grad_(True)
+    # the trainer's call shape: criterion(output, target, meta1.float().unsqueeze(-1))
+    loss = hpe.JointsMSELoss()(p, torch.from_numpy(target).to(cuda_dev), torch.from_numpy(tw).to(cuda_dev))
+    (loss * 2.0).backward()
+    lo, go = hr.joints_mse_loss(p.detach().float().cpu().numpy(), target, tw)
+    assert abs(loss.item() - float(lo)) <= LOSS_RTOL * abs(float(lo))
+    g = p.grad.float().cpu().numpy()
+    tol = 1e-9 if dtype == torch.float32 else np.abs(go).max() * 2 ** -7
+    assert np.abs(g - 2.0 * go).max() <= tol + 2e-6 * np.abs(go).max()
+
+
+def test_loss_full_size_properties(hpe, cuda_dev):
+    """C2 size (B=256,K=17,64x48): (1) pred == rasterised target -> loss 0 and grad 0; (2) run-to-run
+    bit-stable; (3) fused == dense on device-rasterised targets; (4) scaling the residual by 2 scales loss by 4."""
+    B, K, H, W = 256, 17, 64, 48
+    joints = torch.from_numpy(hr.synth_joints(B, K, (256, 192), seed=5)).to(cuda_dev)
+    target, tw = hpe.generate_target(joints, (H, W), 2.0)
+    crit = hpe.JointsMSELoss()
+    p = target.clone().requires_grad_(True)
+    l0 = crit(p, joints, None); l0.backward()
+    assert l0.item() == 0.0 and float(p.grad.abs().max()) == 0.0
+    pred = (target + 0.01 * torch.randn(target.shape, device=cuda_dev, generator=torch.Generator(cuda_dev).manual_seed(1)))
+    a = crit(pred, joints, None).item(); b = crit(pred, joints, None).item()
+    assert a == b
+    d = crit(pred, target, tw).item()
+    assert abs(a - d) <= 1e-6 * abs(d)
+    l2 = crit(target + 2 * (pred - target), joints, None).item()
+    assert abs(l2 - 4 * a) <= 1e-4 * abs(4 * a)
