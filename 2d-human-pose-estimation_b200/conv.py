@@ -1,0 +1,108 @@
+"""Host-side handles for the tcgen05 implicit-GEMM convolution layers (csrc/conv_gemm.cu).
+
+One ``ConvLayer`` = one ``hpe_conv_plan`` (TMA descriptors + launch geometry) + packed bf16 weights +
+folded-BN ``scale``/``shift``.  It replaces ``conv -> bn -> act (-> += shortcut)`` of the reference's
+blocks: timm ``Bottleneck.forward`` (/root/reference/HPE/thirdparty/pytorch-image-models/timm/models/
+resnet.py:244-270) and the first-party ``ConvBlock.forward_fuse`` (HPE/models/nn/modules/block.py:44-45).
+Activations are NHWC bf16 tensors; PyTorch only owns the memory.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import ACT_NONE, ACT_RELU, ACT_SILU, CONV_1x1, CONV_3x3, CONV_DECONV4, CONV_FINAL, CONV_STEM7x7, ConvDesc
+
+
+def fold_bn(weight, bias, running_mean, running_var, eps):
+    """BN(eval) as y = x*scale + shift (same algebra as ConvBlock's fuse, block.py:44-45 / SURVEY §8 a3)."""
+    scale = weight.float() / torch.sqrt(running_var.float() + eps)
+    shift = bias.float() - running_mean.float() * scale
+    return scale.contiguous(), shift.contiguous()
+
+
+class ConvLayer:
+    def __init__(self, kind, B, H, W, Cin, Cout, stride=1, act=ACT_RELU, has_residual=False, device="cuda"):
+        self.device = torch.device(device)
+        self.desc = ConvDesc(kind, B, H, W, Cin, Cout, stride, act, int(has_residual))
+        lib = _lib.lib()
+        ho, wo = C.c_int(), C.c_int()
+        with torch.cuda.device(self.device):
+            _lib.check(lib.hpe_conv_out_hw(C.byref(self.desc), C.byref(ho), C.byref(wo)), "hpe_conv_out_hw")
+            plan = C.c_void_p()
+            _lib.check(lib.hpe_conv_plan_create(C.byref(self.desc), C.byref(plan)), "hpe_conv_plan_create")
+        self.plan = plan
+        self.Ho, self.Wo = ho.value, wo.value
+        self.kind, self.B, self.Cout = kind, B, Cout
+        n = lib.hpe_conv_packed_weight_elems(C.byref(self.desc))
+        self.w_packed = torch.zeros(n, dtype=torch.bfloat16, device=self.device)
+        self.scale = torch.ones(Cout, dtype=torch.float32, device=self.device)
+        self.shift = torch.zeros(Cout, dtype=torch.float32, device=self.device)
+
+    def __del__(self):
+        try:
+            if getattr(self, "plan", None):
+                _lib.lib().hpe_conv_plan_destroy(self.plan)
+                self.plan = None
+        except Exception:
+            pass
+
+    def out_shape(self):
+        if self.kind == CONV_FINAL:
+            return (self.B, self.Cout, self.Ho, self.Wo)
+        return (self.B, self.Ho, self.Wo, self.Cout)
+
+    def alloc_out(self):
+        dt = torch.float32 if self.kind == CONV_FINAL else torch.bfloat16
+        return torch.empty(self.out_shape(), dtype=dt, device=self.device)
+
+    def load(self, weight: torch.Tensor, scale: torch.Tensor = None, shift: torch.Tensor = None):
+        """weight: PyTorch layout fp32 (Conv2d [Cout,Cin,kh,kw] / ConvTranspose2d [Cin,Cout,4,4])."""
+        w = weight.detach().to(self.device, torch.float32).contiguous()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().hpe_conv_pack_weight(C.byref(self.desc), _lib.ptr(w), _lib.ptr(self.w_packed),
+                                                       _lib.stream_ptr()), "hpe_conv_pack_weight")
+        if scale is not None:
+            self.scale.copy_(scale.detach().to(self.device, torch.float32))
+        if shift is not None:
+            self.shift.copy_(shift.detach().to(self.device, torch.float32))
+        return self
+
+    def __call__(self, x: torch.Tensor, residual: torch.Tensor = None, out: torch.Tensor = None):
+        if out is None:
+            out = self.alloc_out()
+        _lib.require_cuda(x, residual, out)
+        with torch.cuda.device(self.device):
+            rc = _lib.lib().hpe_conv_run(self.plan, _lib.ptr(x), _lib.ptr(self.w_packed), _lib.ptr(self.scale),
+                                         _lib.ptr(self.shift), _lib.ptr(residual), _lib.ptr(out), _lib.stream_ptr())
+        _lib.check(rc, "hpe_conv_run")
+        return out
+
+
+def preprocess(img: torch.Tensor, out: torch.Tensor = None):
+    """fp32 NCHW [B,3,H,W] -> the bf16 space-to-depth staging tensor the stem conv reads."""
+    _lib.require_cuda(img)
+    B, Cc, H, W = img.shape
+    if Cc != 3 or img.dtype != torch.float32:
+        raise ValueError("preprocess expects float32 [B,3,H,W]")
+    n = _lib.lib().hpe_preprocess_out_elems(B, H, W)
+    if n == 0:
+        raise ValueError("H and W must be even")
+    if out is None:
+        out = torch.empty(n, dtype=torch.bfloat16, device=img.device)
+    with torch.cuda.device(img.device):
+        _lib.check(_lib.lib().hpe_preprocess(_lib.ptr(img), B, H, W, _lib.ptr(out), _lib.stream_ptr()), "hpe_preprocess")
+    return out
+
+
+def maxpool3x3s2(x: torch.Tensor, out: torch.Tensor = None):
+    """MaxPool2d(3, stride 2, padding 1) on NHWC bf16 (timm resnet.py:574-576)."""
+    _lib.require_cuda(x, out)
+    B, H, W, Cc = x.shape
+    if out is None:
+        out = torch.empty((B, (H - 1) // 2 + 1, (W - 1) // 2 + 1, Cc), dtype=torch.bfloat16, device=x.device)
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.lib().hpe_maxpool3x3s2(_lib.ptr(x), B, H, W, Cc, _lib.ptr(out), _lib.stream_ptr()), "hpe_maxpool3x3s2")
+    return out

@@ -1,0 +1,691 @@
+// Implicit-GEMM convolution for sm_100a: tcgen05.mma (accumulators in TMEM) fed by TMA, with the folded
+// BatchNorm scale/shift (+ residual add) (+ ReLU | SiLU) fused into the epilogue.
+//
+// GEMM view:  D[M = output pixels][N = Cout] = sum_taps  A_tap[M][Cin] * W_tap[N][Cin]^T
+//   * activations are NHWC bf16; an M tile is a (nb x th x tw) brick of 128 output pixels, so for every
+//     filter tap the A operand is ONE 4-D TMA box {64 ch, tw, th, nb} of the input shifted by the tap
+//     offset -- zero padding comes from TMA out-of-bounds fill, stride 2 from TMA element strides, and
+//     no im2col buffer ever exists.  The box lands in shared memory as 128 rows x 128 B with the 128-byte
+//     swizzle, which is exactly the K-major SWIZZLE_128B operand layout tcgen05.mma consumes.
+//   * weights are pre-packed [rows = Cout][K = taps*Cin] bf16 and loaded by 2-D TMA boxes {64, BLOCK_N}.
+//   * ConvTranspose2d(k4,s2,p1) = four 2x2 sub-pixel convolutions (one per output parity class), each a
+//     GEMM with 4 taps whose output tile is written through a strided TMA store map (no zero insertion).
+//   * the 7x7/s2 stem runs on a space-to-depth copy of the image (16 ch per 2x2 pixel block): with an
+//     overlapping-stride TMA map one box row = 4 adjacent blocks = 64 contiguous bf16, so the stem is a
+//     4-tap GEMM with K = 4 x 64.
+//
+// Persistent, warp-specialised CTA (1 per SM, 224 threads):
+//   warp 0  TMA producer (A + W operand ring, STAGES deep)
+//   warp 1  TMEM allocator + single-thread tcgen05.mma issuer (double-buffered accumulators)
+//   warp 2  residual-tile TMA producer (into the epilogue staging ring)
+//   warps 3-6  epilogue: tcgen05.ld -> scale/shift/residual/activation -> bf16 -> swizzled smem -> TMA store
+#include "hpe_common.cuh"
+#include "ptx_sm100.cuh"
+#include <cuda.h>
+#include <mutex>
+
+namespace hpe {
+using namespace ptx;
+
+constexpr int kConvThreads   = 224;
+constexpr int kEpiThreads    = 128;
+constexpr int kEpiWarp0      = 3;
+constexpr int kTileM         = 128;
+constexpr int kKBlock        = 64;                    // bf16 elements per k-block = one 128-byte swizzle row
+constexpr int kABytes        = kTileM * kKBlock * 2;  // 16 KB
+constexpr int kNumSB         = 4;                     // epilogue staging buffers (16 KB each)
+constexpr int kSBBytes       = kTileM * 64 * 2;       // 128 rows x 64 bf16
+constexpr int kMaxTaps       = 9;
+
+struct OutMaps { CUtensorMap m[4]; };
+
+struct ConvParams {
+  int kind, taps, kc_per_tap, in_stride;
+  int tw, th, nb;
+  int tiles_x, tiles_y, tiles_b, n_tiles_n, n_classes, num_tiles;
+  int Ho, Wo, B, Cout;          // Ho,Wo = extent of the tile grid (deconv: input-resolution grid per class)
+  int act, has_res;
+  const float* scale;
+  const float* shift;
+  float* hm_out;                // HPE_CONV_FINAL: fp32 NCHW heatmaps
+};
+
+struct TileCoord { int n_tile, cls, x0, y0, b0; };
+
+__device__ __forceinline__ TileCoord tile_coord(const ConvParams& p, int tile) {
+  TileCoord t;
+  t.n_tile = tile % p.n_tiles_n;  int r = tile / p.n_tiles_n;
+  t.cls = r % p.n_classes;        r /= p.n_classes;
+  t.x0 = (r % p.tiles_x) * p.tw;  r /= p.tiles_x;
+  t.y0 = (r % p.tiles_y) * p.th;  r /= p.tiles_y;
+  t.b0 = r * p.nb;
+  return t;
+}
+
+// input-pixel offset of filter tap `t` (deconv: depends on the output parity class)
+__device__ __forceinline__ void tap_offset(const ConvParams& p, int t, int cls, int& dx, int& dy) {
+  if (p.kind == HPE_CONV_3x3)          { dy = t / 3 - 1; dx = t % 3 - 1; }
+  else if (p.kind == HPE_CONV_STEM7x7) { dy = t - 2;     dx = 0; }
+  else if (p.kind == HPE_CONV_DECONV4) {
+    const int py = cls >> 1, px = cls & 1, ty = t >> 1, tx = t & 1;
+    dy = ty ? (py ? 1 : -1) : 0;
+    dx = tx ? (px ? 1 : -1) : 0;
+  } else { dx = 0; dy = 0; }
+}
+
+__device__ __forceinline__ float apply_act(float v, int act) {
+  if (act == HPE_ACT_RELU) return fmaxf(v, 0.f);
+  if (act == HPE_ACT_SILU) return v / (1.f + __expf(-v));
+  return v;
+}
+
+template <int BLOCK_N, int STAGES>
+struct SmemLayout {
+  static constexpr int kBBytes     = BLOCK_N * kKBlock * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kOffA   = 0;
+  static constexpr int kOffB   = STAGES * kABytes;
+  static constexpr int kOffSB  = kOffB + STAGES * kBBytes;
+  static constexpr int kOffBar = kOffSB + kNumSB * kSBBytes;
+  static constexpr int kNumBar = 2 * STAGES + 4 + 2 * kNumSB;
+  static constexpr int kTotal  = kOffBar + kNumBar * 8 + 16;
+  static constexpr int kDynamic = kTotal + 1024;      // slack for manual 1024-byte alignment
+};
+
+template <int BLOCK_N, int STAGES>
+__global__ void __launch_bounds__(kConvThreads, 1)
+conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+                 const __grid_constant__ OutMaps tmOut, const __grid_constant__ CUtensorMap tmRes,
+                 const ConvParams p) {
+  using L = SmemLayout<BLOCK_N, STAGES>;
+  constexpr int kChunks   = BLOCK_N >= 64 ? BLOCK_N / 64 : 1;
+  constexpr int kTmemCols = 2 * BLOCK_N < 32 ? 32 : 2 * BLOCK_N;
+  constexpr uint32_t kIdesc = make_idesc_bf16_m128(BLOCK_N);
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA  = smem + L::kOffA;
+  uint8_t* sB  = smem + L::kOffB;
+  uint8_t* sSB = smem + L::kOffSB;
+  uint64_t* bars       = reinterpret_cast<uint64_t*>(smem + L::kOffBar);
+  uint64_t* full_bar   = bars;
+  uint64_t* empty_bar  = bars + STAGES;
+  uint64_t* tfull_bar  = bars + 2 * STAGES;
+  uint64_t* tempty_bar = bars + 2 * STAGES + 2;
+  uint64_t* sbfull_bar = bars + 2 * STAGES + 4;
+  uint64_t* sbempty_bar = bars + 2 * STAGES + 4 + kNumSB;
+  uint32_t* tmem_slot  = reinterpret_cast<uint32_t*>(bars + L::kNumBar);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int num_kb = p.taps * p.kc_per_tap;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmA); prefetch_tmap(&tmW);
+    if (p.kind != HPE_CONV_FINAL) for (int c = 0; c < p.n_classes; ++c) prefetch_tmap(&tmOut.m[c]);
+    if (p.has_res) prefetch_tmap(&tmRes);
+    for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], 4); }
+    for (int b = 0; b < kNumSB; ++b) { mbar_init(&sbfull_bar[b], 1); mbar_init(&sbempty_bar[b], 1); }
+    fence_mbar_init();
+  }
+  if (warp == 1) { tmem_alloc(tmem_slot, kTmemCols); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== operand producer =====================
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        const TileCoord t = tile_coord(p, tile);
+        const int wrow = t.cls * p.Cout + t.n_tile * BLOCK_N;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          const int tap = kb / p.kc_per_tap, kc = kb - tap * p.kc_per_tap;
+          int dx, dy; tap_offset(p, tap, t.cls, dx, dy);
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&full_bar[stage], L::kStageBytes);
+          tma_load_4d(sA + stage * kABytes, &tmA, &full_bar[stage], kc * kKBlock,
+                      t.x0 * p.in_stride + dx, t.y0 * p.in_stride + dy, t.b0);
+          tma_load_2d(sB + stage * L::kBBytes, &tmW, &full_bar[stage], kb * kKBlock, wrow);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0; int it = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+        const int acc = it & 1;
+        mbar_wait(&tempty_bar[acc], ((it >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint64_t adesc = make_sw128_kmajor_desc(sA + stage * kABytes);
+          const uint64_t bdesc = make_sw128_kmajor_desc(sB + stage * L::kBBytes);
+#pragma unroll
+          for (int k = 0; k < kKBlock / 16; ++k)      // UMMA_K = 16 bf16 = 32 B -> +2 in the (addr>>4) field
+            umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, kIdesc, (kb | k) != 0);
+          umma_commit(&empty_bar[stage]);             // frees the smem stage when these MMAs retire
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tfull_bar[acc]);                 // accumulator ready for the epilogue
+      }
+    }
+  } else if (warp == 2) {
+    // ===================== residual producer =====================
+    if (lane == 0 && p.has_res) {
+      int r = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        const TileCoord t = tile_coord(p, tile);
+        for (int c = 0; c < kChunks; ++c, ++r) {
+          const int b = r % kNumSB;
+          mbar_wait(&sbempty_bar[b], (r / kNumSB) & 1);
+          mbar_arrive_expect_tx(&sbfull_bar[b], kSBBytes);
+          tma_load_4d(sSB + b * kSBBytes, &tmRes, &sbfull_bar[b], t.n_tile * BLOCK_N + c * 64, t.x0, t.y0, t.b0);
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue (4 warps = 128 TMEM lanes) =====================
+    const int ew = warp & 3;                      // TMEM lane group this warp may access
+    const int row = ew * 32 + lane;               // tile row = TMEM lane = pixel inside the brick
+    const bool leader = threadIdx.x == kEpiWarp0 * 32;
+    if (leader && p.has_res) { mbar_arrive(&sbempty_bar[0]); mbar_arrive(&sbempty_bar[1]); }
+    int q = 0, it = 0;
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      const TileCoord t = tile_coord(p, tile);
+      const int acc = it & 1;
+      mbar_wait(&tfull_bar[acc], (it >> 1) & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BLOCK_N;
+
+      if (p.kind == HPE_CONV_FINAL) {
+        // fp32 NCHW heatmaps straight from registers: for a fixed joint the warp's 32 rows are
+        // consecutive pixels of the brick -> 64-byte (tw=16) contiguous runs
+        const int xi = row % p.tw, yi = (row / p.tw) % p.th, bi = row / (p.tw * p.th);
+        const int x = t.x0 + xi, y = t.y0 + yi, b = t.b0 + bi;
+        const bool ok = x < p.Wo && y < p.Ho && b < p.B;
+        const size_t plane = static_cast<size_t>(p.Ho) * p.Wo;
+        for (int g = 0; g * 32 < p.Cout; ++g) {
+          uint32_t v[32];
+          tmem_ld_x32(taddr + g * 32, v);
+          tmem_ld_wait();
+          if (ok) {
+#pragma unroll
+            for (int e = 0; e < 32; ++e) {
+              const int k = g * 32 + e;
+              if (k < p.Cout) {
+                const float o = apply_act(fmaf(__uint_as_float(v[e]), __ldg(p.scale + k), __ldg(p.shift + k)), p.act);
+                p.hm_out[(static_cast<size_t>(b) * p.Cout + k) * plane + static_cast<size_t>(y) * p.Wo + x] = o;
+              }
+            }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+        continue;
+      }
+
+      for (int c = 0; c < kChunks; ++c, ++q) {
+        const int sb = q % kNumSB;
+        uint8_t* stg = sSB + sb * kSBBytes;
+        if (leader) {
+          bulk_wait_read<1>();                                    // stores <= q-2 have left shared memory
+          if (p.has_res) mbar_arrive(&sbempty_bar[(q + 2) % kNumSB]);   // hand buffer of chunk q+2 to warp 2
+        }
+        uint32_t v[64];
+        tmem_ld_x32(taddr + c * 64, v);
+        tmem_ld_x32(taddr + c * 64 + 32, v + 32);
+        if (p.has_res) mbar_wait(&sbfull_bar[sb], (q / kNumSB) & 1);
+        tmem_ld_wait();
+        if (c == kChunks - 1) {                                   // accumulator drained -> MMA may reuse it
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+        }
+        const int n0 = t.n_tile * BLOCK_N + c * 64;
+        uint8_t* rowp = stg + row * 128;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float4 s0 = __ldg(reinterpret_cast<const float4*>(p.scale + n0 + j * 8));
+          const float4 s1 = __ldg(reinterpret_cast<const float4*>(p.scale + n0 + j * 8 + 4));
+          const float4 h0 = __ldg(reinterpret_cast<const float4*>(p.shift + n0 + j * 8));
+          const float4 h1 = __ldg(reinterpret_cast<const float4*>(p.shift + n0 + j * 8 + 4));
+          float o[8];
+          o[0] = fmaf(__uint_as_float(v[j * 8 + 0]), s0.x, h0.x); o[1] = fmaf(__uint_as_float(v[j * 8 + 1]), s0.y, h0.y);
+          o[2] = fmaf(__uint_as_float(v[j * 8 + 2]), s0.z, h0.z); o[3] = fmaf(__uint_as_float(v[j * 8 + 3]), s0.w, h0.w);
+          o[4] = fmaf(__uint_as_float(v[j * 8 + 4]), s1.x, h1.x); o[5] = fmaf(__uint_as_float(v[j * 8 + 5]), s1.y, h1.y);
+          o[6] = fmaf(__uint_as_float(v[j * 8 + 6]), s1.z, h1.z); o[7] = fmaf(__uint_as_float(v[j * 8 + 7]), s1.w, h1.w);
+          uint4* slot = reinterpret_cast<uint4*>(rowp + ((j ^ (row & 7)) << 4));   // 128-byte swizzle
+          if (p.has_res) {
+            const uint4 rr = *slot;
+            o[0] += bf16_lo(rr.x); o[1] += bf16_hi(rr.x); o[2] += bf16_lo(rr.y); o[3] += bf16_hi(rr.y);
+            o[4] += bf16_lo(rr.z); o[5] += bf16_hi(rr.z); o[6] += bf16_lo(rr.w); o[7] += bf16_hi(rr.w);
+          }
+#pragma unroll
+          for (int e = 0; e < 8; ++e) o[e] = apply_act(o[e], p.act);
+          *slot = make_uint4(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]), pack_bf16(o[6], o[7]));
+        }
+        fence_proxy_async_smem();                                  // generic-proxy writes -> visible to TMA
+        named_bar_sync(1, kEpiThreads);
+        if (leader) {
+          tma_store_4d(&tmOut.m[t.cls], stg, n0, t.x0, t.y0, t.b0);
+          bulk_commit();
+        }
+      }
+    }
+    if (leader) bulk_wait_all();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, kTmemCols); }
+}
+
+// ---- auxiliary bandwidth kernels -------------------------------------------------------------------
+// fp32 NCHW image -> bf16 space-to-depth [B, H/2, W/2 + 4, 16]; channel = (py*2+px)*4 + c (c==3 -> 0),
+// 2 zero columns of left padding and 2 of right padding (the stem's x padding is physical, its y padding
+// is TMA out-of-bounds fill).
+constexpr int kS2DPad = 4;
+__global__ void __launch_bounds__(256)
+preprocess_kernel(const float* __restrict__ img, int B, int H, int W, __nv_bfloat16* __restrict__ out) {
+  const int Hs = H / 2, Ws = W / 2, Wp = Ws + kS2DPad;
+  const long long total = static_cast<long long>(B) * Hs * Wp;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int xp = static_cast<int>(i % Wp);
+    const int ys = static_cast<int>((i / Wp) % Hs);
+    const int b  = static_cast<int>(i / (static_cast<long long>(Wp) * Hs));
+    const int xs = xp - 2;
+    uint4 lo = make_uint4(0, 0, 0, 0), hi = make_uint4(0, 0, 0, 0);
+    if (xs >= 0 && xs < Ws) {
+      float v[2][2][3];
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+#pragma unroll
+        for (int py = 0; py < 2; ++py) {
+          const float2 f = __ldg(reinterpret_cast<const float2*>(
+              img + ((static_cast<size_t>(b) * 3 + c) * H + (2 * ys + py)) * W + 2 * xs));
+          v[py][0][c] = f.x; v[py][1][c] = f.y;
+        }
+      lo = make_uint4(pack_bf16(v[0][0][0], v[0][0][1]), pack_bf16(v[0][0][2], 0.f),
+                      pack_bf16(v[0][1][0], v[0][1][1]), pack_bf16(v[0][1][2], 0.f));
+      hi = make_uint4(pack_bf16(v[1][0][0], v[1][0][1]), pack_bf16(v[1][0][2], 0.f),
+                      pack_bf16(v[1][1][0], v[1][1][1]), pack_bf16(v[1][1][2], 0.f));
+    }
+    uint4* o = reinterpret_cast<uint4*>(out + static_cast<size_t>(i) * 16);
+    o[0] = lo; o[1] = hi;
+  }
+}
+
+__device__ __forceinline__ uint32_t bf16x2_max(uint32_t a, uint32_t b) {
+  __nv_bfloat162 r = __hmax2(*reinterpret_cast<__nv_bfloat162*>(&a), *reinterpret_cast<__nv_bfloat162*>(&b));
+  return *reinterpret_cast<uint32_t*>(&r);
+}
+
+// MaxPool 3x3 s2 p1 on NHWC bf16, 8 channels (16 B) per thread
+__global__ void __launch_bounds__(256)
+maxpool_kernel(const __nv_bfloat16* __restrict__ x, int B, int H, int W, int C, __nv_bfloat16* __restrict__ y) {
+  const int Ho = (H + 2 - 3) / 2 + 1, Wo = (W + 2 - 3) / 2 + 1, Cv = C / 8;
+  const long long total = static_cast<long long>(B) * Ho * Wo * Cv;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int cv = static_cast<int>(i % Cv);
+    const int ox = static_cast<int>((i / Cv) % Wo);
+    const int oy = static_cast<int>((i / (static_cast<long long>(Cv) * Wo)) % Ho);
+    const int b  = static_cast<int>(i / (static_cast<long long>(Cv) * Wo * Ho));
+    const uint32_t ninf = 0xFF80FF80u;    // (-inf, -inf) in bf16
+    uint4 m = make_uint4(ninf, ninf, ninf, ninf);
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky) {
+      const int iy = 2 * oy - 1 + ky;
+      if (iy < 0 || iy >= H) continue;
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) {
+        const int ix = 2 * ox - 1 + kx;
+        if (ix < 0 || ix >= W) continue;
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(x + ((static_cast<size_t>(b) * H + iy) * W + ix) * C) + cv);
+        m.x = bf16x2_max(m.x, v.x); m.y = bf16x2_max(m.y, v.y); m.z = bf16x2_max(m.z, v.z); m.w = bf16x2_max(m.w, v.w);
+      }
+    }
+    reinterpret_cast<uint4*>(y + ((static_cast<size_t>(b) * Ho + oy) * Wo + ox) * C)[cv] = m;
+  }
+}
+
+// PyTorch-layout fp32 weight -> packed bf16 GEMM-B  [rows][Ktot]
+__global__ void __launch_bounds__(256)
+pack_weight_kernel(const float* __restrict__ w, int kind, int Cin, int Cout, long long total,
+                   __nv_bfloat16* __restrict__ out) {
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    float v = 0.f;
+    if (kind == HPE_CONV_1x1 || kind == HPE_CONV_FINAL) {
+      v = w[i];                                                        // [Cout][Cin]
+    } else if (kind == HPE_CONV_3x3) {
+      const int K = 9 * Cin, co = static_cast<int>(i / K), k = static_cast<int>(i % K);
+      const int tap = k / Cin, ci = k % Cin;
+      v = w[(static_cast<size_t>(co) * Cin + ci) * 9 + tap];           // [Cout][Cin][3][3]
+    } else if (kind == HPE_CONV_STEM7x7) {
+      const int co = static_cast<int>(i / 256), k = static_cast<int>(i % 256);
+      const int khp = k / 64, kwp = (k % 64) / 16, q = k % 16, py = q / 8, px = (q / 4) % 2, c = q % 4;
+      const int ky = 2 * khp + py - 1, kx = 2 * kwp + px - 1;
+      if (c < 3 && ky >= 0 && kx >= 0) v = w[((static_cast<size_t>(co) * 3 + c) * 7 + ky) * 7 + kx];   // [64][3][7][7]
+    } else {  // HPE_CONV_DECONV4: torch [Cin][Cout][4][4] -> [(cls*Cout + co)][(ty*2+tx)*Cin + ci]
+      const int K = 4 * Cin;
+      const int row = static_cast<int>(i / K), k = static_cast<int>(i % K);
+      const int cls = row / Cout, co = row % Cout, t = k / Cin, ci = k % Cin;
+      const int py = cls >> 1, px = cls & 1, ty = t >> 1, tx = t & 1;
+      const int ky = py ? (ty ? 0 : 2) : (ty ? 3 : 1);
+      const int kx = px ? (tx ? 0 : 2) : (tx ? 3 : 1);
+      v = w[((static_cast<size_t>(ci) * Cout + co) * 4 + ky) * 4 + kx];
+    }
+    out[i] = __float2bfloat16(v);
+  }
+}
+
+// ---- host side --------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+static int encode_map(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                      const uint32_t* box, const uint32_t* estrides, const char* what) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return fail(HPE_ECUDA, "cuTensorMapEncodeTiled entry point not available");
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), dims, strides_bytes, box, estrides,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return fail(HPE_ECUDA, "cuTensorMapEncodeTiled(%s) failed with CUresult %d (dims %llu,%llu,%llu,%llu box %u,%u,%u,%u)",
+                what, (int)r, (unsigned long long)dims[0], (unsigned long long)dims[1],
+                (unsigned long long)(rank > 2 ? dims[2] : 0), (unsigned long long)(rank > 3 ? dims[3] : 0),
+                box[0], box[1], rank > 2 ? box[2] : 0, rank > 3 ? box[3] : 0);
+  return HPE_OK;
+}
+
+}  // namespace hpe
+
+using namespace hpe;
+
+struct hpe_conv_plan {
+  hpe_conv_desc d;
+  ConvParams p;
+  int block_n, grid;
+  int Ho, Wo;            // real output size
+  size_t smem;
+  CUtensorMap tmA, tmW, tmRes;
+  OutMaps tmOut;
+  const void *x, *w, *res;
+  void* y;
+};
+
+static int desc_check(const hpe_conv_desc* d, const char* fn) {
+  HPE_CHECK_ARG(d, "%s: null desc", fn);
+  HPE_CHECK_ARG(d->kind >= HPE_CONV_1x1 && d->kind <= HPE_CONV_FINAL, "%s: bad kind %d", fn, d->kind);
+  HPE_CHECK_ARG(d->B > 0 && d->H > 0 && d->W > 0 && d->Cin > 0 && d->Cout > 0, "%s: non-positive size", fn);
+  if (d->kind == HPE_CONV_STEM7x7) {
+    if (d->Cin != 3 || d->Cout != 64 || (d->H % 2) || (d->W % 2))
+      return fail(HPE_EUNSUPPORTED, "%s: stem needs Cin=3, Cout=64, even H/W (got %d,%d,%dx%d)", fn, d->Cin, d->Cout, d->H, d->W);
+    return HPE_OK;
+  }
+  if (d->Cin % 64) return fail(HPE_EUNSUPPORTED, "%s: Cin=%d must be a multiple of 64", fn, d->Cin);
+  if (d->kind == HPE_CONV_FINAL) {
+    if (d->Cout > 256) return fail(HPE_EUNSUPPORTED, "%s: final conv supports at most 256 joints (got %d)", fn, d->Cout);
+    return HPE_OK;
+  }
+  if (d->Cout % 64) return fail(HPE_EUNSUPPORTED, "%s: Cout=%d must be a multiple of 64", fn, d->Cout);
+  if (d->kind == HPE_CONV_1x1 || d->kind == HPE_CONV_3x3) {
+    if (d->stride != 1 && d->stride != 2) return fail(HPE_EUNSUPPORTED, "%s: stride %d not in {1,2}", fn, d->stride);
+    if (d->stride == 2 && ((d->H % 2) || (d->W % 2))) return fail(HPE_EUNSUPPORTED, "%s: stride 2 needs even H/W", fn);
+  }
+  return HPE_OK;
+}
+
+static int pick_block_n(const hpe_conv_desc* d) {
+  if (d->kind == HPE_CONV_FINAL) return d->Cout <= 32 ? 32 : (d->Cout <= 64 ? 64 : (d->Cout <= 128 ? 128 : 256));
+  if (d->Cout % 256 == 0) return 256;
+  if (d->Cout % 128 == 0) return 128;
+  return 64;
+}
+
+extern "C" int hpe_conv_out_hw(const hpe_conv_desc* d, int* Ho, int* Wo) {
+  int rc = desc_check(d, "hpe_conv_out_hw");
+  if (rc) return rc;
+  HPE_CHECK_ARG(Ho && Wo, "hpe_conv_out_hw: null out");
+  switch (d->kind) {
+    case HPE_CONV_STEM7x7: *Ho = d->H / 2; *Wo = d->W / 2; break;
+    case HPE_CONV_DECONV4: *Ho = d->H * 2; *Wo = d->W * 2; break;
+    case HPE_CONV_FINAL:   *Ho = d->H; *Wo = d->W; break;
+    default:               *Ho = d->H / d->stride; *Wo = d->W / d->stride; break;
+  }
+  return HPE_OK;
+}
+
+static size_t ktot(const hpe_conv_desc* d) {
+  switch (d->kind) {
+    case HPE_CONV_3x3:     return (size_t)9 * d->Cin;
+    case HPE_CONV_STEM7x7: return 256;
+    case HPE_CONV_DECONV4: return (size_t)4 * d->Cin;
+    default:               return d->Cin;
+  }
+}
+static size_t wrows(const hpe_conv_desc* d) { return d->kind == HPE_CONV_DECONV4 ? (size_t)4 * d->Cout : d->Cout; }
+
+extern "C" size_t hpe_conv_packed_weight_elems(const hpe_conv_desc* d) {
+  if (desc_check(d, "hpe_conv_packed_weight_elems")) return 0;
+  return wrows(d) * ktot(d);
+}
+
+extern "C" int hpe_conv_pack_weight(const hpe_conv_desc* d, const float* w_torch, void* w_packed, void* stream) {
+  int rc = desc_check(d, "hpe_conv_pack_weight");
+  if (rc) return rc;
+  HPE_CHECK_ARG(w_torch && w_packed, "hpe_conv_pack_weight: null pointer");
+  const long long total = (long long)(wrows(d) * ktot(d));
+  const int grid = (int)((total + 255) / 256 > 4096 ? 4096 : (total + 255) / 256);
+  pack_weight_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(w_torch, d->kind, d->Cin, d->Cout, total,
+                                                            (__nv_bfloat16*)w_packed);
+  return launch_status("pack_weight_kernel");
+}
+
+// choose the (tw, th, nb) brick of 128 output pixels that minimises the number of tiles (ties: wider tw)
+static void pick_brick(int Wo, int Ho, int B, int max_tw, int* tw, int* th, int* nb) {
+  long long best = -1;
+  for (int a = 1; a <= 128; a <<= 1) {
+    if (a > max_tw) break;
+    for (int b = 1; a * b <= 128; b <<= 1) {
+      const int c = 128 / (a * b);
+      const long long tiles = (long long)((Wo + a - 1) / a) * ((Ho + b - 1) / b) * ((B + c - 1) / c);
+      if (best < 0 || tiles < best || (tiles == best && a > *tw)) { best = tiles; *tw = a; *th = b; *nb = c; }
+    }
+  }
+}
+
+template <int BN, int ST>
+static int set_smem_attr() {
+  HPE_CUDA_OK(cudaFuncSetAttribute(conv_gemm_kernel<BN, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   SmemLayout<BN, ST>::kDynamic));
+  return HPE_OK;
+}
+
+extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out) {
+  int rc = desc_check(d, "hpe_conv_plan_create");
+  if (rc) return rc;
+  HPE_CHECK_ARG(out, "hpe_conv_plan_create: null out");
+  rc = hpe_check_device();
+  if (rc) return rc;
+  hpe_conv_plan* pl = new hpe_conv_plan();
+  pl->d = *d;
+  hpe_conv_out_hw(d, &pl->Ho, &pl->Wo);
+  ConvParams& p = pl->p;
+  p.kind = d->kind;
+  p.in_stride = (d->kind == HPE_CONV_1x1 || d->kind == HPE_CONV_3x3) ? d->stride : 1;
+  p.taps = d->kind == HPE_CONV_3x3 ? 9 : (d->kind == HPE_CONV_1x1 || d->kind == HPE_CONV_FINAL ? 1 : 4);
+  p.kc_per_tap = d->kind == HPE_CONV_STEM7x7 ? 1 : d->Cin / 64;
+  p.n_classes = d->kind == HPE_CONV_DECONV4 ? 4 : 1;
+  // tile grid extent: deconv tiles walk the INPUT-resolution grid of one parity class
+  p.Ho = d->kind == HPE_CONV_DECONV4 ? d->H : pl->Ho;
+  p.Wo = d->kind == HPE_CONV_DECONV4 ? d->W : pl->Wo;
+  p.B = d->B; p.Cout = d->Cout;
+  p.act = d->act; p.has_res = d->has_residual ? 1 : 0;
+  int tw = 1, th = 1, nb = 128;
+  pick_brick(p.Wo, p.Ho, p.B, p.in_stride == 2 ? 128 : 256, &tw, &th, &nb);
+  p.tw = tw; p.th = th; p.nb = nb;
+  p.tiles_x = (p.Wo + tw - 1) / tw; p.tiles_y = (p.Ho + th - 1) / th; p.tiles_b = (p.B + nb - 1) / nb;
+  pl->block_n = pick_block_n(d);
+  p.n_tiles_n = d->kind == HPE_CONV_FINAL ? 1 : d->Cout / pl->block_n;
+  const long long nt = (long long)p.tiles_x * p.tiles_y * p.tiles_b * p.n_tiles_n * p.n_classes;
+  if (nt > 0x7fffffff) { delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: too many tiles"); }
+  p.num_tiles = (int)nt;
+  pl->grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
+  switch (pl->block_n) {
+    case 32:  rc = set_smem_attr<32, 6>();  pl->smem = SmemLayout<32, 6>::kDynamic; break;
+    case 64:  rc = set_smem_attr<64, 6>();  pl->smem = SmemLayout<64, 6>::kDynamic; break;
+    case 128: rc = set_smem_attr<128, 4>(); pl->smem = SmemLayout<128, 4>::kDynamic; break;
+    default:  rc = set_smem_attr<256, 3>(); pl->smem = SmemLayout<256, 3>::kDynamic; break;
+  }
+  if (rc) { delete pl; return rc; }
+  pl->x = pl->w = pl->res = nullptr; pl->y = nullptr;
+  *out = pl;
+  return HPE_OK;
+}
+
+extern "C" void hpe_conv_plan_destroy(hpe_conv_plan* plan) { delete plan; }
+
+static int encode_plan_maps(hpe_conv_plan* pl, const void* x, const void* w, const void* res, void* y) {
+  const hpe_conv_desc& d = pl->d;
+  const ConvParams& p = pl->p;
+  int rc;
+  const uint32_t ones[4] = {1, 1, 1, 1};
+  if (x != pl->x) {
+    HPE_CHECK_ARG(((uintptr_t)x & 15) == 0, "hpe_conv_run: x must be 16-byte aligned");
+    if (d.kind == HPE_CONV_STEM7x7) {
+      const uint64_t Hs = d.H / 2, Ws = d.W / 2, Wp = Ws + kS2DPad;
+      const uint64_t dims[4] = {64, Ws, Hs, (uint64_t)d.B};
+      const uint64_t str[3] = {32, Wp * 32, Hs * Wp * 32};           // overlapping 64-element windows, 16 el apart
+      const uint32_t box[4] = {64, (uint32_t)p.tw, (uint32_t)p.th, (uint32_t)p.nb};
+      rc = encode_map(&pl->tmA, x, 4, dims, str, box, ones, "stem A");
+    } else {
+      const uint64_t C = d.Cin;
+      const uint64_t dims[4] = {C, (uint64_t)d.W, (uint64_t)d.H, (uint64_t)d.B};
+      const uint64_t str[3] = {C * 2, (uint64_t)d.W * C * 2, (uint64_t)d.H * d.W * C * 2};
+      const uint32_t s = (uint32_t)p.in_stride;
+      const uint32_t box[4] = {64, (uint32_t)p.tw * s, (uint32_t)p.th * s, (uint32_t)p.nb};
+      const uint32_t es[4] = {1, s, s, 1};
+      rc = encode_map(&pl->tmA, x, 4, dims, str, box, es, "A");
+    }
+    if (rc) return rc;
+    pl->x = x;
+  }
+  if (w != pl->w) {
+    HPE_CHECK_ARG(((uintptr_t)w & 15) == 0, "hpe_conv_run: w must be 16-byte aligned");
+    const uint64_t K = ktot(&d), R = wrows(&d);
+    const uint64_t dims[2] = {K, R};
+    const uint64_t str[1] = {K * 2};
+    const uint32_t box[2] = {64, (uint32_t)pl->block_n};
+    rc = encode_map(&pl->tmW, w, 2, dims, str, box, ones, "W");
+    if (rc) return rc;
+    pl->w = w;
+  }
+  if (d.kind != HPE_CONV_FINAL && y != pl->y) {
+    HPE_CHECK_ARG(((uintptr_t)y & 15) == 0, "hpe_conv_run: y must be 16-byte aligned");
+    const uint64_t C = d.Cout;
+    const uint32_t box[4] = {64, (uint32_t)p.tw, (uint32_t)p.th, (uint32_t)p.nb};
+    if (d.kind == HPE_CONV_DECONV4) {
+      const uint64_t Wo = pl->Wo, Ho = pl->Ho;
+      for (int cls = 0; cls < 4; ++cls) {
+        const int py = cls >> 1, px = cls & 1;
+        const char* base = (const char*)y + ((size_t)py * Wo + px) * C * 2;
+        const uint64_t dims[4] = {C, (uint64_t)d.W, (uint64_t)d.H, (uint64_t)d.B};
+        const uint64_t str[3] = {2 * C * 2, 2 * Wo * C * 2, Ho * Wo * C * 2};
+        rc = encode_map(&pl->tmOut.m[cls], base, 4, dims, str, box, ones, "deconv out");
+        if (rc) return rc;
+      }
+    } else {
+      const uint64_t dims[4] = {C, (uint64_t)pl->Wo, (uint64_t)pl->Ho, (uint64_t)d.B};
+      const uint64_t str[3] = {C * 2, (uint64_t)pl->Wo * C * 2, (uint64_t)pl->Ho * pl->Wo * C * 2};
+      rc = encode_map(&pl->tmOut.m[0], y, 4, dims, str, box, ones, "out");
+      if (rc) return rc;
+      pl->tmOut.m[1] = pl->tmOut.m[2] = pl->tmOut.m[3] = pl->tmOut.m[0];
+    }
+    pl->y = y;
+  }
+  if (p.has_res && res != pl->res) {
+    HPE_CHECK_ARG(res && ((uintptr_t)res & 15) == 0, "hpe_conv_run: residual must be non-null and 16-byte aligned");
+    const uint64_t C = d.Cout;
+    const uint64_t dims[4] = {C, (uint64_t)pl->Wo, (uint64_t)pl->Ho, (uint64_t)d.B};
+    const uint64_t str[3] = {C * 2, (uint64_t)pl->Wo * C * 2, (uint64_t)pl->Ho * pl->Wo * C * 2};
+    const uint32_t box[4] = {64, (uint32_t)p.tw, (uint32_t)p.th, (uint32_t)p.nb};
+    rc = encode_map(&pl->tmRes, res, 4, dims, str, box, ones, "residual");
+    if (rc) return rc;
+    pl->res = res;
+  }
+  return HPE_OK;
+}
+
+extern "C" int hpe_conv_run(hpe_conv_plan* pl, const void* x, const void* w_packed, const float* scale,
+                            const float* shift, const void* residual, void* y, void* stream) {
+  HPE_CHECK_ARG(pl && x && w_packed && scale && shift && y, "hpe_conv_run: null pointer");
+  HPE_CHECK_ARG((((uintptr_t)scale | (uintptr_t)shift) & 15) == 0, "hpe_conv_run: scale/shift must be 16-byte aligned");
+  if (pl->d.kind == HPE_CONV_DECONV4 && pl->p.has_res) return fail(HPE_EUNSUPPORTED, "hpe_conv_run: deconv has no residual input");
+  int rc = encode_plan_maps(pl, x, w_packed, residual, y);
+  if (rc) return rc;
+  ConvParams p = pl->p;
+  p.scale = scale; p.shift = shift;
+  p.hm_out = pl->d.kind == HPE_CONV_FINAL ? (float*)y : nullptr;
+  if (!p.has_res) pl->tmRes = pl->tmA;      // unused, but must be a valid object to copy
+  if (pl->d.kind == HPE_CONV_FINAL) for (int c = 0; c < 4; ++c) pl->tmOut.m[c] = pl->tmA;
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (pl->block_n) {
+    case 32:  conv_gemm_kernel<32, 6><<<pl->grid, kConvThreads, pl->smem, st>>>(pl->tmA, pl->tmW, pl->tmOut, pl->tmRes, p); break;
+    case 64:  conv_gemm_kernel<64, 6><<<pl->grid, kConvThreads, pl->smem, st>>>(pl->tmA, pl->tmW, pl->tmOut, pl->tmRes, p); break;
+    case 128: conv_gemm_kernel<128, 4><<<pl->grid, kConvThreads, pl->smem, st>>>(pl->tmA, pl->tmW, pl->tmOut, pl->tmRes, p); break;
+    default:  conv_gemm_kernel<256, 3><<<pl->grid, kConvThreads, pl->smem, st>>>(pl->tmA, pl->tmW, pl->tmOut, pl->tmRes, p); break;
+  }
+  return launch_status("conv_gemm_kernel");
+}
+
+extern "C" size_t hpe_preprocess_out_elems(int B, int H, int W) {
+  if (B <= 0 || H <= 0 || W <= 0 || (H % 2) || (W % 2)) return 0;
+  return (size_t)B * (H / 2) * (W / 2 + kS2DPad) * 16;
+}
+
+extern "C" int hpe_preprocess(const float* img, int B, int H, int W, void* out, void* stream) {
+  HPE_CHECK_ARG(img && out, "hpe_preprocess: null pointer");
+  HPE_CHECK_ARG(B > 0 && H > 0 && W > 0 && H % 2 == 0 && W % 2 == 0, "hpe_preprocess: H and W must be positive and even");
+  HPE_CHECK_ARG((((uintptr_t)img & 7) | ((uintptr_t)out & 15)) == 0, "hpe_preprocess: misaligned pointer");
+  const long long total = (long long)B * (H / 2) * (W / 2 + kS2DPad);
+  const int grid = (int)((total + 255) / 256 > (long long)num_sms() * 16 ? (long long)num_sms() * 16 : (total + 255) / 256);
+  preprocess_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(img, B, H, W, (__nv_bfloat16*)out);
+  return launch_status("preprocess_kernel");
+}
+
+extern "C" int hpe_maxpool3x3s2(const void* x, int B, int H, int W, int C, void* y, void* stream) {
+  HPE_CHECK_ARG(x && y, "hpe_maxpool3x3s2: null pointer");
+  HPE_CHECK_ARG(B > 0 && H > 0 && W > 0 && C > 0 && C % 8 == 0, "hpe_maxpool3x3s2: C must be a positive multiple of 8");
+  HPE_CHECK_ARG((((uintptr_t)x | (uintptr_t)y) & 15) == 0, "hpe_maxpool3x3s2: misaligned pointer");
+  const int Ho = (H - 1) / 2 + 1, Wo = (W - 1) / 2 + 1;
+  const long long total = (long long)B * Ho * Wo * (C / 8);
+  const int grid = (int)((total + 255) / 256 > (long long)num_sms() * 16 ? (long long)num_sms() * 16 : (total + 255) / 256);
+  maxpool_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, B, H, W, C, (__nv_bfloat16*)y);
+  return launch_status("maxpool_kernel");
+}

@@ -1,0 +1,270 @@
+"""Model registry + the top-down heatmap model behind the reference's constructor signature.
+
+Boundary being mirrored:
+  * ``models.__all__`` name table + ``getattr(models, cfg.model.name)(nkpts, backbone, pretrained)``
+    (/root/reference/HPE/models/__init__.py:4-12, HPE/core/builder.py:15-19);
+  * ``DeepPose(num_joints, backbone='resnet50', pretrained=True)``
+    (HPE/models/reference/bottom_up/regression/models/DeepPose.py:4-10);
+  * ``output = model(data)`` with ``data`` fp32 NCHW on the device (HPE/engine/trainer.py:87-90).
+
+The parameter tree uses the timm key names (``backbone.conv1.weight``, ``backbone.layer1.0.bn1.*``,
+``backbone.layer2.0.downsample.{0,1}.*`` ...) so reference checkpoints load with ``load_state_dict``;
+the ``fc`` regression head of DeepPose is replaced by the App. A.1 deconv heatmap head
+(``deconv_layers.{0,3,6}`` / ``.{1,4,7}`` / ``final_layer``).  The ``torch.nn`` modules below are
+parameter containers only: the forward pass never calls them -- it runs the sm_100a kernels of
+libhpe_b200.so through ``ConvLayer`` plans and raises if that library is unavailable.
+"""
+from __future__ import annotations
+
+import os
+
+import torch
+import torch.nn as nn
+
+from . import _lib
+from .conv import (ACT_NONE, ACT_RELU, CONV_1x1, CONV_3x3, CONV_DECONV4, CONV_FINAL, CONV_STEM7x7, ConvLayer, fold_bn,
+                   maxpool3x3s2, preprocess)
+
+__all__ = ("DeepPose", "HeatmapPose")
+
+_LAYERS = (3, 4, 6, 3)
+_PLANES = (64, 128, 256, 512)
+
+
+class _BottleneckParams(nn.Module):
+    def __init__(self, inplanes, planes, stride, downsample):
+        super().__init__()
+        self.conv1 = nn.Conv2d(inplanes, planes, 1, bias=False)
+        self.bn1 = nn.BatchNorm2d(planes)
+        self.conv2 = nn.Conv2d(planes, planes, 3, stride=stride, padding=1, bias=False)
+        self.bn2 = nn.BatchNorm2d(planes)
+        self.conv3 = nn.Conv2d(planes, planes * 4, 1, bias=False)
+        self.bn3 = nn.BatchNorm2d(planes * 4)
+        self.downsample = downsample
+        self.stride = stride
+
+
+class _ResNet50Params(nn.Module):
+    """Parameter container with timm ResNet-50 names/shapes/init (resnet.py:554-621, 1548-1552)."""
+
+    def __init__(self):
+        super().__init__()
+        self.conv1 = nn.Conv2d(3, 64, 7, stride=2, padding=3, bias=False)
+        self.bn1 = nn.BatchNorm2d(64)
+        inplanes = 64
+        for i, (n, p) in enumerate(zip(_LAYERS, _PLANES)):
+            blocks = []
+            for j in range(n):
+                s = 2 if (i > 0 and j == 0) else 1
+                ds = None
+                if j == 0:
+                    ds = nn.Sequential(nn.Conv2d(inplanes, p * 4, 1, stride=s, bias=False), nn.BatchNorm2d(p * 4))
+                blocks.append(_BottleneckParams(inplanes, p, s, ds))
+                inplanes = p * 4
+            setattr(self, f"layer{i + 1}", nn.Sequential(*blocks))
+        for m in self.modules():
+            if isinstance(m, nn.Conv2d):
+                nn.init.kaiming_normal_(m.weight, mode="fan_out", nonlinearity="relu")
+        for m in self.modules():
+            if isinstance(m, _BottleneckParams):
+                nn.init.zeros_(m.bn3.weight)           # timm zero_init_last
+
+
+class HeatmapPose(nn.Module):
+    """``Model(nkpts, backbone, pretrained)`` -> heatmaps ``[B, K, H/4, W/4]`` (fp32) for fp32 NCHW input."""
+
+    def __init__(self, num_joints=17, backbone="resnet50", pretrained=True):
+        super().__init__()
+        if backbone != "resnet50":
+            raise ValueError(f"backbone '{backbone}' not built: this path covers the config-default 'resnet50'")
+        self.njoints = int(num_joints)
+        self.backbone = _ResNet50Params()
+        layers, c = [], 2048
+        for _ in range(3):
+            layers += [nn.ConvTranspose2d(c, 256, 4, stride=2, padding=1, output_padding=0, bias=False),
+                       nn.BatchNorm2d(256), nn.ReLU(inplace=True)]
+            c = 256
+        self.deconv_layers = nn.Sequential(*layers)
+        self.final_layer = nn.Conv2d(256, self.njoints, 1, bias=True)
+        for m in self.deconv_layers:
+            if isinstance(m, nn.ConvTranspose2d):
+                nn.init.normal_(m.weight, std=0.001)
+        nn.init.normal_(self.final_layer.weight, std=0.001)
+        nn.init.zeros_(self.final_layer.bias)
+        self._plans = {}
+        self._weights_version = 0
+        if pretrained:
+            path = pretrained if isinstance(pretrained, str) else os.environ.get("HPE_B200_PRETRAINED", "")
+            if not path:
+                raise RuntimeError("pretrained=True needs a local timm-format ResNet-50 checkpoint: pass its path as "
+                                   "`pretrained` or set HPE_B200_PRETRAINED (there is no network download path)")
+            self.load_backbone(path)
+
+    # ---- checkpoints -------------------------------------------------------------------------------
+    def load_backbone(self, path):
+        sd = torch.load(path, map_location="cpu")
+        sd = sd.get("model_state", sd.get("state_dict", sd))
+        sd = {k[len("backbone."):] if k.startswith("backbone.") else k: v for k, v in sd.items()}
+        sd = {k: v for k, v in sd.items() if not k.startswith("fc.")}
+        self.backbone.load_state_dict(sd, strict=True)
+        self._weights_version += 1
+
+    def load_state_dict(self, state_dict, strict=True, **kw):
+        """Accepts reference DeepPose checkpoints: ``backbone.fc.*`` (the regression head) is ignored."""
+        sd = {k: v for k, v in state_dict.items() if not k.startswith("backbone.fc.")}
+        has_head = any(k.startswith("deconv_layers.") for k in sd)
+        out = super().load_state_dict(sd, strict=strict and has_head, **kw)
+        self._weights_version += 1
+        return out
+
+    def refresh(self):
+        """Re-pack weights / re-fold BN after parameters were modified in place."""
+        self._weights_version += 1
+
+    def _apply(self, fn, *a, **kw):
+        self._weights_version += 1
+        self._plans = {}
+        return super()._apply(fn, *a, **kw)
+
+    # ---- forward -----------------------------------------------------------------------------------
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if self.training:
+            raise NotImplementedError("HeatmapPose: the training forward/backward through the conv stack is not built "
+                                      "yet (inference kernels only); call model.eval().  The loss stage "
+                                      "(JointsMSELoss) does provide dL/dheatmap.")
+        if x.dim() != 4 or x.shape[1] != 3:
+            raise ValueError(f"expected [B,3,H,W] input, got {tuple(x.shape)}")
+        if not x.is_cuda:
+            raise RuntimeError("libhpe_b200 has no CPU path: input must live on a CUDA (sm_100a) device")
+        key = (tuple(x.shape), x.device.index)
+        plan = self._plans.get(key)
+        if plan is None:
+            plan = _ForwardPlan(self, x.shape[0], x.shape[2], x.shape[3], x.device)
+            self._plans[key] = plan
+        if plan.weights_version != self._weights_version:
+            plan.load_weights(self)
+        return plan.run(x.float().contiguous())
+
+    def forward_features(self, x):
+        """``[B, 2048, H/32, W/32]`` fp32 NCHW view of the trunk output (timm ``forward_features`` analogue)."""
+        self.forward(x)
+        plan = self._plans[(tuple(x.shape), x.device.index)]
+        return plan.features.float().permute(0, 3, 1, 2)
+
+
+DeepPose = HeatmapPose     # config-default name (HPE/configs/default.py:13): same constructor, heatmap output
+
+
+class _ForwardPlan:
+    """All ConvLayer plans + activation buffers for one (B, H, W); optionally replayed as a CUDA graph."""
+
+    def __init__(self, model: HeatmapPose, B, H, W, device):
+        if H % 32 or W % 32:
+            raise ValueError(f"input {H}x{W} must be a multiple of 32")
+        self.B, self.H, self.W, self.device = B, H, W, device
+        self.ops = []            # (layer, src_key, res_key, dst_key)
+        self.bufs = {}
+        self.named = {}          # module path -> ConvLayer (for load_weights)
+        K = model.njoints
+        dev = device
+
+        def buf(key, shape, dtype=torch.bfloat16):
+            self.bufs[key] = torch.empty(shape, dtype=dtype, device=dev)
+            return key
+
+        def add(name, layer, src, dst, res=None):
+            self.named[name] = layer
+            buf(dst, layer.out_shape(), torch.float32 if layer.kind == CONV_FINAL else torch.bfloat16)
+            self.ops.append((layer, src, res, dst))
+
+        self.s2d = preprocess(torch.zeros(B, 3, H, W, device=dev))
+        add("backbone.conv1", ConvLayer(CONV_STEM7x7, B, H, W, 3, 64, 2, ACT_RELU, False, dev), "s2d", "stem")
+        h, w = H // 4, W // 4
+        buf("pool", (B, h, w, 64))
+        cur, cin = "pool", 64
+        for i, (n, p) in enumerate(zip(_LAYERS, _PLANES)):
+            for j in range(n):
+                s = 2 if (i > 0 and j == 0) else 1
+                pre = f"backbone.layer{i + 1}.{j}"
+                add(pre + ".conv1", ConvLayer(CONV_1x1, B, h, w, cin, p, 1, ACT_RELU, False, dev), cur, pre + ".t1")
+                add(pre + ".conv2", ConvLayer(CONV_3x3, B, h, w, p, p, s, ACT_RELU, False, dev), pre + ".t1", pre + ".t2")
+                sc = cur
+                if j == 0:
+                    add(pre + ".downsample.0", ConvLayer(CONV_1x1, B, h, w, cin, 4 * p, s, ACT_NONE, False, dev), cur, pre + ".sc")
+                    sc = pre + ".sc"
+                h, w = h // s, w // s
+                add(pre + ".conv3", ConvLayer(CONV_1x1, B, h, w, p, 4 * p, 1, ACT_RELU, True, dev), pre + ".t2", pre + ".out", sc)
+                cur, cin = pre + ".out", 4 * p
+        self.features_key = cur
+        for d, idx in enumerate((0, 3, 6)):
+            add(f"deconv_layers.{idx}", ConvLayer(CONV_DECONV4, B, h, w, cin, 256, 2, ACT_RELU, False, dev), cur, f"deconv{d}")
+            cur, cin, h, w = f"deconv{d}", 256, 2 * h, 2 * w
+        add("final_layer", ConvLayer(CONV_FINAL, B, h, w, 256, K, 1, ACT_NONE, False, dev), cur, "heatmaps")
+        self.bufs["s2d"] = self.s2d
+        self.weights_version = -1
+        self.graph = None
+        self.n_launches = len(self.ops) + 2          # + preprocess + maxpool
+
+    @property
+    def features(self):
+        return self.bufs[self.features_key]
+
+    @property
+    def heatmaps(self):
+        return self.bufs["heatmaps"]
+
+    @torch.no_grad()
+    def load_weights(self, model: HeatmapPose):
+        mods = dict(model.named_modules())
+        for name, layer in self.named.items():
+            m = mods[name]
+            if name == "final_layer":
+                layer.load(m.weight, torch.ones(m.out_channels), m.bias)
+                continue
+            if name.startswith("deconv_layers."):
+                bn = mods[f"deconv_layers.{int(name.split('.')[1]) + 1}"]
+            elif name.endswith("downsample.0"):
+                bn = mods[name[:-1] + "1"]
+            else:
+                bn = mods[name.replace("conv", "bn")]
+            scale, shift = fold_bn(bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps)
+            layer.load(m.weight, scale, shift)
+        self.weights_version = model._weights_version
+        self.graph = None         # packed buffers are updated in place, but be conservative
+
+    def _launch_all(self):
+        b = self.bufs
+        for layer, src, res, dst in self.ops:
+            layer(b[src], b[res] if res else None, b[dst])
+            if dst == "stem":
+                maxpool3x3s2(b["stem"], b["pool"])
+
+    def run(self, x: torch.Tensor) -> torch.Tensor:
+        preprocess(x, self.s2d)
+        use_graph = os.environ.get("HPE_B200_CUDA_GRAPH", "1") != "0"
+        if not use_graph:
+            self._launch_all()
+            return self.heatmaps
+        if self.graph is None:
+            self._launch_all()                       # warm-up: encodes the TMA descriptors once
+            torch.cuda.synchronize(self.device)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._launch_all()
+            self.graph = g
+        self.graph.replay()
+        return self.heatmaps
+
+
+def build_model(cfg):
+    """``Builder.model()`` (HPE/core/builder.py:15-24): registry lookup, positional constructor call, optional
+    checkpoint.  ``''``/``None`` checkpoint = none (the reference would try ``torch.load('')``)."""
+    import sys
+    registry = sys.modules[__name__]
+    name = cfg.model.name
+    assert name in __all__, f'Unknown model : "{name}"\n        Available models : {__all__}'
+    model = getattr(registry, name)(cfg.model.nkpts, cfg.model.backbone, cfg.model.pretrained)
+    if cfg.model.checkpoint:
+        sd = torch.load(cfg.model.checkpoint, map_location="cpu")
+        model.load_state_dict(sd.get("model_state", sd))
+    return model

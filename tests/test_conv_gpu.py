@@ -1,0 +1,133 @@
+"""GPU parity of every conv-kernel flavour (through the C ABI) against a plain PyTorch fp32 reference of the same
+op evaluated on the same bf16-rounded inputs/weights.  Tolerance: one bf16 rounding of the output
+(|err| <= 2^-8 |ref| + 2e-3 * max|ref| covers the fp32 accumulation-order difference)."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def r16(t):
+    return t.to(torch.bfloat16).to(torch.float32)
+
+
+def check(out, ref, what):
+    out = out.float().cpu()
+    tol = ref.abs() * 2 ** -8 + 2e-3 * ref.abs().max()
+    bad = (out - ref).abs() > tol
+    assert not bad.any(), f"{what}: {int(bad.sum())}/{bad.numel()} outside tolerance, max err {(out - ref).abs().max():.4g} (ref max {ref.abs().max():.4g})"
+
+
+def nhwc(t):      # NCHW fp32 cpu -> NHWC bf16 cuda
+    return t.permute(0, 2, 3, 1).contiguous().to(torch.bfloat16).cuda()
+
+
+def nchw(t):      # NHWC cuda -> NCHW fp32 cpu
+    return t.float().cpu().permute(0, 3, 1, 2)
+
+
+def make(g, *shape, s=1.0):
+    return r16(torch.randn(*shape, generator=g) * s)
+
+
+@pytest.mark.parametrize("B,H,W,Cin,Cout,stride,act,res", [
+    (8, 16, 12, 64, 256, 1, 1, True),      # BLOCK_N=256, residual + ReLU (bottleneck conv3)
+    (8, 16, 12, 256, 64, 1, 1, False),     # BLOCK_N=64  (bottleneck conv1)
+    (4, 16, 12, 512, 128, 1, 1, False),    # BLOCK_N=128, 8 k-blocks > ring depth
+    (4, 32, 24, 256, 512, 2, 0, False),    # stride-2 downsample, no activation
+    (3, 10, 7, 64, 64, 1, 2, False),       # ragged tiles + SiLU (ConvBlock act)
+    (2, 8, 6, 1024, 2048, 1, 1, True),     # many N tiles, many k-blocks
+])
+def test_conv1x1(hpe, cuda_dev, B, H, W, Cin, Cout, stride, act, res):
+    from importlib import import_module
+    conv = import_module("2d-human-pose-estimation_b200.conv")
+    g = torch.Generator().manual_seed(1)
+    x = make(g, B, Cin, H, W); w = make(g, Cout, Cin, 1, 1, s=Cin ** -0.5)
+    scale = torch.rand(Cout, generator=g) + 0.5; shift = torch.randn(Cout, generator=g) * 0.1
+    Ho, Wo = H // stride, W // stride
+    rs = make(g, B, Cout, Ho, Wo) if res else None
+    ref = F.conv2d(x, w, stride=stride) * scale[None, :, None, None] + shift[None, :, None, None]
+    if res:
+        ref = ref + rs
+    ref = torch.relu(ref) if act == 1 else (F.silu(ref) if act == 2 else ref)
+    layer = conv.ConvLayer(conv.CONV_1x1, B, H, W, Cin, Cout, stride, act, res).load(w, scale, shift)
+    y = layer(nhwc(x), nhwc(rs) if res else None)
+    torch.cuda.synchronize()
+    assert tuple(y.shape) == (B, Ho, Wo, Cout)
+    check(nchw(y), ref, "conv1x1")
+
+
+@pytest.mark.parametrize("B,H,W,C,Cout,stride", [
+    (4, 16, 12, 64, 64, 1), (4, 16, 12, 128, 128, 1), (4, 32, 24, 128, 128, 2), (2, 16, 12, 256, 256, 2),
+    (3, 10, 6, 64, 64, 1), (2, 8, 6, 512, 512, 1),
+])
+def test_conv3x3(hpe, cuda_dev, B, H, W, C, Cout, stride):
+    from importlib import import_module
+    conv = import_module("2d-human-pose-estimation_b200.conv")
+    g = torch.Generator().manual_seed(2)
+    x = make(g, B, C, H, W); w = make(g, Cout, C, 3, 3, s=(9 * C) ** -0.5)
+    scale = torch.rand(Cout, generator=g) + 0.5; shift = torch.randn(Cout, generator=g) * 0.1
+    ref = torch.relu(F.conv2d(x, w, stride=stride, padding=1) * scale[None, :, None, None] + shift[None, :, None, None])
+    layer = conv.ConvLayer(conv.CONV_3x3, B, H, W, C, Cout, stride, 1, False).load(w, scale, shift)
+    y = layer(nhwc(x))
+    torch.cuda.synchronize()
+    check(nchw(y), ref, "conv3x3")
+
+
+@pytest.mark.parametrize("B,H,W", [(4, 64, 48), (2, 256, 192), (3, 36, 20)])
+def test_stem_and_maxpool(hpe, cuda_dev, B, H, W):
+    from importlib import import_module
+    conv = import_module("2d-human-pose-estimation_b200.conv")
+    g = torch.Generator().manual_seed(3)
+    img = torch.rand(B, 3, H, W, generator=g)
+    w = make(g, 64, 3, 7, 7, s=0.1)
+    scale = torch.rand(64, generator=g) + 0.5; shift = torch.randn(64, generator=g) * 0.1
+    ref = torch.relu(F.conv2d(r16(img), w, stride=2, padding=3) * scale[None, :, None, None] + shift[None, :, None, None])
+    s2d = conv.preprocess(img.cuda())
+    layer = conv.ConvLayer(conv.CONV_STEM7x7, B, H, W, 3, 64, 2, 1, False).load(w, scale, shift)
+    y = layer(s2d)
+    torch.cuda.synchronize()
+    check(nchw(y), ref, "stem")
+    p = conv.maxpool3x3s2(y)
+    pref = F.max_pool2d(nchw(y), 3, 2, 1)
+    assert torch.equal(nchw(p), pref)
+
+
+@pytest.mark.parametrize("B,H,W,Cin", [(4, 8, 6, 256), (2, 8, 6, 2048), (3, 5, 7, 256), (2, 32, 24, 256)])
+def test_deconv4x4s2(hpe, cuda_dev, B, H, W, Cin):
+    from importlib import import_module
+    conv = import_module("2d-human-pose-estimation_b200.conv")
+    g = torch.Generator().manual_seed(4)
+    x = make(g, B, Cin, H, W); w = make(g, Cin, 256, 4, 4, s=(4 * Cin) ** -0.5)
+    scale = torch.rand(256, generator=g) + 0.5; shift = torch.randn(256, generator=g) * 0.1
+    ref = torch.relu(F.conv_transpose2d(x, w, stride=2, padding=1) * scale[None, :, None, None] + shift[None, :, None, None])
+    layer = conv.ConvLayer(conv.CONV_DECONV4, B, H, W, Cin, 256, 2, 1, False).load(w, scale, shift)
+    y = layer(nhwc(x))
+    torch.cuda.synchronize()
+    assert tuple(y.shape) == (B, 2 * H, 2 * W, 256)
+    check(nchw(y), ref, "deconv")
+
+
+@pytest.mark.parametrize("B,H,W,K", [(4, 64, 48, 17), (2, 64, 48, 133), (3, 10, 7, 17), (2, 96, 72, 17)])
+def test_final_1x1_heatmaps(hpe, cuda_dev, B, H, W, K):
+    from importlib import import_module
+    conv = import_module("2d-human-pose-estimation_b200.conv")
+    g = torch.Generator().manual_seed(5)
+    x = make(g, B, 256, H, W); w = make(g, K, 256, 1, 1, s=1 / 16)
+    bias = torch.randn(K, generator=g) * 0.1
+    ref = F.conv2d(x, w, bias)
+    layer = conv.ConvLayer(conv.CONV_FINAL, B, H, W, 256, K, 1, 0, False).load(w, torch.ones(K), bias)
+    y = layer(nhwc(x))
+    torch.cuda.synchronize()
+    assert tuple(y.shape) == (B, K, H, W) and y.dtype == torch.float32
+    assert (y.cpu() - ref).abs().max() <= 1e-4 * ref.abs().max() + 1e-5     # fp32 out: only accumulation order differs
+
+
+def test_conv_rejects_unsupported(hpe, cuda_dev):
+    from importlib import import_module
+    conv = import_module("2d-human-pose-estimation_b200.conv")
+    with pytest.raises(RuntimeError, match="multiple of 64"):
+        conv.ConvLayer(conv.CONV_1x1, 1, 8, 8, 48, 64)
+    with pytest.raises(RuntimeError, match="stride"):
+        conv.ConvLayer(conv.CONV_3x3, 1, 8, 8, 64, 64, stride=3)

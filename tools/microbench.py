@@ -1,0 +1,67 @@
+"""Kernel-level micro-benchmarks (CUDA events, inputs larger than L2 or L2 flushed) -- development aid.
+    python tools/microbench.py decode|loss
+"""
+import json
+import sys
+import os
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import hpe_b200 as hpe  # noqa: E402
+
+PEAK = 6468.9
+try:
+    PEAK = json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")))["hbm_gbs"]
+except Exception:
+    pass
+
+
+def timeit(fn, iters=20, warm=3, flush=None):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(iters):
+        if flush is not None:
+            flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fn(); e1.record(); torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    ts.sort()
+    return ts[len(ts) // 2], ts[0]
+
+
+def decode():
+    dev = torch.device("cuda:0")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    for dtype in (torch.float32, torch.bfloat16):
+        for (B, K, H, W) in [(256, 17, 64, 48), (1024, 17, 64, 48), (16384, 17, 64, 48), (65536, 17, 64, 48),
+                             (4096, 17, 96, 72), (1024, 133, 64, 48), (1024, 133, 128, 96)]:
+            hm = torch.rand(B, K, H, W, device=dev).to(dtype)
+            M = torch.rand(B, 2, 3, device=dev)
+            med, best = timeit(lambda: hpe.get_final_preds_affine(hm, M, return_idx=True), flush=flush)
+            nbytes = hm.numel() * hm.element_size() + B * 24 + B * K * 16
+            print(f"decode {str(dtype)[6:]:9s} B={B:6d} K={K:3d} {H}x{W}: median {med*1e3:8.1f} us  best {best*1e3:8.1f} us "
+                  f"-> {nbytes/med/1e6:7.1f} GB/s ({nbytes/med/1e6/PEAK*100:5.1f}% of measured {PEAK})", flush=True)
+            del hm
+
+
+def loss():
+    dev = torch.device("cuda:0")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    crit = hpe.JointsMSELoss()
+    for dtype in (torch.float32, torch.bfloat16):
+        for (B, K, H, W) in [(256, 17, 64, 48), (4096, 17, 64, 48), (16384, 17, 64, 48)]:
+            pred = torch.rand(B, K, H, W, device=dev).to(dtype)
+            joints = torch.rand(B, K, 3, device=dev) * torch.tensor([192., 256., 1.], device=dev) + torch.tensor([0., 0., .5], device=dev)
+            med, best = timeit(lambda: crit(pred, joints, None), flush=flush)
+            nbytes = pred.numel() * pred.element_size() + joints.numel() * 4
+            print(f"loss-fwd {str(dtype)[6:]:9s} B={B:6d}: median {med*1e3:8.1f} us -> {nbytes/med/1e6:7.1f} GB/s ({nbytes/med/1e6/PEAK*100:5.1f}%)", flush=True)
+            pg = pred.clone().requires_grad_(True)
+            med, best = timeit(lambda: crit(pg, joints, None), flush=flush)
+            print(f"loss-fwd+bwd {str(dtype)[6:]:9s} B={B:6d}: median {med*1e3:8.1f} us -> {2*nbytes/med/1e6:7.1f} GB/s ({2*nbytes/med/1e6/PEAK*100:5.1f}%)", flush=True)
+
+
+if __name__ == "__main__":
+    {"decode": decode, "loss": loss}[sys.argv[1]]()
