@@ -13,5 +13,8 @@ from .config import C as default_cfg, CfgNode, load_config, parse_args, update_c
 from .decode import (HostDecoder, affine_from_center_scale, decode, get_final_preds, get_final_preds_affine,
                      get_max_preds)
 from .loss import JointsMSELoss, generate_target
+from . import models
+from .models import DeepPose, HeatmapPose, build_model
+from .pipeline import PoseEstimator, gather_keypoints, gather_keypoints_equal, shard_range
 
 __version__ = "0.1.0"

@@ -1,0 +1,113 @@
+"""GPU parity of the whole forward (preprocess -> stem -> maxpool -> 16 bottlenecks -> 3 deconvs -> final 1x1)
+against the CPU oracle with identical weights, then decode on the produced heatmaps.
+
+Tolerances.  The synthetic model is normalised so that heatmaps live in [-1,1] like a trained net's
+(oracle.resnet_ref.build_synthetic(normalize=True)).  north_star's example figure (max-abs 1e-2 in bf16) is not
+reachable by ANY bf16 evaluation of this random-init 53-layer net: the CPU oracle evaluated with bf16 weights and
+bf16 stored activations (fp32 accumulate) itself differs from the fp32 oracle by ~1.5e-2 max-abs (printed below,
+measured on every run), and two bf16 evaluations with different accumulation order differ from each other by the
+same amount.  Stated tolerances on the normalised scale:
+  * max-abs <= 3e-2 and RMS <= 5e-3 vs the fp32 oracle, and max-abs no worse than 2x the CPU bf16 emulation's own
+    deviation from fp32 (+5e-3) -- i.e. the kernels add no error beyond the bf16 noise floor;
+  * the per-layer tests (tests/test_conv_gpu.py) hold every kernel flavour to ONE bf16 rounding of the output;
+  * argmax bit-exact on the SAME tensor; keypoints <= 0.05 px on the same tensor; end-to-end argmax only where
+    the top-2 margin exceeds the heatmap tolerance."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import heatmap_ref as hr
+from oracle import resnet_ref as rr
+
+pytestmark = pytest.mark.gpu
+HM_TOL_MAXABS = 3e-2      # normalised heatmaps, vs fp32 and vs bf16-emulating oracle
+HM_TOL_RMS = 5e-3
+
+
+@pytest.fixture(scope="module")
+def pair(hpe, cuda_dev):
+    from importlib import import_module
+    models = import_module("2d-human-pose-estimation_b200.models")
+    ref = rr.build_synthetic(17, seed=0, normalize=True)
+    m = models.HeatmapPose(17, "resnet50", pretrained=False)
+    missing, unexpected = m.load_state_dict(ref.state_dict())
+    assert not missing and not unexpected            # state_dict keys are timm/oracle compatible
+    return m.to(cuda_dev).eval(), ref
+
+
+@pytest.mark.parametrize("B,H,W", [(4, 256, 192), (2, 384, 288), (3, 64, 96)])
+def test_forward_matches_oracle(pair, cuda_dev, B, H, W):
+    m, ref = pair
+    x = torch.rand(B, 3, H, W, generator=torch.Generator().manual_seed(0))
+    hm = m(x.to(cuda_dev)).float().cpu()
+    torch.cuda.synchronize()
+    assert tuple(hm.shape) == (B, 17, H // 4, W // 4)
+    with torch.no_grad():
+        want32 = ref(x)
+    want16, feat16 = rr.forward_bf16_emulated(ref, x, return_features=True)
+    scale = want32.abs().max().item()
+    err32 = (hm - want32).abs().max().item()
+    err16 = (hm - want16).abs().max().item()
+    feat = m.forward_features(x.to(cuda_dev)).cpu()
+    ferr = (feat - feat16).abs().max().item() / feat16.abs().max().item()
+    print(f"[{B}x{H}x{W}] heatmap scale {scale:.3f}  err vs fp32 {err32:.2e}  vs bf16-emulated {err16:.2e}  trunk rel {ferr:.2e}")
+    emu32 = (want16 - want32).abs().max().item()
+    print(f"      (CPU bf16-emulation itself differs from fp32 by {emu32:.2e})")
+    rms32 = (hm - want32).pow(2).mean().sqrt().item()
+    print(f"      rms vs fp32 {rms32:.2e}")
+    assert err16 <= HM_TOL_MAXABS, f"max-abs {err16} vs bf16-emulating oracle exceeds {HM_TOL_MAXABS}"
+    assert err32 <= HM_TOL_MAXABS, f"max-abs {err32} vs fp32 oracle exceeds {HM_TOL_MAXABS}"
+    assert rms32 <= HM_TOL_RMS
+    assert err32 <= 2 * emu32 + 5e-3, "kernel error exceeds the bf16 noise floor of this network"
+    assert ferr <= 3e-2
+
+
+def test_forward_is_deterministic_and_graph_equals_eager(pair, cuda_dev, monkeypatch):
+    m, _ = pair
+    x = torch.rand(2, 3, 256, 192, generator=torch.Generator().manual_seed(3)).to(cuda_dev)
+    a = m(x).clone()
+    b = m(x).clone()
+    assert torch.equal(a, b)
+    monkeypatch.setenv("HPE_B200_CUDA_GRAPH", "0")
+    c = m(x).clone()
+    assert torch.equal(a, c)
+
+
+def test_forward_then_decode_end_to_end(hpe, pair, cuda_dev):
+    m, ref = pair
+    B = 4
+    x = torch.rand(B, 3, 256, 192, generator=torch.Generator().manual_seed(1))
+    center, scale = hr.synth_center_scale(B)
+    hm = m(x.to(cuda_dev))
+    preds, maxvals = hpe.decode(hm, torch.from_numpy(center), torch.from_numpy(scale))
+    _, _, idx = hpe.get_max_preds(hm)
+    # (1) same tensor: bit-exact indices, keypoints within 0.05 px
+    hm_cpu = hm.float().cpu().numpy()
+    po, mo = hr.get_final_preds(hm_cpu, center, scale)
+    _, _, io = hr.get_max_preds(hm_cpu)
+    np.testing.assert_array_equal(idx.cpu().numpy(), io)
+    assert np.abs(preds.cpu().numpy() - po).max() <= 0.05
+    np.testing.assert_array_equal(maxvals.cpu().numpy(), mo)
+    # (2) end to end vs the fp32 oracle network, only where the top-2 margin exceeds the heatmap tolerance
+    with torch.no_grad():
+        want = ref(x).numpy()
+    flat = np.sort(want.reshape(B, 17, -1), axis=2)
+    clear = (flat[..., -1] - flat[..., -2]) > 2 * HM_TOL_MAXABS
+    _, _, iw = hr.get_max_preds(want)
+    assert np.array_equal(idx.cpu().numpy()[clear], iw[clear])
+
+
+def test_model_boundary(hpe, cuda_dev):
+    from importlib import import_module
+    models = import_module("2d-human-pose-estimation_b200.models")
+    assert "DeepPose" in models.__all__ and models.DeepPose is models.HeatmapPose
+    cfg = hpe.load_config()
+    cfg.defrost(); cfg.model.pretrained = False; cfg.freeze()
+    m = models.build_model(cfg)                       # Builder.model(): positional (nkpts, backbone, pretrained)
+    assert m.njoints == 17
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        m.eval()(torch.zeros(1, 3, 64, 64))
+    with pytest.raises(NotImplementedError):
+        m.train()(torch.zeros(1, 3, 64, 64, device=cuda_dev))
+    with pytest.raises(RuntimeError, match="pretrained"):
+        models.HeatmapPose(17, "resnet50", pretrained=True)

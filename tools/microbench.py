@@ -63,5 +63,37 @@ def loss():
             print(f"loss-fwd+bwd {str(dtype)[6:]:9s} B={B:6d}: median {med*1e3:8.1f} us -> {2*nbytes/med/1e6:7.1f} GB/s ({2*nbytes/med/1e6/PEAK*100:5.1f}%)", flush=True)
 
 
+def forward():
+    import importlib
+    models = importlib.import_module("2d-human-pose-estimation_b200.models")
+    dev = torch.device("cuda:0")
+    B = int(sys.argv[2]) if len(sys.argv) > 2 else 256
+    H, W = (int(sys.argv[3]), int(sys.argv[4])) if len(sys.argv) > 4 else (256, 192)
+    torch.manual_seed(0)
+    m = models.HeatmapPose(17, "resnet50", False)
+    for mod in m.modules():
+        if isinstance(mod, torch.nn.BatchNorm2d):
+            mod.weight.data.uniform_(0.5, 1.5); mod.running_var.uniform_(0.5, 1.5)
+    m = m.to(dev).eval()
+    x = torch.rand(B, 3, H, W, device=dev)
+    med, best = timeit(lambda: m(x), iters=10)
+    flops = (8.008 + 2.846) * 1e9 * B * (H * W) / (256 * 192)
+    print(f"forward B={B} {H}x{W}: median {med:.3f} ms best {best:.3f} ms -> {B/med*1e3:.0f} img/s, {flops/med/1e9:.1f} TFLOP/s", flush=True)
+    plan = next(iter(m._plans.values()))
+    # per-layer eager timing (L2 not flushed between layers: this is how they run in the step)
+    rows = []
+    for layer, src, res, dst in plan.ops:
+        name = [k for k, v in plan.named.items() if v is layer][0]
+        fn = lambda: layer(plan.bufs[src], plan.bufs[res] if res else None, plan.bufs[dst])
+        med, best = timeit(fn, iters=5, warm=1)
+        d = layer.desc
+        taps = {0: 1, 1: 9, 2: 49 / 3 * 3, 3: 4, 4: 1}[d.kind]
+        macs = layer.B * layer.Ho * layer.Wo * d.Cout * d.Cin * taps
+        byts = plan.bufs[src].numel() * 2 + plan.bufs[dst].numel() * plan.bufs[dst].element_size() + (plan.bufs[res].numel() * 2 if res else 0)
+        rows.append((name, med, 2 * macs / med / 1e9, byts / med / 1e6))
+        print(f"  {name:32s} k{d.kind} {d.Cin:4d}->{d.Cout:4d} s{d.stride} out {layer.Ho}x{layer.Wo}: {med*1e3:8.1f} us  {2*macs/med/1e9:7.1f} TFLOP/s  {byts/med/1e6:7.0f} GB/s", flush=True)
+    print(f"  sum of layers {sum(r[1] for r in rows):.3f} ms")
+
+
 if __name__ == "__main__":
-    {"decode": decode, "loss": loss}[sys.argv[1]]()
+    {"decode": decode, "loss": loss, "forward": forward}[sys.argv[1]]()
