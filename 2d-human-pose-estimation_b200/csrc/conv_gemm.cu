@@ -14,11 +14,12 @@
 //     overlapping-stride TMA map one box row = 4 adjacent blocks = 64 contiguous bf16, so the stem is a
 //     4-tap GEMM with K = 4 x 64.
 //
-// Persistent, warp-specialised CTA (1 per SM, 224 threads):
+// Persistent, warp-specialised CTA (1 per SM, 352 threads):
 //   warp 0  TMA producer (A + W operand ring, STAGES deep)
 //   warp 1  TMEM allocator + single-thread tcgen05.mma issuer (double-buffered accumulators)
 //   warp 2  residual-tile TMA producer (into the epilogue staging ring)
-//   warps 3-6  epilogue: tcgen05.ld -> scale/shift/residual/activation -> bf16 -> swizzled smem -> TMA store
+//   warps 3-10  epilogue (two warps per TMEM lane quarter, each owning 32 of a chunk's 64 columns):
+//               tcgen05.ld -> scale/shift/residual/activation -> bf16 -> swizzled smem -> TMA store
 #include "hpe_common.cuh"
 #include "ptx_sm100.cuh"
 #include <cuda.h>
@@ -27,15 +28,15 @@
 namespace hpe {
 using namespace ptx;
 
-constexpr int kConvThreads   = 224;
-constexpr int kEpiThreads    = 128;
+constexpr int kConvThreads   = 352;                   // 3 control warps + 8 epilogue warps
+constexpr int kEpiThreads    = 256;
 constexpr int kEpiWarp0      = 3;
+constexpr int kMaxCout       = 2048;                  // scale/shift table staged in shared memory
 constexpr int kTileM         = 128;
 constexpr int kKBlock        = 64;                    // bf16 elements per k-block = one 128-byte swizzle row
 constexpr int kABytes        = kTileM * kKBlock * 2;  // 16 KB
 constexpr int kNumSB         = 4;                     // epilogue staging buffers (16 KB each)
 constexpr int kSBBytes       = kTileM * 64 * 2;       // 128 rows x 64 bf16
-constexpr int kMaxTaps       = 9;
 
 struct OutMaps { CUtensorMap m[4]; };
 
@@ -73,12 +74,6 @@ __device__ __forceinline__ void tap_offset(const ConvParams& p, int t, int cls, 
   } else { dx = 0; dy = 0; }
 }
 
-__device__ __forceinline__ float apply_act(float v, int act) {
-  if (act == HPE_ACT_RELU) return fmaxf(v, 0.f);
-  if (act == HPE_ACT_SILU) return v / (1.f + __expf(-v));
-  return v;
-}
-
 template <int BLOCK_N, int STAGES>
 struct SmemLayout {
   static constexpr int kBBytes     = BLOCK_N * kKBlock * 2;
@@ -86,13 +81,34 @@ struct SmemLayout {
   static constexpr int kOffA   = 0;
   static constexpr int kOffB   = STAGES * kABytes;
   static constexpr int kOffSB  = kOffB + STAGES * kBBytes;
-  static constexpr int kOffBar = kOffSB + kNumSB * kSBBytes;
+  static constexpr int kOffSS  = kOffSB + kNumSB * kSBBytes;          // float scale[kMaxCout], shift[kMaxCout]
+  static constexpr int kOffBar = kOffSS + 2 * kMaxCout * 4;
   static constexpr int kNumBar = 2 * STAGES + 4 + 2 * kNumSB;
   static constexpr int kTotal  = kOffBar + kNumBar * 8 + 16;
   static constexpr int kDynamic = kTotal + 1024;      // slack for manual 1024-byte alignment
 };
 
-template <int BLOCK_N, int STAGES>
+__device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
+  uint4 r;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(addr));
+  return r;
+}
+__device__ __forceinline__ void sts_v4(uint32_t addr, const uint4& v) {
+  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ float4 lds_f4(uint32_t addr) {
+  float4 r;
+  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(addr));
+  return r;
+}
+__device__ __forceinline__ uint32_t relu_bf16x2(uint32_t v) {
+  const __nv_bfloat162 z = __floats2bfloat162_rn(0.f, 0.f);
+  __nv_bfloat162 r = __hmax2(*reinterpret_cast<__nv_bfloat162*>(&v), z);
+  return *reinterpret_cast<uint32_t*>(&r);
+}
+
+// ACT: HPE_ACT_*; RES: residual add; FINAL: fp32 NCHW heatmap epilogue (HPE_CONV_FINAL)
+template <int BLOCK_N, int STAGES, int ACT, bool RES, bool FINAL>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                  const __grid_constant__ OutMaps tmOut, const __grid_constant__ CUtensorMap tmRes,
@@ -107,6 +123,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint8_t* sA  = smem + L::kOffA;
   uint8_t* sB  = smem + L::kOffB;
   uint8_t* sSB = smem + L::kOffSB;
+  float*   sScale = reinterpret_cast<float*>(smem + L::kOffSS);
+  float*   sShift = sScale + kMaxCout;
   uint64_t* bars       = reinterpret_cast<uint64_t*>(smem + L::kOffBar);
   uint64_t* full_bar   = bars;
   uint64_t* empty_bar  = bars + STAGES;
@@ -122,14 +140,15 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA); prefetch_tmap(&tmW);
-    if (p.kind != HPE_CONV_FINAL) for (int c = 0; c < p.n_classes; ++c) prefetch_tmap(&tmOut.m[c]);
-    if (p.has_res) prefetch_tmap(&tmRes);
+    if (!FINAL) for (int c = 0; c < p.n_classes; ++c) prefetch_tmap(&tmOut.m[c]);
+    if (RES) prefetch_tmap(&tmRes);
     for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], 4); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], kEpiThreads / 32); }
     for (int b = 0; b < kNumSB; ++b) { mbar_init(&sbfull_bar[b], 1); mbar_init(&sbempty_bar[b], 1); }
     fence_mbar_init();
   }
   if (warp == 1) { tmem_alloc(tmem_slot, kTmemCols); tmem_relinquish(); }
+  for (int i = threadIdx.x; i < p.Cout; i += kConvThreads) { sScale[i] = __ldg(p.scale + i); sShift[i] = __ldg(p.shift + i); }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -179,7 +198,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
   } else if (warp == 2) {
     // ===================== residual producer =====================
-    if (lane == 0 && p.has_res) {
+    if (RES && lane == 0) {
       int r = 0;
       for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
         const TileCoord t = tile_coord(p, tile);
@@ -192,11 +211,12 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
     }
   } else {
-    // ===================== epilogue (4 warps = 128 TMEM lanes) =====================
-    const int ew = warp & 3;                      // TMEM lane group this warp may access
+    // ===================== epilogue (8 warps: TMEM lane quarter = warp & 3, column half = (warp - 3) >> 2) ====
+    const int ew = warp & 3;                      // TMEM lane quarter this warp may access
+    const int half = (warp - kEpiWarp0) >> 2;     // which 32 of the chunk's 64 columns
     const int row = ew * 32 + lane;               // tile row = TMEM lane = pixel inside the brick
     const bool leader = threadIdx.x == kEpiWarp0 * 32;
-    if (leader && p.has_res) { mbar_arrive(&sbempty_bar[0]); mbar_arrive(&sbempty_bar[1]); }
+    if (RES && leader) { mbar_arrive(&sbempty_bar[0]); mbar_arrive(&sbempty_bar[1]); }
     int q = 0, it = 0;
     for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
       const TileCoord t = tile_coord(p, tile);
@@ -205,14 +225,15 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BLOCK_N;
 
-      if (p.kind == HPE_CONV_FINAL) {
+      if constexpr (FINAL) {
         // fp32 NCHW heatmaps straight from registers: for a fixed joint the warp's 32 rows are
-        // consecutive pixels of the brick -> 64-byte (tw=16) contiguous runs
+        // consecutive pixels of the brick -> 64-byte (tw=16) contiguous runs.  Column groups of 32
+        // alternate between the two warps of a lane quarter.
         const int xi = row % p.tw, yi = (row / p.tw) % p.th, bi = row / (p.tw * p.th);
         const int x = t.x0 + xi, y = t.y0 + yi, b = t.b0 + bi;
         const bool ok = x < p.Wo && y < p.Ho && b < p.B;
         const size_t plane = static_cast<size_t>(p.Ho) * p.Wo;
-        for (int g = 0; g * 32 < p.Cout; ++g) {
+        for (int g = half; g * 32 < p.Cout; g += 2) {
           uint32_t v[32];
           tmem_ld_x32(taddr + g * 32, v);
           tmem_ld_wait();
@@ -221,7 +242,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             for (int e = 0; e < 32; ++e) {
               const int k = g * 32 + e;
               if (k < p.Cout) {
-                const float o = apply_act(fmaf(__uint_as_float(v[e]), __ldg(p.scale + k), __ldg(p.shift + k)), p.act);
+                const float o = fmaf(__uint_as_float(v[e]), sScale[k], sShift[k]);
                 p.hm_out[(static_cast<size_t>(b) * p.Cout + k) * plane + static_cast<size_t>(y) * p.Wo + x] = o;
               }
             }
@@ -230,54 +251,57 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tempty_bar[acc]);
-        continue;
-      }
-
-      for (int c = 0; c < kChunks; ++c, ++q) {
-        const int sb = q % kNumSB;
-        uint8_t* stg = sSB + sb * kSBBytes;
-        if (leader) {
-          bulk_wait_read<1>();                                    // stores <= q-2 have left shared memory
-          if (p.has_res) mbar_arrive(&sbempty_bar[(q + 2) % kNumSB]);   // hand buffer of chunk q+2 to warp 2
-        }
-        uint32_t v[64];
-        tmem_ld_x32(taddr + c * 64, v);
-        tmem_ld_x32(taddr + c * 64 + 32, v + 32);
-        if (p.has_res) mbar_wait(&sbfull_bar[sb], (q / kNumSB) & 1);
-        tmem_ld_wait();
-        if (c == kChunks - 1) {                                   // accumulator drained -> MMA may reuse it
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&tempty_bar[acc]);
-        }
-        const int n0 = t.n_tile * BLOCK_N + c * 64;
-        uint8_t* rowp = stg + row * 128;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const float4 s0 = __ldg(reinterpret_cast<const float4*>(p.scale + n0 + j * 8));
-          const float4 s1 = __ldg(reinterpret_cast<const float4*>(p.scale + n0 + j * 8 + 4));
-          const float4 h0 = __ldg(reinterpret_cast<const float4*>(p.shift + n0 + j * 8));
-          const float4 h1 = __ldg(reinterpret_cast<const float4*>(p.shift + n0 + j * 8 + 4));
-          float o[8];
-          o[0] = fmaf(__uint_as_float(v[j * 8 + 0]), s0.x, h0.x); o[1] = fmaf(__uint_as_float(v[j * 8 + 1]), s0.y, h0.y);
-          o[2] = fmaf(__uint_as_float(v[j * 8 + 2]), s0.z, h0.z); o[3] = fmaf(__uint_as_float(v[j * 8 + 3]), s0.w, h0.w);
-          o[4] = fmaf(__uint_as_float(v[j * 8 + 4]), s1.x, h1.x); o[5] = fmaf(__uint_as_float(v[j * 8 + 5]), s1.y, h1.y);
-          o[6] = fmaf(__uint_as_float(v[j * 8 + 6]), s1.z, h1.z); o[7] = fmaf(__uint_as_float(v[j * 8 + 7]), s1.w, h1.w);
-          uint4* slot = reinterpret_cast<uint4*>(rowp + ((j ^ (row & 7)) << 4));   // 128-byte swizzle
-          if (p.has_res) {
-            const uint4 rr = *slot;
-            o[0] += bf16_lo(rr.x); o[1] += bf16_hi(rr.x); o[2] += bf16_lo(rr.y); o[3] += bf16_hi(rr.y);
-            o[4] += bf16_lo(rr.z); o[5] += bf16_hi(rr.z); o[6] += bf16_lo(rr.w); o[7] += bf16_hi(rr.w);
+      } else {
+        for (int c = 0; c < kChunks; ++c, ++q) {
+          const int sb = q % kNumSB;
+          const uint32_t stg = smem_u32(sSB + sb * kSBBytes);
+          if (leader) {
+            bulk_wait_read<1>();                                    // stores <= q-2 have left shared memory
+            if (RES) mbar_arrive(&sbempty_bar[(q + 2) % kNumSB]);   // hand the buffer of chunk q+2 to warp 2
           }
+          uint32_t v[32];
+          tmem_ld_x32(taddr + c * 64 + half * 32, v);
+          if (RES) mbar_wait(&sbfull_bar[sb], (q / kNumSB) & 1);
+          tmem_ld_wait();
+          if (c == kChunks - 1) {                                   // accumulator drained -> MMA may reuse it
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+          }
+          const int n0 = t.n_tile * BLOCK_N + c * 64 + half * 32;   // first channel of this warp's 32 columns
+          const uint32_t ss = smem_u32(sScale + n0), sh = smem_u32(sShift + n0);
+          const uint32_t rowp = stg + row * 128;
 #pragma unroll
-          for (int e = 0; e < 8; ++e) o[e] = apply_act(o[e], p.act);
-          *slot = make_uint4(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]), pack_bf16(o[6], o[7]));
-        }
-        fence_proxy_async_smem();                                  // generic-proxy writes -> visible to TMA
-        named_bar_sync(1, kEpiThreads);
-        if (leader) {
-          tma_store_4d(&tmOut.m[t.cls], stg, n0, t.x0, t.y0, t.b0);
-          bulk_commit();
+          for (int j = 0; j < 4; ++j) {
+            const float4 s0 = lds_f4(ss + j * 32), s1 = lds_f4(ss + j * 32 + 16);
+            const float4 h0 = lds_f4(sh + j * 32), h1 = lds_f4(sh + j * 32 + 16);
+            float o[8];
+            o[0] = fmaf(__uint_as_float(v[j * 8 + 0]), s0.x, h0.x); o[1] = fmaf(__uint_as_float(v[j * 8 + 1]), s0.y, h0.y);
+            o[2] = fmaf(__uint_as_float(v[j * 8 + 2]), s0.z, h0.z); o[3] = fmaf(__uint_as_float(v[j * 8 + 3]), s0.w, h0.w);
+            o[4] = fmaf(__uint_as_float(v[j * 8 + 4]), s1.x, h1.x); o[5] = fmaf(__uint_as_float(v[j * 8 + 5]), s1.y, h1.y);
+            o[6] = fmaf(__uint_as_float(v[j * 8 + 6]), s1.z, h1.z); o[7] = fmaf(__uint_as_float(v[j * 8 + 7]), s1.w, h1.w);
+            const uint32_t slot = rowp + (((half * 4 + j) ^ (row & 7)) << 4);     // 128-byte swizzle
+            if (RES) {
+              const uint4 rr = lds_v4(slot);
+              o[0] += bf16_lo(rr.x); o[1] += bf16_hi(rr.x); o[2] += bf16_lo(rr.y); o[3] += bf16_hi(rr.y);
+              o[4] += bf16_lo(rr.z); o[5] += bf16_hi(rr.z); o[6] += bf16_lo(rr.w); o[7] += bf16_hi(rr.w);
+            }
+            if (ACT == HPE_ACT_SILU) {
+#pragma unroll
+              for (int e = 0; e < 8; ++e) o[e] = o[e] / (1.f + __expf(-o[e]));
+            }
+            uint4 pk = make_uint4(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]), pack_bf16(o[6], o[7]));
+            if (ACT == HPE_ACT_RELU) {        // relu(round(x)) == round(relu(x)): do it on packed bf16x2
+              pk.x = relu_bf16x2(pk.x); pk.y = relu_bf16x2(pk.y); pk.z = relu_bf16x2(pk.z); pk.w = relu_bf16x2(pk.w);
+            }
+            sts_v4(slot, pk);
+          }
+          fence_proxy_async_smem();                                  // generic-proxy writes -> visible to TMA
+          named_bar_sync(1, kEpiThreads);
+          if (leader) {
+            tma_store_4d(&tmOut.m[t.cls], sSB + sb * kSBBytes, t.n_tile * BLOCK_N + c * 64, t.x0, t.y0, t.b0);
+            bulk_commit();
+          }
         }
       }
     }
@@ -437,6 +461,7 @@ struct hpe_conv_plan {
   OutMaps tmOut;
   const void *x, *w, *res;
   void* y;
+  const void* fn;
 };
 
 static int desc_check(const hpe_conv_desc* d, const char* fn) {
@@ -451,9 +476,12 @@ static int desc_check(const hpe_conv_desc* d, const char* fn) {
   if (d->Cin % 64) return fail(HPE_EUNSUPPORTED, "%s: Cin=%d must be a multiple of 64", fn, d->Cin);
   if (d->kind == HPE_CONV_FINAL) {
     if (d->Cout > 256) return fail(HPE_EUNSUPPORTED, "%s: final conv supports at most 256 joints (got %d)", fn, d->Cout);
+    if (d->act != HPE_ACT_NONE || d->has_residual) return fail(HPE_EUNSUPPORTED, "%s: final conv has no activation/residual", fn);
     return HPE_OK;
   }
   if (d->Cout % 64) return fail(HPE_EUNSUPPORTED, "%s: Cout=%d must be a multiple of 64", fn, d->Cout);
+  if (d->Cout > kMaxCout) return fail(HPE_EUNSUPPORTED, "%s: Cout=%d exceeds %d", fn, d->Cout, kMaxCout);
+  if (d->act < HPE_ACT_NONE || d->act > HPE_ACT_SILU) return fail(HPE_EINVAL, "%s: bad act %d", fn, d->act);
   if (d->kind == HPE_CONV_1x1 || d->kind == HPE_CONV_3x3) {
     if (d->stride != 1 && d->stride != 2) return fail(HPE_EUNSUPPORTED, "%s: stride %d not in {1,2}", fn, d->stride);
     if (d->stride == 2 && ((d->H % 2) || (d->W % 2))) return fail(HPE_EUNSUPPORTED, "%s: stride 2 needs even H/W", fn);
@@ -520,11 +548,28 @@ static void pick_brick(int Wo, int Ho, int B, int max_tw, int* tw, int* th, int*
   }
 }
 
+typedef void (*ConvKernelFn)(const CUtensorMap, const CUtensorMap, const OutMaps, const CUtensorMap, const ConvParams);
+
 template <int BN, int ST>
-static int set_smem_attr() {
-  HPE_CUDA_OK(cudaFuncSetAttribute(conv_gemm_kernel<BN, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   SmemLayout<BN, ST>::kDynamic));
-  return HPE_OK;
+static ConvKernelFn pick_kernel_bn(int act, bool res, bool fin) {
+  if (fin) return conv_gemm_kernel<BN, ST, HPE_ACT_NONE, false, true>;
+  if constexpr (BN >= 64) {
+    switch (act) {
+      case HPE_ACT_RELU: return res ? conv_gemm_kernel<BN, ST, HPE_ACT_RELU, true, false> : conv_gemm_kernel<BN, ST, HPE_ACT_RELU, false, false>;
+      case HPE_ACT_SILU: return res ? conv_gemm_kernel<BN, ST, HPE_ACT_SILU, true, false> : conv_gemm_kernel<BN, ST, HPE_ACT_SILU, false, false>;
+      default:           return res ? conv_gemm_kernel<BN, ST, HPE_ACT_NONE, true, false> : conv_gemm_kernel<BN, ST, HPE_ACT_NONE, false, false>;
+    }
+  }
+  return nullptr;
+}
+
+static ConvKernelFn pick_kernel(int block_n, int act, bool res, bool fin, size_t* smem) {
+  switch (block_n) {
+    case 32:  *smem = SmemLayout<32, 6>::kDynamic;  return pick_kernel_bn<32, 6>(act, res, fin);
+    case 64:  *smem = SmemLayout<64, 6>::kDynamic;  return pick_kernel_bn<64, 6>(act, res, fin);
+    case 128: *smem = SmemLayout<128, 4>::kDynamic; return pick_kernel_bn<128, 4>(act, res, fin);
+    default:  *smem = SmemLayout<256, 3>::kDynamic; return pick_kernel_bn<256, 3>(act, res, fin);
+  }
 }
 
 extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out) {
@@ -557,13 +602,12 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
   if (nt > 0x7fffffff) { delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: too many tiles"); }
   p.num_tiles = (int)nt;
   pl->grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
-  switch (pl->block_n) {
-    case 32:  rc = set_smem_attr<32, 6>();  pl->smem = SmemLayout<32, 6>::kDynamic; break;
-    case 64:  rc = set_smem_attr<64, 6>();  pl->smem = SmemLayout<64, 6>::kDynamic; break;
-    case 128: rc = set_smem_attr<128, 4>(); pl->smem = SmemLayout<128, 4>::kDynamic; break;
-    default:  rc = set_smem_attr<256, 3>(); pl->smem = SmemLayout<256, 3>::kDynamic; break;
+  pl->fn = (const void*)pick_kernel(pl->block_n, d->act, p.has_res != 0, d->kind == HPE_CONV_FINAL, &pl->smem);
+  if (!pl->fn) { delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: no kernel for BLOCK_N=%d", pl->block_n); }
+  {
+    cudaError_t e = cudaFuncSetAttribute((const void*)pl->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem);
+    if (e != cudaSuccess) { delete pl; return fail(HPE_ECUDA, "cudaFuncSetAttribute(smem=%zu) failed: %s", pl->smem, cudaGetErrorString(e)); }
   }
-  if (rc) { delete pl; return rc; }
   pl->x = pl->w = pl->res = nullptr; pl->y = nullptr;
   *out = pl;
   return HPE_OK;
@@ -654,13 +698,9 @@ extern "C" int hpe_conv_run(hpe_conv_plan* pl, const void* x, const void* w_pack
   p.hm_out = pl->d.kind == HPE_CONV_FINAL ? (float*)y : nullptr;
   if (!p.has_res) pl->tmRes = pl->tmA;      // unused, but must be a valid object to copy
   if (pl->d.kind == HPE_CONV_FINAL) for (int c = 0; c < 4; ++c) pl->tmOut.m[c] = pl->tmA;
-  cudaStream_t st = (cudaStream_t)stream;
-  switch (pl->block_n) {
-    case 32:  conv_gemm_kernel<32, 6><<<pl->grid, kConvThreads, pl->smem, st>>>(pl->tmA, pl->tmW, pl->tmOut, pl->tmRes, p); break;
-    case 64:  conv_gemm_kernel<64, 6><<<pl->grid, kConvThreads, pl->smem, st>>>(pl->tmA, pl->tmW, pl->tmOut, pl->tmRes, p); break;
-    case 128: conv_gemm_kernel<128, 4><<<pl->grid, kConvThreads, pl->smem, st>>>(pl->tmA, pl->tmW, pl->tmOut, pl->tmRes, p); break;
-    default:  conv_gemm_kernel<256, 3><<<pl->grid, kConvThreads, pl->smem, st>>>(pl->tmA, pl->tmW, pl->tmOut, pl->tmRes, p); break;
-  }
+  void* args[5] = {&pl->tmA, &pl->tmW, &pl->tmOut, &pl->tmRes, &p};
+  cudaError_t e = cudaLaunchKernel((const void*)pl->fn, dim3(pl->grid), dim3(kConvThreads), args, pl->smem, (cudaStream_t)stream);
+  if (e != cudaSuccess) return fail(HPE_ECUDA, "launch of conv_gemm_kernel failed: %s", cudaGetErrorString(e));
   return launch_status("conv_gemm_kernel");
 }
 

@@ -1,0 +1,35 @@
+"""Run ONE conv layer configuration a few times (target for `ncu --set full` captures).
+    python tools/run_layer.py <kind> B H W Cin Cout stride act res [iters]
+"""
+import importlib
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import hpe_b200  # noqa: F401,E402
+
+conv = importlib.import_module("2d-human-pose-estimation_b200.conv")
+kind, B, H, W, Cin, Cout, stride, act, res = [int(v) for v in sys.argv[1:10]]
+iters = int(sys.argv[10]) if len(sys.argv) > 10 else 5
+dev = torch.device("cuda:0")
+layer = conv.ConvLayer(kind, B, H, W, Cin, Cout, stride, act, bool(res), dev)
+if kind == conv.CONV_DECONV4:
+    w = torch.randn(Cin, Cout, 4, 4) * 0.02
+elif kind == conv.CONV_3x3:
+    w = torch.randn(Cout, Cin, 3, 3) * 0.02
+else:
+    w = torch.randn(Cout, Cin, 1, 1) * 0.05
+layer.load(w, torch.rand(Cout) + 0.5, torch.randn(Cout) * 0.1)
+x = torch.randn(B, H, W, Cin, device=dev).to(torch.bfloat16)
+r = torch.randn(layer.out_shape(), device=dev).to(torch.bfloat16) if res else None
+y = layer.alloc_out()
+flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+ts = []
+for i in range(iters):
+    flush.zero_()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(); layer(x, r, y); e1.record(); torch.cuda.synchronize()
+    ts.append(e0.elapsed_time(e1))
+print(f"kind {kind} {Cin}->{Cout} s{stride} @{H}x{W} B={B}: min {min(ts)*1e3:.1f} us  median {sorted(ts)[len(ts)//2]*1e3:.1f} us")
