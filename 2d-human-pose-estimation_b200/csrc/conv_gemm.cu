@@ -24,6 +24,7 @@
 #include "ptx_sm100.cuh"
 #include <cuda.h>
 #include <mutex>
+#include <stdlib.h>
 
 namespace hpe {
 using namespace ptx;
@@ -153,6 +154,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // PDL: everything above (barrier init, TMEM alloc, descriptor prefetch, scale/shift staging -- all
+  // independent of the previous layer's output) may overlap the previous kernel's tail.
+  griddep_launch_dependents();
+  griddep_wait();
 
   if (warp == 0) {
     // ===================== operand producer =====================
@@ -489,7 +494,10 @@ static int desc_check(const hpe_conv_desc* d, const char* fn) {
   return HPE_OK;
 }
 
-static int pick_block_n(const hpe_conv_desc* d) {
+// BLOCK_N: the widest tile dividing Cout.  (Measured on B200: narrower tiles that fill the last wave of the
+// persistent grid better are still slower -- layer4 3x3 66 -> 78 us -- because every extra N tile re-reads
+// the A operand through the L2->SM fabric, which is what bounds these kernels; see profiles/.)
+static int pick_block_n(const hpe_conv_desc* d, long long /*m_tiles*/) {
   if (d->kind == HPE_CONV_FINAL) return d->Cout <= 32 ? 32 : (d->Cout <= 64 ? 64 : (d->Cout <= 128 ? 128 : 256));
   if (d->Cout % 256 == 0) return 256;
   if (d->Cout % 128 == 0) return 128;
@@ -548,6 +556,12 @@ static void pick_brick(int Wo, int Ho, int B, int max_tw, int* tw, int* th, int*
   }
 }
 
+static bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("HPE_B200_PDL"); v = (e && e[0] == '0') ? 0 : 1; }
+  return v != 0;
+}
+
 typedef void (*ConvKernelFn)(const CUtensorMap, const CUtensorMap, const OutMaps, const CUtensorMap, const ConvParams);
 
 template <int BN, int ST>
@@ -596,7 +610,7 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
   pick_brick(p.Wo, p.Ho, p.B, p.in_stride == 2 ? 128 : 256, &tw, &th, &nb);
   p.tw = tw; p.th = th; p.nb = nb;
   p.tiles_x = (p.Wo + tw - 1) / tw; p.tiles_y = (p.Ho + th - 1) / th; p.tiles_b = (p.B + nb - 1) / nb;
-  pl->block_n = pick_block_n(d);
+  pl->block_n = pick_block_n(d, (long long)p.tiles_x * p.tiles_y * p.tiles_b * p.n_classes);
   p.n_tiles_n = d->kind == HPE_CONV_FINAL ? 1 : d->Cout / pl->block_n;
   const long long nt = (long long)p.tiles_x * p.tiles_y * p.tiles_b * p.n_tiles_n * p.n_classes;
   if (nt > 0x7fffffff) { delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: too many tiles"); }
@@ -699,7 +713,14 @@ extern "C" int hpe_conv_run(hpe_conv_plan* pl, const void* x, const void* w_pack
   if (!p.has_res) pl->tmRes = pl->tmA;      // unused, but must be a valid object to copy
   if (pl->d.kind == HPE_CONV_FINAL) for (int c = 0; c < 4; ++c) pl->tmOut.m[c] = pl->tmA;
   void* args[5] = {&pl->tmA, &pl->tmW, &pl->tmOut, &pl->tmRes, &p};
-  cudaError_t e = cudaLaunchKernel((const void*)pl->fn, dim3(pl->grid), dim3(kConvThreads), args, pl->smem, (cudaStream_t)stream);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(pl->grid); cfg.blockDim = dim3(kConvThreads);
+  cfg.dynamicSmemBytes = pl->smem; cfg.stream = (cudaStream_t)stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cudaError_t e = cudaLaunchKernelExC(&cfg, (const void*)pl->fn, args);
   if (e != cudaSuccess) return fail(HPE_ECUDA, "launch of conv_gemm_kernel failed: %s", cudaGetErrorString(e));
   return launch_status("conv_gemm_kernel");
 }
