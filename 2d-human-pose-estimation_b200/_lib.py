@@ -43,6 +43,10 @@ SIGNATURES = {
     "hpe_preprocess_out_elems": (_sz, [_i, _i, _i]),
     "hpe_preprocess": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "hpe_maxpool3x3s2": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
+    "hpe_wgrad_plan_create": (_i, [C.POINTER(ConvDesc), C.POINTER(_vp)]),
+    "hpe_wgrad_plan_destroy": (None, [_vp]),
+    "hpe_wgrad_workspace_elems": (_sz, [_vp]),
+    "hpe_wgrad_run": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp]),
 }
 
 _lib = None

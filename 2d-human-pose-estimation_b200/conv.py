@@ -106,3 +106,37 @@ def maxpool3x3s2(x: torch.Tensor, out: torch.Tensor = None):
     with torch.cuda.device(x.device):
         _lib.check(_lib.lib().hpe_maxpool3x3s2(_lib.ptr(x), B, H, W, Cc, _lib.ptr(out), _lib.stream_ptr()), "hpe_maxpool3x3s2")
     return out
+
+
+class WgradLayer:
+    """Weight gradient of one conv layer (csrc/wgrad_gemm.cu): ``dW = wgrad(x, dz)`` in the PyTorch weight
+    layout, fp32.  Replaces the cuDNN wgrad autograd launches behind ``loss.backward()``
+    (/root/reference/HPE/engine/trainer.py:96-97)."""
+
+    def __init__(self, kind, B, H, W, Cin, Cout, stride=1, device="cuda"):
+        self.device = torch.device(device)
+        self.desc = ConvDesc(kind, B, H, W, Cin, Cout, stride, ACT_NONE, 0)
+        plan = C.c_void_p()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().hpe_wgrad_plan_create(C.byref(self.desc), C.byref(plan)), "hpe_wgrad_plan_create")
+        self.plan = plan
+        n = _lib.lib().hpe_wgrad_workspace_elems(plan)
+        self.workspace = torch.empty(n, dtype=torch.float32, device=self.device)
+
+    def __del__(self):
+        try:
+            if getattr(self, "plan", None):
+                _lib.lib().hpe_wgrad_plan_destroy(self.plan)
+                self.plan = None
+        except Exception:
+            pass
+
+    def __call__(self, x: torch.Tensor, dz: torch.Tensor, dw: torch.Tensor, accumulate=False):
+        _lib.require_cuda(x, dz, dw)
+        if dw.dtype != torch.float32:
+            raise TypeError("weight gradients are float32")
+        with torch.cuda.device(self.device):
+            rc = _lib.lib().hpe_wgrad_run(self.plan, _lib.ptr(x), _lib.ptr(dz), _lib.ptr(self.workspace), _lib.ptr(dw),
+                                          int(bool(accumulate)), _lib.stream_ptr())
+        _lib.check(rc, "hpe_wgrad_run")
+        return dw

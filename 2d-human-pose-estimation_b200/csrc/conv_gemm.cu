@@ -22,8 +22,7 @@
 //               tcgen05.ld -> scale/shift/residual/activation -> bf16 -> swizzled smem -> TMA store
 #include "hpe_common.cuh"
 #include "ptx_sm100.cuh"
-#include <cuda.h>
-#include <mutex>
+#include "tma_host.cuh"
 #include <stdlib.h>
 
 namespace hpe {
@@ -419,39 +418,6 @@ pack_weight_kernel(const float* __restrict__ w, int kind, int Cin, int Cout, lon
   }
 }
 
-// ---- host side --------------------------------------------------------------------------------------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  static std::once_flag once;
-  std::call_once(once, [] {
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
-        q == cudaDriverEntryPointSuccess)
-      fn = reinterpret_cast<EncodeTiledFn>(p);
-  });
-  return fn;
-}
-
-static int encode_map(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
-                      const uint32_t* box, const uint32_t* estrides, const char* what) {
-  EncodeTiledFn fn = encode_fn();
-  if (!fn) return fail(HPE_ECUDA, "cuTensorMapEncodeTiled entry point not available");
-  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), dims, strides_bytes, box, estrides,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS)
-    return fail(HPE_ECUDA, "cuTensorMapEncodeTiled(%s) failed with CUresult %d (dims %llu,%llu,%llu,%llu box %u,%u,%u,%u)",
-                what, (int)r, (unsigned long long)dims[0], (unsigned long long)dims[1],
-                (unsigned long long)(rank > 2 ? dims[2] : 0), (unsigned long long)(rank > 3 ? dims[3] : 0),
-                box[0], box[1], rank > 2 ? box[2] : 0, rank > 3 ? box[3] : 0);
-  return HPE_OK;
-}
-
 }  // namespace hpe
 
 using namespace hpe;
@@ -543,25 +509,6 @@ extern "C" int hpe_conv_pack_weight(const hpe_conv_desc* d, const float* w_torch
   return launch_status("pack_weight_kernel");
 }
 
-// choose the (tw, th, nb) brick of 128 output pixels that minimises the number of tiles (ties: wider tw)
-static void pick_brick(int Wo, int Ho, int B, int max_tw, int* tw, int* th, int* nb) {
-  long long best = -1;
-  for (int a = 1; a <= 128; a <<= 1) {
-    if (a > max_tw) break;
-    for (int b = 1; a * b <= 128; b <<= 1) {
-      const int c = 128 / (a * b);
-      const long long tiles = (long long)((Wo + a - 1) / a) * ((Ho + b - 1) / b) * ((B + c - 1) / c);
-      if (best < 0 || tiles < best || (tiles == best && a > *tw)) { best = tiles; *tw = a; *th = b; *nb = c; }
-    }
-  }
-}
-
-static bool pdl_enabled() {
-  static int v = -1;
-  if (v < 0) { const char* e = getenv("HPE_B200_PDL"); v = (e && e[0] == '0') ? 0 : 1; }
-  return v != 0;
-}
-
 typedef void (*ConvKernelFn)(const CUtensorMap, const CUtensorMap, const OutMaps, const CUtensorMap, const ConvParams);
 
 template <int BN, int ST>
@@ -607,7 +554,7 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
   p.B = d->B; p.Cout = d->Cout;
   p.act = d->act; p.has_res = d->has_residual ? 1 : 0;
   int tw = 1, th = 1, nb = 128;
-  pick_brick(p.Wo, p.Ho, p.B, p.in_stride == 2 ? 128 : 256, &tw, &th, &nb);
+  pick_brick(128, p.Wo, p.Ho, p.B, p.in_stride == 2 ? 128 : 256, &tw, &th, &nb);
   p.tw = tw; p.th = th; p.nb = nb;
   p.tiles_x = (p.Wo + tw - 1) / tw; p.tiles_y = (p.Ho + th - 1) / th; p.tiles_b = (p.B + nb - 1) / nb;
   pl->block_n = pick_block_n(d, (long long)p.tiles_x * p.tiles_y * p.tiles_b * p.n_classes);

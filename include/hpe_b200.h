@@ -147,6 +147,25 @@ int  hpe_preprocess(const float* img_nchw, int B, int H, int W, void* s2d_out, v
 /* MaxPool 3x3 s2 p1 on NHWC bf16 (timm resnet.py:574-576). */
 int  hpe_maxpool3x3s2(const void* x, int B, int H, int W, int C, void* y, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Training step (BASELINE configs[2]; call sites `loss.backward()` / `optimizer.step()`,
+ * HPE/engine/trainer.py:96-100; in the reference these are cuDNN dgrad/wgrad + ATen BatchNorm backward
+ * launched by autograd).  Activation gradients are bf16 NHWC, weight gradients fp32 in the PyTorch
+ * weight layout.
+ *
+ * Weight gradient of one conv layer described by the FORWARD descriptor:
+ *   x   the layer's forward input  (bf16 NHWC [B,H,W,Cin]; STEM: the hpe_preprocess staging buffer)
+ *   dz  gradient w.r.t. the conv output (bf16 NHWC [B,Ho,Wo,Cout]; FINAL: [B,H,W,64], joints zero-padded)
+ *   workspace  fp32 scratch of hpe_wgrad_workspace_elems(plan) elements
+ *   dw_torch   fp32, same shape as the layer's PyTorch weight; overwritten, or added to if accumulate != 0
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct hpe_wgrad_plan hpe_wgrad_plan;
+int    hpe_wgrad_plan_create(const hpe_conv_desc* fwd_desc, hpe_wgrad_plan** out);
+void   hpe_wgrad_plan_destroy(hpe_wgrad_plan* plan);
+size_t hpe_wgrad_workspace_elems(const hpe_wgrad_plan* plan);
+int    hpe_wgrad_run(hpe_wgrad_plan* plan, const void* x, const void* dz, float* workspace, float* dw_torch,
+                     int accumulate, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
