@@ -14,6 +14,7 @@ LIB_PATH = os.path.join(_PKG, "lib", "libhpe_b200.so")
 HPE_F32, HPE_BF16 = 0, 1
 ACT_NONE, ACT_RELU, ACT_SILU = 0, 1, 2
 CONV_1x1, CONV_3x3, CONV_STEM7x7, CONV_DECONV4, CONV_FINAL = 0, 1, 2, 3, 4
+CONV_DGRAD3x3S2, CONV_DGRAD1x1S2, CONV_4x4S2 = 5, 6, 7
 
 
 class ConvDesc(C.Structure):
@@ -43,6 +44,8 @@ SIGNATURES = {
     "hpe_preprocess_out_elems": (_sz, [_i, _i, _i]),
     "hpe_preprocess": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "hpe_maxpool3x3s2": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
+    "hpe_conv_dgrad_desc": (_i, [C.POINTER(ConvDesc), C.POINTER(ConvDesc)]),
+    "hpe_conv_pack_weight_dgrad": (_i, [C.POINTER(ConvDesc), _vp, _vp, _vp]),
     "hpe_wgrad_plan_create": (_i, [C.POINTER(ConvDesc), C.POINTER(_vp)]),
     "hpe_wgrad_plan_destroy": (None, [_vp]),
     "hpe_wgrad_workspace_elems": (_sz, [_vp]),

@@ -13,7 +13,8 @@ import ctypes as C
 import torch
 
 from . import _lib
-from ._lib import ACT_NONE, ACT_RELU, ACT_SILU, CONV_1x1, CONV_3x3, CONV_DECONV4, CONV_FINAL, CONV_STEM7x7, ConvDesc
+from ._lib import (ACT_NONE, ACT_RELU, ACT_SILU, CONV_1x1, CONV_3x3, CONV_4x4S2, CONV_DECONV4, CONV_DGRAD1x1S2,
+                   CONV_DGRAD3x3S2, CONV_FINAL, CONV_STEM7x7, ConvDesc)
 
 
 def fold_bn(weight, bias, running_mean, running_var, eps):
@@ -24,9 +25,10 @@ def fold_bn(weight, bias, running_mean, running_var, eps):
 
 
 class ConvLayer:
-    def __init__(self, kind, B, H, W, Cin, Cout, stride=1, act=ACT_RELU, has_residual=False, device="cuda"):
+    def __init__(self, kind, B, H, W, Cin, Cout, stride=1, act=ACT_RELU, has_residual=False, device="cuda", desc=None):
         self.device = torch.device(device)
-        self.desc = ConvDesc(kind, B, H, W, Cin, Cout, stride, act, int(has_residual))
+        self.desc = desc if desc is not None else ConvDesc(kind, B, H, W, Cin, Cout, stride, act, int(has_residual))
+        kind, B, Cout = self.desc.kind, self.desc.B, self.desc.Cout
         lib = _lib.lib()
         ho, wo = C.c_int(), C.c_int()
         with torch.cuda.device(self.device):
@@ -106,6 +108,27 @@ def maxpool3x3s2(x: torch.Tensor, out: torch.Tensor = None):
     with torch.cuda.device(x.device):
         _lib.check(_lib.lib().hpe_maxpool3x3s2(_lib.ptr(x), B, H, W, Cc, _lib.ptr(out), _lib.stream_ptr()), "hpe_maxpool3x3s2")
     return out
+
+
+class DgradLayer(ConvLayer):
+    """Backward-data convolution of a forward layer: ``dx = dgrad(dz) (+ residual)`` on the same tcgen05 kernel
+    (weights re-packed: transposed / 180-degree rotated / per-parity-class).  ``fwd`` = the forward layer's
+    (kind, B, H, W, Cin, Cout, stride)."""
+
+    def __init__(self, kind, B, H, W, Cin, Cout, stride=1, accumulate=False, device="cuda"):
+        self.fwd_desc = ConvDesc(kind, B, H, W, Cin, Cout, stride, ACT_NONE, 0)
+        g = ConvDesc()
+        _lib.check(_lib.lib().hpe_conv_dgrad_desc(C.byref(self.fwd_desc), C.byref(g)), "hpe_conv_dgrad_desc")
+        g.has_residual = int(bool(accumulate))
+        super().__init__(None, None, None, None, None, None, device=device, desc=g)
+
+    def load(self, weight: torch.Tensor, scale=None, shift=None):
+        """weight: the FORWARD layer's PyTorch-layout fp32 weight."""
+        w = weight.detach().to(self.device, torch.float32).contiguous()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().hpe_conv_pack_weight_dgrad(C.byref(self.fwd_desc), _lib.ptr(w), _lib.ptr(self.w_packed),
+                                                             _lib.stream_ptr()), "hpe_conv_pack_weight_dgrad")
+        return self
 
 
 class WgradLayer:

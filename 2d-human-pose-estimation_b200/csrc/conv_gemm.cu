@@ -71,7 +71,17 @@ __device__ __forceinline__ void tap_offset(const ConvParams& p, int t, int cls, 
     const int py = cls >> 1, px = cls & 1, ty = t >> 1, tx = t & 1;
     dy = ty ? (py ? 1 : -1) : 0;
     dx = tx ? (px ? 1 : -1) : 0;
-  } else { dx = 0; dy = 0; }
+  } else if (p.kind == HPE_CONV_DGRAD3x3S2) {           // class (py,px): 1 tap on an even axis, 2 on an odd one
+    const int py = cls >> 1, px = cls & 1, nx = 1 + px, ty = t / nx, tx = t - ty * nx;
+    dy = (py && ty) ? 1 : 0;
+    dx = (px && tx) ? 1 : 0;
+  } else if (p.kind == HPE_CONV_4x4S2) { dy = (t >> 2) - 1; dx = (t & 3) - 1; }
+  else { dx = 0; dy = 0; }
+}
+// number of 64-wide k-blocks of a tile (depends on the parity class only for the stride-2 3x3 dgrad)
+__device__ __forceinline__ int kb_count(const ConvParams& p, int cls) {
+  if (p.kind == HPE_CONV_DGRAD3x3S2) return (1 + (cls >> 1)) * (1 + (cls & 1)) * p.kc_per_tap;
+  return p.taps * p.kc_per_tap;
 }
 
 template <int BLOCK_N, int STAGES>
@@ -136,8 +146,6 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int num_kb = p.taps * p.kc_per_tap;
-
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA); prefetch_tmap(&tmW);
     if (!FINAL) for (int c = 0; c < p.n_classes; ++c) prefetch_tmap(&tmOut.m[c]);
@@ -165,6 +173,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
         const TileCoord t = tile_coord(p, tile);
         const int wrow = t.cls * p.Cout + t.n_tile * BLOCK_N;
+        const int num_kb = kb_count(p, t.cls);
         for (int kb = 0; kb < num_kb; ++kb) {
           const int tap = kb / p.kc_per_tap, kc = kb - tap * p.kc_per_tap;
           int dx, dy; tap_offset(p, tap, t.cls, dx, dy);
@@ -186,6 +195,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         mbar_wait(&tempty_bar[acc], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
+        const int num_kb = kb_count(p, tile_coord(p, tile).cls);
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
@@ -437,7 +447,7 @@ struct hpe_conv_plan {
 
 static int desc_check(const hpe_conv_desc* d, const char* fn) {
   HPE_CHECK_ARG(d, "%s: null desc", fn);
-  HPE_CHECK_ARG(d->kind >= HPE_CONV_1x1 && d->kind <= HPE_CONV_FINAL, "%s: bad kind %d", fn, d->kind);
+  HPE_CHECK_ARG(d->kind >= HPE_CONV_1x1 && d->kind <= HPE_CONV_4x4S2, "%s: bad kind %d", fn, d->kind);
   HPE_CHECK_ARG(d->B > 0 && d->H > 0 && d->W > 0 && d->Cin > 0 && d->Cout > 0, "%s: non-positive size", fn);
   if (d->kind == HPE_CONV_STEM7x7) {
     if (d->Cin != 3 || d->Cout != 64 || (d->H % 2) || (d->W % 2))
@@ -457,6 +467,7 @@ static int desc_check(const hpe_conv_desc* d, const char* fn) {
     if (d->stride != 1 && d->stride != 2) return fail(HPE_EUNSUPPORTED, "%s: stride %d not in {1,2}", fn, d->stride);
     if (d->stride == 2 && ((d->H % 2) || (d->W % 2))) return fail(HPE_EUNSUPPORTED, "%s: stride 2 needs even H/W", fn);
   }
+  if (d->kind == HPE_CONV_4x4S2 && ((d->H % 2) || (d->W % 2))) return fail(HPE_EUNSUPPORTED, "%s: 4x4/s2 needs even H/W", fn);
   return HPE_OK;
 }
 
@@ -476,7 +487,8 @@ extern "C" int hpe_conv_out_hw(const hpe_conv_desc* d, int* Ho, int* Wo) {
   HPE_CHECK_ARG(Ho && Wo, "hpe_conv_out_hw: null out");
   switch (d->kind) {
     case HPE_CONV_STEM7x7: *Ho = d->H / 2; *Wo = d->W / 2; break;
-    case HPE_CONV_DECONV4: *Ho = d->H * 2; *Wo = d->W * 2; break;
+    case HPE_CONV_DECONV4: case HPE_CONV_DGRAD3x3S2: case HPE_CONV_DGRAD1x1S2: *Ho = d->H * 2; *Wo = d->W * 2; break;
+    case HPE_CONV_4x4S2:   *Ho = d->H / 2; *Wo = d->W / 2; break;
     case HPE_CONV_FINAL:   *Ho = d->H; *Wo = d->W; break;
     default:               *Ho = d->H / d->stride; *Wo = d->W / d->stride; break;
   }
@@ -487,11 +499,13 @@ static size_t ktot(const hpe_conv_desc* d) {
   switch (d->kind) {
     case HPE_CONV_3x3:     return (size_t)9 * d->Cin;
     case HPE_CONV_STEM7x7: return 256;
-    case HPE_CONV_DECONV4: return (size_t)4 * d->Cin;
+    case HPE_CONV_DECONV4: case HPE_CONV_DGRAD3x3S2: return (size_t)4 * d->Cin;
+    case HPE_CONV_4x4S2:   return (size_t)16 * d->Cin;
     default:               return d->Cin;
   }
 }
-static size_t wrows(const hpe_conv_desc* d) { return d->kind == HPE_CONV_DECONV4 ? (size_t)4 * d->Cout : d->Cout; }
+static bool is_class_strided(int kind) { return kind == HPE_CONV_DECONV4 || kind == HPE_CONV_DGRAD3x3S2; }
+static size_t wrows(const hpe_conv_desc* d) { return is_class_strided(d->kind) ? (size_t)4 * d->Cout : d->Cout; }
 
 extern "C" size_t hpe_conv_packed_weight_elems(const hpe_conv_desc* d) {
   if (desc_check(d, "hpe_conv_packed_weight_elems")) return 0;
@@ -502,11 +516,82 @@ extern "C" int hpe_conv_pack_weight(const hpe_conv_desc* d, const float* w_torch
   int rc = desc_check(d, "hpe_conv_pack_weight");
   if (rc) return rc;
   HPE_CHECK_ARG(w_torch && w_packed, "hpe_conv_pack_weight: null pointer");
+  if (d->kind > HPE_CONV_FINAL) return fail(HPE_EINVAL, "hpe_conv_pack_weight: kind %d is a backward-data kind; use hpe_conv_pack_weight_dgrad", d->kind);
   const long long total = (long long)(wrows(d) * ktot(d));
   const int grid = (int)((total + 255) / 256 > 4096 ? 4096 : (total + 255) / 256);
   pack_weight_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(w_torch, d->kind, d->Cin, d->Cout, total,
                                                             (__nv_bfloat16*)w_packed);
   return launch_status("pack_weight_kernel");
+}
+
+
+namespace hpe {
+// PyTorch-layout fp32 FORWARD weight -> packed bf16 GEMM-B of the layer's backward-data convolution
+__global__ void __launch_bounds__(256)
+pack_weight_dgrad_kernel(const float* __restrict__ w, int fkind, int fstride, int Cin, int Cout, long long total,
+                         __nv_bfloat16* __restrict__ out) {
+  // Cin/Cout are the FORWARD layer's; the dgrad GEMM has N = Cin (rows) and K over Cout.
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    float v = 0.f;
+    if (fkind == HPE_CONV_1x1) {                                        // [ci][co] = w[co][ci]
+      const int ci = static_cast<int>(i / Cout), co = static_cast<int>(i % Cout);
+      v = w[static_cast<size_t>(co) * Cin + ci];
+    } else if (fkind == HPE_CONV_FINAL) {                               // [ci][64]: joints zero-padded
+      const int ci = static_cast<int>(i / 64), k = static_cast<int>(i % 64);
+      if (k < Cout) v = w[static_cast<size_t>(k) * Cin + ci];
+    } else if (fkind == HPE_CONV_3x3 && fstride == 1) {                 // [ci][t*Cout+co] = w[co][ci][2-ty][2-tx]
+      const int K = 9 * Cout, ci = static_cast<int>(i / K), k = static_cast<int>(i % K);
+      const int t = k / Cout, co = k % Cout, ty = t / 3, tx = t % 3;
+      v = w[((static_cast<size_t>(co) * Cin + ci) * 3 + (2 - ty)) * 3 + (2 - tx)];
+    } else if (fkind == HPE_CONV_3x3) {                                 // stride 2: [(cls*Cin+ci)][t*Cout+co]
+      const int K = 4 * Cout;
+      const int row = static_cast<int>(i / K), k = static_cast<int>(i % K);
+      const int cls = row / Cin, ci = row % Cin, t = k / Cout, co = k % Cout;
+      const int py = cls >> 1, px = cls & 1, nx = 1 + px, ny = 1 + py, ty = t / nx, tx = t % nx;
+      if (ty < ny) {
+        const int ky = py ? (ty ? 0 : 2) : 1, kx = px ? (tx ? 0 : 2) : 1;
+        v = w[((static_cast<size_t>(co) * Cin + ci) * 3 + ky) * 3 + kx];
+      }
+    } else {                                                            // deconv: [ci][t*Cout+co] = w[ci][co][ky][kx]
+      const int K = 16 * Cout, ci = static_cast<int>(i / K), k = static_cast<int>(i % K);
+      const int t = k / Cout, co = k % Cout;
+      v = w[(static_cast<size_t>(ci) * Cout + co) * 16 + t];
+    }
+    out[i] = __float2bfloat16(v);
+  }
+}
+
+}  // namespace hpe
+using namespace hpe;
+
+extern "C" int hpe_conv_dgrad_desc(const hpe_conv_desc* f, hpe_conv_desc* g) {
+  HPE_CHECK_ARG(f && g, "hpe_conv_dgrad_desc: null pointer");
+  int Ho = 0, Wo = 0;
+  int rc = hpe_conv_out_hw(f, &Ho, &Wo);
+  if (rc) return rc;
+  *g = *f;
+  g->H = Ho; g->W = Wo; g->Cin = f->Cout; g->Cout = f->Cin; g->stride = 1; g->act = HPE_ACT_NONE; g->has_residual = 0;
+  switch (f->kind) {
+    case HPE_CONV_1x1:     g->kind = f->stride == 2 ? HPE_CONV_DGRAD1x1S2 : HPE_CONV_1x1; break;
+    case HPE_CONV_3x3:     g->kind = f->stride == 2 ? HPE_CONV_DGRAD3x3S2 : HPE_CONV_3x3; break;
+    case HPE_CONV_DECONV4: g->kind = HPE_CONV_4x4S2; g->stride = 2; break;
+    case HPE_CONV_FINAL:   g->kind = HPE_CONV_1x1; g->Cin = 64; break;
+    default: return fail(HPE_EUNSUPPORTED, "hpe_conv_dgrad_desc: kind %d has no backward-data convolution (the stem's input needs no gradient)", f->kind);
+  }
+  return HPE_OK;
+}
+
+extern "C" int hpe_conv_pack_weight_dgrad(const hpe_conv_desc* f, const float* w_torch, void* w_packed, void* stream) {
+  hpe_conv_desc g;
+  int rc = hpe_conv_dgrad_desc(f, &g);
+  if (rc) return rc;
+  HPE_CHECK_ARG(w_torch && w_packed, "hpe_conv_pack_weight_dgrad: null pointer");
+  const long long total = (long long)hpe_conv_packed_weight_elems(&g);
+  const int grid = (int)((total + 255) / 256 > 4096 ? 4096 : (total + 255) / 256);
+  pack_weight_dgrad_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(w_torch, f->kind, f->stride, f->Cin, f->Cout, total,
+                                                                  (__nv_bfloat16*)w_packed);
+  return launch_status("pack_weight_dgrad_kernel");
 }
 
 typedef void (*ConvKernelFn)(const CUtensorMap, const CUtensorMap, const OutMaps, const CUtensorMap, const ConvParams);
@@ -544,13 +629,19 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
   hpe_conv_out_hw(d, &pl->Ho, &pl->Wo);
   ConvParams& p = pl->p;
   p.kind = d->kind;
-  p.in_stride = (d->kind == HPE_CONV_1x1 || d->kind == HPE_CONV_3x3) ? d->stride : 1;
-  p.taps = d->kind == HPE_CONV_3x3 ? 9 : (d->kind == HPE_CONV_1x1 || d->kind == HPE_CONV_FINAL ? 1 : 4);
+  p.in_stride = (d->kind == HPE_CONV_1x1 || d->kind == HPE_CONV_3x3) ? d->stride : (d->kind == HPE_CONV_4x4S2 ? 2 : 1);
+  switch (d->kind) {
+    case HPE_CONV_3x3: p.taps = 9; break;
+    case HPE_CONV_4x4S2: p.taps = 16; break;
+    case HPE_CONV_1x1: case HPE_CONV_FINAL: case HPE_CONV_DGRAD1x1S2: p.taps = 1; break;
+    default: p.taps = 4; break;                 // stem, deconv, (dgrad 3x3/s2: upper bound, see kb_count)
+  }
   p.kc_per_tap = d->kind == HPE_CONV_STEM7x7 ? 1 : d->Cin / 64;
-  p.n_classes = d->kind == HPE_CONV_DECONV4 ? 4 : 1;
-  // tile grid extent: deconv tiles walk the INPUT-resolution grid of one parity class
-  p.Ho = d->kind == HPE_CONV_DECONV4 ? d->H : pl->Ho;
-  p.Wo = d->kind == HPE_CONV_DECONV4 ? d->W : pl->Wo;
+  p.n_classes = is_class_strided(d->kind) ? 4 : 1;
+  // tile grid extent: deconv-like tiles walk the INPUT-resolution grid of one parity class
+  const bool up2 = is_class_strided(d->kind) || d->kind == HPE_CONV_DGRAD1x1S2;
+  p.Ho = up2 ? d->H : pl->Ho;
+  p.Wo = up2 ? d->W : pl->Wo;
   p.B = d->B; p.Cout = d->Cout;
   p.act = d->act; p.has_res = d->has_residual ? 1 : 0;
   int tw = 1, th = 1, nb = 128;
@@ -615,9 +706,11 @@ static int encode_plan_maps(hpe_conv_plan* pl, const void* x, const void* w, con
     HPE_CHECK_ARG(((uintptr_t)y & 15) == 0, "hpe_conv_run: y must be 16-byte aligned");
     const uint64_t C = d.Cout;
     const uint32_t box[4] = {64, (uint32_t)p.tw, (uint32_t)p.th, (uint32_t)p.nb};
-    if (d.kind == HPE_CONV_DECONV4) {
+    if (is_class_strided(d.kind) || d.kind == HPE_CONV_DGRAD1x1S2) {
       const uint64_t Wo = pl->Wo, Ho = pl->Ho;
+      const int ncls = d.kind == HPE_CONV_DGRAD1x1S2 ? 1 : 4;
       for (int cls = 0; cls < 4; ++cls) {
+        if (cls >= ncls) { pl->tmOut.m[cls] = pl->tmOut.m[0]; continue; }
         const int py = cls >> 1, px = cls & 1;
         const char* base = (const char*)y + ((size_t)py * Wo + px) * C * 2;
         const uint64_t dims[4] = {C, (uint64_t)d.W, (uint64_t)d.H, (uint64_t)d.B};
@@ -651,7 +744,10 @@ extern "C" int hpe_conv_run(hpe_conv_plan* pl, const void* x, const void* w_pack
                             const float* shift, const void* residual, void* y, void* stream) {
   HPE_CHECK_ARG(pl && x && w_packed && scale && shift && y, "hpe_conv_run: null pointer");
   HPE_CHECK_ARG((((uintptr_t)scale | (uintptr_t)shift) & 15) == 0, "hpe_conv_run: scale/shift must be 16-byte aligned");
-  if (pl->d.kind == HPE_CONV_DECONV4 && pl->p.has_res) return fail(HPE_EUNSUPPORTED, "hpe_conv_run: deconv has no residual input");
+  if ((is_class_strided(pl->d.kind) || pl->d.kind == HPE_CONV_DGRAD1x1S2) && pl->p.has_res)
+    return fail(HPE_EUNSUPPORTED, "hpe_conv_run: the strided-store kinds have no residual input");
+  if (pl->d.kind == HPE_CONV_DGRAD1x1S2)      // odd rows/columns of dx receive no gradient
+    HPE_CUDA_OK(cudaMemsetAsync(y, 0, (size_t)pl->d.B * pl->Ho * pl->Wo * pl->d.Cout * 2, (cudaStream_t)stream));
   int rc = encode_plan_maps(pl, x, w_packed, residual, y);
   if (rc) return rc;
   ConvParams p = pl->p;

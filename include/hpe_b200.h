@@ -119,6 +119,10 @@ typedef struct hpe_conv_plan hpe_conv_plan;
 #define HPE_CONV_STEM7x7  2   /* 7x7 s2 p3 on the space-to-depth image written by hpe_preprocess */
 #define HPE_CONV_DECONV4  3   /* ConvTranspose2d k4 s2 p1 as four 2x2 sub-pixel convolutions    */
 #define HPE_CONV_FINAL    4   /* 1x1 -> K joints (+bias), writes fp32 NCHW heatmaps             */
+/* backward-data kinds (training): built with hpe_conv_dgrad_desc / hpe_conv_pack_weight_dgrad        */
+#define HPE_CONV_DGRAD3x3S2 5 /* dgrad of 3x3/s2/p1: four output-parity classes with 1/2/2/4 taps  */
+#define HPE_CONV_DGRAD1x1S2 6 /* dgrad of 1x1/s2: GEMM stored to the even pixels, rest zeroed      */
+#define HPE_CONV_4x4S2      7 /* dgrad of the k4/s2/p1 transposed conv = 4x4 stride-2 conv, 16 taps */
 
 typedef struct hpe_conv_desc {
   int kind;                 /* HPE_CONV_*                                         */
@@ -159,6 +163,15 @@ int  hpe_maxpool3x3s2(const void* x, int B, int H, int W, int C, void* y, void* 
  *   workspace  fp32 scratch of hpe_wgrad_workspace_elems(plan) elements
  *   dw_torch   fp32, same shape as the layer's PyTorch weight; overwritten, or added to if accumulate != 0
  * ---------------------------------------------------------------------------------------------- */
+/* Backward-data convolution of a forward layer: `g` receives the descriptor of the conv that maps
+ * dz [B,Ho,Wo,Cout] to dx [B,H,W,Cin] (run it with hpe_conv_plan_create/hpe_conv_run; the epilogue's
+ * residual input doubles as gradient accumulation: dx = dgrad(dz) + residual).  FINAL: dz is the
+ * [B,H,W,64] zero-padded NHWC bf16 heatmap gradient.  The stem has no dgrad (image needs no gradient). */
+int hpe_conv_dgrad_desc(const hpe_conv_desc* fwd_desc, hpe_conv_desc* g);
+/* pack the FORWARD PyTorch-layout fp32 weight for that backward-data conv
+ * (hpe_conv_packed_weight_elems(g) bf16 elements) */
+int hpe_conv_pack_weight_dgrad(const hpe_conv_desc* fwd_desc, const float* w_torch, void* w_packed, void* stream);
+
 typedef struct hpe_wgrad_plan hpe_wgrad_plan;
 int    hpe_wgrad_plan_create(const hpe_conv_desc* fwd_desc, hpe_wgrad_plan** out);
 void   hpe_wgrad_plan_destroy(hpe_wgrad_plan* plan);
