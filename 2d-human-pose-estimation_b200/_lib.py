@@ -46,6 +46,14 @@ SIGNATURES = {
     "hpe_maxpool3x3s2": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "hpe_conv_dgrad_desc": (_i, [C.POINTER(ConvDesc), C.POINTER(ConvDesc)]),
     "hpe_conv_pack_weight_dgrad": (_i, [C.POINTER(ConvDesc), _vp, _vp, _vp]),
+    "hpe_bn_stats": (_i, [_vp, C.c_longlong, _i, _vp, _vp, _f, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "hpe_bn_apply": (_i, [_vp, C.c_longlong, _i, _vp, _vp, _vp, _i, _vp, _vp]),
+    "hpe_bn_scratch_elems": (_sz, [_i]),
+    "hpe_bn_backward": (_i, [_vp, _vp, _vp, C.c_longlong, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "hpe_maxpool3x3s2_train": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp]),
+    "hpe_maxpool3x3s2_backward": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp]),
+    "hpe_heatmap_grad_nhwc": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
+    "hpe_sgd_step": (_i, [_vp, _vp, _vp, C.c_longlong, _f, _f, _f, _f, _vp]),
     "hpe_wgrad_plan_create": (_i, [C.POINTER(ConvDesc), C.POINTER(_vp)]),
     "hpe_wgrad_plan_destroy": (None, [_vp]),
     "hpe_wgrad_workspace_elems": (_sz, [_vp]),

@@ -1,0 +1,414 @@
+// Bandwidth-bound kernels of the training step (NHWC bf16 activations, fp32 statistics / parameters):
+// BatchNorm batch statistics + apply (+residual, ReLU), BatchNorm backward (two passes), MaxPool with
+// saved argmax + its backward, heatmap-gradient layout change, SGD momentum step.
+// All are plain vectorised (16-byte) grid-stride kernels: one pass over the tensor each, fp32 math.
+#include "hpe_common.cuh"
+
+namespace hpe {
+
+__device__ __forceinline__ void unpack8(const uint4& v, float* f) {
+  f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
+  f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
+}
+__device__ __forceinline__ uint4 pack8(const float* f) {
+  return make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+}
+
+// ---- per-channel reductions over the M = B*H*W rows of an [M][C] tensor --------------------------------
+// MODE 0: out0 = sum z, out1 = sum z^2                       (BatchNorm batch statistics)
+// MODE 1: g = relu ? (y > 0 ? dy : 0) : dy;  out0 = sum g,  out1 = sum g * (z - mean) * rstd   (BN backward)
+// 256 threads = (256 / (C/8)) rows x (C/8) 16-byte channel vectors; 4 rows in flight per thread.
+// Deterministic: every block writes its partial sums to part[blockIdx.x][2C]; bn_collect_kernel adds the
+// partials in a fixed order (no atomics), so the forward pass is bit-reproducible run to run.
+template <int MODE>
+__global__ void __launch_bounds__(256)
+bn_reduce_kernel(const __nv_bfloat16* __restrict__ z, const __nv_bfloat16* __restrict__ dy,
+                 const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean, const float* __restrict__ rstd,
+                 int relu, long long M, int C, float* __restrict__ part) {
+  __shared__ float red[256][17];
+  const int cv = C >> 3, rpp = 256 / cv;
+  const int vec = threadIdx.x % cv, r0 = threadIdx.x / cv;
+  float a0[8], a1[8], mu[8], rs[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) { a0[e] = 0.f; a1[e] = 0.f; mu[e] = 0.f; rs[e] = 1.f; }
+  if (MODE == 1) {
+#pragma unroll
+    for (int e = 0; e < 8; ++e) { mu[e] = mean[vec * 8 + e]; rs[e] = rstd[vec * 8 + e]; }
+  }
+  const long long step = static_cast<long long>(gridDim.x) * rpp;
+  if (r0 < rpp) {
+    for (long long row = static_cast<long long>(blockIdx.x) * rpp + r0; row < M; row += 4 * step) {
+      uint4 vz[4], vd[4], vy[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const long long r = row + u * step;
+        if (r < M) {
+          const size_t off = static_cast<size_t>(r) * cv + vec;
+          vz[u] = __ldg(reinterpret_cast<const uint4*>(z) + off);
+          if (MODE == 1) {
+            vd[u] = __ldg(reinterpret_cast<const uint4*>(dy) + off);
+            if (relu) vy[u] = __ldg(reinterpret_cast<const uint4*>(y) + off);
+          }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (row + u * step < M) {
+          float fz[8]; unpack8(vz[u], fz);
+          if (MODE == 0) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) { a0[e] += fz[e]; a1[e] = fmaf(fz[e], fz[e], a1[e]); }
+          } else {
+            float fd[8], fy[8]; unpack8(vd[u], fd);
+            if (relu) unpack8(vy[u], fy);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const float g = (relu && !(fy[e] > 0.f)) ? 0.f : fd[e];
+              a0[e] += g; a1[e] = fmaf(g, (fz[e] - mu[e]) * rs[e], a1[e]);
+            }
+          }
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < 8; ++e) { red[threadIdx.x][e] = a0[e]; red[threadIdx.x][8 + e] = a1[e]; }
+  __syncthreads();
+  // thread t < cv*16 handles (vec = t / 16, component = t % 16): sum over the rpp rows
+  for (int t = threadIdx.x; t < cv * 16; t += 256) {
+    const int v = t >> 4, comp = t & 15;
+    float s = 0.f;
+    for (int r = 0; r < rpp; ++r) s += red[r * cv + v][comp];
+    part[static_cast<size_t>(blockIdx.x) * 2 * C + (comp < 8 ? 0 : C) + v * 8 + (comp & 7)] = s;
+  }
+}
+
+// Fixed-order sum of the per-block partials, then
+// MODE 0: BatchNorm finalize (scale/shift/mean/rstd + running statistics);  MODE 1: dbeta = sum0, dgamma = sum1.
+// block = 32 channels x 8 slices of the partial list.
+template <int MODE>
+__global__ void __launch_bounds__(256)
+bn_collect_kernel(const float* __restrict__ part, int nparts, long long M, int C,
+                  const float* __restrict__ gamma, const float* __restrict__ beta, float eps, float momentum,
+                  float* running_mean, float* running_var, float* __restrict__ o0, float* __restrict__ o1,
+                  float* __restrict__ o2, float* __restrict__ o3) {
+  __shared__ float sm[2][8][32];
+  const int cl = threadIdx.x & 31, r = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + cl;
+  float s0 = 0.f, s1 = 0.f;
+  if (c < C)
+    for (int b = r; b < nparts; b += 8) {
+      s0 += part[static_cast<size_t>(b) * 2 * C + c];
+      s1 += part[static_cast<size_t>(b) * 2 * C + C + c];
+    }
+  sm[0][r][cl] = s0; sm[1][r][cl] = s1;
+  __syncthreads();
+  if (r != 0 || c >= C) return;
+  s0 = 0.f; s1 = 0.f;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) { s0 += sm[0][k][cl]; s1 += sm[1][k][cl]; }
+  if (MODE == 1) { o0[c] = s0; o1[c] = s1; return; }
+  const float inv = 1.f / static_cast<float>(M);
+  const float mu = s0 * inv;
+  const float var = fmaxf(s1 * inv - mu * mu, 0.f);
+  const float rs = rsqrtf(var + eps);
+  const float sc = gamma[c] * rs;
+  o0[c] = sc; o1[c] = beta[c] - mu * sc; o2[c] = mu; o3[c] = rs;
+  if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mu;
+  if (running_var) {
+    const float unbiased = M > 1 ? var * static_cast<float>(M) / static_cast<float>(M - 1) : var;
+    running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+  }
+}
+
+// y = act(z * scale + shift (+ res))
+__global__ void __launch_bounds__(256)
+bn_apply_kernel(const __nv_bfloat16* __restrict__ z, const float* __restrict__ scale, const float* __restrict__ shift,
+                const __nv_bfloat16* __restrict__ res, int relu, long long nvec, int cv, __nv_bfloat16* __restrict__ y) {
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c0 = static_cast<int>(i % cv) * 8;
+    float f[8]; unpack8(__ldg(reinterpret_cast<const uint4*>(z) + i), f);
+    const float4 s0 = __ldg(reinterpret_cast<const float4*>(scale + c0)), s1 = __ldg(reinterpret_cast<const float4*>(scale + c0 + 4));
+    const float4 h0 = __ldg(reinterpret_cast<const float4*>(shift + c0)), h1 = __ldg(reinterpret_cast<const float4*>(shift + c0 + 4));
+    f[0] = fmaf(f[0], s0.x, h0.x); f[1] = fmaf(f[1], s0.y, h0.y); f[2] = fmaf(f[2], s0.z, h0.z); f[3] = fmaf(f[3], s0.w, h0.w);
+    f[4] = fmaf(f[4], s1.x, h1.x); f[5] = fmaf(f[5], s1.y, h1.y); f[6] = fmaf(f[6], s1.z, h1.z); f[7] = fmaf(f[7], s1.w, h1.w);
+    if (res) {
+      float r[8]; unpack8(__ldg(reinterpret_cast<const uint4*>(res) + i), r);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) f[e] += r[e];
+    }
+    if (relu) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.f);
+    }
+    reinterpret_cast<uint4*>(y)[i] = pack8(f);
+  }
+}
+
+// dz = gamma*rstd * (g - sum_g/M - xhat * sum_gxhat/M);  optionally g_out = g (the masked gradient, for the shortcut)
+__global__ void __launch_bounds__(256)
+bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
+                    const __nv_bfloat16* __restrict__ z, const float* __restrict__ mean, const float* __restrict__ rstd,
+                    const float* __restrict__ gamma, const float* __restrict__ sum_g, const float* __restrict__ sum_gx,
+                    int relu, float inv_m, long long nvec, int cv, __nv_bfloat16* __restrict__ dz,
+                    __nv_bfloat16* __restrict__ g_out) {
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c0 = static_cast<int>(i % cv) * 8;
+    float fd[8], fz[8], fy[8], o[8];
+    unpack8(__ldg(reinterpret_cast<const uint4*>(dy) + i), fd);
+    unpack8(__ldg(reinterpret_cast<const uint4*>(z) + i), fz);
+    if (relu) unpack8(__ldg(reinterpret_cast<const uint4*>(y) + i), fy);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int c = c0 + e;
+      const float g = (relu && !(fy[e] > 0.f)) ? 0.f : fd[e];
+      const float rs = rstd[c];
+      const float xh = (fz[e] - mean[c]) * rs;
+      o[e] = gamma[c] * rs * (g - sum_g[c] * inv_m - xh * sum_gx[c] * inv_m);
+      fd[e] = g;
+    }
+    reinterpret_cast<uint4*>(dz)[i] = pack8(o);
+    if (g_out) reinterpret_cast<uint4*>(g_out)[i] = pack8(fd);
+  }
+}
+
+__device__ __forceinline__ bool bf16_gt(uint16_t a, uint16_t b) {
+  return __uint_as_float(static_cast<uint32_t>(a) << 16) > __uint_as_float(static_cast<uint32_t>(b) << 16);
+}
+
+// MaxPool 3x3 s2 p1 forward that also records which window position (ky*3+kx) won (first max in scan order,
+// torch semantics), 8 channels per thread
+__global__ void __launch_bounds__(256)
+maxpool_idx_kernel(const __nv_bfloat16* __restrict__ x, int B, int H, int W, int C, __nv_bfloat16* __restrict__ y,
+                   uint8_t* __restrict__ idx) {
+  const int Ho = (H - 1) / 2 + 1, Wo = (W - 1) / 2 + 1, Cv = C / 8;
+  const long long total = static_cast<long long>(B) * Ho * Wo * Cv;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int cv = static_cast<int>(i % Cv);
+    const int ox = static_cast<int>((i / Cv) % Wo);
+    const int oy = static_cast<int>((i / (static_cast<long long>(Cv) * Wo)) % Ho);
+    const int b  = static_cast<int>(i / (static_cast<long long>(Cv) * Wo * Ho));
+    uint16_t best[8]; uint8_t bi[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) { best[e] = 0xFF80; bi[e] = 0; }      // -inf
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky) {
+      const int iy = 2 * oy - 1 + ky;
+      if (iy < 0 || iy >= H) continue;
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) {
+        const int ix = 2 * ox - 1 + kx;
+        if (ix < 0 || ix >= W) continue;
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(x + ((static_cast<size_t>(b) * H + iy) * W + ix) * C) + cv);
+        const uint16_t* h = reinterpret_cast<const uint16_t*>(&v);
+#pragma unroll
+        for (int e = 0; e < 8; ++e)
+          if (bf16_gt(h[e], best[e])) { best[e] = h[e]; bi[e] = static_cast<uint8_t>(ky * 3 + kx); }
+      }
+    }
+    uint4 o; uint16_t* oh = reinterpret_cast<uint16_t*>(&o);
+    uint2 oi; uint8_t* ob = reinterpret_cast<uint8_t*>(&oi);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) { oh[e] = best[e]; ob[e] = bi[e]; }
+    reinterpret_cast<uint4*>(y)[i] = o;
+    reinterpret_cast<uint2*>(idx)[i] = oi;
+  }
+}
+
+// dx[b,iy,ix,c] = sum of dy over the (<= 4) windows that contain the pixel and whose argmax is this pixel
+__global__ void __launch_bounds__(256)
+maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const uint8_t* __restrict__ idx, int B, int H, int W, int C,
+                   __nv_bfloat16* __restrict__ dx) {
+  const int Ho = (H - 1) / 2 + 1, Wo = (W - 1) / 2 + 1, Cv = C / 8;
+  const long long total = static_cast<long long>(B) * H * W * Cv;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int cv = static_cast<int>(i % Cv);
+    const int ix = static_cast<int>((i / Cv) % W);
+    const int iy = static_cast<int>((i / (static_cast<long long>(Cv) * W)) % H);
+    const int b  = static_cast<int>(i / (static_cast<long long>(Cv) * W * H));
+    float acc[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+    // windows along one axis: even pixel 2a -> (o=a, k=1); odd pixel 2a+1 -> (o=a, k=2), (o=a+1, k=0)
+    const int ny = (iy & 1) ? 2 : 1, nx = (ix & 1) ? 2 : 1;
+    for (int jy = 0; jy < ny; ++jy) {
+      const int oy = (iy >> 1) + jy, ky = (iy & 1) ? (jy ? 0 : 2) : 1;
+      if (oy >= Ho) continue;
+      for (int jx = 0; jx < nx; ++jx) {
+        const int ox = (ix >> 1) + jx, kx = (ix & 1) ? (jx ? 0 : 2) : 1;
+        if (ox >= Wo) continue;
+        const size_t o = ((static_cast<size_t>(b) * Ho + oy) * Wo + ox) * Cv + cv;
+        const uint2 vi = __ldg(reinterpret_cast<const uint2*>(idx) + o);
+        const uint4 vd = __ldg(reinterpret_cast<const uint4*>(dy) + o);
+        const uint8_t* pi = reinterpret_cast<const uint8_t*>(&vi);
+        float fd[8]; unpack8(vd, fd);
+        const uint8_t want = static_cast<uint8_t>(ky * 3 + kx);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) if (pi[e] == want) acc[e] += fd[e];
+      }
+    }
+    reinterpret_cast<uint4*>(dx)[i] = pack8(acc);
+  }
+}
+
+// dL/dheatmap [B,K,H,W] (f32 | bf16, NCHW) -> [B,H,W,64] bf16 NHWC, joints zero-padded (the final conv's dgrad /
+// wgrad operand); also dbias[k] = sum over b,y,x
+template <bool BF16>
+__global__ void __launch_bounds__(256)
+hm_grad_nhwc_kernel(const void* __restrict__ dhm, int B, int K, int HW, __nv_bfloat16* __restrict__ out, float* dbias) {
+  __shared__ float sb[64];
+  if (threadIdx.x < 64) sb[threadIdx.x] = 0.f;
+  __syncthreads();
+  const long long total = static_cast<long long>(B) * HW;
+  const int lane = threadIdx.x & 31;
+  for (long long base = static_cast<long long>(blockIdx.x) * blockDim.x; base < total;
+       base += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long i = base + threadIdx.x;
+    const bool ok = i < total;
+    const int b = ok ? static_cast<int>(i / HW) : 0, pix = ok ? static_cast<int>(i % HW) : 0;
+    for (int k0 = 0; k0 < 64; k0 += 8) {
+      float f[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const int k = k0 + e;
+        float v = 0.f;
+        if (ok && k < K) {
+          const size_t off = (static_cast<size_t>(b) * K + k) * HW + pix;
+          v = BF16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(dhm)[off]) : reinterpret_cast<const float*>(dhm)[off];
+        }
+        f[e] = v;
+        if (dbias && k < K) {                       // warp-uniform condition
+          float s = v;
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+          if (lane == 0) atomicAdd(&sb[k], s);
+        }
+      }
+      if (ok) reinterpret_cast<uint4*>(out + static_cast<size_t>(i) * 64 + k0)[0] = pack8(f);
+    }
+  }
+  __syncthreads();
+  if (dbias && threadIdx.x < K) atomicAdd(dbias + threadIdx.x, sb[threadIdx.x]);
+}
+
+// SGD with momentum (torch.optim.SGD, dampening 0, no nesterov):  g' = g*grad_scale + wd*p; m = mu*m + g'; p -= lr*m
+__global__ void __launch_bounds__(256)
+sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, long long n, float lr, float mu,
+           float wd, float grad_scale) {
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float pi = p[i];
+    const float gi = fmaf(g[i], grad_scale, wd * pi);
+    const float mi = fmaf(mu, m[i], gi);
+    m[i] = mi;
+    p[i] = pi - lr * mi;
+  }
+}
+
+static inline int ew_grid(long long n, int per_block = 256) {
+  long long g = (n + per_block - 1) / per_block;
+  const long long cap = static_cast<long long>(num_sms()) * 16;
+  return static_cast<int>(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+}  // namespace hpe
+
+using namespace hpe;
+
+static int bn_shape_ok(long long M, int C, const char* fn) {
+  HPE_CHECK_ARG(M > 0 && C >= 64 && C <= 2048 && (C & (C - 1)) == 0, "%s: C=%d must be a power of two in [64, 2048] and M > 0", fn, C);
+  return HPE_OK;
+}
+constexpr int kBnMaxParts = 592;            // 4 blocks per SM on B200; bounds the scratch
+static int reduce_grid(long long M, int C) {
+  const int rpp = 256 / (C / 8);
+  long long g = (M + (long long)rpp * 8 - 1) / ((long long)rpp * 8);
+  return (int)(g < 1 ? 1 : (g > kBnMaxParts ? kBnMaxParts : g));
+}
+
+extern "C" size_t hpe_bn_scratch_elems(int C) { return C > 0 ? (size_t)kBnMaxParts * 2 * C : 0; }
+
+extern "C" int hpe_bn_stats(const void* z, long long M, int C, const float* gamma, const float* beta, float eps,
+                            float momentum, float* running_mean, float* running_var, float* scratch, float* scale,
+                            float* shift, float* mean, float* rstd, void* stream) {
+  int rc = bn_shape_ok(M, C, "hpe_bn_stats");
+  if (rc) return rc;
+  HPE_CHECK_ARG(z && gamma && beta && scratch && scale && shift && mean && rstd, "hpe_bn_stats: null pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int grid = reduce_grid(M, C);
+  bn_reduce_kernel<0><<<grid, 256, 0, st>>>((const __nv_bfloat16*)z, nullptr, nullptr, nullptr, nullptr, 0, M, C, scratch);
+  bn_collect_kernel<0><<<(C + 31) / 32, 256, 0, st>>>(scratch, grid, M, C, gamma, beta, eps, momentum, running_mean,
+                                                      running_var, scale, shift, mean, rstd);
+  return launch_status("bn_stats");
+}
+
+extern "C" int hpe_bn_apply(const void* z, long long M, int C, const float* scale, const float* shift, const void* residual,
+                            int relu, void* y, void* stream) {
+  int rc = bn_shape_ok(M, C, "hpe_bn_apply");
+  if (rc) return rc;
+  HPE_CHECK_ARG(z && scale && shift && y, "hpe_bn_apply: null pointer");
+  const long long nvec = M * (C / 8);
+  bn_apply_kernel<<<ew_grid(nvec), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)z, scale, shift,
+                                                                  (const __nv_bfloat16*)residual, relu, nvec, C / 8,
+                                                                  (__nv_bfloat16*)y);
+  return launch_status("bn_apply_kernel");
+}
+
+extern "C" int hpe_bn_backward(const void* dy, const void* y, const void* z, long long M, int C, const float* mean,
+                               const float* rstd, const float* gamma, int relu, float* scratch, float* dbeta,
+                               float* dgamma, void* dz, void* g_out, void* stream) {
+  int rc = bn_shape_ok(M, C, "hpe_bn_backward");
+  if (rc) return rc;
+  HPE_CHECK_ARG(dy && z && mean && rstd && gamma && scratch && dbeta && dgamma && dz && (y || !relu), "hpe_bn_backward: null pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int grid = reduce_grid(M, C);
+  bn_reduce_kernel<1><<<grid, 256, 0, st>>>((const __nv_bfloat16*)z, (const __nv_bfloat16*)dy, (const __nv_bfloat16*)y, mean,
+                                            rstd, relu, M, C, scratch);
+  bn_collect_kernel<1><<<(C + 31) / 32, 256, 0, st>>>(scratch, grid, M, C, nullptr, nullptr, 0.f, 0.f, nullptr, nullptr,
+                                                      dbeta, dgamma, nullptr, nullptr);
+  const long long nvec = M * (C / 8);
+  bn_bwd_apply_kernel<<<ew_grid(nvec), 256, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)y, (const __nv_bfloat16*)z,
+                                                    mean, rstd, gamma, dbeta, dgamma, relu, 1.f / (float)M, nvec, C / 8,
+                                                    (__nv_bfloat16*)dz, (__nv_bfloat16*)g_out);
+  return launch_status("bn_backward");
+}
+
+extern "C" int hpe_maxpool3x3s2_train(const void* x, int B, int H, int W, int C, void* y, uint8_t* idx, void* stream) {
+  HPE_CHECK_ARG(x && y && idx, "hpe_maxpool3x3s2_train: null pointer");
+  HPE_CHECK_ARG(B > 0 && H > 0 && W > 0 && C > 0 && C % 8 == 0, "hpe_maxpool3x3s2_train: C must be a positive multiple of 8");
+  const long long total = (long long)B * ((H - 1) / 2 + 1) * ((W - 1) / 2 + 1) * (C / 8);
+  maxpool_idx_kernel<<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, B, H, W, C, (__nv_bfloat16*)y, idx);
+  return launch_status("maxpool_idx_kernel");
+}
+
+extern "C" int hpe_maxpool3x3s2_backward(const void* dy, const uint8_t* idx, int B, int H, int W, int C, void* dx, void* stream) {
+  HPE_CHECK_ARG(dy && idx && dx, "hpe_maxpool3x3s2_backward: null pointer");
+  HPE_CHECK_ARG(B > 0 && H > 0 && W > 0 && C > 0 && C % 8 == 0, "hpe_maxpool3x3s2_backward: C must be a positive multiple of 8");
+  const long long total = (long long)B * H * W * (C / 8);
+  maxpool_bwd_kernel<<<ew_grid(total), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)dy, idx, B, H, W, C, (__nv_bfloat16*)dx);
+  return launch_status("maxpool_bwd_kernel");
+}
+
+extern "C" int hpe_heatmap_grad_nhwc(const void* dhm, int dtype, int B, int K, int H, int W, void* out, float* dbias, void* stream) {
+  HPE_CHECK_ARG(dhm && out, "hpe_heatmap_grad_nhwc: null pointer");
+  HPE_CHECK_ARG(B > 0 && K > 0 && K <= 64 && H > 0 && W > 0, "hpe_heatmap_grad_nhwc: need 0 < K <= 64");
+  HPE_CHECK_ARG(dtype == HPE_F32 || dtype == HPE_BF16, "hpe_heatmap_grad_nhwc: bad dtype %d", dtype);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dbias) HPE_CUDA_OK(cudaMemsetAsync(dbias, 0, (size_t)K * sizeof(float), st));
+  const long long total = (long long)B * H * W;
+  const int grid = ew_grid(total);
+  if (dtype == HPE_BF16) hm_grad_nhwc_kernel<true><<<grid, 256, 0, st>>>(dhm, B, K, H * W, (__nv_bfloat16*)out, dbias);
+  else                   hm_grad_nhwc_kernel<false><<<grid, 256, 0, st>>>(dhm, B, K, H * W, (__nv_bfloat16*)out, dbias);
+  return launch_status("hm_grad_nhwc_kernel");
+}
+
+extern "C" int hpe_sgd_step(float* param, const float* grad, float* momentum_buf, long long n, float lr, float momentum,
+                            float weight_decay, float grad_scale, void* stream) {
+  HPE_CHECK_ARG(param && grad && momentum_buf && n > 0, "hpe_sgd_step: null pointer or empty");
+  sgd_kernel<<<ew_grid(n), 256, 0, (cudaStream_t)stream>>>(param, grad, momentum_buf, n, lr, momentum, weight_decay, grad_scale);
+  return launch_status("sgd_kernel");
+}

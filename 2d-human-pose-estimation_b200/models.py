@@ -92,6 +92,7 @@ class HeatmapPose(nn.Module):
         nn.init.normal_(self.final_layer.weight, std=0.001)
         nn.init.zeros_(self.final_layer.bias)
         self._plans = {}
+        self._layout = None
         self._weights_version = 0
         if pretrained:
             path = pretrained if isinstance(pretrained, str) else os.environ.get("HPE_B200_PRETRAINED", "")
@@ -128,14 +129,17 @@ class HeatmapPose(nn.Module):
 
     # ---- forward -----------------------------------------------------------------------------------
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        if self.training:
-            raise NotImplementedError("HeatmapPose: the training forward/backward through the conv stack is not built "
-                                      "yet (inference kernels only); call model.eval().  The loss stage "
-                                      "(JointsMSELoss) does provide dL/dheatmap.")
         if x.dim() != 4 or x.shape[1] != 3:
             raise ValueError(f"expected [B,3,H,W] input, got {tuple(x.shape)}")
         if not x.is_cuda:
             raise RuntimeError("libhpe_b200 has no CPU path: input must live on a CUDA (sm_100a) device")
+        if self.training:
+            # model.train() (HPE/engine/trainer.py:77-80): BatchNorm batch statistics, and a backward pass through
+            # the dgrad / wgrad kernels so `loss.backward()` fills every parameter's .grad (trainer.py:96-97)
+            from .train import _TrainForward
+            plan = self._train_plan(x)
+            plan.load_weights(self)               # the optimizer updates parameters in place between steps
+            return _TrainForward.apply(self, x, *self.parameters())
         key = (tuple(x.shape), x.device.index)
         plan = self._plans.get(key)
         if plan is None:
@@ -144,6 +148,21 @@ class HeatmapPose(nn.Module):
         if plan.weights_version != self._weights_version:
             plan.load_weights(self)
         return plan.run(x.float().contiguous())
+
+    def _train_plan(self, x):
+        from .train import TrainPlan
+        key = ("train", tuple(x.shape), x.device.index)
+        plan = self._plans.get(key)
+        if plan is None:
+            plan = TrainPlan(self, x.shape[0], x.shape[2], x.shape[3], x.device)
+            self._plans[key] = plan
+        return plan
+
+    def _param_layout(self):
+        from .train import ParamLayout
+        if getattr(self, "_layout", None) is None:
+            self._layout = ParamLayout(self)
+        return self._layout
 
     def forward_features(self, x):
         """``[B, 2048, H/32, W/32]`` fp32 NCHW view of the trunk output (timm ``forward_features`` analogue)."""

@@ -179,6 +179,35 @@ size_t hpe_wgrad_workspace_elems(const hpe_wgrad_plan* plan);
 int    hpe_wgrad_run(hpe_wgrad_plan* plan, const void* x, const void* dz, float* workspace, float* dw_torch,
                      int accumulate, void* stream);
 
+
+/* BatchNorm2d in training mode over an NHWC bf16 tensor z [M = B*H*W][C] (timm resnet.py:244-270 runs
+ * nn.BatchNorm2d with batch statistics under model.train(), HPE/engine/trainer.py:77-80).
+ * hpe_bn_stats: batch mean / biased variance -> scale = gamma*rstd, shift = beta - mean*scale, saved mean / rstd,
+ *   running statistics updated with `momentum` (unbiased variance), as torch does.
+ *   scratch = fp32 device scratch of hpe_bn_scratch_elems(C) elements (per-block partial sums, added in a fixed
+ *   order: no atomics, the statistics are bit-reproducible run to run).
+ * hpe_bn_apply: y = act(z*scale + shift (+ residual)), act = ReLU if relu != 0.
+ * hpe_bn_backward: g = relu ? dy*(y>0) : dy;  dbeta = sum g;  dgamma = sum g*xhat;
+ *   dz = gamma*rstd*(g - dbeta/M - xhat*dgamma/M);  g_out (optional) = g, the gradient of the residual input. */
+size_t hpe_bn_scratch_elems(int C);
+int hpe_bn_stats(const void* z, long long M, int C, const float* gamma, const float* beta, float eps, float momentum,
+                 float* running_mean, float* running_var, float* scratch, float* scale, float* shift,
+                 float* mean, float* rstd, void* stream);
+int hpe_bn_apply(const void* z, long long M, int C, const float* scale, const float* shift, const void* residual,
+                 int relu, void* y, void* stream);
+int hpe_bn_backward(const void* dy, const void* y, const void* z, long long M, int C, const float* mean,
+                    const float* rstd, const float* gamma, int relu, float* scratch, float* dbeta, float* dgamma,
+                    void* dz, void* g_out, void* stream);
+/* MaxPool 3x3 s2 p1 that records the winning window position (first max, torch semantics) and its backward. */
+int hpe_maxpool3x3s2_train(const void* x, int B, int H, int W, int C, void* y, uint8_t* idx, void* stream);
+int hpe_maxpool3x3s2_backward(const void* dy, const uint8_t* idx, int B, int H, int W, int C, void* dx, void* stream);
+/* dL/dheatmap [B,K,H,W] NCHW (f32|bf16) -> [B,H,W,64] bf16 NHWC, joints zero-padded; dbias[K] (optional) = sum. */
+int hpe_heatmap_grad_nhwc(const void* dhm, int dtype, int B, int K, int H, int W, void* out, float* dbias, void* stream);
+/* torch.optim.SGD step (momentum, weight decay, dampening 0) over a flat fp32 parameter buffer
+ * (`optimizer.step()`, HPE/engine/trainer.py:98-100): g' = grad*grad_scale + wd*p; m = mu*m + g'; p -= lr*m. */
+int hpe_sgd_step(float* param, const float* grad, float* momentum_buf, long long n, float lr, float momentum,
+                 float weight_decay, float grad_scale, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -203,3 +203,128 @@ def forward_bf16_emulated(model: HeatmapPoseRef, x: torch.Tensor, return_feature
         x = r(torch.relu(y * s[None, :, None, None] + b[None, :, None, None]))
     hm = F.conv2d(x, r(model.final_layer.weight), model.final_layer.bias)
     return (hm, feat) if return_features else hm
+
+
+def forward_train_bf16_emulated(model: HeatmapPoseRef, x: torch.Tensor, taps: dict = None):
+    """Training-mode forward (BatchNorm batch statistics) with the bf16 CUDA path's rounding points and a
+    straight-through gradient, so autograd gives the fp32 gradient of the network *as the kernels evaluate it*:
+    conv weights, the raw conv output z and the unit output y = relu(bn(z) + residual) are rounded to bf16,
+    statistics/affine are fp32 and computed from the rounded z.  Needed because the §8(d) random-init net in
+    train() mode amplifies any perturbation ~1.2x per block (BatchNorm removes a mean that is large against the
+    spread), so the plain fp32 forward and ANY bf16 evaluation of it legitimately drift apart by tens of percent
+    at the head; parity of the kernels is checked against this restatement, conditioning against the fp32 one.
+    Does not update running statistics.  ``taps`` (optional dict) receives every unit's z and y by conv name."""
+    import torch.nn.functional as F
+
+    def r(t):                                  # round to bf16, identity gradient
+        return t + (t.to(torch.bfloat16).to(torch.float32) - t).detach()
+
+    def unit(name, x, conv, bn, relu=True, res=None, transposed=False):
+        w = r(conv.weight)
+        z = F.conv_transpose2d(x, w, None, 2, 1) if transposed else F.conv2d(x, w, None, conv.stride, conv.padding)
+        z = r(z)
+        mean = z.mean((0, 2, 3))
+        var = ((z - mean[None, :, None, None]) ** 2).mean((0, 2, 3))
+        scale = bn.weight * torch.rsqrt(var + bn.eps)
+        shift = bn.bias - mean * scale
+        y = z * scale[None, :, None, None] + shift[None, :, None, None]
+        if res is not None:
+            y = y + res
+        if relu:
+            y = torch.relu(y)
+        y = r(y)
+        if taps is not None:
+            taps[name] = (z.detach(), y.detach())
+        return y
+
+    bb = model.backbone
+    x = unit("backbone.conv1", r(x), bb.conv1, bb.bn1)
+    x = bb.maxpool(x)
+    for lname in ("layer1", "layer2", "layer3", "layer4"):
+        for j, blk in enumerate(getattr(bb, lname)):
+            pre = f"backbone.{lname}.{j}"
+            s = x
+            y = unit(pre + ".conv1", x, blk.conv1, blk.bn1)
+            y = unit(pre + ".conv2", y, blk.conv2, blk.bn2)
+            if blk.downsample is not None:
+                s = unit(pre + ".downsample.0", x, blk.downsample[0], blk.downsample[1], relu=False)
+            x = unit(pre + ".conv3", y, blk.conv3, blk.bn3, relu=True, res=s)
+    for i in (0, 3, 6):
+        x = unit(f"deconv_layers.{i}", x, model.deconv_layers[i], model.deconv_layers[i + 1], transposed=True)
+    return F.conv2d(x, r(model.final_layer.weight), model.final_layer.bias)
+
+
+def teacher_forced_backward(model: HeatmapPoseRef, acts: dict, dhm: torch.Tensor):
+    """fp32 backward pass of the training step evaluated on SAVED forward state (``acts[conv_name] = {"x", "z"}``,
+    NCHW fp32 copies of what the CUDA path stored: each unit's input and raw conv output), walking the same
+    topology as ``HeatmapPoseRef.forward``.  Because the ReLU masks and BatchNorm statistics come from the same
+    stored tensors the kernels used, this isolates the backward kernels (BN backward, dgrad, wgrad, maxpool
+    backward) from the forward's chaotic sensitivity (see ``forward_train_bf16_emulated``).
+    Returns ``(grads, fwd_err)``: parameter-name -> gradient, and conv-name -> (max-abs error of the stored z
+    against conv(x) in fp32, relative to max|z|)."""
+    import torch.nn.functional as F
+
+    def r16(t):
+        return t.to(torch.bfloat16).to(torch.float32)
+
+    grads, fwd_err = {}, {}
+
+    def unit_bwd(cname, bname, conv, bn, dy, relu=True, res=None, transposed=False, need_dx=True):
+        x, z = acts[cname]["x"], acts[cname]["z"]
+        zz = z.clone().requires_grad_(True)
+        gam = bn.weight.detach().clone().requires_grad_(True)
+        bet = bn.bias.detach().clone().requires_grad_(True)
+        mean = zz.mean((0, 2, 3))
+        var = ((zz - mean[None, :, None, None]) ** 2).mean((0, 2, 3))
+        y = (zz - mean[None, :, None, None]) * torch.rsqrt(var + bn.eps)[None, :, None, None] * gam[None, :, None, None] \
+            + bet[None, :, None, None]
+        rr = None
+        if res is not None:
+            rr = res.clone().requires_grad_(True)
+            y = y + rr
+        if relu:
+            y = torch.relu(y)
+        y.backward(dy)
+        grads[bname + ".weight"], grads[bname + ".bias"] = gam.grad, bet.grad
+        dz = zz.grad
+        xx = x.clone().requires_grad_(need_dx)
+        ww = r16(conv.weight.detach()).requires_grad_(True)
+        zc = F.conv_transpose2d(xx, ww, None, 2, 1) if transposed else F.conv2d(xx, ww, None, conv.stride, conv.padding)
+        fwd_err[cname] = ((zc.detach() - z).abs().max() / z.abs().max().clamp_min(1e-30)).item()
+        zc.backward(dz)
+        grads[cname + ".weight"] = ww.grad
+        return (xx.grad if need_dx else None), (rr.grad if rr is not None else None)
+
+    # final 1x1 conv (+bias)
+    xf = acts["final_layer"]["x"].clone().requires_grad_(True)
+    wf = r16(model.final_layer.weight.detach()).requires_grad_(True)
+    bf = model.final_layer.bias.detach().clone().requires_grad_(True)
+    F.conv2d(xf, wf, bf).backward(dhm)
+    grads["final_layer.weight"], grads["final_layer.bias"] = wf.grad, bf.grad
+    d = xf.grad
+    for i in (6, 3, 0):
+        d, _ = unit_bwd(f"deconv_layers.{i}", f"deconv_layers.{i + 1}", model.deconv_layers[i], model.deconv_layers[i + 1], d,
+                        transposed=True)
+    bb = model.backbone
+    for lname in ("layer4", "layer3", "layer2", "layer1"):
+        blocks = list(getattr(bb, lname))
+        for j in range(len(blocks) - 1, -1, -1):
+            blk, pre = blocks[j], f"backbone.{lname}.{j}"
+            xin = acts[pre + ".conv1"]["x"]
+            if blk.downsample is not None:
+                short = acts[pre + ".downsample.0"]["y"]
+            else:
+                short = xin
+            dt2, g3 = unit_bwd(pre + ".conv3", pre + ".bn3", blk.conv3, blk.bn3, d, res=short)
+            dt1, _ = unit_bwd(pre + ".conv2", pre + ".bn2", blk.conv2, blk.bn2, dt2)
+            dx, _ = unit_bwd(pre + ".conv1", pre + ".bn1", blk.conv1, blk.bn1, dt1)
+            if blk.downsample is not None:
+                ds, _ = unit_bwd(pre + ".downsample.0", pre + ".downsample.1", blk.downsample[0], blk.downsample[1], g3,
+                                 relu=False)
+                d = dx + ds
+            else:
+                d = dx + g3
+    ys = acts["backbone.conv1"]["y"].clone().requires_grad_(True)
+    F.max_pool2d(ys, 3, 2, 1).backward(d)
+    unit_bwd("backbone.conv1", "backbone.bn1", bb.conv1, bb.bn1, ys.grad, need_dx=False)
+    return grads, fwd_err

@@ -1,0 +1,247 @@
+"""GPU parity of the training step (BASELINE configs[2]) against the CPU oracle: the fp32 torch.nn restatement of the
+network (oracle/resnet_ref.py, pinned bit-exact to the reference's timm ResNet-50) in train() mode with autograd, the
+App. A.5/A.6 loss, and torch.optim.SGD.
+
+Tolerances (stated, bf16 activations / activation gradients with fp32 accumulation vs an all-fp32 oracle):
+  * bandwidth kernels (BN stats/apply/backward, maxpool, SGD): fp32-level or one bf16 rounding of the output;
+  * end-to-end training step (see test_training_step_matches_oracle): heatmaps within 5e-2 relative L2 of the
+    bf16-emulating oracle forward; loss within 1e-4 relative of the oracle loss of the same heatmaps; every stored
+    conv output within one bf16 rounding of an fp32 conv of its stored input; every parameter gradient within
+    4e-2 relative L2 / cos >= 0.999 of the fp32 backward evaluated on the stored forward state (teacher forcing),
+    and cos >= 0.9 (conv weights) / 0.7 (BN affine) against the free-running fp32 oracle; BN running statistics within 2e-2.
+"""
+from importlib import import_module
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def r16(t):
+    return t.to(torch.bfloat16).to(torch.float32)
+
+
+def nhwc16(t):
+    return t.permute(0, 2, 3, 1).contiguous().to(torch.bfloat16).cuda()
+
+
+def nchw(t):
+    return t.float().cpu().permute(0, 3, 1, 2)
+
+
+def close_bf16(out, ref, what, rel=2 ** -7):
+    tol = ref.abs() * rel + 2e-3 * ref.abs().max()
+    bad = (out - ref).abs() > tol
+    assert not bad.any(), f"{what}: {int(bad.sum())}/{bad.numel()} outside tolerance, max err {(out - ref).abs().max():.4g}"
+
+
+@pytest.mark.parametrize("B,H,W,C,relu,res", [(4, 16, 12, 64, True, False), (3, 8, 6, 2048, True, True), (8, 10, 7, 256, False, False)])
+def test_batchnorm_train_fwd_bwd(hpe, cuda_dev, B, H, W, C, relu, res):
+    tr = import_module("2d-human-pose-estimation_b200.train")
+    g = torch.Generator().manual_seed(31)
+    z = r16(torch.randn(B, C, H, W, generator=g) * 2 + 0.5)
+    rs = r16(torch.randn(B, C, H, W, generator=g)) if res else None
+    dy = r16(torch.randn(B, C, H, W, generator=g))
+    bn = torch.nn.BatchNorm2d(C)
+    with torch.no_grad():
+        bn.weight.copy_(torch.rand(C, generator=g) + 0.5); bn.bias.copy_(torch.randn(C, generator=g) * 0.1)
+    bn_ref = torch.nn.BatchNorm2d(C); bn_ref.load_state_dict(bn.state_dict()); bn_ref.train()
+    zr = z.clone().requires_grad_(True)
+    rr = rs.clone().requires_grad_(True) if res else None
+    yr = bn_ref(zr)
+    if res:
+        yr = yr + rr
+    if relu:
+        yr = torch.relu(yr)
+    yr.backward(dy)
+
+    bn = bn.cuda()
+
+    class U:
+        pass
+    u = U()
+    f = lambda n: torch.empty(n, dtype=torch.float32, device="cuda")  # noqa: E731
+    u.scale, u.shift, u.mean, u.rstd = f(C), f(C), f(C), f(C)
+    zd = nhwc16(z)
+    y = torch.empty_like(zd)
+    tr.bn_stats(zd, bn, u)
+    tr.bn_apply(zd, u.scale, u.shift, nhwc16(rs) if res else None, relu, y)
+    torch.cuda.synchronize()
+    close_bf16(nchw(y), yr.detach(), "bn forward")
+    assert torch.allclose(bn.running_mean.cpu(), bn_ref.running_mean, atol=1e-5, rtol=1e-4)
+    assert torch.allclose(bn.running_var.cpu(), bn_ref.running_var, atol=1e-5, rtol=1e-4)
+    dz = torch.empty_like(zd); gout = torch.empty_like(zd) if res else None
+    dbeta, dgamma = f(C), f(C)
+    tr.bn_backward(nhwc16(dy), y if relu else None, zd, u.mean, u.rstd, bn.weight, relu, dbeta, dgamma, dz, gout)
+    torch.cuda.synchronize()
+    # the kernel masks with ITS y (bf16); elements whose oracle y is within rounding of 0 may differ -> compare where |y| is clear
+    clear = (yr.detach().abs() > 1e-2) | (not relu)
+    ref_dz = zr.grad
+    got_dz = nchw(dz)
+    tol = ref_dz.abs() * 2 ** -6 + 4e-3 * ref_dz.abs().max()
+    bad = ((got_dz - ref_dz).abs() > tol) & clear
+    assert bad.float().mean() < 1e-3, f"bn backward dz: {int(bad.sum())}/{bad.numel()} outside tolerance"
+    assert torch.allclose(dbeta.cpu(), bn_ref.bias.grad, rtol=2e-2, atol=2e-2 * bn_ref.bias.grad.abs().max().item())
+    assert torch.allclose(dgamma.cpu(), bn_ref.weight.grad, rtol=2e-2, atol=2e-2 * bn_ref.weight.grad.abs().max().item())
+    if res:
+        bad = ((nchw(gout) - rr.grad).abs() > rr.grad.abs() * 2 ** -7 + 1e-6) & clear
+        assert bad.float().mean() < 1e-3
+
+
+@pytest.mark.parametrize("B,H,W,C", [(4, 32, 24, 64), (2, 15, 9, 64)])
+def test_maxpool_train_and_backward(hpe, cuda_dev, B, H, W, C):
+    tr = import_module("2d-human-pose-estimation_b200.train")
+    g = torch.Generator().manual_seed(32)
+    x = r16(torch.relu(torch.randn(B, C, H, W, generator=g)))          # post-ReLU: many exact ties at 0
+    xr = x.clone().requires_grad_(True)
+    yr = F.max_pool2d(xr, 3, 2, 1)
+    dy = r16(torch.randn(yr.shape, generator=g))
+    yr.backward(dy)
+    Ho, Wo = yr.shape[2:]
+    y = torch.empty(B, Ho, Wo, C, dtype=torch.bfloat16, device="cuda")
+    idx = torch.empty(B, Ho, Wo, C, dtype=torch.uint8, device="cuda")
+    tr.maxpool_train(nhwc16(x), y, idx)
+    dx = torch.empty(B, H, W, C, dtype=torch.bfloat16, device="cuda")
+    tr.maxpool_backward(nhwc16(dy), idx, dx)
+    torch.cuda.synchronize()
+    assert torch.equal(nchw(y), yr.detach())
+    close_bf16(nchw(dx), xr.grad, "maxpool backward")
+
+
+def test_heatmap_grad_and_sgd(hpe, cuda_dev):
+    tr = import_module("2d-human-pose-estimation_b200.train")
+    g = torch.Generator().manual_seed(33)
+    B, K, H, W = 5, 17, 16, 12
+    dhm = torch.randn(B, K, H, W, generator=g)
+    out = torch.empty(B, H, W, 64, dtype=torch.bfloat16, device="cuda")
+    db = torch.empty(K, device="cuda")
+    tr.heatmap_grad_nhwc(dhm.cuda(), out, db)
+    torch.cuda.synchronize()
+    assert torch.equal(out[..., :K].float().cpu(), r16(dhm).permute(0, 2, 3, 1))
+    assert (out[..., K:] == 0).all()
+    assert torch.allclose(db.cpu(), dhm.sum((0, 2, 3)), rtol=1e-4, atol=1e-4)
+    n = 100003
+    p = torch.randn(n, generator=g); gr = torch.randn(n, generator=g); m = torch.randn(n, generator=g)
+    pr = p.clone().requires_grad_(True); pr.grad = gr.clone() * 0.5
+    opt = torch.optim.SGD([pr], lr=0.1, momentum=0.9, weight_decay=1e-3)
+    opt.state[pr]["momentum_buffer"] = m.clone()
+    opt.step()
+    pd, md = p.cuda(), m.cuda()
+    tr.sgd_step(pd, gr.cuda(), md, 0.1, 0.9, 1e-3, 0.5)
+    torch.cuda.synchronize()
+    assert torch.allclose(pd.cpu(), pr.detach(), rtol=1e-5, atol=1e-6)
+    assert torch.allclose(md.cpu(), opt.state[pr]["momentum_buffer"], rtol=1e-5, atol=1e-6)
+
+
+def _damped_oracle(damp=0.1):
+    """§8(d) synthetic net with the residual branches damped (bn3.gamma *= 0.1; timm's own default is
+    zero_init_last, i.e. 0).  With gamma ~ U(0.5,1.5) on bn3 the random-init net in train() mode amplifies ANY
+    perturbation ~1.2x per unit (measured: 2e-5 at the stem -> 0.3 at layer4 between two bf16 evaluations that
+    differ only in fp32 summation order), which makes end-to-end comparisons meaningless; damped, the same
+    perturbation grows to ~2e-2 at the heatmaps."""
+    from oracle import resnet_ref as rr
+    ref = rr.build_synthetic(17, seed=0, normalize=True)
+    with torch.no_grad():
+        for n, mod in ref.named_modules():
+            if n.endswith("bn3"):
+                mod.weight.mul_(damp)
+    return ref
+
+
+def _loss_from(hm, joints, sigma=2.0):
+    from oracle import heatmap_ref as hr
+    target, weight = hr.generate_target(joints.numpy(), hm.shape[2:], sigma)
+    t = torch.from_numpy(target); w = torch.from_numpy(weight).reshape(hm.shape[0], hm.shape[1], 1, 1)
+    return 0.5 * ((w * hm - w * t) ** 2).sum() / hm.numel()
+
+
+def _rel(a, b):
+    return ((a - b).norm() / (b.norm() + 1e-30)).item()
+
+
+def _cos(a, b):
+    return (torch.dot(a.flatten(), b.flatten()) / (a.norm() * b.norm() + 1e-30)).item()
+
+
+@pytest.mark.parametrize("B,H,W", [(8, 128, 96), (4, 256, 192)])
+def test_training_step_matches_oracle(hpe, cuda_dev, B, H, W):
+    from oracle import heatmap_ref as hr
+    from oracle import resnet_ref as rr
+    models = import_module("2d-human-pose-estimation_b200.models")
+    ref = _damped_oracle()
+    m = models.HeatmapPose(17, "resnet50", pretrained=False)
+    m.load_state_dict(ref.state_dict())
+    m = m.cuda().train()
+    x = torch.rand(B, 3, H, W, generator=torch.Generator().manual_seed(0))
+    joints = torch.from_numpy(hr.synth_joints(B, 17, (H, W)))
+    lr, mom, wd = 0.05, 0.9, 1e-4
+
+    # ---- oracle A: plain fp32 torch.nn network in train() mode (also advances its running statistics)
+    ref.train()
+    hm_ref = ref(x)
+    loss_ref = _loss_from(hm_ref, joints)
+    ref.zero_grad(); loss_ref.backward()
+    g_ref = {n: p.grad.clone() for n, p in ref.named_parameters()}
+    # ---- oracle B: the same forward with the kernels' bf16 rounding points
+    hm_emu = rr.forward_train_bf16_emulated(ref, x).detach()
+
+    # ---- drop-in mode: model(x) in train(), criterion, loss.backward() (the reference trainer's calls)
+    crit = hpe.JointsMSELoss()
+    hm = m(x.cuda())
+    hm.retain_grad()
+    loss = crit(hm, joints.cuda(), None)
+    loss.backward()
+    torch.cuda.synchronize()
+    assert _rel(hm.detach().cpu(), hm_emu) <= 5e-2, f"heatmaps vs bf16-emulating oracle: rel {_rel(hm.detach().cpu(), hm_emu):.3g}"
+    assert _rel(hm.detach().cpu(), hm_ref.detach()) <= 1e-1
+    assert abs(loss.item() - loss_ref.item()) <= 1e-3 * abs(loss_ref.item()), (loss.item(), loss_ref.item())
+    # loss of the kernel's own heatmaps, recomputed by the oracle: the 1e-4 bar of north_star
+    loss_same = _loss_from(hm.detach().cpu(), joints).item()
+    assert abs(loss.item() - loss_same) <= 1e-4 * abs(loss_same)
+    sd_ref = ref.state_dict()
+    for n, b in m.named_buffers():
+        if n.endswith("running_mean") or n.endswith("running_var"):
+            r = sd_ref[n]
+            assert (b.cpu() - r).abs().max().item() <= 2e-2 * max(r.abs().max().item(), 1.0), n
+
+    # ---- oracle C: fp32 backward evaluated on the kernels' stored forward state (teacher forcing)
+    plan = m._train_plan(x.cuda())
+    acts = plan.export_acts()
+    acts["backbone.conv1"]["x"] = r16(x)
+    g_tf, fwd_err = rr.teacher_forced_backward(ref, acts, hm.grad.cpu())
+    worst_fwd = max(fwd_err, key=fwd_err.get)
+    assert fwd_err[worst_fwd] <= 2 ** -8 + 1e-3, f"stored conv output of {worst_fwd} is off by {fwd_err[worst_fwd]:.3g} of max|z|"
+    worst = ("", 0.0, 1.0)
+    for n, p in m.named_parameters():
+        assert p.grad is not None, n
+        a, b = p.grad.detach().cpu(), g_tf[n]
+        rel, cos = _rel(a, b), _cos(a, b)
+        if rel > worst[1]:
+            worst = (n, rel, cos)
+        assert rel <= 4e-2 and cos >= 0.999, f"{n}: rel L2 err {rel:.3g}, cos {cos:.5f} vs the teacher-forced fp32 backward"
+        # conditioning check against the free-running fp32 oracle (ReLU masks differ where activations differ)
+        # (4-D weights; the per-channel BN gradients are cancelling sums of few hundred terms and move more)
+        floor = 0.9 if a.dim() == 4 else 0.7
+        assert _cos(a, g_ref[n]) >= floor, f"{n}: cos {_cos(a, g_ref[n]):.4f} vs the fp32 oracle"
+    print(f"worst parameter gradient vs teacher-forced fp32 backward: {worst[0]} rel {worst[1]:.3g} cos {worst[2]:.5f}")
+
+    # ---- fused mode on a fresh copy: TrainStep = forward + loss + backward + SGD on flat buffers
+    ref2 = _damped_oracle()
+    m2 = models.HeatmapPose(17, "resnet50", pretrained=False)
+    m2.load_state_dict(ref2.state_dict())
+    m2 = m2.cuda().train()
+    step = hpe.TrainStep(m2, lr=lr, momentum=mom, weight_decay=wd)
+    l2 = step(x.cuda(), joints.cuda().float().contiguous())
+    torch.cuda.synchronize()
+    assert abs(l2.item() - loss.item()) <= 1e-5 * abs(loss.item())
+    before = ref2.state_dict()
+    moms = step.layout.views(step.flat_mom)
+    for n, p in m2.named_parameters():
+        # first SGD step: momentum buffer = g + wd*p, p' = p - lr*buffer.  (The update itself is below fp32 resolution
+        # of p for many elements at this loss scale, so the buffer is what is compared against the drop-in gradients.)
+        want_m = m.get_parameter(n).grad.cpu() + wd * before[n]
+        assert _rel(moms[n].cpu(), want_m) <= 5e-3, f"{n}: momentum buffer rel err {_rel(moms[n].cpu(), want_m):.3g}"
+        assert torch.allclose(p.detach().cpu(), before[n] - lr * moms[n].cpu(), rtol=1e-6, atol=1e-9), n
