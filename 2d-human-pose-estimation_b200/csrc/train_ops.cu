@@ -37,10 +37,11 @@ bn_reduce_kernel(const __nv_bfloat16* __restrict__ z, const __nv_bfloat16* __res
   }
   const long long step = static_cast<long long>(gridDim.x) * rpp;
   if (r0 < rpp) {
-    for (long long row = static_cast<long long>(blockIdx.x) * rpp + r0; row < M; row += 4 * step) {
-      uint4 vz[4], vd[4], vy[4];
+    constexpr int U = MODE == 0 ? 8 : 4;
+    for (long long row = static_cast<long long>(blockIdx.x) * rpp + r0; row < M; row += U * step) {
+      uint4 vz[U], vd[U], vy[U];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < U; ++u) {
         const long long r = row + u * step;
         if (r < M) {
           const size_t off = static_cast<size_t>(r) * cv + vec;
@@ -52,7 +53,7 @@ bn_reduce_kernel(const __nv_bfloat16* __restrict__ z, const __nv_bfloat16* __res
         }
       }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < U; ++u) {
         if (row + u * step < M) {
           float fz[8]; unpack8(vz[u], fz);
           if (MODE == 0) {
@@ -84,20 +85,22 @@ bn_reduce_kernel(const __nv_bfloat16* __restrict__ z, const __nv_bfloat16* __res
 }
 
 // Fixed-order sum of the per-block partials, then
-// MODE 0: BatchNorm finalize (scale/shift/mean/rstd + running statistics);  MODE 1: dbeta = sum0, dgamma = sum1.
-// block = 32 channels x 8 slices of the partial list.
+// MODE 0: BatchNorm finalize (scale/shift/mean/rstd + running statistics);
+// MODE 1: dbeta = sum g, dgamma = sum g*xhat, and the per-channel coefficients of
+//         dz = A*g + Bz*z + C0  with  A = gamma*rstd, Bz = -gamma*rstd^2*dgamma/M, C0 = A*(mean*rstd*dgamma - dbeta)/M.
+// block = 32 channels x 32 slices of the partial list.
 template <int MODE>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 bn_collect_kernel(const float* __restrict__ part, int nparts, long long M, int C,
                   const float* __restrict__ gamma, const float* __restrict__ beta, float eps, float momentum,
                   float* running_mean, float* running_var, float* __restrict__ o0, float* __restrict__ o1,
-                  float* __restrict__ o2, float* __restrict__ o3) {
-  __shared__ float sm[2][8][32];
+                  float* __restrict__ o2, float* __restrict__ o3, float* __restrict__ coef) {
+  __shared__ float sm[2][32][33];
   const int cl = threadIdx.x & 31, r = threadIdx.x >> 5;
   const int c = blockIdx.x * 32 + cl;
   float s0 = 0.f, s1 = 0.f;
   if (c < C)
-    for (int b = r; b < nparts; b += 8) {
+    for (int b = r; b < nparts; b += 32) {
       s0 += part[static_cast<size_t>(b) * 2 * C + c];
       s1 += part[static_cast<size_t>(b) * 2 * C + C + c];
     }
@@ -106,9 +109,15 @@ bn_collect_kernel(const float* __restrict__ part, int nparts, long long M, int C
   if (r != 0 || c >= C) return;
   s0 = 0.f; s1 = 0.f;
 #pragma unroll
-  for (int k = 0; k < 8; ++k) { s0 += sm[0][k][cl]; s1 += sm[1][k][cl]; }
-  if (MODE == 1) { o0[c] = s0; o1[c] = s1; return; }
+  for (int k = 0; k < 32; ++k) { s0 += sm[0][k][cl]; s1 += sm[1][k][cl]; }
   const float inv = 1.f / static_cast<float>(M);
+  if (MODE == 1) {
+    o0[c] = s0; o1[c] = s1;                      // dbeta, dgamma
+    const float rs = o3[c], mu = o2[c];          // saved rstd, mean
+    const float A = gamma[c] * rs;
+    coef[c] = A; coef[C + c] = -A * rs * s1 * inv; coef[2 * C + c] = A * (mu * rs * s1 - s0) * inv;
+    return;
+  }
   const float mu = s0 * inv;
   const float var = fmaxf(s1 * inv - mu * mu, 0.f);
   const float rs = rsqrtf(var + eps);
@@ -146,27 +155,31 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ z, const float* __restrict__ s
   }
 }
 
-// dz = gamma*rstd * (g - sum_g/M - xhat * sum_gxhat/M);  optionally g_out = g (the masked gradient, for the shortcut)
+// dz = A*g + Bz*z + C0 (coefficients from bn_collect_kernel<1>);  optionally g_out = g (masked gradient, for the shortcut)
 __global__ void __launch_bounds__(256)
 bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
-                    const __nv_bfloat16* __restrict__ z, const float* __restrict__ mean, const float* __restrict__ rstd,
-                    const float* __restrict__ gamma, const float* __restrict__ sum_g, const float* __restrict__ sum_gx,
-                    int relu, float inv_m, long long nvec, int cv, __nv_bfloat16* __restrict__ dz,
-                    __nv_bfloat16* __restrict__ g_out) {
+                    const __nv_bfloat16* __restrict__ z, const float* __restrict__ coef, int C,
+                    int relu, long long nvec, int cv, __nv_bfloat16* __restrict__ dz, __nv_bfloat16* __restrict__ g_out) {
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
     const int c0 = static_cast<int>(i % cv) * 8;
-    float fd[8], fz[8], fy[8], o[8];
-    unpack8(__ldg(reinterpret_cast<const uint4*>(dy) + i), fd);
-    unpack8(__ldg(reinterpret_cast<const uint4*>(z) + i), fz);
-    if (relu) unpack8(__ldg(reinterpret_cast<const uint4*>(y) + i), fy);
+    float fd[8], fz[8], fy[8], o[8], ca[8], cb[8], cc[8];
+    const uint4 vd = __ldg(reinterpret_cast<const uint4*>(dy) + i);
+    const uint4 vz = __ldg(reinterpret_cast<const uint4*>(z) + i);
+    uint4 vy = make_uint4(0, 0, 0, 0);
+    if (relu) vy = __ldg(reinterpret_cast<const uint4*>(y) + i);
+    *reinterpret_cast<float4*>(ca) = __ldg(reinterpret_cast<const float4*>(coef + c0));
+    *reinterpret_cast<float4*>(ca + 4) = __ldg(reinterpret_cast<const float4*>(coef + c0 + 4));
+    *reinterpret_cast<float4*>(cb) = __ldg(reinterpret_cast<const float4*>(coef + C + c0));
+    *reinterpret_cast<float4*>(cb + 4) = __ldg(reinterpret_cast<const float4*>(coef + C + c0 + 4));
+    *reinterpret_cast<float4*>(cc) = __ldg(reinterpret_cast<const float4*>(coef + 2 * C + c0));
+    *reinterpret_cast<float4*>(cc + 4) = __ldg(reinterpret_cast<const float4*>(coef + 2 * C + c0 + 4));
+    unpack8(vd, fd); unpack8(vz, fz);
+    if (relu) unpack8(vy, fy);
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
-      const int c = c0 + e;
       const float g = (relu && !(fy[e] > 0.f)) ? 0.f : fd[e];
-      const float rs = rstd[c];
-      const float xh = (fz[e] - mean[c]) * rs;
-      o[e] = gamma[c] * rs * (g - sum_g[c] * inv_m - xh * sum_gx[c] * inv_m);
+      o[e] = fmaf(ca[e], g, fmaf(cb[e], fz[e], cc[e]));
       fd[e] = g;
     }
     reinterpret_cast<uint4*>(dz)[i] = pack8(o);
@@ -323,14 +336,15 @@ static int bn_shape_ok(long long M, int C, const char* fn) {
   HPE_CHECK_ARG(M > 0 && C >= 64 && C <= 2048 && (C & (C - 1)) == 0, "%s: C=%d must be a power of two in [64, 2048] and M > 0", fn, C);
   return HPE_OK;
 }
-constexpr int kBnMaxParts = 592;            // 4 blocks per SM on B200; bounds the scratch
+constexpr int kBnMaxParts = 1184;           // 8 blocks per SM on B200; bounds the scratch
 static int reduce_grid(long long M, int C) {
   const int rpp = 256 / (C / 8);
   long long g = (M + (long long)rpp * 8 - 1) / ((long long)rpp * 8);
   return (int)(g < 1 ? 1 : (g > kBnMaxParts ? kBnMaxParts : g));
 }
 
-extern "C" size_t hpe_bn_scratch_elems(int C) { return C > 0 ? (size_t)kBnMaxParts * 2 * C : 0; }
+// per-block partials [kBnMaxParts][2C] followed by the three backward coefficient arrays [3C]
+extern "C" size_t hpe_bn_scratch_elems(int C) { return C > 0 ? (size_t)kBnMaxParts * 2 * C + 3 * (size_t)C : 0; }
 
 extern "C" int hpe_bn_stats(const void* z, long long M, int C, const float* gamma, const float* beta, float eps,
                             float momentum, float* running_mean, float* running_var, float* scratch, float* scale,
@@ -341,8 +355,8 @@ extern "C" int hpe_bn_stats(const void* z, long long M, int C, const float* gamm
   cudaStream_t st = (cudaStream_t)stream;
   const int grid = reduce_grid(M, C);
   bn_reduce_kernel<0><<<grid, 256, 0, st>>>((const __nv_bfloat16*)z, nullptr, nullptr, nullptr, nullptr, 0, M, C, scratch);
-  bn_collect_kernel<0><<<(C + 31) / 32, 256, 0, st>>>(scratch, grid, M, C, gamma, beta, eps, momentum, running_mean,
-                                                      running_var, scale, shift, mean, rstd);
+  bn_collect_kernel<0><<<(C + 31) / 32, 1024, 0, st>>>(scratch, grid, M, C, gamma, beta, eps, momentum, running_mean,
+                                                       running_var, scale, shift, mean, rstd, nullptr);
   return launch_status("bn_stats");
 }
 
@@ -368,12 +382,12 @@ extern "C" int hpe_bn_backward(const void* dy, const void* y, const void* z, lon
   const int grid = reduce_grid(M, C);
   bn_reduce_kernel<1><<<grid, 256, 0, st>>>((const __nv_bfloat16*)z, (const __nv_bfloat16*)dy, (const __nv_bfloat16*)y, mean,
                                             rstd, relu, M, C, scratch);
-  bn_collect_kernel<1><<<(C + 31) / 32, 256, 0, st>>>(scratch, grid, M, C, nullptr, nullptr, 0.f, 0.f, nullptr, nullptr,
-                                                      dbeta, dgamma, nullptr, nullptr);
+  float* coef = scratch + (size_t)kBnMaxParts * 2 * C;
+  bn_collect_kernel<1><<<(C + 31) / 32, 1024, 0, st>>>(scratch, grid, M, C, gamma, nullptr, 0.f, 0.f, nullptr, nullptr,
+                                                       dbeta, dgamma, const_cast<float*>(mean), const_cast<float*>(rstd), coef);
   const long long nvec = M * (C / 8);
   bn_bwd_apply_kernel<<<ew_grid(nvec), 256, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)y, (const __nv_bfloat16*)z,
-                                                    mean, rstd, gamma, dbeta, dgamma, relu, 1.f / (float)M, nvec, C / 8,
-                                                    (__nv_bfloat16*)dz, (__nv_bfloat16*)g_out);
+                                                    coef, C, relu, nvec, C / 8, (__nv_bfloat16*)dz, (__nv_bfloat16*)g_out);
   return launch_status("bn_backward");
 }
 

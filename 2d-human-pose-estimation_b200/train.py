@@ -120,7 +120,7 @@ class _Unit:
         self.fwd.load(conv.weight)                 # scale = 1, shift = 0: the conv kernel writes the raw output z
         if self.dg is not None:
             self.dg.load(conv.weight)
-        self.bn = bn
+        self.bn, self.conv_mod = bn, conv
 
     def forward(self, x, residual=None):
         self.x = x
@@ -208,9 +208,20 @@ class TrainPlan:
         for u in self.units():
             u.load(mods[u.conv_name], mods[u.bn_name])
         fl = mods["final_layer"]
-        self.final.load(fl.weight, torch.ones(fl.out_channels), fl.bias)
+        self._final_mod = fl
+        self.final.scale.fill_(1.0)
+        self.final.load(fl.weight, None, fl.bias)
         self.final_dg.load(fl.weight)
         self.weights_version = model._weights_version
+
+    @torch.no_grad()
+    def repack(self):
+        """Re-pack the bf16 GEMM operands from the (updated) fp32 parameters: device-side kernels only, no host
+        tensors, so it can live inside a captured CUDA graph.  Needs one prior load_weights()."""
+        for u in self.units():
+            u.load(u.conv_mod, u.bn)
+        self.final.load(self._final_mod.weight, None, self._final_mod.bias)
+        self.final_dg.load(self._final_mod.weight)
 
     # ---- forward (training mode: batch statistics, running stats updated) --------------------------------------
     def forward(self, x):
@@ -315,8 +326,10 @@ class TrainStep:
     shard are summed over ranks with one NCCL all-reduce of the flat buffer and divided by the world size in the
     SGD kernel (equal shards => the global-batch mean)."""
 
-    def __init__(self, model, lr=1e-3, momentum=0.9, weight_decay=0.0, sigma=2.0, group=None):
+    def __init__(self, model, lr=1e-3, momentum=0.9, weight_decay=0.0, sigma=2.0, group=None, cuda_graph=True):
         self.model = model.train()
+        self.use_graph = bool(cuda_graph)
+        self._key, self.graph, self.plan = None, None, None
         self.lr, self.momentum, self.weight_decay, self.sigma = lr, momentum, weight_decay, sigma
         self.group = group
         self.layout = ParamLayout(model)
@@ -343,15 +356,11 @@ class TrainStep:
                 if b.dtype.is_floating_point:
                     dist.broadcast(b, src, group=self.group)
 
-    def __call__(self, images, joints):
-        model = self.model
-        plan = model._train_plan(images)
-        plan.load_weights(model)                      # parameters changed last step: re-pack bf16 GEMM operands
+    def _step(self, images, joints):
+        model, plan = self.model, self.plan
+        plan.repack()                                 # parameters changed last step: re-pack bf16 GEMM operands
         hm = plan.forward(images)
         B, K, H, W = hm.shape
-        if self.dhm is None or self.dhm.shape != hm.shape:
-            self.dhm = torch.empty_like(hm)
-            self.partials = torch.empty(B * K, dtype=torch.float32, device=hm.device)
         sx, sy = images.shape[3] / W, images.shape[2] / H
         with torch.cuda.device(hm.device):
             rc = _lib.lib().hpe_joints_mse_fused(_lib.ptr(hm), _lib.HPE_F32, _lib.ptr(joints), B, K, H, W, float(self.sigma),
@@ -362,5 +371,34 @@ class TrainStep:
         if self.world > 1:
             dist.all_reduce(self.flat_grad, op=dist.ReduceOp.SUM, group=self.group)
         sgd_step(self.flat_param, self.flat_grad, self.flat_mom, self.lr, self.momentum, self.weight_decay, 1.0 / self.world)
+
+    def __call__(self, images, joints):
+        model = self.model
+        key = (tuple(images.shape), tuple(joints.shape))
+        if self._key != key:
+            self._key, self.graph = key, None
+            self.plan = model._train_plan(images)
+            self.plan.load_weights(model)
+            hm = self.plan.heatmaps
+            self.dhm = torch.empty_like(hm)
+            self.partials = torch.empty(hm.shape[0] * hm.shape[1], dtype=torch.float32, device=hm.device)
+            self.x_static = torch.empty_like(images, dtype=torch.float32)
+            self.j_static = torch.empty_like(joints, dtype=torch.float32)
+            self._warm = 0
+        self.x_static.copy_(images)
+        self.j_static.copy_(joints)
+        if not self.use_graph:
+            self._step(self.x_static, self.j_static)
+        elif self.graph is None and self._warm < 1:
+            self._step(self.x_static, self.j_static)          # eager warm-up: encodes the TMA descriptors, NCCL init
+            self._warm += 1
+        else:
+            if self.graph is None:
+                torch.cuda.synchronize(self.device)
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    self._step(self.x_static, self.j_static)
+                self.graph = g
+            self.graph.replay()
         model._weights_version += 1
         return self.loss

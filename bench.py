@@ -293,8 +293,88 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
+def run_train(args):
+    """BASELINE configs[2]: data-parallel training step (forward with batch-stat BN, fused Gaussian-target MSE loss,
+    backward through dgrad/wgrad, ONE NCCL all-reduce of the flat fp32 gradient buffer, SGD) at N GPUs."""
+    import torch.distributed as dist
+    import hpe_b200 as hpe
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py --mode train: no CUDA device (no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    B, H, W, K = args.batch, args.height, args.width, args.joints
+    torch.manual_seed(0)
+    model = hpe.HeatmapPose(K, "resnet50", pretrained=False)
+    g = torch.Generator().manual_seed(1)
+    for n, m in model.named_modules():
+        if isinstance(m, torch.nn.BatchNorm2d):
+            m.weight.data.copy_((torch.rand(m.weight.shape, generator=g) + 0.5) * (0.1 if n.endswith("bn3") else 1.0))
+            m.bias.data.copy_(torch.randn(m.bias.shape, generator=g) * 0.1)
+    model = model.to(dev).train()
+    step = hpe.TrainStep(model, lr=1e-3, momentum=0.9, weight_decay=1e-4, cuda_graph=not args.no_graph)
+    step.broadcast_parameters(0)
+    gen = torch.Generator().manual_seed(100 + rank)
+    x = [torch.rand(B, 3, H, W, generator=gen).to(dev) for _ in range(2)]
+    joints = torch.rand(B, K, 3, generator=gen) * torch.tensor([float(W), float(H), 1.0]) + torch.tensor([0.0, 0.0, 0.3])
+    joints = joints.to(dev).contiguous()
+
+    def barrier():
+        if world > 1:
+            dist.barrier(device_ids=[local])
+        torch.cuda.synchronize(dev)
+
+    for i in range(max(args.warmup, 3)):
+        step(x[i & 1], joints)
+    barrier()
+    sampler = ClockSampler(physical_gpu_index(local)) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
+    start, end = ev(), ev()
+    barrier()
+    start.record()
+    for i in range(args.steps):
+        loss = step(x[i & 1], joints)
+    end.record()
+    barrier()
+    clocks = sampler.stop() if sampler else None
+    t = torch.tensor([start.elapsed_time(end)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    if rank == 0:
+        peaks = load_peaks()
+        flops_step = 3 * GFLOP_PER_IMG_256x192 * 1e9 * (H * W) / (256 * 192) * B      # fwd + dgrad + wgrad
+        ms = ms_total / args.steps
+        line = {
+            "metric": "images/sec train step @256x192 COCO-17", "value": round(world * B * args.steps / ms_total * 1e3, 1),
+            "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(ms, 4),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": f"resnet50+deconv-head data-parallel training step (batch-stat BN, fused Gaussian-target JointsMSE, "
+                                   f"dgrad+wgrad, NCCL all-reduce of {step.layout.total * 4 / 1e6:.0f} MB fp32 grads, SGD momentum), "
+                                   f"{H}x{W}, K={K}, batch {B}/GPU (BASELINE configs[2])",
+                       "global_batch": world * B, "parallelism": f"dp{world}"},
+            "roofline": {"bound": "tensor", "kernel": "conv_gemm_kernel + wgrad_gemm_kernel (whole step)",
+                         "achieved": round(flops_step / (ms * 1e-3) / 1e12, 2), "peak": peaks["tflops"], "unit": "TFLOP/s",
+                         "frac": round(flops_step / (ms * 1e-3) / 1e12 / peaks["tflops"], 4), "traffic": None,
+                         "note": "3x forward algorithmic FLOPs / step time; the step also contains the HBM-bound BN passes"},
+            "loss": float(loss.item()), "clocks": clocks,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--mode", default="infer", choices=["infer", "train"])
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
@@ -305,9 +385,12 @@ def main():
     ap.add_argument("--joints", type=int, default=17)
     ap.add_argument("--cpu-batch", type=int, default=32, help="images per CPU-baseline step (bounded sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="train mode: launch eagerly instead of replaying a CUDA graph")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.mode == "train":
+        run_train(args)
     else:
         run_b200(args)
 

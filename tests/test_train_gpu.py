@@ -245,3 +245,29 @@ def test_training_step_matches_oracle(hpe, cuda_dev, B, H, W):
         want_m = m.get_parameter(n).grad.cpu() + wd * before[n]
         assert _rel(moms[n].cpu(), want_m) <= 5e-3, f"{n}: momentum buffer rel err {_rel(moms[n].cpu(), want_m):.3g}"
         assert torch.allclose(p.detach().cpu(), before[n] - lr * moms[n].cpu(), rtol=1e-6, atol=1e-9), n
+
+
+def test_train_step_cuda_graph_matches_eager(hpe, cuda_dev):
+    """The captured-graph replay of the fused step (what bench.py --mode train times) follows the eager launches."""
+    from oracle import heatmap_ref as hr
+    models = import_module("2d-human-pose-estimation_b200.models")
+    B, H, W = 4, 128, 96
+    x = torch.rand(B, 3, H, W, generator=torch.Generator().manual_seed(0)).cuda()
+    joints = torch.from_numpy(hr.synth_joints(B, 17, (H, W))).cuda().float().contiguous()
+    losses, finals = [], []
+    for graph in (False, True):
+        ref = _damped_oracle()
+        m = models.HeatmapPose(17, "resnet50", pretrained=False)
+        m.load_state_dict(ref.state_dict())
+        m = m.cuda().train()
+        step = hpe.TrainStep(m, lr=0.05, momentum=0.9, weight_decay=1e-4, cuda_graph=graph)
+        ls = [step(x, joints).item() for _ in range(4)]
+        torch.cuda.synchronize()
+        assert (step.graph is not None) == graph
+        losses.append(ls)
+        finals.append(m.final_layer.weight.detach().cpu().clone())
+    assert losses[0][0] == losses[1][0]                       # identical first step (forward is bit-reproducible)
+    for a, b in zip(*losses):
+        assert abs(a - b) <= 1e-3 * abs(a), (losses[0], losses[1])
+    assert losses[0][-1] < losses[0][0]                       # the loss goes down
+    assert _rel(finals[1], finals[0]) <= 1e-2
