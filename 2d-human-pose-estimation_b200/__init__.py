@@ -15,6 +15,7 @@ from .decode import (HostDecoder, affine_from_center_scale, decode, get_final_pr
 from .loss import JointsMSELoss, generate_target
 from . import models
 from .models import DeepPose, HeatmapPose, build_model
+from . import train
 from .train import TrainPlan, TrainStep
 from .pipeline import PoseEstimator, gather_keypoints, gather_keypoints_equal, shard_range
 

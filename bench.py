@@ -369,7 +369,12 @@ def run_train(args):
         }
         print(json.dumps(line), flush=True)
     if world > 1:
-        dist.destroy_process_group()
+        # a live captured graph that contains the NCCL all-reduce has been seen to block communicator teardown:
+        # drop the graph first, and leave without the teardown once every rank is done
+        step.graph = None
+        barrier()
+        sys.stdout.flush(); sys.stderr.flush()
+        os._exit(0)
 
 
 def main():
