@@ -107,7 +107,9 @@ def test_model_boundary(hpe, cuda_dev):
     assert m.njoints == 17
     with pytest.raises(RuntimeError, match="no CPU path"):
         m.eval()(torch.zeros(1, 3, 64, 64))
-    with pytest.raises(NotImplementedError):
-        m.train()(torch.zeros(1, 3, 64, 64, device=cuda_dev))
+    # model.train() runs the batch-statistics forward and returns an autograd-connected heatmap (trainer.py:77-97)
+    out = m.to(cuda_dev).train()(torch.rand(2, 3, 64, 64, device=cuda_dev))
+    assert out.shape == (2, 17, 16, 16) and out.requires_grad
+    m = models.build_model(cfg)
     with pytest.raises(RuntimeError, match="pretrained"):
         models.HeatmapPose(17, "resnet50", pretrained=True)
