@@ -58,6 +58,14 @@ SIGNATURES = {
     "hpe_wgrad_plan_destroy": (None, [_vp]),
     "hpe_wgrad_workspace_elems": (_sz, [_vp]),
     "hpe_wgrad_run": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp]),
+    "hpe_pose_decode": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp]),
+    "hpe_pose_nms_scratch_elems": (_sz, [_i, _i]),
+    "hpe_pose_nms": (_i, [_vp, _i, _i, _i, _i, _i, _f, C.c_double, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "hpe_compute_loss_workspace_bytes": (_sz, [_i, _i, _vp, _vp, _i, _i]),
+    "hpe_compute_loss": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _i, _vp, _vp, _sz, _vp, _vp, _f, _vp]),
+    "hpe_oks": (_i, [_vp, _vp, _vp, _vp, _i, _i, _f, _f, _vp, _vp]),
+    "hpe_pck": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _f, _f, _vp, _vp, _vp]),
+    "hpe_keypoint_loss": (_i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp]),
 }
 
 _lib = None

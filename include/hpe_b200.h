@@ -208,6 +208,54 @@ int hpe_heatmap_grad_nhwc(const void* dhm, int dtype, int B, int K, int H, int W
 int hpe_sgd_step(float* param, const float* grad, float* momentum_buf, long long n, float lr, float momentum,
                  float weight_decay, float grad_scale, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * The reference's OWN pose-head post-processing, loss and metrics: these stages
+ * exist in the reference, so their oracle is pinned against the reference's outputs (tests/golden/detpose_golden.npz).
+ *
+ * hpe_pose_decode = PoseHead._inference_pose + kpts_decode + make_anchors
+ *   (HPE/models/nn/modules/head.py:185-211, HPE/models/utils.py:15-27).
+ *   levels[l]  raw head map [B, nc + nkpts*ndim, Hs[l], Ws[l]] (dtype f32|bf16, NCHW), strides[l] = 8/16/32
+ *   out        [B, nc + nkpts*ndim, A] f32, A = sum Hs*Ws: sigmoid(cls) | (raw-0.5+anchor)*stride | sigmoid(vis)
+ * hpe_pose_nms = non_max_suppression_pose (HPE/test.py:69-185) incl. torchvision.ops.nms (greedy, stable order):
+ *   pred [B,C,A] f32 (output of hpe_pose_decode); per image: score = max class prob > conf_thres, first-max label,
+ *   box = min/max of the keypoint xy, class offset label*7680, IoU > iou_thres (compared as double) suppresses.
+ *   Outputs are fixed-capacity: boxes [B,max_det,4], scores [B,max_det], labels [B,max_det] i32,
+ *   keypoints [B,max_det,nkpts,3] (conf = 1 when ndim == 2), count [B] i32 = detections kept (descending score).
+ *   scratch = f32 device scratch of hpe_pose_nms_scratch_elems(B, A) elements.  A <= 16384.
+ * ---------------------------------------------------------------------------------------------- */
+int hpe_pose_decode(const void* const* levels, const int* Hs, const int* Ws, const float* strides, int n_levels,
+                    int dtype, int B, int nc, int nkpts, int ndim, float* out, void* stream);
+size_t hpe_pose_nms_scratch_elems(int B, int A);
+int hpe_pose_nms(const float* pred, int B, int C, int A, int nc, int nkpts, float conf_thres, double iou_thres,
+                 int max_det, float* scratch, float* boxes, float* scores, int32_t* labels, float* keypoints,
+                 int32_t* count, void* stream);
+
+/* hpe_compute_loss = ComputeLoss.__call__ (HPE/loss.py:349-448; varifocal class term over all cells, wing-OKS +
+ * 0.5 L1 + 0.1 smoothness keypoint term, BCE visibility term, robust keypoint box + CIoU soft label) and -- when
+ * `grads` is non-NULL -- its analytic gradient (what `loss.backward()` produces, HPE/train.py training step).
+ *   preds[l]  [B, nc + 3*nkpts, Hs[l], Ws[l]] f32 NCHW (the head's training output, head.py:176-181)
+ *   targets   [n_targets, 6 + 3*nkpts] f32 rows (batch, class, cx, cy, w, h, (x, y, v)*K), normalised (HPE/dataset.py:76-86)
+ *   sigmas    [nkpts] f32 (COCO sigmas / 10 for 17 keypoints, loss.py:250-257)
+ *   loss_out  [4] f32 = {total, cls, kpt, vis};  grads[l] same shape as preds[l], overwritten with grad_scale * dL/dpred
+ *   workspace device scratch of hpe_compute_loss_workspace_bytes(...) bytes (zeroed inside, stream-ordered). */
+size_t hpe_compute_loss_workspace_bytes(int n_levels, int B, const int* Hs, const int* Ws, int nc, int n_targets);
+int hpe_compute_loss(const float* const* preds, const int* Hs, const int* Ws, int n_levels, int B, int nc, int nkpts,
+                     const float* targets, int n_targets, const float* sigmas, void* workspace, size_t workspace_bytes,
+                     float* loss_out, float* const* grads, float grad_scale, void* stream);
+
+/* Keypoint metrics / losses on decoded keypoints (HPE/core/metric/oksap.py:32-74, pck.py:14-104, HPE/core/loss/keypoint.py:13-21).
+ *   hpe_oks: gt [N,K,3] (x,y,v), pred [N,K,2], areas [N], sigmas [K] -> out [N]
+ *   hpe_pck: gt,pred [N,K,2], visible [N,K] u8 or NULL, normalizer NULL (gt bbox) | [1] | [N] -> counts[2] i64 = {correct, visible};
+ *            scratch = i32 [2*N]
+ *   hpe_keypoint_loss: pred/gt rows of pred_stride/gt_stride floats (x,y first), mask [N,K], area [N], sigmas [K]
+ *            -> loss [1]; scratch = f32 [N] */
+int hpe_oks(const float* gt, const float* pred, const float* areas, const float* sigmas, int N, int K,
+            float in_vis_thres, float eps, float* out, void* stream);
+int hpe_pck(const float* gt, const float* pred, const unsigned char* visible, const float* normalizer, int norm_n,
+            int N, int K, float alpha, float eps, int32_t* scratch, long long* counts, void* stream);
+int hpe_keypoint_loss(const float* pred, int pred_stride, const float* gt, int gt_stride, const float* mask,
+                      const float* area, const float* sigmas, int N, int K, float* scratch, float* loss, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
