@@ -12,14 +12,15 @@ _PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_PKG, "lib", "libhpe_b200.so")
 
 HPE_F32, HPE_BF16 = 0, 1
-ACT_NONE, ACT_RELU, ACT_SILU = 0, 1, 2
+ACT_NONE, ACT_RELU, ACT_SILU, ACT_GELU = 0, 1, 2, 3
 CONV_1x1, CONV_3x3, CONV_STEM7x7, CONV_DECONV4, CONV_FINAL = 0, 1, 2, 3, 4
-CONV_DGRAD3x3S2, CONV_DGRAD1x1S2, CONV_4x4S2 = 5, 6, 7
+CONV_DGRAD3x3S2, CONV_DGRAD1x1S2, CONV_4x4S2, CONV_2x2S2 = 5, 6, 7, 8
 
 
 class ConvDesc(C.Structure):
     _fields_ = [("kind", C.c_int), ("B", C.c_int), ("H", C.c_int), ("W", C.c_int), ("Cin", C.c_int),
-                ("Cout", C.c_int), ("stride", C.c_int), ("act", C.c_int), ("has_residual", C.c_int)]
+                ("Cout", C.c_int), ("stride", C.c_int), ("act", C.c_int), ("has_residual", C.c_int),
+                ("in_cstride", C.c_int), ("out_cstride", C.c_int)]
 
 
 _vp, _i, _f, _sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
@@ -58,6 +59,11 @@ SIGNATURES = {
     "hpe_wgrad_plan_destroy": (None, [_vp]),
     "hpe_wgrad_workspace_elems": (_sz, [_vp]),
     "hpe_wgrad_run": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp]),
+    "hpe_dwconv": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _f, _vp, _i, _vp]),
+    "hpe_layernorm_nhwc": (_i, [_vp, _i, C.c_longlong, _i, _vp, _vp, _f, _vp, _i, _vp]),
+    "hpe_patchify4": (_i, [_vp, _i, _i, _i, _vp, _vp]),
+    "hpe_maxpool5": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _i, _vp]),
+    "hpe_upsample_bilinear": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _vp, _i, _vp]),
     "hpe_pose_decode": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp]),
     "hpe_pose_nms_scratch_elems": (_sz, [_i, _i]),
     "hpe_pose_nms": (_i, [_vp, _i, _i, _i, _i, _i, _f, C.c_double, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -45,6 +45,7 @@ struct ConvParams {
   int tw, th, nb;
   int tiles_x, tiles_y, tiles_b, n_tiles_n, n_classes, num_tiles;
   int Ho, Wo, B, Cout;          // Ho,Wo = extent of the tile grid (deconv: input-resolution grid per class)
+  int cout_total;               // HPE_CONV_FINAL: channel count of the NCHW tensor y is a slice of
   int act, has_res;
   const float* scale;
   const float* shift;
@@ -76,6 +77,7 @@ __device__ __forceinline__ void tap_offset(const ConvParams& p, int t, int cls, 
     dy = (py && ty) ? 1 : 0;
     dx = (px && tx) ? 1 : 0;
   } else if (p.kind == HPE_CONV_4x4S2) { dy = (t >> 2) - 1; dx = (t & 3) - 1; }
+  else if (p.kind == HPE_CONV_2x2S2) { dy = t >> 1; dx = t & 1; }
   else { dx = 0; dy = 0; }
 }
 // number of 64-wide k-blocks of a tile (depends on the parity class only for the stride-2 3x3 dgrad)
@@ -125,7 +127,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                  const ConvParams p) {
   using L = SmemLayout<BLOCK_N, STAGES>;
   constexpr int kChunks   = BLOCK_N >= 64 ? BLOCK_N / 64 : 1;
-  constexpr int kTmemCols = 2 * BLOCK_N < 32 ? 32 : 2 * BLOCK_N;
+  constexpr int kTmemCols = 2 * BLOCK_N <= 32 ? 32 : (2 * BLOCK_N <= 64 ? 64 : (2 * BLOCK_N <= 128 ? 128 : (2 * BLOCK_N <= 256 ? 256 : 512)));  // power of two
   constexpr uint32_t kIdesc = make_idesc_bf16_m128(BLOCK_N);
 
   extern __shared__ uint8_t smem_raw[];
@@ -156,7 +158,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     fence_mbar_init();
   }
   if (warp == 1) { tmem_alloc(tmem_slot, kTmemCols); tmem_relinquish(); }
-  for (int i = threadIdx.x; i < p.Cout; i += kConvThreads) { sScale[i] = __ldg(p.scale + i); sShift[i] = __ldg(p.shift + i); }
+  for (int i = threadIdx.x; i < p.n_tiles_n * BLOCK_N && i < kMaxCout; i += kConvThreads) {   // channels of a partial last N tile: 0
+    sScale[i] = i < p.Cout ? __ldg(p.scale + i) : 0.f; sShift[i] = i < p.Cout ? __ldg(p.shift + i) : 0.f;
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -257,7 +261,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               const int k = g * 32 + e;
               if (k < p.Cout) {
                 const float o = fmaf(__uint_as_float(v[e]), sScale[k], sShift[k]);
-                p.hm_out[(static_cast<size_t>(b) * p.Cout + k) * plane + static_cast<size_t>(y) * p.Wo + x] = o;
+                p.hm_out[(static_cast<size_t>(b) * p.cout_total + k) * plane + static_cast<size_t>(y) * p.Wo + x] = o;
               }
             }
           }
@@ -303,6 +307,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             if (ACT == HPE_ACT_SILU) {
 #pragma unroll
               for (int e = 0; e < 8; ++e) o[e] = o[e] / (1.f + __expf(-o[e]));
+            }
+            if (ACT == HPE_ACT_GELU) {         // exact (erf) GELU = nn.GELU() default (dinov3 convnext.py:60)
+#pragma unroll
+              for (int e = 0; e < 8; ++e) o[e] = 0.5f * o[e] * (1.f + erff(o[e] * 0.70710678118654752f));
             }
             uint4 pk = make_uint4(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]), pack_bf16(o[6], o[7]));
             if (ACT == HPE_ACT_RELU) {        // relu(round(x)) == round(relu(x)): do it on packed bf16x2
@@ -397,32 +405,31 @@ maxpool_kernel(const __nv_bfloat16* __restrict__ x, int B, int H, int W, int C, 
   }
 }
 
-// PyTorch-layout fp32 weight -> packed bf16 GEMM-B  [rows][Ktot]
+// PyTorch-layout fp32 weight -> packed bf16 GEMM-B  [rows][Ktot]; every tap's Cin is zero-padded to Cp = kc*64
 __global__ void __launch_bounds__(256)
-pack_weight_kernel(const float* __restrict__ w, int kind, int Cin, int Cout, long long total,
+pack_weight_kernel(const float* __restrict__ w, int kind, int Cin, int Cp, int Cout, long long total,
                    __nv_bfloat16* __restrict__ out) {
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
     float v = 0.f;
-    if (kind == HPE_CONV_1x1 || kind == HPE_CONV_FINAL) {
-      v = w[i];                                                        // [Cout][Cin]
-    } else if (kind == HPE_CONV_3x3) {
-      const int K = 9 * Cin, co = static_cast<int>(i / K), k = static_cast<int>(i % K);
-      const int tap = k / Cin, ci = k % Cin;
-      v = w[(static_cast<size_t>(co) * Cin + ci) * 9 + tap];           // [Cout][Cin][3][3]
-    } else if (kind == HPE_CONV_STEM7x7) {
+    if (kind == HPE_CONV_STEM7x7) {
       const int co = static_cast<int>(i / 256), k = static_cast<int>(i % 256);
       const int khp = k / 64, kwp = (k % 64) / 16, q = k % 16, py = q / 8, px = (q / 4) % 2, c = q % 4;
       const int ky = 2 * khp + py - 1, kx = 2 * kwp + px - 1;
       if (c < 3 && ky >= 0 && kx >= 0) v = w[((static_cast<size_t>(co) * 3 + c) * 7 + ky) * 7 + kx];   // [64][3][7][7]
-    } else {  // HPE_CONV_DECONV4: torch [Cin][Cout][4][4] -> [(cls*Cout + co)][(ty*2+tx)*Cin + ci]
-      const int K = 4 * Cin;
+    } else if (kind == HPE_CONV_DECONV4) {   // torch [Cin][Cout][4][4] -> [(cls*Cout + co)][(ty*2+tx)*Cp + ci]
+      const int K = 4 * Cp;
       const int row = static_cast<int>(i / K), k = static_cast<int>(i % K);
-      const int cls = row / Cout, co = row % Cout, t = k / Cin, ci = k % Cin;
+      const int cls = row / Cout, co = row % Cout, t = k / Cp, ci = k % Cp;
       const int py = cls >> 1, px = cls & 1, ty = t >> 1, tx = t & 1;
       const int ky = py ? (ty ? 0 : 2) : (ty ? 3 : 1);
       const int kx = px ? (tx ? 0 : 2) : (tx ? 3 : 1);
-      v = w[((static_cast<size_t>(ci) * Cout + co) * 4 + ky) * 4 + kx];
+      if (ci < Cin) v = w[((static_cast<size_t>(ci) * Cout + co) * 4 + ky) * 4 + kx];
+    } else {                                  // Conv2d [Cout][Cin][kh][kw] -> [co][tap*Cp + ci], tap = ky*kw + kx
+      const int taps = kind == HPE_CONV_3x3 ? 9 : (kind == HPE_CONV_2x2S2 ? 4 : 1);
+      const int K = taps * Cp, co = static_cast<int>(i / K), k = static_cast<int>(i % K);
+      const int tap = k / Cp, ci = k % Cp;
+      if (ci < Cin) v = w[(static_cast<size_t>(co) * Cin + ci) * taps + tap];
     }
     out[i] = __float2bfloat16(v);
   }
@@ -447,27 +454,37 @@ struct hpe_conv_plan {
 
 static int desc_check(const hpe_conv_desc* d, const char* fn) {
   HPE_CHECK_ARG(d, "%s: null desc", fn);
-  HPE_CHECK_ARG(d->kind >= HPE_CONV_1x1 && d->kind <= HPE_CONV_4x4S2, "%s: bad kind %d", fn, d->kind);
+  HPE_CHECK_ARG(d->kind >= HPE_CONV_1x1 && d->kind <= HPE_CONV_2x2S2, "%s: bad kind %d", fn, d->kind);
   HPE_CHECK_ARG(d->B > 0 && d->H > 0 && d->W > 0 && d->Cin > 0 && d->Cout > 0, "%s: non-positive size", fn);
+  HPE_CHECK_ARG(d->in_cstride >= 0 && d->out_cstride >= 0, "%s: negative channel stride", fn);
   if (d->kind == HPE_CONV_STEM7x7) {
     if (d->Cin != 3 || d->Cout != 64 || (d->H % 2) || (d->W % 2))
       return fail(HPE_EUNSUPPORTED, "%s: stem needs Cin=3, Cout=64, even H/W (got %d,%d,%dx%d)", fn, d->Cin, d->Cout, d->H, d->W);
     return HPE_OK;
   }
-  if (d->Cin % 64) return fail(HPE_EUNSUPPORTED, "%s: Cin=%d must be a multiple of 64", fn, d->Cin);
+  if (d->Cin % 8) return fail(HPE_EUNSUPPORTED, "%s: Cin=%d must be a multiple of 8", fn, d->Cin);
+  if (d->in_cstride && (d->in_cstride % 8 || d->in_cstride < d->Cin))
+    return fail(HPE_EINVAL, "%s: in_cstride=%d must be a multiple of 8 and >= Cin", fn, d->in_cstride);
   if (d->kind == HPE_CONV_FINAL) {
     if (d->Cout > 256) return fail(HPE_EUNSUPPORTED, "%s: final conv supports at most 256 joints (got %d)", fn, d->Cout);
     if (d->act != HPE_ACT_NONE || d->has_residual) return fail(HPE_EUNSUPPORTED, "%s: final conv has no activation/residual", fn);
+    if (d->out_cstride && d->out_cstride < d->Cout) return fail(HPE_EINVAL, "%s: out_cstride < Cout", fn);
     return HPE_OK;
   }
-  if (d->Cout % 64) return fail(HPE_EUNSUPPORTED, "%s: Cout=%d must be a multiple of 64", fn, d->Cout);
+  if (d->Cout % 8) return fail(HPE_EUNSUPPORTED, "%s: Cout=%d must be a multiple of 8", fn, d->Cout);
+  if (d->out_cstride && (d->out_cstride % 8 || d->out_cstride < d->Cout))
+    return fail(HPE_EINVAL, "%s: out_cstride=%d must be a multiple of 8 and >= Cout", fn, d->out_cstride);
   if (d->Cout > kMaxCout) return fail(HPE_EUNSUPPORTED, "%s: Cout=%d exceeds %d", fn, d->Cout, kMaxCout);
-  if (d->act < HPE_ACT_NONE || d->act > HPE_ACT_SILU) return fail(HPE_EINVAL, "%s: bad act %d", fn, d->act);
+  if (d->act < HPE_ACT_NONE || d->act > HPE_ACT_GELU) return fail(HPE_EINVAL, "%s: bad act %d", fn, d->act);
+  if (d->act == HPE_ACT_GELU && d->has_residual) return fail(HPE_EUNSUPPORTED, "%s: GELU epilogue has no residual variant", fn);
   if (d->kind == HPE_CONV_1x1 || d->kind == HPE_CONV_3x3) {
     if (d->stride != 1 && d->stride != 2) return fail(HPE_EUNSUPPORTED, "%s: stride %d not in {1,2}", fn, d->stride);
     if (d->stride == 2 && ((d->H % 2) || (d->W % 2))) return fail(HPE_EUNSUPPORTED, "%s: stride 2 needs even H/W", fn);
   }
-  if (d->kind == HPE_CONV_4x4S2 && ((d->H % 2) || (d->W % 2))) return fail(HPE_EUNSUPPORTED, "%s: 4x4/s2 needs even H/W", fn);
+  if ((d->kind == HPE_CONV_4x4S2 || d->kind == HPE_CONV_2x2S2) && ((d->H % 2) || (d->W % 2)))
+    return fail(HPE_EUNSUPPORTED, "%s: stride-2 kinds need even H/W", fn);
+  if (d->kind >= HPE_CONV_DGRAD3x3S2 && d->kind <= HPE_CONV_4x4S2 && ((d->Cin % 64) || (d->Cout % 64)))
+    return fail(HPE_EUNSUPPORTED, "%s: backward-data kinds need Cin, Cout multiples of 64", fn);
   return HPE_OK;
 }
 
@@ -476,9 +493,14 @@ static int desc_check(const hpe_conv_desc* d, const char* fn) {
 // the A operand through the L2->SM fabric, which is what bounds these kernels; see profiles/.)
 static int pick_block_n(const hpe_conv_desc* d, long long /*m_tiles*/) {
   if (d->kind == HPE_CONV_FINAL) return d->Cout <= 32 ? 32 : (d->Cout <= 64 ? 64 : (d->Cout <= 128 ? 128 : 256));
-  if (d->Cout % 256 == 0) return 256;
-  if (d->Cout % 128 == 0) return 128;
-  return 64;
+  // the tile width wasting the fewest padded columns; ties -> the wider tile (fewer re-reads of A)
+  const int cand[4] = {256, 192, 128, 64};
+  int best = 64, best_waste = 1 << 30;
+  for (int i = 0; i < 4; ++i) {
+    const int bn = cand[i], waste = (d->Cout + bn - 1) / bn * bn - d->Cout;
+    if (waste < best_waste) { best_waste = waste; best = bn; }
+  }
+  return best;
 }
 
 extern "C" int hpe_conv_out_hw(const hpe_conv_desc* d, int* Ho, int* Wo) {
@@ -488,20 +510,22 @@ extern "C" int hpe_conv_out_hw(const hpe_conv_desc* d, int* Ho, int* Wo) {
   switch (d->kind) {
     case HPE_CONV_STEM7x7: *Ho = d->H / 2; *Wo = d->W / 2; break;
     case HPE_CONV_DECONV4: case HPE_CONV_DGRAD3x3S2: case HPE_CONV_DGRAD1x1S2: *Ho = d->H * 2; *Wo = d->W * 2; break;
-    case HPE_CONV_4x4S2:   *Ho = d->H / 2; *Wo = d->W / 2; break;
+    case HPE_CONV_4x4S2: case HPE_CONV_2x2S2: *Ho = d->H / 2; *Wo = d->W / 2; break;
     case HPE_CONV_FINAL:   *Ho = d->H; *Wo = d->W; break;
     default:               *Ho = d->H / d->stride; *Wo = d->W / d->stride; break;
   }
   return HPE_OK;
 }
 
+static int cin_padded(const hpe_conv_desc* d) { return (d->Cin + 63) / 64 * 64; }
 static size_t ktot(const hpe_conv_desc* d) {
+  const size_t cp = cin_padded(d);
   switch (d->kind) {
-    case HPE_CONV_3x3:     return (size_t)9 * d->Cin;
+    case HPE_CONV_3x3:     return 9 * cp;
     case HPE_CONV_STEM7x7: return 256;
-    case HPE_CONV_DECONV4: case HPE_CONV_DGRAD3x3S2: return (size_t)4 * d->Cin;
-    case HPE_CONV_4x4S2:   return (size_t)16 * d->Cin;
-    default:               return d->Cin;
+    case HPE_CONV_DECONV4: case HPE_CONV_DGRAD3x3S2: case HPE_CONV_2x2S2: return 4 * cp;
+    case HPE_CONV_4x4S2:   return 16 * cp;
+    default:               return cp;
   }
 }
 static bool is_class_strided(int kind) { return kind == HPE_CONV_DECONV4 || kind == HPE_CONV_DGRAD3x3S2; }
@@ -519,7 +543,7 @@ extern "C" int hpe_conv_pack_weight(const hpe_conv_desc* d, const float* w_torch
   if (d->kind > HPE_CONV_FINAL) return fail(HPE_EINVAL, "hpe_conv_pack_weight: kind %d is a backward-data kind; use hpe_conv_pack_weight_dgrad", d->kind);
   const long long total = (long long)(wrows(d) * ktot(d));
   const int grid = (int)((total + 255) / 256 > 4096 ? 4096 : (total + 255) / 256);
-  pack_weight_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(w_torch, d->kind, d->Cin, d->Cout, total,
+  pack_weight_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(w_torch, d->kind, d->Cin, cin_padded(d), d->Cout, total,
                                                             (__nv_bfloat16*)w_packed);
   return launch_status("pack_weight_kernel");
 }
@@ -603,6 +627,7 @@ static ConvKernelFn pick_kernel_bn(int act, bool res, bool fin) {
     switch (act) {
       case HPE_ACT_RELU: return res ? conv_gemm_kernel<BN, ST, HPE_ACT_RELU, true, false> : conv_gemm_kernel<BN, ST, HPE_ACT_RELU, false, false>;
       case HPE_ACT_SILU: return res ? conv_gemm_kernel<BN, ST, HPE_ACT_SILU, true, false> : conv_gemm_kernel<BN, ST, HPE_ACT_SILU, false, false>;
+      case HPE_ACT_GELU: return res ? nullptr : conv_gemm_kernel<BN, ST, HPE_ACT_GELU, false, false>;
       default:           return res ? conv_gemm_kernel<BN, ST, HPE_ACT_NONE, true, false> : conv_gemm_kernel<BN, ST, HPE_ACT_NONE, false, false>;
     }
   }
@@ -614,6 +639,7 @@ static ConvKernelFn pick_kernel(int block_n, int act, bool res, bool fin, size_t
     case 32:  *smem = SmemLayout<32, 6>::kDynamic;  return pick_kernel_bn<32, 6>(act, res, fin);
     case 64:  *smem = SmemLayout<64, 6>::kDynamic;  return pick_kernel_bn<64, 6>(act, res, fin);
     case 128: *smem = SmemLayout<128, 4>::kDynamic; return pick_kernel_bn<128, 4>(act, res, fin);
+    case 192: *smem = SmemLayout<192, 3>::kDynamic; return pick_kernel_bn<192, 3>(act, res, fin);
     default:  *smem = SmemLayout<256, 3>::kDynamic; return pick_kernel_bn<256, 3>(act, res, fin);
   }
 }
@@ -629,14 +655,15 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
   hpe_conv_out_hw(d, &pl->Ho, &pl->Wo);
   ConvParams& p = pl->p;
   p.kind = d->kind;
-  p.in_stride = (d->kind == HPE_CONV_1x1 || d->kind == HPE_CONV_3x3) ? d->stride : (d->kind == HPE_CONV_4x4S2 ? 2 : 1);
+  p.in_stride = (d->kind == HPE_CONV_1x1 || d->kind == HPE_CONV_3x3) ? d->stride
+                : ((d->kind == HPE_CONV_4x4S2 || d->kind == HPE_CONV_2x2S2) ? 2 : 1);
   switch (d->kind) {
     case HPE_CONV_3x3: p.taps = 9; break;
     case HPE_CONV_4x4S2: p.taps = 16; break;
     case HPE_CONV_1x1: case HPE_CONV_FINAL: case HPE_CONV_DGRAD1x1S2: p.taps = 1; break;
     default: p.taps = 4; break;                 // stem, deconv, (dgrad 3x3/s2: upper bound, see kb_count)
   }
-  p.kc_per_tap = d->kind == HPE_CONV_STEM7x7 ? 1 : d->Cin / 64;
+  p.kc_per_tap = d->kind == HPE_CONV_STEM7x7 ? 1 : cin_padded(d) / 64;
   p.n_classes = is_class_strided(d->kind) ? 4 : 1;
   // tile grid extent: deconv-like tiles walk the INPUT-resolution grid of one parity class
   const bool up2 = is_class_strided(d->kind) || d->kind == HPE_CONV_DGRAD1x1S2;
@@ -649,7 +676,10 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
   p.tw = tw; p.th = th; p.nb = nb;
   p.tiles_x = (p.Wo + tw - 1) / tw; p.tiles_y = (p.Ho + th - 1) / th; p.tiles_b = (p.B + nb - 1) / nb;
   pl->block_n = pick_block_n(d, (long long)p.tiles_x * p.tiles_y * p.tiles_b * p.n_classes);
-  p.n_tiles_n = d->kind == HPE_CONV_FINAL ? 1 : d->Cout / pl->block_n;
+  p.n_tiles_n = d->kind == HPE_CONV_FINAL ? 1 : (d->Cout + pl->block_n - 1) / pl->block_n;
+  p.cout_total = d->out_cstride ? d->out_cstride : d->Cout;
+  if (is_class_strided(d->kind) && d->Cout % pl->block_n) { delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: parity-class kinds need Cout %% %d == 0", pl->block_n); }
+  if (p.n_tiles_n * pl->block_n > kMaxCout) { delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: padded Cout exceeds %d", kMaxCout); }
   const long long nt = (long long)p.tiles_x * p.tiles_y * p.tiles_b * p.n_tiles_n * p.n_classes;
   if (nt > 0x7fffffff) { delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: too many tiles"); }
   p.num_tiles = (int)nt;
@@ -681,9 +711,9 @@ static int encode_plan_maps(hpe_conv_plan* pl, const void* x, const void* w, con
       const uint32_t box[4] = {64, (uint32_t)p.tw, (uint32_t)p.th, (uint32_t)p.nb};
       rc = encode_map(&pl->tmA, x, 4, dims, str, box, ones, "stem A");
     } else {
-      const uint64_t C = d.Cin;
+      const uint64_t C = d.Cin, P = d.in_cstride ? d.in_cstride : d.Cin;      // P = channel pitch of a pixel
       const uint64_t dims[4] = {C, (uint64_t)d.W, (uint64_t)d.H, (uint64_t)d.B};
-      const uint64_t str[3] = {C * 2, (uint64_t)d.W * C * 2, (uint64_t)d.H * d.W * C * 2};
+      const uint64_t str[3] = {P * 2, (uint64_t)d.W * P * 2, (uint64_t)d.H * d.W * P * 2};
       const uint32_t s = (uint32_t)p.in_stride;
       const uint32_t box[4] = {64, (uint32_t)p.tw * s, (uint32_t)p.th * s, (uint32_t)p.nb};
       const uint32_t es[4] = {1, s, s, 1};
@@ -704,7 +734,7 @@ static int encode_plan_maps(hpe_conv_plan* pl, const void* x, const void* w, con
   }
   if (d.kind != HPE_CONV_FINAL && y != pl->y) {
     HPE_CHECK_ARG(((uintptr_t)y & 15) == 0, "hpe_conv_run: y must be 16-byte aligned");
-    const uint64_t C = d.Cout;
+    const uint64_t C = d.Cout, P = d.out_cstride ? d.out_cstride : d.Cout;
     const uint32_t box[4] = {64, (uint32_t)p.tw, (uint32_t)p.th, (uint32_t)p.nb};
     if (is_class_strided(d.kind) || d.kind == HPE_CONV_DGRAD1x1S2) {
       const uint64_t Wo = pl->Wo, Ho = pl->Ho;
@@ -712,15 +742,15 @@ static int encode_plan_maps(hpe_conv_plan* pl, const void* x, const void* w, con
       for (int cls = 0; cls < 4; ++cls) {
         if (cls >= ncls) { pl->tmOut.m[cls] = pl->tmOut.m[0]; continue; }
         const int py = cls >> 1, px = cls & 1;
-        const char* base = (const char*)y + ((size_t)py * Wo + px) * C * 2;
+        const char* base = (const char*)y + ((size_t)py * Wo + px) * P * 2;
         const uint64_t dims[4] = {C, (uint64_t)d.W, (uint64_t)d.H, (uint64_t)d.B};
-        const uint64_t str[3] = {2 * C * 2, 2 * Wo * C * 2, Ho * Wo * C * 2};
+        const uint64_t str[3] = {2 * P * 2, 2 * Wo * P * 2, Ho * Wo * P * 2};
         rc = encode_map(&pl->tmOut.m[cls], base, 4, dims, str, box, ones, "deconv out");
         if (rc) return rc;
       }
     } else {
       const uint64_t dims[4] = {C, (uint64_t)pl->Wo, (uint64_t)pl->Ho, (uint64_t)d.B};
-      const uint64_t str[3] = {C * 2, (uint64_t)pl->Wo * C * 2, (uint64_t)pl->Ho * pl->Wo * C * 2};
+      const uint64_t str[3] = {P * 2, (uint64_t)pl->Wo * P * 2, (uint64_t)pl->Ho * pl->Wo * P * 2};
       rc = encode_map(&pl->tmOut.m[0], y, 4, dims, str, box, ones, "out");
       if (rc) return rc;
       pl->tmOut.m[1] = pl->tmOut.m[2] = pl->tmOut.m[3] = pl->tmOut.m[0];
@@ -729,7 +759,7 @@ static int encode_plan_maps(hpe_conv_plan* pl, const void* x, const void* w, con
   }
   if (p.has_res && res != pl->res) {
     HPE_CHECK_ARG(res && ((uintptr_t)res & 15) == 0, "hpe_conv_run: residual must be non-null and 16-byte aligned");
-    const uint64_t C = d.Cout;
+    const uint64_t C = d.Cout;                  // the residual is always a dense [B,Ho,Wo,Cout] tensor
     const uint64_t dims[4] = {C, (uint64_t)pl->Wo, (uint64_t)pl->Ho, (uint64_t)d.B};
     const uint64_t str[3] = {C * 2, (uint64_t)pl->Wo * C * 2, (uint64_t)pl->Ho * pl->Wo * C * 2};
     const uint32_t box[4] = {64, (uint32_t)p.tw, (uint32_t)p.th, (uint32_t)p.nb};

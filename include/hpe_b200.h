@@ -39,6 +39,7 @@ extern "C" {
 #define HPE_ACT_NONE 0
 #define HPE_ACT_RELU 1        /* timm Bottleneck act (resnet.py:244-270)                               */
 #define HPE_ACT_SILU 2        /* first-party ConvBlock default act (HPE/models/nn/modules/block.py:20-45) */
+#define HPE_ACT_GELU 3        /* exact erf GELU of the ConvNeXt block MLP (HPE/thirdparty/dinov3/dinov3/models/convnext.py:60) */
 
 int         hpe_abi_version(void);
 const char* hpe_last_error(void);
@@ -123,6 +124,7 @@ typedef struct hpe_conv_plan hpe_conv_plan;
 #define HPE_CONV_DGRAD3x3S2 5 /* dgrad of 3x3/s2/p1: four output-parity classes with 1/2/2/4 taps  */
 #define HPE_CONV_DGRAD1x1S2 6 /* dgrad of 1x1/s2: GEMM stored to the even pixels, rest zeroed      */
 #define HPE_CONV_4x4S2      7 /* dgrad of the k4/s2/p1 transposed conv = 4x4 stride-2 conv, 16 taps */
+#define HPE_CONV_2x2S2      8 /* 2x2 stride-2 pad-0 conv: ConvNeXt downsample layers (dinov3 convnext.py:163-167) */
 
 typedef struct hpe_conv_desc {
   int kind;                 /* HPE_CONV_*                                         */
@@ -130,7 +132,12 @@ typedef struct hpe_conv_desc {
   int stride;               /* 1 or 2 (ignored for STEM/DECONV/FINAL)             */
   int act;                  /* HPE_ACT_*                                          */
   int has_residual;         /* epilogue adds `residual` before the activation     */
+  int in_cstride;           /* channels between consecutive pixels of x (0 = Cin): x may be a channel slice of a wider NHWC tensor */
+  int out_cstride;          /* same for y (the residual stays dense); 0 = Cout.  This is how torch.cat along channels disappears:
+                               producers write straight into their slice (HPE/models/nn/modules/block.py:100,113,142-155).
+                               HPE_CONV_FINAL: channel count of the NCHW tensor y is a slice of (head.py:176-179) */
 } hpe_conv_desc;
+/* Channel counts: Cin and Cout must be multiples of 8 (16-byte pixels); partial 64-channel blocks are zero-filled by TMA. */
 
 int  hpe_conv_plan_create(const hpe_conv_desc* desc, hpe_conv_plan** out);
 void hpe_conv_plan_destroy(hpe_conv_plan* plan);
@@ -255,6 +262,28 @@ int hpe_pck(const float* gt, const float* pred, const unsigned char* visible, co
             int N, int K, float alpha, float eps, int32_t* scratch, long long* counts, void* stream);
 int hpe_keypoint_loss(const float* pred, int pred_stride, const float* gt, int gt_stride, const float* mask,
                       const float* area, const float* sigmas, int N, int K, float* scratch, float* loss, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Bandwidth-bound NHWC bf16 ops of the reference's real pose model (DINOv3Pose, HPE/models/pose.py:9-65: ConvNeXt
+ * backbone + FeatureAdaptor + SPPF + PAN + PoseHead).  Every tensor takes an explicit channel
+ * pitch (elements between consecutive pixels) so producers can write into a slice of a concat buffer.
+ *   hpe_dwconv            depthwise ksize x ksize (3|7), pad ksize/2, stride 1.  w_taps = fp32 [ksize*ksize][C].
+ *                         mode 0: y = SiLU(acc*p0 + p1)            (ConvBlock(k=3, g=C), head.py:143; block.py:20-45)
+ *                         mode 1: y = LayerNorm_C(acc + p0; gamma=p1, beta=p2, eps)   (ConvNeXt Block, convnext.py:73-76)
+ *   hpe_layernorm_nhwc    per-pixel LayerNorm over C (channels_first LayerNorm, convnext.py:112-117)
+ *   hpe_patchify4         fp32 NCHW [B,3,H,W] -> bf16 [B,H/4,W/4,64]: the 48 inputs (c,ky,kx) of the 4x4/s4 stem conv
+ *                         (convnext.py:157-160) + 16 zeros, so the stem is a 1x1 GEMM with Cin = 64
+ *   hpe_maxpool5          MaxPool2d(5,1,2) (SPPF, block.py:102-114)
+ *   hpe_upsample_bilinear F.interpolate(size=(Ho,Wo), mode='bilinear', align_corners=False) (PAN, block.py:132-151)
+ * ---------------------------------------------------------------------------------------------- */
+int hpe_dwconv(const void* x, int in_pitch, int B, int H, int W, int C, int ksize, int mode, const float* w_taps,
+               const float* p0, const float* p1, const float* p2, float eps, void* y, int out_pitch, void* stream);
+int hpe_layernorm_nhwc(const void* x, int in_pitch, long long M, int C, const float* gamma, const float* beta, float eps,
+                       void* y, int out_pitch, void* stream);
+int hpe_patchify4(const float* img_nchw, int B, int H, int W, void* out, void* stream);
+int hpe_maxpool5(const void* x, int in_pitch, int B, int H, int W, int C, void* y, int out_pitch, void* stream);
+int hpe_upsample_bilinear(const void* x, int in_pitch, int B, int Hi, int Wi, int C, int Ho, int Wo, void* y, int out_pitch,
+                          void* stream);
 
 #ifdef __cplusplus
 }
