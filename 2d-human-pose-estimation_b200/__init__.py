@@ -19,6 +19,7 @@ from . import train
 from .train import TrainPlan, TrainStep
 from .detpose import (OKS, OKS_SIGMAS, PCK, ComputeLoss, KeypointLoss, non_max_suppression_pose, pose_decode,
                       pose_nms_raw)
+from .posemodel import DINOv3Pose
 from .pipeline import PoseEstimator, gather_keypoints, gather_keypoints_equal, shard_range
 
 __version__ = "0.1.0"

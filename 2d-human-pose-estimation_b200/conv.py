@@ -13,8 +13,8 @@ import ctypes as C
 import torch
 
 from . import _lib
-from ._lib import (ACT_NONE, ACT_RELU, ACT_SILU, CONV_1x1, CONV_3x3, CONV_4x4S2, CONV_DECONV4, CONV_DGRAD1x1S2,
-                   CONV_DGRAD3x3S2, CONV_FINAL, CONV_STEM7x7, ConvDesc)
+from ._lib import (ACT_GELU, ACT_NONE, ACT_RELU, ACT_SILU, CONV_1x1, CONV_2x2S2, CONV_3x3, CONV_4x4S2, CONV_DECONV4,
+                   CONV_DGRAD1x1S2, CONV_DGRAD3x3S2, CONV_FINAL, CONV_STEM7x7, ConvDesc)
 
 
 def fold_bn(weight, bias, running_mean, running_var, eps):
@@ -25,9 +25,11 @@ def fold_bn(weight, bias, running_mean, running_var, eps):
 
 
 class ConvLayer:
-    def __init__(self, kind, B, H, W, Cin, Cout, stride=1, act=ACT_RELU, has_residual=False, device="cuda", desc=None):
+    def __init__(self, kind, B, H, W, Cin, Cout, stride=1, act=ACT_RELU, has_residual=False, device="cuda", desc=None,
+                 in_cstride=0, out_cstride=0):
         self.device = torch.device(device)
-        self.desc = desc if desc is not None else ConvDesc(kind, B, H, W, Cin, Cout, stride, act, int(has_residual))
+        self.desc = desc if desc is not None else ConvDesc(kind, B, H, W, Cin, Cout, stride, act, int(has_residual),
+                                                           in_cstride, out_cstride)
         kind, B, Cout = self.desc.kind, self.desc.B, self.desc.Cout
         lib = _lib.lib()
         ho, wo = C.c_int(), C.c_int()
@@ -75,7 +77,14 @@ class ConvLayer:
     def __call__(self, x: torch.Tensor, residual: torch.Tensor = None, out: torch.Tensor = None):
         if out is None:
             out = self.alloc_out()
-        _lib.require_cuda(x, residual, out)
+        if self.desc.in_cstride or self.desc.out_cstride:
+            # channel slices of wider NHWC buffers: the innermost stride must be 1 and the pixel pitch the declared one
+            _lib.require_cuda(residual)
+            for t, pitch in ((x, self.desc.in_cstride), (out, self.desc.out_cstride)):
+                if not t.is_cuda or (pitch and self.kind != CONV_FINAL and (t.stride(-1) != 1 or t.stride(-2) != pitch)):
+                    raise RuntimeError("libhpe_b200: channel-slice tensor does not match the plan's channel pitch")
+        else:
+            _lib.require_cuda(x, residual, out)
         with torch.cuda.device(self.device):
             rc = _lib.lib().hpe_conv_run(self.plan, _lib.ptr(x), _lib.ptr(self.w_packed), _lib.ptr(self.scale),
                                          _lib.ptr(self.shift), _lib.ptr(residual), _lib.ptr(out), _lib.stream_ptr())

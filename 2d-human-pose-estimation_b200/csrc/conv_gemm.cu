@@ -540,7 +540,7 @@ extern "C" int hpe_conv_pack_weight(const hpe_conv_desc* d, const float* w_torch
   int rc = desc_check(d, "hpe_conv_pack_weight");
   if (rc) return rc;
   HPE_CHECK_ARG(w_torch && w_packed, "hpe_conv_pack_weight: null pointer");
-  if (d->kind > HPE_CONV_FINAL) return fail(HPE_EINVAL, "hpe_conv_pack_weight: kind %d is a backward-data kind; use hpe_conv_pack_weight_dgrad", d->kind);
+  if (d->kind > HPE_CONV_FINAL && d->kind != HPE_CONV_2x2S2) return fail(HPE_EINVAL, "hpe_conv_pack_weight: kind %d is a backward-data kind; use hpe_conv_pack_weight_dgrad", d->kind);
   const long long total = (long long)(wrows(d) * ktot(d));
   const int grid = (int)((total + 255) / 256 > 4096 ? 4096 : (total + 255) / 256);
   pack_weight_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(w_torch, d->kind, d->Cin, cin_padded(d), d->Cout, total,

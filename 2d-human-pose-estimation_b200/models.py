@@ -25,7 +25,7 @@ from . import _lib
 from .conv import (ACT_NONE, ACT_RELU, CONV_1x1, CONV_3x3, CONV_DECONV4, CONV_FINAL, CONV_STEM7x7, ConvLayer, fold_bn,
                    maxpool3x3s2, preprocess)
 
-__all__ = ("DeepPose", "HeatmapPose")
+__all__ = ("DeepPose", "HeatmapPose")      # names Builder.model() may construct positionally (nkpts, backbone, pretrained)
 
 _LAYERS = (3, 4, 6, 3)
 _PLANES = (64, 128, 256, 512)
@@ -170,6 +170,8 @@ class HeatmapPose(nn.Module):
         plan = self._plans[(tuple(x.shape), x.device.index)]
         return plan.features.float().permute(0, 3, 1, 2)
 
+
+from .posemodel import DINOv3Pose  # noqa: E402  (the reference's real pose model, HPE/models/pose.py)
 
 DeepPose = HeatmapPose     # config-default name (HPE/configs/default.py:13): same constructor, heatmap output
 

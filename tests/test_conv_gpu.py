@@ -127,7 +127,7 @@ def test_final_1x1_heatmaps(hpe, cuda_dev, B, H, W, K):
 def test_conv_rejects_unsupported(hpe, cuda_dev):
     from importlib import import_module
     conv = import_module("2d-human-pose-estimation_b200.conv")
-    with pytest.raises(RuntimeError, match="multiple of 64"):
-        conv.ConvLayer(conv.CONV_1x1, 1, 8, 8, 48, 64)
+    with pytest.raises(RuntimeError, match="multiple of 8"):
+        conv.ConvLayer(conv.CONV_1x1, 1, 8, 8, 44, 64)
     with pytest.raises(RuntimeError, match="stride"):
         conv.ConvLayer(conv.CONV_3x3, 1, 8, 8, 64, 64, stride=3)
