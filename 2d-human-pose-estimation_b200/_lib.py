@@ -60,6 +60,7 @@ SIGNATURES = {
     "hpe_wgrad_workspace_elems": (_sz, [_vp]),
     "hpe_wgrad_run": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp]),
     "hpe_dwconv": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _f, _vp, _i, _vp]),
+    "hpe_dwconv7_bias": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _i, _vp]),
     "hpe_layernorm_nhwc": (_i, [_vp, _i, C.c_longlong, _i, _vp, _vp, _f, _vp, _i, _vp]),
     "hpe_patchify4": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "hpe_maxpool5": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _i, _vp]),

@@ -24,135 +24,283 @@ __device__ __forceinline__ uint4 pack8(const float* f) {
   return make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
 }
 
+constexpr int kDwThreads = 256;
 constexpr int kDwRX = 4;          // output pixels along x per thread (register sliding window)
-constexpr int kDwThreads = 128;
 
-// grid: (ceil(W / (kDwRX * px_per_cta)), H, B); block: Cv = C/8 channel groups x px_per_cta pixel groups.
-// LN epilogue: conv results of the CTA's pixels go through shared memory so one warp can normalise a pixel.
+// Work unit = "pixel group": kDwRX consecutive output pixels of one row x all C channels, handled by Cv = C/8 threads
+// (8 channels each).  Groups are numbered over the flattened (b, y, x-group) space and a CTA takes G = 256 / Cv
+// consecutive ones, so every lane is busy whatever W is and the groups of one CTA are vertically adjacent (their input
+// rows are shared through L1).  Per filter row a thread keeps the KS x 8 weights in registers and slides over
+// kDwRX + KS - 1 input pixels (one 16-byte load each).
+// LN epilogue: two fixed-order reductions over the Cv threads of a pixel through shared memory (mean, then centred
+// variance); the normalised values never leave registers before the bf16 store.
 template <int KS, bool LN>
-__global__ void __launch_bounds__(kDwThreads)
+__global__ void __launch_bounds__(kDwThreads, 2)
 dwconv_kernel(const __nv_bfloat16* __restrict__ x, int in_pitch, const float* __restrict__ wt /* [KS*KS][C] */,
               const float* __restrict__ a /* LN: bias | BNACT: scale */, const float* __restrict__ b2 /* LN: gamma | BNACT: shift */,
-              const float* __restrict__ b3 /* LN: beta */, float eps, int H, int W, int C,
-              __nv_bfloat16* __restrict__ y, int out_pitch, int groups_per_cta) {
-  extern __shared__ float tile[];                  // LN: [groups_per_cta * kDwRX][C] fp32
+              const float* __restrict__ b3 /* LN: beta */, float eps, int H, int W, int C, long long n_groups,
+              __nv_bfloat16* __restrict__ y, int out_pitch, int G, int red_lanes) {
+  extern __shared__ float smem_f[];                // LN: part[G*kDwRX][Cv], stat[G*kDwRX]
   constexpr int R = KS / 2;
+  constexpr int RX = kDwRX;
   const int Cv = C / 8;
   const int cv = threadIdx.x % Cv, pg = threadIdx.x / Cv;
-  const int b = blockIdx.z, oy = blockIdx.y;
-  const int ox0 = (blockIdx.x * groups_per_cta + pg) * kDwRX;
-  const bool active = pg < groups_per_cta && ox0 < W;
-  float acc[kDwRX][8];
+  const int gx = (W + RX - 1) / RX;
+  const long long gid = static_cast<long long>(blockIdx.x) * G + pg;
+  const bool active = pg < G && gid < n_groups;
+  const int xg = static_cast<int>(gid % gx), oy = static_cast<int>((gid / gx) % H);
+  const long long b = gid / (static_cast<long long>(gx) * H);
+  const int ox0 = xg * RX;
+  float acc[RX][8];
 #pragma unroll
-  for (int r = 0; r < kDwRX; ++r)
+  for (int r = 0; r < RX; ++r)
 #pragma unroll
     for (int e = 0; e < 8; ++e) acc[r][e] = 0.f;
   if (active) {
+#pragma unroll 1
     for (int ky = 0; ky < KS; ++ky) {
       const int iy = oy + ky - R;
       if (iy < 0 || iy >= H) continue;
+      float wk[KS][8];
+#pragma unroll
+      for (int kx = 0; kx < KS; ++kx) {
+        const float4 w0 = __ldg(reinterpret_cast<const float4*>(wt + static_cast<size_t>(ky * KS + kx) * C + cv * 8));
+        const float4 w1 = __ldg(reinterpret_cast<const float4*>(wt + static_cast<size_t>(ky * KS + kx) * C + cv * 8 + 4));
+        wk[kx][0] = w0.x; wk[kx][1] = w0.y; wk[kx][2] = w0.z; wk[kx][3] = w0.w;
+        wk[kx][4] = w1.x; wk[kx][5] = w1.y; wk[kx][6] = w1.z; wk[kx][7] = w1.w;
+      }
       const __nv_bfloat16* rowp = x + (static_cast<size_t>(b) * H + iy) * W * in_pitch + cv * 8;
 #pragma unroll
-      for (int ix_rel = 0; ix_rel < kDwRX + KS - 1; ++ix_rel) {
+      for (int ix_rel = 0; ix_rel < RX + KS - 1; ++ix_rel) {
         const int ix = ox0 + ix_rel - R;
         if (ix < 0 || ix >= W) continue;
         float v[8];
         unpack8(__ldg(reinterpret_cast<const uint4*>(rowp + static_cast<size_t>(ix) * in_pitch)), v);
 #pragma unroll
-        for (int r = 0; r < kDwRX; ++r) {
+        for (int r = 0; r < RX; ++r) {
           const int kx = ix_rel - r;
           if (kx < 0 || kx >= KS) continue;
-          const float4 w0 = __ldg(reinterpret_cast<const float4*>(wt + static_cast<size_t>(ky * KS + kx) * C + cv * 8));
-          const float4 w1 = __ldg(reinterpret_cast<const float4*>(wt + static_cast<size_t>(ky * KS + kx) * C + cv * 8 + 4));
-          acc[r][0] = fmaf(v[0], w0.x, acc[r][0]); acc[r][1] = fmaf(v[1], w0.y, acc[r][1]);
-          acc[r][2] = fmaf(v[2], w0.z, acc[r][2]); acc[r][3] = fmaf(v[3], w0.w, acc[r][3]);
-          acc[r][4] = fmaf(v[4], w1.x, acc[r][4]); acc[r][5] = fmaf(v[5], w1.y, acc[r][5]);
-          acc[r][6] = fmaf(v[6], w1.z, acc[r][6]); acc[r][7] = fmaf(v[7], w1.w, acc[r][7]);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) acc[r][e] = fmaf(v[e], wk[kx][e], acc[r][e]);
         }
       }
     }
   }
+  __nv_bfloat16* yo = y + ((static_cast<size_t>(b) * H + oy) * W + ox0) * out_pitch + cv * 8;
   if (!LN) {
     if (!active) return;
     float sc[8], sh[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) { sc[e] = __ldg(a + cv * 8 + e); sh[e] = __ldg(b2 + cv * 8 + e); }
 #pragma unroll
-    for (int r = 0; r < kDwRX; ++r) {
-      const int ox = ox0 + r;
-      if (ox >= W) break;
-      float o[8];
+    for (int r = 0; r < RX; ++r) {
+      if (ox0 + r < W) {
+        float o[8];
 #pragma unroll
-      for (int e = 0; e < 8; ++e) { const float t = fmaf(acc[r][e], sc[e], sh[e]); o[e] = t / (1.f + __expf(-t)); }
-      *reinterpret_cast<uint4*>(y + ((static_cast<size_t>(b) * H + oy) * W + ox) * out_pitch + cv * 8) = pack8(o);
+        for (int e = 0; e < 8; ++e) { const float t = fmaf(acc[r][e], sc[e], sh[e]); o[e] = t / (1.f + __expf(-t)); }
+        *reinterpret_cast<uint4*>(yo + static_cast<size_t>(r) * out_pitch) = pack8(o);
+      }
     }
     return;
   }
-  // ---- LayerNorm epilogue
+  // ---- LayerNorm over C for each of the group's RX pixels
+  float* part = smem_f;                              // [G*RX][Cv]
+  float* stat = smem_f + G * RX * Cv;                // [G*RX]
+  const int pairs = G * RX;
+  const int rp = threadIdx.x / red_lanes, rs = threadIdx.x % red_lanes;     // reducer: pixel slot, sub-lane
   if (active) {
 #pragma unroll
-    for (int r = 0; r < kDwRX; ++r)
+    for (int e = 0; e < 8; ++e) { const float bias = __ldg(a + cv * 8 + e);
 #pragma unroll
-      for (int e = 0; e < 8; ++e) tile[static_cast<size_t>(pg * kDwRX + r) * C + cv * 8 + e] = acc[r][e] + __ldg(a + cv * 8 + e);
+      for (int r = 0; r < RX; ++r) acc[r][e] += bias; }
+#pragma unroll
+    for (int r = 0; r < RX; ++r)
+      part[(pg * RX + r) * Cv + cv] = ((acc[r][0] + acc[r][1]) + (acc[r][2] + acc[r][3])) + ((acc[r][4] + acc[r][5]) + (acc[r][6] + acc[r][7]));
   }
   __syncthreads();
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = kDwThreads / 32;
-  for (int pl = warp; pl < groups_per_cta * kDwRX; pl += nwarps) {
-    const int ox = blockIdx.x * groups_per_cta * kDwRX + pl;
-    if (ox >= W) continue;
-    const float* t = tile + static_cast<size_t>(pl) * C;
+  {
     float s = 0.f;
-    for (int c = lane; c < C; c += 32) s += t[c];
+    if (rp < pairs) for (int c = rs; c < Cv; c += red_lanes) s += part[rp * Cv + c];
+    for (int o = red_lanes >> 1; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (rp < pairs && rs == 0) stat[rp] = s / C;
+  }
+  __syncthreads();
+  float mean[RX];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    const float mean = s / C;
-    float q = 0.f;
-    for (int c = lane; c < C; c += 32) { const float d = t[c] - mean; q += d * d; }
+  for (int r = 0; r < RX; ++r) mean[r] = active ? stat[pg * RX + r] : 0.f;
+  __syncthreads();                                   // stat and part are reused for the variance
+  if (active) {
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
-    const float rstd = rsqrtf(q / C + eps);
-    __nv_bfloat16* yo = y + ((static_cast<size_t>(b) * H + oy) * W + ox) * out_pitch;
-    for (int c8 = lane; c8 < Cv; c8 += 32) {
+    for (int r = 0; r < RX; ++r) {
+      float q = 0.f;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) { acc[r][e] -= mean[r]; q = fmaf(acc[r][e], acc[r][e], q); }
+      part[(pg * RX + r) * Cv + cv] = q;
+    }
+  }
+  __syncthreads();
+  {
+    float s = 0.f;
+    if (rp < pairs) for (int c = rs; c < Cv; c += red_lanes) s += part[rp * Cv + c];
+    for (int o = red_lanes >> 1; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (rp < pairs && rs == 0) stat[rp] = rsqrtf(s / C + eps);
+  }
+  __syncthreads();
+  if (!active) return;
+  float gam[8], bet[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) { gam[e] = __ldg(b2 + cv * 8 + e); bet[e] = __ldg(b3 + cv * 8 + e); }
+#pragma unroll
+  for (int r = 0; r < RX; ++r) {
+    if (ox0 + r < W) {
+      const float rstd = stat[pg * RX + r];
       float o[8];
 #pragma unroll
-      for (int e = 0; e < 8; ++e) { const int c = c8 * 8 + e; o[e] = (t[c] - mean) * rstd * __ldg(b2 + c) + __ldg(b3 + c); }
-      *reinterpret_cast<uint4*>(yo + c8 * 8) = pack8(o);
+      for (int e = 0; e < 8; ++e) o[e] = fmaf(acc[r][e] * rstd, gam[e], bet[e]);
+      *reinterpret_cast<uint4*>(yo + static_cast<size_t>(r) * out_pitch) = pack8(o);
     }
   }
 }
 
-// warp per pixel; C multiple of 8
+// ---- FMA-bound formulation of the 7x7 depthwise conv (the ConvNeXt block's 0.34 GFLOP/img run on the fp32 CUDA cores).
+// CTA = one image tile (th x tw outputs, halo 3) x one 64-channel slice, staged ONCE into shared memory as fp32 with a zero
+// halo; a lane owns a channel PAIR and keeps all 49 x 2 filter weights in registers; a warp computes 4 x 4 output blocks:
+// 100 conflict-free 8-byte shared loads feed 1568 FMAs with no bounds checks and no weight reloads.
+constexpr int kDtTY = 4, kDtRX = 4, kDtSlice = 64, kDtMaxWarps = 6;   // 2 CTAs/SM: one stages its tile while the other computes
+__global__ void __launch_bounds__(kDtMaxWarps * 32, 2)
+dwconv7_tiled_kernel(const __nv_bfloat16* __restrict__ x, int in_pitch, const float* __restrict__ wt /* [49][C] */,
+                     const float* __restrict__ bias, int H, int W, int C, int th, int tw, int tiles_x, int tiles_y, int n_slices,
+                     __nv_bfloat16* __restrict__ y, int out_pitch) {
+  extern __shared__ float tile[];                  // [(th+6)][(tw+6)][64]
+  int t = blockIdx.x;
+  const int slice = t % n_slices; t /= n_slices;
+  const int tx = t % tiles_x; t /= tiles_x;
+  const int ty = t % tiles_y; const int b = t / tiles_y;
+  const int x0 = tx * tw, y0 = ty * th, c0 = slice * kDtSlice;
+  const int pw = tw + 6, ph = th + 6;
+  // stage: 8 x (8 channels = 16 B) per pixel; 4 independent loads in flight per thread
+  const int n_items = ph * pw * 8;
+  for (int i0 = threadIdx.x; i0 < n_items; i0 += 4 * blockDim.x) {
+    uint4 v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int i = i0 + j * blockDim.x;
+      const int q = i & 7, pix = i >> 3;
+      const int iy = y0 - 3 + pix / pw, ix = x0 - 3 + pix % pw, c = c0 + q * 8;
+      v[j] = make_uint4(0u, 0u, 0u, 0u);
+      if (i < n_items && iy >= 0 && iy < H && ix >= 0 && ix < W && c < C)
+        v[j] = __ldg(reinterpret_cast<const uint4*>(x + ((static_cast<size_t>(b) * H + iy) * W + ix) * in_pitch + c));
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int i = i0 + j * blockDim.x;
+      if (i < n_items) {
+        float f[8]; unpack8(v[j], f);
+        float4* d = reinterpret_cast<float4*>(tile + static_cast<size_t>(i >> 3) * kDtSlice + (i & 7) * 8);
+        d[0] = make_float4(f[0], f[1], f[2], f[3]); d[1] = make_float4(f[4], f[5], f[6], f[7]);
+      }
+    }
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const int ch = c0 + 2 * lane;
+  const bool chok = ch < C;
+  float2 w[49];
+#pragma unroll
+  for (int k = 0; k < 49; ++k) w[k] = chok ? __ldg(reinterpret_cast<const float2*>(wt + static_cast<size_t>(k) * C + ch)) : make_float2(0.f, 0.f);
+  const float2 bs = chok ? __ldg(reinterpret_cast<const float2*>(bias + ch)) : make_float2(0.f, 0.f);
+  __syncthreads();
+  const int nbx = tw / kDtRX, nblk = (th / kDtTY) * nbx;
+  for (int blk = warp; blk < nblk; blk += nwarps) {
+    const int by = (blk / nbx) * kDtTY, bx = (blk % nbx) * kDtRX;
+    float2 acc[kDtTY][kDtRX];
+#pragma unroll
+    for (int ry = 0; ry < kDtTY; ++ry)
+#pragma unroll
+      for (int rx = 0; rx < kDtRX; ++rx) acc[ry][rx] = bs;
+    const float* tb = tile + (static_cast<size_t>(by) * pw + bx) * kDtSlice + 2 * lane;
+#pragma unroll
+    for (int iy = 0; iy < kDtTY + 6; ++iy) {
+#pragma unroll
+      for (int ix = 0; ix < kDtRX + 6; ++ix) {
+        const float2 v = *reinterpret_cast<const float2*>(tb + (static_cast<size_t>(iy) * pw + ix) * kDtSlice);
+#pragma unroll
+        for (int ry = 0; ry < kDtTY; ++ry) {
+          const int ky = iy - ry;
+          if (ky < 0 || ky > 6) continue;
+#pragma unroll
+          for (int rx = 0; rx < kDtRX; ++rx) {
+            const int kx = ix - rx;
+            if (kx < 0 || kx > 6) continue;
+            acc[ry][rx].x = fmaf(v.x, w[ky * 7 + kx].x, acc[ry][rx].x);
+            acc[ry][rx].y = fmaf(v.y, w[ky * 7 + kx].y, acc[ry][rx].y);
+          }
+        }
+      }
+    }
+    if (chok) {
+#pragma unroll
+      for (int ry = 0; ry < kDtTY; ++ry) {
+        const int oy = y0 + by + ry;
+        if (oy >= H) continue;
+#pragma unroll
+        for (int rx = 0; rx < kDtRX; ++rx) {
+          const int ox = x0 + bx + rx;
+          if (ox < W)
+            *reinterpret_cast<uint32_t*>(y + ((static_cast<size_t>(b) * H + oy) * W + ox) * out_pitch + ch) = pack_bf16(acc[ry][rx].x, acc[ry][rx].y);
+        }
+      }
+    }
+  }
+}
+
+// A pixel is normalised by a group of `gsz` lanes (power of two >= C/8, at most 32; narrow tensors put 2-8 pixels in a
+// warp); the pixel's channels stay in registers (C <= 1024: 4 x 16 B per lane), so the kernel is one read + one write and
+// in-place safe.
 __global__ void __launch_bounds__(256)
 layernorm_nhwc_kernel(const __nv_bfloat16* __restrict__ x, int in_pitch, const float* __restrict__ gamma,
-                      const float* __restrict__ beta, float eps, long long M, int C, __nv_bfloat16* __restrict__ y, int out_pitch) {
-  const long long pix = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  if (pix >= M) return;
+                      const float* __restrict__ beta, float eps, long long M, int C, int gsz,
+                      __nv_bfloat16* __restrict__ y, int out_pitch) {
+  const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long pix = tid / gsz;
+  const int sub = static_cast<int>(tid % gsz);
+  const bool ok = pix < M;
   const int Cv = C / 8;
-  const __nv_bfloat16* xp = x + pix * in_pitch;
+  const __nv_bfloat16* xp = x + (ok ? pix : 0) * in_pitch;
+  float v[4][8];
   float s = 0.f, q = 0.f;
-  for (int c8 = lane; c8 < Cv; c8 += 32) {
-    float v[8]; unpack8(__ldg(reinterpret_cast<const uint4*>(xp + c8 * 8)), v);
 #pragma unroll
-    for (int e = 0; e < 8; ++e) s += v[e];
+  for (int j = 0; j < 4; ++j) {
+    const int c8 = sub + gsz * j;
+    if (ok && c8 < Cv) {
+      unpack8(__ldg(reinterpret_cast<const uint4*>(xp + c8 * 8)), v[j]);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) s += v[j][e];
+    }
   }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  for (int o = gsz >> 1; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
   const float mean = s / C;
-  for (int c8 = lane; c8 < Cv; c8 += 32) {
-    float v[8]; unpack8(__ldg(reinterpret_cast<const uint4*>(xp + c8 * 8)), v);
 #pragma unroll
-    for (int e = 0; e < 8; ++e) { const float d = v[e] - mean; q += d * d; }
-  }
+  for (int j = 0; j < 4; ++j)
+    if (ok && sub + gsz * j < Cv) {
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+      for (int e = 0; e < 8; ++e) { v[j][e] -= mean; q = fmaf(v[j][e], v[j][e], q); }
+    }
+  for (int o = gsz >> 1; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
   const float rstd = rsqrtf(q / C + eps);
-  __nv_bfloat16* yp = y + pix * out_pitch;
-  for (int c8 = lane; c8 < Cv; c8 += 32) {
-    float v[8], o[8]; unpack8(__ldg(reinterpret_cast<const uint4*>(xp + c8 * 8)), v);
+  __nv_bfloat16* yp = y + (ok ? pix : 0) * out_pitch;
 #pragma unroll
-    for (int e = 0; e < 8; ++e) o[e] = (v[e] - mean) * rstd * __ldg(gamma + c8 * 8 + e) + __ldg(beta + c8 * 8 + e);
-    *reinterpret_cast<uint4*>(yp + c8 * 8) = pack8(o);
+  for (int j = 0; j < 4; ++j) {
+    const int c8 = sub + gsz * j;
+    if (ok && c8 < Cv) {
+      const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + c8 * 8)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + c8 * 8 + 4));
+      const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta + c8 * 8)), b1 = __ldg(reinterpret_cast<const float4*>(beta + c8 * 8 + 4));
+      float o[8];
+      o[0] = fmaf(v[j][0] * rstd, g0.x, b0.x); o[1] = fmaf(v[j][1] * rstd, g0.y, b0.y);
+      o[2] = fmaf(v[j][2] * rstd, g0.z, b0.z); o[3] = fmaf(v[j][3] * rstd, g0.w, b0.w);
+      o[4] = fmaf(v[j][4] * rstd, g1.x, b1.x); o[5] = fmaf(v[j][5] * rstd, g1.y, b1.y);
+      o[6] = fmaf(v[j][6] * rstd, g1.z, b1.z); o[7] = fmaf(v[j][7] * rstd, g1.w, b1.w);
+      *reinterpret_cast<uint4*>(yp + c8 * 8) = pack8(o);
+    }
   }
 }
 
@@ -256,25 +404,62 @@ extern "C" int hpe_dwconv(const void* x, int in_pitch, int B, int H, int W, int 
   HPE_CHECK_ARG(mode == 0 || (mode == 1 && p2), "hpe_dwconv: mode 0 = scale/shift+SiLU, 1 = bias+LayerNorm (needs beta)");
   const int Cv = C / 8;
   if (Cv > kDwThreads) return fail(HPE_EUNSUPPORTED, "hpe_dwconv: C=%d exceeds %d", C, kDwThreads * 8);
-  const int groups = kDwThreads / Cv;                       // pixel groups per CTA
-  const size_t smem = mode == 1 ? (size_t)groups * kDwRX * C * 4 : 0;
-  dim3 grid((W + groups * kDwRX - 1) / (groups * kDwRX), H, B);
+  const int G = kDwThreads / Cv;                            // pixel groups per CTA
+  const long long n_groups = (long long)B * H * ((W + kDwRX - 1) / kDwRX);
+  int red_lanes = 1;                                        // lanes cooperating on one pixel's reduction (power of two)
+  while (red_lanes < 32 && G * kDwRX * red_lanes * 2 <= kDwThreads && red_lanes * 2 <= Cv) red_lanes <<= 1;
+  const size_t smem = mode == 1 ? ((size_t)G * kDwRX * Cv + (size_t)G * kDwRX) * 4 : 0;
+  const long long grid = (n_groups + G - 1) / G;
+  if (grid > 0x7fffffffLL) return fail(HPE_EUNSUPPORTED, "hpe_dwconv: too many pixel groups");
   cudaStream_t st = (cudaStream_t)stream;
   const __nv_bfloat16* xi = (const __nv_bfloat16*)x; __nv_bfloat16* yo = (__nv_bfloat16*)y;
-  if (ksize == 7 && mode == 1)      dwconv_kernel<7, true><<<grid, kDwThreads, smem, st>>>(xi, in_pitch, w_taps, p0, p1, p2, eps, H, W, C, yo, out_pitch, groups);
-  else if (ksize == 3 && mode == 0) dwconv_kernel<3, false><<<grid, kDwThreads, smem, st>>>(xi, in_pitch, w_taps, p0, p1, p2, eps, H, W, C, yo, out_pitch, groups);
-  else if (ksize == 7 && mode == 0) dwconv_kernel<7, false><<<grid, kDwThreads, smem, st>>>(xi, in_pitch, w_taps, p0, p1, p2, eps, H, W, C, yo, out_pitch, groups);
-  else if (ksize == 3 && mode == 1) dwconv_kernel<3, true><<<grid, kDwThreads, smem, st>>>(xi, in_pitch, w_taps, p0, p1, p2, eps, H, W, C, yo, out_pitch, groups);
+#define HPE_DW_LAUNCH(KS, LNM) dwconv_kernel<KS, LNM><<<(unsigned)grid, kDwThreads, smem, st>>>(xi, in_pitch, w_taps, p0, p1, p2, eps, H, W, C, n_groups, yo, out_pitch, G, red_lanes)
+  if (ksize == 7 && mode == 1)      HPE_DW_LAUNCH(7, true);
+  else if (ksize == 7 && mode == 0) HPE_DW_LAUNCH(7, false);
+  else if (ksize == 3 && mode == 0) HPE_DW_LAUNCH(3, false);
+  else if (ksize == 3 && mode == 1) HPE_DW_LAUNCH(3, true);
   else return fail(HPE_EUNSUPPORTED, "hpe_dwconv: kernel size %d not in {3,7}", ksize);
+#undef HPE_DW_LAUNCH
   return launch_status("dwconv_kernel");
+}
+
+extern "C" int hpe_dwconv7_bias(const void* x, int in_pitch, int B, int H, int W, int C, const float* w_taps, const float* bias,
+                               void* y, int out_pitch, void* stream) {
+  HPE_CHECK_ARG(x && y && w_taps && bias, "hpe_dwconv7_bias: null pointer");
+  HPE_CHECK_ARG(B > 0 && H > 0 && W > 0 && C > 0 && C % 8 == 0, "hpe_dwconv7_bias: C must be a positive multiple of 8");
+  HPE_CHECK_ARG(HPE_PITCH_OK(in_pitch, C) && HPE_PITCH_OK(out_pitch, C), "hpe_dwconv7_bias: bad channel pitch");
+  HPE_CHECK_ARG((((uintptr_t)x | (uintptr_t)y | (uintptr_t)w_taps | (uintptr_t)bias) & 15) == 0, "hpe_dwconv7_bias: misaligned pointer");
+  auto tile_of = [](int n) { int t = (n + 3) / 4 * 4; return t > 16 ? 16 : t; };     // (16+6)*(12+6)*256 B = 99 KB -> 2 CTAs/SM
+  // tiles as even as possible: n = 24 -> two tiles of 12, not 16 + 8
+  auto even_tile = [&](int n) { const int full = tile_of(n); const int cnt = (n + full - 1) / full; return ((n + cnt - 1) / cnt + 3) / 4 * 4; };
+  int th = even_tile(H), tw = even_tile(W);
+  if (th * tw > 16 * 12) { if (tw > 12) tw = 12; else th = 12; }
+  const int tiles_y = (H + th - 1) / th, tiles_x = (W + tw - 1) / tw, n_slices = (C + kDtSlice - 1) / kDtSlice;
+  const int nblk = (th / kDtTY) * (tw / kDtRX);
+  const int warps = nblk <= kDtMaxWarps ? nblk : kDtMaxWarps;
+  const size_t smem = (size_t)(th + 6) * (tw + 6) * kDtSlice * 4;
+  static thread_local size_t configured = 0;
+  if (smem > 48 * 1024 && smem > configured) {
+    HPE_CUDA_OK(cudaFuncSetAttribute((const void*)dwconv7_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  const long long grid = (long long)B * tiles_y * tiles_x * n_slices;
+  if (grid > 0x7fffffffLL) return fail(HPE_EUNSUPPORTED, "hpe_dwconv7_bias: too many tiles");
+  dwconv7_tiled_kernel<<<(unsigned)grid, warps * 32, smem, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, in_pitch, w_taps, bias, H, W, C, th, tw,
+                                                                                 tiles_x, tiles_y, n_slices, (__nv_bfloat16*)y, out_pitch);
+  return launch_status("dwconv7_tiled_kernel");
 }
 
 extern "C" int hpe_layernorm_nhwc(const void* x, int in_pitch, long long M, int C, const float* gamma, const float* beta,
                                   float eps, void* y, int out_pitch, void* stream) {
   HPE_CHECK_ARG(x && y && gamma && beta, "hpe_layernorm_nhwc: null pointer");
   HPE_CHECK_ARG(M > 0 && C > 0 && C % 8 == 0 && HPE_PITCH_OK(in_pitch, C) && HPE_PITCH_OK(out_pitch, C), "hpe_layernorm_nhwc: bad size/pitch");
-  const long long blocks = (M * 32 + 255) / 256;
-  layernorm_nhwc_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, in_pitch, gamma, beta, eps, M, C,
+  if (C > 1024) return fail(HPE_EUNSUPPORTED, "hpe_layernorm_nhwc: C=%d exceeds 1024", C);
+  HPE_CHECK_ARG((((uintptr_t)gamma | (uintptr_t)beta) & 15) == 0, "hpe_layernorm_nhwc: gamma/beta must be 16-byte aligned");
+  int gsz = 4;
+  while (gsz < 32 && gsz < C / 8) gsz <<= 1;       // smallest power of two >= C/8, capped at 32
+  const long long blocks = (M * gsz + 255) / 256;
+  layernorm_nhwc_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, in_pitch, gamma, beta, eps, M, C, gsz,
                                                                           (__nv_bfloat16*)y, out_pitch);
   return launch_status("layernorm_nhwc_kernel");
 }

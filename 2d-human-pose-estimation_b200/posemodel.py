@@ -143,6 +143,14 @@ def _dwconv(x, w_taps, p0, p1, p2, eps, ksize, mode, y):
     _lib.check(rc, "hpe_dwconv")
 
 
+def _dwconv7_bias(x, w_taps, bias, y):
+    B, H, W, C = x.shape
+    with torch.cuda.device(x.device):
+        rc = _lib.lib().hpe_dwconv7_bias(_lib.ptr(x), _pitch(x), B, H, W, C, _lib.ptr(w_taps), _lib.ptr(bias), _lib.ptr(y), _pitch(y),
+                                         _lib.stream_ptr())
+    _lib.check(rc, "hpe_dwconv7_bias")
+
+
 def _layernorm(x, gamma, beta, eps, y):
     B, H, W, C = x.shape
     with torch.cuda.device(x.device):
@@ -259,7 +267,11 @@ class _PosePlan:
             for blk in bb.stages[i]:
                 wt = f32(blk.dwconv.weight.detach().reshape(C, 49).t())             # [49][C]
                 p0, p1, p2 = f32(blk.dwconv.bias), f32(blk.norm.weight), f32(blk.norm.bias); self.keep += [wt, p0, p1, p2]
-                step(lambda x=cur, y=t1, wt=wt, p0=p0, p1=p1, p2=p2, e=blk.norm.eps: _dwconv(x, wt, p0, p1, p2, e, 7, 1, y))
+                if os.environ.get("HPE_B200_DWCONV", "tiled") == "fused":      # one kernel: dwconv + bias + LayerNorm
+                    step(lambda x=cur, y=t1, wt=wt, p0=p0, p1=p1, p2=p2, e=blk.norm.eps: _dwconv(x, wt, p0, p1, p2, e, 7, 1, y))
+                else:                                                          # FMA-bound tiled dwconv, then LayerNorm in place
+                    step(lambda x=cur, y=t1, wt=wt, p0=p0: _dwconv7_bias(x, wt, p0, y))
+                    step(lambda y=t1, p1=p1, p2=p2, e=blk.norm.eps: _layernorm(y, p1, p2, e, y))
                 conv(CONV_1x1, t1, t2, blk.pwconv1.weight.detach().reshape(4 * C, C, 1, 1), ones(4 * C), blk.pwconv1.bias, ACT_GELU)
                 gam = blk.gamma.detach().float()
                 conv(CONV_1x1, t2, other, blk.pwconv2.weight.detach().reshape(C, 4 * C, 1, 1), gam, gam * blk.pwconv2.bias.detach().float(),

@@ -278,6 +278,9 @@ int hpe_keypoint_loss(const float* pred, int pred_stride, const float* gt, int g
  * ---------------------------------------------------------------------------------------------- */
 int hpe_dwconv(const void* x, int in_pitch, int B, int H, int W, int C, int ksize, int mode, const float* w_taps,
                const float* p0, const float* p1, const float* p2, float eps, void* y, int out_pitch, void* stream);
+/* depthwise 7x7 + bias only (FMA-bound tiled formulation; the LayerNorm that follows is hpe_layernorm_nhwc) */
+int hpe_dwconv7_bias(const void* x, int in_pitch, int B, int H, int W, int C, const float* w_taps, const float* bias,
+                     void* y, int out_pitch, void* stream);
 int hpe_layernorm_nhwc(const void* x, int in_pitch, long long M, int C, const float* gamma, const float* beta, float eps,
                        void* y, int out_pitch, void* stream);
 int hpe_patchify4(const float* img_nchw, int B, int H, int W, void* out, void* stream);

@@ -96,7 +96,7 @@ def test_conv_channel_slices_and_final_slice(hpe, cuda_dev):
     assert (out[:, 0] == -3.0).all()
 
 
-@pytest.mark.parametrize("C,H,W", [(96, 16, 12), (384, 9, 7), (768, 4, 3), (1024, 8, 6)])
+@pytest.mark.parametrize("C,H,W", [(96, 16, 12), (384, 9, 7), (768, 4, 3), (1024, 8, 6), (192, 32, 24), (96, 64, 48)])
 def test_dwconv7_layernorm(hpe, cuda_dev, C, H, W):
     _, pm = _mods()
     g = torch.Generator().manual_seed(5)
@@ -109,6 +109,14 @@ def test_dwconv7_layernorm(hpe, cuda_dev, C, H, W):
     pm._dwconv(nhwc(x), d(w.reshape(C, 49).t()), d(bias), d(gam), d(bet), 1e-6, 7, 1, y)
     torch.cuda.synchronize()
     check(nchw(y), ref, "dwconv7+LN")
+    # tiled FMA-bound formulation: dwconv + bias, then LayerNorm in place
+    y2 = torch.empty((B, H, W, C), dtype=torch.bfloat16, device="cuda")
+    pm._dwconv7_bias(nhwc(x), d(w.reshape(C, 49).t()), d(bias), y2)
+    torch.cuda.synchronize()
+    check(nchw(y2), F.conv2d(x, w, bias, padding=3, groups=C), "tiled dwconv7+bias")
+    pm._layernorm(y2, d(gam), d(bet), 1e-6, y2)
+    torch.cuda.synchronize()
+    check(nchw(y2), ref, "tiled dwconv7 -> LN", k=2.0)            # one extra bf16 rounding before the normalisation
 
 
 def test_dwconv3_bn_silu_layernorm_pool_upsample(hpe, cuda_dev):
