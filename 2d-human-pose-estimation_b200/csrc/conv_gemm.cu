@@ -23,6 +23,7 @@
 #include "hpe_common.cuh"
 #include "ptx_sm100.cuh"
 #include "tma_host.cuh"
+#include "conv_halo.cuh"
 #include <stdlib.h>
 
 namespace hpe {
@@ -450,7 +451,20 @@ struct hpe_conv_plan {
   const void *x, *w, *res;
   void* y;
   const void* fn;
+  int halo_taps_y, halo_boxes;        // != 0: the layer runs on the y-halo variant (conv_halo.cu)
+  HaloParams hp;
 };
+
+// Layers whose generic kernel is operand-delivery bound and that fit the y-halo variant: the stem, and 3x3/s1 64->64.
+static bool halo_eligible(const hpe_conv_desc* d, int Ho, int Wo) {
+  const char* e = getenv("HPE_B200_HALO");
+  if (e && e[0] == '0') return false;
+  if (d->has_residual || d->in_cstride || d->out_cstride) return false;
+  const bool shape_ok = d->Cout == 64 && (Wo + 7) / 8 * 8 * ((Ho + 15) / 16 * 16) <= (long long)Wo * Ho * 9 / 8;   // <= 12.5 % padded
+  if (d->kind == HPE_CONV_STEM7x7) return shape_ok;
+  if (d->kind == HPE_CONV_3x3) return shape_ok && d->Cin == 64 && d->stride == 1;
+  return false;
+}
 
 static int desc_check(const hpe_conv_desc* d, const char* fn) {
   HPE_CHECK_ARG(d, "%s: null desc", fn);
@@ -691,6 +705,16 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
     if (e != cudaSuccess) { delete pl; return fail(HPE_ECUDA, "cudaFuncSetAttribute(smem=%zu) failed: %s", pl->smem, cudaGetErrorString(e)); }
   }
   pl->x = pl->w = pl->res = nullptr; pl->y = nullptr;
+  pl->halo_taps_y = pl->halo_boxes = 0;
+  if (halo_eligible(d, pl->Ho, pl->Wo)) {
+    const bool stem = d->kind == HPE_CONV_STEM7x7;
+    pl->halo_taps_y = stem ? 4 : 3; pl->halo_boxes = stem ? 1 : 3;
+    pl->hp.tiles_x = (pl->Wo + 7) / 8; pl->hp.tiles_y = (pl->Ho + 15) / 16;
+    pl->hp.num_tiles = pl->hp.tiles_x * pl->hp.tiles_y * d->B;
+    pl->hp.x_lo = stem ? 0 : 1; pl->hp.y_lo = stem ? 2 : 1;
+    pl->grid = pl->hp.num_tiles < num_sms() ? pl->hp.num_tiles : num_sms();
+    p.tw = 8; p.th = 16; p.nb = 1;               // brick of the output / A maps encoded below
+  }
   *out = pl;
   return HPE_OK;
 }
@@ -708,14 +732,14 @@ static int encode_plan_maps(hpe_conv_plan* pl, const void* x, const void* w, con
       const uint64_t Hs = d.H / 2, Ws = d.W / 2, Wp = Ws + kS2DPad;
       const uint64_t dims[4] = {64, Ws, Hs, (uint64_t)d.B};
       const uint64_t str[3] = {32, Wp * 32, Hs * Wp * 32};           // overlapping 64-element windows, 16 el apart
-      const uint32_t box[4] = {64, (uint32_t)p.tw, (uint32_t)p.th, (uint32_t)p.nb};
+      const uint32_t box[4] = {64, (uint32_t)p.tw, (uint32_t)(pl->halo_taps_y ? 16 + pl->halo_taps_y - 1 : p.th), (uint32_t)p.nb};
       rc = encode_map(&pl->tmA, x, 4, dims, str, box, ones, "stem A");
     } else {
       const uint64_t C = d.Cin, P = d.in_cstride ? d.in_cstride : d.Cin;      // P = channel pitch of a pixel
       const uint64_t dims[4] = {C, (uint64_t)d.W, (uint64_t)d.H, (uint64_t)d.B};
       const uint64_t str[3] = {P * 2, (uint64_t)d.W * P * 2, (uint64_t)d.H * d.W * P * 2};
       const uint32_t s = (uint32_t)p.in_stride;
-      const uint32_t box[4] = {64, (uint32_t)p.tw * s, (uint32_t)p.th * s, (uint32_t)p.nb};
+      const uint32_t box[4] = {64, (uint32_t)p.tw * s, (uint32_t)(pl->halo_taps_y ? 16 + pl->halo_taps_y - 1 : p.th * s), (uint32_t)p.nb};
       const uint32_t es[4] = {1, s, s, 1};
       rc = encode_map(&pl->tmA, x, 4, dims, str, box, es, "A");
     }
@@ -727,7 +751,7 @@ static int encode_plan_maps(hpe_conv_plan* pl, const void* x, const void* w, con
     const uint64_t K = ktot(&d), R = wrows(&d);
     const uint64_t dims[2] = {K, R};
     const uint64_t str[1] = {K * 2};
-    const uint32_t box[2] = {64, (uint32_t)pl->block_n};
+    const uint32_t box[2] = {64, (uint32_t)(pl->halo_taps_y ? 64 : pl->block_n)};
     rc = encode_map(&pl->tmW, w, 2, dims, str, box, ones, "W");
     if (rc) return rc;
     pl->w = w;
@@ -780,6 +804,11 @@ extern "C" int hpe_conv_run(hpe_conv_plan* pl, const void* x, const void* w_pack
     HPE_CUDA_OK(cudaMemsetAsync(y, 0, (size_t)pl->d.B * pl->Ho * pl->Wo * pl->d.Cout * 2, (cudaStream_t)stream));
   int rc = encode_plan_maps(pl, x, w_packed, residual, y);
   if (rc) return rc;
+  if (pl->halo_taps_y) {
+    pl->hp.scale = scale; pl->hp.shift = shift;
+    return halo_launch(pl->halo_taps_y, pl->halo_boxes, pl->d.act, &pl->tmA, &pl->tmW, &pl->tmOut.m[0], pl->hp, pl->grid,
+                       (cudaStream_t)stream);
+  }
   ConvParams p = pl->p;
   p.scale = scale; p.shift = shift;
   p.hm_out = pl->d.kind == HPE_CONV_FINAL ? (float*)y : nullptr;

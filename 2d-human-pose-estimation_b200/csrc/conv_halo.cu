@@ -1,0 +1,203 @@
+// "y-halo" implicit-GEMM convolution for the layers whose generic kernel is bound by operand delivery from L2
+// (profiles/: one TMA box per filter tap moves 7x-27x the algorithmic bytes through the L2->SM fabric):
+//   * the 7x7/s2 stem on the space-to-depth image (4 row taps, K = 64 per tap, Cout = 64),
+//   * 3x3 / stride 1 / 64 -> 64 (ResNet layer1 conv2; also its backward-data conv).
+// An M tile is an 8-wide x 16-tall brick of ONE image, so a filter-row shift dy is a shift of 8 shared-memory rows =
+// 1024 bytes = exactly one SWIZZLE_128B atom: the A operand of every row tap is the SAME halo'd TMA box
+// {64 ch, 8 px, 16 + taps_y - 1 rows} read through a 1024-byte-aligned descriptor offset.  Column taps (3x3: dx = -1,0,1)
+// use one such box each.  The whole packed weight (<= 72 KB) is loaded into shared memory once per CTA.
+// L2->SM traffic per 128-pixel tile: stem 19 KB instead of 96 KB, 3x3 54 KB instead of 216 KB.
+//
+// Warp roles as in conv_gemm.cu: warp 0 TMA producer, warp 1 TMEM + tcgen05.mma issuer, warps 3-10 epilogue
+// (tcgen05.ld -> scale/shift -> ReLU|SiLU -> bf16 -> swizzled smem -> TMA store).
+#include "hpe_common.cuh"
+#include "ptx_sm100.cuh"
+#include "tma_host.cuh"
+#include "conv_halo.cuh"
+
+namespace hpe {
+using namespace ptx;
+
+constexpr int kHThreads = 352, kHEpiThreads = 256, kHEpiWarp0 = 3;
+constexpr int kHN = 64;                       // Cout = BLOCK_N
+constexpr int kHStages = 2;                   // halo'd A tiles in flight
+constexpr int kHNumSB = 2;                    // epilogue staging buffers (16 KB each)
+constexpr int kHSBBytes = 128 * 64 * 2;
+
+__device__ __forceinline__ uint4 h_lds_v4(uint32_t addr) {
+  uint4 r;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(addr));
+  return r;
+}
+__device__ __forceinline__ void h_sts_v4(uint32_t addr, const uint4& v) {
+  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// TAPS_Y row taps per box, BOXES column taps (one halo'd box each)
+template <int TAPS_Y, int BOXES, int ACT>
+__global__ void __launch_bounds__(kHThreads, 1)
+conv_yhalo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
+                  const __grid_constant__ CUtensorMap tmOut, const HaloParams p) {
+  constexpr int kTaps = TAPS_Y * BOXES;
+  constexpr int kBoxRows = (16 + TAPS_Y - 1) * 8;                  // smem rows (128 B each) of one halo'd box
+  constexpr int kBoxBytes = kBoxRows * 128;                        // multiple of 1024
+  constexpr int kABytes = BOXES * kBoxBytes;
+  constexpr int kWBytes = kTaps * kHN * 128;                       // [tap][64 rows][64 k] bf16
+  constexpr int kOffW = kHStages * kABytes;
+  constexpr int kOffSB = kOffW + kWBytes;
+  constexpr int kOffSS = kOffSB + kHNumSB * kHSBBytes;
+  constexpr int kOffBar = kOffSS + 2 * kHN * 4;
+  constexpr uint32_t kIdesc = make_idesc_bf16_m128(kHN);
+  constexpr int kTmemCols = 128;                                   // 2 accumulators x 64 columns
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem; uint8_t* sW = smem + kOffW; uint8_t* sSB = smem + kOffSB;
+  float* sScale = reinterpret_cast<float*>(smem + kOffSS); float* sShift = sScale + kHN;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kOffBar);
+  uint64_t* full_bar = bars;                    // [kHStages]
+  uint64_t* empty_bar = bars + kHStages;        // [kHStages]
+  uint64_t* tfull_bar = bars + 2 * kHStages;    // [2]
+  uint64_t* tempty_bar = tfull_bar + 2;         // [2]
+  uint64_t* wfull_bar = tempty_bar + 2;         // [1]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wfull_bar + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmA); prefetch_tmap(&tmW); prefetch_tmap(&tmOut);
+    for (int s = 0; s < kHStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], kHEpiThreads / 32); }
+    mbar_init(wfull_bar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) { tmem_alloc(tmem_slot, kTmemCols); tmem_relinquish(); }
+  for (int i = threadIdx.x; i < kHN; i += kHThreads) { sScale[i] = __ldg(p.scale + i); sShift[i] = __ldg(p.shift + i); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  griddep_launch_dependents();
+  griddep_wait();
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // weights: resident for the whole kernel (they do not depend on the previous layer, but TMA reads global memory
+      // written by the pack kernel earlier in the stream: keep it after griddep_wait)
+      mbar_arrive_expect_tx(wfull_bar, kWBytes);
+      for (int t = 0; t < kTaps; ++t) tma_load_2d(sW + t * kHN * 128, &tmW, wfull_bar, t * 64, 0);
+      int stage = 0; uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        const int x0 = (tile % p.tiles_x) * 8, y0 = ((tile / p.tiles_x) % p.tiles_y) * 16, b = tile / (p.tiles_x * p.tiles_y);
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        mbar_arrive_expect_tx(&full_bar[stage], kABytes);
+#pragma unroll
+        for (int bx = 0; bx < BOXES; ++bx)
+          tma_load_4d(sA + stage * kABytes + bx * kBoxBytes, &tmA, &full_bar[stage], 0, x0 + bx - p.x_lo, y0 - p.y_lo, b);
+        if (++stage == kHStages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      mbar_wait(wfull_bar, 0);
+      int stage = 0; uint32_t phase = 0; int it = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+        const int acc = it & 1;
+        mbar_wait(&tempty_bar[acc], ((it >> 1) & 1) ^ 1);
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * kHN;
+#pragma unroll
+        for (int bx = 0; bx < BOXES; ++bx)
+#pragma unroll
+          for (int ty = 0; ty < TAPS_Y; ++ty) {
+            const int tap = ty * BOXES + bx;                        // packed weight order: tap = ky * kw + kx
+            const uint64_t adesc = make_sw128_kmajor_desc(sA + stage * kABytes + bx * kBoxBytes + ty * 1024);
+            const uint64_t bdesc = make_sw128_kmajor_desc(sW + tap * kHN * 128);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, kIdesc, (bx | ty | k) != 0);
+          }
+        umma_commit(&empty_bar[stage]);
+        umma_commit(&tfull_bar[acc]);
+        if (++stage == kHStages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp >= kHEpiWarp0) {
+    const int ew = warp & 3, half = (warp - kHEpiWarp0) >> 2;
+    const int row = ew * 32 + lane;
+    const bool leader = threadIdx.x == kHEpiWarp0 * 32;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      const int x0 = (tile % p.tiles_x) * 8, y0 = ((tile / p.tiles_x) % p.tiles_y) * 16, b = tile / (p.tiles_x * p.tiles_y);
+      const int acc = it & 1, sb = it % kHNumSB;
+      mbar_wait(&tfull_bar[acc], (it >> 1) & 1);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * kHN + half * 32;
+      if (leader) bulk_wait_read<kHNumSB - 1>();                  // the store that last used this staging buffer has left smem
+      uint32_t v[32];
+      tmem_ld_x32(taddr, v);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+      named_bar_sync(2, kHEpiThreads);                             // leader's wait is visible before anyone writes the buffer
+      const uint32_t rowp = smem_u32(sSB + sb * kHSBBytes) + row * 128;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float o[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const int n = half * 32 + j * 8 + e;
+          o[e] = fmaf(__uint_as_float(v[j * 8 + e]), sScale[n], sShift[n]);
+          if (ACT == HPE_ACT_RELU) o[e] = fmaxf(o[e], 0.f);
+          if (ACT == HPE_ACT_SILU) o[e] = o[e] / (1.f + __expf(-o[e]));
+        }
+        const uint4 pk = make_uint4(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]), pack_bf16(o[6], o[7]));
+        h_sts_v4(rowp + (((half * 4 + j) ^ (row & 7)) << 4), pk);
+      }
+      fence_proxy_async_smem();
+      named_bar_sync(1, kHEpiThreads);
+      if (leader) { tma_store_4d(&tmOut, sSB + sb * kHSBBytes, 0, x0, y0, b); bulk_commit(); }
+    }
+    if (leader) bulk_wait_all();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, kTmemCols); }
+}
+
+template <int TAPS_Y, int BOXES>
+static size_t halo_smem_bytes() {
+  return (size_t)kHStages * BOXES * (16 + TAPS_Y - 1) * 8 * 128 + (size_t)TAPS_Y * BOXES * kHN * 128 + kHNumSB * kHSBBytes + 2 * kHN * 4 +
+         16 * 8 + 16 + 1024;
+}
+
+typedef void (*HaloFn)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const HaloParams);
+
+int halo_launch(int taps_y, int boxes, int act, const CUtensorMap* tmA, const CUtensorMap* tmW, const CUtensorMap* tmOut,
+                const HaloParams& p, int grid, cudaStream_t stream) {
+  HaloFn fn = nullptr; size_t smem = 0;
+  if (taps_y == 4 && boxes == 1) {
+    smem = halo_smem_bytes<4, 1>();
+    fn = act == HPE_ACT_RELU ? conv_yhalo_kernel<4, 1, HPE_ACT_RELU> : (act == HPE_ACT_SILU ? conv_yhalo_kernel<4, 1, HPE_ACT_SILU> : conv_yhalo_kernel<4, 1, HPE_ACT_NONE>);
+  } else if (taps_y == 3 && boxes == 3) {
+    smem = halo_smem_bytes<3, 3>();
+    fn = act == HPE_ACT_RELU ? conv_yhalo_kernel<3, 3, HPE_ACT_RELU> : (act == HPE_ACT_SILU ? conv_yhalo_kernel<3, 3, HPE_ACT_SILU> : conv_yhalo_kernel<3, 3, HPE_ACT_NONE>);
+  } else {
+    return fail(HPE_EUNSUPPORTED, "halo_launch: no kernel for %d x %d taps", taps_y, boxes);
+  }
+  cudaError_t e = cudaFuncSetAttribute((const void*)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return fail(HPE_ECUDA, "cudaFuncSetAttribute(halo smem=%zu) failed: %s", smem, cudaGetErrorString(e));
+  HaloParams pp = p;
+  void* args[4] = {(void*)tmA, (void*)tmW, (void*)tmOut, &pp};
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kHThreads); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  e = cudaLaunchKernelExC(&cfg, (const void*)fn, args);
+  if (e != cudaSuccess) return fail(HPE_ECUDA, "launch of conv_yhalo_kernel failed: %s", cudaGetErrorString(e));
+  return launch_status("conv_yhalo_kernel");
+}
+
+}  // namespace hpe
