@@ -712,6 +712,15 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
     pl->hp.tiles_x = (pl->Wo + 7) / 8; pl->hp.tiles_y = (pl->Ho + 15) / 16;
     pl->hp.num_tiles = pl->hp.tiles_x * pl->hp.tiles_y * d->B;
     pl->hp.x_lo = stem ? 0 : 1; pl->hp.y_lo = stem ? 2 : 1;
+    pl->hp.base_off_mode = 0;
+    if (!stem) {
+      // Default: ONE 10-pixel-wide halo'd box per tile (23 KB); the column taps are 128-byte shifts of the descriptor start.
+      // Measured on B200: SWIZZLE_128B is a function of the absolute shared-memory address, so such starts need base offset 0
+      // (setting the descriptor's base-offset field to (start >> 7) & 7 instead FAILS parity).  HPE_B200_HALO_WIDE=0 selects
+      // three 8-wide boxes, whose starts are all 1024-byte aligned.
+      const char* wv = getenv("HPE_B200_HALO_WIDE");
+      if (!(wv && wv[0] == '0')) pl->halo_boxes = 0;
+    }
     pl->grid = pl->hp.num_tiles < num_sms() ? pl->hp.num_tiles : num_sms();
     p.tw = 8; p.th = 16; p.nb = 1;               // brick of the output / A maps encoded below
   }
@@ -739,7 +748,8 @@ static int encode_plan_maps(hpe_conv_plan* pl, const void* x, const void* w, con
       const uint64_t dims[4] = {C, (uint64_t)d.W, (uint64_t)d.H, (uint64_t)d.B};
       const uint64_t str[3] = {P * 2, (uint64_t)d.W * P * 2, (uint64_t)d.H * d.W * P * 2};
       const uint32_t s = (uint32_t)p.in_stride;
-      const uint32_t box[4] = {64, (uint32_t)p.tw * s, (uint32_t)(pl->halo_taps_y ? 16 + pl->halo_taps_y - 1 : p.th * s), (uint32_t)p.nb};
+      const uint32_t box[4] = {64, (uint32_t)(pl->halo_taps_y && !pl->halo_boxes ? 10 : p.tw * s),
+                               (uint32_t)(pl->halo_taps_y ? 16 + pl->halo_taps_y - 1 : p.th * s), (uint32_t)p.nb};
       const uint32_t es[4] = {1, s, s, 1};
       rc = encode_map(&pl->tmA, x, 4, dims, str, box, es, "A");
     }

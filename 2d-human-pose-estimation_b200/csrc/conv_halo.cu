@@ -20,7 +20,6 @@ using namespace ptx;
 
 constexpr int kHThreads = 352, kHEpiThreads = 256, kHEpiWarp0 = 3;
 constexpr int kHN = 64;                       // Cout = BLOCK_N
-constexpr int kHStages = 2;                   // halo'd A tiles in flight
 constexpr int kHNumSB = 2;                    // epilogue staging buffers (16 KB each)
 constexpr int kHSBBytes = 128 * 64 * 2;
 
@@ -33,14 +32,23 @@ __device__ __forceinline__ void h_sts_v4(uint32_t addr, const uint4& v) {
   asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
+// K-major SWIZZLE_128B descriptor from a shared-memory byte address with an explicit 8-row-group stride.  Measured on B200:
+// the 128-byte swizzle is a function of the ABSOLUTE shared-memory address bits, so a TMA-written tile can be read through
+// any 128-byte-aligned start (row shift) with base offset 0 -- this is what makes the column taps of the wide box work.
+__device__ __forceinline__ uint64_t desc_sw128(uint32_t saddr, uint32_t sbo_bytes) {
+  return static_cast<uint64_t>((saddr & 0x3FFFFu) >> 4) | (static_cast<uint64_t>(1) << 16) |
+         (static_cast<uint64_t>(sbo_bytes >> 4) << 32) | (static_cast<uint64_t>(1) << 46) | (static_cast<uint64_t>(2) << 61);
+}
+
 // TAPS_Y row taps per box, BOXES column taps (one halo'd box each)
-template <int TAPS_Y, int BOXES, int ACT>
+template <int TAPS_Y, int BOXES, int ACT, int kHStages, int TX = 1>
 __global__ void __launch_bounds__(kHThreads, 1)
 conv_yhalo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                   const __grid_constant__ CUtensorMap tmOut, const HaloParams p) {
-  constexpr int kTaps = TAPS_Y * BOXES;
-  constexpr int kBoxRows = (16 + TAPS_Y - 1) * 8;                  // smem rows (128 B each) of one halo'd box
-  constexpr int kBoxBytes = kBoxRows * 128;                        // multiple of 1024
+  constexpr int kTaps = TAPS_Y * BOXES * TX;
+  constexpr int kBW = 8 + TX - 1;                                  // box width in pixels (TX column taps inside one box)
+  constexpr int kBoxRows = (16 + TAPS_Y - 1) * kBW;                // smem rows (128 B each) of one halo'd box
+  constexpr int kBoxBytes = (kBoxRows * 128 + 1023) / 1024 * 1024;
   constexpr int kABytes = BOXES * kBoxBytes;
   constexpr int kWBytes = kTaps * kHN * 128;                       // [tap][64 rows][64 k] bf16
   constexpr int kOffW = kHStages * kABytes;
@@ -66,7 +74,7 @@ conv_yhalo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA); prefetch_tmap(&tmW); prefetch_tmap(&tmOut);
     for (int s = 0; s < kHStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], kHEpiThreads / 32); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], 4); }
     mbar_init(wfull_bar, 1);
     fence_mbar_init();
   }
@@ -75,7 +83,7 @@ conv_yhalo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);      // warp-uniform for the compiler
   griddep_launch_dependents();
   griddep_wait();
 
@@ -89,74 +97,89 @@ conv_yhalo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
         const int x0 = (tile % p.tiles_x) * 8, y0 = ((tile / p.tiles_x) % p.tiles_y) * 16, b = tile / (p.tiles_x * p.tiles_y);
         mbar_wait(&empty_bar[stage], phase ^ 1);
-        mbar_arrive_expect_tx(&full_bar[stage], kABytes);
+        mbar_arrive_expect_tx(&full_bar[stage], BOXES * kBoxRows * 128);      // bytes the boxes deliver (a stage may be padded to 1 KB)
 #pragma unroll
         for (int bx = 0; bx < BOXES; ++bx)
           tma_load_4d(sA + stage * kABytes + bx * kBoxBytes, &tmA, &full_bar[stage], 0, x0 + bx - p.x_lo, y0 - p.y_lo, b);
         if (++stage == kHStages) { stage = 0; phase ^= 1; }
       }
     }
-  } else if (warp == 1) {
-    if (lane == 0) {
-      mbar_wait(wfull_bar, 0);
-      int stage = 0; uint32_t phase = 0; int it = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
-        const int acc = it & 1;
-        mbar_wait(&tempty_bar[acc], ((it >> 1) & 1) ^ 1);
-        mbar_wait(&full_bar[stage], phase);
-        tc_fence_after();
-        const uint32_t tmem_d = tmem_base + acc * kHN;
+  } else if (warp == 1 || warp == 2) {
+    // TWO issuing warps: warp 1 takes the even tiles (accumulator 0), warp 2 the odd ones (accumulator 1), so the issue paths
+    // of consecutive tiles overlap; the tensor pipe serialises the execution.
+    // The whole warp walks the tile loop (uniform control flow keeps the stage / descriptor arithmetic in uniform registers);
+    // only lane 0 issues the tcgen05 instructions.  With N = 64 an MMA occupies the tensor pipe for just 32 cycles, so the
+    // issue path must stay that short.
+    mbar_wait(wfull_bar, 0);
+    int stage = 0; uint32_t phase = 0; int it = 0;
+    const uint32_t sA0 = smem_u32(sA), sW0 = smem_u32(sW);
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      const int acc = it & 1;
+      if (acc != warp - 1) { if (++stage == kHStages) { stage = 0; phase ^= 1; } continue; }
+      mbar_wait(&tempty_bar[acc], ((it >> 1) & 1) ^ 1);
+      mbar_wait(&full_bar[stage], phase);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + acc * kHN;
+      const uint32_t a_stage = sA0 + stage * kABytes;
 #pragma unroll
-        for (int bx = 0; bx < BOXES; ++bx)
+      for (int bx = 0; bx < BOXES; ++bx)
 #pragma unroll
-          for (int ty = 0; ty < TAPS_Y; ++ty) {
-            const int tap = ty * BOXES + bx;                        // packed weight order: tap = ky * kw + kx
-            const uint64_t adesc = make_sw128_kmajor_desc(sA + stage * kABytes + bx * kBoxBytes + ty * 1024);
-            const uint64_t bdesc = make_sw128_kmajor_desc(sW + tap * kHN * 128);
+        for (int ty = 0; ty < TAPS_Y; ++ty)
 #pragma unroll
-            for (int k = 0; k < 4; ++k) umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, kIdesc, (bx | ty | k) != 0);
+          for (int tx = 0; tx < TX; ++tx) {
+            const int tap = ty * (BOXES * TX) + bx * TX + tx;       // packed weight order: tap = ky * kw + kx
+            // low descriptor word = (address >> 4) | LBO field; high word = SBO | version | SWIZZLE_128B (constants)
+            const uint32_t a_lo = (((a_stage + bx * kBoxBytes + (ty * kBW + tx) * 128) & 0x3FFFFu) >> 4) | (1u << 16);
+            const uint32_t b_lo = (((sW0 + tap * kHN * 128) & 0x3FFFFu) >> 4) | (1u << 16);
+            constexpr uint32_t a_hi = ((kBW * 128) >> 4) | (1u << 14) | (2u << 29);
+            constexpr uint32_t b_hi = (1024 >> 4) | (1u << 14) | (2u << 29);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              umma_bf16_elect_lo(tmem_d, a_lo + 2 * k, a_hi, b_lo + 2 * k, b_hi, kIdesc, (bx | ty | tx | k) != 0);
           }
-        umma_commit(&empty_bar[stage]);
-        umma_commit(&tfull_bar[acc]);
-        if (++stage == kHStages) { stage = 0; phase ^= 1; }
-      }
+      umma_commit_elect(&empty_bar[stage]); umma_commit_elect(&tfull_bar[acc]);
+      __syncwarp();
+      if (++stage == kHStages) { stage = 0; phase ^= 1; }
     }
   } else if (warp >= kHEpiWarp0) {
-    const int ew = warp & 3, half = (warp - kHEpiWarp0) >> 2;
+    // Two independent epilogue groups of 4 warps: group g drains accumulator g (tiles with it % 2 == g) through its own
+    // staging buffer, so the tcgen05.ld -> math -> fence -> TMA-store chains of consecutive tiles overlap.
+    const int ew = warp & 3, grp = (warp - kHEpiWarp0) >> 2;
     const int row = ew * 32 + lane;
-    const bool leader = threadIdx.x == kHEpiWarp0 * 32;
+    const bool leader = (warp - kHEpiWarp0) % 4 == 0 && lane == 0;
+    const uint32_t rowp = smem_u32(sSB + grp * kHSBBytes) + row * 128;
+    const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + grp * kHN;
     int it = 0;
     for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      if ((it & 1) != grp) continue;
       const int x0 = (tile % p.tiles_x) * 8, y0 = ((tile / p.tiles_x) % p.tiles_y) * 16, b = tile / (p.tiles_x * p.tiles_y);
-      const int acc = it & 1, sb = it % kHNumSB;
-      mbar_wait(&tfull_bar[acc], (it >> 1) & 1);
+      mbar_wait(&tfull_bar[grp], (it >> 1) & 1);
       tc_fence_after();
-      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * kHN + half * 32;
-      if (leader) bulk_wait_read<kHNumSB - 1>();                  // the store that last used this staging buffer has left smem
-      uint32_t v[32];
+      uint32_t v[64];
       tmem_ld_x32(taddr, v);
+      tmem_ld_x32(taddr + 32, v + 32);
       tmem_ld_wait();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
-      named_bar_sync(2, kHEpiThreads);                             // leader's wait is visible before anyone writes the buffer
-      const uint32_t rowp = smem_u32(sSB + sb * kHSBBytes) + row * 128;
+      if (lane == 0) mbar_arrive(&tempty_bar[grp]);                // accumulator drained: hand it back before anything else
+      if (leader) bulk_wait_read<0>();                             // this group's previous store has left its staging buffer
+      named_bar_sync(1 + grp, 128);                                // leader's wait is visible before anyone writes the buffer
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
+      for (int j = 0; j < 8; ++j) {
         float o[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
-          const int n = half * 32 + j * 8 + e;
-          o[e] = fmaf(__uint_as_float(v[j * 8 + e]), sScale[n], sShift[n]);
+          const int n = j * 8 + e;
+          o[e] = fmaf(__uint_as_float(v[n]), sScale[n], sShift[n]);
           if (ACT == HPE_ACT_RELU) o[e] = fmaxf(o[e], 0.f);
           if (ACT == HPE_ACT_SILU) o[e] = o[e] / (1.f + __expf(-o[e]));
         }
         const uint4 pk = make_uint4(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]), pack_bf16(o[6], o[7]));
-        h_sts_v4(rowp + (((half * 4 + j) ^ (row & 7)) << 4), pk);
+        h_sts_v4(rowp + ((j ^ (row & 7)) << 4), pk);
       }
       fence_proxy_async_smem();
-      named_bar_sync(1, kHEpiThreads);
-      if (leader) { tma_store_4d(&tmOut, sSB + sb * kHSBBytes, 0, x0, y0, b); bulk_commit(); }
+      named_bar_sync(3 + grp, 128);
+      if (leader) { tma_store_4d(&tmOut, sSB + grp * kHSBBytes, 0, x0, y0, b); bulk_commit(); }
     }
     if (leader) bulk_wait_all();
   }
@@ -165,10 +188,10 @@ conv_yhalo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, kTmemCols); }
 }
 
-template <int TAPS_Y, int BOXES>
+template <int TAPS_Y, int BOXES, int kHStages, int TX = 1>
 static size_t halo_smem_bytes() {
-  return (size_t)kHStages * BOXES * (16 + TAPS_Y - 1) * 8 * 128 + (size_t)TAPS_Y * BOXES * kHN * 128 + kHNumSB * kHSBBytes + 2 * kHN * 4 +
-         16 * 8 + 16 + 1024;
+  return (size_t)kHStages * BOXES * (((16 + TAPS_Y - 1) * (8 + TX - 1) * 128 + 1023) / 1024 * 1024) + (size_t)TAPS_Y * BOXES * TX * kHN * 128 + kHNumSB * kHSBBytes + 2 * kHN * 4 +
+         (2 * kHStages + 5) * 8 + 16 + 1024;
 }
 
 typedef void (*HaloFn)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const HaloParams);
@@ -177,11 +200,14 @@ int halo_launch(int taps_y, int boxes, int act, const CUtensorMap* tmA, const CU
                 const HaloParams& p, int grid, cudaStream_t stream) {
   HaloFn fn = nullptr; size_t smem = 0;
   if (taps_y == 4 && boxes == 1) {
-    smem = halo_smem_bytes<4, 1>();
-    fn = act == HPE_ACT_RELU ? conv_yhalo_kernel<4, 1, HPE_ACT_RELU> : (act == HPE_ACT_SILU ? conv_yhalo_kernel<4, 1, HPE_ACT_SILU> : conv_yhalo_kernel<4, 1, HPE_ACT_NONE>);
+    smem = halo_smem_bytes<4, 1, 6>();            // 19 KB per tile: 6 tiles in flight hide the HBM latency of the image read
+    fn = act == HPE_ACT_RELU ? conv_yhalo_kernel<4, 1, HPE_ACT_RELU, 6> : (act == HPE_ACT_SILU ? conv_yhalo_kernel<4, 1, HPE_ACT_SILU, 6> : conv_yhalo_kernel<4, 1, HPE_ACT_NONE, 6>);
   } else if (taps_y == 3 && boxes == 3) {
-    smem = halo_smem_bytes<3, 3>();
-    fn = act == HPE_ACT_RELU ? conv_yhalo_kernel<3, 3, HPE_ACT_RELU> : (act == HPE_ACT_SILU ? conv_yhalo_kernel<3, 3, HPE_ACT_SILU> : conv_yhalo_kernel<3, 3, HPE_ACT_NONE>);
+    smem = halo_smem_bytes<3, 3, 2>();            // 54 KB per tile + 72 KB of resident weights
+    fn = act == HPE_ACT_RELU ? conv_yhalo_kernel<3, 3, HPE_ACT_RELU, 2> : (act == HPE_ACT_SILU ? conv_yhalo_kernel<3, 3, HPE_ACT_SILU, 2> : conv_yhalo_kernel<3, 3, HPE_ACT_NONE, 2>);
+  } else if (taps_y == 3 && boxes == 0) {          // wide box: 23 KB per tile, 4 tiles in flight
+    smem = halo_smem_bytes<3, 1, 4, 3>();
+    fn = act == HPE_ACT_RELU ? conv_yhalo_kernel<3, 1, HPE_ACT_RELU, 4, 3> : (act == HPE_ACT_SILU ? conv_yhalo_kernel<3, 1, HPE_ACT_SILU, 4, 3> : conv_yhalo_kernel<3, 1, HPE_ACT_NONE, 4, 3>);
   } else {
     return fail(HPE_EUNSUPPORTED, "halo_launch: no kernel for %d x %d taps", taps_y, boxes);
   }

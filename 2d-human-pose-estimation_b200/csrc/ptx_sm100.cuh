@@ -100,6 +100,37 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint6
       "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
       ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
+// Same, executed by a whole CONVERGED warp: one elected lane issues the MMA.  Keeping the call site in uniform control flow
+// (and every operand warp-uniform) lets the compiler hold descriptors in uniform registers and issue UTCHMMA back to back;
+// with N = 64 an MMA occupies the tensor pipe for only 32 cycles, so the issue path must be that short.
+__device__ __forceinline__ void umma_bf16_elect(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, e;\n\t"
+      "elect.sync _|e, 0xffffffff;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "@e tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// Descriptors passed as 32-bit halves: the high words (SBO, version, swizzle mode) are compile-time constants and the low
+// words differ from a per-stage base by immediates, so the per-MMA address arithmetic is one 32-bit uniform add each.
+__device__ __forceinline__ void umma_bf16_elect_lo(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                                   uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, e;\n\t.reg .b64 da, db;\n\t"
+      "mov.b64 da, {%1, %2};\n\t"
+      "mov.b64 db, {%3, %4};\n\t"
+      "elect.sync _|e, 0xffffffff;\n\t"
+      "setp.ne.b32 p, %6, 0;\n\t"
+      "@e tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}"
+      ::"r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit_elect(uint64_t* bar) {
+  asm volatile(
+      "{\n\t.reg .pred e;\n\t"
+      "elect.sync _|e, 0xffffffff;\n\t"
+      "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}"
+      ::"r"(smem_u32(bar)) : "memory");
+}
 // arrive on an mbarrier once every tcgen05 op previously issued by this thread has completed
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
@@ -129,6 +160,18 @@ __device__ __forceinline__ uint64_t make_sw128_kmajor_desc(const void* smem) {
   d |= static_cast<uint64_t>(1024 >> 4) << 32;          // SBO
   d |= static_cast<uint64_t>(1) << 46;                  // descriptor version (Blackwell)
   d |= static_cast<uint64_t>(2) << 61;                  // SWIZZLE_128B
+  return d;
+}
+// Same, with an explicit stride between 8-row groups (SBO) and the 3-bit matrix base offset (bits 49-51) for start addresses
+// that are 128-byte but not 1024-byte aligned.
+__device__ __forceinline__ uint64_t make_sw128_kmajor_desc_ex(const void* smem, uint32_t sbo_bytes, uint32_t base_offset) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_u32(smem) & 0x3FFFFu) >> 4);
+  d |= static_cast<uint64_t>(1) << 16;
+  d |= static_cast<uint64_t>(sbo_bytes >> 4) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(base_offset & 7u) << 49;
+  d |= static_cast<uint64_t>(2) << 61;
   return d;
 }
 // kind::f16 instruction descriptor: D=f32, A=B=bf16, both K-major, M=128 (cute::UMMA::InstrDescriptor)
