@@ -44,6 +44,7 @@ SIGNATURES = {
     "hpe_conv_out_hw": (_i, [C.POINTER(ConvDesc), C.POINTER(_i), C.POINTER(_i)]),
     "hpe_preprocess_out_elems": (_sz, [_i, _i, _i]),
     "hpe_preprocess": (_i, [_vp, _i, _i, _i, _vp, _vp]),
+    "hpe_preprocess_u8": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "hpe_maxpool3x3s2": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "hpe_conv_dgrad_desc": (_i, [C.POINTER(ConvDesc), C.POINTER(ConvDesc)]),
     "hpe_conv_pack_weight_dgrad": (_i, [C.POINTER(ConvDesc), _vp, _vp, _vp]),
@@ -63,6 +64,7 @@ SIGNATURES = {
     "hpe_dwconv7_bias": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _i, _vp]),
     "hpe_layernorm_nhwc": (_i, [_vp, _i, C.c_longlong, _i, _vp, _vp, _f, _vp, _i, _vp]),
     "hpe_patchify4": (_i, [_vp, _i, _i, _i, _vp, _vp]),
+    "hpe_patchify4_u8": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "hpe_maxpool5": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _i, _vp]),
     "hpe_upsample_bilinear": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _vp, _i, _vp]),
     "hpe_pose_decode": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp]),

@@ -93,18 +93,20 @@ class ConvLayer:
 
 
 def preprocess(img: torch.Tensor, out: torch.Tensor = None):
-    """fp32 NCHW [B,3,H,W] -> the bf16 space-to-depth staging tensor the stem conv reads."""
+    """fp32 (or uint8, = ``img.float() / 255``: HPE/train.py:117-120) NCHW [B,3,H,W] -> the bf16 space-to-depth staging
+    tensor the stem conv reads."""
     _lib.require_cuda(img)
     B, Cc, H, W = img.shape
-    if Cc != 3 or img.dtype != torch.float32:
-        raise ValueError("preprocess expects float32 [B,3,H,W]")
+    if Cc != 3 or img.dtype not in (torch.float32, torch.uint8):
+        raise ValueError("preprocess expects float32 or uint8 [B,3,H,W]")
     n = _lib.lib().hpe_preprocess_out_elems(B, H, W)
     if n == 0:
         raise ValueError("H and W must be even")
     if out is None:
         out = torch.empty(n, dtype=torch.bfloat16, device=img.device)
+    fn = _lib.lib().hpe_preprocess_u8 if img.dtype == torch.uint8 else _lib.lib().hpe_preprocess
     with torch.cuda.device(img.device):
-        _lib.check(_lib.lib().hpe_preprocess(_lib.ptr(img), B, H, W, _lib.ptr(out), _lib.stream_ptr()), "hpe_preprocess")
+        _lib.check(fn(_lib.ptr(img), B, H, W, _lib.ptr(out), _lib.stream_ptr()), "hpe_preprocess")
     return out
 
 

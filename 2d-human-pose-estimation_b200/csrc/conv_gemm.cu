@@ -341,8 +341,16 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 // 2 zero columns of left padding and 2 of right padding (the stem's x padding is physical, its y padding
 // is TMA out-of-bounds fill).
 constexpr int kS2DPad = 4;
+// two horizontally adjacent pixels of one channel row; uint8 input = the reference's `imgs.float() / 255.0`
+// (/root/reference/HPE/train.py:117-120, HPE/test.py:16-29) fused into the layout change
+__device__ __forceinline__ float2 load_px2(const float* p) { return __ldg(reinterpret_cast<const float2*>(p)); }
+__device__ __forceinline__ float2 load_px2(const unsigned char* p) {
+  const uchar2 u = __ldg(reinterpret_cast<const uchar2*>(p));
+  return make_float2(__fdiv_rn(static_cast<float>(u.x), 255.f), __fdiv_rn(static_cast<float>(u.y), 255.f));
+}
+template <typename T>
 __global__ void __launch_bounds__(256)
-preprocess_kernel(const float* __restrict__ img, int B, int H, int W, __nv_bfloat16* __restrict__ out) {
+preprocess_kernel(const T* __restrict__ img, int B, int H, int W, __nv_bfloat16* __restrict__ out) {
   const int Hs = H / 2, Ws = W / 2, Wp = Ws + kS2DPad;
   const long long total = static_cast<long long>(B) * Hs * Wp;
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -358,8 +366,7 @@ preprocess_kernel(const float* __restrict__ img, int B, int H, int W, __nv_bfloa
       for (int c = 0; c < 3; ++c)
 #pragma unroll
         for (int py = 0; py < 2; ++py) {
-          const float2 f = __ldg(reinterpret_cast<const float2*>(
-              img + ((static_cast<size_t>(b) * 3 + c) * H + (2 * ys + py)) * W + 2 * xs));
+          const float2 f = load_px2(img + ((static_cast<size_t>(b) * 3 + c) * H + (2 * ys + py)) * W + 2 * xs);
           v[py][0][c] = f.x; v[py][1][c] = f.y;
         }
       lo = make_uint4(pack_bf16(v[0][0][0], v[0][0][1]), pack_bf16(v[0][0][2], 0.f),
@@ -848,8 +855,18 @@ extern "C" int hpe_preprocess(const float* img, int B, int H, int W, void* out, 
   HPE_CHECK_ARG((((uintptr_t)img & 7) | ((uintptr_t)out & 15)) == 0, "hpe_preprocess: misaligned pointer");
   const long long total = (long long)B * (H / 2) * (W / 2 + kS2DPad);
   const int grid = (int)((total + 255) / 256 > (long long)num_sms() * 16 ? (long long)num_sms() * 16 : (total + 255) / 256);
-  preprocess_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(img, B, H, W, (__nv_bfloat16*)out);
+  preprocess_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(img, B, H, W, (__nv_bfloat16*)out);
   return launch_status("preprocess_kernel");
+}
+
+extern "C" int hpe_preprocess_u8(const unsigned char* img, int B, int H, int W, void* out, void* stream) {
+  HPE_CHECK_ARG(img && out, "hpe_preprocess_u8: null pointer");
+  HPE_CHECK_ARG(B > 0 && H > 0 && W > 0 && H % 2 == 0 && W % 2 == 0, "hpe_preprocess_u8: H and W must be positive and even");
+  HPE_CHECK_ARG((((uintptr_t)img & 1) | ((uintptr_t)out & 15)) == 0, "hpe_preprocess_u8: misaligned pointer");
+  const long long total = (long long)B * (H / 2) * (W / 2 + kS2DPad);
+  const int grid = (int)((total + 255) / 256 > (long long)num_sms() * 16 ? (long long)num_sms() * 16 : (total + 255) / 256);
+  preprocess_kernel<unsigned char><<<grid, 256, 0, (cudaStream_t)stream>>>(img, B, H, W, (__nv_bfloat16*)out);
+  return launch_status("preprocess_kernel<u8>");
 }
 
 extern "C" int hpe_maxpool3x3s2(const void* x, int B, int H, int W, int C, void* y, void* stream) {

@@ -304,9 +304,17 @@ layernorm_nhwc_kernel(const __nv_bfloat16* __restrict__ x, int in_pitch, const f
   }
 }
 
-// one thread per (output pixel, 8-element group of the 64-wide row); k = c*16 + ky*4 + kx  (Conv2d weight.reshape(Cout, 48))
+// one thread per (output pixel, 8-element group of the 64-wide row); k = c*16 + ky*4 + kx  (Conv2d weight.reshape(Cout, 48)).
+// uint8 input = the reference's `imgs.float() / 255.0` (HPE/train.py:117-120) fused in.
+__device__ __forceinline__ float4 load_px4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+__device__ __forceinline__ float4 load_px4(const unsigned char* p) {
+  const uchar4 u = __ldg(reinterpret_cast<const uchar4*>(p));
+  return make_float4(__fdiv_rn(static_cast<float>(u.x), 255.f), __fdiv_rn(static_cast<float>(u.y), 255.f),
+                     __fdiv_rn(static_cast<float>(u.z), 255.f), __fdiv_rn(static_cast<float>(u.w), 255.f));
+}
+template <typename T>
 __global__ void __launch_bounds__(256)
-patchify4_kernel(const float* __restrict__ img, int B, int H, int W, __nv_bfloat16* __restrict__ out) {
+patchify4_kernel(const T* __restrict__ img, int B, int H, int W, __nv_bfloat16* __restrict__ out) {
   const int Ho = H / 4, Wo = W / 4;
   const long long total = static_cast<long long>(B) * Ho * Wo * 8;
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
@@ -319,7 +327,7 @@ patchify4_kernel(const float* __restrict__ img, int B, int H, int W, __nv_bfloat
       const int c = g >> 1, ky0 = (g & 1) * 2;
 #pragma unroll
       for (int j = 0; j < 2; ++j) {
-        const float4 v = __ldg(reinterpret_cast<const float4*>(img + ((static_cast<size_t>(b) * 3 + c) * H + (4 * oy + ky0 + j)) * W + 4 * ox));
+        const float4 v = load_px4(img + ((static_cast<size_t>(b) * 3 + c) * H + (4 * oy + ky0 + j)) * W + 4 * ox);
         o[4 * j] = v.x; o[4 * j + 1] = v.y; o[4 * j + 2] = v.z; o[4 * j + 3] = v.w;
       }
     }
@@ -468,8 +476,16 @@ extern "C" int hpe_patchify4(const float* img, int B, int H, int W, void* out, v
   HPE_CHECK_ARG(img && out, "hpe_patchify4: null pointer");
   HPE_CHECK_ARG(B > 0 && H > 0 && W > 0 && H % 4 == 0 && W % 4 == 0, "hpe_patchify4: H and W must be multiples of 4");
   HPE_CHECK_ARG((((uintptr_t)img | (uintptr_t)out) & 15) == 0, "hpe_patchify4: misaligned pointer");
-  patchify4_kernel<<<ew_grid((long long)B * (H / 4) * (W / 4) * 8), 256, 0, (cudaStream_t)stream>>>(img, B, H, W, (__nv_bfloat16*)out);
+  patchify4_kernel<float><<<ew_grid((long long)B * (H / 4) * (W / 4) * 8), 256, 0, (cudaStream_t)stream>>>(img, B, H, W, (__nv_bfloat16*)out);
   return launch_status("patchify4_kernel");
+}
+
+extern "C" int hpe_patchify4_u8(const unsigned char* img, int B, int H, int W, void* out, void* stream) {
+  HPE_CHECK_ARG(img && out, "hpe_patchify4_u8: null pointer");
+  HPE_CHECK_ARG(B > 0 && H > 0 && W > 0 && H % 4 == 0 && W % 4 == 0, "hpe_patchify4_u8: H and W must be multiples of 4");
+  HPE_CHECK_ARG((((uintptr_t)img & 3) | ((uintptr_t)out & 15)) == 0, "hpe_patchify4_u8: misaligned pointer");
+  patchify4_kernel<unsigned char><<<ew_grid((long long)B * (H / 4) * (W / 4) * 8), 256, 0, (cudaStream_t)stream>>>(img, B, H, W, (__nv_bfloat16*)out);
+  return launch_status("patchify4_kernel<u8>");
 }
 
 extern "C" int hpe_maxpool5(const void* x, int in_pitch, int B, int H, int W, int C, void* y, int out_pitch, void* stream) {

@@ -147,7 +147,7 @@ class HeatmapPose(nn.Module):
             self._plans[key] = plan
         if plan.weights_version != self._weights_version:
             plan.load_weights(self)
-        return plan.run(x.float().contiguous())
+        return plan.run(x.contiguous() if x.dtype == torch.uint8 else x.float().contiguous())   # uint8 = x.float()/255 fused in
 
     def _train_plan(self, x):
         from .train import TrainPlan

@@ -81,13 +81,13 @@ class PoseEstimator:
         return get_final_preds_affine(hm, affine)
 
     # ---- host-buffer paths ---------------------------------------------------------------------------
-    def _buffers(self, shape, slot):
-        key = (tuple(shape), slot)
+    def _buffers(self, shape, slot, dtype=torch.float32):
+        key = (tuple(shape), slot, dtype)
         b = self._stage.get(key)
         if b is None:
             B = shape[0]
             K = self.model.njoints
-            b = {"img": torch.empty(shape, dtype=torch.float32, device=self.device),
+            b = {"img": torch.empty(shape, dtype=dtype, device=self.device),      # uint8 images: 4x less H2D, /255 fused in the stem
                  "aff": torch.empty((B, 2, 3), dtype=torch.float32, device=self.device),
                  "preds": torch.empty((B, K, 2), dtype=torch.float32).pin_memory(),
                  "maxvals": torch.empty((B, K, 1), dtype=torch.float32).pin_memory(),
@@ -97,7 +97,7 @@ class PoseEstimator:
 
     def infer_host(self, images: torch.Tensor, affine: torch.Tensor):
         """One batch, fully synchronous: returns pinned host ``preds, maxvals``."""
-        b = self._buffers(images.shape, 0)
+        b = self._buffers(images.shape, 0, images.dtype)
         b["img"].copy_(images, non_blocking=True)
         b["aff"].copy_(affine, non_blocking=True)
         preds, maxvals = self(b["img"], affine=b["aff"])
@@ -117,7 +117,7 @@ class PoseEstimator:
 
         def upload(item, slot):
             images, affine = item
-            b = self._buffers(images.shape, slot)
+            b = self._buffers(images.shape, slot, images.dtype)
             cs.wait_event(b["done"])                 # previous use of this slot's device buffers has finished
             with torch.cuda.stream(cs):
                 b["img"].copy_(images, non_blocking=True)

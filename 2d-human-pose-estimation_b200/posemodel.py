@@ -177,7 +177,8 @@ def _upsample(x, y):
 def _patchify4(img, out):
     B, _, H, W = img.shape
     with torch.cuda.device(img.device):
-        rc = _lib.lib().hpe_patchify4(_lib.ptr(img), B, H, W, _lib.ptr(out), _lib.stream_ptr())
+        fn = _lib.lib().hpe_patchify4_u8 if img.dtype == torch.uint8 else _lib.lib().hpe_patchify4
+        rc = fn(_lib.ptr(img), B, H, W, _lib.ptr(out), _lib.stream_ptr())
     _lib.check(rc, "hpe_patchify4")
 
 
@@ -425,13 +426,13 @@ class DINOv3Pose(nn.Module):
     def forward_features(self, x):
         """PAN outputs as fp32 NCHW (pose.py:60-65)."""
         plan = self._plan(x)
-        plan.run(x.float().contiguous())
+        plan.run(x.contiguous() if x.dtype == torch.uint8 else x.float().contiguous())
         return [f.float().permute(0, 3, 1, 2) for f in plan.features]
 
     @torch.no_grad()
     def forward(self, x):
         plan = self._plan(x)
-        levels = plan.run(x.float().contiguous())
+        levels = plan.run(x.contiguous() if x.dtype == torch.uint8 else x.float().contiguous())   # uint8 = x.float()/255 (train.py:120)
         if self.training:
             return list(levels)                       # head.py:176-181 (forward only: no autograd graph is built)
         return pose_decode(levels, self.head.nc, self.head.kpt_shape, tuple(self.head.stride.tolist()))

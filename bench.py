@@ -269,6 +269,26 @@ def run_b200(args):
         sweep = {"B": SB, "ms": sweep_ms, "gbs": sweep_bytes / (sweep_ms * 1e-3) / 1e9}
         del big, big_aff
 
+    # ---- same e2e with uint8 host images (the reference's real input, HPE/train.py:117-120: `imgs.float() / 255.0` fused into the stem)
+    h_u8 = [(t * 255).to(torch.uint8).pin_memory() for t in h_img]
+
+    def host_batches_u8(n):
+        for i in range(n):
+            yield h_u8[i & 1], h_aff
+    for _ in est.stream(host_batches_u8(3)):
+        pass
+    barrier()
+    u_start, u_end = ev(), ev()
+    u_start.record()
+    for preds_h, maxvals_h in est.stream(host_batches_u8(args.steps)):
+        checksum += float(maxvals_h[0, 0, 0])
+    u_end.record()
+    barrier()
+    tu = torch.tensor([u_start.elapsed_time(u_end)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tu, op=dist.ReduceOp.MAX)
+    e2e_u8_ms = float(tu.item())
+
     if rank == 0:
         peaks = load_peaks()
         plan = next(iter(model._plans.values()))
@@ -301,7 +321,9 @@ def run_b200(args):
             "e2e": {"value": round(total_imgs / e2e_ms * 1e3, 1), "unit": "images/s",
                     "h2d_bytes_per_step": B * 3 * H * W * 4 + B * 24, "d2h_bytes_per_step": B * K * 3 * 4,
                     "ms_per_step": round(e2e_ms / args.steps, 4), "wall_ms_per_step": round(e2e_wall_ms / args.steps, 4),
-                    "api": "PoseEstimator.stream (pinned host fp32 images -> H2D overlapped on a side stream -> forward -> decode -> D2H)"},
+                    "api": "PoseEstimator.stream (pinned host fp32 images -> H2D overlapped on a side stream -> forward -> decode -> D2H)",
+                    "uint8_images": {"value": round(total_imgs / e2e_u8_ms * 1e3, 1), "h2d_bytes_per_step": B * 3 * H * W + B * 24,
+                                     "note": "same call with uint8 host images (/255 fused into the stem, HPE/train.py:117-120)"}},
             "gpu_launches": launches_per_step * args.steps,
             "gpu_launches_per_step": launches_per_step,
             "clocks": clocks,

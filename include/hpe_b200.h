@@ -155,6 +155,8 @@ int  hpe_conv_out_hw(const hpe_conv_desc* desc, int* Ho, int* Wo);
  * (replaces `data.float()` + cuDNN's layout transform, HPE/engine/trainer.py:88-90). */
 size_t hpe_preprocess_out_elems(int B, int H, int W);
 int  hpe_preprocess(const float* img_nchw, int B, int H, int W, void* s2d_out, void* stream);
+/* same from a uint8 NCHW image: the reference's `imgs.float() / 255.0` (HPE/train.py:117-120, HPE/test.py:16-29) fused in */
+int  hpe_preprocess_u8(const unsigned char* img_nchw, int B, int H, int W, void* s2d_out, void* stream);
 /* MaxPool 3x3 s2 p1 on NHWC bf16 (timm resnet.py:574-576). */
 int  hpe_maxpool3x3s2(const void* x, int B, int H, int W, int C, void* y, void* stream);
 
@@ -284,6 +286,7 @@ int hpe_dwconv7_bias(const void* x, int in_pitch, int B, int H, int W, int C, co
 int hpe_layernorm_nhwc(const void* x, int in_pitch, long long M, int C, const float* gamma, const float* beta, float eps,
                        void* y, int out_pitch, void* stream);
 int hpe_patchify4(const float* img_nchw, int B, int H, int W, void* out, void* stream);
+int hpe_patchify4_u8(const unsigned char* img_nchw, int B, int H, int W, void* out, void* stream);   /* uint8 / 255 fused in */
 int hpe_maxpool5(const void* x, int in_pitch, int B, int H, int W, int C, void* y, int out_pitch, void* stream);
 int hpe_upsample_bilinear(const void* x, int in_pitch, int B, int Hi, int Wi, int C, int Ho, int Wo, void* y, int out_pitch,
                           void* stream);

@@ -113,3 +113,21 @@ def test_model_boundary(hpe, cuda_dev):
     m = models.build_model(cfg)
     with pytest.raises(RuntimeError, match="pretrained"):
         models.HeatmapPose(17, "resnet50", pretrained=True)
+
+
+def test_uint8_input_is_float_div_255(hpe, cuda_dev):
+    """uint8 images take the fused `imgs.float() / 255.0` path (HPE/train.py:117-120, HPE/test.py:16-29): identical heatmaps."""
+    torch.manual_seed(3)
+    m = hpe.HeatmapPose(17, "resnet50", pretrained=False)
+    for mod in m.modules():
+        if isinstance(mod, torch.nn.BatchNorm2d):
+            mod.weight.data.uniform_(0.5, 1.5); mod.running_var.uniform_(0.5, 1.5)
+    m = m.to(cuda_dev).eval()
+    u8 = torch.randint(0, 256, (3, 3, 128, 96), dtype=torch.uint8, device=cuda_dev)
+    a = m(u8).clone()
+    b = m(u8.float() / 255.0)
+    assert torch.equal(a, b)
+    p = hpe.DINOv3Pose("dinov3_convnext_tiny", nkpts=(17, 3), ncls=1, device=cuda_dev).eval()
+    u8 = torch.randint(0, 256, (2, 3, 64, 64), dtype=torch.uint8, device=cuda_dev)
+    a = p(u8).clone()
+    assert torch.equal(a, p(u8.float() / 255.0))
