@@ -26,10 +26,10 @@ def fold_bn(weight, bias, running_mean, running_var, eps):
 
 class ConvLayer:
     def __init__(self, kind, B, H, W, Cin, Cout, stride=1, act=ACT_RELU, has_residual=False, device="cuda", desc=None,
-                 in_cstride=0, out_cstride=0):
+                 in_cstride=0, out_cstride=0, Cin2=0, stride2=1):
         self.device = torch.device(device)
         self.desc = desc if desc is not None else ConvDesc(kind, B, H, W, Cin, Cout, stride, act, int(has_residual),
-                                                           in_cstride, out_cstride)
+                                                           in_cstride, out_cstride, Cin2, stride2 if Cin2 else 0)
         kind, B, Cout = self.desc.kind, self.desc.B, self.desc.Cout
         lib = _lib.lib()
         ho, wo = C.c_int(), C.c_int()
@@ -74,7 +74,23 @@ class ConvLayer:
             self.shift.copy_(shift.detach().to(self.device, torch.float32))
         return self
 
-    def __call__(self, x: torch.Tensor, residual: torch.Tensor = None, out: torch.Tensor = None):
+    def load2(self, weight: torch.Tensor, scale: torch.Tensor, shift: torch.Tensor, weight2: torch.Tensor, scale2: torch.Tensor,
+              shift2: torch.Tensor):
+        """Two-input layer (``Cin2``): ``y = act(bn(conv(x)) + bn2(conv2(x2)))`` -- conv3 + bn3 + the projection shortcut
+        ``downsample(x)`` + add + ReLU of timm ``Bottleneck.forward`` (resnet.py:247-268) as ONE GEMM over the concatenated
+        K.  The two accumulations share one TMEM tile, so both BN scales are folded into the weights (in fp32, before the
+        bf16 rounding) and the epilogue applies ``shift + shift2`` only."""
+        f32 = dict(device=self.device, dtype=torch.float32)
+        w = (weight.detach().to(**f32) * scale.detach().to(**f32).view(-1, 1, 1, 1)).contiguous()
+        w2 = (weight2.detach().to(**f32) * scale2.detach().to(**f32).view(-1, 1, 1, 1)).contiguous()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().hpe_conv_pack_weight2(C.byref(self.desc), _lib.ptr(w), _lib.ptr(w2), _lib.ptr(self.w_packed),
+                                                        _lib.stream_ptr()), "hpe_conv_pack_weight2")
+        self.scale.fill_(1.0)
+        self.shift.copy_(shift.detach().to(**f32) + shift2.detach().to(**f32))
+        return self
+
+    def __call__(self, x: torch.Tensor, residual: torch.Tensor = None, out: torch.Tensor = None, x2: torch.Tensor = None):
         if out is None:
             out = self.alloc_out()
         if self.desc.in_cstride or self.desc.out_cstride:
@@ -85,9 +101,10 @@ class ConvLayer:
                     raise RuntimeError("libhpe_b200: channel-slice tensor does not match the plan's channel pitch")
         else:
             _lib.require_cuda(x, residual, out)
+        _lib.require_cuda(x2)
         with torch.cuda.device(self.device):
-            rc = _lib.lib().hpe_conv_run(self.plan, _lib.ptr(x), _lib.ptr(self.w_packed), _lib.ptr(self.scale),
-                                         _lib.ptr(self.shift), _lib.ptr(residual), _lib.ptr(out), _lib.stream_ptr())
+            rc = _lib.lib().hpe_conv_run2(self.plan, _lib.ptr(x), _lib.ptr(x2), _lib.ptr(self.w_packed), _lib.ptr(self.scale),
+                                          _lib.ptr(self.shift), _lib.ptr(residual), _lib.ptr(out), _lib.stream_ptr())
         _lib.check(rc, "hpe_conv_run")
         return out
 

@@ -43,6 +43,7 @@ struct OutMaps { CUtensorMap m[4]; };
 
 struct ConvParams {
   int kind, taps, kc_per_tap, in_stride;
+  int kc2, in_stride2;          // second A source (fused projection shortcut): its k-blocks follow the first source's
   int tw, th, nb;
   int tiles_x, tiles_y, tiles_b, n_tiles_n, n_classes, num_tiles;
   int Ho, Wo, B, Cout;          // Ho,Wo = extent of the tile grid (deconv: input-resolution grid per class)
@@ -84,7 +85,7 @@ __device__ __forceinline__ void tap_offset(const ConvParams& p, int t, int cls, 
 // number of 64-wide k-blocks of a tile (depends on the parity class only for the stride-2 3x3 dgrad)
 __device__ __forceinline__ int kb_count(const ConvParams& p, int cls) {
   if (p.kind == HPE_CONV_DGRAD3x3S2) return (1 + (cls >> 1)) * (1 + (cls & 1)) * p.kc_per_tap;
-  return p.taps * p.kc_per_tap;
+  return p.taps * p.kc_per_tap + p.kc2;
 }
 
 template <int BLOCK_N, int STAGES>
@@ -123,9 +124,9 @@ __device__ __forceinline__ uint32_t relu_bf16x2(uint32_t v) {
 // ACT: HPE_ACT_*; RES: residual add; FINAL: fp32 NCHW heatmap epilogue (HPE_CONV_FINAL)
 template <int BLOCK_N, int STAGES, int ACT, bool RES, bool FINAL>
 __global__ void __launch_bounds__(kConvThreads, 1)
-conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
-                 const __grid_constant__ OutMaps tmOut, const __grid_constant__ CUtensorMap tmRes,
-                 const ConvParams p) {
+conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
+                 const __grid_constant__ CUtensorMap tmW, const __grid_constant__ OutMaps tmOut,
+                 const __grid_constant__ CUtensorMap tmRes, const ConvParams p) {
   using L = SmemLayout<BLOCK_N, STAGES>;
   constexpr int kChunks   = BLOCK_N >= 64 ? BLOCK_N / 64 : 1;
   constexpr int kTmemCols = 2 * BLOCK_N <= 32 ? 32 : (2 * BLOCK_N <= 64 ? 64 : (2 * BLOCK_N <= 128 ? 128 : (2 * BLOCK_N <= 256 ? 256 : 512)));  // power of two
@@ -151,6 +152,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int lane = threadIdx.x & 31;
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA); prefetch_tmap(&tmW);
+    if (p.kc2) prefetch_tmap(&tmA2);
     if (!FINAL) for (int c = 0; c < p.n_classes; ++c) prefetch_tmap(&tmOut.m[c]);
     if (RES) prefetch_tmap(&tmRes);
     for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
@@ -178,14 +180,19 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
         const TileCoord t = tile_coord(p, tile);
         const int wrow = t.cls * p.Cout + t.n_tile * BLOCK_N;
-        const int num_kb = kb_count(p, t.cls);
+        const int num_kb = kb_count(p, t.cls), num_kb1 = num_kb - p.kc2;
         for (int kb = 0; kb < num_kb; ++kb) {
-          const int tap = kb / p.kc_per_tap, kc = kb - tap * p.kc_per_tap;
-          int dx, dy; tap_offset(p, tap, t.cls, dx, dy);
           mbar_wait(&empty_bar[stage], phase ^ 1);
           mbar_arrive_expect_tx(&full_bar[stage], L::kStageBytes);
-          tma_load_4d(sA + stage * kABytes, &tmA, &full_bar[stage], kc * kKBlock,
-                      t.x0 * p.in_stride + dx, t.y0 * p.in_stride + dy, t.b0);
+          if (kb < num_kb1) {
+            const int tap = kb / p.kc_per_tap, kc = kb - tap * p.kc_per_tap;
+            int dx, dy; tap_offset(p, tap, t.cls, dx, dy);
+            tma_load_4d(sA + stage * kABytes, &tmA, &full_bar[stage], kc * kKBlock,
+                        t.x0 * p.in_stride + dx, t.y0 * p.in_stride + dy, t.b0);
+          } else {          // second source (1x1, own stride): the block input feeding the projection shortcut
+            tma_load_4d(sA + stage * kABytes, &tmA2, &full_bar[stage], (kb - num_kb1) * kKBlock,
+                        t.x0 * p.in_stride2, t.y0 * p.in_stride2, t.b0);
+          }
           tma_load_2d(sB + stage * L::kBBytes, &tmW, &full_bar[stage], kb * kKBlock, wrow);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -416,7 +423,7 @@ maxpool_kernel(const __nv_bfloat16* __restrict__ x, int B, int H, int W, int C, 
 // PyTorch-layout fp32 weight -> packed bf16 GEMM-B  [rows][Ktot]; every tap's Cin is zero-padded to Cp = kc*64
 __global__ void __launch_bounds__(256)
 pack_weight_kernel(const float* __restrict__ w, int kind, int Cin, int Cp, int Cout, long long total,
-                   __nv_bfloat16* __restrict__ out) {
+                   __nv_bfloat16* __restrict__ out, long long ldo = 0, int koff = 0) {
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
     float v = 0.f;
@@ -438,6 +445,7 @@ pack_weight_kernel(const float* __restrict__ w, int kind, int Cin, int Cp, int C
       const int K = taps * Cp, co = static_cast<int>(i / K), k = static_cast<int>(i % K);
       const int tap = k / Cp, ci = k % Cp;
       if (ci < Cin) v = w[(static_cast<size_t>(co) * Cin + ci) * taps + tap];
+      if (ldo) { out[static_cast<size_t>(co) * ldo + koff + k] = __float2bfloat16(v); continue; }   // K-slice of a wider row
     }
     out[i] = __float2bfloat16(v);
   }
@@ -455,8 +463,9 @@ struct hpe_conv_plan {
   size_t smem;
   CUtensorMap tmA, tmW, tmRes;
   OutMaps tmOut;
-  const void *x, *w, *res;
+  const void *x, *x2, *w, *res;
   void* y;
+  CUtensorMap tmA2;
   const void* fn;
   int halo_taps_y, halo_boxes;        // != 0: the layer runs on the y-halo variant (conv_halo.cu)
   HaloParams hp;
@@ -466,7 +475,7 @@ struct hpe_conv_plan {
 static bool halo_eligible(const hpe_conv_desc* d, int Ho, int Wo) {
   const char* e = getenv("HPE_B200_HALO");
   if (e && e[0] == '0') return false;
-  if (d->has_residual || d->in_cstride || d->out_cstride) return false;
+  if (d->has_residual || d->in_cstride || d->out_cstride || d->Cin2) return false;
   const bool shape_ok = d->Cout == 64 && (Wo + 7) / 8 * 8 * ((Ho + 15) / 16 * 16) <= (long long)Wo * Ho * 9 / 8;   // <= 12.5 % padded
   if (d->kind == HPE_CONV_STEM7x7) return shape_ok;
   if (d->kind == HPE_CONV_3x3) return shape_ok && d->Cin == 64 && d->stride == 1;
@@ -484,6 +493,11 @@ static int desc_check(const hpe_conv_desc* d, const char* fn) {
     return HPE_OK;
   }
   if (d->Cin % 8) return fail(HPE_EUNSUPPORTED, "%s: Cin=%d must be a multiple of 8", fn, d->Cin);
+  if (d->Cin2) {
+    if (d->kind != HPE_CONV_1x1 || d->stride != 1) return fail(HPE_EUNSUPPORTED, "%s: a second input needs a 1x1 stride-1 main conv", fn);
+    if (d->Cin2 < 0 || d->Cin2 % 8) return fail(HPE_EUNSUPPORTED, "%s: Cin2=%d must be a positive multiple of 8", fn, d->Cin2);
+    if (d->stride2 != 1 && d->stride2 != 2) return fail(HPE_EUNSUPPORTED, "%s: stride2 %d not in {1,2}", fn, d->stride2);
+  }
   if (d->in_cstride && (d->in_cstride % 8 || d->in_cstride < d->Cin))
     return fail(HPE_EINVAL, "%s: in_cstride=%d must be a multiple of 8 and >= Cin", fn, d->in_cstride);
   if (d->kind == HPE_CONV_FINAL) {
@@ -546,7 +560,7 @@ static size_t ktot(const hpe_conv_desc* d) {
     case HPE_CONV_STEM7x7: return 256;
     case HPE_CONV_DECONV4: case HPE_CONV_DGRAD3x3S2: case HPE_CONV_2x2S2: return 4 * cp;
     case HPE_CONV_4x4S2:   return 16 * cp;
-    default:               return cp;
+    default:               return cp + (size_t)(d->Cin2 + 63) / 64 * 64;
   }
 }
 static bool is_class_strided(int kind) { return kind == HPE_CONV_DECONV4 || kind == HPE_CONV_DGRAD3x3S2; }
@@ -561,6 +575,7 @@ extern "C" int hpe_conv_pack_weight(const hpe_conv_desc* d, const float* w_torch
   int rc = desc_check(d, "hpe_conv_pack_weight");
   if (rc) return rc;
   HPE_CHECK_ARG(w_torch && w_packed, "hpe_conv_pack_weight: null pointer");
+  if (d->Cin2) return fail(HPE_EINVAL, "hpe_conv_pack_weight: the layer has a second input; use hpe_conv_pack_weight2");
   if (d->kind > HPE_CONV_FINAL && d->kind != HPE_CONV_2x2S2) return fail(HPE_EINVAL, "hpe_conv_pack_weight: kind %d is a backward-data kind; use hpe_conv_pack_weight_dgrad", d->kind);
   const long long total = (long long)(wrows(d) * ktot(d));
   const int grid = (int)((total + 255) / 256 > 4096 ? 4096 : (total + 255) / 256);
@@ -569,6 +584,25 @@ extern "C" int hpe_conv_pack_weight(const hpe_conv_desc* d, const float* w_torch
   return launch_status("pack_weight_kernel");
 }
 
+extern "C" int hpe_conv_pack_weight2(const hpe_conv_desc* d, const float* w_torch, const float* w2_torch, void* w_packed,
+                                     void* stream) {
+  int rc = desc_check(d, "hpe_conv_pack_weight2");
+  if (rc) return rc;
+  HPE_CHECK_ARG(w_torch && w2_torch && w_packed, "hpe_conv_pack_weight2: null pointer");
+  if (!d->Cin2) return fail(HPE_EINVAL, "hpe_conv_pack_weight2: the layer has no second input");
+  const int cp1 = cin_padded(d), cp2 = (d->Cin2 + 63) / 64 * 64;
+  const long long ldo = (long long)ktot(d);
+  for (int src = 0; src < 2; ++src) {
+    const int cp = src ? cp2 : cp1;
+    const long long total = (long long)d->Cout * cp;
+    const int grid = (int)((total + 255) / 256 > 4096 ? 4096 : (total + 255) / 256);
+    pack_weight_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src ? w2_torch : w_torch, HPE_CONV_1x1, src ? d->Cin2 : d->Cin, cp,
+                                                              d->Cout, total, (__nv_bfloat16*)w_packed, ldo, src ? cp1 : 0);
+    rc = launch_status("pack_weight_kernel");
+    if (rc) return rc;
+  }
+  return HPE_OK;
+}
 
 namespace hpe {
 // PyTorch-layout fp32 FORWARD weight -> packed bf16 GEMM-B of the layer's backward-data convolution
@@ -617,6 +651,8 @@ extern "C" int hpe_conv_dgrad_desc(const hpe_conv_desc* f, hpe_conv_desc* g) {
   if (rc) return rc;
   *g = *f;
   g->H = Ho; g->W = Wo; g->Cin = f->Cout; g->Cout = f->Cin; g->stride = 1; g->act = HPE_ACT_NONE; g->has_residual = 0;
+  g->Cin2 = 0; g->stride2 = 0;
+  if (f->Cin2) return fail(HPE_EUNSUPPORTED, "hpe_conv_dgrad_desc: fused two-input layers are inference-only");
   switch (f->kind) {
     case HPE_CONV_1x1:     g->kind = f->stride == 2 ? HPE_CONV_DGRAD1x1S2 : HPE_CONV_1x1; break;
     case HPE_CONV_3x3:     g->kind = f->stride == 2 ? HPE_CONV_DGRAD3x3S2 : HPE_CONV_3x3; break;
@@ -639,7 +675,7 @@ extern "C" int hpe_conv_pack_weight_dgrad(const hpe_conv_desc* f, const float* w
   return launch_status("pack_weight_dgrad_kernel");
 }
 
-typedef void (*ConvKernelFn)(const CUtensorMap, const CUtensorMap, const OutMaps, const CUtensorMap, const ConvParams);
+typedef void (*ConvKernelFn)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const OutMaps, const CUtensorMap, const ConvParams);
 
 template <int BN, int ST>
 static ConvKernelFn pick_kernel_bn(int act, bool res, bool fin) {
@@ -685,6 +721,7 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
     default: p.taps = 4; break;                 // stem, deconv, (dgrad 3x3/s2: upper bound, see kb_count)
   }
   p.kc_per_tap = d->kind == HPE_CONV_STEM7x7 ? 1 : cin_padded(d) / 64;
+  p.kc2 = (d->Cin2 + 63) / 64; p.in_stride2 = d->Cin2 ? d->stride2 : 1;
   p.n_classes = is_class_strided(d->kind) ? 4 : 1;
   // tile grid extent: deconv-like tiles walk the INPUT-resolution grid of one parity class
   const bool up2 = is_class_strided(d->kind) || d->kind == HPE_CONV_DGRAD1x1S2;
@@ -693,7 +730,7 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
   p.B = d->B; p.Cout = d->Cout;
   p.act = d->act; p.has_res = d->has_residual ? 1 : 0;
   int tw = 1, th = 1, nb = 128;
-  pick_brick(128, p.Wo, p.Ho, p.B, p.in_stride == 2 ? 128 : 256, &tw, &th, &nb);
+  pick_brick(128, p.Wo, p.Ho, p.B, (p.in_stride == 2 || p.in_stride2 == 2) ? 128 : 256, &tw, &th, &nb);
   p.tw = tw; p.th = th; p.nb = nb;
   p.tiles_x = (p.Wo + tw - 1) / tw; p.tiles_y = (p.Ho + th - 1) / th; p.tiles_b = (p.B + nb - 1) / nb;
   pl->block_n = pick_block_n(d, (long long)p.tiles_x * p.tiles_y * p.tiles_b * p.n_classes);
@@ -711,7 +748,7 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
     cudaError_t e = cudaFuncSetAttribute((const void*)pl->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem);
     if (e != cudaSuccess) { delete pl; return fail(HPE_ECUDA, "cudaFuncSetAttribute(smem=%zu) failed: %s", pl->smem, cudaGetErrorString(e)); }
   }
-  pl->x = pl->w = pl->res = nullptr; pl->y = nullptr;
+  pl->x = pl->x2 = pl->w = pl->res = nullptr; pl->y = nullptr;
   pl->halo_taps_y = pl->halo_boxes = 0;
   if (halo_eligible(d, pl->Ho, pl->Wo)) {
     const bool stem = d->kind == HPE_CONV_STEM7x7;
@@ -737,7 +774,7 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
 
 extern "C" void hpe_conv_plan_destroy(hpe_conv_plan* plan) { delete plan; }
 
-static int encode_plan_maps(hpe_conv_plan* pl, const void* x, const void* w, const void* res, void* y) {
+static int encode_plan_maps(hpe_conv_plan* pl, const void* x, const void* x2, const void* w, const void* res, void* y) {
   const hpe_conv_desc& d = pl->d;
   const ConvParams& p = pl->p;
   int rc;
@@ -762,6 +799,18 @@ static int encode_plan_maps(hpe_conv_plan* pl, const void* x, const void* w, con
     }
     if (rc) return rc;
     pl->x = x;
+  }
+  if (d.Cin2 && x2 != pl->x2) {
+    HPE_CHECK_ARG(x2 && ((uintptr_t)x2 & 15) == 0, "hpe_conv_run2: x2 must be non-null and 16-byte aligned");
+    const uint32_t s = (uint32_t)p.in_stride2;                // dense [B, Ho*s, Wo*s, Cin2]
+    const uint64_t C = d.Cin2, W2 = (uint64_t)pl->Wo * s, H2 = (uint64_t)pl->Ho * s;
+    const uint64_t dims[4] = {C, W2, H2, (uint64_t)d.B};
+    const uint64_t str[3] = {C * 2, W2 * C * 2, H2 * W2 * C * 2};
+    const uint32_t box[4] = {64, (uint32_t)p.tw * s, (uint32_t)p.th * s, (uint32_t)p.nb};
+    const uint32_t es[4] = {1, s, s, 1};
+    rc = encode_map(&pl->tmA2, x2, 4, dims, str, box, es, "A2");
+    if (rc) return rc;
+    pl->x2 = x2;
   }
   if (w != pl->w) {
     HPE_CHECK_ARG(((uintptr_t)w & 15) == 0, "hpe_conv_run: w must be 16-byte aligned");
@@ -813,13 +862,19 @@ static int encode_plan_maps(hpe_conv_plan* pl, const void* x, const void* w, con
 
 extern "C" int hpe_conv_run(hpe_conv_plan* pl, const void* x, const void* w_packed, const float* scale,
                             const float* shift, const void* residual, void* y, void* stream) {
+  return hpe_conv_run2(pl, x, nullptr, w_packed, scale, shift, residual, y, stream);
+}
+
+extern "C" int hpe_conv_run2(hpe_conv_plan* pl, const void* x, const void* x2, const void* w_packed, const float* scale,
+                             const float* shift, const void* residual, void* y, void* stream) {
   HPE_CHECK_ARG(pl && x && w_packed && scale && shift && y, "hpe_conv_run: null pointer");
+  HPE_CHECK_ARG((pl->d.Cin2 != 0) == (x2 != nullptr), "hpe_conv_run2: x2 must be given exactly when the plan has a second input (Cin2=%d)", pl->d.Cin2);
   HPE_CHECK_ARG((((uintptr_t)scale | (uintptr_t)shift) & 15) == 0, "hpe_conv_run: scale/shift must be 16-byte aligned");
   if ((is_class_strided(pl->d.kind) || pl->d.kind == HPE_CONV_DGRAD1x1S2) && pl->p.has_res)
     return fail(HPE_EUNSUPPORTED, "hpe_conv_run: the strided-store kinds have no residual input");
   if (pl->d.kind == HPE_CONV_DGRAD1x1S2)      // odd rows/columns of dx receive no gradient
     HPE_CUDA_OK(cudaMemsetAsync(y, 0, (size_t)pl->d.B * pl->Ho * pl->Wo * pl->d.Cout * 2, (cudaStream_t)stream));
-  int rc = encode_plan_maps(pl, x, w_packed, residual, y);
+  int rc = encode_plan_maps(pl, x, x2, w_packed, residual, y);
   if (rc) return rc;
   if (pl->halo_taps_y) {
     pl->hp.scale = scale; pl->hp.shift = shift;
@@ -831,7 +886,8 @@ extern "C" int hpe_conv_run(hpe_conv_plan* pl, const void* x, const void* w_pack
   p.hm_out = pl->d.kind == HPE_CONV_FINAL ? (float*)y : nullptr;
   if (!p.has_res) pl->tmRes = pl->tmA;      // unused, but must be a valid object to copy
   if (pl->d.kind == HPE_CONV_FINAL) for (int c = 0; c < 4; ++c) pl->tmOut.m[c] = pl->tmA;
-  void* args[5] = {&pl->tmA, &pl->tmW, &pl->tmOut, &pl->tmRes, &p};
+  if (!pl->d.Cin2) pl->tmA2 = pl->tmA;      // unused, but must be a valid object to copy
+  void* args[6] = {&pl->tmA, &pl->tmA2, &pl->tmW, &pl->tmOut, &pl->tmRes, &p};
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(pl->grid); cfg.blockDim = dim3(kConvThreads);
   cfg.dynamicSmemBytes = pl->smem; cfg.stream = (cudaStream_t)stream;

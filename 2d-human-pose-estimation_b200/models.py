@@ -183,7 +183,10 @@ class _ForwardPlan:
         if H % 32 or W % 32:
             raise ValueError(f"input {H}x{W} must be a multiple of 32")
         self.B, self.H, self.W, self.device = B, H, W, device
-        self.ops = []            # (layer, src_key, res_key, dst_key)
+        self.ops = []            # (layer, src_key, res_key, dst_key, src2_key)
+        self.fused_shortcut = {}  # conv3 path -> downsample path folded into it
+        # projection shortcut (downsample conv + BN) accumulated into conv3's TMEM tile: the shortcut tensor never exists
+        fuse_sc = os.environ.get("HPE_B200_FUSE_SHORTCUT", "1") != "0"
         self.bufs = {}
         self.named = {}          # module path -> ConvLayer (for load_weights)
         K = model.njoints
@@ -193,10 +196,10 @@ class _ForwardPlan:
             self.bufs[key] = torch.empty(shape, dtype=dtype, device=dev)
             return key
 
-        def add(name, layer, src, dst, res=None):
+        def add(name, layer, src, dst, res=None, src2=None):
             self.named[name] = layer
             buf(dst, layer.out_shape(), torch.float32 if layer.kind == CONV_FINAL else torch.bfloat16)
-            self.ops.append((layer, src, res, dst))
+            self.ops.append((layer, src, res, dst, src2))
 
         self.s2d = preprocess(torch.zeros(B, 3, H, W, device=dev))
         add("backbone.conv1", ConvLayer(CONV_STEM7x7, B, H, W, 3, 64, 2, ACT_RELU, False, dev), "s2d", "stem")
@@ -210,11 +213,16 @@ class _ForwardPlan:
                 add(pre + ".conv1", ConvLayer(CONV_1x1, B, h, w, cin, p, 1, ACT_RELU, False, dev), cur, pre + ".t1")
                 add(pre + ".conv2", ConvLayer(CONV_3x3, B, h, w, p, p, s, ACT_RELU, False, dev), pre + ".t1", pre + ".t2")
                 sc = cur
-                if j == 0:
+                if j == 0 and not fuse_sc:
                     add(pre + ".downsample.0", ConvLayer(CONV_1x1, B, h, w, cin, 4 * p, s, ACT_NONE, False, dev), cur, pre + ".sc")
                     sc = pre + ".sc"
                 h, w = h // s, w // s
-                add(pre + ".conv3", ConvLayer(CONV_1x1, B, h, w, p, 4 * p, 1, ACT_RELU, True, dev), pre + ".t2", pre + ".out", sc)
+                if j == 0 and fuse_sc:
+                    self.fused_shortcut[pre + ".conv3"] = pre + ".downsample"
+                    add(pre + ".conv3", ConvLayer(CONV_1x1, B, h, w, p, 4 * p, 1, ACT_RELU, False, dev, Cin2=cin, stride2=s),
+                        pre + ".t2", pre + ".out", None, cur)
+                else:
+                    add(pre + ".conv3", ConvLayer(CONV_1x1, B, h, w, p, 4 * p, 1, ACT_RELU, True, dev), pre + ".t2", pre + ".out", sc)
                 cur, cin = pre + ".out", 4 * p
         self.features_key = cur
         for d, idx in enumerate((0, 3, 6)):
@@ -249,14 +257,20 @@ class _ForwardPlan:
             else:
                 bn = mods[name.replace("conv", "bn")]
             scale, shift = fold_bn(bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps)
+            if name in self.fused_shortcut:
+                ds = self.fused_shortcut[name]
+                bn2 = mods[ds + ".1"]
+                scale2, shift2 = fold_bn(bn2.weight, bn2.bias, bn2.running_mean, bn2.running_var, bn2.eps)
+                layer.load2(m.weight, scale, shift, mods[ds + ".0"].weight, scale2, shift2)
+                continue
             layer.load(m.weight, scale, shift)
         self.weights_version = model._weights_version
         self.graph = None         # packed buffers are updated in place, but be conservative
 
     def _launch_all(self):
         b = self.bufs
-        for layer, src, res, dst in self.ops:
-            layer(b[src], b[res] if res else None, b[dst])
+        for layer, src, res, dst, src2 in self.ops:
+            layer(b[src], b[res] if res else None, b[dst], b[src2] if src2 else None)
             if dst == "stem":
                 maxpool3x3s2(b["stem"], b["pool"])
 

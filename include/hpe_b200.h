@@ -136,6 +136,12 @@ typedef struct hpe_conv_desc {
   int out_cstride;          /* same for y (the residual stays dense); 0 = Cout.  This is how torch.cat along channels disappears:
                                producers write straight into their slice (HPE/models/nn/modules/block.py:100,113,142-155).
                                HPE_CONV_FINAL: channel count of the NCHW tensor y is a slice of (head.py:176-179) */
+  int Cin2;                 /* != 0 (HPE_CONV_1x1, stride 1 only): a SECOND 1x1 conv over x2 [B,Ho*stride2,Wo*stride2,Cin2] is
+                               accumulated into the same output tile before the epilogue -- the projection shortcut of a timm
+                               Bottleneck (`shortcut = self.downsample(x)`; `x += shortcut`, resnet.py:247-268) fused into conv3,
+                               so the shortcut tensor is never written or re-read.  Both BN scales are folded into the weights
+                               by the caller (scale = 1, shift = shift3 + shift_ds). */
+  int stride2;              /* stride of the second conv: 1 or 2 */
 } hpe_conv_desc;
 /* Channel counts: Cin and Cout must be multiples of 8 (16-byte pixels); partial 64-channel blocks are zero-filled by TMA. */
 
@@ -148,6 +154,11 @@ size_t hpe_conv_packed_weight_elems(const hpe_conv_desc* desc);
 int  hpe_conv_pack_weight(const hpe_conv_desc* desc, const float* w_torch, void* w_packed, void* stream);
 int  hpe_conv_run(hpe_conv_plan* plan, const void* x, const void* w_packed,
                   const float* scale, const float* shift, const void* residual, void* y, void* stream);
+/* two-input variant (desc.Cin2 != 0): w_packed from hpe_conv_pack_weight2 = [Cout][ceil64(Cin) + ceil64(Cin2)];
+ * x2 is the dense bf16 NHWC tensor the second 1x1 conv reads with stride2 */
+int  hpe_conv_pack_weight2(const hpe_conv_desc* desc, const float* w_torch, const float* w2_torch, void* w_packed, void* stream);
+int  hpe_conv_run2(hpe_conv_plan* plan, const void* x, const void* x2, const void* w_packed,
+                   const float* scale, const float* shift, const void* residual, void* y, void* stream);
 /* output spatial size of the layer */
 int  hpe_conv_out_hw(const hpe_conv_desc* desc, int* Ho, int* Wo);
 

@@ -58,6 +58,35 @@ def test_conv1x1(hpe, cuda_dev, B, H, W, Cin, Cout, stride, act, res):
     check(nchw(y), ref, "conv1x1")
 
 
+@pytest.mark.parametrize("B,H,W,Cin,Cin2,Cout,stride2", [
+    (8, 16, 12, 64, 64, 256, 1),        # layer1.0: conv3 + stride-1 projection shortcut
+    (4, 16, 12, 128, 256, 512, 2),      # layer2.0: shortcut reads the block input with stride 2
+    (2, 8, 6, 512, 1024, 2048, 2),      # layer4.0: many k-blocks from both sources, 8 N tiles
+    (3, 10, 6, 64, 72, 128, 2),         # ragged bricks, second source with a partial 64-channel block
+])
+def test_conv1x1_fused_projection_shortcut(hpe, cuda_dev, B, H, W, Cin, Cin2, Cout, stride2):
+    """conv3 + bn3 + downsample(x) + add + ReLU of timm Bottleneck.forward (resnet.py:247-268) as ONE two-source GEMM;
+    both BN scales are folded into the weights in fp32 before the bf16 rounding."""
+    from importlib import import_module
+    conv = import_module("2d-human-pose-estimation_b200.conv")
+    g = torch.Generator().manual_seed(11)
+    x = make(g, B, Cin, H, W); w = torch.randn(Cout, Cin, 1, 1, generator=g) * Cin ** -0.5
+    x2 = make(g, B, Cin2, H * stride2, W * stride2); w2 = torch.randn(Cout, Cin2, 1, 1, generator=g) * Cin2 ** -0.5
+    scale = torch.rand(Cout, generator=g) + 0.5; shift = torch.randn(Cout, generator=g) * 0.1
+    scale2 = torch.rand(Cout, generator=g) + 0.5; shift2 = torch.randn(Cout, generator=g) * 0.1
+    ref = (F.conv2d(x, r16(w * scale.view(-1, 1, 1, 1))) + F.conv2d(x2, r16(w2 * scale2.view(-1, 1, 1, 1)), stride=stride2)
+           + (shift + shift2)[None, :, None, None])
+    ref = torch.relu(ref)
+    layer = conv.ConvLayer(conv.CONV_1x1, B, H, W, Cin, Cout, 1, 1, False, Cin2=Cin2, stride2=stride2)
+    layer.load2(w, scale, shift, w2, scale2, shift2)
+    y = layer(nhwc(x), None, None, nhwc(x2))
+    torch.cuda.synchronize()
+    assert tuple(y.shape) == (B, H, W, Cout)
+    check(nchw(y), ref, "conv1x1 + projection shortcut")
+    with pytest.raises(RuntimeError, match="x2"):
+        layer(nhwc(x))
+
+
 @pytest.mark.parametrize("B,H,W,C,Cout,stride", [
     (4, 16, 12, 64, 64, 1), (4, 16, 12, 128, 128, 1), (4, 32, 24, 128, 128, 2), (2, 16, 12, 256, 256, 2),
     (3, 10, 6, 64, 64, 1), (2, 8, 6, 512, 512, 1),

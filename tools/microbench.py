@@ -82,16 +82,16 @@ def forward():
     plan = next(iter(m._plans.values()))
     # per-layer eager timing (L2 not flushed between layers: this is how they run in the step)
     rows = []
-    for layer, src, res, dst in plan.ops:
+    for layer, src, res, dst, src2 in plan.ops:
         name = [k for k, v in plan.named.items() if v is layer][0]
-        fn = lambda: layer(plan.bufs[src], plan.bufs[res] if res else None, plan.bufs[dst])
+        fn = lambda: layer(plan.bufs[src], plan.bufs[res] if res else None, plan.bufs[dst], plan.bufs[src2] if src2 else None)
         med, best = timeit(fn, iters=5, warm=1)
         d = layer.desc
         taps = {0: 1, 1: 9, 2: 49 / 3 * 3, 3: 4, 4: 1}[d.kind]
-        macs = layer.B * layer.Ho * layer.Wo * d.Cout * d.Cin * taps
-        byts = plan.bufs[src].numel() * 2 + plan.bufs[dst].numel() * plan.bufs[dst].element_size() + (plan.bufs[res].numel() * 2 if res else 0)
+        macs = layer.B * layer.Ho * layer.Wo * d.Cout * (d.Cin * taps + d.Cin2)
+        byts = (plan.bufs[src2].numel() * 2 // (d.stride2 ** 2) if src2 else 0) + plan.bufs[src].numel() * 2 + plan.bufs[dst].numel() * plan.bufs[dst].element_size() + (plan.bufs[res].numel() * 2 if res else 0)
         rows.append((name, med, 2 * macs / med / 1e9, byts / med / 1e6))
-        print(f"  {name:32s} k{d.kind} {d.Cin:4d}->{d.Cout:4d} s{d.stride} out {layer.Ho}x{layer.Wo}: {med*1e3:8.1f} us  {2*macs/med/1e9:7.1f} TFLOP/s  {byts/med/1e6:7.0f} GB/s", flush=True)
+        print(f"  {name:32s} k{d.kind} {d.Cin:4d}{'+%d' % d.Cin2 if d.Cin2 else ''}->{d.Cout:4d} s{d.stride} out {layer.Ho}x{layer.Wo}: {med*1e3:8.1f} us  {2*macs/med/1e9:7.1f} TFLOP/s  {byts/med/1e6:7.0f} GB/s", flush=True)
     print(f"  sum of layers {sum(r[1] for r in rows):.3f} ms")
 
 
