@@ -45,7 +45,7 @@ struct ConvParams {
   int kind, taps, kc_per_tap, in_stride;
   int kc2, in_stride2;          // second A source (fused projection shortcut): its k-blocks follow the first source's
   int tw, th, nb;
-  int tiles_x, tiles_y, tiles_b, n_tiles_n, n_classes, num_tiles;
+  int tiles_x, tiles_y, tiles_b, n_tiles_n, n_classes, num_tiles;   // PAIR kernels: num_tiles counts tile PAIRS
   int Ho, Wo, B, Cout;          // Ho,Wo = extent of the tile grid (deconv: input-resolution grid per class)
   int cout_total;               // HPE_CONV_FINAL: channel count of the NCHW tensor y is a slice of
   int act, has_res;
@@ -88,9 +88,9 @@ __device__ __forceinline__ int kb_count(const ConvParams& p, int cls) {
   return p.taps * p.kc_per_tap + p.kc2;
 }
 
-template <int BLOCK_N, int STAGES>
+template <int BLOCK_N, int STAGES, bool PAIR = false>
 struct SmemLayout {
-  static constexpr int kBBytes     = BLOCK_N * kKBlock * 2;
+  static constexpr int kBBytes     = (PAIR ? BLOCK_N / 2 : BLOCK_N) * kKBlock * 2;    // a CTA of a pair holds half of B's rows
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kOffA   = 0;
   static constexpr int kOffB   = STAGES * kABytes;
@@ -121,16 +121,33 @@ __device__ __forceinline__ uint32_t relu_bf16x2(uint32_t v) {
   return *reinterpret_cast<uint32_t*>(&r);
 }
 
-// ACT: HPE_ACT_*; RES: residual add; FINAL: fp32 NCHW heatmap epilogue (HPE_CONV_FINAL)
-template <int BLOCK_N, int STAGES, int ACT, bool RES, bool FINAL>
+// work item -> this CTA's tile.  PAIR: work item = (n_tile, class, pair of M tiles); CTA `rank` of the 2-CTA cluster takes
+// M tile 2*pair + rank.  An odd tile count leaves the last peer an M tile past the batch: its TMA loads zero-fill and its
+// stores are clipped.
+template <bool PAIR>
+__device__ __forceinline__ int work_tile(const ConvParams& p, int work, int rank) {
+  if (!PAIR) return work;
+  const int per_m = p.n_tiles_n * p.n_classes;
+  return ((work / per_m) * 2 + rank) * per_m + work % per_m;
+}
+
+// ACT: HPE_ACT_*; RES: residual add; FINAL: fp32 NCHW heatmap epilogue (HPE_CONV_FINAL);
+// PAIR: cta_group::2 -- a 2-CTA cluster computes a 256 x BLOCK_N tile with ONE tcgen05.mma stream issued by the leader:
+// each CTA loads its own 128-pixel A brick and HALF of the weight tile, so a CTA ingests 32 KB instead of 48 KB per k-block
+// (BLOCK_N = 256) through the L2->SM path that bounds the deep-K layers.  Each CTA drains its own 128 TMEM lanes.
+template <int BLOCK_N, int STAGES, int ACT, bool RES, bool FINAL, bool PAIR = false>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
                  const __grid_constant__ CUtensorMap tmW, const __grid_constant__ OutMaps tmOut,
                  const __grid_constant__ CUtensorMap tmRes, const ConvParams p) {
-  using L = SmemLayout<BLOCK_N, STAGES>;
+  using L = SmemLayout<BLOCK_N, STAGES, PAIR>;
+  static_assert(!PAIR || (BLOCK_N % 32 == 0 && !FINAL), "pair kernels: N multiple of 32, bf16 NHWC epilogue");
   constexpr int kChunks   = BLOCK_N >= 64 ? BLOCK_N / 64 : 1;
   constexpr int kTmemCols = 2 * BLOCK_N <= 32 ? 32 : (2 * BLOCK_N <= 64 ? 64 : (2 * BLOCK_N <= 128 ? 128 : (2 * BLOCK_N <= 256 ? 256 : 512)));  // power of two
-  constexpr uint32_t kIdesc = make_idesc_bf16_m128(BLOCK_N);
+  constexpr uint32_t kIdesc = PAIR ? make_idesc_bf16_m256(BLOCK_N) : make_idesc_bf16_m128(BLOCK_N);
+  const int rank  = PAIR ? static_cast<int>(cluster_ctarank()) : 0;
+  const int work0 = PAIR ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
+  const int wstep = PAIR ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -155,17 +172,22 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (p.kc2) prefetch_tmap(&tmA2);
     if (!FINAL) for (int c = 0; c < p.n_classes; ++c) prefetch_tmap(&tmOut.m[c]);
     if (RES) prefetch_tmap(&tmRes);
-    for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], kEpiThreads / 32); }
+    // PAIR: the leader's full barrier collects both producers' arrivals, its tempty both CTAs' epilogue warps
+    for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], PAIR ? 2 : 1); mbar_init(&empty_bar[s], 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], (PAIR ? 2 : 1) * kEpiThreads / 32); }
     for (int b = 0; b < kNumSB; ++b) { mbar_init(&sbfull_bar[b], 1); mbar_init(&sbempty_bar[b], 1); }
     fence_mbar_init();
   }
-  if (warp == 1) { tmem_alloc(tmem_slot, kTmemCols); tmem_relinquish(); }
+  if (warp == 1) {
+    if constexpr (PAIR) { tmem_alloc_2sm(tmem_slot, kTmemCols); tmem_relinquish_2sm(); }
+    else                { tmem_alloc(tmem_slot, kTmemCols); tmem_relinquish(); }
+  }
   for (int i = threadIdx.x; i < p.n_tiles_n * BLOCK_N && i < kMaxCout; i += kConvThreads) {   // channels of a partial last N tile: 0
     sScale[i] = i < p.Cout ? __ldg(p.scale + i) : 0.f; sShift[i] = i < p.Cout ? __ldg(p.shift + i) : 0.f;
   }
   tc_fence_before();
   __syncthreads();
+  if constexpr (PAIR) cluster_sync_all();       // the peer's barriers are initialised before any remote arrive / multicast commit
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   // PDL: everything above (barrier init, TMEM alloc, descriptor prefetch, scale/shift staging -- all
@@ -175,59 +197,78 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   if (warp == 0) {
     // ===================== operand producer =====================
-    if (lane == 0) {
-      int stage = 0; uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-        const TileCoord t = tile_coord(p, tile);
-        const int wrow = t.cls * p.Cout + t.n_tile * BLOCK_N;
-        const int num_kb = kb_count(p, t.cls), num_kb1 = num_kb - p.kc2;
-        for (int kb = 0; kb < num_kb; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
-          mbar_arrive_expect_tx(&full_bar[stage], L::kStageBytes);
-          if (kb < num_kb1) {
-            const int tap = kb / p.kc_per_tap, kc = kb - tap * p.kc_per_tap;
-            int dx, dy; tap_offset(p, tap, t.cls, dx, dy);
-            tma_load_4d(sA + stage * kABytes, &tmA, &full_bar[stage], kc * kKBlock,
-                        t.x0 * p.in_stride + dx, t.y0 * p.in_stride + dy, t.b0);
-          } else {          // second source (1x1, own stride): the block input feeding the projection shortcut
-            tma_load_4d(sA + stage * kABytes, &tmA2, &full_bar[stage], (kb - num_kb1) * kKBlock,
-                        t.x0 * p.in_stride2, t.y0 * p.in_stride2, t.b0);
-          }
-          tma_load_2d(sB + stage * L::kBBytes, &tmW, &full_bar[stage], kb * kKBlock, wrow);
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+    // The WHOLE warp runs this loop converged and one elected lane issues (elect.sync inside the asm): every operand is
+    // warp-uniform, so the barrier/TMA instructions take uniform registers directly.  Issued from a divergent
+    // `if (lane == 0)` the same loop compiled to ~190 instructions per k-block (R2UR.BROADCAST + BRA.U.ANY re-broadcast loops
+    // around each UTMALDG, an integer division and the tap switch) -- measured ~540 cycles per k-block with loads, MMAs and
+    // epilogue all disabled, i.e. slower than the 512-cycle MMA work of a 128x256x64 block.
+    int stage = 0; uint32_t phase = 0;
+    for (int work = work0; work < p.num_tiles; work += wstep) {
+      const TileCoord t = tile_coord(p, work_tile<PAIR>(p, work, rank));
+      const int wrow = t.cls * p.Cout + t.n_tile * BLOCK_N + (PAIR ? rank * (BLOCK_N / 2) : 0);
+      const int num_kb = kb_count(p, t.cls), num_kb1 = num_kb - p.kc2;
+      const int bx = t.x0 * p.in_stride, by = t.y0 * p.in_stride;
+      int tap = 0, kc = 0, dx, dy;
+      tap_offset(p, 0, t.cls, dx, dy);
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);          // own barrier: the multicast commit frees the stage in both CTAs
+        const uint32_t dA = smem_u32(sA + stage * kABytes), dB = smem_u32(sB + stage * L::kBBytes);
+        const uint32_t fb = smem_u32(&full_bar[stage]);
+        const CUtensorMap* mA = &tmA;
+        int c0 = kc * kKBlock, cx = bx + dx, cy = by + dy;
+        if (kb >= num_kb1) {       // second source (1x1, own stride): the block input feeding the projection shortcut
+          mA = &tmA2; c0 = (kb - num_kb1) * kKBlock; cx = t.x0 * p.in_stride2; cy = t.y0 * p.in_stride2;
         }
+        if constexpr (PAIR) {
+          // both CTAs' bytes are accounted on the LEADER's barrier (the one its MMA warp waits on)
+          const uint32_t full0 = mapa_shared(fb, 0);
+          if (rank == 0) mbar_arrive_expect_tx_elect(fb, 2 * L::kStageBytes);
+          else           mbar_arrive_cluster_elect(full0);
+          tma_load_ab_2sm_elect(full0, dA, mA, c0, cx, cy, t.b0, dB, &tmW, kb * kKBlock, wrow);
+        } else {
+          tma_load_ab_elect(fb, L::kStageBytes, dA, mA, c0, cx, cy, t.b0, dB, &tmW, kb * kKBlock, wrow);
+        }
+        if (++kc == p.kc_per_tap) { kc = 0; ++tap; tap_offset(p, tap, t.cls, dx, dy); }
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
+    // whole warp converged, one elected lane issues; descriptors as 32-bit halves (constant high word, low word = stage
+    // base + immediate), see umma_bf16_elect_lo.  PAIR: only the leader CTA issues (for both CTAs' TMEM).
+    if (rank == 0) {
+      constexpr uint32_t kDescHi = (1024u >> 4) | (1u << 14) | (2u << 29);     // SBO = 1024 B, version 1, SWIZZLE_128B
       int stage = 0; uint32_t phase = 0; int it = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      for (int work = work0; work < p.num_tiles; work += wstep, ++it) {
         const int acc = it & 1;
         mbar_wait(&tempty_bar[acc], ((it >> 1) & 1) ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
-        const int num_kb = kb_count(p, tile_coord(p, tile).cls);
+        const int num_kb = kb_count(p, tile_coord(p, work_tile<PAIR>(p, work, 0)).cls);
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          const uint64_t adesc = make_sw128_kmajor_desc(sA + stage * kABytes);
-          const uint64_t bdesc = make_sw128_kmajor_desc(sB + stage * L::kBBytes);
+          const uint32_t a_lo = ((smem_u32(sA + stage * kABytes) & 0x3FFFFu) >> 4) | (1u << 16);
+          const uint32_t b_lo = ((smem_u32(sB + stage * L::kBBytes) & 0x3FFFFu) >> 4) | (1u << 16);
 #pragma unroll
-          for (int k = 0; k < kKBlock / 16; ++k)      // UMMA_K = 16 bf16 = 32 B -> +2 in the (addr>>4) field
-            umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, kIdesc, (kb | k) != 0);
-          umma_commit(&empty_bar[stage]);             // frees the smem stage when these MMAs retire
+          for (int k = 0; k < kKBlock / 16; ++k) {    // UMMA_K = 16 bf16 = 32 B -> +2 in the (addr>>4) field
+            if constexpr (PAIR) umma_bf16_2sm_elect_lo(tmem_d, a_lo + 2 * k, kDescHi, b_lo + 2 * k, kDescHi, kIdesc, (kb | k) != 0);
+            else                umma_bf16_elect_lo(tmem_d, a_lo + 2 * k, kDescHi, b_lo + 2 * k, kDescHi, kIdesc, (kb | k) != 0);
+          }
+          // frees the smem stage (in both CTAs of a pair) when these MMAs retire
+          if constexpr (PAIR) umma_commit_2sm_elect(&empty_bar[stage], 3); else umma_commit_elect(&empty_bar[stage]);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tfull_bar[acc]);                 // accumulator ready for the epilogue
+        // accumulator ready for the epilogue (of both CTAs)
+        if constexpr (PAIR) umma_commit_2sm_elect(&tfull_bar[acc], 3); else umma_commit_elect(&tfull_bar[acc]);
       }
     }
   } else if (warp == 2) {
     // ===================== residual producer =====================
     if (RES && lane == 0) {
       int r = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-        const TileCoord t = tile_coord(p, tile);
+      for (int work = work0; work < p.num_tiles; work += wstep) {
+        const TileCoord t = tile_coord(p, work_tile<PAIR>(p, work, rank));
         for (int c = 0; c < kChunks; ++c, ++r) {
           const int b = r % kNumSB;
           mbar_wait(&sbempty_bar[b], (r / kNumSB) & 1);
@@ -244,8 +285,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const bool leader = threadIdx.x == kEpiWarp0 * 32;
     if (RES && leader) { mbar_arrive(&sbempty_bar[0]); mbar_arrive(&sbempty_bar[1]); }
     int q = 0, it = 0;
-    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
-      const TileCoord t = tile_coord(p, tile);
+    for (int work = work0; work < p.num_tiles; work += wstep, ++it) {
+      const TileCoord t = tile_coord(p, work_tile<PAIR>(p, work, rank));
       const int acc = it & 1;
       mbar_wait(&tfull_bar[acc], (it >> 1) & 1);
       tc_fence_after();
@@ -292,7 +333,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           if (c == kChunks - 1) {                                   // accumulator drained -> MMA may reuse it
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+            if (lane == 0) {
+              if constexpr (PAIR) mbar_arrive_cluster(mapa_shared(smem_u32(&tempty_bar[acc]), 0));   // the leader's barrier
+              else                mbar_arrive(&tempty_bar[acc]);
+            }
           }
           const int n0 = t.n_tile * BLOCK_N + c * 64 + half * 32;   // first channel of this warp's 32 columns
           const uint32_t ss = smem_u32(sScale + n0), sh = smem_u32(sShift + n0);
@@ -340,7 +384,11 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) { tc_fence_after(); tmem_dealloc(tmem_base, kTmemCols); }
+  if constexpr (PAIR) cluster_sync_all();       // no CTA leaves while its peer may still signal its barriers / read its smem
+  if (warp == 1) {
+    tc_fence_after();
+    if constexpr (PAIR) tmem_dealloc_2sm(tmem_base, kTmemCols); else tmem_dealloc(tmem_base, kTmemCols);
+  }
 }
 
 // ---- auxiliary bandwidth kernels -------------------------------------------------------------------
@@ -459,6 +507,7 @@ struct hpe_conv_plan {
   hpe_conv_desc d;
   ConvParams p;
   int block_n, grid;
+  int pair;              // cta_group::2 kernel: 2-CTA clusters, each CTA loads half of the weight tile
   int Ho, Wo;            // real output size
   size_t smem;
   CUtensorMap tmA, tmW, tmRes;
@@ -691,7 +740,18 @@ static ConvKernelFn pick_kernel_bn(int act, bool res, bool fin) {
   return nullptr;
 }
 
-static ConvKernelFn pick_kernel(int block_n, int act, bool res, bool fin, size_t* smem) {
+template <int BN, int ST>
+static ConvKernelFn pick_kernel_pair(int act, bool res) {
+  switch (act) {
+    case HPE_ACT_RELU: return res ? conv_gemm_kernel<BN, ST, HPE_ACT_RELU, true, false, true> : conv_gemm_kernel<BN, ST, HPE_ACT_RELU, false, false, true>;
+    case HPE_ACT_SILU: return res ? conv_gemm_kernel<BN, ST, HPE_ACT_SILU, true, false, true> : conv_gemm_kernel<BN, ST, HPE_ACT_SILU, false, false, true>;
+    case HPE_ACT_GELU: return res ? nullptr : conv_gemm_kernel<BN, ST, HPE_ACT_GELU, false, false, true>;
+    default:           return res ? conv_gemm_kernel<BN, ST, HPE_ACT_NONE, true, false, true> : conv_gemm_kernel<BN, ST, HPE_ACT_NONE, false, false, true>;
+  }
+}
+
+static ConvKernelFn pick_kernel(int block_n, int act, bool res, bool fin, bool pair, size_t* smem) {
+  if (pair) { *smem = SmemLayout<256, 4, true>::kDynamic; return pick_kernel_pair<256, 4>(act, res); }
   switch (block_n) {
     case 32:  *smem = SmemLayout<32, 6>::kDynamic;  return pick_kernel_bn<32, 6>(act, res, fin);
     case 64:  *smem = SmemLayout<64, 6>::kDynamic;  return pick_kernel_bn<64, 6>(act, res, fin);
@@ -742,11 +802,42 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
   if (nt > 0x7fffffff) { delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: too many tiles"); }
   p.num_tiles = (int)nt;
   pl->grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
-  pl->fn = (const void*)pick_kernel(pl->block_n, d->act, p.has_res != 0, d->kind == HPE_CONV_FINAL, &pl->smem);
+  {
+    // cta_group::2 for the 256-wide tiles (HPE_B200_PAIR=0 disables): pairs of M tiles share one MMA stream
+    const char* e = getenv("HPE_B200_PAIR");
+    const long long m_tiles = (long long)p.tiles_x * p.tiles_y * p.tiles_b;
+    pl->pair = !(e && e[0] == '0') && pl->block_n == 256 && d->kind != HPE_CONV_FINAL && m_tiles >= 2 && !halo_eligible(d, pl->Ho, pl->Wo);
+    if (pl->pair) {
+      const long long np = (m_tiles + 1) / 2 * p.n_tiles_n * p.n_classes;
+      p.num_tiles = (int)np;
+      const int max_clusters = num_sms() / 2;
+      pl->grid = 2 * (int)(np < max_clusters ? np : max_clusters);
+    }
+  }
+  pl->fn = (const void*)pick_kernel(pl->block_n, d->act, p.has_res != 0, d->kind == HPE_CONV_FINAL, pl->pair != 0, &pl->smem);
   if (!pl->fn) { delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: no kernel for BLOCK_N=%d", pl->block_n); }
   {
     cudaError_t e = cudaFuncSetAttribute((const void*)pl->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem);
     if (e != cudaSuccess) { delete pl; return fail(HPE_ECUDA, "cudaFuncSetAttribute(smem=%zu) failed: %s", pl->smem, cudaGetErrorString(e)); }
+  }
+  if (pl->pair) {
+    // the persistent schedule strides by the number of clusters, so every cluster must be co-resident: ask the driver how
+    // many 2-CTA clusters of this kernel fit (not every TPC of a B200 has both SMs enabled)
+    static int max_clusters = -1;
+    if (max_clusters < 0) {
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(num_sms() / 2 * 2); cfg.blockDim = dim3(kConvThreads); cfg.dynamicSmemBytes = pl->smem;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+      cfg.attrs = at; cfg.numAttrs = 1;
+      int n = 0;
+      cudaError_t e = cudaOccupancyMaxActiveClusters(&n, (const void*)pl->fn, &cfg);
+      if (e != cudaSuccess || n <= 0) { delete pl; return fail(HPE_ECUDA, "cudaOccupancyMaxActiveClusters failed: %s", cudaGetErrorString(e)); }
+      const char* ov = getenv("HPE_B200_PAIR_CLUSTERS");
+      max_clusters = ov ? atoi(ov) : n;
+      if (getenv("HPE_B200_DEBUG")) fprintf(stderr, "[hpe] max active 2-CTA clusters: %d (using %d)\n", n, max_clusters);
+    }
+    pl->grid = 2 * (p.num_tiles < max_clusters ? p.num_tiles : max_clusters);
   }
   pl->x = pl->x2 = pl->w = pl->res = nullptr; pl->y = nullptr;
   pl->halo_taps_y = pl->halo_boxes = 0;
@@ -817,7 +908,7 @@ static int encode_plan_maps(hpe_conv_plan* pl, const void* x, const void* x2, co
     const uint64_t K = ktot(&d), R = wrows(&d);
     const uint64_t dims[2] = {K, R};
     const uint64_t str[1] = {K * 2};
-    const uint32_t box[2] = {64, (uint32_t)(pl->halo_taps_y ? 64 : pl->block_n)};
+    const uint32_t box[2] = {64, (uint32_t)(pl->halo_taps_y ? 64 : (pl->pair ? pl->block_n / 2 : pl->block_n))};
     rc = encode_map(&pl->tmW, w, 2, dims, str, box, ones, "W");
     if (rc) return rc;
     pl->w = w;
@@ -891,10 +982,19 @@ extern "C" int hpe_conv_run2(hpe_conv_plan* pl, const void* x, const void* x2, c
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(pl->grid); cfg.blockDim = dim3(kConvThreads);
   cfg.dynamicSmemBytes = pl->smem; cfg.stream = (cudaStream_t)stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (pl->pair) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = 2; attr[na].val.clusterDim.y = 1; attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
+  if (pdl_enabled()) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  cfg.attrs = attr; cfg.numAttrs = na;
   cudaError_t e = cudaLaunchKernelExC(&cfg, (const void*)pl->fn, args);
   if (e != cudaSuccess) return fail(HPE_ECUDA, "launch of conv_gemm_kernel failed: %s", cudaGetErrorString(e));
   return launch_status("conv_gemm_kernel");
