@@ -32,11 +32,11 @@ using namespace ptx;
 constexpr int kConvThreads   = 352;                   // 3 control warps + 8 epilogue warps
 constexpr int kEpiThreads    = 256;
 constexpr int kEpiWarp0      = 3;
-constexpr int kMaxCout       = 2048;                  // scale/shift table staged in shared memory
+constexpr int kMaxCout       = 2048;
+constexpr int kMaxBlockN     = 256;                   // scale/shift of ONE N tile staged in shared memory
 constexpr int kTileM         = 128;
 constexpr int kKBlock        = 64;                    // bf16 elements per k-block = one 128-byte swizzle row
 constexpr int kABytes        = kTileM * kKBlock * 2;  // 16 KB
-constexpr int kNumSB         = 4;                     // epilogue staging buffers (16 KB each)
 constexpr int kSBBytes       = kTileM * 64 * 2;       // 128 rows x 64 bf16
 
 struct OutMaps { CUtensorMap m[4]; };
@@ -88,18 +88,21 @@ __device__ __forceinline__ int kb_count(const ConvParams& p, int cls) {
   return p.taps * p.kc_per_tap + p.kc2;
 }
 
-template <int BLOCK_N, int STAGES, bool PAIR = false>
+// NSB = epilogue staging buffers (16 KB each): 4 with a residual (they double as its prefetch ring), else 3 -- the bytes
+// saved go to a deeper operand ring, which is what bounds the deep-K layers (ring depth / hand-off round trip).
+template <int BLOCK_N, int STAGES, bool PAIR = false, int NSB = 4>
 struct SmemLayout {
   static constexpr int kBBytes     = (PAIR ? BLOCK_N / 2 : BLOCK_N) * kKBlock * 2;    // a CTA of a pair holds half of B's rows
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kOffA   = 0;
   static constexpr int kOffB   = STAGES * kABytes;
   static constexpr int kOffSB  = kOffB + STAGES * kBBytes;
-  static constexpr int kOffSS  = kOffSB + kNumSB * kSBBytes;          // float scale[kMaxCout], shift[kMaxCout]
-  static constexpr int kOffBar = kOffSS + 2 * kMaxCout * 4;
-  static constexpr int kNumBar = 2 * STAGES + 4 + 2 * kNumSB;
+  static constexpr int kOffSS  = kOffSB + NSB * kSBBytes;             // float scale[kMaxBlockN], shift[kMaxBlockN]
+  static constexpr int kOffBar = kOffSS + 2 * kMaxBlockN * 4;
+  static constexpr int kNumBar = 2 * STAGES + 4 + 2 * NSB;
   static constexpr int kTotal  = kOffBar + kNumBar * 8 + 16;
-  static constexpr int kDynamic = kTotal + 1024;      // slack for manual 1024-byte alignment
+  static constexpr int kDynamic = kTotal;             // the dynamic segment starts 1024-byte aligned (checked in the kernel)
+  static_assert(kTotal <= 232448, "exceeds the 227 KB of shared memory a CTA may use");
 };
 
 __device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
@@ -140,7 +143,12 @@ __global__ void __launch_bounds__(kConvThreads, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
                  const __grid_constant__ CUtensorMap tmW, const __grid_constant__ OutMaps tmOut,
                  const __grid_constant__ CUtensorMap tmRes, const ConvParams p) {
-  using L = SmemLayout<BLOCK_N, STAGES, PAIR>;
+  // staging buffer q % kNumSB is rewritten by chunk q; the leader confirms "stores <= j-2 have left smem" at the start of
+  // chunk j and everyone meets at chunk j's named barrier, so at the start of chunk q only stores <= q-3 are known done:
+  // 3 buffers is the minimum.  With a residual the buffers double as its prefetch ring (4, lead 2).
+  constexpr int kNumSB = RES ? 4 : 3;
+  constexpr int kResLead = 2;                   // the residual of chunk q + 2 is requested while chunk q is processed
+  using L = SmemLayout<BLOCK_N, STAGES, PAIR, kNumSB>;
   static_assert(!PAIR || (BLOCK_N % 32 == 0 && !FINAL), "pair kernels: N multiple of 32, bf16 NHWC epilogue");
   constexpr int kChunks   = BLOCK_N >= 64 ? BLOCK_N / 64 : 1;
   constexpr int kTmemCols = 2 * BLOCK_N <= 32 ? 32 : (2 * BLOCK_N <= 64 ? 64 : (2 * BLOCK_N <= 128 ? 128 : (2 * BLOCK_N <= 256 ? 256 : 512)));  // power of two
@@ -149,13 +157,14 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int work0 = PAIR ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
   const int wstep = PAIR ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
 
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if (smem_u32(smem) & 1023u) __trap();         // SWIZZLE_128B operand tiles need 1024-byte alignment
   uint8_t* sA  = smem + L::kOffA;
   uint8_t* sB  = smem + L::kOffB;
   uint8_t* sSB = smem + L::kOffSB;
   float*   sScale = reinterpret_cast<float*>(smem + L::kOffSS);
-  float*   sShift = sScale + kMaxCout;
+  float*   sShift = sScale + kMaxBlockN;
   uint64_t* bars       = reinterpret_cast<uint64_t*>(smem + L::kOffBar);
   uint64_t* full_bar   = bars;
   uint64_t* empty_bar  = bars + STAGES;
@@ -181,9 +190,6 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 1) {
     if constexpr (PAIR) { tmem_alloc_2sm(tmem_slot, kTmemCols); tmem_relinquish_2sm(); }
     else                { tmem_alloc(tmem_slot, kTmemCols); tmem_relinquish(); }
-  }
-  for (int i = threadIdx.x; i < p.n_tiles_n * BLOCK_N && i < kMaxCout; i += kConvThreads) {   // channels of a partial last N tile: 0
-    sScale[i] = i < p.Cout ? __ldg(p.scale + i) : 0.f; sShift[i] = i < p.Cout ? __ldg(p.shift + i) : 0.f;
   }
   tc_fence_before();
   __syncthreads();
@@ -283,11 +289,22 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int half = (warp - kEpiWarp0) >> 2;     // which 32 of the chunk's 64 columns
     const int row = ew * 32 + lane;               // tile row = TMEM lane = pixel inside the brick
     const bool leader = threadIdx.x == kEpiWarp0 * 32;
-    if (RES && leader) { mbar_arrive(&sbempty_bar[0]); mbar_arrive(&sbempty_bar[1]); }
-    int q = 0, it = 0;
+    if (RES && leader) for (int b = 0; b < kResLead; ++b) mbar_arrive(&sbempty_bar[b]);
+    const int etid = threadIdx.x - kEpiWarp0 * 32;
+    int q = 0, it = 0, staged_n = -1;
     for (int work = work0; work < p.num_tiles; work += wstep, ++it) {
       const TileCoord t = tile_coord(p, work_tile<PAIR>(p, work, rank));
       const int acc = it & 1;
+      if (t.n_tile != staged_n) {
+        // this N tile's folded-BN scale/shift -> smem (channels past Cout: 0).  Every thread finished reading the previous
+        // tile's values before the named barrier of its last chunk, so the table is free to overwrite here.
+        if (etid < BLOCK_N) {
+          const int n = t.n_tile * BLOCK_N + etid;
+          sScale[etid] = n < p.Cout ? __ldg(p.scale + n) : 0.f; sShift[etid] = n < p.Cout ? __ldg(p.shift + n) : 0.f;
+        }
+        staged_n = t.n_tile;
+        named_bar_sync(1, kEpiThreads);
+      }
       mbar_wait(&tfull_bar[acc], (it >> 1) & 1);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BLOCK_N;
@@ -324,7 +341,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const uint32_t stg = smem_u32(sSB + sb * kSBBytes);
           if (leader) {
             bulk_wait_read<1>();                                    // stores <= q-2 have left shared memory
-            if (RES) mbar_arrive(&sbempty_bar[(q + 2) % kNumSB]);   // hand the buffer of chunk q+2 to warp 2
+            if (RES) mbar_arrive(&sbempty_bar[(q + kResLead) % kNumSB]);   // hand the buffer of chunk q+2 to warp 2
           }
           uint32_t v[32];
           tmem_ld_x32(taddr + c * 64 + half * 32, v);
@@ -338,7 +355,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               else                mbar_arrive(&tempty_bar[acc]);
             }
           }
-          const int n0 = t.n_tile * BLOCK_N + c * 64 + half * 32;   // first channel of this warp's 32 columns
+          const int n0 = c * 64 + half * 32;                        // first tile-local channel of this warp's 32 columns
           const uint32_t ss = smem_u32(sScale + n0), sh = smem_u32(sShift + n0);
           const uint32_t rowp = stg + row * 128;
 #pragma unroll
@@ -726,38 +743,42 @@ extern "C" int hpe_conv_pack_weight_dgrad(const hpe_conv_desc* f, const float* w
 
 typedef void (*ConvKernelFn)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const OutMaps, const CUtensorMap, const ConvParams);
 
-template <int BN, int ST>
-static ConvKernelFn pick_kernel_bn(int act, bool res, bool fin) {
-  if (fin) return conv_gemm_kernel<BN, ST, HPE_ACT_NONE, false, true>;
+// ST_N / ST_R: operand-ring depth without / with a residual (the residual variant keeps 4 staging buffers)
+template <int BN, int ST_N, int ST_R>
+static ConvKernelFn pick_kernel_bn(int act, bool res, bool fin, size_t* smem) {
+  *smem = res ? SmemLayout<BN, ST_R, false, 4>::kDynamic : SmemLayout<BN, ST_N, false, 3>::kDynamic;
+  if (fin) return conv_gemm_kernel<BN, ST_N, HPE_ACT_NONE, false, true>;
   if constexpr (BN >= 64) {
     switch (act) {
-      case HPE_ACT_RELU: return res ? conv_gemm_kernel<BN, ST, HPE_ACT_RELU, true, false> : conv_gemm_kernel<BN, ST, HPE_ACT_RELU, false, false>;
-      case HPE_ACT_SILU: return res ? conv_gemm_kernel<BN, ST, HPE_ACT_SILU, true, false> : conv_gemm_kernel<BN, ST, HPE_ACT_SILU, false, false>;
-      case HPE_ACT_GELU: return res ? nullptr : conv_gemm_kernel<BN, ST, HPE_ACT_GELU, false, false>;
-      default:           return res ? conv_gemm_kernel<BN, ST, HPE_ACT_NONE, true, false> : conv_gemm_kernel<BN, ST, HPE_ACT_NONE, false, false>;
+      case HPE_ACT_RELU: return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_RELU, true, false> : conv_gemm_kernel<BN, ST_N, HPE_ACT_RELU, false, false>;
+      case HPE_ACT_SILU: return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_SILU, true, false> : conv_gemm_kernel<BN, ST_N, HPE_ACT_SILU, false, false>;
+      case HPE_ACT_GELU: return res ? nullptr : conv_gemm_kernel<BN, ST_N, HPE_ACT_GELU, false, false>;
+      default:           return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_NONE, true, false> : conv_gemm_kernel<BN, ST_N, HPE_ACT_NONE, false, false>;
     }
   }
   return nullptr;
 }
 
-template <int BN, int ST>
-static ConvKernelFn pick_kernel_pair(int act, bool res) {
+template <int BN, int ST_N, int ST_R>
+static ConvKernelFn pick_kernel_pair(int act, bool res, size_t* smem) {
+  *smem = res ? SmemLayout<BN, ST_R, true, 4>::kDynamic : SmemLayout<BN, ST_N, true, 3>::kDynamic;
   switch (act) {
-    case HPE_ACT_RELU: return res ? conv_gemm_kernel<BN, ST, HPE_ACT_RELU, true, false, true> : conv_gemm_kernel<BN, ST, HPE_ACT_RELU, false, false, true>;
-    case HPE_ACT_SILU: return res ? conv_gemm_kernel<BN, ST, HPE_ACT_SILU, true, false, true> : conv_gemm_kernel<BN, ST, HPE_ACT_SILU, false, false, true>;
-    case HPE_ACT_GELU: return res ? nullptr : conv_gemm_kernel<BN, ST, HPE_ACT_GELU, false, false, true>;
-    default:           return res ? conv_gemm_kernel<BN, ST, HPE_ACT_NONE, true, false, true> : conv_gemm_kernel<BN, ST, HPE_ACT_NONE, false, false, true>;
+    case HPE_ACT_RELU: return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_RELU, true, false, true> : conv_gemm_kernel<BN, ST_N, HPE_ACT_RELU, false, false, true>;
+    case HPE_ACT_SILU: return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_SILU, true, false, true> : conv_gemm_kernel<BN, ST_N, HPE_ACT_SILU, false, false, true>;
+    case HPE_ACT_GELU: return res ? nullptr : conv_gemm_kernel<BN, ST_N, HPE_ACT_GELU, false, false, true>;
+    default:           return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_NONE, true, false, true> : conv_gemm_kernel<BN, ST_N, HPE_ACT_NONE, false, false, true>;
   }
 }
 
+// ring depths: as many stages as fit beside the staging buffers in the 227 KB a CTA may use
 static ConvKernelFn pick_kernel(int block_n, int act, bool res, bool fin, bool pair, size_t* smem) {
-  if (pair) { *smem = SmemLayout<256, 4, true>::kDynamic; return pick_kernel_pair<256, 4>(act, res); }
+  if (pair) return pick_kernel_pair<256, 5, 5>(act, res, smem);       // 32 KB stages (A + half of B)
   switch (block_n) {
-    case 32:  *smem = SmemLayout<32, 6>::kDynamic;  return pick_kernel_bn<32, 6>(act, res, fin);
-    case 64:  *smem = SmemLayout<64, 6>::kDynamic;  return pick_kernel_bn<64, 6>(act, res, fin);
-    case 128: *smem = SmemLayout<128, 4>::kDynamic; return pick_kernel_bn<128, 4>(act, res, fin);
-    case 192: *smem = SmemLayout<192, 3>::kDynamic; return pick_kernel_bn<192, 3>(act, res, fin);
-    default:  *smem = SmemLayout<256, 3>::kDynamic; return pick_kernel_bn<256, 3>(act, res, fin);
+    case 32:  return pick_kernel_bn<32, 6, 6>(act, res, fin, smem);
+    case 64:  return pick_kernel_bn<64, 7, 6>(act, res, fin, smem);      // 24 KB stages
+    case 128: return pick_kernel_bn<128, 5, 5>(act, res, fin, smem);     // 32 KB
+    case 192: return pick_kernel_bn<192, 4, 4>(act, res, fin, smem);     // 40 KB
+    default:  return pick_kernel_bn<256, 3, 3>(act, res, fin, smem);     // 48 KB
   }
 }
 
