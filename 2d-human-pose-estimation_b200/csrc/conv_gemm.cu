@@ -146,7 +146,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   // staging buffer q % kNumSB is rewritten by chunk q; the leader confirms "stores <= j-2 have left smem" at the start of
   // chunk j and everyone meets at chunk j's named barrier, so at the start of chunk q only stores <= q-3 are known done:
   // 3 buffers is the minimum.  With a residual the buffers double as its prefetch ring (4, lead 2).
-  constexpr int kNumSB = RES ? 4 : 3;
+  constexpr int kNumSB = FINAL ? 0 : (RES ? 4 : 3);      // the fp32 heatmap epilogue stores from registers: all smem to the ring
   constexpr int kResLead = 2;                   // the residual of chunk q + 2 is requested while chunk q is processed
   using L = SmemLayout<BLOCK_N, STAGES, PAIR, kNumSB>;
   static_assert(!PAIR || (BLOCK_N % 32 == 0 && !FINAL), "pair kernels: N multiple of 32, bf16 NHWC epilogue");
@@ -744,10 +744,10 @@ extern "C" int hpe_conv_pack_weight_dgrad(const hpe_conv_desc* f, const float* w
 typedef void (*ConvKernelFn)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const OutMaps, const CUtensorMap, const ConvParams);
 
 // ST_N / ST_R: operand-ring depth without / with a residual (the residual variant keeps 4 staging buffers)
-template <int BN, int ST_N, int ST_R>
+template <int BN, int ST_N, int ST_R, int ST_F>
 static ConvKernelFn pick_kernel_bn(int act, bool res, bool fin, size_t* smem) {
   *smem = res ? SmemLayout<BN, ST_R, false, 4>::kDynamic : SmemLayout<BN, ST_N, false, 3>::kDynamic;
-  if (fin) return conv_gemm_kernel<BN, ST_N, HPE_ACT_NONE, false, true>;
+  if (fin) { *smem = SmemLayout<BN, ST_F, false, 0>::kDynamic; return conv_gemm_kernel<BN, ST_F, HPE_ACT_NONE, false, true>; }
   if constexpr (BN >= 64) {
     switch (act) {
       case HPE_ACT_RELU: return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_RELU, true, false> : conv_gemm_kernel<BN, ST_N, HPE_ACT_RELU, false, false>;
@@ -772,13 +772,14 @@ static ConvKernelFn pick_kernel_pair(int act, bool res, size_t* smem) {
 
 // ring depths: as many stages as fit beside the staging buffers in the 227 KB a CTA may use
 static ConvKernelFn pick_kernel(int block_n, int act, bool res, bool fin, bool pair, size_t* smem) {
-  if (pair) return pick_kernel_pair<256, 5, 5>(act, res, smem);       // 32 KB stages (A + half of B)
+  if (pair && block_n == 256) return pick_kernel_pair<256, 5, 5>(act, res, smem);       // 32 KB stages (A + half of B)
+  if (pair) return pick_kernel_pair<128, 7, 6>(act, res, smem);                         // 24 KB stages
   switch (block_n) {
-    case 32:  return pick_kernel_bn<32, 6, 6>(act, res, fin, smem);
-    case 64:  return pick_kernel_bn<64, 7, 6>(act, res, fin, smem);      // 24 KB stages
-    case 128: return pick_kernel_bn<128, 5, 5>(act, res, fin, smem);     // 32 KB
-    case 192: return pick_kernel_bn<192, 4, 4>(act, res, fin, smem);     // 40 KB
-    default:  return pick_kernel_bn<256, 3, 3>(act, res, fin, smem);     // 48 KB
+    case 32:  return pick_kernel_bn<32, 6, 6, 11>(act, res, fin, smem);     // 20 KB stages (FINAL only)
+    case 64:  return pick_kernel_bn<64, 7, 6, 9>(act, res, fin, smem);      // 24 KB stages
+    case 128: return pick_kernel_bn<128, 5, 5, 7>(act, res, fin, smem);     // 32 KB
+    case 192: return pick_kernel_bn<192, 4, 4, 4>(act, res, fin, smem);     // 40 KB
+    default:  return pick_kernel_bn<256, 3, 3, 4>(act, res, fin, smem);     // 48 KB
   }
 }
 
@@ -826,8 +827,11 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
   {
     // cta_group::2 for the 256-wide tiles (HPE_B200_PAIR=0 disables): pairs of M tiles share one MMA stream
     const char* e = getenv("HPE_B200_PAIR");
+    // 128-wide tiles: opt-in only (HPE_B200_PAIR128=1) -- measured slower (layer2 3x3 128->128: 74 -> 88 us): their 24 KB
+    // stages hold only 256 cycles of MMA work, so the longer cross-CTA hand-off outweighs the two extra ring stages
+    const char* e128 = getenv("HPE_B200_PAIR128");
     const long long m_tiles = (long long)p.tiles_x * p.tiles_y * p.tiles_b;
-    pl->pair = !(e && e[0] == '0') && pl->block_n == 256 && d->kind != HPE_CONV_FINAL && m_tiles >= 2 && !halo_eligible(d, pl->Ho, pl->Wo);
+    pl->pair = !(e && e[0] == '0') && (pl->block_n == 256 || (pl->block_n == 128 && e128 && e128[0] == '1')) && d->kind != HPE_CONV_FINAL && m_tiles >= 2 && !halo_eligible(d, pl->Ho, pl->Wo);
     if (pl->pair) {
       const long long np = (m_tiles + 1) / 2 * p.n_tiles_n * p.n_classes;
       p.num_tiles = (int)np;

@@ -211,6 +211,12 @@ __device__ __forceinline__ void mbar_arrive_cluster_elect(uint32_t cluster_addr)
   asm volatile("{\n\t.reg .pred e;\n\telect.sync _|e, 0xffffffff;\n\t"
                "@e mbarrier.arrive.shared::cluster.b64 _, [%0];\n\t}" ::"r"(cluster_addr) : "memory");
 }
+__device__ __forceinline__ void tma_load_4d_elect(uint32_t dst, const CUtensorMap* m, uint32_t bar, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "{\n\t.reg .pred e;\n\telect.sync _|e, 0xffffffff;\n\t"
+      "@e cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];\n\t}"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
 // expect_tx + the A box (4-D) + the W box (2-D) of one ring stage, one election
 __device__ __forceinline__ void tma_load_ab_elect(uint32_t bar, uint32_t bytes, uint32_t dA, const CUtensorMap* mA,
                                                   int c0, int c1, int c2, int c3, uint32_t dB, const CUtensorMap* mW, int k, int row) {

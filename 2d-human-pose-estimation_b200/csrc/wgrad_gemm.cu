@@ -114,59 +114,62 @@ wgrad_gemm_kernel(const __grid_constant__ CUtensorMap tmL, const __grid_constant
   };
 
   if (warp == 0) {
-    if (lane == 0) {
-      int stage = 0; uint32_t phase = 0;
-      for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
-        int mt, nt, q0, q1; item_range(item, mt, nt, q0, q1);
-        int lch[2], ldx[2], ldy[2];
+    // producer: the whole warp runs the loop converged, one elected lane issues (see conv_gemm.cu: issued from a divergent
+    // `if (lane == 0)` every UTMALDG is wrapped in an R2UR.BROADCAST loop and the 2 + BLOCK_N/64 loads of a stage cost more
+    // issue time than the stage's 512 cycles of MMA work)
+    int stage = 0; uint32_t phase = 0;
+    for (int item = blockIdx.x; item < p.num_items; item += gridDim.x) {
+      int mt, nt, q0, q1; item_range(item, mt, nt, q0, q1);
+      int lch[2], ldx[2], ldy[2];
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          int lb = 2 * mt + h; if (lb >= p.n_lblocks) lb = p.n_lblocks - 1;
-          const int tap = lb / p.lblocks_per_tap;
-          lch[h] = (lb - tap * p.lblocks_per_tap) * 64;
-          wg_tap_offset(p.swapped ? HPE_CONV_1x1 : p.kind, tap, ldx[h], ldy[h]);
-        }
-        for (int q = q0; q < q1; ++q) {
-          const int x0 = (q % p.tiles_x) * p.kw; int r = q / p.tiles_x;
-          const int y0 = (r % p.tiles_y) * p.kh;
-          const int b0 = (r / p.tiles_y) * p.knb;
-          mbar_wait(&empty_bar[stage], phase ^ 1);
-          mbar_arrive_expect_tx(&full_bar[stage], S::kStageBytes);
-          uint8_t* sL = smem + stage * S::kStageBytes;
-          uint8_t* sR = sL + S::kLBytes;
+      for (int h = 0; h < 2; ++h) {
+        int lb = 2 * mt + h; if (lb >= p.n_lblocks) lb = p.n_lblocks - 1;
+        const int tap = lb / p.lblocks_per_tap;
+        lch[h] = (lb - tap * p.lblocks_per_tap) * 64;
+        wg_tap_offset(p.swapped ? HPE_CONV_1x1 : p.kind, tap, ldx[h], ldy[h]);
+      }
+      // brick coordinates advance incrementally (no per-stage division)
+      int tx = q0 % p.tiles_x, r0 = q0 / p.tiles_x, ty = r0 % p.tiles_y, tb = r0 / p.tiles_y;
+      for (int q = q0; q < q1; ++q) {
+        const int x0 = tx * p.kw, y0 = ty * p.kh, b0 = tb * p.knb;
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        const uint32_t fb = smem_u32(&full_bar[stage]);
+        const uint32_t sL = smem_u32(smem + stage * S::kStageBytes), sR = sL + S::kLBytes;
+        mbar_arrive_expect_tx_elect(fb, S::kStageBytes);
 #pragma unroll
-          for (int h = 0; h < 2; ++h)
-            tma_load_4d(sL + h * kBlkBytes, &tmL, &full_bar[stage], lch[h], x0 * p.lstride + ldx[h], y0 * p.lstride + ldy[h], b0);
+        for (int h = 0; h < 2; ++h)
+          tma_load_4d_elect(sL + h * kBlkBytes, &tmL, fb, lch[h], x0 * p.lstride + ldx[h], y0 * p.lstride + ldy[h], b0);
 #pragma unroll
-          for (int j = 0; j < BLOCK_N / 64; ++j)
-            tma_load_4d(sR + j * kBlkBytes, &tmR, &full_bar[stage], nt * BLOCK_N + j * 64, x0, y0, b0);
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
-        }
+        for (int j = 0; j < BLOCK_N / 64; ++j)
+          tma_load_4d_elect(sR + j * kBlkBytes, &tmR, fb, nt * BLOCK_N + j * 64, x0, y0, b0);
+        if (++tx == p.tiles_x) { tx = 0; if (++ty == p.tiles_y) { ty = 0; ++tb; } }
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      int stage = 0; uint32_t phase = 0; int it = 0;
-      for (int item = blockIdx.x; item < p.num_items; item += gridDim.x, ++it) {
-        int mt, nt, q0, q1; item_range(item, mt, nt, q0, q1);
-        const int acc = it & 1;
-        mbar_wait(&tempty_bar[acc], ((it >> 1) & 1) ^ 1);
+    // MMA issuer: converged warp, elected issue, descriptors as 32-bit halves (constant high word)
+    constexpr uint32_t kDescHi = (1024u >> 4) | (1u << 14) | (2u << 29);     // SBO = 1024 B, version 1, SWIZZLE_128B
+    constexpr uint32_t kLboLo  = static_cast<uint32_t>(kBlkBytes >> 4) << 16;  // 64-element MN blocks 8 KB apart
+    int stage = 0; uint32_t phase = 0; int it = 0;
+    for (int item = blockIdx.x; item < p.num_items; item += gridDim.x, ++it) {
+      int mt, nt, q0, q1; item_range(item, mt, nt, q0, q1);
+      const int acc = it & 1;
+      mbar_wait(&tempty_bar[acc], ((it >> 1) & 1) ^ 1);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
+      for (int q = q0; q < q1; ++q) {
+        mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
-        const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
-        for (int q = q0; q < q1; ++q) {
-          mbar_wait(&full_bar[stage], phase);
-          tc_fence_after();
-          uint8_t* sL = smem + stage * S::kStageBytes;
-          const uint64_t adesc = make_sw128_mnmajor_desc(sL, kBlkBytes);
-          const uint64_t bdesc = make_sw128_mnmajor_desc(sL + S::kLBytes, kBlkBytes);
+        const uint32_t sL = smem_u32(smem + stage * S::kStageBytes);
+        const uint32_t a_lo = ((sL & 0x3FFFFu) >> 4) | kLboLo;
+        const uint32_t b_lo = (((sL + S::kLBytes) & 0x3FFFFu) >> 4) | kLboLo;
 #pragma unroll
-          for (int k = 0; k < kBrickPx / 16; ++k)     // 16 pixel rows = 2048 B per MMA -> +128 in the (addr>>4) field
-            umma_bf16(tmem_d, adesc + 128 * k, bdesc + 128 * k, kIdesc, ((q - q0) | k) != 0);
-          umma_commit(&empty_bar[stage]);
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
-        }
-        umma_commit(&tfull_bar[acc]);
+        for (int k = 0; k < kBrickPx / 16; ++k)     // 16 pixel rows = 2048 B per MMA -> +128 in the (addr>>4) field
+          umma_bf16_elect_lo(tmem_d, a_lo + 128 * k, kDescHi, b_lo + 128 * k, kDescHi, kIdesc, ((q - q0) | k) != 0);
+        umma_commit_elect(&empty_bar[stage]);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
+      umma_commit_elect(&tfull_bar[acc]);
     }
   } else {
     // epilogue: TMEM lane quarter = warp & 3; the two warps of a quarter alternate 32-column groups

@@ -1,4 +1,2 @@
-timeout 240 python -m pytest tests/test_conv_gpu.py tests/test_dgrad_gpu.py -m gpu -x -q 2>&1 | tail -4
-for pair in 0 1; do
-HPE_B200_PAIR=$pair timeout 120 python tools/microbench.py forward 256 > gpurun_out/fwd_elect_pair$pair.log 2>&1; echo "pair=$pair $(head -1 gpurun_out/fwd_elect_pair$pair.log)"
-done
+timeout 400 python -m pytest tests/test_wgrad_gpu.py tests/test_train_gpu.py tests/test_dgrad_gpu.py tests/test_conv_gpu.py -m gpu -x -q 2>&1 | tail -3
+timeout 300 python bench.py --mode train --steps 20 --warmup 3 --no-cpu-baseline > gpurun_out/bench_train_n1.json 2> gpurun_out/bench_train_n1.err; cut -c1-600 gpurun_out/bench_train_n1.json
