@@ -130,28 +130,49 @@ bn_collect_kernel(const float* __restrict__ part, int nparts, long long M, int C
   }
 }
 
-// y = act(z * scale + shift (+ res))
+// y = act(z * scale + shift (+ res)).  The grid stride (gridDim.x * 256 vectors) is a multiple of cv (a power of two <= 256),
+// so a thread stays on ONE channel vector: its 16 coefficients are loaded once, and 4 independent 16-byte loads per input
+// are issued before any arithmetic (bytes in flight, not instruction count, bound these passes).
 __global__ void __launch_bounds__(256)
 bn_apply_kernel(const __nv_bfloat16* __restrict__ z, const float* __restrict__ scale, const float* __restrict__ shift,
                 const __nv_bfloat16* __restrict__ res, int relu, long long nvec, int cv, __nv_bfloat16* __restrict__ y) {
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int c0 = static_cast<int>(i % cv) * 8;
-    float f[8]; unpack8(__ldg(reinterpret_cast<const uint4*>(z) + i), f);
-    const float4 s0 = __ldg(reinterpret_cast<const float4*>(scale + c0)), s1 = __ldg(reinterpret_cast<const float4*>(scale + c0 + 4));
-    const float4 h0 = __ldg(reinterpret_cast<const float4*>(shift + c0)), h1 = __ldg(reinterpret_cast<const float4*>(shift + c0 + 4));
-    f[0] = fmaf(f[0], s0.x, h0.x); f[1] = fmaf(f[1], s0.y, h0.y); f[2] = fmaf(f[2], s0.z, h0.z); f[3] = fmaf(f[3], s0.w, h0.w);
-    f[4] = fmaf(f[4], s1.x, h1.x); f[5] = fmaf(f[5], s1.y, h1.y); f[6] = fmaf(f[6], s1.z, h1.z); f[7] = fmaf(f[7], s1.w, h1.w);
-    if (res) {
-      float r[8]; unpack8(__ldg(reinterpret_cast<const uint4*>(res) + i), r);
+  constexpr int U = 4;
+  const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const int c0 = static_cast<int>(tid % cv) * 8;
+  float sc[8], sh[8];
+  *reinterpret_cast<float4*>(sc) = __ldg(reinterpret_cast<const float4*>(scale + c0));
+  *reinterpret_cast<float4*>(sc + 4) = __ldg(reinterpret_cast<const float4*>(scale + c0 + 4));
+  *reinterpret_cast<float4*>(sh) = __ldg(reinterpret_cast<const float4*>(shift + c0));
+  *reinterpret_cast<float4*>(sh + 4) = __ldg(reinterpret_cast<const float4*>(shift + c0 + 4));
+  for (long long i = tid; i < nvec; i += U * stride) {
+    uint4 vz[U], vr[U];
 #pragma unroll
-      for (int e = 0; e < 8; ++e) f[e] += r[e];
+    for (int u = 0; u < U; ++u) {
+      const long long j = i + u * stride;
+      if (j < nvec) {
+        vz[u] = __ldg(reinterpret_cast<const uint4*>(z) + j);
+        if (res) vr[u] = __ldg(reinterpret_cast<const uint4*>(res) + j);
+      }
     }
-    if (relu) {
 #pragma unroll
-      for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.f);
+    for (int u = 0; u < U; ++u) {
+      const long long j = i + u * stride;
+      if (j >= nvec) break;
+      float f[8]; unpack8(vz[u], f);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) f[e] = fmaf(f[e], sc[e], sh[e]);
+      if (res) {
+        float r[8]; unpack8(vr[u], r);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[e] += r[e];
+      }
+      if (relu) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.f);
+      }
+      reinterpret_cast<uint4*>(y)[j] = pack8(f);
     }
-    reinterpret_cast<uint4*>(y)[i] = pack8(f);
   }
 }
 
@@ -160,30 +181,45 @@ __global__ void __launch_bounds__(256)
 bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
                     const __nv_bfloat16* __restrict__ z, const float* __restrict__ coef, int C,
                     int relu, long long nvec, int cv, __nv_bfloat16* __restrict__ dz, __nv_bfloat16* __restrict__ g_out) {
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int c0 = static_cast<int>(i % cv) * 8;
-    float fd[8], fz[8], fy[8], o[8], ca[8], cb[8], cc[8];
-    const uint4 vd = __ldg(reinterpret_cast<const uint4*>(dy) + i);
-    const uint4 vz = __ldg(reinterpret_cast<const uint4*>(z) + i);
-    uint4 vy = make_uint4(0, 0, 0, 0);
-    if (relu) vy = __ldg(reinterpret_cast<const uint4*>(y) + i);
-    *reinterpret_cast<float4*>(ca) = __ldg(reinterpret_cast<const float4*>(coef + c0));
-    *reinterpret_cast<float4*>(ca + 4) = __ldg(reinterpret_cast<const float4*>(coef + c0 + 4));
-    *reinterpret_cast<float4*>(cb) = __ldg(reinterpret_cast<const float4*>(coef + C + c0));
-    *reinterpret_cast<float4*>(cb + 4) = __ldg(reinterpret_cast<const float4*>(coef + C + c0 + 4));
-    *reinterpret_cast<float4*>(cc) = __ldg(reinterpret_cast<const float4*>(coef + 2 * C + c0));
-    *reinterpret_cast<float4*>(cc + 4) = __ldg(reinterpret_cast<const float4*>(coef + 2 * C + c0 + 4));
-    unpack8(vd, fd); unpack8(vz, fz);
-    if (relu) unpack8(vy, fy);
+  constexpr int U = 2;
+  const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const int c0 = static_cast<int>(tid % cv) * 8;       // constant per thread: the stride is a multiple of cv
+  float ca[8], cb[8], cc[8];
+  *reinterpret_cast<float4*>(ca) = __ldg(reinterpret_cast<const float4*>(coef + c0));
+  *reinterpret_cast<float4*>(ca + 4) = __ldg(reinterpret_cast<const float4*>(coef + c0 + 4));
+  *reinterpret_cast<float4*>(cb) = __ldg(reinterpret_cast<const float4*>(coef + C + c0));
+  *reinterpret_cast<float4*>(cb + 4) = __ldg(reinterpret_cast<const float4*>(coef + C + c0 + 4));
+  *reinterpret_cast<float4*>(cc) = __ldg(reinterpret_cast<const float4*>(coef + 2 * C + c0));
+  *reinterpret_cast<float4*>(cc + 4) = __ldg(reinterpret_cast<const float4*>(coef + 2 * C + c0 + 4));
+  for (long long i = tid; i < nvec; i += U * stride) {
+    uint4 vd[U], vz[U], vy[U];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      const float g = (relu && !(fy[e] > 0.f)) ? 0.f : fd[e];
-      o[e] = fmaf(ca[e], g, fmaf(cb[e], fz[e], cc[e]));
-      fd[e] = g;
+    for (int u = 0; u < U; ++u) {
+      const long long j = i + u * stride;
+      vy[u] = make_uint4(0, 0, 0, 0);
+      if (j < nvec) {
+        vd[u] = __ldg(reinterpret_cast<const uint4*>(dy) + j);
+        vz[u] = __ldg(reinterpret_cast<const uint4*>(z) + j);
+        if (relu) vy[u] = __ldg(reinterpret_cast<const uint4*>(y) + j);
+      }
     }
-    reinterpret_cast<uint4*>(dz)[i] = pack8(o);
-    if (g_out) reinterpret_cast<uint4*>(g_out)[i] = pack8(fd);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long j = i + u * stride;
+      if (j >= nvec) break;
+      float fd[8], fz[8], fy[8], o[8];
+      unpack8(vd[u], fd); unpack8(vz[u], fz);
+      if (relu) unpack8(vy[u], fy);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const float g = (relu && !(fy[e] > 0.f)) ? 0.f : fd[e];
+        o[e] = fmaf(ca[e], g, fmaf(cb[e], fz[e], cc[e]));
+        fd[e] = g;
+      }
+      reinterpret_cast<uint4*>(dz)[j] = pack8(o);
+      if (g_out) reinterpret_cast<uint4*>(g_out)[j] = pack8(fd);
+    }
   }
 }
 
