@@ -17,6 +17,8 @@ __device__ __forceinline__ uint4 pack8(const float* f) {
 // ---- per-channel reductions over the M = B*H*W rows of an [M][C] tensor --------------------------------
 // MODE 0: out0 = sum z, out1 = sum z^2                       (BatchNorm batch statistics)
 // MODE 1: g = relu ? (y > 0 ? dy : 0) : dy;  out0 = sum g,  out1 = sum g * (z - mean) * rstd   (BN backward)
+//         With y == nullptr and msc/msh given, the ReLU mask is recomputed as fmaf(z, msc, msh) > 0 -- the forward's own
+//         expression for units without a residual -- so the backward never reads y (2 of its 6 bytes per element).
 // 256 threads = (256 / (C/8)) rows x (C/8) 16-byte channel vectors; 4 rows in flight per thread.
 // Deterministic: every block writes its partial sums to part[blockIdx.x][2C]; bn_collect_kernel adds the
 // partials in a fixed order (no atomics), so the forward pass is bit-reproducible run to run.
@@ -24,16 +26,21 @@ template <int MODE>
 __global__ void __launch_bounds__(256)
 bn_reduce_kernel(const __nv_bfloat16* __restrict__ z, const __nv_bfloat16* __restrict__ dy,
                  const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean, const float* __restrict__ rstd,
-                 int relu, long long M, int C, float* __restrict__ part) {
+                 int relu, long long M, int C, float* __restrict__ part,
+                 const float* __restrict__ msc = nullptr, const float* __restrict__ msh = nullptr) {
   __shared__ float red[256][17];
   const int cv = C >> 3, rpp = 256 / cv;
   const int vec = threadIdx.x % cv, r0 = threadIdx.x / cv;
   float a0[8], a1[8], mu[8], rs[8];
 #pragma unroll
   for (int e = 0; e < 8; ++e) { a0[e] = 0.f; a1[e] = 0.f; mu[e] = 0.f; rs[e] = 1.f; }
+  float ks[8], kh[8];
+  const bool zmask = MODE == 1 && relu && y == nullptr;
   if (MODE == 1) {
 #pragma unroll
     for (int e = 0; e < 8; ++e) { mu[e] = mean[vec * 8 + e]; rs[e] = rstd[vec * 8 + e]; }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) { ks[e] = zmask ? msc[vec * 8 + e] : 0.f; kh[e] = zmask ? msh[vec * 8 + e] : 0.f; }
   }
   const long long step = static_cast<long long>(gridDim.x) * rpp;
   if (r0 < rpp) {
@@ -48,7 +55,7 @@ bn_reduce_kernel(const __nv_bfloat16* __restrict__ z, const __nv_bfloat16* __res
           vz[u] = __ldg(reinterpret_cast<const uint4*>(z) + off);
           if (MODE == 1) {
             vd[u] = __ldg(reinterpret_cast<const uint4*>(dy) + off);
-            if (relu) vy[u] = __ldg(reinterpret_cast<const uint4*>(y) + off);
+            if (relu && !zmask) vy[u] = __ldg(reinterpret_cast<const uint4*>(y) + off);
           }
         }
       }
@@ -61,7 +68,11 @@ bn_reduce_kernel(const __nv_bfloat16* __restrict__ z, const __nv_bfloat16* __res
             for (int e = 0; e < 8; ++e) { a0[e] += fz[e]; a1[e] = fmaf(fz[e], fz[e], a1[e]); }
           } else {
             float fd[8], fy[8]; unpack8(vd[u], fd);
-            if (relu) unpack8(vy[u], fy);
+            if (relu && !zmask) unpack8(vy[u], fy);
+            if (zmask) {
+#pragma unroll
+              for (int e = 0; e < 8; ++e) fy[e] = fmaf(fz[e], ks[e], kh[e]);
+            }
 #pragma unroll
             for (int e = 0; e < 8; ++e) {
               const float g = (relu && !(fy[e] > 0.f)) ? 0.f : fd[e];
@@ -100,7 +111,8 @@ bn_collect_kernel(const float* __restrict__ part, int nparts, long long M, int C
   const int c = blockIdx.x * 32 + cl;
   float s0 = 0.f, s1 = 0.f;
   if (c < C)
-    for (int b = r; b < nparts; b += 32) {
+#pragma unroll 8
+    for (int b = r; b < nparts; b += 32) {      // independent loads: unrolled so ~8 L2 round trips overlap (was latency-bound)
       s0 += part[static_cast<size_t>(b) * 2 * C + c];
       s1 += part[static_cast<size_t>(b) * 2 * C + C + c];
     }
@@ -131,20 +143,19 @@ bn_collect_kernel(const float* __restrict__ part, int nparts, long long M, int C
 }
 
 // y = act(z * scale + shift (+ res)).  The grid stride (gridDim.x * 256 vectors) is a multiple of cv (a power of two <= 256),
-// so a thread stays on ONE channel vector: its 16 coefficients are loaded once, and 4 independent 16-byte loads per input
-// are issued before any arithmetic (bytes in flight, not instruction count, bound these passes).
+// so a thread stays on ONE channel vector.  Its coefficients sit in shared memory (read with LDS.128 at the point of use):
+// keeping them in registers cost occupancy, and these passes are bound by bytes in flight per SM (measured: 96 registers ->
+// 2 blocks/SM -> 49 KB in flight was slower although it read fewer bytes).  4 independent 16-byte loads per input per thread.
 __global__ void __launch_bounds__(256)
 bn_apply_kernel(const __nv_bfloat16* __restrict__ z, const float* __restrict__ scale, const float* __restrict__ shift,
                 const __nv_bfloat16* __restrict__ res, int relu, long long nvec, int cv, __nv_bfloat16* __restrict__ y) {
   constexpr int U = 4;
+  __shared__ __align__(16) float sk[2][2048];
+  for (int c = threadIdx.x; c < cv * 8; c += 256) { sk[0][c] = __ldg(scale + c); sk[1][c] = __ldg(shift + c); }
+  __syncthreads();
   const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-  const int c0 = static_cast<int>(tid % cv) * 8;
-  float sc[8], sh[8];
-  *reinterpret_cast<float4*>(sc) = __ldg(reinterpret_cast<const float4*>(scale + c0));
-  *reinterpret_cast<float4*>(sc + 4) = __ldg(reinterpret_cast<const float4*>(scale + c0 + 4));
-  *reinterpret_cast<float4*>(sh) = __ldg(reinterpret_cast<const float4*>(shift + c0));
-  *reinterpret_cast<float4*>(sh + 4) = __ldg(reinterpret_cast<const float4*>(shift + c0 + 4));
+  const int c0 = static_cast<int>(threadIdx.x % cv) * 8;        // == (tid % cv) * 8 since 256 % cv == 0
   for (long long i = tid; i < nvec; i += U * stride) {
     uint4 vz[U], vr[U];
 #pragma unroll
@@ -159,7 +170,11 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ z, const float* __restrict__ s
     for (int u = 0; u < U; ++u) {
       const long long j = i + u * stride;
       if (j >= nvec) break;
-      float f[8]; unpack8(vz[u], f);
+      float f[8], sc[8], sh[8]; unpack8(vz[u], f);
+      *reinterpret_cast<float4*>(sc) = *reinterpret_cast<const float4*>(&sk[0][c0]);
+      *reinterpret_cast<float4*>(sc + 4) = *reinterpret_cast<const float4*>(&sk[0][c0 + 4]);
+      *reinterpret_cast<float4*>(sh) = *reinterpret_cast<const float4*>(&sk[1][c0]);
+      *reinterpret_cast<float4*>(sh + 4) = *reinterpret_cast<const float4*>(&sk[1][c0 + 4]);
 #pragma unroll
       for (int e = 0; e < 8; ++e) f[e] = fmaf(f[e], sc[e], sh[e]);
       if (res) {
@@ -180,18 +195,19 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ z, const float* __restrict__ s
 __global__ void __launch_bounds__(256)
 bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
                     const __nv_bfloat16* __restrict__ z, const float* __restrict__ coef, int C,
-                    int relu, long long nvec, int cv, __nv_bfloat16* __restrict__ dz, __nv_bfloat16* __restrict__ g_out) {
+                    int relu, long long nvec, int cv, __nv_bfloat16* __restrict__ dz, __nv_bfloat16* __restrict__ g_out,
+                    const float* __restrict__ msc, const float* __restrict__ msh) {
   constexpr int U = 2;
+  const bool zmask = relu && y == nullptr;      // ReLU mask recomputed from z (see bn_reduce_kernel)
+  __shared__ __align__(16) float sk[5][2048];   // A, Bz, C0, mask scale, mask shift
+  for (int c = threadIdx.x; c < C; c += 256) {
+    sk[0][c] = __ldg(coef + c); sk[1][c] = __ldg(coef + C + c); sk[2][c] = __ldg(coef + 2 * C + c);
+    sk[3][c] = zmask ? __ldg(msc + c) : 0.f; sk[4][c] = zmask ? __ldg(msh + c) : 0.f;
+  }
+  __syncthreads();
   const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-  const int c0 = static_cast<int>(tid % cv) * 8;       // constant per thread: the stride is a multiple of cv
-  float ca[8], cb[8], cc[8];
-  *reinterpret_cast<float4*>(ca) = __ldg(reinterpret_cast<const float4*>(coef + c0));
-  *reinterpret_cast<float4*>(ca + 4) = __ldg(reinterpret_cast<const float4*>(coef + c0 + 4));
-  *reinterpret_cast<float4*>(cb) = __ldg(reinterpret_cast<const float4*>(coef + C + c0));
-  *reinterpret_cast<float4*>(cb + 4) = __ldg(reinterpret_cast<const float4*>(coef + C + c0 + 4));
-  *reinterpret_cast<float4*>(cc) = __ldg(reinterpret_cast<const float4*>(coef + 2 * C + c0));
-  *reinterpret_cast<float4*>(cc + 4) = __ldg(reinterpret_cast<const float4*>(coef + 2 * C + c0 + 4));
+  const int c0 = static_cast<int>(threadIdx.x % cv) * 8;       // constant per thread: the stride is a multiple of cv
   for (long long i = tid; i < nvec; i += U * stride) {
     uint4 vd[U], vz[U], vy[U];
 #pragma unroll
@@ -201,22 +217,39 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
       if (j < nvec) {
         vd[u] = __ldg(reinterpret_cast<const uint4*>(dy) + j);
         vz[u] = __ldg(reinterpret_cast<const uint4*>(z) + j);
-        if (relu) vy[u] = __ldg(reinterpret_cast<const uint4*>(y) + j);
+        if (relu && !zmask) vy[u] = __ldg(reinterpret_cast<const uint4*>(y) + j);
       }
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const long long j = i + u * stride;
       if (j >= nvec) break;
-      float fd[8], fz[8], fy[8], o[8];
+      float fd[8], fz[8], fy[8], o[8], k[8];
       unpack8(vd[u], fd); unpack8(vz[u], fz);
-      if (relu) unpack8(vy[u], fy);
+      if (relu && !zmask) unpack8(vy[u], fy);
+      if (zmask) {
+        float ks[8];
+        *reinterpret_cast<float4*>(ks) = *reinterpret_cast<const float4*>(&sk[3][c0]);
+        *reinterpret_cast<float4*>(ks + 4) = *reinterpret_cast<const float4*>(&sk[3][c0 + 4]);
+        *reinterpret_cast<float4*>(k) = *reinterpret_cast<const float4*>(&sk[4][c0]);
+        *reinterpret_cast<float4*>(k + 4) = *reinterpret_cast<const float4*>(&sk[4][c0 + 4]);
 #pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        const float g = (relu && !(fy[e] > 0.f)) ? 0.f : fd[e];
-        o[e] = fmaf(ca[e], g, fmaf(cb[e], fz[e], cc[e]));
-        fd[e] = g;
+        for (int e = 0; e < 8; ++e) fy[e] = fmaf(fz[e], ks[e], k[e]);
       }
+#pragma unroll
+      for (int e = 0; e < 8; ++e) fd[e] = (relu && !(fy[e] > 0.f)) ? 0.f : fd[e];     // g
+      *reinterpret_cast<float4*>(k) = *reinterpret_cast<const float4*>(&sk[1][c0]);
+      *reinterpret_cast<float4*>(k + 4) = *reinterpret_cast<const float4*>(&sk[1][c0 + 4]);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) o[e] = k[e] * fz[e];
+      *reinterpret_cast<float4*>(k) = *reinterpret_cast<const float4*>(&sk[2][c0]);
+      *reinterpret_cast<float4*>(k + 4) = *reinterpret_cast<const float4*>(&sk[2][c0 + 4]);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) o[e] += k[e];                    // == fmaf(Bz, z, C0)
+      *reinterpret_cast<float4*>(k) = *reinterpret_cast<const float4*>(&sk[0][c0]);
+      *reinterpret_cast<float4*>(k + 4) = *reinterpret_cast<const float4*>(&sk[0][c0 + 4]);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) o[e] = fmaf(k[e], fd[e], o[e]);
       reinterpret_cast<uint4*>(dz)[j] = pack8(o);
       if (g_out) reinterpret_cast<uint4*>(g_out)[j] = pack8(fd);
     }
@@ -411,19 +444,27 @@ extern "C" int hpe_bn_apply(const void* z, long long M, int C, const float* scal
 extern "C" int hpe_bn_backward(const void* dy, const void* y, const void* z, long long M, int C, const float* mean,
                                const float* rstd, const float* gamma, int relu, float* scratch, float* dbeta,
                                float* dgamma, void* dz, void* g_out, void* stream) {
+  HPE_CHECK_ARG(y || !relu, "hpe_bn_backward: the ReLU mask needs y (or use hpe_bn_backward_zmask)");
+  return hpe_bn_backward_zmask(dy, y, z, M, C, mean, rstd, gamma, relu, nullptr, nullptr, scratch, dbeta, dgamma, dz, g_out, stream);
+}
+
+extern "C" int hpe_bn_backward_zmask(const void* dy, const void* y, const void* z, long long M, int C, const float* mean,
+                                     const float* rstd, const float* gamma, int relu, const float* scale, const float* shift,
+                                     float* scratch, float* dbeta, float* dgamma, void* dz, void* g_out, void* stream) {
   int rc = bn_shape_ok(M, C, "hpe_bn_backward");
   if (rc) return rc;
-  HPE_CHECK_ARG(dy && z && mean && rstd && gamma && scratch && dbeta && dgamma && dz && (y || !relu), "hpe_bn_backward: null pointer");
+  HPE_CHECK_ARG(dy && z && mean && rstd && gamma && scratch && dbeta && dgamma && dz && (y || !relu || (scale && shift)),
+                "hpe_bn_backward: null pointer");
   cudaStream_t st = (cudaStream_t)stream;
   const int grid = reduce_grid(M, C);
   bn_reduce_kernel<1><<<grid, 256, 0, st>>>((const __nv_bfloat16*)z, (const __nv_bfloat16*)dy, (const __nv_bfloat16*)y, mean,
-                                            rstd, relu, M, C, scratch);
+                                            rstd, relu, M, C, scratch, scale, shift);
   float* coef = scratch + (size_t)kBnMaxParts * 2 * C;
   bn_collect_kernel<1><<<(C + 31) / 32, 1024, 0, st>>>(scratch, grid, M, C, gamma, nullptr, 0.f, 0.f, nullptr, nullptr,
                                                        dbeta, dgamma, const_cast<float*>(mean), const_cast<float*>(rstd), coef);
   const long long nvec = M * (C / 8);
   bn_bwd_apply_kernel<<<ew_grid(nvec), 256, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)y, (const __nv_bfloat16*)z,
-                                                    coef, C, relu, nvec, C / 8, (__nv_bfloat16*)dz, (__nv_bfloat16*)g_out);
+                                                    coef, C, relu, nvec, C / 8, (__nv_bfloat16*)dz, (__nv_bfloat16*)g_out, scale, shift);
   return launch_status("bn_backward");
 }
 

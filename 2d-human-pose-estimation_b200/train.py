@@ -62,12 +62,15 @@ def bn_scratch(device):
     return _bn_scratch[key]
 
 
-def bn_backward(dy, y, z, mean, rstd, gamma, relu, dbeta, dgamma, dz, g_out=None):
+def bn_backward(dy, y, z, mean, rstd, gamma, relu, dbeta, dgamma, dz, g_out=None, scale=None, shift=None):
+    """``y=None`` with ``relu`` and the forward's ``scale``/``shift``: the ReLU mask is recomputed from z (units without a
+    residual), so y is not read."""
     M, Cc = z.numel() // z.shape[-1], z.shape[-1]
     with torch.cuda.device(z.device):
-        rc = _lib.lib().hpe_bn_backward(_lib.ptr(dy), _lib.ptr(y), _lib.ptr(z), M, Cc, _lib.ptr(mean), _lib.ptr(rstd),
-                                        _lib.ptr(gamma), int(relu), _lib.ptr(bn_scratch(z.device)), _lib.ptr(dbeta),
-                                        _lib.ptr(dgamma), _lib.ptr(dz), _lib.ptr(g_out), _lib.stream_ptr())
+        rc = _lib.lib().hpe_bn_backward_zmask(_lib.ptr(dy), _lib.ptr(y), _lib.ptr(z), M, Cc, _lib.ptr(mean), _lib.ptr(rstd),
+                                              _lib.ptr(gamma), int(relu), _lib.ptr(scale), _lib.ptr(shift),
+                                              _lib.ptr(bn_scratch(z.device)), _lib.ptr(dbeta),
+                                              _lib.ptr(dgamma), _lib.ptr(dz), _lib.ptr(g_out), _lib.stream_ptr())
     _lib.check(rc, "hpe_bn_backward")
 
 
@@ -124,6 +127,7 @@ class _Unit:
 
     def forward(self, x, residual=None):
         self.x = x
+        self.has_res = residual is not None
         self.fwd(x, None, self.z)
         bn_stats(self.z, self.bn, self)
         bn_apply(self.z, self.scale, self.shift, residual, self.relu, self.y)
@@ -133,8 +137,10 @@ class _Unit:
         """dy: gradient w.r.t. this unit's output y.  Writes the conv-weight / BN-affine gradients into ``grads``;
         returns dx (or None when the unit has no dgrad)."""
         dzv = dz.narrow(0, 0, self.z.numel()).view(self.z.shape)
-        bn_backward(dy, self.y if self.relu else None, self.z, self.mean, self.rstd, self.bn.weight, self.relu,
-                    grads[self.bn_name + ".bias"], grads[self.bn_name + ".weight"], dzv, g_out)
+        zmask = self.relu and not getattr(self, "has_res", True)      # y = relu(z*scale + shift): mask recomputed from z
+        bn_backward(dy, self.y if (self.relu and not zmask) else None, self.z, self.mean, self.rstd, self.bn.weight, self.relu,
+                    grads[self.bn_name + ".bias"], grads[self.bn_name + ".weight"], dzv, g_out,
+                    self.scale if zmask else None, self.shift if zmask else None)
         self.wg(self.x, dzv, grads[self.conv_name + ".weight"])
         if self.dg is None:
             return None

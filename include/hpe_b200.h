@@ -218,6 +218,11 @@ int hpe_bn_apply(const void* z, long long M, int C, const float* scale, const fl
 int hpe_bn_backward(const void* dy, const void* y, const void* z, long long M, int C, const float* mean,
                     const float* rstd, const float* gamma, int relu, float* scratch, float* dbeta, float* dgamma,
                     void* dz, void* g_out, void* stream);
+/* Same with y == NULL allowed for ReLU units WITHOUT a residual: the mask y > 0 is recomputed as z*scale + shift > 0 from the
+ * forward's own scale/shift (hpe_bn_stats outputs), so the backward reads 4 instead of 6 bytes per element. */
+int hpe_bn_backward_zmask(const void* dy, const void* y, const void* z, long long M, int C, const float* mean,
+                          const float* rstd, const float* gamma, int relu, const float* scale, const float* shift,
+                          float* scratch, float* dbeta, float* dgamma, void* dz, void* g_out, void* stream);
 /* MaxPool 3x3 s2 p1 that records the winning window position (first max, torch semantics) and its backward. */
 int hpe_maxpool3x3s2_train(const void* x, int B, int H, int W, int C, void* y, uint8_t* idx, void* stream);
 int hpe_maxpool3x3s2_backward(const void* dy, const uint8_t* idx, int B, int H, int W, int C, void* dx, void* stream);

@@ -38,6 +38,9 @@ def make(g, *shape, s=1.0):
     (4, 32, 24, 256, 512, 2, 0, False),    # stride-2 downsample, no activation
     (3, 10, 7, 64, 64, 1, 2, False),       # ragged tiles + SiLU (ConvBlock act)
     (2, 8, 6, 1024, 2048, 1, 1, True),     # many N tiles, many k-blocks
+    (3, 16, 8, 128, 256, 1, 1, True),      # cta_group::2 pair kernel with an ODD number of M tiles (3): the last peer tile is out of range
+    (1, 16, 8, 64, 512, 1, 2, False),      # a single M tile: too few for a pair -> 1-CTA 256-wide kernel, SiLU
+    (5, 10, 6, 256, 256, 2, 1, False),     # pair kernel, stride 2, ragged bricks
 ])
 def test_conv1x1(hpe, cuda_dev, B, H, W, Cin, Cout, stride, act, res):
     from importlib import import_module
@@ -124,7 +127,7 @@ def test_stem_and_maxpool(hpe, cuda_dev, B, H, W):
     assert torch.equal(nchw(p), pref)
 
 
-@pytest.mark.parametrize("B,H,W,Cin", [(4, 8, 6, 256), (2, 8, 6, 2048), (3, 5, 7, 256), (2, 32, 24, 256)])
+@pytest.mark.parametrize("B,H,W,Cin", [(4, 8, 6, 256), (2, 8, 6, 2048), (3, 5, 7, 256), (2, 32, 24, 256), (3, 8, 8, 128)])
 def test_deconv4x4s2(hpe, cuda_dev, B, H, W, Cin):
     from importlib import import_module
     conv = import_module("2d-human-pose-estimation_b200.conv")

@@ -89,6 +89,12 @@ def test_batchnorm_train_fwd_bwd(hpe, cuda_dev, B, H, W, C, relu, res):
     if res:
         bad = ((nchw(gout) - rr.grad).abs() > rr.grad.abs() * 2 ** -7 + 1e-6) & clear
         assert bad.float().mean() < 1e-3
+    if relu and not res:
+        # mask recomputed from z (y never read): identical results to the y-mask path
+        dz2 = torch.empty_like(zd); dbeta2, dgamma2 = f(C), f(C)
+        tr.bn_backward(nhwc16(dy), None, zd, u.mean, u.rstd, bn.weight, relu, dbeta2, dgamma2, dz2, None, u.scale, u.shift)
+        torch.cuda.synchronize()
+        assert torch.equal(dz2, dz) and torch.equal(dbeta2, dbeta) and torch.equal(dgamma2, dgamma)
 
 
 @pytest.mark.parametrize("B,H,W,C", [(4, 32, 24, 64), (2, 15, 9, 64)])
