@@ -19,8 +19,19 @@ import sys
 import threading
 import time
 
-# stdout carries exactly ONE JSON line: NCCL's own log lines (version banner, NCCL_DEBUG output) go to stderr
+# stdout carries exactly ONE JSON line.  Native libraries write their banners to fd 1 (NCCL prints "NCCL version ..." there at
+# NCCL_DEBUG=VERSION and ignores NCCL_DEBUG_FILE at that level), so fd 1 is pointed at stderr for the whole process and the
+# JSON line goes to a private duplicate of the original stdout.
 os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+sys.stdout.flush()
+_REAL_STDOUT = os.fdopen(os.dup(1), "w")
+os.dup2(2, 1)
+
+
+def emit(line: dict) -> None:
+    _REAL_STDOUT.write(json.dumps(line) + "\n")
+    _REAL_STDOUT.flush()
+
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
@@ -146,7 +157,7 @@ def run_reference(args):
         "e2e": {"value": round(ips, 3), "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # --------------------------------------------------------------------------------------------- GPU arm
@@ -342,7 +353,7 @@ def run_b200(args):
             line["cpu_baseline"] = {"value": round(ips, 3), "unit": "images/s", "cores": nthr, "kind": "port",
                                     "sample": f"3 steps x {args.cpu_batch} images of the same workload (torch fp32 ResNet-50+head on "
                                               f"{nthr} threads + numpy decode), {mean:.2f} s/step"}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -421,7 +432,7 @@ def run_train(args):
                          "note": "3x forward algorithmic FLOPs / step time; the step also contains the HBM-bound BN passes"},
             "loss": float(loss.item()), "clocks": clocks,
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         # a live captured graph that contains the NCCL all-reduce has been seen to block communicator teardown:
         # drop the graph first, and leave without the teardown once every rank is done
@@ -487,7 +498,7 @@ def run_pose(args):
             "e2e": {"value": round(B / e2e_ms * 1e3, 1), "unit": "images/s", "h2d_bytes_per_step": B * 3 * H * W * 4,
                     "d2h_bytes_per_step": 4 * B, "ms_per_step": round(e2e_ms, 4), "kept_last_step": n_kept},
             "gpu_launches": (plan.n_launches + 3) * args.steps, "clocks": clocks}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def main():
