@@ -44,16 +44,8 @@ __device__ __forceinline__ void wg_tap_offset(int kind, int t, int& dx, int& dy)
   else { dx = 0; dy = 0; }
 }
 
-// MN-major SWIZZLE_128B descriptor: 64-element MN blocks `lbo` bytes apart, 8-row K groups 1024 B apart
-__device__ __forceinline__ uint64_t make_sw128_mnmajor_desc(const void* smem, uint32_t lbo) {
-  uint64_t d = 0;
-  d |= static_cast<uint64_t>((smem_u32(smem) & 0x3FFFFu) >> 4);
-  d |= static_cast<uint64_t>(lbo >> 4) << 16;
-  d |= static_cast<uint64_t>(1024 >> 4) << 32;
-  d |= static_cast<uint64_t>(1) << 46;
-  d |= static_cast<uint64_t>(2) << 61;
-  return d;
-}
+// MN-major SWIZZLE_128B operands: 64-element MN blocks kBlkBytes apart (LBO), 8-row K groups 1024 B apart (SBO); the 64-bit
+// descriptors are assembled in the MMA warp from a per-stage low word and a constant high word
 __host__ __device__ constexpr uint32_t make_idesc_bf16_m128_mnmajor(int n) {
   return make_idesc_bf16_m128(n) | (1u << 15) | (1u << 16);
 }
