@@ -26,10 +26,10 @@ def fold_bn(weight, bias, running_mean, running_var, eps):
 
 class ConvLayer:
     def __init__(self, kind, B, H, W, Cin, Cout, stride=1, act=ACT_RELU, has_residual=False, device="cuda", desc=None,
-                 in_cstride=0, out_cstride=0, Cin2=0, stride2=1):
+                 in_cstride=0, out_cstride=0, Cin2=0, stride2=1, head2=0):
         self.device = torch.device(device)
         self.desc = desc if desc is not None else ConvDesc(kind, B, H, W, Cin, Cout, stride, act, int(has_residual),
-                                                           in_cstride, out_cstride, Cin2, stride2 if Cin2 else 0)
+                                                           in_cstride, out_cstride, Cin2, stride2 if Cin2 else 0, head2)
         kind, B, Cout = self.desc.kind, self.desc.B, self.desc.Cout
         lib = _lib.lib()
         ho, wo = C.c_int(), C.c_int()
@@ -42,6 +42,10 @@ class ConvLayer:
         self.kind, self.B, self.Cout = kind, B, Cout
         n = lib.hpe_conv_packed_weight_elems(C.byref(self.desc))
         self.w_packed = torch.zeros(n, dtype=torch.bfloat16, device=self.device)
+        self.head2 = int(self.desc.head2)
+        if self.head2:       # fused head: the final 1x1's weights (32 zero-padded rows x 256) and bias
+            self.w2_packed = torch.zeros(32 * 256, dtype=torch.bfloat16, device=self.device)
+            self.bias2 = torch.zeros(self.head2, dtype=torch.float32, device=self.device)
         self.scale = torch.ones(Cout, dtype=torch.float32, device=self.device)
         self.shift = torch.zeros(Cout, dtype=torch.float32, device=self.device)
 
@@ -54,12 +58,14 @@ class ConvLayer:
             pass
 
     def out_shape(self):
+        if self.head2:
+            return (self.B, self.head2, self.Ho, self.Wo)
         if self.kind == CONV_FINAL:
             return (self.B, self.Cout, self.Ho, self.Wo)
         return (self.B, self.Ho, self.Wo, self.Cout)
 
     def alloc_out(self):
-        dt = torch.float32 if self.kind == CONV_FINAL else torch.bfloat16
+        dt = torch.float32 if (self.kind == CONV_FINAL or self.head2) else torch.bfloat16
         return torch.empty(self.out_shape(), dtype=dt, device=self.device)
 
     def load(self, weight: torch.Tensor, scale: torch.Tensor = None, shift: torch.Tensor = None):
@@ -72,6 +78,18 @@ class ConvLayer:
             self.scale.copy_(scale.detach().to(self.device, torch.float32))
         if shift is not None:
             self.shift.copy_(shift.detach().to(self.device, torch.float32))
+        return self
+
+    def load_head2(self, weight: torch.Tensor, bias: torch.Tensor):
+        """Fused head (``head2 = K``): ``weight`` [K,256,1,1] / ``bias`` [K] of the final 1x1 conv (SURVEY App. A.1
+        ``final_layer``), applied to this layer's output tile while it is still in shared memory."""
+        w = weight.detach().to(self.device, torch.float32).contiguous()
+        fd = ConvDesc(CONV_FINAL, self.B, self.Ho, self.Wo, 256, self.head2, 1, ACT_NONE, 0, 0, 0, 0, 0, 0)
+        self.w2_packed.zero_()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().hpe_conv_pack_weight(C.byref(fd), _lib.ptr(w), _lib.ptr(self.w2_packed), _lib.stream_ptr()),
+                       "hpe_conv_pack_weight")
+        self.bias2.copy_(bias.detach().to(self.device, torch.float32))
         return self
 
     def load2(self, weight: torch.Tensor, scale: torch.Tensor, shift: torch.Tensor, weight2: torch.Tensor, scale2: torch.Tensor,
@@ -102,6 +120,15 @@ class ConvLayer:
         else:
             _lib.require_cuda(x, residual, out)
         _lib.require_cuda(x2)
+        if self.head2:
+            if out.dtype != torch.float32:
+                raise TypeError("the fused head writes float32 heatmaps")
+            with torch.cuda.device(self.device):
+                rc = _lib.lib().hpe_conv_run_head2(self.plan, _lib.ptr(x), _lib.ptr(self.w_packed), _lib.ptr(self.scale),
+                                                   _lib.ptr(self.shift), _lib.ptr(self.w2_packed), _lib.ptr(self.bias2),
+                                                   _lib.ptr(out), _lib.stream_ptr())
+            _lib.check(rc, "hpe_conv_run_head2")
+            return out
         with torch.cuda.device(self.device):
             rc = _lib.lib().hpe_conv_run2(self.plan, _lib.ptr(x), _lib.ptr(x2), _lib.ptr(self.w_packed), _lib.ptr(self.scale),
                                           _lib.ptr(self.shift), _lib.ptr(residual), _lib.ptr(out), _lib.stream_ptr())

@@ -51,7 +51,9 @@ struct ConvParams {
   int act, has_res;
   const float* scale;
   const float* shift;
-  float* hm_out;                // HPE_CONV_FINAL: fp32 NCHW heatmaps
+  float* hm_out;                // HPE_CONV_FINAL / fused head: fp32 NCHW heatmaps
+  int head2_k;                  // fused head (HEAD2): number of joints K <= 32 of the second GEMM
+  const float* bias2;           // fused head: conv bias [K]
 };
 
 struct TileCoord { int n_tile, cls, x0, y0, b0; };
@@ -90,16 +92,18 @@ __device__ __forceinline__ int kb_count(const ConvParams& p, int cls) {
 
 // NSB = epilogue staging buffers (16 KB each): 4 with a residual (they double as its prefetch ring), else 3 -- the bytes
 // saved go to a deeper operand ring, which is what bounds the deep-K layers (ring depth / hand-off round trip).
-template <int BLOCK_N, int STAGES, bool PAIR = false, int NSB = 4>
+template <int BLOCK_N, int STAGES, bool PAIR = false, int NSB = 4, bool HEAD2 = false>
 struct SmemLayout {
+  static constexpr int kW2Bytes    = HEAD2 ? 4 * 16 * 128 : 0;       // fused head: this CTA's 16 rows x 256 K of the joint weights
   static constexpr int kBBytes     = (PAIR ? BLOCK_N / 2 : BLOCK_N) * kKBlock * 2;    // a CTA of a pair holds half of B's rows
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kOffA   = 0;
   static constexpr int kOffB   = STAGES * kABytes;
   static constexpr int kOffSB  = kOffB + STAGES * kBBytes;
   static constexpr int kOffSS  = kOffSB + NSB * kSBBytes;             // float scale[kMaxBlockN], shift[kMaxBlockN]
-  static constexpr int kOffBar = kOffSS + 2 * kMaxBlockN * 4;
-  static constexpr int kNumBar = 2 * STAGES + 4 + 2 * NSB;
+  static constexpr int kOffW2  = kOffSS + 2 * kMaxBlockN * 4;         // 1024-byte aligned (all sizes above are multiples of 1 KB)
+  static constexpr int kOffBar = kOffW2 + kW2Bytes;
+  static constexpr int kNumBar = 2 * STAGES + 4 + 2 * NSB + 3;       // + w2full, s2full, d2full (fused head)
   static constexpr int kTotal  = kOffBar + kNumBar * 8 + 16;
   static constexpr int kDynamic = kTotal;             // the dynamic segment starts 1024-byte aligned (checked in the kernel)
   static_assert(kTotal <= 232448, "exceeds the 227 KB of shared memory a CTA may use");
@@ -138,7 +142,11 @@ __device__ __forceinline__ int work_tile(const ConvParams& p, int work, int rank
 // PAIR: cta_group::2 -- a 2-CTA cluster computes a 256 x BLOCK_N tile with ONE tcgen05.mma stream issued by the leader:
 // each CTA loads its own 128-pixel A brick and HALF of the weight tile, so a CTA ingests 32 KB instead of 48 KB per k-block
 // (BLOCK_N = 256) through the L2->SM path that bounds the deep-K layers.  Each CTA drains its own 128 TMEM lanes.
-template <int BLOCK_N, int STAGES, int ACT, bool RES, bool FINAL, bool PAIR = false>
+// HEAD2 (pair kernels, Cout == BLOCK_N == 256): the layer's bf16 output tile is NOT stored; its four staged 64-channel chunks are
+// exactly the SWIZZLE_128B K-major A operand of a second GEMM against the K-joint 1x1 weights (16 rows per CTA, resident in
+// smem), accumulated into the first 32 columns of the accumulator just drained, and written as fp32 NCHW heatmaps: deconv3 +
+// final_layer of the App. A.1 head in one kernel (saves writing and re-reading the 403 MB deconv3 output at B=256).
+template <int BLOCK_N, int STAGES, int ACT, bool RES, bool FINAL, bool PAIR = false, bool HEAD2 = false>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
                  const __grid_constant__ CUtensorMap tmW, const __grid_constant__ OutMaps tmOut,
@@ -146,9 +154,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   // staging buffer q % kNumSB is rewritten by chunk q; the leader confirms "stores <= j-2 have left smem" at the start of
   // chunk j and everyone meets at chunk j's named barrier, so at the start of chunk q only stores <= q-3 are known done:
   // 3 buffers is the minimum.  With a residual the buffers double as its prefetch ring (4, lead 2).
-  constexpr int kNumSB = FINAL ? 0 : (RES ? 4 : 3);      // the fp32 heatmap epilogue stores from registers: all smem to the ring
+  static_assert(!HEAD2 || (PAIR && BLOCK_N == 256 && !RES && !FINAL), "fused head: pair kernel, 256 channels, no residual");
+  constexpr int kNumSB = FINAL ? 0 : ((RES || HEAD2) ? 4 : 3);      // the fp32 heatmap epilogue stores from registers: all smem to the ring
   constexpr int kResLead = 2;                   // the residual of chunk q + 2 is requested while chunk q is processed
-  using L = SmemLayout<BLOCK_N, STAGES, PAIR, kNumSB>;
+  using L = SmemLayout<BLOCK_N, STAGES, PAIR, kNumSB, HEAD2>;
   static_assert(!PAIR || (BLOCK_N % 32 == 0 && !FINAL), "pair kernels: N multiple of 32, bf16 NHWC epilogue");
   constexpr int kChunks   = BLOCK_N >= 64 ? BLOCK_N / 64 : 1;
   constexpr int kTmemCols = 2 * BLOCK_N <= 32 ? 32 : (2 * BLOCK_N <= 64 ? 64 : (2 * BLOCK_N <= 128 ? 128 : (2 * BLOCK_N <= 256 ? 256 : 512)));  // power of two
@@ -172,6 +181,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint64_t* tempty_bar = bars + 2 * STAGES + 2;
   uint64_t* sbfull_bar = bars + 2 * STAGES + 4;
   uint64_t* sbempty_bar = bars + 2 * STAGES + 4 + kNumSB;
+  uint64_t* w2full_bar = bars + 2 * STAGES + 4 + 2 * kNumSB;       // fused head: joint weights landed (own CTA)
+  uint64_t* s2full_bar = w2full_bar + 1;                           // fused head: both CTAs staged their A' tile (leader's barrier)
+  uint64_t* d2full_bar = w2full_bar + 2;                           // fused head: second GEMM done (multicast commit)
+  uint8_t*  sW2 = smem + L::kOffW2;
   uint32_t* tmem_slot  = reinterpret_cast<uint32_t*>(bars + L::kNumBar);
 
   const int warp = threadIdx.x >> 5;
@@ -185,6 +198,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], PAIR ? 2 : 1); mbar_init(&empty_bar[s], 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], (PAIR ? 2 : 1) * kEpiThreads / 32); }
     for (int b = 0; b < kNumSB; ++b) { mbar_init(&sbfull_bar[b], 1); mbar_init(&sbempty_bar[b], 1); }
+    mbar_init(w2full_bar, 1); mbar_init(s2full_bar, 2); mbar_init(d2full_bar, 1);
     fence_mbar_init();
   }
   if (warp == 1) {
@@ -271,6 +285,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
   } else if (warp == 2) {
     // ===================== residual producer =====================
+    if (HEAD2 && lane == 0) {        // fused head: this CTA's 16 joint-weight rows (4 k-blocks of 16 x 128 B), loaded once
+      mbar_arrive_expect_tx(w2full_bar, L::kW2Bytes);
+      for (int kb = 0; kb < 4; ++kb) tma_load_2d(sW2 + kb * 2048, &tmRes, w2full_bar, kb * kKBlock, rank * 16);
+    }
     if (RES && lane == 0) {
       int r = 0;
       for (int work = work0; work < p.num_tiles; work += wstep) {
@@ -337,9 +355,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (lane == 0) mbar_arrive(&tempty_bar[acc]);
       } else {
         for (int c = 0; c < kChunks; ++c, ++q) {
-          const int sb = q % kNumSB;
+          const int sb = HEAD2 ? c : q % kNumSB;                    // fused head: the tile's four chunks stay staged (A' operand)
           const uint32_t stg = smem_u32(sSB + sb * kSBBytes);
-          if (leader) {
+          if (!HEAD2 && leader) {
             bulk_wait_read<1>();                                    // stores <= q-2 have left shared memory
             if (RES) mbar_arrive(&sbempty_bar[(q + kResLead) % kNumSB]);   // hand the buffer of chunk q+2 to warp 2
           }
@@ -347,7 +365,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           tmem_ld_x32(taddr + c * 64 + half * 32, v);
           if (RES) mbar_wait(&sbfull_bar[sb], (q / kNumSB) & 1);
           tmem_ld_wait();
-          if (c == kChunks - 1) {                                   // accumulator drained -> MMA may reuse it
+          if (!HEAD2 && c == kChunks - 1) {                         // accumulator drained -> MMA may reuse it
             tc_fence_before();
             __syncwarp();
             if (lane == 0) {
@@ -387,16 +405,66 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
             sts_v4(slot, pk);
           }
-          fence_proxy_async_smem();                                  // generic-proxy writes -> visible to TMA
-          named_bar_sync(1, kEpiThreads);
-          if (leader) {
-            tma_store_4d(&tmOut.m[t.cls], sSB + sb * kSBBytes, t.n_tile * BLOCK_N + c * 64, t.x0, t.y0, t.b0);
-            bulk_commit();
+          if constexpr (HEAD2) {
+            if (c == kChunks - 1) {                                  // all four chunks staged: one fence + barrier per tile
+              fence_proxy_async_smem();                              // generic-proxy writes -> visible to the tensor core
+              tc_fence_before();                                     // our tcgen05.ld of this accumulator precede its reuse below
+              named_bar_sync(1, kEpiThreads);
+            }
+          } else {
+            fence_proxy_async_smem();                                // generic-proxy writes -> visible to TMA
+            named_bar_sync(1, kEpiThreads);
+            if (leader) {
+              tma_store_4d(&tmOut.m[t.cls], sSB + sb * kSBBytes, t.n_tile * BLOCK_N + c * 64, t.x0, t.y0, t.b0);
+              bulk_commit();
+            }
           }
+        }
+        if constexpr (HEAD2) {
+          // ---- second GEMM: heatmaps[256 px (both CTAs)][32] = A'[256][256] * W2[32][256]^T into columns 0-31 of `acc` ----
+          if (leader) {
+            if (it == 0) mbar_wait(w2full_bar, 0);                   // own joint weights landed (implied for the peer by its arrive)
+            mbar_arrive_cluster_release(mapa_shared(smem_u32(s2full_bar), 0));
+            if (rank == 0) {
+              mbar_wait_cluster_acquire(s2full_bar, it & 1);         // both CTAs staged their A' tile
+              tc_fence_after();
+              constexpr uint32_t kIdesc2 = make_idesc_bf16_m256(32);
+              const uint32_t tmem_d2 = tmem_base + acc * BLOCK_N;
+#pragma unroll
+              for (int c = 0; c < 4; ++c) {
+                const uint64_t adesc = make_sw128_kmajor_desc(sSB + c * kSBBytes);
+                const uint64_t bdesc = make_sw128_kmajor_desc(sW2 + c * 2048);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) umma_bf16_2sm(tmem_d2, adesc + 2 * k, bdesc + 2 * k, kIdesc2, (c | k) != 0);
+              }
+              umma_commit_2sm(d2full_bar, 3);
+            }
+          }
+          mbar_wait(d2full_bar, it & 1);
+          tc_fence_after();
+          if (half == 0) {
+            uint32_t v[32];
+            tmem_ld_x32(taddr, v);
+            tmem_ld_wait();
+            const int xi = row % p.tw, yi = (row / p.tw) % p.th, bi = row / (p.tw * p.th);
+            const int x = t.x0 + xi, y = t.y0 + yi, b = t.b0 + bi;
+            if (x < p.Wo && y < p.Ho && b < p.B) {
+              const int up = p.n_classes == 4 ? 2 : 1;               // deconv: tile = one parity class of the 2x-upsampled output
+              const int oy = up * y + (up == 2 ? (t.cls >> 1) : 0), ox = up * x + (up == 2 ? (t.cls & 1) : 0);
+              const size_t plane = static_cast<size_t>(up * p.Ho) * (up * p.Wo);
+              float* dst = p.hm_out + static_cast<size_t>(b) * p.head2_k * plane + static_cast<size_t>(oy) * (up * p.Wo) + ox;
+#pragma unroll
+              for (int e = 0; e < 32; ++e)
+                if (e < p.head2_k) dst[e * plane] = __uint_as_float(v[e]) + __ldg(p.bias2 + e);
+            }
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(mapa_shared(smem_u32(&tempty_bar[acc]), 0));     // accumulator free (leader's barrier)
         }
       }
     }
-    if (leader) bulk_wait_all();
+    if (!HEAD2 && leader) bulk_wait_all();
   }
 
   tc_fence_before();
@@ -529,7 +597,7 @@ struct hpe_conv_plan {
   size_t smem;
   CUtensorMap tmA, tmW, tmRes;
   OutMaps tmOut;
-  const void *x, *x2, *w, *res;
+  const void *x, *x2, *w, *res, *w2;
   void* y;
   CUtensorMap tmA2;
   const void* fn;
@@ -559,6 +627,12 @@ static int desc_check(const hpe_conv_desc* d, const char* fn) {
     return HPE_OK;
   }
   if (d->Cin % 8) return fail(HPE_EUNSUPPORTED, "%s: Cin=%d must be a multiple of 8", fn, d->Cin);
+  if (d->head2) {
+    if (d->head2 < 0 || d->head2 > 32) return fail(HPE_EUNSUPPORTED, "%s: the fused head supports at most 32 joints (got %d)", fn, d->head2);
+    const bool kind_ok = d->kind == HPE_CONV_DECONV4 || ((d->kind == HPE_CONV_1x1 || d->kind == HPE_CONV_3x3) && d->stride == 1);
+    if (!kind_ok || d->Cout != 256 || d->has_residual || d->out_cstride || d->Cin2 || d->act != HPE_ACT_RELU)
+      return fail(HPE_EUNSUPPORTED, "%s: the fused head needs a ReLU deconv / stride-1 conv with Cout = 256, no residual, no second input", fn);
+  }
   if (d->Cin2) {
     if (d->kind != HPE_CONV_1x1 || d->stride != 1) return fail(HPE_EUNSUPPORTED, "%s: a second input needs a 1x1 stride-1 main conv", fn);
     if (d->Cin2 < 0 || d->Cin2 % 8) return fail(HPE_EUNSUPPORTED, "%s: Cin2=%d must be a positive multiple of 8", fn, d->Cin2);
@@ -717,7 +791,7 @@ extern "C" int hpe_conv_dgrad_desc(const hpe_conv_desc* f, hpe_conv_desc* g) {
   if (rc) return rc;
   *g = *f;
   g->H = Ho; g->W = Wo; g->Cin = f->Cout; g->Cout = f->Cin; g->stride = 1; g->act = HPE_ACT_NONE; g->has_residual = 0;
-  g->Cin2 = 0; g->stride2 = 0;
+  g->Cin2 = 0; g->stride2 = 0; g->head2 = 0;
   if (f->Cin2) return fail(HPE_EUNSUPPORTED, "hpe_conv_dgrad_desc: fused two-input layers are inference-only");
   switch (f->kind) {
     case HPE_CONV_1x1:     g->kind = f->stride == 2 ? HPE_CONV_DGRAD1x1S2 : HPE_CONV_1x1; break;
@@ -771,7 +845,8 @@ static ConvKernelFn pick_kernel_pair(int act, bool res, size_t* smem) {
 }
 
 // ring depths: as many stages as fit beside the staging buffers in the 227 KB a CTA may use
-static ConvKernelFn pick_kernel(int block_n, int act, bool res, bool fin, bool pair, size_t* smem) {
+static ConvKernelFn pick_kernel(int block_n, int act, bool res, bool fin, bool pair, bool head2, size_t* smem) {
+  if (head2) { *smem = SmemLayout<256, 4, true, 4, true>::kDynamic; return conv_gemm_kernel<256, 4, HPE_ACT_RELU, false, false, true, true>; }
   if (pair && block_n == 256) return pick_kernel_pair<256, 5, 5>(act, res, smem);       // 32 KB stages (A + half of B)
   if (pair) return pick_kernel_pair<128, 7, 6>(act, res, smem);                         // 24 KB stages
   switch (block_n) {
@@ -804,6 +879,7 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
   }
   p.kc_per_tap = d->kind == HPE_CONV_STEM7x7 ? 1 : cin_padded(d) / 64;
   p.kc2 = (d->Cin2 + 63) / 64; p.in_stride2 = d->Cin2 ? d->stride2 : 1;
+  p.head2_k = d->head2; p.bias2 = nullptr;
   p.n_classes = is_class_strided(d->kind) ? 4 : 1;
   // tile grid extent: deconv-like tiles walk the INPUT-resolution grid of one parity class
   const bool up2 = is_class_strided(d->kind) || d->kind == HPE_CONV_DGRAD1x1S2;
@@ -832,6 +908,7 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
     const char* e128 = getenv("HPE_B200_PAIR128");
     const long long m_tiles = (long long)p.tiles_x * p.tiles_y * p.tiles_b;
     pl->pair = !(e && e[0] == '0') && (pl->block_n == 256 || (pl->block_n == 128 && e128 && e128[0] == '1')) && d->kind != HPE_CONV_FINAL && m_tiles >= 2 && !halo_eligible(d, pl->Ho, pl->Wo);
+    if (d->head2 && !pl->pair) { delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: the fused head runs on the cta_group::2 kernel only (needs >= 2 M tiles, HPE_B200_PAIR != 0)"); }
     if (pl->pair) {
       const long long np = (m_tiles + 1) / 2 * p.n_tiles_n * p.n_classes;
       p.num_tiles = (int)np;
@@ -839,7 +916,7 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
       pl->grid = 2 * (int)(np < max_clusters ? np : max_clusters);
     }
   }
-  pl->fn = (const void*)pick_kernel(pl->block_n, d->act, p.has_res != 0, d->kind == HPE_CONV_FINAL, pl->pair != 0, &pl->smem);
+  pl->fn = (const void*)pick_kernel(pl->block_n, d->act, p.has_res != 0, d->kind == HPE_CONV_FINAL, pl->pair != 0, d->head2 != 0, &pl->smem);
   if (!pl->fn) { delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: no kernel for BLOCK_N=%d", pl->block_n); }
   {
     cudaError_t e = cudaFuncSetAttribute((const void*)pl->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem);
@@ -864,7 +941,7 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
     }
     pl->grid = 2 * (p.num_tiles < max_clusters ? p.num_tiles : max_clusters);
   }
-  pl->x = pl->x2 = pl->w = pl->res = nullptr; pl->y = nullptr;
+  pl->x = pl->x2 = pl->w = pl->res = pl->w2 = nullptr; pl->y = nullptr;
   pl->halo_taps_y = pl->halo_boxes = 0;
   if (halo_eligible(d, pl->Ho, pl->Wo)) {
     const bool stem = d->kind == HPE_CONV_STEM7x7;
@@ -890,7 +967,8 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
 
 extern "C" void hpe_conv_plan_destroy(hpe_conv_plan* plan) { delete plan; }
 
-static int encode_plan_maps(hpe_conv_plan* pl, const void* x, const void* x2, const void* w, const void* res, void* y) {
+static int encode_plan_maps(hpe_conv_plan* pl, const void* x, const void* x2, const void* w, const void* res, void* y,
+                            const void* w2 = nullptr) {
   const hpe_conv_desc& d = pl->d;
   const ConvParams& p = pl->p;
   int rc;
@@ -938,7 +1016,16 @@ static int encode_plan_maps(hpe_conv_plan* pl, const void* x, const void* x2, co
     if (rc) return rc;
     pl->w = w;
   }
-  if (d.kind != HPE_CONV_FINAL && y != pl->y) {
+  if (d.head2 && w2 != pl->w2) {               // fused head: joint weights [32][256] bf16 (rows >= K zero), 16 rows per CTA
+    HPE_CHECK_ARG(w2 && ((uintptr_t)w2 & 15) == 0, "hpe_conv_run_head2: w2 must be non-null and 16-byte aligned");
+    const uint64_t dims[2] = {256, 32};
+    const uint64_t str[1] = {256 * 2};
+    const uint32_t box[2] = {64, 16};
+    rc = encode_map(&pl->tmRes, w2, 2, dims, str, box, ones, "head2 W");
+    if (rc) return rc;
+    pl->w2 = w2;
+  }
+  if (d.kind != HPE_CONV_FINAL && !d.head2 && y != pl->y) {
     HPE_CHECK_ARG(((uintptr_t)y & 15) == 0, "hpe_conv_run: y must be 16-byte aligned");
     const uint64_t C = d.Cout, P = d.out_cstride ? d.out_cstride : d.Cout;
     const uint32_t box[4] = {64, (uint32_t)p.tw, (uint32_t)p.th, (uint32_t)p.nb};
@@ -981,8 +1068,24 @@ extern "C" int hpe_conv_run(hpe_conv_plan* pl, const void* x, const void* w_pack
   return hpe_conv_run2(pl, x, nullptr, w_packed, scale, shift, residual, y, stream);
 }
 
+static int conv_launch(hpe_conv_plan* pl, const void* x, const void* x2, const void* w_packed, const float* scale,
+                       const float* shift, const void* residual, void* y, const void* w2, const float* bias2, void* stream);
+
 extern "C" int hpe_conv_run2(hpe_conv_plan* pl, const void* x, const void* x2, const void* w_packed, const float* scale,
                              const float* shift, const void* residual, void* y, void* stream) {
+  HPE_CHECK_ARG(pl && !pl->d.head2, "hpe_conv_run: the plan has a fused head; use hpe_conv_run_head2");
+  return conv_launch(pl, x, x2, w_packed, scale, shift, residual, y, nullptr, nullptr, stream);
+}
+
+extern "C" int hpe_conv_run_head2(hpe_conv_plan* pl, const void* x, const void* w_packed, const float* scale, const float* shift,
+                                  const void* w2_packed, const float* bias2, float* heatmaps, void* stream) {
+  HPE_CHECK_ARG(pl && pl->d.head2, "hpe_conv_run_head2: the plan has no fused head (desc.head2 = 0)");
+  HPE_CHECK_ARG(w2_packed && bias2 && heatmaps, "hpe_conv_run_head2: null pointer");
+  return conv_launch(pl, x, nullptr, w_packed, scale, shift, nullptr, heatmaps, w2_packed, bias2, stream);
+}
+
+static int conv_launch(hpe_conv_plan* pl, const void* x, const void* x2, const void* w_packed, const float* scale,
+                       const float* shift, const void* residual, void* y, const void* w2, const float* bias2, void* stream) {
   HPE_CHECK_ARG(pl && x && w_packed && scale && shift && y, "hpe_conv_run: null pointer");
   HPE_CHECK_ARG((pl->d.Cin2 != 0) == (x2 != nullptr), "hpe_conv_run2: x2 must be given exactly when the plan has a second input (Cin2=%d)", pl->d.Cin2);
   HPE_CHECK_ARG((((uintptr_t)scale | (uintptr_t)shift) & 15) == 0, "hpe_conv_run: scale/shift must be 16-byte aligned");
@@ -990,7 +1093,7 @@ extern "C" int hpe_conv_run2(hpe_conv_plan* pl, const void* x, const void* x2, c
     return fail(HPE_EUNSUPPORTED, "hpe_conv_run: the strided-store kinds have no residual input");
   if (pl->d.kind == HPE_CONV_DGRAD1x1S2)      // odd rows/columns of dx receive no gradient
     HPE_CUDA_OK(cudaMemsetAsync(y, 0, (size_t)pl->d.B * pl->Ho * pl->Wo * pl->d.Cout * 2, (cudaStream_t)stream));
-  int rc = encode_plan_maps(pl, x, x2, w_packed, residual, y);
+  int rc = encode_plan_maps(pl, x, x2, w_packed, residual, y, w2);
   if (rc) return rc;
   if (pl->halo_taps_y) {
     pl->hp.scale = scale; pl->hp.shift = shift;
@@ -999,9 +1102,10 @@ extern "C" int hpe_conv_run2(hpe_conv_plan* pl, const void* x, const void* x2, c
   }
   ConvParams p = pl->p;
   p.scale = scale; p.shift = shift;
-  p.hm_out = pl->d.kind == HPE_CONV_FINAL ? (float*)y : nullptr;
-  if (!p.has_res) pl->tmRes = pl->tmA;      // unused, but must be a valid object to copy
-  if (pl->d.kind == HPE_CONV_FINAL) for (int c = 0; c < 4; ++c) pl->tmOut.m[c] = pl->tmA;
+  p.hm_out = (pl->d.kind == HPE_CONV_FINAL || pl->d.head2) ? (float*)y : nullptr;
+  p.bias2 = bias2;
+  if (!p.has_res && !pl->d.head2) pl->tmRes = pl->tmA;      // unused, but must be a valid object to copy
+  if (pl->d.kind == HPE_CONV_FINAL || pl->d.head2) for (int c = 0; c < 4; ++c) pl->tmOut.m[c] = pl->tmA;
   if (!pl->d.Cin2) pl->tmA2 = pl->tmA;      // unused, but must be a valid object to copy
   void* args[6] = {&pl->tmA, &pl->tmA2, &pl->tmW, &pl->tmOut, &pl->tmRes, &p};
   cudaLaunchConfig_t cfg = {};

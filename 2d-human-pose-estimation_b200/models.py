@@ -198,7 +198,7 @@ class _ForwardPlan:
 
         def add(name, layer, src, dst, res=None, src2=None):
             self.named[name] = layer
-            buf(dst, layer.out_shape(), torch.float32 if layer.kind == CONV_FINAL else torch.bfloat16)
+            buf(dst, layer.out_shape(), torch.float32 if (layer.kind == CONV_FINAL or layer.head2) else torch.bfloat16)
             self.ops.append((layer, src, res, dst, src2))
 
         self.s2d = preprocess(torch.zeros(B, 3, H, W, device=dev))
@@ -225,10 +225,25 @@ class _ForwardPlan:
                     add(pre + ".conv3", ConvLayer(CONV_1x1, B, h, w, p, 4 * p, 1, ACT_RELU, True, dev), pre + ".t2", pre + ".out", sc)
                 cur, cin = pre + ".out", 4 * p
         self.features_key = cur
+        # last deconv stage + final_layer in one kernel (the 256-channel deconv3 output never leaves shared memory) when the
+        # joints fit one 32-column second GEMM and the layer runs on the CTA-pair kernel
+        self.fused_head = None
         for d, idx in enumerate((0, 3, 6)):
+            layer = None
+            if d == 2 and K <= 32 and os.environ.get("HPE_B200_FUSE_HEAD", "1") != "0":
+                try:
+                    layer = ConvLayer(CONV_DECONV4, B, h, w, cin, 256, 2, ACT_RELU, False, dev, head2=K)
+                    self.fused_head = f"deconv_layers.{idx}"
+                except RuntimeError:
+                    layer = None          # too few tiles for a CTA pair (tiny batch): separate layers
+            if layer is not None:
+                add(f"deconv_layers.{idx}", layer, cur, "heatmaps")
+                h, w = 2 * h, 2 * w
+                break
             add(f"deconv_layers.{idx}", ConvLayer(CONV_DECONV4, B, h, w, cin, 256, 2, ACT_RELU, False, dev), cur, f"deconv{d}")
             cur, cin, h, w = f"deconv{d}", 256, 2 * h, 2 * w
-        add("final_layer", ConvLayer(CONV_FINAL, B, h, w, 256, K, 1, ACT_NONE, False, dev), cur, "heatmaps")
+        if self.fused_head is None:
+            add("final_layer", ConvLayer(CONV_FINAL, B, h, w, 256, K, 1, ACT_NONE, False, dev), cur, "heatmaps")
         self.bufs["s2d"] = self.s2d
         self.weights_version = -1
         self.graph = None
@@ -257,6 +272,8 @@ class _ForwardPlan:
             else:
                 bn = mods[name.replace("conv", "bn")]
             scale, shift = fold_bn(bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps)
+            if name == self.fused_head:
+                layer.load_head2(mods["final_layer"].weight, mods["final_layer"].bias)
             if name in self.fused_shortcut:
                 ds = self.fused_shortcut[name]
                 bn2 = mods[ds + ".1"]

@@ -142,6 +142,10 @@ typedef struct hpe_conv_desc {
                                so the shortcut tensor is never written or re-read.  Both BN scales are folded into the weights
                                by the caller (scale = 1, shift = shift3 + shift_ds). */
   int stride2;              /* stride of the second conv: 1 or 2 */
+  int head2;                /* K != 0 (K <= 32; ReLU HPE_CONV_DECONV4 or stride-1 1x1/3x3 with Cout = 256): the layer's bf16 output is
+                               NOT written; a second GEMM against the K-joint 1x1 weights runs on the tile while it is still in shared
+                               memory and fp32 NCHW heatmaps [B,K,Ho,Wo] are written instead -- the last deconv stage + final_layer of
+                               the App. A.1 head in one kernel.  Run with hpe_conv_run_head2. */
 } hpe_conv_desc;
 /* Channel counts: Cin and Cout must be multiples of 8 (16-byte pixels); partial 64-channel blocks are zero-filled by TMA. */
 
@@ -159,6 +163,10 @@ int  hpe_conv_run(hpe_conv_plan* plan, const void* x, const void* w_packed,
 int  hpe_conv_pack_weight2(const hpe_conv_desc* desc, const float* w_torch, const float* w2_torch, void* w_packed, void* stream);
 int  hpe_conv_run2(hpe_conv_plan* plan, const void* x, const void* x2, const void* w_packed,
                    const float* scale, const float* shift, const void* residual, void* y, void* stream);
+/* fused-head variant (desc.head2 = K): w2_packed = the final 1x1 weights packed with hpe_conv_pack_weight (kind HPE_CONV_FINAL,
+ * Cin 256, Cout K) into a ZERO-initialised buffer of 32*256 bf16; bias2 [K] f32; heatmaps [B,K,Ho,Wo] f32 NCHW */
+int  hpe_conv_run_head2(hpe_conv_plan* plan, const void* x, const void* w_packed, const float* scale, const float* shift,
+                        const void* w2_packed, const float* bias2, float* heatmaps, void* stream);
 /* output spatial size of the layer */
 int  hpe_conv_out_hw(const hpe_conv_desc* desc, int* Ho, int* Wo);
 

@@ -142,6 +142,32 @@ def test_deconv4x4s2(hpe, cuda_dev, B, H, W, Cin):
     check(nchw(y), ref, "deconv")
 
 
+@pytest.mark.parametrize("B,H,W,Cin,K", [(4, 32, 24, 256, 17), (3, 10, 6, 256, 17), (4, 8, 6, 2048, 32), (5, 16, 12, 64, 1)])
+def test_deconv_with_fused_final_head(hpe, cuda_dev, B, H, W, Cin, K):
+    """deconv (+BN+ReLU) and the K-joint final 1x1 in ONE kernel (desc.head2): the bf16 deconv output never leaves shared memory.
+    Reference = the two separate layers' math: fp32 deconv -> BN -> ReLU -> round to bf16 -> 1x1 conv + bias."""
+    from importlib import import_module
+    conv = import_module("2d-human-pose-estimation_b200.conv")
+    g = torch.Generator().manual_seed(12)
+    x = make(g, B, Cin, H, W); w = make(g, Cin, 256, 4, 4, s=(4 * Cin) ** -0.5)
+    scale = torch.rand(256, generator=g) + 0.5; shift = torch.randn(256, generator=g) * 0.1
+    wf = make(g, K, 256, 1, 1, s=1 / 16); bias = torch.randn(K, generator=g) * 0.1
+    mid = torch.relu(F.conv_transpose2d(x, w, stride=2, padding=1) * scale[None, :, None, None] + shift[None, :, None, None])
+    ref = F.conv2d(r16(mid), wf, bias)
+    fused = conv.ConvLayer(conv.CONV_DECONV4, B, H, W, Cin, 256, 2, 1, False, head2=K).load(w, scale, shift).load_head2(wf, bias)
+    hm = fused(nhwc(x))
+    torch.cuda.synchronize()
+    assert tuple(hm.shape) == (B, K, 2 * H, 2 * W) and hm.dtype == torch.float32
+    # the separate layers through the same library: identical bf16 intermediate, so only fp32 accumulation order differs
+    d3 = conv.ConvLayer(conv.CONV_DECONV4, B, H, W, Cin, 256, 2, 1, False).load(w, scale, shift)
+    fin = conv.ConvLayer(conv.CONV_FINAL, B, 2 * H, 2 * W, 256, K, 1, 0, False).load(wf, torch.ones(K), bias)
+    hm2 = fin(d3(nhwc(x)))
+    torch.cuda.synchronize()
+    assert (hm - hm2).abs().max() <= 1e-5 * hm2.abs().max() + 1e-6
+    # vs PyTorch: the bf16 rounding of the intermediate may differ by one ulp where the fp32 accumulation order differs
+    assert (hm.cpu() - ref).abs().max() <= 2e-3 * ref.abs().max() + 1e-4
+
+
 @pytest.mark.parametrize("B,H,W,K", [(4, 64, 48, 17), (2, 64, 48, 133), (3, 10, 7, 17), (2, 96, 72, 17)])
 def test_final_1x1_heatmaps(hpe, cuda_dev, B, H, W, K):
     from importlib import import_module
@@ -160,6 +186,10 @@ def test_final_1x1_heatmaps(hpe, cuda_dev, B, H, W, K):
 def test_conv_rejects_unsupported(hpe, cuda_dev):
     from importlib import import_module
     conv = import_module("2d-human-pose-estimation_b200.conv")
+    with pytest.raises(RuntimeError, match="fused head"):      # a single M tile cannot form a CTA pair
+        conv.ConvLayer(conv.CONV_DECONV4, 1, 8, 6, 256, 256, 2, 1, False, head2=17)
+    with pytest.raises(RuntimeError, match="32 joints"):
+        conv.ConvLayer(conv.CONV_DECONV4, 4, 8, 6, 256, 256, 2, 1, False, head2=133)
     with pytest.raises(RuntimeError, match="multiple of 8"):
         conv.ConvLayer(conv.CONV_1x1, 1, 8, 8, 44, 64)
     with pytest.raises(RuntimeError, match="stride"):
