@@ -874,6 +874,7 @@ static ConvKernelFn pick_kernel_pair(int act, bool res, size_t* smem) {
 static ConvKernelFn pick_kernel(int block_n, int act, bool res, bool fin, bool pair, bool head2, size_t* smem) {
   if (head2) { *smem = SmemLayout<256, 4, true, 4, true>::kDynamic; return conv_gemm_kernel<256, 4, HPE_ACT_RELU, false, false, true, true>; }
   if (pair && block_n == 256) return pick_kernel_pair<256, 5, 5>(act, res, smem);       // 32 KB stages (A + half of B)
+  if (pair && block_n == 192) return pick_kernel_pair<192, 6, 5>(act, res, smem);       // 28 KB stages (ConvNeXt C = 192/384/768)
   if (pair) return pick_kernel_pair<128, 7, 6>(act, res, smem);                         // 24 KB stages
   switch (block_n) {
     case 32:  return pick_kernel_bn<32, 6, 6, 11>(act, res, fin, smem);     // 20 KB stages (FINAL only)
@@ -932,8 +933,9 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
     // 128-wide tiles: opt-in only (HPE_B200_PAIR128=1) -- measured slower (layer2 3x3 128->128: 74 -> 88 us): their 24 KB
     // stages hold only 256 cycles of MMA work, so the longer cross-CTA hand-off outweighs the two extra ring stages
     const char* e128 = getenv("HPE_B200_PAIR128");
+    const char* e192 = getenv("HPE_B200_PAIR192");
     const long long m_tiles = (long long)p.tiles_x * p.tiles_y * p.tiles_b;
-    pl->pair = !(e && e[0] == '0') && (pl->block_n == 256 || (pl->block_n == 128 && e128 && e128[0] == '1')) && d->kind != HPE_CONV_FINAL && m_tiles >= 2 && !halo_eligible(d, pl->Ho, pl->Wo);
+    pl->pair = !(e && e[0] == '0') && (pl->block_n == 256 || (pl->block_n == 192 && !(e192 && e192[0] == '0')) || (pl->block_n == 128 && e128 && e128[0] == '1')) && d->kind != HPE_CONV_FINAL && m_tiles >= 2 && !halo_eligible(d, pl->Ho, pl->Wo);
     if (d->head2 && !pl->pair) { delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: the fused head runs on the cta_group::2 kernel only (needs >= 2 M tiles, HPE_B200_PAIR != 0)"); }
     if (pl->pair) {
       const long long np = (m_tiles + 1) / 2 * p.n_tiles_n * p.n_classes;
