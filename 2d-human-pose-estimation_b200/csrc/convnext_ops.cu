@@ -178,21 +178,38 @@ dwconv7_tiled_kernel(const __nv_bfloat16* __restrict__ x, int in_pitch, const fl
   const int ty = t % tiles_y; const int b = t / tiles_y;
   const int x0 = tx * tw, y0 = ty * th, c0 = slice * kDtSlice;
   const int pw = tw + 6, ph = th + 6;
-  // stage: 8 x (8 channels = 16 B) per pixel; 4 independent loads in flight per thread
-  const int n_items = ph * pw * 8;
-  for (int i0 = threadIdx.x; i0 < n_items; i0 += 4 * blockDim.x) {
-    uint4 v[4];
+  // filter weights first: their global loads overlap the tile staging below instead of adding a latency round trip after it
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const int ch = c0 + 2 * lane;
+  const bool chok = ch < C;
+  float2 w[49];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
+  for (int k = 0; k < 49; ++k) w[k] = chok ? __ldg(reinterpret_cast<const float2*>(wt + static_cast<size_t>(k) * C + ch)) : make_float2(0.f, 0.f);
+  const float2 bs = chok ? __ldg(reinterpret_cast<const float2*>(bias + ch)) : make_float2(0.f, 0.f);
+  // stage: 8 x (8 channels = 16 B) per pixel; 8 independent loads in flight per thread (a 22 x 18 tile is ~16 loads per thread:
+  // the staging phase is a chain of global-load round trips and was as long as the FMA phase with 4 in flight)
+  constexpr int kStageU = 8;
+  const int n_items = ph * pw * 8;
+  // (row, col) of a thread's item advance by blockDim / 8 pixels per step: tracked incrementally -- the two integer divisions
+  // per item were ~40 of the staging loop's ~60 instructions (ncu: only 52 % of the kernel's instructions were FFMAs)
+  const int ppstep = blockDim.x >> 3;               // pixels per step (blockDim is a multiple of 32)
+  int srow = (threadIdx.x >> 3) / pw, scol = (threadIdx.x >> 3) % pw;
+  const int sc = c0 + (threadIdx.x & 7) * 8;
+  const __nv_bfloat16* xb = x + static_cast<size_t>(b) * H * W * in_pitch + sc;
+  for (int i0 = threadIdx.x; i0 < n_items; i0 += kStageU * blockDim.x) {
+    uint4 v[kStageU];
+#pragma unroll
+    for (int j = 0; j < kStageU; ++j) {
       const int i = i0 + j * blockDim.x;
-      const int q = i & 7, pix = i >> 3;
-      const int iy = y0 - 3 + pix / pw, ix = x0 - 3 + pix % pw, c = c0 + q * 8;
+      const int iy = y0 - 3 + srow, ix = x0 - 3 + scol;
       v[j] = make_uint4(0u, 0u, 0u, 0u);
-      if (i < n_items && iy >= 0 && iy < H && ix >= 0 && ix < W && c < C)
-        v[j] = __ldg(reinterpret_cast<const uint4*>(x + ((static_cast<size_t>(b) * H + iy) * W + ix) * in_pitch + c));
+      if (i < n_items && iy >= 0 && iy < H && ix >= 0 && ix < W && sc < C)
+        v[j] = __ldg(reinterpret_cast<const uint4*>(xb + (static_cast<size_t>(iy) * W + ix) * in_pitch));
+      scol += ppstep;
+      while (scol >= pw) { scol -= pw; ++srow; }
     }
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
+    for (int j = 0; j < kStageU; ++j) {
       const int i = i0 + j * blockDim.x;
       if (i < n_items) {
         float f[8]; unpack8(v[j], f);
@@ -201,13 +218,6 @@ dwconv7_tiled_kernel(const __nv_bfloat16* __restrict__ x, int in_pitch, const fl
       }
     }
   }
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-  const int ch = c0 + 2 * lane;
-  const bool chok = ch < C;
-  float2 w[49];
-#pragma unroll
-  for (int k = 0; k < 49; ++k) w[k] = chok ? __ldg(reinterpret_cast<const float2*>(wt + static_cast<size_t>(k) * C + ch)) : make_float2(0.f, 0.f);
-  const float2 bs = chok ? __ldg(reinterpret_cast<const float2*>(bias + ch)) : make_float2(0.f, 0.f);
   __syncthreads();
   const int nbx = tw / kDtRX, nblk = (th / kDtTY) * nbx;
   for (int blk = warp; blk < nblk; blk += nwarps) {
