@@ -44,6 +44,9 @@ SIGNATURES = {
     "hpe_conv_pack_weight2": (_i, [C.POINTER(ConvDesc), _vp, _vp, _vp, _vp]),
     "hpe_conv_run2": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "hpe_conv_run_head2": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "hpe_pack_job_bytes": (_sz, []),
+    "hpe_conv_pack_job_fill": (_i, [C.POINTER(ConvDesc), _i, _vp, _vp, _i, _vp, C.POINTER(_i)]),
+    "hpe_conv_pack_jobs_run": (_i, [_vp, _i, _i, _vp]),
     "hpe_conv_out_hw": (_i, [C.POINTER(ConvDesc), C.POINTER(_i), C.POINTER(_i)]),
     "hpe_preprocess_out_elems": (_sz, [_i, _i, _i]),
     "hpe_preprocess": (_i, [_vp, _i, _i, _i, _vp, _vp]),

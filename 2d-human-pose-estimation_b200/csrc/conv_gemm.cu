@@ -25,6 +25,7 @@
 #include "tma_host.cuh"
 #include "conv_halo.cuh"
 #include <stdlib.h>
+#include <string.h>
 
 namespace hpe {
 using namespace ptx;
@@ -580,11 +581,9 @@ maxpool_kernel(const __nv_bfloat16* __restrict__ x, int B, int H, int W, int C, 
 }
 
 // PyTorch-layout fp32 weight -> packed bf16 GEMM-B  [rows][Ktot]; every tap's Cin is zero-padded to Cp = kc*64
-__global__ void __launch_bounds__(256)
-pack_weight_kernel(const float* __restrict__ w, int kind, int Cin, int Cp, int Cout, long long total,
-                   __nv_bfloat16* __restrict__ out, long long ldo = 0, int koff = 0) {
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+__device__ __forceinline__ void pack_weight_body(const float* __restrict__ w, int kind, int Cin, int Cp, int Cout, long long total,
+                                                 __nv_bfloat16* __restrict__ out, long long ldo, int koff, long long i0, long long istep) {
+  for (long long i = i0; i < total; i += istep) {
     float v = 0.f;
     if (kind == HPE_CONV_STEM7x7) {
       const int co = static_cast<int>(i / 256), k = static_cast<int>(i % 256);
@@ -608,6 +607,12 @@ pack_weight_kernel(const float* __restrict__ w, int kind, int Cin, int Cp, int C
     }
     out[i] = __float2bfloat16(v);
   }
+}
+__global__ void __launch_bounds__(256)
+pack_weight_kernel(const float* __restrict__ w, int kind, int Cin, int Cp, int Cout, long long total,
+                   __nv_bfloat16* __restrict__ out, long long ldo = 0, int koff = 0) {
+  pack_weight_body(w, kind, Cin, Cp, Cout, total, out, ldo, koff, static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x,
+                   static_cast<long long>(gridDim.x) * blockDim.x);
 }
 
 }  // namespace hpe
@@ -772,12 +777,10 @@ extern "C" int hpe_conv_pack_weight2(const hpe_conv_desc* d, const float* w_torc
 
 namespace hpe {
 // PyTorch-layout fp32 FORWARD weight -> packed bf16 GEMM-B of the layer's backward-data convolution
-__global__ void __launch_bounds__(256)
-pack_weight_dgrad_kernel(const float* __restrict__ w, int fkind, int fstride, int Cin, int Cout, long long total,
-                         __nv_bfloat16* __restrict__ out) {
+__device__ __forceinline__ void pack_weight_dgrad_body(const float* __restrict__ w, int fkind, int fstride, int Cin, int Cout,
+                                                       long long total, __nv_bfloat16* __restrict__ out, long long i0, long long istep) {
   // Cin/Cout are the FORWARD layer's; the dgrad GEMM has N = Cin (rows) and K over Cout.
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+  for (long long i = i0; i < total; i += istep) {
     float v = 0.f;
     if (fkind == HPE_CONV_1x1) {                                        // [ci][co] = w[co][ci]
       const int ci = static_cast<int>(i / Cout), co = static_cast<int>(i % Cout);
@@ -806,9 +809,69 @@ pack_weight_dgrad_kernel(const float* __restrict__ w, int fkind, int fstride, in
     out[i] = __float2bfloat16(v);
   }
 }
+__global__ void __launch_bounds__(256)
+pack_weight_dgrad_kernel(const float* __restrict__ w, int fkind, int fstride, int Cin, int Cout, long long total,
+                         __nv_bfloat16* __restrict__ out) {
+  pack_weight_dgrad_body(w, fkind, fstride, Cin, Cout, total, out, static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x,
+                         static_cast<long long>(gridDim.x) * blockDim.x);
+}
+
+// Every layer's forward and backward-data pack in ONE launch (training re-packs all bf16 operands from the updated fp32
+// parameters each step: ~110 separate launches of a few microseconds each were 1.4 ms of a 25 ms step).
+struct PackJob {
+  const float* src; __nv_bfloat16* dst; long long total;
+  int dgrad, kind, stride, Cin, Cp, Cout, block_begin, n_blocks;
+};
+__global__ void __launch_bounds__(256)
+pack_jobs_kernel(const PackJob* __restrict__ jobs, int n_jobs) {
+  int lo = 0, hi = n_jobs - 1;                       // last job whose first block is <= this block
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (jobs[mid].block_begin <= static_cast<int>(blockIdx.x)) lo = mid; else hi = mid - 1;
+  }
+  const PackJob j = jobs[lo];
+  const long long i0 = static_cast<long long>(blockIdx.x - j.block_begin) * blockDim.x + threadIdx.x;
+  const long long istep = static_cast<long long>(j.n_blocks) * blockDim.x;
+  if (j.dgrad) pack_weight_dgrad_body(j.src, j.kind, j.stride, j.Cin, j.Cout, j.total, j.dst, i0, istep);
+  else         pack_weight_body(j.src, j.kind, j.Cin, j.Cp, j.Cout, j.total, j.dst, 0, 0, i0, istep);
+}
 
 }  // namespace hpe
 using namespace hpe;
+
+extern "C" size_t hpe_pack_job_bytes(void) { return sizeof(PackJob); }
+
+extern "C" int hpe_conv_pack_job_fill(const hpe_conv_desc* fwd_desc, int dgrad, const float* w_torch, void* w_packed,
+                                      int block_begin, void* job_host, int* n_blocks) {
+  HPE_CHECK_ARG(fwd_desc && w_torch && w_packed && job_host && n_blocks && block_begin >= 0, "hpe_conv_pack_job_fill: bad argument");
+  PackJob j;
+  j.src = w_torch; j.dst = (__nv_bfloat16*)w_packed; j.dgrad = dgrad ? 1 : 0;
+  j.kind = fwd_desc->kind; j.stride = fwd_desc->stride; j.Cin = fwd_desc->Cin; j.Cout = fwd_desc->Cout;
+  if (dgrad) {
+    hpe_conv_desc g;
+    int rc = hpe_conv_dgrad_desc(fwd_desc, &g);
+    if (rc) return rc;
+    j.total = (long long)hpe_conv_packed_weight_elems(&g); j.Cp = 0;
+  } else {
+    int rc = desc_check(fwd_desc, "hpe_conv_pack_job_fill");
+    if (rc) return rc;
+    if (fwd_desc->Cin2 || (fwd_desc->kind > HPE_CONV_FINAL && fwd_desc->kind != HPE_CONV_2x2S2))
+      return fail(HPE_EINVAL, "hpe_conv_pack_job_fill: forward jobs take single-input forward kinds");
+    j.total = (long long)(wrows(fwd_desc) * ktot(fwd_desc)); j.Cp = cin_padded(fwd_desc);
+  }
+  const long long nb = (j.total + 1023) / 1024;              // ~4 elements per thread
+  j.n_blocks = (int)(nb < 1 ? 1 : (nb > 4096 ? 4096 : nb));
+  j.block_begin = block_begin;
+  *n_blocks = j.n_blocks;
+  memcpy(job_host, &j, sizeof(j));
+  return HPE_OK;
+}
+
+extern "C" int hpe_conv_pack_jobs_run(const void* jobs_device, int n_jobs, int total_blocks, void* stream) {
+  HPE_CHECK_ARG(jobs_device && n_jobs > 0 && total_blocks > 0, "hpe_conv_pack_jobs_run: bad argument");
+  pack_jobs_kernel<<<total_blocks, 256, 0, (cudaStream_t)stream>>>((const PackJob*)jobs_device, n_jobs);
+  return launch_status("pack_jobs_kernel");
+}
 
 extern "C" int hpe_conv_dgrad_desc(const hpe_conv_desc* f, hpe_conv_desc* g) {
   HPE_CHECK_ARG(f && g, "hpe_conv_dgrad_desc: null pointer");

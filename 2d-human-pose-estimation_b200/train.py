@@ -18,6 +18,7 @@ all-reduced.  Here:
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 import torch.distributed as dist
@@ -224,10 +225,39 @@ class TrainPlan:
     def repack(self):
         """Re-pack the bf16 GEMM operands from the (updated) fp32 parameters: device-side kernels only, no host
         tensors, so it can live inside a captured CUDA graph.  Needs one prior load_weights()."""
+        if os.environ.get("HPE_B200_BATCHED_PACK", "1") == "0":
+            for u in self.units():
+                u.load(u.conv_mod, u.bn)
+            self.final.load(self._final_mod.weight, None, self._final_mod.bias)
+            self.final_dg.load(self._final_mod.weight)
+            return
+        # ONE launch for every layer's forward + backward-data operand (job table built once; the parameters are updated in place)
+        items = []
         for u in self.units():
-            u.load(u.conv_mod, u.bn)
-        self.final.load(self._final_mod.weight, None, self._final_mod.bias)
-        self.final_dg.load(self._final_mod.weight)
+            items.append((u.fwd.desc, 0, u.conv_mod.weight, u.fwd.w_packed))
+            if u.dg is not None:
+                items.append((u.dg.fwd_desc, 1, u.conv_mod.weight, u.dg.w_packed))
+        items.append((self.final.desc, 0, self._final_mod.weight, self.final.w_packed))
+        items.append((self.final_dg.fwd_desc, 1, self._final_mod.weight, self.final_dg.w_packed))
+        key = tuple((w.data_ptr(), wp.data_ptr()) for _, _, w, wp in items)
+        if getattr(self, "_pack_key", None) != key:
+            lib = _lib.lib()
+            jb = lib.hpe_pack_job_bytes()
+            host = (C.c_char * (jb * len(items)))()
+            begin = 0
+            for k, (desc, dg, w, wp) in enumerate(items):
+                if not (w.is_cuda and w.dtype == torch.float32 and w.is_contiguous()):
+                    raise RuntimeError("libhpe_b200: parameters must be contiguous float32 CUDA tensors")
+                nb = C.c_int()
+                _lib.check(lib.hpe_conv_pack_job_fill(C.byref(desc), dg, w.data_ptr(), wp.data_ptr(), begin,
+                                                      C.addressof(host) + k * jb, C.byref(nb)), "hpe_conv_pack_job_fill")
+                begin += nb.value
+            self._pack_jobs = torch.frombuffer(bytearray(host.raw), dtype=torch.uint8).to(self.device)
+            self._pack_n, self._pack_blocks, self._pack_key = len(items), begin, key
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().hpe_conv_pack_jobs_run(_lib.ptr(self._pack_jobs), self._pack_n, self._pack_blocks,
+                                                         _lib.stream_ptr()), "hpe_conv_pack_jobs_run")
+        self.final.shift.copy_(self._final_mod.bias.detach())
 
     # ---- forward (training mode: batch statistics, running stats updated) --------------------------------------
     def forward(self, x):

@@ -167,6 +167,13 @@ int  hpe_conv_run2(hpe_conv_plan* plan, const void* x, const void* x2, const voi
  * Cin 256, Cout K) into a ZERO-initialised buffer of 32*256 bf16; bias2 [K] f32; heatmaps [B,K,Ho,Wo] f32 NCHW */
 int  hpe_conv_run_head2(hpe_conv_plan* plan, const void* x, const void* w_packed, const float* scale, const float* shift,
                         const void* w2_packed, const float* bias2, float* heatmaps, void* stream);
+/* Batched packing (training re-packs every layer's forward and backward-data operands each step): fill one job record per
+ * (layer, direction) on the HOST (hpe_pack_job_bytes() bytes each, consecutive block ranges: pass the running sum of
+ * *n_blocks as block_begin), copy the records to the device once, then ONE launch re-packs everything. */
+size_t hpe_pack_job_bytes(void);
+int  hpe_conv_pack_job_fill(const hpe_conv_desc* fwd_desc, int dgrad, const float* w_torch, void* w_packed, int block_begin,
+                            void* job_host, int* n_blocks);
+int  hpe_conv_pack_jobs_run(const void* jobs_device, int n_jobs, int total_blocks, void* stream);
 /* output spatial size of the layer */
 int  hpe_conv_out_hw(const hpe_conv_desc* desc, int* Ho, int* Wo);
 

@@ -253,6 +253,37 @@ def test_training_step_matches_oracle(hpe, cuda_dev, B, H, W):
         assert torch.allclose(p.detach().cpu(), before[n] - lr * moms[n].cpu(), rtol=1e-6, atol=1e-9), n
 
 
+def test_batched_repack_equals_per_layer_packs(hpe, cuda_dev, monkeypatch):
+    """One-launch re-pack of every forward / backward-data operand (hpe_conv_pack_jobs_run) == the per-layer pack calls, bit for bit."""
+    models = import_module("2d-human-pose-estimation_b200.models")
+    torch.manual_seed(5)
+    m = models.HeatmapPose(17, "resnet50", pretrained=False).cuda().train()
+    x = torch.rand(2, 3, 64, 64, device="cuda")
+    plan = m._train_plan(x)
+    plan.load_weights(m)
+
+    def packed():
+        out = []
+        for u in plan.units():
+            out.append(u.fwd.w_packed.clone())
+            if u.dg is not None:
+                out.append(u.dg.w_packed.clone())
+        return out + [plan.final.w_packed.clone(), plan.final_dg.w_packed.clone(), plan.final.shift.clone()]
+
+    monkeypatch.setenv("HPE_B200_BATCHED_PACK", "0")
+    plan.repack(); torch.cuda.synchronize()
+    want = packed()
+    for u in plan.units():                       # scribble, so a no-op batched path cannot pass
+        u.fwd.w_packed.zero_()
+        if u.dg is not None:
+            u.dg.w_packed.zero_()
+    plan.final.w_packed.zero_(); plan.final_dg.w_packed.zero_()
+    monkeypatch.setenv("HPE_B200_BATCHED_PACK", "1")
+    plan.repack(); torch.cuda.synchronize()
+    got = packed()
+    assert len(got) == len(want) and all(torch.equal(a, b) for a, b in zip(got, want))
+
+
 def test_train_step_cuda_graph_matches_eager(hpe, cuda_dev):
     """The captured-graph replay of the fused step (what bench.py --mode train times) follows the eager launches."""
     from oracle import heatmap_ref as hr
