@@ -28,6 +28,6 @@ print(f"  backward {timed(lambda: plan.backward(step.dhm, step.grads)):.3f} ms")
 from torch.profiler import profile, ProfilerActivity
 with profile(activities=[ProfilerActivity.CUDA]) as prof:
     step(x, joints); torch.cuda.synchronize()
-rows = sorted(prof.key_averages(), key=lambda r: -r.device_time_total)[:14]
+rows = sorted(prof.key_averages(), key=lambda r: -r.device_time_total)[:32]
 for r in rows:
     print(f"  {r.device_time_total/1e3:9.3f} ms  x{r.count:4d}  {r.key[:90]}")

@@ -1,5 +1,5 @@
 """Run ONE conv layer configuration a few times (target for `ncu --set full` captures).
-    python tools/run_layer.py <kind> B H W Cin Cout stride act res [iters]
+    python tools/run_layer.py <kind> B H W Cin Cout stride act res [iters] [head2_K]
 """
 import importlib
 import os
@@ -13,8 +13,11 @@ import hpe_b200  # noqa: F401,E402
 conv = importlib.import_module("2d-human-pose-estimation_b200.conv")
 kind, B, H, W, Cin, Cout, stride, act, res = [int(v) for v in sys.argv[1:10]]
 iters = int(sys.argv[10]) if len(sys.argv) > 10 else 5
+head2 = int(sys.argv[11]) if len(sys.argv) > 11 else 0        # K joints of a fused final 1x1 (deconv3 + final_layer kernel)
 dev = torch.device("cuda:0")
-layer = conv.ConvLayer(kind, B, H, W, Cin, Cout, stride, act, bool(res), dev)
+layer = conv.ConvLayer(kind, B, H, W, Cin, Cout, stride, act, bool(res), dev, head2=head2)
+if head2:
+    layer.load_head2(torch.randn(head2, 256, 1, 1) * 0.05, torch.zeros(head2))
 if kind == conv.CONV_DECONV4:
     w = torch.randn(Cin, Cout, 4, 4) * 0.02
 elif kind == conv.CONV_3x3:
