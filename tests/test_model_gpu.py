@@ -73,6 +73,33 @@ def test_forward_is_deterministic_and_graph_equals_eager(pair, cuda_dev, monkeyp
     assert torch.equal(a, c)
 
 
+@pytest.mark.parametrize("B", [1, 3, 5, 8, 33])
+def test_fused_paths_equal_unfused_layers(pair, cuda_dev, monkeypatch, B):
+    """The shipped forward (projection shortcuts accumulated into conv3, cta_group::2 tile pairs incl. odd tile counts, deconv3 +
+    final 1x1 in one kernel) against the same library with every fusion and the pair kernels switched off: same bf16
+    activations up to accumulation order and the fp32-before-rounding fold of the shortcut's BN scale.  Also run twice: the
+    persistent schedules are static, so the result is bit-reproducible."""
+    from importlib import import_module
+    models = import_module("2d-human-pose-estimation_b200.models")
+    m, ref = pair
+    x = torch.rand(B, 3, 256, 192, generator=torch.Generator().manual_seed(40 + B)).to(cuda_dev)
+    hm1 = m(x).clone()
+    hm2 = m(x).clone()
+    assert torch.equal(hm1, hm2)
+    for k in ("HPE_B200_FUSE_SHORTCUT", "HPE_B200_FUSE_HEAD", "HPE_B200_PAIR"):
+        monkeypatch.setenv(k, "0")
+    plain = models.HeatmapPose(17, "resnet50", pretrained=False)
+    plain.load_state_dict(ref.state_dict())
+    plain = plain.to(cuda_dev).eval()
+    want = plain(x)
+    torch.cuda.synchronize()
+    plan = next(iter(plain._plans.values()))
+    assert plan.fused_head is None and not plan.fused_shortcut
+    scale = want.abs().max().item()
+    assert (hm1 - want).abs().max().item() <= 2e-2 * scale, (hm1 - want).abs().max().item() / scale
+    assert ((hm1 - want) ** 2).mean().sqrt().item() <= 3e-3 * scale
+
+
 def test_forward_then_decode_end_to_end(hpe, pair, cuda_dev):
     m, ref = pair
     B = 4
