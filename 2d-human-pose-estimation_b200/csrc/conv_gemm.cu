@@ -14,12 +14,19 @@
 //     overlapping-stride TMA map one box row = 4 adjacent blocks = 64 contiguous bf16, so the stem is a
 //     4-tap GEMM with K = 4 x 64.
 //
+//   * a 1x1 conv may take a SECOND input (Cin2): its k-blocks follow the first input's in the same accumulation, which is how
+//     a Bottleneck's projection shortcut disappears into conv3 (hpe_conv_run2).
+//   * HEAD2: the last deconv stage keeps its bf16 output tile in shared memory and feeds it to a second tcgen05 GEMM against
+//     the joint weights -- deconv3 + final_layer in one kernel (hpe_conv_run_head2).
+//
 // Persistent, warp-specialised CTA (1 per SM, 352 threads):
-//   warp 0  TMA producer (A + W operand ring, STAGES deep)
-//   warp 1  TMEM allocator + single-thread tcgen05.mma issuer (double-buffered accumulators)
-//   warp 2  residual-tile TMA producer (into the epilogue staging ring)
+//   warp 0  TMA producer (A + W operand ring, STAGES deep); the whole warp runs the loop, one elected lane issues
+//   warp 1  TMEM allocator + tcgen05.mma issuer (elected lane; double-buffered accumulators)
+//   warp 2  residual-tile TMA producer (into the epilogue staging ring) / loads the fused head's joint weights
 //   warps 3-10  epilogue (two warps per TMEM lane quarter, each owning 32 of a chunk's 64 columns):
 //               tcgen05.ld -> scale/shift/residual/activation -> bf16 -> swizzled smem -> TMA store
+// PAIR kernels (256- and 192-wide tiles): the two CTAs of a cluster share ONE tcgen05.mma.cta_group::2 stream with M = 256;
+// each CTA loads its own A brick and half of the weight tile and drains its own 128 TMEM lanes.
 #include "hpe_common.cuh"
 #include "ptx_sm100.cuh"
 #include "tma_host.cuh"
