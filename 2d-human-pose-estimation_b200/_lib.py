@@ -20,7 +20,7 @@ CONV_DGRAD3x3S2, CONV_DGRAD1x1S2, CONV_4x4S2, CONV_2x2S2 = 5, 6, 7, 8
 class ConvDesc(C.Structure):
     _fields_ = [("kind", C.c_int), ("B", C.c_int), ("H", C.c_int), ("W", C.c_int), ("Cin", C.c_int),
                 ("Cout", C.c_int), ("stride", C.c_int), ("act", C.c_int), ("has_residual", C.c_int),
-                ("in_cstride", C.c_int), ("out_cstride", C.c_int), ("Cin2", C.c_int), ("stride2", C.c_int), ("head2", C.c_int)]
+                ("in_cstride", C.c_int), ("out_cstride", C.c_int), ("Cin2", C.c_int), ("stride2", C.c_int), ("head2", C.c_int), ("pool", C.c_int)]
 
 
 _vp, _i, _f, _sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t

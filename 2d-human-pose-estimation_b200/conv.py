@@ -26,10 +26,10 @@ def fold_bn(weight, bias, running_mean, running_var, eps):
 
 class ConvLayer:
     def __init__(self, kind, B, H, W, Cin, Cout, stride=1, act=ACT_RELU, has_residual=False, device="cuda", desc=None,
-                 in_cstride=0, out_cstride=0, Cin2=0, stride2=1, head2=0):
+                 in_cstride=0, out_cstride=0, Cin2=0, stride2=1, head2=0, pool=0):
         self.device = torch.device(device)
         self.desc = desc if desc is not None else ConvDesc(kind, B, H, W, Cin, Cout, stride, act, int(has_residual),
-                                                           in_cstride, out_cstride, Cin2, stride2 if Cin2 else 0, head2)
+                                                           in_cstride, out_cstride, Cin2, stride2 if Cin2 else 0, head2, int(pool))
         kind, B, Cout = self.desc.kind, self.desc.B, self.desc.Cout
         lib = _lib.lib()
         ho, wo = C.c_int(), C.c_int()

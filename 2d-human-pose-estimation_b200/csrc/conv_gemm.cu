@@ -649,7 +649,7 @@ static bool halo_eligible(const hpe_conv_desc* d, int Ho, int Wo) {
   if (e && e[0] == '0') return false;
   if (d->has_residual || d->in_cstride || d->out_cstride || d->Cin2) return false;
   const bool shape_ok = d->Cout == 64 && (Wo + 7) / 8 * 8 * ((Ho + 15) / 16 * 16) <= (long long)Wo * Ho * 9 / 8;   // <= 12.5 % padded
-  if (d->kind == HPE_CONV_STEM7x7) return shape_ok;
+  if (d->kind == HPE_CONV_STEM7x7) return shape_ok || d->pool;      // the pooled stem has its own (overlapping) tiling
   if (d->kind == HPE_CONV_3x3) return shape_ok && d->Cin == 64 && d->stride == 1;
   return false;
 }
@@ -659,6 +659,8 @@ static int desc_check(const hpe_conv_desc* d, const char* fn) {
   HPE_CHECK_ARG(d->kind >= HPE_CONV_1x1 && d->kind <= HPE_CONV_2x2S2, "%s: bad kind %d", fn, d->kind);
   HPE_CHECK_ARG(d->B > 0 && d->H > 0 && d->W > 0 && d->Cin > 0 && d->Cout > 0, "%s: non-positive size", fn);
   HPE_CHECK_ARG(d->in_cstride >= 0 && d->out_cstride >= 0, "%s: negative channel stride", fn);
+  if (d->pool && (d->kind != HPE_CONV_STEM7x7 || d->act != HPE_ACT_RELU || d->has_residual || d->in_cstride || d->out_cstride))
+    return fail(HPE_EUNSUPPORTED, "%s: the fused max-pool needs the dense ReLU stem (kind %d, act %d)", fn, d->kind, d->act);
   if (d->kind == HPE_CONV_STEM7x7) {
     if (d->Cin != 3 || d->Cout != 64 || (d->H % 2) || (d->W % 2))
       return fail(HPE_EUNSUPPORTED, "%s: stem needs Cin=3, Cout=64, even H/W (got %d,%d,%dx%d)", fn, d->Cin, d->Cout, d->H, d->W);
@@ -721,7 +723,8 @@ extern "C" int hpe_conv_out_hw(const hpe_conv_desc* d, int* Ho, int* Wo) {
   if (rc) return rc;
   HPE_CHECK_ARG(Ho && Wo, "hpe_conv_out_hw: null out");
   switch (d->kind) {
-    case HPE_CONV_STEM7x7: *Ho = d->H / 2; *Wo = d->W / 2; break;
+    case HPE_CONV_STEM7x7:                      // pool: MaxPool2d(3, 2, 1) of the H/2 x W/2 convolution output
+      *Ho = d->pool ? (d->H / 2 - 1) / 2 + 1 : d->H / 2; *Wo = d->pool ? (d->W / 2 - 1) / 2 + 1 : d->W / 2; break;
     case HPE_CONV_DECONV4: case HPE_CONV_DGRAD3x3S2: case HPE_CONV_DGRAD1x1S2: *Ho = d->H * 2; *Wo = d->W * 2; break;
     case HPE_CONV_4x4S2: case HPE_CONV_2x2S2: *Ho = d->H / 2; *Wo = d->W / 2; break;
     case HPE_CONV_FINAL:   *Ho = d->H; *Wo = d->W; break;
@@ -887,7 +890,7 @@ extern "C" int hpe_conv_dgrad_desc(const hpe_conv_desc* f, hpe_conv_desc* g) {
   if (rc) return rc;
   *g = *f;
   g->H = Ho; g->W = Wo; g->Cin = f->Cout; g->Cout = f->Cin; g->stride = 1; g->act = HPE_ACT_NONE; g->has_residual = 0;
-  g->Cin2 = 0; g->stride2 = 0; g->head2 = 0;
+  g->Cin2 = 0; g->stride2 = 0; g->head2 = 0; g->pool = 0;
   if (f->Cin2) return fail(HPE_EUNSUPPORTED, "hpe_conv_dgrad_desc: fused two-input layers are inference-only");
   switch (f->kind) {
     case HPE_CONV_1x1:     g->kind = f->stride == 2 ? HPE_CONV_DGRAD1x1S2 : HPE_CONV_1x1; break;
@@ -1047,7 +1050,14 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
     pl->hp.tiles_x = (pl->Wo + 7) / 8; pl->hp.tiles_y = (pl->Ho + 15) / 16;
     pl->hp.num_tiles = pl->hp.tiles_x * pl->hp.tiles_y * d->B;
     pl->hp.x_lo = stem ? 0 : 1; pl->hp.y_lo = stem ? 2 : 1;
-    pl->hp.base_off_mode = 0;
+    pl->hp.pool = d->pool ? 1 : 0; pl->hp.Wc = d->W / 2; pl->hp.Hc = d->H / 2;
+    { const char* dv = getenv("HPE_B200_HALO_DBG"); pl->hp.dbg = dv ? atoi(dv) : 0; }
+    { const char* dv = getenv("HPE_B200_HALO_DIRECT"); pl->hp.direct = !(dv && dv[0] == '0'); }
+    pl->hp.Wo = pl->Wo; pl->hp.Ho = pl->Ho; pl->hp.out = nullptr;
+    if (d->pool) {                              // 3 x 7 pooled pixels per (overlapping) 8 x 16 brick; pl->Wo/Ho are the POOLED extent
+      pl->hp.tiles_x = (pl->Wo + 2) / 3; pl->hp.tiles_y = (pl->Ho + 6) / 7;
+      pl->hp.num_tiles = pl->hp.tiles_x * pl->hp.tiles_y * d->B;
+    }
     if (!stem) {
       // Default: ONE 10-pixel-wide halo'd box per tile (23 KB); the column taps are 128-byte shifts of the descriptor start.
       // Measured on B200: SWIZZLE_128B is a function of the absolute shared-memory address, so such starts need base offset 0
@@ -1058,6 +1068,9 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
     }
     pl->grid = pl->hp.num_tiles < num_sms() ? pl->hp.num_tiles : num_sms();
     p.tw = 8; p.th = 16; p.nb = 1;               // brick of the output / A maps encoded below
+  } else if (d->pool) {
+    delete pl;
+    return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: the fused max-pool runs on the y-halo stem kernel only (HPE_B200_HALO=0 disables it)");
   }
   *out = pl;
   return HPE_OK;
@@ -1126,7 +1139,7 @@ static int encode_plan_maps(hpe_conv_plan* pl, const void* x, const void* x2, co
   if (d.kind != HPE_CONV_FINAL && !d.head2 && y != pl->y) {
     HPE_CHECK_ARG(((uintptr_t)y & 15) == 0, "hpe_conv_run: y must be 16-byte aligned");
     const uint64_t C = d.Cout, P = d.out_cstride ? d.out_cstride : d.Cout;
-    const uint32_t box[4] = {64, (uint32_t)p.tw, (uint32_t)p.th, (uint32_t)p.nb};
+    const uint32_t box[4] = {64, (uint32_t)(d.pool ? 3 : p.tw), (uint32_t)(d.pool ? 7 : p.th), (uint32_t)p.nb};
     if (is_class_strided(d.kind) || d.kind == HPE_CONV_DGRAD1x1S2) {
       const uint64_t Wo = pl->Wo, Ho = pl->Ho;
       const int ncls = d.kind == HPE_CONV_DGRAD1x1S2 ? 1 : 4;
@@ -1194,8 +1207,8 @@ static int conv_launch(hpe_conv_plan* pl, const void* x, const void* x2, const v
   int rc = encode_plan_maps(pl, x, x2, w_packed, residual, y, w2);
   if (rc) return rc;
   if (pl->halo_taps_y) {
-    pl->hp.scale = scale; pl->hp.shift = shift;
-    return halo_launch(pl->halo_taps_y, pl->halo_boxes, pl->d.act, &pl->tmA, &pl->tmW, &pl->tmOut.m[0], pl->hp, pl->grid,
+    pl->hp.scale = scale; pl->hp.shift = shift; pl->hp.out = y;
+    return halo_launch(pl->halo_taps_y, pl->halo_boxes, pl->d.act, pl->hp.pool, &pl->tmA, &pl->tmW, &pl->tmOut.m[0], pl->hp, pl->grid,
                        (cudaStream_t)stream);
   }
   ConvParams p = pl->p;

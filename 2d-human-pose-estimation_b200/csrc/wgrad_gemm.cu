@@ -263,6 +263,7 @@ extern "C" int hpe_wgrad_plan_create(const hpe_conv_desc* d, hpe_wgrad_plan** ou
   int Ho = 0, Wo = 0;
   int rc = hpe_conv_out_hw(d, &Ho, &Wo);      // validates the descriptor
   if (rc) return rc;
+  if (d->pool || d->head2 || d->Cin2) return fail(HPE_EUNSUPPORTED, "hpe_wgrad_plan_create: describe the plain layer (no fused pool / head / second input)");
   rc = hpe_check_device();
   if (rc) return rc;
   hpe_wgrad_plan* pl = new hpe_wgrad_plan();

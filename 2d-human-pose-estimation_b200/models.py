@@ -202,9 +202,18 @@ class _ForwardPlan:
             self.ops.append((layer, src, res, dst, src2))
 
         self.s2d = preprocess(torch.zeros(B, 3, H, W, device=dev))
-        add("backbone.conv1", ConvLayer(CONV_STEM7x7, B, H, W, 3, 64, 2, ACT_RELU, False, dev), "s2d", "stem")
+        # `x = self.maxpool(x)` (timm ResNet.forward_features) taken in the stem's epilogue: the H/2 x W/2 tensor never exists
+        self.fused_pool = False
         h, w = H // 4, W // 4
-        buf("pool", (B, h, w, 64))
+        if os.environ.get("HPE_B200_FUSE_POOL", "1") != "0":
+            try:
+                add("backbone.conv1", ConvLayer(CONV_STEM7x7, B, H, W, 3, 64, 2, ACT_RELU, False, dev, pool=1), "s2d", "pool")
+                self.fused_pool = True
+            except Exception:      # e.g. HPE_B200_HALO=0: the pooled stem exists on the y-halo kernel only
+                pass
+        if not self.fused_pool:
+            add("backbone.conv1", ConvLayer(CONV_STEM7x7, B, H, W, 3, 64, 2, ACT_RELU, False, dev), "s2d", "stem")
+            buf("pool", (B, h, w, 64))
         cur, cin = "pool", 64
         for i, (n, p) in enumerate(zip(_LAYERS, _PLANES)):
             for j in range(n):
@@ -247,7 +256,7 @@ class _ForwardPlan:
         self.bufs["s2d"] = self.s2d
         self.weights_version = -1
         self.graph = None
-        self.n_launches = len(self.ops) + 2          # + preprocess + maxpool
+        self.n_launches = len(self.ops) + (1 if self.fused_pool else 2)          # + preprocess (+ maxpool)
 
     @property
     def features(self):

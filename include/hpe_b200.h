@@ -146,6 +146,10 @@ typedef struct hpe_conv_desc {
                                NOT written; a second GEMM against the K-joint 1x1 weights runs on the tile while it is still in shared
                                memory and fp32 NCHW heatmaps [B,K,Ho,Wo] are written instead -- the last deconv stage + final_layer of
                                the App. A.1 head in one kernel.  Run with hpe_conv_run_head2. */
+  int pool;                 /* != 0 (HPE_CONV_STEM7x7 with HPE_ACT_RELU only): `x = self.maxpool(x)` of timm ResNet.forward_features
+                               (MaxPool2d(3, 2, 1) after conv1/bn1/act1) is taken in the stem's epilogue; y is the POOLED
+                               [B, Hp, Wp, 64] tensor and the H/2 x W/2 stem output is never written.  Bit-identical to
+                               hpe_conv_run followed by hpe_maxpool3x3s2. */
 } hpe_conv_desc;
 /* Channel counts: Cin and Cout must be multiples of 8 (16-byte pixels); partial 64-channel blocks are zero-filled by TMA. */
 

@@ -127,6 +127,39 @@ def test_stem_and_maxpool(hpe, cuda_dev, B, H, W):
     assert torch.equal(nchw(p), pref)
 
 
+@pytest.mark.parametrize("B,H,W", [(4, 64, 48), (2, 256, 192), (3, 36, 20), (3, 96, 80), (1, 38, 44), (5, 128, 96), (2, 26, 14),
+                                   (150, 64, 64)])
+def test_stem_with_fused_maxpool(hpe, cuda_dev, B, H, W):
+    """hpe_conv_desc.pool: MaxPool2d(3, 2, 1) taken in the stem's epilogue == stem launch followed by hpe_maxpool3x3s2, bit for bit
+    (odd/even conv extents, bricks hanging over every image edge, more tiles than CTAs)."""
+    from importlib import import_module
+    conv = import_module("2d-human-pose-estimation_b200.conv")
+    g = torch.Generator().manual_seed(31)
+    img = torch.rand(B, 3, H, W, generator=g) - 0.3
+    w = make(g, 64, 3, 7, 7, s=0.1)
+    scale = torch.rand(64, generator=g) + 0.5; shift = torch.randn(64, generator=g) * 0.1
+    s2d = conv.preprocess(img.cuda())
+    plain = conv.ConvLayer(conv.CONV_STEM7x7, B, H, W, 3, 64, 2, 1, False).load(w, scale, shift)
+    want = conv.maxpool3x3s2(plain(s2d))
+    fused = conv.ConvLayer(conv.CONV_STEM7x7, B, H, W, 3, 64, 2, 1, False, pool=1).load(w, scale, shift)
+    assert fused.out_shape() == tuple(want.shape)
+    out = torch.full(want.shape, float("nan"), dtype=torch.bfloat16, device="cuda")
+    fused(s2d, None, out)
+    torch.cuda.synchronize()
+    assert torch.equal(out, want)
+    ref = F.max_pool2d(torch.relu(F.conv2d(r16(img), w, stride=2, padding=3) * scale[None, :, None, None] + shift[None, :, None, None]), 3, 2, 1)
+    check(nchw(out), ref, "stem+pool")
+
+
+def test_fused_maxpool_rejected_off_the_relu_stem(hpe, cuda_dev):
+    from importlib import import_module
+    conv = import_module("2d-human-pose-estimation_b200.conv")
+    with pytest.raises(Exception):
+        conv.ConvLayer(conv.CONV_3x3, 2, 16, 16, 64, 64, 1, 1, False, pool=1)
+    with pytest.raises(Exception):
+        conv.ConvLayer(conv.CONV_STEM7x7, 2, 64, 64, 3, 64, 2, 0, False, pool=1)      # no activation
+
+
 @pytest.mark.parametrize("B,H,W,Cin", [(4, 8, 6, 256), (2, 8, 6, 2048), (3, 5, 7, 256), (2, 32, 24, 256), (3, 8, 8, 128)])
 def test_deconv4x4s2(hpe, cuda_dev, B, H, W, Cin):
     from importlib import import_module

@@ -86,7 +86,7 @@ def test_fused_paths_equal_unfused_layers(pair, cuda_dev, monkeypatch, B):
     hm1 = m(x).clone()
     hm2 = m(x).clone()
     assert torch.equal(hm1, hm2)
-    for k in ("HPE_B200_FUSE_SHORTCUT", "HPE_B200_FUSE_HEAD", "HPE_B200_PAIR"):
+    for k in ("HPE_B200_FUSE_SHORTCUT", "HPE_B200_FUSE_HEAD", "HPE_B200_PAIR", "HPE_B200_FUSE_POOL"):
         monkeypatch.setenv(k, "0")
     plain = models.HeatmapPose(17, "resnet50", pretrained=False)
     plain.load_state_dict(ref.state_dict())
@@ -94,7 +94,7 @@ def test_fused_paths_equal_unfused_layers(pair, cuda_dev, monkeypatch, B):
     want = plain(x)
     torch.cuda.synchronize()
     plan = next(iter(plain._plans.values()))
-    assert plan.fused_head is None and not plan.fused_shortcut
+    assert plan.fused_head is None and not plan.fused_shortcut and not plan.fused_pool
     scale = want.abs().max().item()
     assert (hm1 - want).abs().max().item() <= 2e-2 * scale, (hm1 - want).abs().max().item() / scale
     assert ((hm1 - want) ** 2).mean().sqrt().item() <= 3e-3 * scale
