@@ -639,7 +639,7 @@ struct hpe_conv_plan {
   void* y;
   CUtensorMap tmA2;
   const void* fn;
-  int halo_taps_y, halo_boxes;        // != 0: the layer runs on the y-halo variant (conv_halo.cu)
+  int halo_taps_y, halo_boxes;        // halo_taps_y != 0: the layer runs on the y-halo variant (conv_halo.cu); halo_boxes unused
   HaloParams hp;
 };
 
@@ -648,7 +648,7 @@ static bool halo_eligible(const hpe_conv_desc* d, int Ho, int Wo) {
   const char* e = getenv("HPE_B200_HALO");
   if (e && e[0] == '0') return false;
   if (d->has_residual || d->in_cstride || d->out_cstride || d->Cin2) return false;
-  const bool shape_ok = d->Cout == 64 && (Wo + 7) / 8 * 8 * ((Ho + 15) / 16 * 16) <= (long long)Wo * Ho * 9 / 8;   // <= 12.5 % padded
+  const bool shape_ok = d->Cout == 64 && (Wo + 7) / 8 * 8 * ((Ho + kHaloRows - 1) / kHaloRows * kHaloRows) <= (long long)Wo * Ho * 9 / 8;   // <= 12.5 % padded
   if (d->kind == HPE_CONV_STEM7x7) return shape_ok || d->pool;      // the pooled stem has its own (overlapping) tiling
   if (d->kind == HPE_CONV_3x3) return shape_ok && d->Cin == 64 && d->stride == 1;
   return false;
@@ -1045,29 +1045,21 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
   pl->x = pl->x2 = pl->w = pl->res = pl->w2 = nullptr; pl->y = nullptr;
   pl->halo_taps_y = pl->halo_boxes = 0;
   if (halo_eligible(d, pl->Ho, pl->Wo)) {
+    // 8-wide x 32-tall bricks; the 3x3 reads ONE 10-pixel-wide halo'd box per brick whose column taps are 128-byte shifts of
+    // the descriptor start.  Measured on B200: SWIZZLE_128B is a function of the absolute shared-memory address, so such starts
+    // need base offset 0 (setting the descriptor's base-offset field to (start >> 7) & 7 instead FAILS parity).
     const bool stem = d->kind == HPE_CONV_STEM7x7;
-    pl->halo_taps_y = stem ? 4 : 3; pl->halo_boxes = stem ? 1 : 3;
-    pl->hp.tiles_x = (pl->Wo + 7) / 8; pl->hp.tiles_y = (pl->Ho + 15) / 16;
-    pl->hp.num_tiles = pl->hp.tiles_x * pl->hp.tiles_y * d->B;
+    pl->halo_taps_y = stem ? 4 : 3;
+    pl->hp.tiles_x = (pl->Wo + 7) / 8; pl->hp.tiles_y = (pl->Ho + kHaloRows - 1) / kHaloRows;
     pl->hp.x_lo = stem ? 0 : 1; pl->hp.y_lo = stem ? 2 : 1;
     pl->hp.pool = d->pool ? 1 : 0; pl->hp.Wc = d->W / 2; pl->hp.Hc = d->H / 2;
-    { const char* dv = getenv("HPE_B200_HALO_DBG"); pl->hp.dbg = dv ? atoi(dv) : 0; }
-    { const char* dv = getenv("HPE_B200_HALO_DIRECT"); pl->hp.direct = !(dv && dv[0] == '0'); }
     pl->hp.Wo = pl->Wo; pl->hp.Ho = pl->Ho; pl->hp.out = nullptr;
-    if (d->pool) {                              // 3 x 7 pooled pixels per (overlapping) 8 x 16 brick; pl->Wo/Ho are the POOLED extent
-      pl->hp.tiles_x = (pl->Wo + 2) / 3; pl->hp.tiles_y = (pl->Ho + 6) / 7;
-      pl->hp.num_tiles = pl->hp.tiles_x * pl->hp.tiles_y * d->B;
+    if (d->pool) {                              // 3 x 15 pooled pixels per (overlapping) brick; pl->Wo/Ho are the POOLED extent
+      pl->hp.tiles_x = (pl->Wo + 2) / 3; pl->hp.tiles_y = (pl->Ho + 14) / 15;
     }
-    if (!stem) {
-      // Default: ONE 10-pixel-wide halo'd box per tile (23 KB); the column taps are 128-byte shifts of the descriptor start.
-      // Measured on B200: SWIZZLE_128B is a function of the absolute shared-memory address, so such starts need base offset 0
-      // (setting the descriptor's base-offset field to (start >> 7) & 7 instead FAILS parity).  HPE_B200_HALO_WIDE=0 selects
-      // three 8-wide boxes, whose starts are all 1024-byte aligned.
-      const char* wv = getenv("HPE_B200_HALO_WIDE");
-      if (!(wv && wv[0] == '0')) pl->halo_boxes = 0;
-    }
+    pl->hp.num_tiles = pl->hp.tiles_x * pl->hp.tiles_y * d->B;
     pl->grid = pl->hp.num_tiles < num_sms() ? pl->hp.num_tiles : num_sms();
-    p.tw = 8; p.th = 16; p.nb = 1;               // brick of the output / A maps encoded below
+    p.tw = 8; p.th = kHaloRows; p.nb = 1;        // brick of the A map encoded below
   } else if (d->pool) {
     delete pl;
     return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: the fused max-pool runs on the y-halo stem kernel only (HPE_B200_HALO=0 disables it)");
@@ -1090,15 +1082,15 @@ static int encode_plan_maps(hpe_conv_plan* pl, const void* x, const void* x2, co
       const uint64_t Hs = d.H / 2, Ws = d.W / 2, Wp = Ws + kS2DPad;
       const uint64_t dims[4] = {64, Ws, Hs, (uint64_t)d.B};
       const uint64_t str[3] = {32, Wp * 32, Hs * Wp * 32};           // overlapping 64-element windows, 16 el apart
-      const uint32_t box[4] = {64, (uint32_t)p.tw, (uint32_t)(pl->halo_taps_y ? 16 + pl->halo_taps_y - 1 : p.th), (uint32_t)p.nb};
+      const uint32_t box[4] = {64, (uint32_t)p.tw, (uint32_t)(pl->halo_taps_y ? kHaloRows + pl->halo_taps_y - 1 : p.th), (uint32_t)p.nb};
       rc = encode_map(&pl->tmA, x, 4, dims, str, box, ones, "stem A");
     } else {
       const uint64_t C = d.Cin, P = d.in_cstride ? d.in_cstride : d.Cin;      // P = channel pitch of a pixel
       const uint64_t dims[4] = {C, (uint64_t)d.W, (uint64_t)d.H, (uint64_t)d.B};
       const uint64_t str[3] = {P * 2, (uint64_t)d.W * P * 2, (uint64_t)d.H * d.W * P * 2};
       const uint32_t s = (uint32_t)p.in_stride;
-      const uint32_t box[4] = {64, (uint32_t)(pl->halo_taps_y && !pl->halo_boxes ? 10 : p.tw * s),
-                               (uint32_t)(pl->halo_taps_y ? 16 + pl->halo_taps_y - 1 : p.th * s), (uint32_t)p.nb};
+      const uint32_t box[4] = {64, (uint32_t)(pl->halo_taps_y ? 10 : p.tw * s),
+                               (uint32_t)(pl->halo_taps_y ? kHaloRows + pl->halo_taps_y - 1 : p.th * s), (uint32_t)p.nb};
       const uint32_t es[4] = {1, s, s, 1};
       rc = encode_map(&pl->tmA, x, 4, dims, str, box, es, "A");
     }
@@ -1136,10 +1128,10 @@ static int encode_plan_maps(hpe_conv_plan* pl, const void* x, const void* x2, co
     if (rc) return rc;
     pl->w2 = w2;
   }
-  if (d.kind != HPE_CONV_FINAL && !d.head2 && y != pl->y) {
+  if (d.kind != HPE_CONV_FINAL && !d.head2 && !pl->halo_taps_y && y != pl->y) {      // (the y-halo kernel stores without TMA)
     HPE_CHECK_ARG(((uintptr_t)y & 15) == 0, "hpe_conv_run: y must be 16-byte aligned");
     const uint64_t C = d.Cout, P = d.out_cstride ? d.out_cstride : d.Cout;
-    const uint32_t box[4] = {64, (uint32_t)(d.pool ? 3 : p.tw), (uint32_t)(d.pool ? 7 : p.th), (uint32_t)p.nb};
+    const uint32_t box[4] = {64, (uint32_t)p.tw, (uint32_t)p.th, (uint32_t)p.nb};
     if (is_class_strided(d.kind) || d.kind == HPE_CONV_DGRAD1x1S2) {
       const uint64_t Wo = pl->Wo, Ho = pl->Ho;
       const int ncls = d.kind == HPE_CONV_DGRAD1x1S2 ? 1 : 4;
@@ -1208,8 +1200,7 @@ static int conv_launch(hpe_conv_plan* pl, const void* x, const void* x2, const v
   if (rc) return rc;
   if (pl->halo_taps_y) {
     pl->hp.scale = scale; pl->hp.shift = shift; pl->hp.out = y;
-    return halo_launch(pl->halo_taps_y, pl->halo_boxes, pl->d.act, pl->hp.pool, &pl->tmA, &pl->tmW, &pl->tmOut.m[0], pl->hp, pl->grid,
-                       (cudaStream_t)stream);
+    return halo_launch(pl->halo_taps_y, pl->d.act, &pl->tmA, &pl->tmW, pl->hp, pl->grid, (cudaStream_t)stream);
   }
   ConvParams p = pl->p;
   p.scale = scale; p.shift = shift;

@@ -94,6 +94,7 @@ def test_conv1x1_fused_projection_shortcut(hpe, cuda_dev, B, H, W, Cin, Cin2, Co
     (4, 16, 12, 64, 64, 1), (4, 16, 12, 128, 128, 1), (4, 32, 24, 128, 128, 2), (2, 16, 12, 256, 256, 2),
     (3, 10, 6, 64, 64, 1), (2, 8, 6, 512, 512, 1),
     (3, 32, 24, 64, 64, 1), (2, 16, 8, 64, 64, 1), (2, 64, 48, 64, 64, 1), (5, 48, 40, 64, 64, 1),   # y-halo variant (conv_halo.cu)
+    (1, 120, 56, 64, 64, 1), (2, 124, 44, 64, 64, 1), (160, 32, 8, 64, 64, 1),                        # ... bricks hanging over the bottom / right edge
 ])
 def test_conv3x3(hpe, cuda_dev, B, H, W, C, Cout, stride):
     from importlib import import_module
@@ -108,7 +109,7 @@ def test_conv3x3(hpe, cuda_dev, B, H, W, C, Cout, stride):
     check(nchw(y), ref, "conv3x3")
 
 
-@pytest.mark.parametrize("B,H,W", [(4, 64, 48), (2, 256, 192), (3, 36, 20), (3, 96, 80)])
+@pytest.mark.parametrize("B,H,W", [(4, 64, 48), (2, 256, 192), (3, 36, 20), (3, 96, 80), (2, 240, 112), (1, 248, 90), (200, 64, 32)])
 def test_stem_and_maxpool(hpe, cuda_dev, B, H, W):
     from importlib import import_module
     conv = import_module("2d-human-pose-estimation_b200.conv")

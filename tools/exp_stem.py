@@ -18,7 +18,7 @@ def timeit(layer, x, tag):
     print(f"{tag}: min {min(ts)*1e3:.1f} us median {sorted(ts)[3]*1e3:.1f} us", flush=True)
 for pool in (0, 1):
     l = conv.ConvLayer(conv.CONV_STEM7x7, B, 256, 192, 3, 64, 2, 1, False, pool=pool).load(torch.randn(64, 3, 7, 7) * 0.1, torch.rand(64) + 0.5, torch.randn(64) * 0.1)
-    timeit(l, s2d, f"stem pool={pool} dbg={os.environ.get('HPE_B200_HALO_DBG', '0')}")
+    timeit(l, s2d, f"stem pool={pool}")
 x = torch.randn(B, 64, 48, 64, device="cuda").to(torch.bfloat16)
 l = conv.ConvLayer(conv.CONV_3x3, B, 64, 48, 64, 64, 1, 1, False).load(torch.randn(64, 64, 3, 3) * 0.05, torch.rand(64) + 0.5, torch.randn(64) * 0.1)
-timeit(l, x, f"l1conv2 dbg={os.environ.get('HPE_B200_HALO_DBG', '0')}")
+timeit(l, x, f"l1conv2")
