@@ -40,8 +40,8 @@ import torch  # noqa: E402
 
 METRIC = "images/sec fwd+decode @256x192 COCO-17"
 GFLOP_PER_IMG_256x192 = 8.008 + 2.846          # trunk + head, 2*MAC, no padding/zero-insertion waste
-# ncu (profiles/r01_launches_step_v3.csv): DRAM bytes of one B=256 256x192 step's conv launches / 52 launches
-NCU_DRAM_BYTES_PER_CONV_LAUNCH = round((6704 + 2671 + 408 + 490) * 1e6 / 52)
+# ncu (profiles/r01_launches_step_v4.csv): DRAM bytes of one B=256 256x192 step's conv launches / 52 launches
+NCU_DRAM_BYTES_PER_CONV_LAUNCH = round((6703 + 2672 + 407 + 204) * 1e6 / 52)
 
 
 def load_peaks():
@@ -321,16 +321,16 @@ def run_b200(args):
                                    "random-init weights (BASELINE configs[1])",
                        "global_batch": world * B, "parallelism": f"dp{world}",
                        "l2": "inputs (151 MB/step, 2 alternating batches) and every activation exceed the 126 MB L2; no flush needed"},
-            "roofline": {"bound": "tensor", "kernel": "conv_gemm_kernel + conv_yhalo_kernel (52 launches/step: trunk with the projection "
+            "roofline": {"bound": "tensor", "kernel": "conv_gemm_kernel + conv_yhalo_kernel (52 launches/step: stem with the max-pool in its epilogue, trunk with the projection "
                                                       "shortcuts fused into conv3, deconv head with the final 1x1 fused into its last stage; 256-wide tiles as cta_group::2 pairs)",
                          "achieved": round(flops_step / (fwd_ms * 1e-3) / 1e12, 2), "peak": peaks["tflops"], "unit": "TFLOP/s",
                          "frac": round(flops_step / (fwd_ms * 1e-3) / 1e12 / peaks["tflops"], 4),
                          "traffic": NCU_DRAM_BYTES_PER_CONV_LAUNCH if (B, H, W, K) == (256, 256, 192, 17) else None,
                          "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum averaged over the step's 52 conv launches "
-                                           "(10.27 GB / step vs 12.1 GB of per-layer algorithmic input+output+residual+weight bytes: part of each layer's input is still in L2, no re-reads), profiles/r01_launches_step_v3.csv",
+                                           "(9.99 GB / step vs 11.8 GB of per-layer algorithmic input+output+residual+weight bytes: part of each layer's input is still in L2, no re-reads), profiles/r01_launches_step_v4.csv",
                          "peak_source": f"{peaks['src']} bf16_tflops_sustained (kernel timed inside a long step)",
                          "ms_forward": round(fwd_ms, 4),
-                         "note": "algorithmic FLOPs of the step / CUDA-event time of the forward graph (incl. preprocess+maxpool)"},
+                         "note": "algorithmic FLOPs of the step / CUDA-event time of the forward graph (incl. preprocess; the max-pool runs in the stem's epilogue)"},
             "decode_roofline": {"bound": "hbm", "kernel": "decode_kernel", "achieved": round(sweep["gbs"], 1), "peak": peaks["hbm"],
                                 "unit": "GB/s", "frac": round(sweep["gbs"] / peaks["hbm"], 4), "traffic": None,
                                 "workload": f"decode sweep point: {sweep['B']} x {K} maps of {H // 4}x{W // 4} fp32 (3.4 GB, > L2), "
