@@ -639,7 +639,7 @@ struct hpe_conv_plan {
   void* y;
   CUtensorMap tmA2;
   const void* fn;
-  int halo_taps_y, halo_boxes;        // halo_taps_y != 0: the layer runs on the y-halo variant (conv_halo.cu); halo_boxes unused
+  int halo_taps_y;                    // != 0: the layer runs on the y-halo variant (conv_halo.cu)
   HaloParams hp;
 };
 
@@ -1043,7 +1043,7 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
     pl->grid = 2 * (p.num_tiles < max_clusters ? p.num_tiles : max_clusters);
   }
   pl->x = pl->x2 = pl->w = pl->res = pl->w2 = nullptr; pl->y = nullptr;
-  pl->halo_taps_y = pl->halo_boxes = 0;
+  pl->halo_taps_y = 0;
   if (halo_eligible(d, pl->Ho, pl->Wo)) {
     // 8-wide x 32-tall bricks; the 3x3 reads ONE 10-pixel-wide halo'd box per brick whose column taps are 128-byte shifts of
     // the descriptor start.  Measured on B200: SWIZZLE_128B is a function of the absolute shared-memory address, so such starts
