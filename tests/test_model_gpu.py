@@ -100,6 +100,20 @@ def test_fused_paths_equal_unfused_layers(pair, cuda_dev, monkeypatch, B):
     assert ((hm1 - want) ** 2).mean().sqrt().item() <= 3e-3 * scale
 
 
+def test_full_size_batch_equals_small_batches(pair, cuda_dev):
+    """BASELINE configs[1] size (B=256 @256x192): a size-independent property instead of the (slow) oracle -- an image's heatmaps do not
+    depend on the batch it sits in or on its position in it.  The 256-batch runs different bricks, tile pairs, waves and persistent
+    schedules than the 32-batch the oracle tests cover, but every output element is the same sequence of MMAs: bit-identical."""
+    m, _ = pair
+    x32 = torch.rand(32, 3, 256, 192, generator=torch.Generator().manual_seed(77)).to(cuda_dev)
+    hm32 = m(x32).clone()
+    hm256 = m(x32.repeat(8, 1, 1, 1))
+    torch.cuda.synchronize()
+    assert hm256.shape == (256, 17, 64, 48)
+    assert torch.isfinite(hm256).all()
+    assert torch.equal(hm256.view(8, 32, 17, 64, 48), hm32.unsqueeze(0).expand(8, -1, -1, -1, -1))
+
+
 def test_forward_then_decode_end_to_end(hpe, pair, cuda_dev):
     m, ref = pair
     B = 4
