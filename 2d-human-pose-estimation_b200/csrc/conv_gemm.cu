@@ -414,17 +414,19 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           for (int j = 0; j < 4; ++j) {
             const float4 s0 = lds_f4(ss + j * 32), s1 = lds_f4(ss + j * 32 + 16);
             const float4 h0 = lds_f4(sh + j * 32), h1 = lds_f4(sh + j * 32 + 16);
-            float o[8];
-            o[0] = fmaf(__uint_as_float(v[j * 8 + 0]), s0.x, h0.x); o[1] = fmaf(__uint_as_float(v[j * 8 + 1]), s0.y, h0.y);
-            o[2] = fmaf(__uint_as_float(v[j * 8 + 2]), s0.z, h0.z); o[3] = fmaf(__uint_as_float(v[j * 8 + 3]), s0.w, h0.w);
-            o[4] = fmaf(__uint_as_float(v[j * 8 + 4]), s1.x, h1.x); o[5] = fmaf(__uint_as_float(v[j * 8 + 5]), s1.y, h1.y);
-            o[6] = fmaf(__uint_as_float(v[j * 8 + 6]), s1.z, h1.z); o[7] = fmaf(__uint_as_float(v[j * 8 + 7]), s1.w, h1.w);
+            // packed fp32x2 arithmetic (FFMA2 / FADD2: two independent IEEE operations per instruction, same bits as the scalar
+            // form) -- the epilogue is issue-bound (two epilogue warps per scheduler, in-kernel profile in profiles/)
+            float2 o01 = __ffma2_rn(make_float2(__uint_as_float(v[j * 8 + 0]), __uint_as_float(v[j * 8 + 1])), make_float2(s0.x, s0.y), make_float2(h0.x, h0.y));
+            float2 o23 = __ffma2_rn(make_float2(__uint_as_float(v[j * 8 + 2]), __uint_as_float(v[j * 8 + 3])), make_float2(s0.z, s0.w), make_float2(h0.z, h0.w));
+            float2 o45 = __ffma2_rn(make_float2(__uint_as_float(v[j * 8 + 4]), __uint_as_float(v[j * 8 + 5])), make_float2(s1.x, s1.y), make_float2(h1.x, h1.y));
+            float2 o67 = __ffma2_rn(make_float2(__uint_as_float(v[j * 8 + 6]), __uint_as_float(v[j * 8 + 7])), make_float2(s1.z, s1.w), make_float2(h1.z, h1.w));
             const uint32_t slot = rowp + (((half * 4 + j) ^ (row & 7)) << 4);     // 128-byte swizzle
             if (RES) {
               const uint4 rr = lds_v4(slot);
-              o[0] += bf16_lo(rr.x); o[1] += bf16_hi(rr.x); o[2] += bf16_lo(rr.y); o[3] += bf16_hi(rr.y);
-              o[4] += bf16_lo(rr.z); o[5] += bf16_hi(rr.z); o[6] += bf16_lo(rr.w); o[7] += bf16_hi(rr.w);
+              o01 = __fadd2_rn(o01, make_float2(bf16_lo(rr.x), bf16_hi(rr.x))); o23 = __fadd2_rn(o23, make_float2(bf16_lo(rr.y), bf16_hi(rr.y)));
+              o45 = __fadd2_rn(o45, make_float2(bf16_lo(rr.z), bf16_hi(rr.z))); o67 = __fadd2_rn(o67, make_float2(bf16_lo(rr.w), bf16_hi(rr.w)));
             }
+            float o[8] = {o01.x, o01.y, o23.x, o23.y, o45.x, o45.y, o67.x, o67.y};
             if (ACT == HPE_ACT_SILU) {
 #pragma unroll
               for (int e = 0; e < 8; ++e) o[e] = silu_fast(o[e]);
