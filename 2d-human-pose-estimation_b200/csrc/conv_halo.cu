@@ -49,6 +49,10 @@ __device__ __forceinline__ float4 h_lds_f4(uint32_t addr) {
 __device__ __forceinline__ void h_sts_v4(uint32_t addr, const uint4& v) {
   asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
+__device__ __forceinline__ uint32_t h_relu2(uint32_t v) {
+  __nv_bfloat162 r = __hmax2(*reinterpret_cast<__nv_bfloat162*>(&v), __nv_bfloat162(__float2bfloat16(0.f), __float2bfloat16(0.f)));
+  return *reinterpret_cast<uint32_t*>(&r);
+}
 __device__ __forceinline__ uint32_t h_max2(uint32_t a, uint32_t b) {
   __nv_bfloat162 r = __hmax2(*reinterpret_cast<__nv_bfloat162*>(&a), *reinterpret_cast<__nv_bfloat162*>(&b));
   return *reinterpret_cast<uint32_t*>(&r);
@@ -243,14 +247,21 @@ conv_yhalo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           }
           const float sc[8] = {sa.x, sa.y, sa.z, sa.w, sb4.x, sb4.y, sb4.z, sb4.w};
           const float sh[8] = {ha.x, ha.y, ha.z, ha.w, hb.x, hb.y, hb.z, hb.w};
+          // packed fp32x2 FMAs (same bits as fmaf per element) and ReLU on the packed bf16 pairs (relu(round(x)) == round(relu(x))):
+          // 12 instead of 20 arithmetic instructions per 8 channels in an epilogue that shares its schedulers with the MMA issuers
           float o[8];
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            o[e] = fmaf(__uint_as_float(v[j * 8 + e]), sc[e], sh[e]);
-            if (ACT == HPE_ACT_RELU) o[e] = fmaxf(o[e], 0.f);
-            if (ACT == HPE_ACT_SILU) o[e] = o[e] / (1.f + __expf(-o[e]));
+          for (int e = 0; e < 8; e += 2) {
+            const float2 r = __ffma2_rn(make_float2(__uint_as_float(v[j * 8 + e]), __uint_as_float(v[j * 8 + e + 1])),
+                                        make_float2(sc[e], sc[e + 1]), make_float2(sh[e], sh[e + 1]));
+            o[e] = r.x; o[e + 1] = r.y;
+          }
+          if (ACT == HPE_ACT_SILU) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) o[e] = o[e] / (1.f + __expf(-o[e]));
           }
           uint4 pk = make_uint4(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]), pack_bf16(o[6], o[7]));
+          if (ACT == HPE_ACT_RELU) { pk.x = h_relu2(pk.x); pk.y = h_relu2(pk.y); pk.z = h_relu2(pk.z); pk.w = h_relu2(pk.w); }
           if (POOL && !inside) pk = make_uint4(0u, 0u, 0u, 0u);
           h_sts_v4(rowp + ((j ^ px) << 4), pk);                      // srow & 7 == px
         }
