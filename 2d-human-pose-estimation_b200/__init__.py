@@ -11,7 +11,7 @@ Public surface mirrors the reference's duck-typed plugin API:
 from . import _lib
 from .config import C as default_cfg, CfgNode, load_config, parse_args, update_config
 from .decode import (HostDecoder, affine_from_center_scale, decode, get_final_preds, get_final_preds_affine,
-                     get_max_preds)
+                     get_final_preds_xyv, get_max_preds)
 from .loss import JointsMSELoss, generate_target
 from . import models
 from .models import DeepPose, HeatmapPose, build_model
@@ -20,6 +20,6 @@ from .train import TrainPlan, TrainStep
 from .detpose import (OKS, OKS_SIGMAS, PCK, ComputeLoss, KeypointLoss, non_max_suppression_pose, pose_decode,
                       pose_nms_raw)
 from .posemodel import DINOv3Pose
-from .pipeline import PoseEstimator, gather_keypoints, gather_keypoints_equal, shard_range
+from .pipeline import PoseEstimator, ResultGather, gather_keypoints, gather_keypoints_equal, shard_range
 
 __version__ = "0.1.0"

@@ -31,6 +31,7 @@ SIGNATURES = {
     "hpe_last_error": (C.c_char_p, []),
     "hpe_check_device": (_i, []),
     "hpe_decode_heatmaps": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _i, _vp, _vp, _vp, _vp]),
+    "hpe_decode_heatmaps_xyv": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _i, _vp, _vp, _vp]),
     "hpe_decode_host_scratch_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "hpe_decode_heatmaps_host": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
     "hpe_joints_mse_fused": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _f, _f, _f, _vp, _vp, _vp, _f, _vp, _vp]),

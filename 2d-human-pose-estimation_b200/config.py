@@ -70,7 +70,7 @@ def _defaults() -> CfgNode:
         "train": {"batch_size": 32, "num_epochs": 100, "mini_batch_count": 1, "optimizer": "SGD",
                   "shuffle": True, "lr": 2.5e-4, "lr_step": 30, "lr_gamma": 0.1, "momentum": 0.9,
                   "weight_decay": 5e-4, "save_freq": 10, "dropLR": 5, "dropMag": 0.7},
-        "valid": {"val_interval": 5, "save_interval": 5},
+        "valid": {"val_interval": 5, "save_interval": 5},      # default.py:62-63 (they override the 3 / 5 set at :57-58)
         "test": {"batch_size": 32, "shuffle": False},
         "data": {"dataset": "MPII", "data_dir": "./data/MPII/images", "train_split": "train",
                  "val_split": "valid", "test_split": "test", "num_workers": 4, "pin_memory": True,

@@ -1028,8 +1028,9 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
   if (pl->pair) {
     // the persistent schedule strides by the number of clusters, so every cluster must be co-resident: ask the driver how
     // many 2-CTA clusters of this kernel fit (not every TPC of a B200 has both SMs enabled)
-    static int max_clusters = -1;
-    if (max_clusters < 0) {
+    // (queried per plan: the answer depends on the kernel variant, its shared memory and the current device)
+    int max_clusters = -1;
+    {
       cudaLaunchConfig_t cfg = {};
       cfg.gridDim = dim3(num_sms() / 2 * 2); cfg.blockDim = dim3(kConvThreads); cfg.dynamicSmemBytes = pl->smem;
       cudaLaunchAttribute at[1];

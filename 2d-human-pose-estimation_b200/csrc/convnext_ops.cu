@@ -456,11 +456,9 @@ extern "C" int hpe_dwconv7_bias(const void* x, int in_pitch, int B, int H, int W
   const int nblk = (th / kDtTY) * (tw / kDtRX);
   const int warps = nblk <= kDtMaxWarps ? nblk : kDtMaxWarps;
   const size_t smem = (size_t)(th + 6) * (tw + 6) * kDtSlice * 4;
-  static thread_local size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
+  // per-DEVICE function attribute: set on every call that needs it
+  if (smem > 48 * 1024)
     HPE_CUDA_OK(cudaFuncSetAttribute((const void*)dwconv7_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
   const long long grid = (long long)B * tiles_y * tiles_x * n_slices;
   if (grid > 0x7fffffffLL) return fail(HPE_EUNSUPPORTED, "hpe_dwconv7_bias: too many tiles");
   dwconv7_tiled_kernel<<<(unsigned)grid, warps * 32, smem, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, in_pitch, w_taps, bias, H, W, C, th, tw,

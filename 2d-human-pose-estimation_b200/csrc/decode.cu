@@ -29,7 +29,8 @@ template <bool BF16>
 __global__ void __launch_bounds__(kDecodeThreads, 4)
 decode_kernel(const void* __restrict__ hm, int n_maps, int K, int H, int W, int vec_ok,
               const float* __restrict__ affine, int refine,
-              float* __restrict__ coords, float* __restrict__ maxvals, int32_t* __restrict__ idx_out) {
+              float* __restrict__ coords, float* __restrict__ maxvals, int32_t* __restrict__ idx_out,
+              float* __restrict__ xyv) {
   constexpr int EPV   = BF16 ? 8 : 4;          // elements per 16-byte vector
   constexpr int ESIZE = BF16 ? 2 : 4;
   const int lane   = threadIdx.x & 31;
@@ -99,15 +100,19 @@ decode_kernel(const void* __restrict__ hm, int n_maps, int K, int H, int W, int 
         const float yi = fmaf(M[3], x, fmaf(M[4], y, M[5]));
         x = xi; y = yi;
       }
-      reinterpret_cast<float2*>(coords)[map] = make_float2(x, y);
-      maxvals[map] = best;
+      if (xyv) {                                 // packed (x, y, maxval) rows: the layout the result gather ships
+        xyv[(size_t)map * 3 + 0] = x; xyv[(size_t)map * 3 + 1] = y; xyv[(size_t)map * 3 + 2] = best;
+      } else {
+        reinterpret_cast<float2*>(coords)[map] = make_float2(x, y);
+        maxvals[map] = best;
+      }
       if (idx_out) idx_out[map] = bidx;
     }
   }
 }
 
 static int decode_launch(const void* hm, int dtype, int B, int K, int H, int W, const float* affine,
-                         int refine, float* coords, float* maxvals, int32_t* idx, cudaStream_t st) {
+                         int refine, float* coords, float* maxvals, int32_t* idx, cudaStream_t st, float* xyv = nullptr) {
   const long long n_maps_ll = (long long)B * K;
   const int n_maps = (int)n_maps_ll;
   const int esize = dtype == HPE_BF16 ? 2 : 4;
@@ -119,10 +124,10 @@ static int decode_launch(const void* hm, int dtype, int B, int K, int H, int W, 
   if (ctas > cap) ctas = cap;
   if (dtype == HPE_BF16)
     decode_kernel<true><<<(int)ctas, kDecodeThreads, 0, st>>>(hm, n_maps, K, H, W, vec_ok, affine, refine,
-                                                             coords, maxvals, idx);
+                                                             coords, maxvals, idx, xyv);
   else
     decode_kernel<false><<<(int)ctas, kDecodeThreads, 0, st>>>(hm, n_maps, K, H, W, vec_ok, affine, refine,
-                                                              coords, maxvals, idx);
+                                                              coords, maxvals, idx, xyv);
   return launch_status("decode_kernel");
 }
 
@@ -146,6 +151,13 @@ extern "C" int hpe_decode_heatmaps(const void* hm, int dtype, int B, int K, int 
   int rc = decode_check(hm, dtype, B, K, H, W, coords, maxvals);
   if (rc) return rc;
   return decode_launch(hm, dtype, B, K, H, W, affine, refine, coords, maxvals, idx, (cudaStream_t)stream);
+}
+
+extern "C" int hpe_decode_heatmaps_xyv(const void* hm, int dtype, int B, int K, int H, int W,
+                                       const float* affine, int refine, float* xyv, int32_t* idx, void* stream) {
+  int rc = decode_check(hm, dtype, B, K, H, W, xyv, xyv);
+  if (rc) return rc;
+  return decode_launch(hm, dtype, B, K, H, W, affine, refine, nullptr, nullptr, idx, (cudaStream_t)stream, xyv);
 }
 
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }

@@ -207,11 +207,9 @@ extern "C" int hpe_pose_nms(const float* pred, int B, int C, int A, int nc, int 
   int n_pow2 = 1; while (n_pow2 < A) n_pow2 <<= 1;
   const size_t smem = (size_t)n_pow2 * 8 + (size_t)(A + 31) / 32 * 4 + 16;
   if (smem > 200 * 1024) return fail(HPE_EUNSUPPORTED, "hpe_pose_nms: %d anchors need %zu B of shared memory (max 16384 anchors)", A, smem);
-  static thread_local size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
+  // the opt-in is a per-DEVICE function attribute: set it on every call that needs it (a cached flag would skip a second GPU)
+  if (smem > 48 * 1024)
     HPE_CUDA_OK(cudaFuncSetAttribute((const void*)pose_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
-  }
   pose_nms_kernel<<<B, kNmsThreads, smem, (cudaStream_t)stream>>>(pred, C, A, nc, nkpts, nk / nkpts, conf_thres, iou_thres, max_det,
                                                                  n_pow2, scratch, boxes, scores, labels, keypoints, count);
   return launch_status("pose_nms_kernel");

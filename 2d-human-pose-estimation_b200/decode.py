@@ -60,6 +60,28 @@ def get_final_preds_affine(heatmaps: torch.Tensor, affine: torch.Tensor, return_
     return (coords, maxvals, idx) if return_idx else (coords, maxvals)
 
 
+def get_final_preds_xyv(heatmaps: torch.Tensor, affine: torch.Tensor, out: torch.Tensor = None, refine: bool = True):
+    """A.2 -> A.3 -> A.4 into ONE packed tensor ``xyv[B,K,3] = (x, y, maxval)``: the row layout the data-parallel
+    result gather ships, written by the decode kernel itself -- no ``torch.cat`` afterwards."""
+    if heatmaps.dim() != 4:
+        raise ValueError(f"heatmaps must be [B,K,H,W], got {tuple(heatmaps.shape)}")
+    _lib.require_cuda(heatmaps, affine, out)
+    B, K, H, W = heatmaps.shape
+    if affine is not None and (affine.dtype != torch.float32 or tuple(affine.shape) != (B, 2, 3)):
+        raise ValueError(f"affine must be float32 [B,2,3], got {affine.dtype} {tuple(affine.shape)}")
+    if out is None:
+        out = torch.empty((B, K, 3), dtype=torch.float32, device=heatmaps.device)
+    elif out.dtype != torch.float32 or tuple(out.shape) != (B, K, 3):
+        raise ValueError(f"out must be float32 [B,K,3], got {out.dtype} {tuple(out.shape)}")
+    if B * K == 0:
+        return out
+    with torch.cuda.device(heatmaps.device):
+        rc = _lib.lib().hpe_decode_heatmaps_xyv(_lib.ptr(heatmaps), _lib.dtype_code(heatmaps), B, K, H, W, _lib.ptr(affine),
+                                                int(refine), _lib.ptr(out), 0, _lib.stream_ptr())
+    _lib.check(rc, "hpe_decode_heatmaps_xyv")
+    return out
+
+
 def get_final_preds(heatmaps: torch.Tensor, center, scale):
     """App. A.4 top level: ``preds[B,K,2]`` in image pixels and ``maxvals[B,K,1]``."""
     M = affine_from_center_scale(torch.as_tensor(center), torch.as_tensor(scale), heatmaps.shape[2:])

@@ -123,9 +123,26 @@ class HeatmapPose(nn.Module):
         self._weights_version += 1
 
     def _apply(self, fn, *a, **kw):
-        self._weights_version += 1
-        self._plans = {}
-        return super()._apply(fn, *a, **kw)
+        # The reference trainer calls ``model.to(device)`` on EVERY batch (HPE/engine/trainer.py:87): a no-op move must keep the
+        # plans (TMA maps, activation buffers, captured graph).  Plans are dropped only when a parameter really changed device,
+        # dtype or storage; the packed weights are refreshed either way (cheap, and ``fn`` may have changed values).
+        p0 = next(self.parameters(), None)
+        before = None if p0 is None else (p0.device, p0.dtype, p0.data_ptr())
+        out = super()._apply(fn, *a, **kw)
+        p1 = next(self.parameters(), None)
+        after = None if p1 is None else (p1.device, p1.dtype, p1.data_ptr())
+        if before != after:
+            self._plans = {}
+            self._layout = None
+            self._weights_version += 1
+        return out
+
+    def train(self, mode: bool = True):
+        # parameters / running statistics may have been updated in place by an optimizer or the training kernels while in
+        # training mode: every eval plan re-packs its weights and re-folds BN on the next forward (stale eval plan)
+        if mode != self.training:
+            self._weights_version += 1
+        return super().train(mode)
 
     # ---- forward -----------------------------------------------------------------------------------
     def forward(self, x: torch.Tensor) -> torch.Tensor:
@@ -139,7 +156,22 @@ class HeatmapPose(nn.Module):
             from .train import _TrainForward
             plan = self._train_plan(x)
             plan.load_weights(self)               # the optimizer updates parameters in place between steps
+            self._weights_version += 1            # ... and this step's backward/optimizer will: eval plans are stale from here on
             return _TrainForward.apply(self, x, *self.parameters())
+        # a fresh tensor, like the reference's `output = model(data)` (HPE/engine/trainer.py:90): the plan's persistent
+        # heatmap buffer is overwritten by the next call (CUDA-graph replay), so flip-test averaging / collecting outputs
+        # in a list must not alias it.  53 MB at B=256 = ~16 us; PoseEstimator and the benchmark use forward_static.
+        return self.forward_static(x).clone()
+
+    def forward_static(self, x: torch.Tensor) -> torch.Tensor:
+        """Eval forward returning the plan's PERSISTENT heatmap buffer (zero-copy): valid until the next call with
+        the same input shape.  The public ``forward`` returns a clone of it."""
+        if x.dim() != 4 or x.shape[1] != 3:
+            raise ValueError(f"expected [B,3,H,W] input, got {tuple(x.shape)}")
+        if not x.is_cuda:
+            raise RuntimeError("libhpe_b200 has no CPU path: input must live on a CUDA (sm_100a) device")
+        if self.training:
+            raise RuntimeError("forward_static is the inference path: call model.eval() first")
         key = (tuple(x.shape), x.device.index)
         plan = self._plans.get(key)
         if plan is None:
@@ -166,9 +198,9 @@ class HeatmapPose(nn.Module):
 
     def forward_features(self, x):
         """``[B, 2048, H/32, W/32]`` fp32 NCHW view of the trunk output (timm ``forward_features`` analogue)."""
-        self.forward(x)
+        self.forward_static(x)
         plan = self._plans[(tuple(x.shape), x.device.index)]
-        return plan.features.float().permute(0, 3, 1, 2)
+        return plan.features.float().permute(0, 3, 1, 2)     # .float() makes a fresh tensor
 
 
 from .posemodel import DINOv3Pose  # noqa: E402  (the reference's real pose model, HPE/models/pose.py)
@@ -299,6 +331,61 @@ class _ForwardPlan:
             layer(b[src], b[res] if res else None, b[dst], b[src2] if src2 else None)
             if dst == "stem":
                 maxpool3x3s2(b["stem"], b["pool"])
+
+    def layer_table(self):
+        """(module path, family, algorithmic FLOPs, ConvLayer, buffers) per conv launch, in launch order.  FLOPs = 2 x MAC
+        over the REAL filter taps / channels (no padding, no zero insertion); a fused projection shortcut
+        or fused final 1x1 counts the work of both convolutions."""
+        rows = []
+        for name, layer, src, res, dst, src2 in ((n, *op) for n, op in zip(self.named, self.ops)):
+            d = layer.desc
+            m = d.B * layer.Ho * layer.Wo
+            taps = {CONV_1x1: 1, CONV_3x3: 9, CONV_STEM7x7: 49, CONV_DECONV4: 4, CONV_FINAL: 1}[d.kind]
+            flops = 2.0 * m * d.Cin * d.Cout * taps + 2.0 * m * d.Cin2 * d.Cout + 2.0 * m * 256 * layer.head2
+            if name.startswith("deconv") or name == "final_layer":
+                fam = "deconv_head"
+            elif name == "backbone.conv1":
+                fam = "stem"
+            else:
+                fam = name.split(".")[1] + (".3x3" if d.kind == CONV_3x3 else ".1x1")
+            rows.append((name, fam, flops, layer, (src, res, dst, src2)))
+        return rows
+
+    def export_acts(self):
+        """NCHW fp32 CPU copies of every launch's stored inputs and output, keyed by module path: ``{"x", "res", "x2", "y"}``
+        (the stem's ``x`` is omitted: its input is the image).  Teacher-forced parity tests feed these to the fp32 oracle
+        layer by layer (tests/test_model_gpu.py)."""
+        def nchw(t):
+            return t.float().cpu() if t.dtype == torch.float32 else t.float().cpu().permute(0, 3, 1, 2).contiguous()
+        acts = {}
+        for name, (layer, src, res, dst, src2) in zip(self.named, self.ops):
+            a = {"y": nchw(self.bufs[dst])}
+            if src != "s2d":
+                a["x"] = nchw(self.bufs[src])
+            if res:
+                a["res"] = nchw(self.bufs[res])
+            if src2:
+                a["x2"] = nchw(self.bufs[src2])
+            acts[name] = a
+        return acts
+
+    def time_layers(self, reps=3):
+        """CUDA-event time of every conv launch of the step, eagerly (no graph): per launch, one untimed call then ``reps``
+        back-to-back calls between two events (the launch gap of all but the first is hidden behind the previous call).
+        Returns [(name, family, flops, microseconds)].  Diagnostic / benchmark use."""
+        b = self.bufs
+        out = []
+        for name, fam, flops, layer, (src, res, dst, src2) in self.layer_table():
+            call = lambda: layer(b[src], b[res] if res else None, b[dst], b[src2] if src2 else None)  # noqa: E731
+            call()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(reps):
+                call()
+            e1.record()
+            e1.synchronize()
+            out.append((name, fam, flops, e0.elapsed_time(e1) / reps * 1e3))
+        return out
 
     def run(self, x: torch.Tensor) -> torch.Tensor:
         preprocess(x, self.s2d)

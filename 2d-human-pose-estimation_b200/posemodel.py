@@ -397,8 +397,14 @@ class DINOv3Pose(nn.Module):
         self.to(device)
 
     def _apply(self, fn, *a, **kw):
-        self._plans = {}
-        return super()._apply(fn, *a, **kw)
+        # a no-op `.to(device)` (the reference trainer does one per batch, HPE/engine/trainer.py:87) keeps the plans
+        p0 = next(self.parameters(), None)
+        before = None if p0 is None else (p0.device, p0.dtype, p0.data_ptr())
+        out = super()._apply(fn, *a, **kw)
+        p1 = next(self.parameters(), None)
+        if before != (None if p1 is None else (p1.device, p1.dtype, p1.data_ptr())):
+            self._plans = {}
+        return out
 
     def load_state_dict(self, state_dict, strict=True, **kw):
         out = super().load_state_dict(state_dict, strict=strict, **kw)
@@ -434,5 +440,7 @@ class DINOv3Pose(nn.Module):
         plan = self._plan(x)
         levels = plan.run(x.contiguous() if x.dtype == torch.uint8 else x.float().contiguous())   # uint8 = x.float()/255 (train.py:120)
         if self.training:
-            return list(levels)                       # head.py:176-181 (forward only: no autograd graph is built)
+            # head.py:176-181 (forward only: no autograd graph is built).  Fresh tensors: the plan's level buffers are
+            # overwritten by the next call.
+            return [lv.clone() for lv in levels]
         return pose_decode(levels, self.head.nc, self.head.kpt_shape, tuple(self.head.stride.tolist()))

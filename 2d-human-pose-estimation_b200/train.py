@@ -56,8 +56,10 @@ _bn_scratch = {}
 
 
 def bn_scratch(device):
-    """One fp32 scratch per device for the per-block partial sums of the BatchNorm reductions (stream-ordered reuse)."""
-    key = torch.device(device).index
+    """One fp32 scratch per (device, stream) for the per-block partial sums of the BatchNorm reductions (stream-ordered
+    reuse; a CUDA-graph capture stream gets its own, which the graph keeps using on replay)."""
+    dev = torch.device(device)
+    key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)     # per stream: two plans on different streams must not share it
     if key not in _bn_scratch:
         _bn_scratch[key] = torch.empty(_lib.lib().hpe_bn_scratch_elems(2048), dtype=torch.float32, device=device)
     return _bn_scratch[key]
@@ -318,11 +320,20 @@ class ParamLayout:
     def __init__(self, model):
         self.names, self.offsets, self.shapes = [], {}, {}
         off = 0
-        for n, p in model.named_parameters():
-            self.names.append(n)
-            self.offsets[n] = off
-            self.shapes[n] = tuple(p.shape)
-            off += (p.numel() + 3) // 4 * 4            # keep every slice 16-byte aligned
+        params = list(model.named_parameters())
+        self.trainable_total = 0
+        # trainable parameters first: the optimizer kernel and the gradient all-reduce run over that prefix only, so
+        # `requires_grad=False` parameters (a frozen backbone) are neither updated nor weight-decayed, like torch.optim.SGD
+        for want in (True, False):
+            for n, p in params:
+                if p.requires_grad != want:
+                    continue
+                self.names.append(n)
+                self.offsets[n] = off
+                self.shapes[n] = tuple(p.shape)
+                off += (p.numel() + 3) // 4 * 4            # keep every slice 16-byte aligned
+            if want:
+                self.trainable_total = off
         self.total = off
 
     def views(self, flat):
@@ -341,7 +352,11 @@ class _TrainForward(torch.autograd.Function):
     @staticmethod
     def forward(ctx, model, x, *params):
         plan = model._train_plan(x)
-        hm = plan.forward(x.float().contiguous())
+        hm = plan.forward(x.contiguous() if x.dtype == torch.uint8 else x.float().contiguous())   # uint8 = x.float()/255 fused in
+        nbt = [m.num_batches_tracked for m in model.modules()
+               if isinstance(m, nn.BatchNorm2d) and m.num_batches_tracked is not None]
+        if nbt:
+            torch._foreach_add_(nbt, 1)              # what every torch BatchNorm does in a training forward
         ctx.model, ctx.plan = model, plan
         return hm.clone()
 
@@ -380,6 +395,14 @@ class TrainStep:
                 pv[n].copy_(p.data)
                 p.data = pv[n]
         self.grads = self.layout.views(self.flat_grad)
+        # BatchNorm `num_batches_tracked` counters re-pointed at one flat int64 buffer: ONE add per step keeps saved
+        # state_dicts identical to the reference's (torch BatchNorm increments it in every training forward)
+        bns = [m for m in model.modules() if isinstance(m, nn.BatchNorm2d) and m.num_batches_tracked is not None]
+        self.flat_nbt = torch.zeros(max(len(bns), 1), dtype=torch.int64, device=dev)
+        with torch.no_grad():
+            for i, m in enumerate(bns):
+                self.flat_nbt[i] = m.num_batches_tracked.to(dev)
+                m.num_batches_tracked.data = self.flat_nbt[i]
         self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
         self.partials = None
         self.loss = torch.zeros((), dtype=torch.float32, device=dev)
@@ -392,8 +415,9 @@ class TrainStep:
                 if b.dtype.is_floating_point:
                     dist.broadcast(b, src, group=self.group)
 
-    def _step(self, images, joints):
-        model, plan = self.model, self.plan
+    def _compute(self, images, joints):
+        """repack -> forward -> fused loss + dL/dheatmap -> backward into the flat gradient buffer (this rank's shard)."""
+        plan = self.plan
         plan.repack()                                 # parameters changed last step: re-pack bf16 GEMM operands
         hm = plan.forward(images)
         B, K, H, W = hm.shape
@@ -404,13 +428,25 @@ class TrainStep:
                                                  _lib.ptr(self.dhm), 1.0, 0, _lib.stream_ptr())
         _lib.check(rc, "hpe_joints_mse_fused")
         plan.backward(self.dhm, self.grads)
+
+    def _update(self):
+        """ONE NCCL all-reduce of the trainable prefix of the flat gradient buffer, then ONE SGD kernel over it."""
+        nt = self.layout.trainable_total
         if self.world > 1:
-            dist.all_reduce(self.flat_grad, op=dist.ReduceOp.SUM, group=self.group)
-        sgd_step(self.flat_param, self.flat_grad, self.flat_mom, self.lr, self.momentum, self.weight_decay, 1.0 / self.world)
+            dist.all_reduce(self.flat_grad[:nt], op=dist.ReduceOp.SUM, group=self.group)
+        sgd_step(self.flat_param[:nt], self.flat_grad[:nt], self.flat_mom[:nt], self.lr, self.momentum, self.weight_decay,
+                 1.0 / self.world)
+        self.flat_nbt.add_(1)
+
+    def _step(self, images, joints):
+        self._compute(images, joints)
+        self._update()
 
     def __call__(self, images, joints):
         model = self.model
-        key = (tuple(images.shape), tuple(joints.shape))
+        if images.dtype not in (torch.float32, torch.uint8):
+            raise TypeError(f"TrainStep takes float32 or uint8 images, got {images.dtype}")
+        key = (tuple(images.shape), tuple(joints.shape), images.dtype)
         if self._key != key:
             self._key, self.graph = key, None
             self.plan = model._train_plan(images)
@@ -418,7 +454,9 @@ class TrainStep:
             hm = self.plan.heatmaps
             self.dhm = torch.empty_like(hm)
             self.partials = torch.empty(hm.shape[0] * hm.shape[1], dtype=torch.float32, device=hm.device)
-            self.x_static = torch.empty_like(images, dtype=torch.float32)
+            # uint8 images stay uint8: `imgs.float() / 255` (HPE/train.py:117-120) is fused into the stem's layout kernel,
+            # exactly as in the eval forward and PoseEstimator
+            self.x_static = torch.empty_like(images)
             self.j_static = torch.empty_like(joints, dtype=torch.float32)
             self._warm = 0
         self.x_static.copy_(images)
@@ -429,12 +467,25 @@ class TrainStep:
             self._step(self.x_static, self.j_static)          # eager warm-up: encodes the TMA descriptors, NCCL init
             self._warm += 1
         else:
+            # The CUDA graph holds the ~430 compute launches of the step.  The NCCL all-reduce stays OUTSIDE it (one eager
+            # collective + the optimizer kernel per step, ~2 launches): a captured collective keeps the communicator alive
+            # inside the graph, which blocked `destroy_process_group()` at exit in round 1.
             if self.graph is None:
                 torch.cuda.synchronize(self.device)
                 g = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(g):
-                    self._step(self.x_static, self.j_static)
+                    if self.world > 1:
+                        self._compute(self.x_static, self.j_static)
+                    else:
+                        self._step(self.x_static, self.j_static)
                 self.graph = g
             self.graph.replay()
+            if self.world > 1:
+                self._update()
         model._weights_version += 1
         return self.loss
+
+    def close(self):
+        """Drop the captured graph and the plan (call before tearing the process group down)."""
+        self.graph = None
+        self._key = None

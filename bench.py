@@ -40,17 +40,51 @@ import torch  # noqa: E402
 
 METRIC = "images/sec fwd+decode @256x192 COCO-17"
 GFLOP_PER_IMG_256x192 = 8.008 + 2.846          # trunk + head, 2*MAC, no padding/zero-insertion waste
-# ncu (profiles/r01_launches_step_v4.csv): DRAM bytes of one B=256 256x192 step's conv launches / 52 launches
-NCU_DRAM_BYTES_PER_CONV_LAUNCH = round((6703 + 2672 + 407 + 204) * 1e6 / 52)
+TRAFFIC_FILE = os.path.join(ROOT, "profiles", "r02_traffic.json")     # written by tools/ncu_traffic.py from an ncu launch list
 
 
 def load_peaks():
+    """MEASURED_PEAKS.json (driver-written): `tflops_burst` = cuBLAS bf16 best-of-10, the like-for-like peak of a kernel or a
+    short K-step region at full clocks; `tflops` = the 4-second back-to-back figure, for a region long enough to be power-capped."""
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
             p = json.load(f)
-        return {"hbm": float(p["hbm_gbs"]), "tflops": float(p["bf16_tflops_sustained"]), "src": "measured"}
+        return {"hbm": float(p["hbm_gbs"]), "tflops": float(p["bf16_tflops_sustained"]), "tflops_burst": float(p["bf16_tflops"]),
+                "src": "measured"}
     except Exception:
-        return {"hbm": 6650.0, "tflops": 1400.0, "src": "fallback"}
+        return {"hbm": 6650.0, "tflops": 1400.0, "tflops_burst": 1650.0, "src": "fallback (B200_PROFILING.md)"}
+
+
+def source_hash():
+    """sha256 over the CUDA sources + the host files that decide which kernels a step launches: ties profiles/r02_traffic.json
+    (an ncu capture) to the build it was taken from."""
+    import hashlib
+    h = hashlib.sha256()
+    pkg = os.path.join(ROOT, "2d-human-pose-estimation_b200")
+    files = sorted(os.path.join(pkg, "csrc", f) for f in os.listdir(os.path.join(pkg, "csrc")))
+    files += [os.path.join(pkg, f) for f in ("conv.py", "models.py")]
+    for f in files:
+        with open(f, "rb") as fh:
+            h.update(os.path.basename(f).encode() + b"\0" + fh.read())
+    return h.hexdigest()[:16]
+
+
+def load_traffic(workload_key):
+    """DRAM bytes per launch of the dominant kernel family from the committed ncu launch list of the CURRENT build; a capture
+    taken from other sources is reported as stale (traffic null), never silently reused."""
+    try:
+        with open(TRAFFIC_FILE) as f:
+            t = json.load(f)
+    except Exception:
+        return None, "no profiles/r02_traffic.json (run tools/ncu_traffic.py on the GPU box)"
+    if t.get("workload") != workload_key:
+        return None, f"profiles/r02_traffic.json is for workload {t.get('workload')}"
+    cur = source_hash()
+    if t.get("source_hash") != cur:
+        print(f"[bench] WARNING: profiles/r02_traffic.json was captured from sources {t.get('source_hash')}, the tree is {cur}: "
+              "roofline.traffic omitted (stale capture)", file=sys.stderr)
+        return None, f"stale: captured from sources {t.get('source_hash')}, tree is {cur}"
+    return t, t.get("how", "")
 
 
 class ClockSampler(threading.Thread):
@@ -112,6 +146,16 @@ def physical_gpu_index(local):
     return local
 
 
+def workload_config(args, world):
+    """`config` of the JSON line -- identical for the B200 arm and the reference arm (same workload)."""
+    B, H, W, K = args.batch, args.height, args.width, args.joints
+    return {"workload": f"resnet50+deconv-head heatmap fwd+decode, {H}x{W}, K={K}, batch {B}/GPU, random-init weights "
+                        "(BASELINE configs[1])",
+            "global_batch": world * B, "parallelism": f"dp{world}",
+            "l2": f"inputs ({B * 3 * H * W / 1e6:.0f} MB uint8 / {B * 3 * H * W * 4 / 1e6:.0f} MB fp32 per step, 2 alternating batches) and "
+                  "every activation exceed the 126 MB L2; no flush needed"}
+
+
 # --------------------------------------------------------------------------------------------- CPU arm
 def cpu_forward_decode(batch, H, W, K, steps, warmup, threads=None):
     """The CPU restatement of the path (oracle port; the reference itself is Python/timm and cannot travel to
@@ -139,21 +183,25 @@ def cpu_forward_decode(batch, H, W, K, steps, warmup, threads=None):
 
 
 def run_reference(args):
+    """Reference arm: the reference's CPU implementation of the path (oracle port, pinned bit-identical to the reference's own
+    timm trunk) on all host threads.  Honours --steps/--warmup; each step is a bounded sample (--cpu-batch images) of the
+    B200 arm's batch, so the per-image metric is comparable."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     H, W = args.height, args.width
     batch = args.cpu_batch
-    steps, warmup = min(args.steps, 10), min(args.warmup, 2)
-    ips, mean, nthr = cpu_forward_decode(batch, H, W, args.joints, steps, max(warmup, 1))
+    steps, warmup = max(args.steps, 1), max(args.warmup, 1)
+    ips, mean, nthr = cpu_forward_decode(batch, H, W, args.joints, steps, warmup)
     line = {
         "impl": "reference", "metric": METRIC, "value": round(ips, 3), "unit": "images/s", "n_gpus": args.gpus,
-        "steps": steps, "warmup": max(warmup, 1), "ms_per_step": round(mean * 1e3, 3), "higher_is_better": True,
+        "steps": steps, "warmup": warmup, "ms_per_step": round(mean * 1e3, 3), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"resnet50+deconv-head heatmap fwd+decode, {H}x{W}, K={args.joints}, CPU sample of {batch} images/step "
-                               f"(GPU arm: {args.batch}/GPU), random-init weights"},
+        "config": workload_config(args, world),
         "cpu_baseline": {"value": round(ips, 3), "unit": "images/s", "cores": nthr, "kind": "port",
-                         "sample": f"{steps} steps x {batch} images, torch fp32 {nthr} threads + numpy decode"},
+                         "sample": f"{steps} steps x {batch} images (bounded sample of the {args.batch}-image batch), torch fp32 "
+                                   f"{nthr} threads + numpy decode"},
         "e2e": {"value": round(ips, 3), "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -161,285 +209,361 @@ def run_reference(args):
 
 
 # --------------------------------------------------------------------------------------------- GPU arm
-def run_b200(args):
-    import torch.distributed as dist
-    import hpe_b200 as hpe
+class Ctx:
+    """Process-wide state of the B200 arm: rank layout, device, process group, barrier and max-over-ranks helpers."""
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise RuntimeError("bench.py: no CUDA device; the B200 arm has no CPU fallback (use --impl reference for the CPU arm)")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
-    hpe._lib.check(hpe._lib.lib().hpe_check_device(), "hpe_check_device")
+    def __init__(self, what):
+        import torch.distributed as dist
+        self.dist = dist
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise RuntimeError(f"bench.py {what}: no CUDA device; the B200 arm has no CPU fallback (use --impl reference for the CPU arm)")
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        if self.world > 1:
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            dist.init_process_group("nccl", device_id=self.dev)
 
-    B, H, W, K = args.batch, args.height, args.width, args.joints
-    torch.manual_seed(0)
-    model = hpe.HeatmapPose(K, "resnet50", pretrained=False)
-    g = torch.Generator().manual_seed(1)
-    for m in model.modules():               # random-init net with randomised BN so it is not degenerate
-        if isinstance(m, torch.nn.BatchNorm2d):
-            m.weight.data.copy_(torch.rand(m.weight.shape, generator=g) + 0.5)
-            m.bias.data.copy_(torch.randn(m.bias.shape, generator=g) * 0.1)
-            m.running_mean.copy_(torch.randn(m.running_mean.shape, generator=g) * 0.1)
-            m.running_var.copy_(torch.rand(m.running_var.shape, generator=g) + 0.5)
-    model = model.to(dev).eval()
-    est = hpe.PoseEstimator(model, dev)
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier(device_ids=[self.local])
+        torch.cuda.synchronize(self.dev)
 
-    gen = torch.Generator().manual_seed(100 + rank)
-    h_img = [torch.rand(B, 3, H, W, generator=gen).pin_memory() for _ in range(2)]
-    x = [t.to(dev) for t in h_img]
-    from_center = torch.rand(B, 2, generator=gen) * torch.tensor([640.0, 480.0])
-    sw = torch.rand(B, 1, generator=gen) * 2 + 0.5
-    h_aff = hpe.affine_from_center_scale(from_center, torch.cat([sw, sw * 4 / 3], 1), (H // 4, W // 4)).pin_memory()
-    aff = h_aff.to(dev)
-    gathered = torch.empty((world * B, K, 3), dtype=torch.float32, device=dev) if world > 1 else None
+    def max_over_ranks(self, v):
+        t = torch.tensor([float(v)], dtype=torch.float64, device=self.dev)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
 
-    ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
-    marks = []
+    def sampler(self):
+        return ClockSampler(physical_gpu_index(self.local)) if self.rank == 0 else None
 
-    def step(i, record=False):
-        if record:
-            e0 = ev(); e0.record()
-        hm = model(x[i & 1])
-        if record:
-            e1 = ev(); e1.record()
-        preds, maxvals = hpe.get_final_preds_affine(hm, aff)
-        if record:
-            e2 = ev(); e2.record()
-            marks.append((e0, e1, e2))
-        if world > 1:
-            return hpe.gather_keypoints_equal(preds, maxvals, gathered)
-        return preds
+    def close(self):
+        if self.world > 1:
+            self.barrier()
+            self.dist.destroy_process_group()
 
-    def barrier():
-        if world > 1:
-            dist.barrier(device_ids=[local])
-        torch.cuda.synchronize(dev)
 
-    for i in range(max(args.warmup, 3)):
-        step(i)
-    barrier()
-    sampler = ClockSampler(physical_gpu_index(local)) if rank == 0 else None
+def ev():
+    return torch.cuda.Event(enable_timing=True)
+
+
+def timed(ctx, step, steps):
+    """Barrier + synchronize, EXACTLY `steps` calls of step(i) between two CUDA events on the launching stream, barrier +
+    synchronize; returns (ms over the region as the MAX over ranks, clock record of rank 0)."""
+    sampler = ctx.sampler()
     if sampler:
         sampler.start()
     start, end = ev(), ev()
-    barrier()
+    ctx.barrier()
     start.record()
-    for i in range(args.steps):
-        step(i, record=True)
+    for i in range(steps):
+        step(i)
     end.record()
-    barrier()
+    ctx.barrier()
     clocks = sampler.stop() if sampler else None
-    ms_total = start.elapsed_time(end)
-    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total = float(t.item())
+    return ctx.max_over_ranks(start.elapsed_time(end)), clocks
+
+
+def make_model(hpe, K, dev, train=False):
+    """random-init net with randomised BatchNorm so it is not degenerate (timm zero-inits every block's last gamma)."""
+    torch.manual_seed(0)
+    model = hpe.HeatmapPose(K, "resnet50", pretrained=False)
+    g = torch.Generator().manual_seed(1)
+    for n, m in model.named_modules():
+        if isinstance(m, torch.nn.BatchNorm2d):
+            m.weight.data.copy_((torch.rand(m.weight.shape, generator=g) + 0.5) * (0.1 if (train and n.endswith("bn3")) else 1.0))
+            m.bias.data.copy_(torch.randn(m.bias.shape, generator=g) * 0.1)
+            if not train:
+                m.running_mean.copy_(torch.randn(m.running_mean.shape, generator=g) * 0.1)
+                m.running_var.copy_(torch.rand(m.running_var.shape, generator=g) + 0.5)
+    model = model.to(dev)
+    return model.train() if train else model.eval()
+
+
+def infer_setup(hpe, ctx, model, B, H, W, K, seed=100):
+    """Synthetic inputs of one rank: two alternating uint8 host batches (the reference's host format, HPE/train.py:117-120),
+    their fp32 twins (= u8 / 255, what the reference uploads after `.float() / 255`), device copies, per-sample affines."""
+    gen = torch.Generator().manual_seed(seed + ctx.rank)
+    h_u8 = [torch.randint(0, 256, (B, 3, H, W), generator=gen, dtype=torch.uint8).pin_memory() for _ in range(2)]
+    center = torch.rand(B, 2, generator=gen) * torch.tensor([640.0, 480.0])
+    sw = torch.rand(B, 1, generator=gen) * 2 + 0.5
+    h_aff = hpe.affine_from_center_scale(center, torch.cat([sw, sw * 4 / 3], 1), (H // 4, W // 4)).pin_memory()
+    return {"h_u8": h_u8, "h_aff": h_aff, "x": [t.to(ctx.dev).float().div_(255.0) for t in h_u8], "aff": h_aff.to(ctx.dev),
+            "rg": hpe.ResultGather(B, K, ctx.dev)}
+
+
+def infer_step_fn(hpe, model, s, marks=None):
+    """One step of the hot path on device-resident inputs: forward -> decode (packed x,y,maxval rows written by the decode
+    kernel) -> result all-gather on a side stream when N > 1."""
+    rg = s["rg"]
+
+    def step(i):
+        if marks is not None:
+            e0 = ev(); e0.record()
+        hm = model.forward_static(s["x"][i & 1])
+        if marks is not None:
+            e1 = ev(); e1.record()
+        hpe.get_final_preds_xyv(hm, s["aff"], rg.slot())
+        if marks is not None:
+            e2 = ev(); e2.record()
+            marks.append((e0, e1, e2))
+        return rg.gather()
+    return step
+
+
+def e2e_region(ctx, est, host_batches, steps):
+    """`steps` batches through PoseEstimator.stream (pinned host images in, keypoints read on the host); CUDA events around the
+    whole loop on the compute stream (the last D2H is waited for by the generator before the end event), max over ranks."""
+    for _ in est.stream(host_batches(3)):
+        pass
+    ctx.barrier()
+    t0 = time.perf_counter()
+    a, b = ev(), ev()
+    a.record()
+    checksum = 0.0
+    for preds_h, maxvals_h in est.stream(host_batches(steps)):
+        checksum += float(maxvals_h[0, 0, 0])
+    b.record()
+    ctx.barrier()
+    wall = (time.perf_counter() - t0) * 1e3
+    return ctx.max_over_ranks(max(a.elapsed_time(b), 0.0)), wall, checksum
+
+
+def decode_sweep(hpe, dev, K, H, W, peaks):
+    """Decode at an HBM-saturating size (BASELINE configs[4] sweep point: K=17, 64x48, fp32, 16384 x 17 maps = 3.4 GB, far
+    beyond the 126 MB L2): the "decode HBM GB/s vs peak" half of the metric.  The in-step decode is 53 MB."""
+    SB = 16384
+    big = torch.rand(SB, K, H // 4, W // 4, device=dev)
+    big_aff = torch.rand(SB, 2, 3, device=dev)
+    out = torch.empty(SB, K, 3, device=dev)
+    for _ in range(3):
+        hpe.get_final_preds_xyv(big, big_aff, out)
+    torch.cuda.synchronize(dev)
+    ts = []
+    for _ in range(10):
+        a, b = ev(), ev()
+        a.record(); hpe.get_final_preds_xyv(big, big_aff, out); b.record(); torch.cuda.synchronize(dev)
+        ts.append(a.elapsed_time(b))
+    ms = sum(ts) / len(ts)
+    nbytes = big.numel() * 4 + SB * 24 + SB * K * 12
+    gbs = nbytes / (ms * 1e-3) / 1e9
+    return {"bound": "hbm", "kernel": "decode_kernel", "achieved": round(gbs, 1), "peak": peaks["hbm"], "unit": "GB/s",
+            "frac": round(gbs / peaks["hbm"], 4), "traffic": None,
+            "workload": f"decode sweep point: {SB} x {K} maps of {H // 4}x{W // 4} fp32 ({nbytes / 1e9:.1f} GB, > L2), {ms:.3f} ms/launch, "
+                        "mean of 10 launches (CUDA events)",
+            "algorithmic_bytes_per_map": (H // 4) * (W // 4) * 4 + 12}
+
+
+def per_kernel_table(model, x, peaks):
+    """roofline.per_kernel: CUDA-event time of every conv launch of ONE un-graphed step, summed by family
+    (stem / 1x1 and 3x3 by stage / deconv head), with TFLOP/s and the fraction of the burst tensor peak."""
+    model.forward_static(x)
+    plan = model._plans[(tuple(x.shape), x.device.index)]
+    rows = plan.time_layers(reps=3)
+    fam = {}
+    for name, f, flops, us in rows:
+        d = fam.setdefault(f, {"launches": 0, "us": 0.0, "gflop": 0.0})
+        d["launches"] += 1; d["us"] += us; d["gflop"] += flops / 1e9
+    out = {}
+    for f, d in fam.items():
+        tf = d["gflop"] / 1e3 / (d["us"] * 1e-6) if d["us"] > 0 else 0.0
+        out[f] = {"launches": d["launches"], "us_per_step": round(d["us"], 1), "tflops": round(tf, 1),
+                  "frac_burst": round(tf / peaks["tflops_burst"], 3)}
+    return out, rows
+
+
+def hires_subbench(hpe, ctx, model, args, peaks):
+    """BASELINE configs[3]: 384x288 input -> 96x72 heatmaps, 64 images per GPU (B=512 over 8 GPUs), forward + decode
+    (+ result all-gather), same model and kernels, its own timed region."""
+    B, H, W, K = args.hires_batch, 384, 288, args.joints
+    s = infer_setup(hpe, ctx, model, B, H, W, K, seed=300)
+    step = infer_step_fn(hpe, model, s)
+    for i in range(3):
+        step(i)
+    s["rg"].wait()
+    steps = max(args.steps, 10)
+    ms_total, clocks = timed(ctx, lambda i: step(i), steps)
+    s["rg"].wait()
+    ms = ms_total / steps
+    tf = GFLOP_PER_IMG_256x192 * 2.25 * 1e9 * B / (ms * 1e-3) / 1e12
+    return {"workload": f"384x288 -> 96x72 heatmaps, K={K}, batch {B}/GPU fwd+decode (BASELINE configs[3]: B={B * ctx.world} over {ctx.world} GPUs)",
+            "value": round(ctx.world * B * steps / ms_total * 1e3, 1), "unit": "images/s", "ms_per_step": round(ms, 4), "steps": steps,
+            "tflops_per_gpu": round(tf, 1), "frac_burst": round(tf / peaks["tflops_burst"], 4), "clocks": clocks}
+
+
+def train_subbench(hpe, ctx, args, peaks):
+    """BASELINE configs[2]: the data-parallel training step (batch-stat BN per rank, fused Gaussian-target JointsMSE, dgrad +
+    wgrad, ONE NCCL all-reduce of the flat fp32 gradient buffer, SGD momentum) at N GPUs, >= 10 timed steps."""
+    B, H, W, K = args.batch, args.height, args.width, args.joints
+    model = make_model(hpe, K, ctx.dev, train=True)
+    step = hpe.TrainStep(model, lr=1e-3, momentum=0.9, weight_decay=1e-4, cuda_graph=not args.no_graph)
+    step.broadcast_parameters(0)
+    gen = torch.Generator().manual_seed(200 + ctx.rank)
+    x = [torch.rand(B, 3, H, W, generator=gen).to(ctx.dev) for _ in range(2)]
+    joints = torch.rand(B, K, 3, generator=gen) * torch.tensor([float(W), float(H), 1.0]) + torch.tensor([0.0, 0.0, 0.3])
+    joints = joints.to(ctx.dev).contiguous()
+    for i in range(3):
+        step(x[i & 1], joints)
+    steps = max(args.steps, 10)
+    ms_total, clocks = timed(ctx, lambda i: step(x[i & 1], joints), steps)
+    loss = float(step.loss.item())
+    ms = ms_total / steps
+    tf = 3 * GFLOP_PER_IMG_256x192 * 1e9 * (H * W) / (256 * 192) * B / (ms * 1e-3) / 1e12      # fwd + dgrad + wgrad
+    nbytes = step.layout.trainable_total * 4
+    out = {"workload": f"resnet50+deconv-head data-parallel training step, {H}x{W}, K={K}, batch {B}/GPU (BASELINE configs[2]); "
+                       "per-rank BatchNorm statistics and averaged gradients as under the reference's DDP wrap (pose/pose/core/builder.py:92-123)",
+           "value": round(ctx.world * B * steps / ms_total * 1e3, 1), "unit": "images/s", "ms_per_step": round(ms, 4), "steps": steps,
+           "allreduce_bytes_per_step": nbytes if ctx.world > 1 else 0, "allreduce": "one NCCL all-reduce(sum) of the flat fp32 gradient buffer" if ctx.world > 1 else "none (1 GPU)",
+           "tflops_per_gpu": round(tf, 1), "frac_burst": round(tf / peaks["tflops_burst"], 4),
+           "frac_sustained": round(tf / peaks["tflops"], 4), "loss": loss, "clocks": clocks}
+    step.close()
+    del step, model
+    torch.cuda.empty_cache()
+    return out
+
+
+def run_b200(args):
+    import hpe_b200 as hpe
+    ctx = Ctx("(B200 arm)")
+    dev, world, rank = ctx.dev, ctx.world, ctx.rank
+    hpe._lib.check(hpe._lib.lib().hpe_check_device(), "hpe_check_device")
+    B, H, W, K = args.batch, args.height, args.width, args.joints
+    peaks = load_peaks()
+    model = make_model(hpe, K, dev)
+    est = hpe.PoseEstimator(model, dev)
+    s = infer_setup(hpe, ctx, model, B, H, W, K)
+    warm = max(args.warmup, 3)
+
+    # ---- headline `value`: inputs resident in HBM, EXACTLY --steps steps, device-timed, max over ranks
+    marks = []
+    step_plain, step_marked = infer_step_fn(hpe, model, s), infer_step_fn(hpe, model, s, marks)
+    for i in range(warm):
+        step_plain(i)
+    s["rg"].wait()
+    ms_total, clocks = timed(ctx, step_marked, args.steps)
+    s["rg"].wait()
+    torch.cuda.synchronize(dev)
     fwd_ms = sum(a.elapsed_time(b) for a, b, _ in marks) / len(marks)
     dec_ms = sum(b.elapsed_time(c) for _, b, c in marks) / len(marks)
 
-    # ---- e2e: pinned host images in, keypoints read on the host every step (public API, H2D overlapped)
-    def host_batches(n):
-        for i in range(n):
-            yield h_img[i & 1], h_aff
-    for _ in est.stream(host_batches(3)):
-        pass
-    barrier()
-    t0 = time.perf_counter()
-    e_start, e_end = ev(), ev()
-    e_start.record()
-    checksum = 0.0
-    for preds_h, maxvals_h in est.stream(host_batches(args.steps)):
-        checksum += float(maxvals_h[0, 0, 0])
-    e_end.record()
-    barrier()
-    e2e_ms = e_start.elapsed_time(e_end)
-    e2e_wall_ms = (time.perf_counter() - t0) * 1e3
-    te = torch.tensor([max(e2e_ms, 0.0)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    e2e_ms = float(te.item())
-
-    # ---- decode at an HBM-saturating size (BASELINE configs[4] sweep point: K=17, 64x48, fp32, 16384 maps x 17 joints = 3.4 GB,
-    # far beyond the 126 MB L2): the "decode HBM GB/s vs peak" half of the metric.  The in-step decode above is 53 MB.
-    sweep = None
-    if rank == 0:
-        SB = 16384
-        big = torch.rand(SB, K, H // 4, W // 4, device=dev)
-        big_aff = torch.rand(SB, 2, 3, device=dev)
-        for _ in range(3):
-            hpe.get_final_preds_affine(big, big_aff)
+    # ---- the same step for >= 2 s back to back: the power-capped (sustained) regime, with its own clock record
+    n_sus = int(min(args.sustain_s * 1e3 / (ms_total / args.steps) + 1, 5000)) if args.sustain_s > 0 else 0
+    sus = None
+    if n_sus:
+        marks_s = []
+        step_s = infer_step_fn(hpe, model, s, marks_s)
+        sus_ms_total, sus_clocks = timed(ctx, step_s, n_sus)
+        s["rg"].wait()
         torch.cuda.synchronize(dev)
-        ts = []
-        for _ in range(10):
-            a, b = ev(), ev()
-            a.record(); hpe.get_final_preds_affine(big, big_aff); b.record(); torch.cuda.synchronize(dev)
-            ts.append(a.elapsed_time(b))
-        sweep_ms = sum(ts) / len(ts)
-        sweep_bytes = big.numel() * 4 + SB * 24 + SB * K * 16
-        sweep = {"B": SB, "ms": sweep_ms, "gbs": sweep_bytes / (sweep_ms * 1e-3) / 1e9}
-        del big, big_aff
+        sus = {"steps": n_sus, "seconds": round(sus_ms_total / 1e3, 3), "ms_per_step": round(sus_ms_total / n_sus, 4),
+               "ms_forward": round(sum(a.elapsed_time(b) for a, b, _ in marks_s) / len(marks_s), 4), "clocks": sus_clocks,
+               "value": round(world * B * n_sus / sus_ms_total * 1e3, 1)}
 
-    # ---- same e2e with uint8 host images (the reference's real input, HPE/train.py:117-120: `imgs.float() / 255.0` fused into the stem)
-    h_u8 = [(t * 255).to(torch.uint8).pin_memory() for t in h_img]
+    # ---- e2e through the public host-buffer API: uint8 host images (the reference's real input type) = the headline;
+    # fp32 host images (4x the H2D bytes) as the secondary number
+    u_ms, u_wall, chk = e2e_region(ctx, est, lambda n: ((s["h_u8"][i & 1], s["h_aff"]) for i in range(n)), args.steps)
+    h_f32 = [t.float().div_(255.0).pin_memory() for t in s["h_u8"]]
+    f_ms, f_wall, chk2 = e2e_region(ctx, est, lambda n: ((h_f32[i & 1], s["h_aff"]) for i in range(n)), args.steps)
+    del h_f32
 
-    def host_batches_u8(n):
-        for i in range(n):
-            yield h_u8[i & 1], h_aff
-    for _ in est.stream(host_batches_u8(3)):
-        pass
-    barrier()
-    u_start, u_end = ev(), ev()
-    u_start.record()
-    for preds_h, maxvals_h in est.stream(host_batches_u8(args.steps)):
-        checksum += float(maxvals_h[0, 0, 0])
-    u_end.record()
-    barrier()
-    tu = torch.tensor([u_start.elapsed_time(u_end)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(tu, op=dist.ReduceOp.MAX)
-    e2e_u8_ms = float(tu.item())
+    sweep = per_kernel = hires = train = None
+    if rank == 0 and not args.quick:
+        sweep = decode_sweep(hpe, dev, K, H, W, peaks)
+        per_kernel, layer_rows = per_kernel_table(model, s["x"][0], peaks)
+        if args.layers_log:
+            with open(args.layers_log, "w") as f:
+                for name, famn, flops, us in layer_rows:
+                    f.write(f"{name:34s} {famn:14s} {us:8.1f} us {flops / 1e6 / us if us else 0:8.1f} TFLOP/s\n")
+    ctx.barrier()
+    if not args.quick and not args.no_hires:
+        hires = hires_subbench(hpe, ctx, model, args, peaks)
+    plan = next(iter(model._plans.values()))
+    launches_per_step = plan.n_launches + 1 + (1 if world > 1 else 0)        # preprocess + convs, decode, (NCCL all-gather)
+    own_launches_per_step = plan.n_launches + 1
+    del est, s, model
+    torch.cuda.empty_cache()
+    if not args.quick and not args.no_train:
+        train = train_subbench(hpe, ctx, args, peaks)
 
     if rank == 0:
-        peaks = load_peaks()
-        plan = next(iter(model._plans.values()))
-        launches_per_step = plan.n_launches + 1
         img_scale = (H * W) / (256 * 192)
         flops_step = GFLOP_PER_IMG_256x192 * 1e9 * img_scale * B
-        dec_bytes = B * K * (H // 4) * (W // 4) * 4 + B * 24 + B * K * 16
+        tf = flops_step / (fwd_ms * 1e-3) / 1e12
+        dec_bytes = B * K * (H // 4) * (W // 4) * 4 + B * 24 + B * K * 12
         total_imgs = world * B * args.steps
+        traffic, traffic_note = load_traffic(f"{B}x{H}x{W}x{K}")
+        roof = {"bound": "tensor",
+                "kernel": "conv_gemm_kernel + conv_yhalo_kernel (every conv launch of the step: stem with the max-pool in its epilogue, trunk with the "
+                          "projection shortcuts fused into conv3, deconv head with the final 1x1 fused into its last stage)",
+                "achieved": round(tf, 2), "peak": peaks["tflops_burst"], "unit": "TFLOP/s", "frac": round(tf / peaks["tflops_burst"], 4),
+                "peak_source": f"{peaks['src']} bf16_tflops (burst: the --steps region lasts {ms_total / 1e3:.2f} s at full clocks)",
+                "frac_burst": round(tf / peaks["tflops_burst"], 4),
+                "traffic": traffic["dram_bytes_per_conv_launch"] if traffic else None, "traffic_source": traffic_note,
+                "ms_forward": round(fwd_ms, 4),
+                "note": "algorithmic FLOPs of the step (10.854 GFLOP/image, SURVEY §8d) / CUDA-event time of the forward graph (incl. preprocess)",
+                "per_kernel": per_kernel}
+        if sus:
+            tfs = flops_step / (sus["ms_forward"] * 1e-3) / 1e12
+            roof["frac_sustained"] = round(tfs / peaks["tflops"], 4)
+            roof["sustained"] = dict(sus, achieved=round(tfs, 2), peak=peaks["tflops"],
+                                     peak_source=f"{peaks['src']} bf16_tflops_sustained (4 s of back-to-back cuBLAS)")
         line = {
             "metric": METRIC, "value": round(total_imgs / ms_total * 1e3, 1), "unit": "images/s", "n_gpus": world,
-            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(ms_total / args.steps, 4),
+            "steps": args.steps, "warmup": warm, "ms_per_step": round(ms_total / args.steps, 4),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": f"resnet50+deconv-head heatmap fwd+decode, {H}x{W}, K={K}, batch {B}/GPU, bf16 (fp32 accum), "
-                                   "random-init weights (BASELINE configs[1])",
-                       "global_batch": world * B, "parallelism": f"dp{world}",
-                       "l2": "inputs (151 MB/step, 2 alternating batches) and every activation exceed the 126 MB L2; no flush needed"},
-            "roofline": {"bound": "tensor", "kernel": "conv_gemm_kernel + conv_yhalo_kernel (52 launches/step: stem with the max-pool in its epilogue, trunk with the projection "
-                                                      "shortcuts fused into conv3, deconv head with the final 1x1 fused into its last stage; 256-wide tiles as cta_group::2 pairs)",
-                         "achieved": round(flops_step / (fwd_ms * 1e-3) / 1e12, 2), "peak": peaks["tflops"], "unit": "TFLOP/s",
-                         "frac": round(flops_step / (fwd_ms * 1e-3) / 1e12 / peaks["tflops"], 4),
-                         "traffic": NCU_DRAM_BYTES_PER_CONV_LAUNCH if (B, H, W, K) == (256, 256, 192, 17) else None,
-                         "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum averaged over the step's 52 conv launches "
-                                           "(9.99 GB / step vs 11.8 GB of per-layer algorithmic input+output+residual+weight bytes: part of each layer's input is still in L2, no re-reads), profiles/r01_launches_step_v4.csv",
-                         "peak_source": f"{peaks['src']} bf16_tflops_sustained (kernel timed inside a long step)",
-                         "ms_forward": round(fwd_ms, 4),
-                         "note": "algorithmic FLOPs of the step / CUDA-event time of the forward graph (incl. preprocess; the max-pool runs in the stem's epilogue)"},
-            "decode_roofline": {"bound": "hbm", "kernel": "decode_kernel", "achieved": round(sweep["gbs"], 1), "peak": peaks["hbm"],
-                                "unit": "GB/s", "frac": round(sweep["gbs"] / peaks["hbm"], 4), "traffic": None,
-                                "workload": f"decode sweep point: {sweep['B']} x {K} maps of {H // 4}x{W // 4} fp32 (3.4 GB, > L2), "
-                                            f"{sweep['ms']:.3f} ms/launch, mean of 10 launches (CUDA events)",
-                                "algorithmic_bytes_per_map": (H // 4) * (W // 4) * 4 + 16,
-                                "in_step": {"ms_decode": round(dec_ms, 4), "achieved": round(dec_bytes / (dec_ms * 1e-3) / 1e9, 1),
-                                            "note": "the step's own 53 MB of heatmaps is launch/latency-bound, not bandwidth-bound"}},
-            "e2e": {"value": round(total_imgs / e2e_ms * 1e3, 1), "unit": "images/s",
-                    "h2d_bytes_per_step": B * 3 * H * W * 4 + B * 24, "d2h_bytes_per_step": B * K * 3 * 4,
-                    "ms_per_step": round(e2e_ms / args.steps, 4), "wall_ms_per_step": round(e2e_wall_ms / args.steps, 4),
-                    "api": "PoseEstimator.stream (pinned host fp32 images -> H2D overlapped on a side stream -> forward -> decode -> D2H)",
-                    "uint8_images": {"value": round(total_imgs / e2e_u8_ms * 1e3, 1), "h2d_bytes_per_step": B * 3 * H * W + B * 24,
-                                     "note": "same call with uint8 host images (/255 fused into the stem, HPE/train.py:117-120)"}},
-            "gpu_launches": launches_per_step * args.steps,
-            "gpu_launches_per_step": launches_per_step,
+            "config": workload_config(args, world),
+            "roofline": roof,
+            "e2e": {"value": round(total_imgs / u_ms * 1e3, 1), "unit": "images/s",
+                    "h2d_bytes_per_step": B * 3 * H * W + B * 24, "d2h_bytes_per_step": B * K * 3 * 4,
+                    "ms_per_step": round(u_ms / args.steps, 4), "wall_ms_per_step": round(u_wall / args.steps, 4),
+                    "api": "PoseEstimator.stream: pinned host uint8 images (the reference's host format, HPE/train.py:117-120, HPE/test.py:16-29; "
+                           "/255 fused into the stem) -> H2D on a copy stream -> forward -> decode -> D2H of the packed keypoints on a third "
+                           "stream, two-deep result ring",
+                    "fp32_images": {"value": round(total_imgs / f_ms * 1e3, 1), "h2d_bytes_per_step": B * 3 * H * W * 4 + B * 24,
+                                    "ms_per_step": round(f_ms / args.steps, 4),
+                                    "note": "same call with fp32 host images (4x the H2D bytes: PCIe / host-DRAM bound at N >= 4)"}},
+            "gpu_launches": own_launches_per_step * args.steps,
+            "gpu_launches_per_step": own_launches_per_step,
+            "launches_per_step_incl_nccl": launches_per_step,
             "clocks": clocks,
         }
+        if sweep:
+            sweep["in_step"] = {"ms_decode": round(dec_ms, 4), "achieved": round(dec_bytes / (dec_ms * 1e-3) / 1e9, 1),
+                                "note": "the step's own 53 MB of heatmaps is launch/latency-bound, not bandwidth-bound"}
+            line["decode_roofline"] = sweep
+        if hires:
+            line["hires"] = hires
+        if train:
+            line["train"] = train
         if world == 1 and not args.no_cpu_baseline:
             ips, mean, nthr = cpu_forward_decode(args.cpu_batch, H, W, K, 3, 1)
             line["cpu_baseline"] = {"value": round(ips, 3), "unit": "images/s", "cores": nthr, "kind": "port",
                                     "sample": f"3 steps x {args.cpu_batch} images of the same workload (torch fp32 ResNet-50+head on "
                                               f"{nthr} threads + numpy decode), {mean:.2f} s/step"}
         emit(line)
-    if world > 1:
-        dist.destroy_process_group()
+    ctx.close()
 
 
 def run_train(args):
-    """BASELINE configs[2]: data-parallel training step (forward with batch-stat BN, fused Gaussian-target MSE loss,
-    backward through dgrad/wgrad, ONE NCCL all-reduce of the flat fp32 gradient buffer, SGD) at N GPUs."""
-    import torch.distributed as dist
+    """`--mode train`: BASELINE configs[2] alone, as its own JSON line (the default mode carries the same numbers as `train`)."""
     import hpe_b200 as hpe
-
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise RuntimeError("bench.py --mode train: no CUDA device (no CPU fallback)")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
-    B, H, W, K = args.batch, args.height, args.width, args.joints
-    torch.manual_seed(0)
-    model = hpe.HeatmapPose(K, "resnet50", pretrained=False)
-    g = torch.Generator().manual_seed(1)
-    for n, m in model.named_modules():
-        if isinstance(m, torch.nn.BatchNorm2d):
-            m.weight.data.copy_((torch.rand(m.weight.shape, generator=g) + 0.5) * (0.1 if n.endswith("bn3") else 1.0))
-            m.bias.data.copy_(torch.randn(m.bias.shape, generator=g) * 0.1)
-    model = model.to(dev).train()
-    step = hpe.TrainStep(model, lr=1e-3, momentum=0.9, weight_decay=1e-4, cuda_graph=not args.no_graph)
-    step.broadcast_parameters(0)
-    gen = torch.Generator().manual_seed(100 + rank)
-    x = [torch.rand(B, 3, H, W, generator=gen).to(dev) for _ in range(2)]
-    joints = torch.rand(B, K, 3, generator=gen) * torch.tensor([float(W), float(H), 1.0]) + torch.tensor([0.0, 0.0, 0.3])
-    joints = joints.to(dev).contiguous()
-
-    def barrier():
-        if world > 1:
-            dist.barrier(device_ids=[local])
-        torch.cuda.synchronize(dev)
-
-    for i in range(max(args.warmup, 3)):
-        step(x[i & 1], joints)
-    barrier()
-    sampler = ClockSampler(physical_gpu_index(local)) if rank == 0 else None
-    if sampler:
-        sampler.start()
-    ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
-    start, end = ev(), ev()
-    barrier()
-    start.record()
-    for i in range(args.steps):
-        loss = step(x[i & 1], joints)
-    end.record()
-    barrier()
-    clocks = sampler.stop() if sampler else None
-    t = torch.tensor([start.elapsed_time(end)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total = float(t.item())
-    if rank == 0:
-        peaks = load_peaks()
-        flops_step = 3 * GFLOP_PER_IMG_256x192 * 1e9 * (H * W) / (256 * 192) * B      # fwd + dgrad + wgrad
-        ms = ms_total / args.steps
-        line = {
-            "metric": "images/sec train step @256x192 COCO-17", "value": round(world * B * args.steps / ms_total * 1e3, 1),
-            "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": round(ms, 4),
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": f"resnet50+deconv-head data-parallel training step (batch-stat BN, fused Gaussian-target JointsMSE, "
-                                   f"dgrad+wgrad, NCCL all-reduce of {step.layout.total * 4 / 1e6:.0f} MB fp32 grads, SGD momentum), "
-                                   f"{H}x{W}, K={K}, batch {B}/GPU (BASELINE configs[2])",
-                       "global_batch": world * B, "parallelism": f"dp{world}"},
-            "roofline": {"bound": "tensor", "kernel": "conv_gemm_kernel + wgrad_gemm_kernel (whole step)",
-                         "achieved": round(flops_step / (ms * 1e-3) / 1e12, 2), "peak": peaks["tflops"], "unit": "TFLOP/s",
-                         "frac": round(flops_step / (ms * 1e-3) / 1e12 / peaks["tflops"], 4), "traffic": None,
-                         "note": "3x forward algorithmic FLOPs / step time; the step also contains the HBM-bound BN passes"},
-            "loss": float(loss.item()), "clocks": clocks,
-        }
-        emit(line)
-    if world > 1:
-        # a live captured graph that contains the NCCL all-reduce has been seen to block communicator teardown:
-        # drop the graph first, and leave without the teardown once every rank is done
-        step.graph = None
-        barrier()
-        sys.stdout.flush(); sys.stderr.flush()
-        os._exit(0)
+    ctx = Ctx("--mode train")
+    peaks = load_peaks()
+    t = train_subbench(hpe, ctx, args, peaks)
+    if ctx.rank == 0:
+        B, H, W, K = args.batch, args.height, args.width, args.joints
+        emit({"metric": "images/sec train step @256x192 COCO-17", "value": t["value"], "unit": "images/s", "n_gpus": ctx.world,
+              "steps": t["steps"], "warmup": 3, "ms_per_step": t["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+              "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+              "config": {"workload": t["workload"], "global_batch": ctx.world * B, "parallelism": f"dp{ctx.world}"},
+              "roofline": {"bound": "tensor", "kernel": "conv_gemm_kernel + wgrad_gemm_kernel (whole step)", "achieved": t["tflops_per_gpu"],
+                           "peak": peaks["tflops_burst"], "unit": "TFLOP/s", "frac": t["frac_burst"], "frac_sustained": t["frac_sustained"],
+                           "traffic": None, "note": "3x forward algorithmic FLOPs / step time; the step also contains the HBM-bound BN passes"},
+              "allreduce_bytes_per_step": t["allreduce_bytes_per_step"], "loss": t["loss"], "clocks": t["clocks"]})
+    ctx.close()
 
 
 def run_pose(args):
@@ -515,7 +639,13 @@ def main():
     ap.add_argument("--joints", type=int, default=17)
     ap.add_argument("--cpu-batch", type=int, default=32, help="images per CPU-baseline step (bounded sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-graph", action="store_true", help="train mode: launch eagerly instead of replaying a CUDA graph")
+    ap.add_argument("--no-graph", action="store_true", help="train: launch eagerly instead of replaying a CUDA graph")
+    ap.add_argument("--quick", action="store_true", help="headline + e2e only (no sweep / per-kernel / hires / train sub-benchmarks)")
+    ap.add_argument("--no-hires", action="store_true")
+    ap.add_argument("--no-train", action="store_true")
+    ap.add_argument("--hires-batch", type=int, default=64, help="images per GPU of the 384x288 sub-benchmark (configs[3])")
+    ap.add_argument("--sustain-s", type=float, default=2.0, help="length of the second (sustained) timed region; 0 = skip")
+    ap.add_argument("--layers-log", default="", help="write the per-launch timings behind roofline.per_kernel to this file")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

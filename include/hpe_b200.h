@@ -61,6 +61,11 @@ int hpe_decode_heatmaps(const void* hm, int dtype, int B, int K, int H, int W,
                         const float* affine, int refine,
                         float* coords, float* maxvals, int32_t* idx, void* stream);
 
+/* Same decode writing packed rows xyv[B,K,3] = (x, y, maxval) f32: the layout the data-parallel result gather ships
+ * (one all-gather of (B/W)*K*12 bytes per rank), so no concatenation kernel follows the decode. */
+int hpe_decode_heatmaps_xyv(const void* hm, int dtype, int B, int K, int H, int W,
+                            const float* affine, int refine, float* xyv, int32_t* idx, void* stream);
+
 /* Same call with HOST buffers (pageable or pinned): H2D of hm/affine, kernel, D2H of the results on
  * `stream`, then a stream synchronise.  `d_scratch` is caller-owned DEVICE scratch of at least
  * hpe_decode_host_scratch_bytes(...) bytes. */

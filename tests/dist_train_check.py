@@ -75,7 +75,7 @@ def main():
     dist.all_gather(rms, rm)
     assert not torch.equal(rms[0], rms[1]), "running statistics should be per-rank (different shards)"
     note("parameters identical, running stats per rank")
-    # graph-captured replay with the collective inside the graph
+    # graph replay: the compute launches are captured, the all-reduce + optimizer kernel follow the replay eagerly
     step_g = hpe.TrainStep(make(), lr=lr, momentum=mom, weight_decay=wd, cuda_graph=True)
     for _ in range(3):
         lg = step_g(x, joints)
@@ -89,11 +89,14 @@ def main():
     if rank == 0:
         print(f"DIST_TRAIN_OK world={world} loss={loss.item():.6f} avg-grad rel err {err:.2e}", flush=True)
     torch.cuda.synchronize()
+    # clean teardown: the captured graph holds no collective (TrainStep keeps the all-reduce outside it), so the
+    # communicator can be destroyed normally -- a long-lived trainer that rebuilds its graph must be able to do this
+    step_g.close(); step.close()
     dist.barrier(device_ids=[local])
-    # Tearing the NCCL communicator down while a captured graph that contains a collective is still alive has been
-    # seen to block at interpreter exit; everything has been checked and flushed, so leave without the teardown.
-    sys.stdout.flush(); sys.stderr.flush()
-    os._exit(0)
+    dist.destroy_process_group()
+    note("process group destroyed")
+    if rank == 0:
+        print("DIST_TEARDOWN_OK", flush=True)
 
 
 if __name__ == "__main__":

@@ -68,7 +68,9 @@ def main():
     np.savez_compressed(os.path.join(HERE, "heatmap_stage_golden.npz"),
                         preds=preds, maxvals=maxvals, idx=idx, target_weight=tw,
                         target_sum=target.sum(axis=(2, 3)), loss=np.float32(loss),
-                        grad_abs_sum=np.float64(np.abs(grad).sum()))
+                        grad_abs_sum=np.float64(np.abs(grad).sum()),
+                        # FULL arrays for the first two samples (sums alone would let compensating errors through)
+                        joints=joints, heatmaps_first2=hm[:2], target_first2=target[:2], grad_first2=grad[:2])
     print("wrote golden fixtures; loss", loss)
 
 

@@ -95,3 +95,63 @@ def test_decode_bad_args_fail_loudly(hpe, cuda_dev):
         hpe.get_max_preds(torch.zeros(4, 4, device=cuda_dev))
     c, m, i = hpe.get_max_preds(torch.zeros(0, 17, 64, 48, device=cuda_dev))     # empty batch
     assert c.shape == (0, 17, 2) and m.shape == (0, 17, 1)
+
+
+def test_packed_xyv_output_equals_separate_outputs(hpe, cuda_dev):
+    """hpe_decode_heatmaps_xyv (the layout the result gather ships) = the same kernel writing (x, y, maxval) rows."""
+    hm = torch.from_numpy(hr.synth_heatmaps(9, 17, 64, 48, seed=8)).to(cuda_dev)
+    aff = torch.rand(9, 2, 3, device=cuda_dev)
+    p, v = hpe.get_final_preds_affine(hm, aff)
+    xyv = hpe.get_final_preds_xyv(hm, aff)
+    assert xyv.shape == (9, 17, 3)
+    assert torch.equal(xyv[..., :2], p) and torch.equal(xyv[..., 2:], v)
+    out = torch.empty(9, 17, 3, device=cuda_dev)
+    assert hpe.get_final_preds_xyv(hm.to(torch.bfloat16), aff, out) is out
+    p16, v16 = hpe.get_final_preds_affine(hm.to(torch.bfloat16), aff)
+    assert torch.equal(out[..., :2], p16) and torch.equal(out[..., 2:], v16)
+
+
+def _sweep_corner_heatmaps(B, K, H, W, dev, seed):
+    """Full-size synthetic heatmaps generated ON the device (the NumPy generator would take minutes at these sizes): a third of
+    the maps are quantised to 1/32 steps (thousands of exact ties per map -> the first-max rule decides), a third smooth noise
+    with a planted peak, the rest noise; 1 % of the maps all-negative, 1 % all-zero (maxval <= 0 -> zero coordinates)."""
+    g = torch.Generator(device=dev).manual_seed(seed)
+    hm = torch.rand(B, K, H, W, device=dev, generator=g)
+    kind = torch.randint(0, 100, (B, K), device=dev, generator=g)
+    q = (kind < 33)[..., None, None]
+    hm = torch.where(q, torch.round(hm * 32) / 32, hm)
+    peak = torch.randint(0, H * W, (B, K), device=dev, generator=g)
+    planted = (kind >= 33) & (kind < 66)
+    flat = hm.view(B, K, H * W)
+    cur = flat.gather(2, peak[..., None])
+    flat.scatter_(2, peak[..., None], torch.where(planted[..., None], cur + 1.5, cur))
+    hm = torch.where((kind == 98)[..., None, None], -hm - 0.1, hm)
+    hm = torch.where((kind == 99)[..., None, None], torch.zeros_like(hm), hm)
+    return hm.contiguous()
+
+
+@pytest.mark.parametrize("B,K,H,W,dtype,chunk", [(1024, 133, 128, 96, torch.float32, 128), (1024, 133, 128, 96, torch.bfloat16, 128),
+                                                  (65536, 17, 64, 48, torch.float32, 8192)])
+def test_decode_sweep_corners_against_the_oracle(hpe, cuda_dev, B, K, H, W, dtype, chunk):
+    """BASELINE configs[4] corners compared with oracle/heatmap_ref.py itself (not with properties): ONE kernel launch over the
+    whole tensor (6.7 GB fp32 / 3.3 GB bf16 at K=133 128x96 B=1024; 13.7 GB at K=17 64x48 B=65536), the oracle over host chunks of
+    the same values.  Bar: argmax indices and maxvals bit-exact, keypoints within 0.05 px."""
+    hm = _sweep_corner_heatmaps(B, K, H, W, cuda_dev, seed=21).to(dtype)
+    g = torch.Generator().manual_seed(22)
+    M = torch.rand(B, 2, 3, generator=g) * 4 - 2
+    preds, maxv, idx = hpe.get_final_preds_affine(hm, M.to(cuda_dev), return_idx=True)
+    torch.cuda.synchronize()
+    preds, maxv, idx = preds.cpu().numpy(), maxv.cpu().numpy(), idx.cpu().numpy()
+    n_ties = 0
+    for b0 in range(0, B, chunk):
+        sl = slice(b0, b0 + chunk)
+        ref_in = hm[sl].float().cpu().numpy()              # the exact values the kernel saw (bf16 upcast is value-preserving)
+        po, mo, io = hr.get_final_preds_affine(ref_in, M[sl].numpy())
+        np.testing.assert_array_equal(idx[sl], io)
+        np.testing.assert_array_equal(maxv[sl], mo)
+        assert np.abs(preds[sl] - po).max() <= KP_TOL
+        if b0 == 0:
+            flat = ref_in.reshape(chunk * K, -1)
+            n_ties = int(((flat == flat.max(1, keepdims=True)).sum(1) > 1).sum())
+    assert n_ties > chunk * K // 10, "the corner case must contain tied maxima"
+    assert (maxv <= 0).any() and (idx > 0).any()

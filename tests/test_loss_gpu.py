@@ -75,3 +75,40 @@ def test_loss_full_size_properties(hpe, cuda_dev):
     assert abs(a - d) <= 1e-6 * abs(d)
     l2 = crit(target + 2 * (pred - target), joints, None).item()
     assert abs(l2 - 4 * a) <= 1e-4 * abs(4 * a)
+
+
+def test_fused_loss_against_committed_full_array_golden(hpe, cuda_dev):
+    """tests/golden/heatmap_stage_golden.npz holds FULL target and gradient arrays (not sums) for two samples: the device
+    rasteriser and the fused loss gradient are compared element by element with the frozen oracle output."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "heatmap_stage_golden.npz"))
+    joints = torch.from_numpy(g["joints"]).to(cuda_dev)
+    t, w = hpe.generate_target(joints, (64, 48), 2.0)
+    assert np.abs(t[:2].cpu().numpy() - g["target_first2"]).max() <= 2e-7
+    assert np.array_equal(t[:2].cpu().numpy() == 0, g["target_first2"] == 0)
+    np.testing.assert_array_equal(w.cpu().numpy(), g["target_weight"])
+    hm = torch.from_numpy(hr.synth_heatmaps(8, 17, 64, 48, seed=3)).to(cuda_dev).requires_grad_(True)
+    assert np.array_equal(hm[:2].detach().cpu().numpy(), g["heatmaps_first2"])
+    loss = hpe.JointsMSELoss(sigma=2.0)(hm, joints, None)
+    loss.backward()
+    assert abs(loss.item() - float(g["loss"])) <= LOSS_RTOL * abs(float(g["loss"]))
+    go = g["grad_first2"]
+    assert np.abs(hm.grad[:2].cpu().numpy() - go).max() <= 1e-6 * np.abs(go).max() + 1e-12
+
+
+@pytest.mark.parametrize("B,K,H,W,sigma,dtype", [(256, 17, 64, 48, 2.0, torch.float32), (1024, 17, 64, 48, 2.0, torch.bfloat16),
+                                                 (64, 17, 96, 72, 3.0, torch.float32), (32, 133, 128, 96, 2.0, torch.float32)])
+def test_fused_loss_full_size_against_the_oracle(hpe, cuda_dev, B, K, H, W, sigma, dtype):
+    """BASELINE sizes (configs[1] B=256, configs[3] 96x72 at 64/GPU, sweep corners) compared with oracle/heatmap_ref.py itself:
+    loss within 1e-4 relative, gradient element-wise."""
+    g = torch.Generator(device=cuda_dev).manual_seed(31)
+    pred = (torch.randn(B, K, H, W, device=cuda_dev, generator=g) * 0.1).to(dtype)
+    joints = hr.synth_joints(B, K, (H * 4, W * 4), seed=6)
+    p = pred.clone().requires_grad_(True)
+    loss = hpe.JointsMSELoss(sigma=sigma)(p, torch.from_numpy(joints).to(cuda_dev), None)
+    loss.backward()
+    lo, go = hr.joints_mse_loss_from_joints(pred.float().cpu().numpy(), joints, sigma)
+    assert abs(loss.item() - float(lo)) <= LOSS_RTOL * abs(float(lo))
+    gg = p.grad.float().cpu().numpy()
+    tol = 1e-9 if dtype == torch.float32 else np.abs(go).max() * 2 ** -8
+    assert np.abs(gg - go).max() <= tol + 1e-6 * np.abs(go).max()

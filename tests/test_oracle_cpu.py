@@ -62,6 +62,11 @@ def test_heatmap_stage_golden():
     loss, grad = hr.joints_mse_loss(hm, target, tw)
     assert abs(float(loss) - float(g["loss"])) <= 1e-7 * abs(float(g["loss"])) + 1e-12
     assert abs(float(np.abs(grad).sum()) - float(g["grad_abs_sum"])) < 1e-6 * float(g["grad_abs_sum"])
+    # full arrays (first two samples), not only sums
+    np.testing.assert_array_equal(joints, g["joints"])
+    np.testing.assert_array_equal(hm[:2], g["heatmaps_first2"])
+    np.testing.assert_allclose(target[:2], g["target_first2"], rtol=0, atol=1e-7)
+    np.testing.assert_allclose(grad[:2], g["grad_first2"], rtol=1e-6, atol=1e-12)
 
 
 def test_get_max_preds_tie_and_mask_rules():

@@ -24,6 +24,8 @@ def _worker(rank, world, port, n_total, ragged, q):
         lo, hi = hpe.shard_range(n_total, rank, world)
         if ragged:
             out = hpe.gather_keypoints(preds[lo:hi], maxvals[lo:hi])
+        elif ragged is None:       # packed rows straight from the decode kernel: nothing to concatenate
+            out = hpe.gather_keypoints_equal(torch.cat([preds[lo:hi], maxvals[lo:hi]], 2).contiguous())
         else:
             out = hpe.gather_keypoints_equal(preds[lo:hi], maxvals[lo:hi])
         want = torch.cat([preds, maxvals], 2)
@@ -61,6 +63,10 @@ def test_shard_range_partitions_exactly():
 
 def test_gather_equal_shards_gloo_world2():
     _run(8, ragged=False)
+
+
+def test_gather_packed_rows_gloo_world2():
+    _run(8, ragged=None)
 
 
 def test_gather_ragged_shards_gloo_world2():
