@@ -62,6 +62,9 @@ struct ConvParams {
   float* hm_out;                // HPE_CONV_FINAL / fused head: fp32 NCHW heatmaps
   int head2_k;                  // fused head (HEAD2): number of joints K <= 32 of the second GEMM
   const float* bias2;           // fused head: conv bias [K]
+  // DIRECT epilogue: plain coalesced stores into y [B][out_up*Ho][out_up*Wo][out_pitch] (out_up = 2 for the parity-class kinds)
+  __nv_bfloat16* y_out;
+  int out_pitch, out_up;
 };
 
 struct TileCoord { int n_tile, cls, x0, y0, b0; };
@@ -100,7 +103,7 @@ __device__ __forceinline__ int kb_count(const ConvParams& p, int cls) {
 
 // NSB = epilogue staging buffers (16 KB each): 4 with a residual (they double as its prefetch ring), else 3 -- the bytes
 // saved go to a deeper operand ring, which is what bounds the deep-K layers (ring depth / hand-off round trip).
-template <int BLOCK_N, int STAGES, bool PAIR = false, int NSB = 4, bool HEAD2 = false>
+template <int BLOCK_N, int STAGES, bool PAIR = false, int NSB = 4, bool HEAD2 = false, bool DIRECT = false>
 struct SmemLayout {
   static constexpr int kW2Bytes    = HEAD2 ? 4 * 16 * 128 : 0;       // fused head: this CTA's 16 rows x 256 K of the joint weights
   static constexpr int kBBytes     = (PAIR ? BLOCK_N / 2 : BLOCK_N) * kKBlock * 2;    // a CTA of a pair holds half of B's rows
@@ -109,7 +112,7 @@ struct SmemLayout {
   static constexpr int kOffB   = STAGES * kABytes;
   static constexpr int kOffSB  = kOffB + STAGES * kBBytes;
   static constexpr int kOffSS  = kOffSB + NSB * kSBBytes;             // float scale[kMaxBlockN], shift[kMaxBlockN]
-  static constexpr int kOffW2  = kOffSS + 2 * kMaxBlockN * 4;         // 1024-byte aligned (all sizes above are multiples of 1 KB)
+  static constexpr int kOffW2  = kOffSS + (DIRECT ? 4 : 2) * kMaxBlockN * 4;   // the DIRECT epilogue double-buffers the table; 1024-byte aligned
   static constexpr int kOffBar = kOffW2 + kW2Bytes;
   static constexpr int kNumBar = 2 * STAGES + 4 + 2 * NSB + 3;       // + w2full, s2full, d2full (fused head)
   static constexpr int kTotal  = kOffBar + kNumBar * 8 + 16;
@@ -180,7 +183,11 @@ __device__ __forceinline__ float silu_fast(float x) {
 // exactly the SWIZZLE_128B K-major A operand of a second GEMM against the K-joint 1x1 weights (16 rows per CTA, resident in
 // smem), accumulated into the first 32 columns of the accumulator just drained, and written as fp32 NCHW heatmaps: deconv3 +
 // final_layer of the App. A.1 head in one kernel (saves writing and re-reading the 403 MB deconv3 output at B=256).
-template <int BLOCK_N, int STAGES, int ACT, bool RES, bool FINAL, bool PAIR = false, bool HEAD2 = false>
+// DIRECT: decoupled epilogue -- every epilogue warp stages its own 32 rows x 32 columns and writes them with plain coalesced
+// 16-byte stores: no 256-thread barrier, proxy fence, TMA store or bulk-group wait per 64-column chunk (in-kernel profile of the
+// lock-step TMA-store epilogue: 8.2 k cycles per residual tile against 2 k of MMA, the schedulers 26 % busy because all eight
+// warps waited at the same points).  The residual ring is released by an 8-arrival mbarrier.
+template <int BLOCK_N, int STAGES, int ACT, bool RES, bool FINAL, bool PAIR = false, bool HEAD2 = false, bool DIRECT = false>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
                  const __grid_constant__ CUtensorMap tmW, const __grid_constant__ OutMaps tmOut,
@@ -189,9 +196,12 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   // chunk j and everyone meets at chunk j's named barrier, so at the start of chunk q only stores <= q-3 are known done:
   // 3 buffers is the minimum.  With a residual the buffers double as its prefetch ring (4, lead 2).
   static_assert(!HEAD2 || (PAIR && BLOCK_N == 256 && !RES && !FINAL), "fused head: pair kernel, 256 channels, no residual");
-  constexpr int kNumSB = FINAL ? 0 : ((RES || HEAD2) ? 4 : 3);      // the fp32 heatmap epilogue stores from registers: all smem to the ring
+  static_assert(!DIRECT || (!FINAL && !HEAD2), "the direct-store epilogue replaces the bf16 NHWC TMA-store path only");
+  // DIRECT without a residual: one 16 KB region holds the eight warps' private 2 KB staging tiles
+  // DIRECT with a residual: 3 chunk buffers (a buffer is free again as soon as the eight warps have read it back)
+  constexpr int kNumSB = FINAL ? 0 : (DIRECT ? (RES ? 3 : 1) : ((RES || HEAD2) ? 4 : 3));      // the fp32 heatmap epilogue stores from registers: all smem to the ring
   constexpr int kResLead = 2;                   // the residual of chunk q + 2 is requested while chunk q is processed
-  using L = SmemLayout<BLOCK_N, STAGES, PAIR, kNumSB, HEAD2>;
+  using L = SmemLayout<BLOCK_N, STAGES, PAIR, kNumSB, HEAD2, DIRECT>;
   static_assert(!PAIR || (BLOCK_N % 32 == 0 && !FINAL), "pair kernels: N multiple of 32, bf16 NHWC epilogue");
   constexpr int kChunks   = BLOCK_N >= 64 ? BLOCK_N / 64 : 1;
   constexpr int kTmemCols = 2 * BLOCK_N <= 32 ? 32 : (2 * BLOCK_N <= 64 ? 64 : (2 * BLOCK_N <= 128 ? 128 : (2 * BLOCK_N <= 256 ? 256 : 512)));  // power of two
@@ -231,7 +241,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // PAIR: the leader's full barrier collects both producers' arrivals, its tempty both CTAs' epilogue warps
     for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], PAIR ? 2 : 1); mbar_init(&empty_bar[s], 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], (PAIR ? 2 : 1) * kEpiThreads / 32); }
-    for (int b = 0; b < kNumSB; ++b) { mbar_init(&sbfull_bar[b], 1); mbar_init(&sbempty_bar[b], 1); }
+    for (int b = 0; b < kNumSB; ++b) { mbar_init(&sbfull_bar[b], 1); mbar_init(&sbempty_bar[b], DIRECT ? kEpiThreads / 32 : 1); }
     mbar_init(w2full_bar, 1); mbar_init(s2full_bar, 2); mbar_init(d2full_bar, 1);
     fence_mbar_init();
   }
@@ -329,7 +339,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const TileCoord t = tile_coord(p, work_tile<PAIR>(p, work, rank));
         for (int c = 0; c < kChunks; ++c, ++r) {
           const int b = r % kNumSB;
-          mbar_wait(&sbempty_bar[b], (r / kNumSB) & 1);
+          // DIRECT: a buffer is free once the eight epilogue warps have read it back (fresh barrier: parity 1 passes at once);
+          // TMA-store path: the epilogue leader hands buffers over with a lead of kResLead chunks
+          mbar_wait(&sbempty_bar[b], DIRECT ? (((r / kNumSB) & 1) ^ 1) : ((r / kNumSB) & 1));
           mbar_arrive_expect_tx(&sbfull_bar[b], kSBBytes);
           tma_load_4d(sSB + b * kSBBytes, &tmRes, &sbfull_bar[b], t.n_tile * BLOCK_N + c * 64, t.x0, t.y0, t.b0);
         }
@@ -341,15 +353,32 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int half = (warp - kEpiWarp0) >> 2;     // which 32 of the chunk's 64 columns
     const int row = ew * 32 + lane;               // tile row = TMEM lane = pixel inside the brick
     const bool leader = threadIdx.x == kEpiWarp0 * 32;
-    if (RES && leader) for (int b = 0; b < kResLead; ++b) mbar_arrive(&sbempty_bar[b]);
+    if (RES && !DIRECT && leader) for (int b = 0; b < kResLead; ++b) mbar_arrive(&sbempty_bar[b]);
     const int etid = threadIdx.x - kEpiWarp0 * 32;
     int q = 0, it = 0, staged_n = -1;
+    float* const sTab0 = sScale; int tab_par = 1;
+    // DIRECT store mapping: lane -> (pixel slot ps = lane & 7, 16-byte unit u4 = lane >> 3 of the warp's 64-byte column group);
+    // the lane stores pixels ps + 8 i (i < 4) of the warp's 32 rows.  A quarter-warp then reads 8 different rows of the staging
+    // tile at the same logical unit: conflict-free under the 128-byte swizzle (RES) and under the private tile's own XOR.
+    const int ps = lane & 7, u4 = lane >> 3;
+    int dxi[4], dyi[4], dbi[4];
+    if constexpr (DIRECT) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int r = ew * 32 + ps + 8 * i;
+        dxi[i] = r % p.tw; dyi[i] = (r / p.tw) % p.th; dbi[i] = r / (p.tw * p.th);
+      }
+    }
+    const uint32_t wstg = smem_u32(sSB) + (warp - kEpiWarp0) * 2048;      // DIRECT without a residual: this warp's 32 x 64 B tile
     for (int work = work0; work < p.num_tiles; work += wstep, ++it) {
       const TileCoord t = tile_coord(p, work_tile<PAIR>(p, work, rank));
       const int acc = it & 1;
       if (t.n_tile != staged_n) {
         // this N tile's folded-BN scale/shift -> smem (channels past Cout: 0).  Every thread finished reading the previous
-        // tile's values before the named barrier of its last chunk, so the table is free to overwrite here.
+        // tile's values before the named barrier of its last chunk, so the table is free to overwrite here.  DIRECT (no
+        // per-chunk barrier): the tables alternate, and a warp that writes table `par` has passed the barrier that followed the
+        // staging of table `par ^ 1`, which every warp reached only after its last read of the old table `par`.
+        if constexpr (DIRECT) { tab_par ^= 1; sScale = sTab0 + tab_par * 2 * kMaxBlockN; sShift = sScale + kMaxBlockN; }
         if (etid < BLOCK_N) {
           const int n = t.n_tile * BLOCK_N + etid;
           sScale[etid] = n < p.Cout ? __ldg(p.scale + n) : 0.f; sShift[etid] = n < p.Cout ? __ldg(p.shift + n) : 0.f;
@@ -387,6 +416,84 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+      } else if constexpr (DIRECT) {
+        // ---- decoupled epilogue: no cross-warp synchronisation per chunk ----
+        const int up = p.out_up, cy = up == 2 ? (t.cls >> 1) : 0, cx = up == 2 ? (t.cls & 1) : 0;
+        __nv_bfloat16* dst[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int x = t.x0 + dxi[i], y = t.y0 + dyi[i], b = t.b0 + dbi[i];
+          const bool ok = x < p.Wo && y < p.Ho && b < p.B;
+          const size_t pix = (static_cast<size_t>(b) * (up * p.Ho) + (up * y + cy)) * (up * p.Wo) + (up * x + cx);
+          dst[i] = ok ? p.y_out + pix * p.out_pitch + t.n_tile * BLOCK_N + u4 * 8 : nullptr;
+        }
+        for (int c = 0; c < kChunks; ++c, ++q) {
+          const int sb = RES ? q % kNumSB : 0;
+          uint32_t v[32];
+          tmem_ld_x32(taddr + c * 64 + half * 32, v);
+          if (RES) mbar_wait(&sbfull_bar[sb], (q / kNumSB) & 1);
+          tmem_ld_wait();
+          if (c == kChunks - 1) {                                   // accumulator drained -> MMA may reuse it
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+              if constexpr (PAIR) mbar_arrive_cluster(mapa_shared(smem_u32(&tempty_bar[acc]), 0));   // the leader's barrier
+              else                mbar_arrive(&tempty_bar[acc]);
+            }
+          }
+          const int n0 = c * 64 + half * 32;                        // first tile-local channel of this warp's 32 columns
+          const uint32_t ss = smem_u32(sScale + n0), sh = smem_u32(sShift + n0);
+          // RES: in place in the residual chunk buffer (128-byte rows, TMA's 128-byte swizzle); else the warp's private tile
+          // (64-byte rows, unit XOR (row >> 1) & 3: conflict-free for both the row-wise writes and the 8-row read-back)
+          const uint32_t rowp = RES ? smem_u32(sSB + sb * kSBBytes) + row * 128 : wstg + lane * 64;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float4 s0 = lds_f4(ss + j * 32), s1 = lds_f4(ss + j * 32 + 16);
+            const float4 h0 = lds_f4(sh + j * 32), h1 = lds_f4(sh + j * 32 + 16);
+            float2 o01 = __ffma2_rn(make_float2(__uint_as_float(v[j * 8 + 0]), __uint_as_float(v[j * 8 + 1])), make_float2(s0.x, s0.y), make_float2(h0.x, h0.y));
+            float2 o23 = __ffma2_rn(make_float2(__uint_as_float(v[j * 8 + 2]), __uint_as_float(v[j * 8 + 3])), make_float2(s0.z, s0.w), make_float2(h0.z, h0.w));
+            float2 o45 = __ffma2_rn(make_float2(__uint_as_float(v[j * 8 + 4]), __uint_as_float(v[j * 8 + 5])), make_float2(s1.x, s1.y), make_float2(h1.x, h1.y));
+            float2 o67 = __ffma2_rn(make_float2(__uint_as_float(v[j * 8 + 6]), __uint_as_float(v[j * 8 + 7])), make_float2(s1.z, s1.w), make_float2(h1.z, h1.w));
+            const uint32_t slot = RES ? rowp + (((half * 4 + j) ^ (row & 7)) << 4) : rowp + ((j ^ ((lane >> 1) & 3)) << 4);
+            if (RES) {
+              const uint4 rr = lds_v4(slot);
+              o01 = __fadd2_rn(o01, make_float2(bf16_lo(rr.x), bf16_hi(rr.x))); o23 = __fadd2_rn(o23, make_float2(bf16_lo(rr.y), bf16_hi(rr.y)));
+              o45 = __fadd2_rn(o45, make_float2(bf16_lo(rr.z), bf16_hi(rr.z))); o67 = __fadd2_rn(o67, make_float2(bf16_lo(rr.w), bf16_hi(rr.w)));
+            }
+            float o[8] = {o01.x, o01.y, o23.x, o23.y, o45.x, o45.y, o67.x, o67.y};
+            if (ACT == HPE_ACT_SILU) {
+#pragma unroll
+              for (int e = 0; e < 8; ++e) o[e] = silu_fast(o[e]);
+            }
+            if (ACT == HPE_ACT_GELU) {
+#pragma unroll
+              for (int e = 0; e < 8; ++e) o[e] = gelu_erf(o[e]);
+            }
+            uint4 pk = make_uint4(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]), pack_bf16(o[6], o[7]));
+            if (ACT == HPE_ACT_RELU) {
+              pk.x = relu_bf16x2(pk.x); pk.y = relu_bf16x2(pk.y); pk.z = relu_bf16x2(pk.z); pk.w = relu_bf16x2(pk.w);
+            }
+            sts_v4(slot, pk);
+          }
+          __syncwarp();                                             // the warp's 32 rows are staged
+          uint4 ov[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int r = ps + 8 * i;                               // row inside the warp's 32
+            ov[i] = RES ? lds_v4(smem_u32(sSB + sb * kSBBytes) + (ew * 32 + r) * 128 + (((half * 4 + u4) ^ (r & 7)) << 4))
+                        : lds_v4(wstg + r * 64 + ((u4 ^ ((r >> 1) & 3)) << 4));
+          }
+          __syncwarp();                                             // read back before the next chunk's writes / the buffer's release
+          if (RES) {
+            // generic-proxy accesses of the buffer are ordered before the TMA (async proxy) write that refills it
+            fence_proxy_async_smem();
+            if (lane == 0) mbar_arrive(&sbempty_bar[sb]);
+          }
+          const bool ch_ok = t.n_tile * BLOCK_N + n0 + u4 * 8 < p.Cout;      // channel clipping (Cout is a multiple of 8)
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            if (dst[i] != nullptr && ch_ok) *reinterpret_cast<uint4*>(dst[i] + n0) = ov[i];
+        }
       } else {
         for (int c = 0; c < kChunks; ++c, ++q) {
           const int sb = HEAD2 ? c : q % kNumSB;                    // fused head: the tile's four chunks stay staged (A' operand)
@@ -500,7 +607,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
       }
     }
-    if (!HEAD2 && leader) bulk_wait_all();
+    if (!HEAD2 && !DIRECT && leader) bulk_wait_all();
   }
 
   tc_fence_before();
@@ -641,6 +748,7 @@ struct hpe_conv_plan {
   void* y;
   CUtensorMap tmA2;
   const void* fn;
+  int direct;                         // direct-store epilogue (plain coalesced stores instead of TMA stores)
   int halo_taps_y;                    // != 0: the layer runs on the y-halo variant (conv_halo.cu)
   HaloParams hp;
 };
@@ -918,45 +1026,57 @@ extern "C" int hpe_conv_pack_weight_dgrad(const hpe_conv_desc* f, const float* w
 
 typedef void (*ConvKernelFn)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const OutMaps, const CUtensorMap, const ConvParams);
 
-// ST_N / ST_R: operand-ring depth without / with a residual (the residual variant keeps 4 staging buffers)
-template <int BN, int ST_N, int ST_R, int ST_F>
+// ST_N / ST_R: operand-ring depth without / with a residual; D = direct-store epilogue (1 / 3 staging buffers instead of 3 / 4)
+template <int BN, int ST_N, int ST_R, int ST_F, bool D>
 static ConvKernelFn pick_kernel_bn(int act, bool res, bool fin, size_t* smem) {
-  *smem = res ? SmemLayout<BN, ST_R, false, 4>::kDynamic : SmemLayout<BN, ST_N, false, 3>::kDynamic;
+  *smem = res ? SmemLayout<BN, ST_R, false, D ? 3 : 4, false, D>::kDynamic : SmemLayout<BN, ST_N, false, D ? 1 : 3, false, D>::kDynamic;
   if (fin) { *smem = SmemLayout<BN, ST_F, false, 0>::kDynamic; return conv_gemm_kernel<BN, ST_F, HPE_ACT_NONE, false, true>; }
   if constexpr (BN >= 64) {
     switch (act) {
-      case HPE_ACT_RELU: return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_RELU, true, false> : conv_gemm_kernel<BN, ST_N, HPE_ACT_RELU, false, false>;
-      case HPE_ACT_SILU: return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_SILU, true, false> : conv_gemm_kernel<BN, ST_N, HPE_ACT_SILU, false, false>;
-      case HPE_ACT_GELU: return res ? nullptr : conv_gemm_kernel<BN, ST_N, HPE_ACT_GELU, false, false>;
-      default:           return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_NONE, true, false> : conv_gemm_kernel<BN, ST_N, HPE_ACT_NONE, false, false>;
+      case HPE_ACT_RELU: return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_RELU, true, false, false, false, D> : conv_gemm_kernel<BN, ST_N, HPE_ACT_RELU, false, false, false, false, D>;
+      case HPE_ACT_SILU: return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_SILU, true, false, false, false, D> : conv_gemm_kernel<BN, ST_N, HPE_ACT_SILU, false, false, false, false, D>;
+      case HPE_ACT_GELU: return res ? nullptr : conv_gemm_kernel<BN, ST_N, HPE_ACT_GELU, false, false, false, false, D>;
+      default:           return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_NONE, true, false, false, false, D> : conv_gemm_kernel<BN, ST_N, HPE_ACT_NONE, false, false, false, false, D>;
     }
   }
   return nullptr;
 }
 
-template <int BN, int ST_N, int ST_R>
+template <int BN, int ST_N, int ST_R, bool D>
 static ConvKernelFn pick_kernel_pair(int act, bool res, size_t* smem) {
-  *smem = res ? SmemLayout<BN, ST_R, true, 4>::kDynamic : SmemLayout<BN, ST_N, true, 3>::kDynamic;
+  *smem = res ? SmemLayout<BN, ST_R, true, D ? 3 : 4, false, D>::kDynamic : SmemLayout<BN, ST_N, true, D ? 1 : 3, false, D>::kDynamic;
   switch (act) {
-    case HPE_ACT_RELU: return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_RELU, true, false, true> : conv_gemm_kernel<BN, ST_N, HPE_ACT_RELU, false, false, true>;
-    case HPE_ACT_SILU: return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_SILU, true, false, true> : conv_gemm_kernel<BN, ST_N, HPE_ACT_SILU, false, false, true>;
-    case HPE_ACT_GELU: return res ? nullptr : conv_gemm_kernel<BN, ST_N, HPE_ACT_GELU, false, false, true>;
-    default:           return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_NONE, true, false, true> : conv_gemm_kernel<BN, ST_N, HPE_ACT_NONE, false, false, true>;
+    case HPE_ACT_RELU: return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_RELU, true, false, true, false, D> : conv_gemm_kernel<BN, ST_N, HPE_ACT_RELU, false, false, true, false, D>;
+    case HPE_ACT_SILU: return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_SILU, true, false, true, false, D> : conv_gemm_kernel<BN, ST_N, HPE_ACT_SILU, false, false, true, false, D>;
+    case HPE_ACT_GELU: return res ? nullptr : conv_gemm_kernel<BN, ST_N, HPE_ACT_GELU, false, false, true, false, D>;
+    default:           return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_NONE, true, false, true, false, D> : conv_gemm_kernel<BN, ST_N, HPE_ACT_NONE, false, false, true, false, D>;
   }
 }
 
 // ring depths: as many stages as fit beside the staging buffers in the 227 KB a CTA may use
-static ConvKernelFn pick_kernel(int block_n, int act, bool res, bool fin, bool pair, bool head2, size_t* smem) {
+static ConvKernelFn pick_kernel(int block_n, int act, bool res, bool fin, bool pair, bool head2, bool direct, size_t* smem) {
   if (head2) { *smem = SmemLayout<256, 4, true, 4, true>::kDynamic; return conv_gemm_kernel<256, 4, HPE_ACT_RELU, false, false, true, true>; }
-  if (pair && block_n == 256) return pick_kernel_pair<256, 5, 5>(act, res, smem);       // 32 KB stages (A + half of B)
-  if (pair && block_n == 192) return pick_kernel_pair<192, 6, 5>(act, res, smem);       // 28 KB stages (ConvNeXt C = 192/384/768)
-  if (pair) return pick_kernel_pair<128, 7, 6>(act, res, smem);                         // 24 KB stages
+  if (direct && !fin) {
+    // direct-store epilogue: 16 KB (no residual) / 48 KB (residual) of staging instead of 48 / 64 KB -> one more ring stage
+    if (pair && block_n == 256) return pick_kernel_pair<256, 6, 5, true>(act, res, smem);
+    if (pair && block_n == 192) return pick_kernel_pair<192, 7, 6, true>(act, res, smem);
+    if (pair) return pick_kernel_pair<128, 8, 7, true>(act, res, smem);
+    switch (block_n) {
+      case 64:  return pick_kernel_bn<64, 8, 7, 9, true>(act, res, fin, smem);
+      case 128: return pick_kernel_bn<128, 6, 5, 7, true>(act, res, fin, smem);
+      case 192: return pick_kernel_bn<192, 5, 4, 4, true>(act, res, fin, smem);
+      default:  return pick_kernel_bn<256, 4, 3, 4, true>(act, res, fin, smem);
+    }
+  }
+  if (pair && block_n == 256) return pick_kernel_pair<256, 5, 5, false>(act, res, smem);       // 32 KB stages (A + half of B)
+  if (pair && block_n == 192) return pick_kernel_pair<192, 6, 5, false>(act, res, smem);       // 28 KB stages (ConvNeXt C = 192/384/768)
+  if (pair) return pick_kernel_pair<128, 7, 6, false>(act, res, smem);                         // 24 KB stages
   switch (block_n) {
-    case 32:  return pick_kernel_bn<32, 6, 6, 11>(act, res, fin, smem);     // 20 KB stages (FINAL only)
-    case 64:  return pick_kernel_bn<64, 7, 6, 9>(act, res, fin, smem);      // 24 KB stages
-    case 128: return pick_kernel_bn<128, 5, 5, 7>(act, res, fin, smem);     // 32 KB
-    case 192: return pick_kernel_bn<192, 4, 4, 4>(act, res, fin, smem);     // 40 KB
-    default:  return pick_kernel_bn<256, 3, 3, 4>(act, res, fin, smem);     // 48 KB
+    case 32:  return pick_kernel_bn<32, 6, 6, 11, false>(act, res, fin, smem);     // 20 KB stages (FINAL only)
+    case 64:  return pick_kernel_bn<64, 7, 6, 9, false>(act, res, fin, smem);      // 24 KB stages
+    case 128: return pick_kernel_bn<128, 5, 5, 7, false>(act, res, fin, smem);     // 32 KB
+    case 192: return pick_kernel_bn<192, 4, 4, 4, false>(act, res, fin, smem);     // 40 KB
+    default:  return pick_kernel_bn<256, 3, 3, 4, false>(act, res, fin, smem);     // 48 KB
   }
 }
 
@@ -1019,7 +1139,12 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
       pl->grid = 2 * (int)(np < max_clusters ? np : max_clusters);
     }
   }
-  pl->fn = (const void*)pick_kernel(pl->block_n, d->act, p.has_res != 0, d->kind == HPE_CONV_FINAL, pl->pair != 0, d->head2 != 0, &pl->smem);
+  {
+    // direct-store epilogue (HPE_B200_EPI_TMA=1 selects the lock-step TMA-store epilogue instead)
+    const char* e = getenv("HPE_B200_EPI_TMA");
+    pl->direct = !(e && e[0] == '1') && d->kind != HPE_CONV_FINAL && !d->head2;
+  }
+  pl->fn = (const void*)pick_kernel(pl->block_n, d->act, p.has_res != 0, d->kind == HPE_CONV_FINAL, pl->pair != 0, d->head2 != 0, pl->direct != 0, &pl->smem);
   if (!pl->fn) { delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: no kernel for BLOCK_N=%d", pl->block_n); }
   {
     cudaError_t e = cudaFuncSetAttribute((const void*)pl->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem);
@@ -1209,6 +1334,9 @@ static int conv_launch(hpe_conv_plan* pl, const void* x, const void* x2, const v
   p.scale = scale; p.shift = shift;
   p.hm_out = (pl->d.kind == HPE_CONV_FINAL || pl->d.head2) ? (float*)y : nullptr;
   p.bias2 = bias2;
+  p.y_out = (__nv_bfloat16*)y;
+  p.out_pitch = pl->d.out_cstride ? pl->d.out_cstride : pl->d.Cout;
+  p.out_up = (is_class_strided(pl->d.kind) || pl->d.kind == HPE_CONV_DGRAD1x1S2) ? 2 : 1;
   if (!p.has_res && !pl->d.head2) pl->tmRes = pl->tmA;      // unused, but must be a valid object to copy
   if (pl->d.kind == HPE_CONV_FINAL || pl->d.head2) for (int c = 0; c < 4; ++c) pl->tmOut.m[c] = pl->tmA;
   if (!pl->d.Cin2) pl->tmA2 = pl->tmA;      // unused, but must be a valid object to copy

@@ -21,10 +21,8 @@ struct GaussSpec {
 };
 
 // A.5: weight and rounded centre of one joint
-__device__ __forceinline__ GaussSpec make_spec(const float* __restrict__ joints, int map, int H, int W,
-                                               float sigma, float sx, float sy) {
+__device__ __forceinline__ GaussSpec make_spec(float x, float y, float v, int H, int W, float sigma, float sx, float sy) {
   GaussSpec g;
-  const float x = joints[(size_t)map * 3 + 0], y = joints[(size_t)map * 3 + 1], v = joints[(size_t)map * 3 + 2];
   float fx = truncf(x / sx + 0.5f), fy = truncf(y / sy + 0.5f);           // C int() truncation
   fx = fminf(fmaxf(fx, -1.0e6f), 1.0e6f);  fy = fminf(fmaxf(fy, -1.0e6f), 1.0e6f);
   if (!(fx == fx)) fx = -1.0e6f;
@@ -53,7 +51,7 @@ __device__ __forceinline__ float warp_sum_fixed(float v) {
 
 // ---- fused: pred + joints ------------------------------------------------------------------------
 template <bool BF16, bool GRAD>
-__global__ void __launch_bounds__(kLossThreads, 4)
+__global__ void __launch_bounds__(kLossThreads, GRAD ? 4 : 3)
 mse_fused_kernel(const void* __restrict__ pred, const float* __restrict__ joints, int n_maps, int H, int W,
                  int vec_ok, float sigma, float sx, float sy, float* __restrict__ partials,
                  void* __restrict__ grad, float gcoef, float* __restrict__ weight_out) {
@@ -64,9 +62,20 @@ mse_fused_kernel(const void* __restrict__ pred, const float* __restrict__ joints
   const int nwarps = (gridDim.x * kLossThreads) >> 5;
   const int HW     = H * W;
   const int nvec   = vec_ok ? HW / EPV : 0;       // vec_ok also guarantees W % EPV == 0
+  // forward-only: 12 independent 16-byte loads per lane in flight (4 left this pass latency-bound at 66 % / 41 % of HBM: per
+  // map a warp pays joints-load latency + data-load latency + reduction in sequence, and without the gradient store nothing
+  // else overlaps them) and the NEXT map's joint is fetched while the current map streams.  With the gradient store 4 is enough.
+  constexpr int U  = GRAD ? kLossUnroll : 12;     // forward-only: a whole 64x48 bf16 map (12 vectors per lane) in one batch of loads
+  const float inv_w = 1.0f / (float)W;            // row of a vector without an integer division (exact: e < 2^22, see below)
 
+  float jx = 0.f, jy = 0.f, jv = 0.f;
+  if (warp < n_maps) { jx = __ldg(joints + (size_t)warp * 3); jy = __ldg(joints + (size_t)warp * 3 + 1); jv = __ldg(joints + (size_t)warp * 3 + 2); }
   for (int map = warp; map < n_maps; map += nwarps) {
-    const GaussSpec g = make_spec(joints, map, H, W, sigma, sx, sy);
+    const GaussSpec g = make_spec(jx, jy, jv, H, W, sigma, sx, sy);
+    if (map + nwarps < n_maps) {                  // next map's joint: its latency hides behind this map's stream
+      const size_t nj = (size_t)(map + nwarps) * 3;
+      jx = __ldg(joints + nj); jy = __ldg(joints + nj + 1); jv = __ldg(joints + nj + 2);
+    }
     const char* base = reinterpret_cast<const char*>(pred) + (size_t)map * HW * ESIZE;
     char* gbase = GRAD ? reinterpret_cast<char*>(grad) + (size_t)map * HW * ESIZE : nullptr;
     if (lane == 0 && weight_out) weight_out[map] = g.w;
@@ -83,19 +92,23 @@ mse_fused_kernel(const void* __restrict__ pred, const float* __restrict__ joints
       continue;
     }
     const float gc = gcoef * g.w;                 // dL/dp = gscale * w^2 (p-g)/n = (w p - w g) * gscale * w / n
-    for (int v0 = 0; v0 < nvec; v0 += 32 * kLossUnroll) {
-      uint4 r[kLossUnroll];
+    for (int v0 = 0; v0 < nvec; v0 += 32 * U) {
+      uint4 r[U];
 #pragma unroll
-      for (int u = 0; u < kLossUnroll; ++u) {
+      for (int u = 0; u < U; ++u) {
         const int v = v0 + u * 32 + lane;
         if (v < nvec) r[u] = ld_stream_v4(base + (size_t)v * 16);
       }
 #pragma unroll
-      for (int u = 0; u < kLossUnroll; ++u) {
+      for (int u = 0; u < U; ++u) {
         const int v = v0 + u * 32 + lane;
         if (v < nvec) {
           const int e = v * EPV;
-          const int y = e / W, x0 = e - y * W;        // one row per vector (W % EPV == 0)
+          // one row per vector (W % EPV == 0).  y = floor(e / W) from the fp32 product, corrected by one step: exact for
+          // every e < 2^22 (maps up to 2048 x 2048), no integer division in the loop
+          int y = (int)(((float)e + 0.5f) * inv_w);
+          int x0 = e - y * W;
+          if (x0 < 0) { --y; x0 += W; } else if (x0 >= W) { ++y; x0 -= W; }
           float p[EPV];
           if constexpr (BF16) {
             p[0] = bf16_lo(r[u].x); p[1] = bf16_hi(r[u].x); p[2] = bf16_lo(r[u].y); p[3] = bf16_hi(r[u].y);
@@ -224,7 +237,7 @@ generate_target_kernel(const float* __restrict__ joints, int n_maps, int H, int 
   const int HW     = H * W;
   const int nvec   = vec_ok ? HW / 4 : 0;
   for (int map = warp; map < n_maps; map += nwarps) {
-    const GaussSpec g = make_spec(joints, map, H, W, sigma, sx, sy);
+    const GaussSpec g = make_spec(joints[(size_t)map * 3 + 0], joints[(size_t)map * 3 + 1], joints[(size_t)map * 3 + 2], H, W, sigma, sx, sy);
     if (lane == 0) weight[map] = g.w;
     float* tb = target + (size_t)map * HW;
     for (int v = lane; v < nvec; v += 32) {
@@ -289,7 +302,8 @@ extern "C" int hpe_joints_mse_fused(const void* pred, int dtype, const float* jo
   cudaStream_t st = (cudaStream_t)stream;
   const int n_maps = B * K, HW = H * W;
   const int epv = dtype == HPE_BF16 ? 8 : 4;
-  const int vec_ok = (((uintptr_t)pred & 15) == 0) && (!grad || ((uintptr_t)grad & 15) == 0) && (W % epv == 0);
+  const int vec_ok = (((uintptr_t)pred & 15) == 0) && (!grad || ((uintptr_t)grad & 15) == 0) && (W % epv == 0) &&
+                     HW <= (1 << 22);      // the kernel's fp32 row computation is exact up to 2^22 elements per map
   const double n = (double)K * B * HW;
   const float gcoef = (float)((double)grad_scale / n);
   const int grid = loss_grid(n_maps);

@@ -75,11 +75,24 @@ class HeatmapPose(nn.Module):
 
     def __init__(self, num_joints=17, backbone="resnet50", pretrained=True):
         super().__init__()
-        if backbone != "resnet50":
-            raise ValueError(f"backbone '{backbone}' not built: this path covers the config-default 'resnet50'")
         self.njoints = int(num_joints)
-        self.backbone = _ResNet50Params()
-        layers, c = [], 2048
+        self.backbone_name = backbone
+        if backbone == "resnet50":
+            self.backbone = _ResNet50Params()
+            c = 2048
+        elif backbone.startswith("dinov3_convnext_") and backbone.split("_")[2] in ("tiny", "small", "base", "large"):
+            # the reference's ConvNeXt/DINOv3 backbone (HPE/models/backbones/dinov3convnext.py:76-110,
+            # dinov3/models/convnext.py:121-180) as an alternate backbone behind the SAME heatmap head; parameter names are
+            # the dinov3 checkpoint's (`backbone.stages.2.5.pwconv1.weight` ...)
+            from .posemodel import _ConvNeXt, convnext_sizes
+            cfg = convnext_sizes[backbone.split("_")[2]]
+            self.dims, self.depths = cfg["dims"], cfg["depths"]
+            self.backbone = _ConvNeXt(self.depths, self.dims)
+            c = self.dims[-1]
+        else:
+            raise ValueError(f"backbone '{backbone}' not built: this path covers 'resnet50' (config default) and "
+                             "'dinov3_convnext_{tiny,small,base,large}'")
+        layers = []
         for _ in range(3):
             layers += [nn.ConvTranspose2d(c, 256, 4, stride=2, padding=1, output_padding=0, bias=False),
                        nn.BatchNorm2d(256), nn.ReLU(inplace=True)]
@@ -150,6 +163,8 @@ class HeatmapPose(nn.Module):
             raise ValueError(f"expected [B,3,H,W] input, got {tuple(x.shape)}")
         if not x.is_cuda:
             raise RuntimeError("libhpe_b200 has no CPU path: input must live on a CUDA (sm_100a) device")
+        if self.training and self.backbone_name != "resnet50":
+            raise RuntimeError("training mode is built for the resnet50 backbone only (ConvNeXt backbones: inference)")
         if self.training:
             # model.train() (HPE/engine/trainer.py:77-80): BatchNorm batch statistics, and a backward pass through
             # the dgrad / wgrad kernels so `loss.backward()` fills every parameter's .grad (trainer.py:96-97)
@@ -174,12 +189,24 @@ class HeatmapPose(nn.Module):
             raise RuntimeError("forward_static is the inference path: call model.eval() first")
         key = (tuple(x.shape), x.device.index)
         plan = self._plans.get(key)
+        xin = x.contiguous() if x.dtype == torch.uint8 else x.float().contiguous()      # uint8 = x.float()/255 fused in
+        if self.backbone_name != "resnet50":
+            # ConvNeXt backbone: the launch plan of posemodel.py with the deconv heatmap head; its weights are packed when the
+            # plan is built, so a weight change rebuilds it
+            if plan is None or plan.weights_version != self._weights_version:
+                from .posemodel import _PosePlan
+                with torch.no_grad():
+                    plan = _PosePlan(self, x.shape[0], x.shape[2], x.shape[3], x.device, heatmap_head=True)
+                plan.weights_version = self._weights_version
+                self._plans[key] = plan
+            plan.run(xin)
+            return plan.heatmaps
         if plan is None:
             plan = _ForwardPlan(self, x.shape[0], x.shape[2], x.shape[3], x.device)
             self._plans[key] = plan
         if plan.weights_version != self._weights_version:
             plan.load_weights(self)
-        return plan.run(x.contiguous() if x.dtype == torch.uint8 else x.float().contiguous())   # uint8 = x.float()/255 fused in
+        return plan.run(xin)
 
     def _train_plan(self, x):
         from .train import TrainPlan
@@ -200,7 +227,8 @@ class HeatmapPose(nn.Module):
         """``[B, 2048, H/32, W/32]`` fp32 NCHW view of the trunk output (timm ``forward_features`` analogue)."""
         self.forward_static(x)
         plan = self._plans[(tuple(x.shape), x.device.index)]
-        return plan.features.float().permute(0, 3, 1, 2)     # .float() makes a fresh tensor
+        feat = plan.features if self.backbone_name == "resnet50" else plan.features[-1]
+        return feat.float().permute(0, 3, 1, 2)              # .float() makes a fresh tensor
 
 
 from .posemodel import DINOv3Pose  # noqa: E402  (the reference's real pose model, HPE/models/pose.py)

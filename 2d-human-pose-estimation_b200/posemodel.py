@@ -24,7 +24,7 @@ import torch
 import torch.nn as nn
 
 from . import _lib
-from ._lib import ACT_GELU, ACT_NONE, ACT_SILU, CONV_1x1, CONV_2x2S2, CONV_3x3, CONV_FINAL, ConvDesc
+from ._lib import ACT_GELU, ACT_NONE, ACT_RELU, ACT_SILU, CONV_1x1, CONV_2x2S2, CONV_3x3, CONV_DECONV4, CONV_FINAL, ConvDesc
 from .conv import ConvLayer, fold_bn
 from .detpose import pose_decode
 
@@ -190,9 +190,11 @@ def _pad_to(t, dim, n):
 
 
 class _PosePlan:
-    """Every kernel launch of one DINOv3Pose forward at one (B, H, W), with its buffers; replayed as a CUDA graph."""
+    """Every kernel launch of one DINOv3Pose forward at one (B, H, W), with its buffers; replayed as a CUDA graph.
+    ``heatmap_head=True``: ``model`` is a ``HeatmapPose`` with a ConvNeXt backbone -- the four ConvNeXt stages feed the App. A.1
+    deconv heatmap head instead of adaptor + SPPF + PAN + PoseHead."""
 
-    def __init__(self, model, B, H, W, device):
+    def __init__(self, model, B, H, W, device, heatmap_head=False):
         if H % 32 or W % 32:
             raise ValueError(f"input {H}x{W} must be a multiple of 32")
         self.B, self.H, self.W, self.dev = B, H, W, device
@@ -280,6 +282,9 @@ class _PosePlan:
                 cur, other = other, cur
             if i > 0:                                # later stages own fresh buffers, so `cur` survives as a pyramid level
                 feats.append((cur, h, w, C))
+        if heatmap_head:
+            self._build_heatmap_head(model, feats[-1], B, device)
+            return
         # ---------------- neck (pose.py:58-65; block.py:236-254, 102-114, 117-157)
         c1n, c2n, c3n = model.tc
         (f1, h1, w1, _), (f2, h2, w2, _), (f3, h3, w3, _) = feats
@@ -350,6 +355,44 @@ class _PosePlan:
             convblock(hd.cv4[i][0], f, k1, pad_out=c4p); convblock(hd.cv4[i][1], k1, k2, pad_out=c4p, pad_in=c4p)
             fk = hd.cv4[i][2]
             conv(CONV_FINAL, k2, (out[:, nc:], nc + nk), _pad_to(fk.weight.detach().float(), 1, c4p), ones(nk), fk.bias, ACT_NONE)
+
+    def _build_heatmap_head(self, model, feat, B, device):
+        """SURVEY App. A.1 on the last ConvNeXt stage: 3 x [ConvTranspose2d(k4,s2,p1) + BN + ReLU] + final 1x1; the last deconv
+        stage and the final 1x1 run as ONE kernel (fused head) when K <= 32, exactly as behind the ResNet-50 trunk."""
+        cur, h, w, cin = feat
+        K = model.njoints
+        self.features = [cur]
+        self.fused_head = False
+        for d, idx in enumerate((0, 3, 6)):
+            dc, bn = model.deconv_layers[idx], model.deconv_layers[idx + 1]
+            scale, shift = fold_bn(bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps)
+            layer, out = None, None
+            if d == 2 and K <= 32 and os.environ.get("HPE_B200_FUSE_HEAD", "1") != "0":
+                try:
+                    layer = ConvLayer(CONV_DECONV4, B, h, w, cin, 256, 2, ACT_RELU, False, device, head2=K)
+                    layer.load(dc.weight, scale, shift)
+                    layer.load_head2(model.final_layer.weight, model.final_layer.bias)
+                    out = torch.zeros((B, K, 2 * h, 2 * w), dtype=torch.float32, device=device)
+                    self.fused_head = True
+                except RuntimeError:
+                    layer = None                    # too few tiles for a CTA pair (tiny batch): separate layers
+            if layer is None:
+                layer = ConvLayer(CONV_DECONV4, B, h, w, cin, 256, 2, ACT_RELU, False, device)
+                layer.load(dc.weight, scale, shift)
+                out = torch.zeros((B, 2 * h, 2 * w, 256), dtype=torch.bfloat16, device=device)
+            self.steps.append(lambda layer=layer, src=cur, out=out: layer(src, None, out))
+            self.n_launches += 1
+            cur, cin, h, w = out, 256, 2 * h, 2 * w
+        if cur.dtype != torch.float32:              # separate final 1x1 (K > 32 or tiny batch)
+            fl = model.final_layer
+            layer = ConvLayer(CONV_FINAL, B, h, w, 256, K, 1, ACT_NONE, False, device)
+            layer.load(fl.weight, torch.ones(K), fl.bias)
+            out = torch.zeros((B, K, h, w), dtype=torch.float32, device=device)
+            self.steps.append(lambda layer=layer, src=cur, out=out: layer(src, None, out))
+            self.n_launches += 1
+            cur = out
+        self.heatmaps = cur
+        self.levels = [cur]
 
     def _launch_all(self):
         for s in self.steps:

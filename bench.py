@@ -449,6 +449,14 @@ def run_b200(args):
     fwd_ms = sum(a.elapsed_time(b) for a, b, _ in marks) / len(marks)
     dec_ms = sum(b.elapsed_time(c) for _, b, c in marks) / len(marks)
 
+    # ---- e2e through the public host-buffer API: uint8 host images (the reference's real input type) = the headline;
+    # fp32 host images (4x the H2D bytes) as the secondary number.  Measured right after the headline region, BEFORE the
+    # 2-second sustained region heats the GPU into its power cap (r02 first run: 3.59 vs 3.32 ms/step came from that order)
+    u_ms, u_wall, chk = e2e_region(ctx, est, lambda n: ((s["h_u8"][i & 1], s["h_aff"]) for i in range(n)), args.steps)
+    h_f32 = [t.float().div_(255.0).pin_memory() for t in s["h_u8"]]
+    f_ms, f_wall, chk2 = e2e_region(ctx, est, lambda n: ((h_f32[i & 1], s["h_aff"]) for i in range(n)), args.steps)
+    del h_f32
+
     # ---- the same step for >= 2 s back to back: the power-capped (sustained) regime, with its own clock record
     n_sus = int(min(args.sustain_s * 1e3 / (ms_total / args.steps) + 1, 5000)) if args.sustain_s > 0 else 0
     sus = None
@@ -461,13 +469,6 @@ def run_b200(args):
         sus = {"steps": n_sus, "seconds": round(sus_ms_total / 1e3, 3), "ms_per_step": round(sus_ms_total / n_sus, 4),
                "ms_forward": round(sum(a.elapsed_time(b) for a, b, _ in marks_s) / len(marks_s), 4), "clocks": sus_clocks,
                "value": round(world * B * n_sus / sus_ms_total * 1e3, 1)}
-
-    # ---- e2e through the public host-buffer API: uint8 host images (the reference's real input type) = the headline;
-    # fp32 host images (4x the H2D bytes) as the secondary number
-    u_ms, u_wall, chk = e2e_region(ctx, est, lambda n: ((s["h_u8"][i & 1], s["h_aff"]) for i in range(n)), args.steps)
-    h_f32 = [t.float().div_(255.0).pin_memory() for t in s["h_u8"]]
-    f_ms, f_wall, chk2 = e2e_region(ctx, est, lambda n: ((h_f32[i & 1], s["h_aff"]) for i in range(n)), args.steps)
-    del h_f32
 
     sweep = per_kernel = hires = train = None
     if rank == 0 and not args.quick:

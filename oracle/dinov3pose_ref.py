@@ -242,3 +242,59 @@ def build_synthetic(size="tiny", nkpts=(17, 3), ncls=1, seed=0):
             elif isinstance(mod, Block):
                 mod.gamma.copy_(torch.rand(mod.gamma.shape, generator=g) * 0.8 + 0.2)
     return m.eval()
+
+
+class HeatmapConvNeXtRef(nn.Module):
+    """the reference's ConvNeXt/DINOv3 backbone (all four stages, ``forward_features_list``,
+    dinov3convnext.py:76-84) behind the SAME App. A.1 deconv heatmap head as the ResNet-50 model
+    (``oracle.resnet_ref.HeatmapHeadRef``).  The backbone half is pinned with the rest of this file (its weights load
+    into the reference's own ConvNeXt); the head half is spec-pinned (App. A.1, parity unpinned)."""
+
+    def __init__(self, size="tiny", num_joints=17):
+        super().__init__()
+        from .resnet_ref import HeatmapHeadRef
+        cfg = CONVNEXT_SIZES[size]
+        self.njoints = num_joints
+        self.backbone = ConvNeXt(cfg["depths"], cfg["dims"])
+        head = HeatmapHeadRef(cfg["dims"][-1], num_joints)
+        self.deconv_layers, self.final_layer = head.deconv_layers, head.final_layer
+
+    def forward_features(self, x):
+        return self.backbone.forward_features_list(x)[-1]
+
+    def forward(self, x):
+        return self.final_layer(self.deconv_layers(self.forward_features(x)))
+
+
+def build_synthetic_heatmap(size="tiny", num_joints=17, seed=0):
+    """Seeded ConvNeXt + heatmap head: backbone randomised like ``build_synthetic``; head deconv / final weights
+    N(0, 1/sqrt(fan_in)), BN affine and running statistics randomised; the final 1x1 is rescaled so that max|heatmap| = 1 on a
+    seeded calibration image (absolute tolerances are then on the scale of a trained net's heatmaps)."""
+    torch.manual_seed(seed)
+    m = HeatmapConvNeXtRef(size, num_joints)
+    g = torch.Generator().manual_seed(seed + 1)
+    with torch.no_grad():
+        for name, mod in m.named_modules():
+            if isinstance(mod, nn.ConvTranspose2d):
+                fan_in = mod.weight.shape[0] * 4                      # 2x2 taps reach every output pixel
+                mod.weight.copy_(torch.randn(mod.weight.shape, generator=g) * (1.0 / math.sqrt(fan_in)))
+            elif isinstance(mod, (nn.Conv2d, nn.Linear)):
+                fan_in = mod.weight[0].numel()
+                mod.weight.copy_(torch.randn(mod.weight.shape, generator=g) * (1.0 / math.sqrt(fan_in)))
+                if mod.bias is not None:
+                    mod.bias.copy_(torch.randn(mod.bias.shape, generator=g) * 0.02)
+            elif isinstance(mod, (LayerNorm, nn.LayerNorm)):
+                mod.weight.copy_(torch.rand(mod.weight.shape, generator=g) + 0.5)
+                mod.bias.copy_(torch.randn(mod.bias.shape, generator=g) * 0.1)
+            elif isinstance(mod, nn.BatchNorm2d):
+                mod.weight.copy_(torch.rand(mod.weight.shape, generator=g) + 0.5)
+                mod.bias.copy_(torch.randn(mod.bias.shape, generator=g) * 0.1)
+                mod.running_mean.copy_(torch.randn(mod.running_mean.shape, generator=g) * 0.1)
+                mod.running_var.copy_(torch.rand(mod.running_var.shape, generator=g) + 0.5)
+            elif isinstance(mod, Block):
+                mod.gamma.copy_(torch.rand(mod.gamma.shape, generator=g) * 0.8 + 0.2)
+        m.eval()
+        x = torch.rand(1, 3, 128, 96, generator=torch.Generator().manual_seed(1234))
+        m.final_layer.weight.div_(m(x).abs().max())
+        m.final_layer.bias.zero_()
+    return m

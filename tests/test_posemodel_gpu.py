@@ -191,3 +191,38 @@ def test_dinov3pose_base_runs_and_features(hpe, cuda_dev):
     for a, b in zip(m.train()(x.to(cuda_dev)), want_lv):
         mx, rms = _rel_err(a.cpu().numpy(), b.numpy())
         assert mx <= 3e-2 and rms <= 1e-2, (mx, rms)
+
+
+@pytest.mark.parametrize("size,B,H,W", [("tiny", 3, 128, 96), ("tiny", 40, 256, 192)])
+def test_heatmap_pose_with_convnext_backbone(hpe, cuda_dev, size, B, H, W):
+    """the reference's ConvNeXt/DINOv3 backbone as an alternate backbone behind the SAME deconv heatmap head --
+    ``HeatmapPose(nkpts, 'dinov3_convnext_<size>', pretrained)`` (the constructor call of HPE/core/builder.py:19).  Parity vs the
+    oracle ConvNeXt (pinned to the reference's own, tests/test_dinov3pose_oracle_cpu.py) + App. A.1 head, same weights."""
+    ref = dp.build_synthetic_heatmap(size, 17, seed=0)
+    m = hpe.HeatmapPose(17, f"dinov3_convnext_{size}", pretrained=False)
+    missing, unexpected = m.load_state_dict(ref.state_dict())
+    assert not missing and not unexpected
+    m = m.to(cuda_dev).eval()
+    x = torch.rand(B, 3, H, W, generator=torch.Generator().manual_seed(2))
+    hm = m(x.to(cuda_dev)).cpu()
+    assert hm.shape == (B, 17, H // 4, W // 4) and hm.dtype == torch.float32
+    n = min(B, 4)
+    with torch.no_grad():
+        want = ref(x[:n])
+        feat_want = ref.forward_features(x[:n])
+    scale = want.abs().max().item()
+    err, rms = (hm[:n] - want).abs().max().item(), (hm[:n] - want).pow(2).mean().sqrt().item()
+    feat = m.forward_features(x.to(cuda_dev)).cpu()[:n]
+    ferr = (feat - feat_want).abs().max().item() / feat_want.abs().max().item()
+    print(f"convnext_{size} heatmap head [{B}x{H}x{W}]: scale {scale:.3f} max-abs err {err:.2e} rms {rms:.2e}; backbone rel {ferr:.2e}")
+    assert ferr <= 2e-2
+    assert err <= 1e-2 * max(scale, 1.0), "north_star: heatmaps within max-abs 1e-2 in bf16"
+    assert rms <= 2e-3 * max(scale, 1.0)
+    # decode runs on it like on the ResNet model's heatmaps, and the result is a fresh tensor
+    preds, maxvals = hpe.decode(hm.to(cuda_dev), torch.rand(B, 2) * 100, torch.rand(B, 2) + 0.5)
+    assert preds.shape == (B, 17, 2) and torch.isfinite(preds).all()
+    assert m(x.to(cuda_dev)).data_ptr() != m(x.to(cuda_dev)).data_ptr()
+    with pytest.raises(RuntimeError, match="resnet50 backbone only"):
+        m.train()(x[:1].to(cuda_dev))
+    with pytest.raises(ValueError, match="not built"):
+        hpe.HeatmapPose(17, "vit_base", pretrained=False)
