@@ -16,7 +16,7 @@ from .loss import JointsMSELoss, generate_target
 from . import models
 from .models import DeepPose, HeatmapPose, build_model
 from . import train
-from .train import TrainPlan, TrainStep
+from .train import TrainPlan, TrainStep, adamw_step, grad_sumsq
 from .detpose import (OKS, OKS_SIGMAS, PCK, ComputeLoss, KeypointLoss, non_max_suppression_pose, pose_decode,
                       pose_nms_raw)
 from .posemodel import DINOv3Pose

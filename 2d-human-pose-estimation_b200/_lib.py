@@ -64,6 +64,9 @@ SIGNATURES = {
     "hpe_maxpool3x3s2_backward": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp]),
     "hpe_heatmap_grad_nhwc": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
     "hpe_sgd_step": (_i, [_vp, _vp, _vp, C.c_longlong, _f, _f, _f, _f, _vp]),
+    "hpe_grad_sumsq_scratch_elems": (_sz, []),
+    "hpe_grad_sumsq": (_i, [_vp, C.c_longlong, _vp, _vp, _i, _vp]),
+    "hpe_adamw_step": (_i, [_vp, _vp, _vp, _vp, C.c_longlong, _f, _f, _f, _f, _f, _i, _f, _vp, _f, _vp]),
     "hpe_wgrad_plan_create": (_i, [C.POINTER(ConvDesc), C.POINTER(_vp)]),
     "hpe_wgrad_plan_destroy": (None, [_vp]),
     "hpe_wgrad_workspace_elems": (_sz, [_vp]),

@@ -1140,9 +1140,11 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
     }
   }
   {
-    // direct-store epilogue (HPE_B200_EPI_TMA=1 selects the lock-step TMA-store epilogue instead)
-    const char* e = getenv("HPE_B200_EPI_TMA");
-    pl->direct = !(e && e[0] == '1') && d->kind != HPE_CONV_FINAL && !d->head2;
+    // direct-store epilogue: opt-in (HPE_B200_EPI_DIRECT=1).  Measured on B200 (profiles/r02_epilogue_direct_ab.log): parity-
+    // green but SLOWER than the lock-step TMA-store epilogue -- forward 3.37 -> 3.81 ms, the residual 1x1 layers +25...+80 us
+    // each -- so bulk TMA stores stay the default.
+    const char* e = getenv("HPE_B200_EPI_DIRECT");
+    pl->direct = (e && e[0] == '1') && d->kind != HPE_CONV_FINAL && !d->head2;
   }
   pl->fn = (const void*)pick_kernel(pl->block_n, d->act, p.has_res != 0, d->kind == HPE_CONV_FINAL, pl->pair != 0, d->head2 != 0, pl->direct != 0, &pl->smem);
   if (!pl->fn) { delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: no kernel for BLOCK_N=%d", pl->block_n); }

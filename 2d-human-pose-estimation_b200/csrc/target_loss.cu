@@ -51,7 +51,7 @@ __device__ __forceinline__ float warp_sum_fixed(float v) {
 
 // ---- fused: pred + joints ------------------------------------------------------------------------
 template <bool BF16, bool GRAD>
-__global__ void __launch_bounds__(kLossThreads, GRAD ? 4 : 3)
+__global__ void __launch_bounds__(kLossThreads, 4)
 mse_fused_kernel(const void* __restrict__ pred, const float* __restrict__ joints, int n_maps, int H, int W,
                  int vec_ok, float sigma, float sx, float sy, float* __restrict__ partials,
                  void* __restrict__ grad, float gcoef, float* __restrict__ weight_out) {
@@ -62,10 +62,11 @@ mse_fused_kernel(const void* __restrict__ pred, const float* __restrict__ joints
   const int nwarps = (gridDim.x * kLossThreads) >> 5;
   const int HW     = H * W;
   const int nvec   = vec_ok ? HW / EPV : 0;       // vec_ok also guarantees W % EPV == 0
-  // forward-only: 12 independent 16-byte loads per lane in flight (4 left this pass latency-bound at 66 % / 41 % of HBM: per
-  // map a warp pays joints-load latency + data-load latency + reduction in sequence, and without the gradient store nothing
-  // else overlaps them) and the NEXT map's joint is fetched while the current map streams.  With the gradient store 4 is enough.
-  constexpr int U  = GRAD ? kLossUnroll : 12;     // forward-only: a whole 64x48 bf16 map (12 vectors per lane) in one batch of loads
+  // This pass is ALU-bound, not latency-bound (r02 measurement: forward-only moved exactly half the bytes per second of the
+  // forward+backward variant, bf16 half of fp32, and deeper unrolling made it slower): what counts is instructions per element.
+  // Hence no integer division per vector, and vectors outside the +-3 sigma support (94 % of a 64x48 map) take the short
+  // path d = p (w == 1 here: maps with w == 0 never reach this loop), one FMA per element.
+  constexpr int U  = kLossUnroll;
   const float inv_w = 1.0f / (float)W;            // row of a vector without an integer division (exact: e < 2^22, see below)
 
   float jx = 0.f, jy = 0.f, jv = 0.f;
@@ -91,6 +92,9 @@ mse_fused_kernel(const void* __restrict__ pred, const float* __restrict__ joints
       if (lane == 0) partials[map] = 0.f;
       continue;
     }
+    // first / one-past-last vector of the rows the Gaussian support touches (one row per vector: W % EPV == 0)
+    const int vpr = W / EPV;
+    const int v_lo = max(g.mu_y - g.t, 0) * vpr, v_hi = min(g.mu_y + g.t + 1, H) * vpr;
     const float gc = gcoef * g.w;                 // dL/dp = gscale * w^2 (p-g)/n = (w p - w g) * gscale * w / n
     for (int v0 = 0; v0 < nvec; v0 += 32 * U) {
       uint4 r[U];
@@ -104,11 +108,6 @@ mse_fused_kernel(const void* __restrict__ pred, const float* __restrict__ joints
         const int v = v0 + u * 32 + lane;
         if (v < nvec) {
           const int e = v * EPV;
-          // one row per vector (W % EPV == 0).  y = floor(e / W) from the fp32 product, corrected by one step: exact for
-          // every e < 2^22 (maps up to 2048 x 2048), no integer division in the loop
-          int y = (int)(((float)e + 0.5f) * inv_w);
-          int x0 = e - y * W;
-          if (x0 < 0) { --y; x0 += W; } else if (x0 >= W) { ++y; x0 -= W; }
           float p[EPV];
           if constexpr (BF16) {
             p[0] = bf16_lo(r[u].x); p[1] = bf16_hi(r[u].x); p[2] = bf16_lo(r[u].y); p[3] = bf16_hi(r[u].y);
@@ -117,13 +116,27 @@ mse_fused_kernel(const void* __restrict__ pred, const float* __restrict__ joints
             p[0] = __uint_as_float(r[u].x); p[1] = __uint_as_float(r[u].y);
             p[2] = __uint_as_float(r[u].z); p[3] = __uint_as_float(r[u].w);
           }
-          const bool hit = abs(y - g.mu_y) <= g.t && x0 <= g.mu_x + g.t && x0 + EPV - 1 >= g.mu_x - g.t;
+          // vectors of rows mu_y - t .. mu_y + t only (two compares); the row / column of a vector is computed inside that
+          // window alone: y = floor(e / W) from the fp32 product, corrected by one step -- exact for e < 2^22, no integer division
+          bool hit = v >= v_lo && v < v_hi;
+          int y = 0, x0 = 0;
+          if (hit) {
+            y = (int)(((float)e + 0.5f) * inv_w);
+            x0 = e - y * W;
+            if (x0 < 0) { --y; x0 += W; } else if (x0 >= W) { ++y; x0 -= W; }
+            hit = abs(y - g.mu_y) <= g.t && x0 <= g.mu_x + g.t && x0 + EPV - 1 >= g.mu_x - g.t;
+          }
           float d[EPV];
+          if (!hit) {                                 // g == 0 and w == 1:  w*p - w*0 == p  (same bits as the general form)
 #pragma unroll
-          for (int j = 0; j < EPV; ++j) {
-            const float gt = hit ? gauss_at(g, x0 + j, y) : 0.f;
-            d[j] = g.w * p[j] - g.w * gt;
-            acc = fmaf(d[j], d[j], acc);
+            for (int j = 0; j < EPV; ++j) { d[j] = p[j]; acc = fmaf(p[j], p[j], acc); }
+          } else {
+#pragma unroll
+            for (int j = 0; j < EPV; ++j) {
+              const float gt = gauss_at(g, x0 + j, y);
+              d[j] = g.w * p[j] - g.w * gt;
+              acc = fmaf(d[j], d[j], acc);
+            }
           }
           if (GRAD) {
             uint4 o;

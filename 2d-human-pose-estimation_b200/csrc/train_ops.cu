@@ -3,6 +3,7 @@
 // saved argmax + its backward, heatmap-gradient layout change, SGD momentum step.
 // All are plain vectorised (16-byte) grid-stride kernels: one pass over the tensor each, fp32 math.
 #include "hpe_common.cuh"
+#include <math.h>
 
 namespace hpe {
 
@@ -391,6 +392,59 @@ sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict
   }
 }
 
+// ---- AdamW + gradient-norm clipping (the reference's working trainer: optim.AdamW + clip_grad_norm_(10), HPE/train.py:52-55, 136) --
+// Sum of squares of a flat fp32 buffer, deterministic: fixed per-thread order, shuffle tree, one partial per block, then a
+// single-block fixed-order finish (no atomics) -> the clip coefficient, hence the whole update, is run-to-run bit-stable.
+__global__ void __launch_bounds__(256)
+sumsq_partial_kernel(const float* __restrict__ g, long long n, float* __restrict__ part) {
+  __shared__ float red[8];
+  float a = 0.f;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) { const float v = g[i]; a = fmaf(v, v, a); }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) a += __shfl_xor_sync(0xffffffffu, a, off);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = a;
+  __syncthreads();
+  if (threadIdx.x == 0) { float s = 0.f; for (int w = 0; w < 8; ++w) s += red[w]; part[blockIdx.x] = s; }
+}
+__global__ void __launch_bounds__(256)
+sumsq_finish_kernel(const float* __restrict__ part, int nparts, float* __restrict__ out, int accumulate) {
+  __shared__ double red[256];
+  double a = 0.0;
+  for (int i = threadIdx.x; i < nparts; i += 256) a += static_cast<double>(part[i]);
+  red[threadIdx.x] = a;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double s = 0.0;
+    for (int i = 0; i < 256; ++i) s += red[i];
+    out[0] = (accumulate ? out[0] : 0.f) + static_cast<float>(s);
+  }
+}
+// torch.optim.AdamW (decoupled weight decay, no amsgrad), with torch.nn.utils.clip_grad_norm_ folded in:
+//   clip = min(1, max_norm / (sqrt(sumsq) + 1e-6));  g = grad * grad_scale * clip;  p *= 1 - lr*wd
+//   m = b1*m + (1-b1)*g;  v = b2*v + (1-b2)*g*g;  p -= (lr / bc1) * m / (sqrt(v) / sqrt(bc2) + eps)
+__global__ void __launch_bounds__(256)
+adamw_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, long long n,
+             float lr, float b1, float b2, float eps, float wd, float bc1, float rsqrt_bc2, float grad_scale,
+             const float* __restrict__ sumsq, float max_norm) {
+  float clip = 1.f;
+  if (sumsq != nullptr && max_norm > 0.f) {
+    // the norm is of the gradient AFTER grad_scale (the averaged gradient), like clip_grad_norm_ on DDP-averaged .grad
+    const float norm = sqrtf(__ldg(sumsq)) * fabsf(grad_scale);
+    clip = fminf(1.f, max_norm / (norm + 1e-6f));
+  }
+  const float gs = grad_scale * clip, step = lr / bc1, decay = 1.f - lr * wd;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float gi = g[i] * gs;
+    const float mi = fmaf(b1, m[i], (1.f - b1) * gi);
+    const float vi = fmaf(b2, v[i], (1.f - b2) * gi * gi);
+    m[i] = mi; v[i] = vi;
+    const float denom = fmaf(sqrtf(vi), rsqrt_bc2, eps);
+    p[i] = fmaf(-step, __fdiv_rn(mi, denom), p[i] * decay);
+  }
+}
+
 static inline int ew_grid(long long n, int per_block = 256) {
   long long g = (n + per_block - 1) / per_block;
   const long long cap = static_cast<long long>(num_sms()) * 16;
@@ -502,4 +556,27 @@ extern "C" int hpe_sgd_step(float* param, const float* grad, float* momentum_buf
   HPE_CHECK_ARG(param && grad && momentum_buf && n > 0, "hpe_sgd_step: null pointer or empty");
   sgd_kernel<<<ew_grid(n), 256, 0, (cudaStream_t)stream>>>(param, grad, momentum_buf, n, lr, momentum, weight_decay, grad_scale);
   return launch_status("sgd_kernel");
+}
+
+extern "C" size_t hpe_grad_sumsq_scratch_elems(void) { return (size_t)num_sms() * 16; }
+
+extern "C" int hpe_grad_sumsq(const float* grad, long long n, float* scratch, float* out, int accumulate, void* stream) {
+  HPE_CHECK_ARG(grad && scratch && out && n > 0, "hpe_grad_sumsq: null pointer or empty");
+  const int grid = ew_grid(n);
+  sumsq_partial_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(grad, n, scratch);
+  int rc = launch_status("sumsq_partial_kernel");
+  if (rc) return rc;
+  sumsq_finish_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(scratch, grid, out, accumulate);
+  return launch_status("sumsq_finish_kernel");
+}
+
+extern "C" int hpe_adamw_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, long long n, float lr, float beta1,
+                              float beta2, float eps, float weight_decay, int step, float grad_scale, const float* grad_sumsq,
+                              float max_norm, void* stream) {
+  HPE_CHECK_ARG(param && grad && exp_avg && exp_avg_sq && n > 0, "hpe_adamw_step: null pointer or empty");
+  HPE_CHECK_ARG(step >= 1 && beta1 >= 0.f && beta1 < 1.f && beta2 >= 0.f && beta2 < 1.f, "hpe_adamw_step: step must be >= 1 and betas in [0,1)");
+  const double bc1 = 1.0 - pow((double)beta1, (double)step), bc2 = 1.0 - pow((double)beta2, (double)step);
+  adamw_kernel<<<ew_grid(n), 256, 0, (cudaStream_t)stream>>>(param, grad, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay,
+                                                            (float)bc1, (float)(1.0 / sqrt(bc2)), grad_scale, grad_sumsq, max_norm);
+  return launch_status("adamw_kernel");
 }

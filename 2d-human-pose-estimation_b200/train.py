@@ -106,6 +106,32 @@ def sgd_step(param, grad, mom, lr, momentum, weight_decay, grad_scale=1.0):
     _lib.check(rc, "hpe_sgd_step")
 
 
+_sumsq_scratch = {}
+
+
+def grad_sumsq(grad, out, accumulate=False):
+    """``out[0] (+)= sum(grad**2)`` over a flat fp32 buffer, deterministic (``clip_grad_norm_``'s norm without a host sync)."""
+    key = (grad.device.index, torch.cuda.current_stream(grad.device).cuda_stream)
+    if key not in _sumsq_scratch:
+        _sumsq_scratch[key] = torch.empty(_lib.lib().hpe_grad_sumsq_scratch_elems(), dtype=torch.float32, device=grad.device)
+    with torch.cuda.device(grad.device):
+        rc = _lib.lib().hpe_grad_sumsq(_lib.ptr(grad), grad.numel(), _lib.ptr(_sumsq_scratch[key]), _lib.ptr(out), int(bool(accumulate)),
+                                       _lib.stream_ptr())
+    _lib.check(rc, "hpe_grad_sumsq")
+    return out
+
+
+def adamw_step(param, grad, exp_avg, exp_avg_sq, step, lr, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2, grad_scale=1.0,
+               sumsq=None, max_norm=0.0):
+    """``torch.optim.AdamW`` step over a flat fp32 buffer with ``clip_grad_norm_(max_norm)`` folded in (HPE/train.py:52-55, 136);
+    ``sumsq`` = device scalar from ``grad_sumsq`` (the squared global gradient norm)."""
+    with torch.cuda.device(param.device):
+        rc = _lib.lib().hpe_adamw_step(_lib.ptr(param), _lib.ptr(grad), _lib.ptr(exp_avg), _lib.ptr(exp_avg_sq), param.numel(),
+                                       float(lr), float(betas[0]), float(betas[1]), float(eps), float(weight_decay), int(step),
+                                       float(grad_scale), _lib.ptr(sumsq), float(max_norm), _lib.stream_ptr())
+    _lib.check(rc, "hpe_adamw_step")
+
+
 # ---- one conv + BatchNorm (+ReLU) (+residual) unit in training mode ------------------------------------------------
 class _Unit:
     def __init__(self, conv_name, bn_name, kind, B, H, W, Cin, Cout, stride, relu, dev, dgrad=True, dgrad_acc=False):
@@ -377,7 +403,14 @@ class TrainStep:
     shard are summed over ranks with one NCCL all-reduce of the flat buffer and divided by the world size in the
     SGD kernel (equal shards => the global-batch mean)."""
 
-    def __init__(self, model, lr=1e-3, momentum=0.9, weight_decay=0.0, sigma=2.0, group=None, cuda_graph=True):
+    def __init__(self, model, lr=1e-3, momentum=0.9, weight_decay=0.0, sigma=2.0, group=None, cuda_graph=True,
+                 optimizer="sgd", betas=(0.9, 0.999), eps=1e-8, max_grad_norm=0.0):
+        """``optimizer``: "sgd" (config default, HPE/configs/default.py:34: momentum SGD) or "adamw" (the reference's working
+        trainer, HPE/train.py:52-55) with ``clip_grad_norm_(max_grad_norm)`` (HPE/train.py:136; 0 = no clipping)."""
+        if optimizer not in ("sgd", "adamw"):
+            raise ValueError(f"optimizer '{optimizer}' not built (sgd | adamw)")
+        self.optimizer, self.betas, self.eps, self.max_grad_norm = optimizer, tuple(betas), eps, float(max_grad_norm)
+        self._t = 0
         self.model = model.train()
         self.use_graph = bool(cuda_graph)
         self._key, self.graph, self.plan = None, None, None
@@ -388,7 +421,9 @@ class TrainStep:
         self.device = dev
         self.flat_param = torch.zeros(self.layout.total, dtype=torch.float32, device=dev)
         self.flat_grad = torch.zeros_like(self.flat_param)
-        self.flat_mom = torch.zeros_like(self.flat_param)
+        self.flat_mom = torch.zeros_like(self.flat_param)              # SGD momentum / AdamW exp_avg
+        self.flat_sq = torch.zeros_like(self.flat_param) if optimizer == "adamw" else None      # AdamW exp_avg_sq
+        self.grad_sumsq = torch.zeros(1, dtype=torch.float32, device=dev)
         pv = self.layout.views(self.flat_param)
         with torch.no_grad():
             for n, p in model.named_parameters():       # re-point the parameters at the flat buffer
@@ -434,8 +469,16 @@ class TrainStep:
         nt = self.layout.trainable_total
         if self.world > 1:
             dist.all_reduce(self.flat_grad[:nt], op=dist.ReduceOp.SUM, group=self.group)
-        sgd_step(self.flat_param[:nt], self.flat_grad[:nt], self.flat_mom[:nt], self.lr, self.momentum, self.weight_decay,
-                 1.0 / self.world)
+        if self.optimizer == "adamw":
+            self._t += 1
+            clip = self.max_grad_norm > 0
+            if clip:                                  # global norm of the (summed) gradient; the kernel scales it by 1/world
+                grad_sumsq(self.flat_grad[:nt], self.grad_sumsq)
+            adamw_step(self.flat_param[:nt], self.flat_grad[:nt], self.flat_mom[:nt], self.flat_sq[:nt], self._t, self.lr, self.betas,
+                       self.eps, self.weight_decay, 1.0 / self.world, self.grad_sumsq if clip else None, self.max_grad_norm)
+        else:
+            sgd_step(self.flat_param[:nt], self.flat_grad[:nt], self.flat_mom[:nt], self.lr, self.momentum, self.weight_decay,
+                     1.0 / self.world)
         self.flat_nbt.add_(1)
 
     def _step(self, images, joints):
@@ -473,14 +516,15 @@ class TrainStep:
             if self.graph is None:
                 torch.cuda.synchronize(self.device)
                 g = torch.cuda.CUDAGraph()
+                self._update_outside = self.world > 1 or self.optimizer == "adamw"    # AdamW's bias correction changes per step
                 with torch.cuda.graph(g):
-                    if self.world > 1:
+                    if self._update_outside:
                         self._compute(self.x_static, self.j_static)
                     else:
                         self._step(self.x_static, self.j_static)
                 self.graph = g
             self.graph.replay()
-            if self.world > 1:
+            if self._update_outside:
                 self._update()
         model._weights_version += 1
         return self.loss

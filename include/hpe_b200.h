@@ -256,6 +256,19 @@ int hpe_heatmap_grad_nhwc(const void* dhm, int dtype, int B, int K, int H, int W
  * (`optimizer.step()`, HPE/engine/trainer.py:98-100): g' = grad*grad_scale + wd*p; m = mu*m + g'; p -= lr*m. */
 int hpe_sgd_step(float* param, const float* grad, float* momentum_buf, long long n, float lr, float momentum,
                  float weight_decay, float grad_scale, void* stream);
+/* The optimizer of the reference's WORKING trainer: optim.AdamW (two learning-rate groups, HPE/train.py:52-55) after
+ * torch.nn.utils.clip_grad_norm_(model.parameters(), 10.0) (HPE/train.py:136).
+ * hpe_grad_sumsq: out[0] (+)= sum grad^2 over a flat fp32 buffer, deterministic two-stage reduction; `scratch` holds at least
+ *   hpe_grad_sumsq_scratch_elems() floats.  Call once per parameter group with accumulate = 1 to get the global norm.
+ * hpe_adamw_step: decoupled weight decay, bias correction for the 1-based `step`, no amsgrad (torch.optim.AdamW):
+ *   clip = min(1, max_norm / (sqrt(*grad_sumsq) * |grad_scale| + 1e-6))  (grad_sumsq NULL or max_norm <= 0: no clipping)
+ *   g = grad*grad_scale*clip;  p *= 1 - lr*wd;  m = b1 m + (1-b1) g;  v = b2 v + (1-b2) g^2;
+ *   p -= lr/(1-b1^step) * m / (sqrt(v)/sqrt(1-b2^step) + eps).   The norm is read on the device: no host synchronisation. */
+size_t hpe_grad_sumsq_scratch_elems(void);
+int hpe_grad_sumsq(const float* grad, long long n, float* scratch, float* out, int accumulate, void* stream);
+int hpe_adamw_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, long long n, float lr, float beta1,
+                   float beta2, float eps, float weight_decay, int step, float grad_scale, const float* grad_sumsq,
+                   float max_norm, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * The reference's OWN pose-head post-processing, loss and metrics: these stages

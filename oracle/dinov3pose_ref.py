@@ -294,7 +294,15 @@ def build_synthetic_heatmap(size="tiny", num_joints=17, seed=0):
             elif isinstance(mod, Block):
                 mod.gamma.copy_(torch.rand(mod.gamma.shape, generator=g) * 0.8 + 0.2)
         m.eval()
-        x = torch.rand(1, 3, 128, 96, generator=torch.Generator().manual_seed(1234))
-        m.final_layer.weight.div_(m(x).abs().max())
+        # head BatchNorm running statistics CALIBRATED on a seeded batch (like a trained net's; random statistics make the three
+        # un-normalised deconv stages amplify every upstream rounding error), then the final 1x1 rescaled to max|heatmap| = 1
+        x = torch.rand(2, 3, 128, 96, generator=torch.Generator().manual_seed(1234))
+        f = m.forward_features(x)
+        for i in (0, 3, 6):
+            z = m.deconv_layers[i](f)
+            bn = m.deconv_layers[i + 1]
+            bn.running_mean.copy_(z.mean((0, 2, 3))); bn.running_var.copy_(z.var((0, 2, 3), unbiased=False))
+            f = torch.relu(bn(z))
         m.final_layer.bias.zero_()
+        m.final_layer.weight.div_(m.final_layer(f).abs().max())
     return m

@@ -308,3 +308,62 @@ def test_train_step_cuda_graph_matches_eager(hpe, cuda_dev):
         assert abs(a - b) <= 1e-3 * abs(a), (losses[0], losses[1])
     assert losses[0][-1] < losses[0][0]                       # the loss goes down
     assert _rel(finals[1], finals[0]) <= 1e-2
+
+
+@pytest.mark.parametrize("max_norm", [0.0, 10.0, 0.05])
+def test_adamw_step_and_grad_clip_match_torch(hpe, cuda_dev, max_norm):
+    """hpe_adamw_step / hpe_grad_sumsq vs torch.optim.AdamW after torch.nn.utils.clip_grad_norm_ (the optimizer of the reference's
+    working trainer, HPE/train.py:52-55 and :136), several steps, two parameter groups with their own learning rates."""
+    g = torch.Generator().manual_seed(17)
+    sizes, lrs = (100_003, 4_096), (1e-2, 1e-3)
+    ps = [torch.randn(n, generator=g).to(cuda_dev) for n in sizes]
+    ref_p = [torch.nn.Parameter(p.clone()) for p in ps]
+    opt = torch.optim.AdamW([{"params": [ref_p[0]], "lr": lrs[0]}, {"params": [ref_p[1]], "lr": lrs[1]}], weight_decay=5e-4)
+    m = [torch.zeros_like(p) for p in ps]
+    v = [torch.zeros_like(p) for p in ps]
+    sumsq = torch.zeros(1, device=cuda_dev)
+    for step in range(1, 5):
+        grads = [(torch.randn(n, generator=g) * (0.5 if step % 2 else 3.0)).to(cuda_dev) for n in sizes]
+        for rp, gr in zip(ref_p, grads):
+            rp.grad = gr.clone()
+        if max_norm > 0:
+            total = torch.nn.utils.clip_grad_norm_(ref_p, max_norm)
+        opt.step()
+        if max_norm > 0:
+            for k, gr in enumerate(grads):                       # global norm over BOTH groups
+                hpe.grad_sumsq(gr, sumsq, accumulate=k > 0)
+            assert abs(sumsq.sqrt().item() - total.item()) <= 1e-5 * total.item()
+        for k in range(2):
+            hpe.adamw_step(ps[k], grads[k], m[k], v[k], step, lrs[k], (0.9, 0.999), 1e-8, 5e-4, 1.0,
+                           sumsq if max_norm > 0 else None, max_norm)
+        for k in range(2):
+            assert torch.allclose(ps[k], ref_p[k].detach(), rtol=2e-5, atol=2e-7), (step, k, (ps[k] - ref_p[k]).abs().max().item())
+    a = hpe.grad_sumsq(grads[0], torch.zeros(1, device=cuda_dev)).item()
+    b = hpe.grad_sumsq(grads[0], torch.zeros(1, device=cuda_dev)).item()
+    assert a == b                                               # deterministic reduction
+
+
+def test_train_step_adamw_with_clipping_trains(hpe, cuda_dev):
+    """TrainStep(optimizer='adamw', max_grad_norm=10): the fused step with the reference trainer's optimizer (HPE/train.py:52-55,
+    136): the loss falls and every parameter moves by at most lr per step (AdamW's bound)."""
+    def run():
+        torch.manual_seed(3)
+        m = hpe.HeatmapPose(17, "resnet50", pretrained=False)
+        for n, mod in m.named_modules():
+            if isinstance(mod, torch.nn.BatchNorm2d):
+                mod.weight.data.uniform_(0.5, 1.5)
+                if n.endswith("bn3"):
+                    mod.weight.data.mul_(0.2)
+        m = m.to(cuda_dev).train()
+        step = hpe.TrainStep(m, lr=1e-3, weight_decay=5e-4, optimizer="adamw", max_grad_norm=10.0)
+        g = torch.Generator().manual_seed(4)
+        x = torch.rand(4, 3, 128, 96, generator=g).to(cuda_dev)
+        joints = (torch.rand(4, 17, 3, generator=g) * torch.tensor([96.0, 128.0, 1.0]) + torch.tensor([0.0, 0.0, 0.3])).to(cuda_dev)
+        p0 = step.flat_param.clone()
+        losses = [step(x, joints).item() for _ in range(4)]
+        return p0, step.flat_param.clone(), losses, step.flat_grad.clone()
+    p0, p1, losses, g1 = run()
+    assert all(l == l and l > 0 for l in losses) and not torch.equal(p0, p1)
+    upd = (p1 - p0).abs().max().item()
+    assert 0 < upd <= 4 * 1e-3 * 1.05 + 1e-3, upd              # |AdamW update| <= lr per step (+ decay)
+    assert losses[-1] < losses[0]
