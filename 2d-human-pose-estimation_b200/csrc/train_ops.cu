@@ -342,40 +342,51 @@ maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const uint8_t* __restri
 // wgrad operand); also dbias[k] = sum over b,y,x
 template <bool BF16>
 __global__ void __launch_bounds__(256)
-hm_grad_nhwc_kernel(const void* __restrict__ dhm, int B, int K, int HW, __nv_bfloat16* __restrict__ out, float* dbias) {
-  __shared__ float sb[64];
-  if (threadIdx.x < 64) sb[threadIdx.x] = 0.f;
-  __syncthreads();
+hm_grad_nhwc_kernel(const void* __restrict__ dhm, int B, int K, int HW, __nv_bfloat16* __restrict__ out) {
   const long long total = static_cast<long long>(B) * HW;
-  const int lane = threadIdx.x & 31;
   for (long long base = static_cast<long long>(blockIdx.x) * blockDim.x; base < total;
        base += static_cast<long long>(gridDim.x) * blockDim.x) {
     const long long i = base + threadIdx.x;
-    const bool ok = i < total;
-    const int b = ok ? static_cast<int>(i / HW) : 0, pix = ok ? static_cast<int>(i % HW) : 0;
+    if (i >= total) continue;
+    const int b = static_cast<int>(i / HW), pix = static_cast<int>(i % HW);
     for (int k0 = 0; k0 < 64; k0 += 8) {
       float f[8];
 #pragma unroll
       for (int e = 0; e < 8; ++e) {
         const int k = k0 + e;
         float v = 0.f;
-        if (ok && k < K) {
+        if (k < K) {
           const size_t off = (static_cast<size_t>(b) * K + k) * HW + pix;
           v = BF16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(dhm)[off]) : reinterpret_cast<const float*>(dhm)[off];
         }
         f[e] = v;
-        if (dbias && k < K) {                       // warp-uniform condition
-          float s = v;
-#pragma unroll
-          for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-          if (lane == 0) atomicAdd(&sb[k], s);
-        }
       }
-      if (ok) reinterpret_cast<uint4*>(out + static_cast<size_t>(i) * 64 + k0)[0] = pack8(f);
+      reinterpret_cast<uint4*>(out + static_cast<size_t>(i) * 64 + k0)[0] = pack8(f);
     }
   }
+}
+
+// dbias[k] = sum over b, y, x of dL/dheatmap[b][k]: one block per joint, a warp per map (coalesced, fixed lane order + shuffle
+// tree), maps b = warp, warp + 8, ... added in order, the eight warps' sums added in order -> deterministic (round 1 used
+// shared + global fp32 atomics here, the last run-to-run varying reduction of the training step besides the wgrad split-K)
+template <bool BF16>
+__global__ void __launch_bounds__(256)
+hm_dbias_kernel(const void* __restrict__ dhm, int B, int K, int HW, float* __restrict__ dbias) {
+  __shared__ float red[8];
+  const int k = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float acc = 0.f;
+  for (int b = warp; b < B; b += 8) {
+    const size_t off = (static_cast<size_t>(b) * K + k) * HW;
+    float a = 0.f;
+    for (int i = lane; i < HW; i += 32)
+      a += BF16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(dhm)[off + i]) : reinterpret_cast<const float*>(dhm)[off + i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+    acc += a;
+  }
+  if (lane == 0) red[warp] = acc;
   __syncthreads();
-  if (dbias && threadIdx.x < K) atomicAdd(dbias + threadIdx.x, sb[threadIdx.x]);
+  if (threadIdx.x == 0) { float s = 0.f; for (int w = 0; w < 8; ++w) s += red[w]; dbias[k] = s; }
 }
 
 // SGD with momentum (torch.optim.SGD, dampening 0, no nesterov):  g' = g*grad_scale + wd*p; m = mu*m + g'; p -= lr*m
@@ -543,12 +554,15 @@ extern "C" int hpe_heatmap_grad_nhwc(const void* dhm, int dtype, int B, int K, i
   HPE_CHECK_ARG(B > 0 && K > 0 && K <= 64 && H > 0 && W > 0, "hpe_heatmap_grad_nhwc: need 0 < K <= 64");
   HPE_CHECK_ARG(dtype == HPE_F32 || dtype == HPE_BF16, "hpe_heatmap_grad_nhwc: bad dtype %d", dtype);
   cudaStream_t st = (cudaStream_t)stream;
-  if (dbias) HPE_CUDA_OK(cudaMemsetAsync(dbias, 0, (size_t)K * sizeof(float), st));
   const long long total = (long long)B * H * W;
   const int grid = ew_grid(total);
-  if (dtype == HPE_BF16) hm_grad_nhwc_kernel<true><<<grid, 256, 0, st>>>(dhm, B, K, H * W, (__nv_bfloat16*)out, dbias);
-  else                   hm_grad_nhwc_kernel<false><<<grid, 256, 0, st>>>(dhm, B, K, H * W, (__nv_bfloat16*)out, dbias);
-  return launch_status("hm_grad_nhwc_kernel");
+  if (dtype == HPE_BF16) hm_grad_nhwc_kernel<true><<<grid, 256, 0, st>>>(dhm, B, K, H * W, (__nv_bfloat16*)out);
+  else                   hm_grad_nhwc_kernel<false><<<grid, 256, 0, st>>>(dhm, B, K, H * W, (__nv_bfloat16*)out);
+  int rc = launch_status("hm_grad_nhwc_kernel");
+  if (rc || !dbias) return rc;
+  if (dtype == HPE_BF16) hm_dbias_kernel<true><<<K, 256, 0, st>>>(dhm, B, K, H * W, dbias);
+  else                   hm_dbias_kernel<false><<<K, 256, 0, st>>>(dhm, B, K, H * W, dbias);
+  return launch_status("hm_dbias_kernel");
 }
 
 extern "C" int hpe_sgd_step(float* param, const float* grad, float* momentum_buf, long long n, float lr, float momentum,

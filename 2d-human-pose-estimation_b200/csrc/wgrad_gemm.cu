@@ -11,8 +11,10 @@
 //     transposed convolutions (dW[ci,co,ky,kx] = sum x[iy,ix,ci] dz[2iy-1+ky, 2ix-1+kx, co]).
 //     An M tile = two 64-channel blocks, each with its own (tap, channel block).
 //   * R ("right", the N side, BLOCK_N <= 256 channels) is read unshifted on the pixel grid.
-//   * split-K over pixel bricks across the persistent grid; fp32 partial tiles are added into a workspace
-//     [n_lblocks*64][N] with red.global.add.v4.f32; a tiny kernel then permutes it into the PyTorch weight layout.
+//   * split-K over pixel bricks across the persistent grid; every (tile, split) item writes its fp32 partial tile with plain
+//     stores into ITS OWN slice of the workspace [splits][n_lblocks*64][N]; a small kernel then adds the slices in a fixed
+//     order while permuting into the PyTorch weight layout.  No atomics, no memset: the weight gradients -- like the forward --
+//     are run-to-run bit-stable (round 1 accumulated with red.global.add.f32, whose order varies from run to run).
 // Warp roles: warp 0 TMA producer, warp 1 TMEM alloc + MMA issuer, warps 2-9 epilogue (TMEM -> red.global).
 #include "hpe_common.cuh"
 #include "ptx_sm100.cuh"
@@ -34,6 +36,7 @@ struct WgradParams {
   int kw, kh, knb, tiles_x, tiles_y;
   int lstride;
   int out_cols;
+  long long ws_slice;          // elements of one split's slice of the workspace
   float* ws;
 };
 
@@ -50,8 +53,8 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16_m128_mnmajor(int n) {
   return make_idesc_bf16_m128(n) | (1u << 15) | (1u << 16);
 }
 
-__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
-  asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+__device__ __forceinline__ void st_v4f(float* p, float a, float b, float c, float d) {
+  asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
 template <int BLOCK_N, int STAGES>
@@ -98,8 +101,9 @@ wgrad_gemm_kernel(const __grid_constant__ CUtensorMap tmL, const __grid_constant
   griddep_wait();
 
   // work item -> (m tile, n tile, brick range)
-  auto item_range = [&](int item, int& mt, int& nt, int& q0, int& q1) {
+  auto item_range = [&](int item, int& mt, int& nt, int& q0, int& q1, int* split = nullptr) {
     const int sp = item % p.splits; int r = item / p.splits;
+    if (split) *split = sp;
     nt = r % p.n_ntiles; mt = r / p.n_ntiles;
     q0 = sp * p.bricks_per_split;
     q1 = q0 + p.bricks_per_split; if (q1 > p.bricks) q1 = p.bricks;
@@ -170,14 +174,14 @@ wgrad_gemm_kernel(const __grid_constant__ CUtensorMap tmL, const __grid_constant
     const int row = ew * 32 + lane;                 // tile row: block h = row / 64, channel-in-block = row % 64
     int it = 0;
     for (int item = blockIdx.x; item < p.num_items; item += gridDim.x, ++it) {
-      int mt, nt, q0, q1; item_range(item, mt, nt, q0, q1);
+      int mt, nt, q0, q1, sp; item_range(item, mt, nt, q0, q1, &sp);
       const int acc = it & 1;
       mbar_wait(&tfull_bar[acc], (it >> 1) & 1);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + acc * BLOCK_N;
       const int lb = 2 * mt + (row >> 6);
       const bool live = lb < p.n_lblocks;
-      float* dst = p.ws + (static_cast<size_t>(lb) * 64 + (row & 63)) * p.out_cols + nt * BLOCK_N;
+      float* dst = p.ws + static_cast<size_t>(sp) * p.ws_slice + (static_cast<size_t>(lb) * 64 + (row & 63)) * p.out_cols + nt * BLOCK_N;
       for (int g = half; g * 32 < BLOCK_N; g += 2) {
         uint32_t v[32];
         tmem_ld_x32(taddr + g * 32, v);
@@ -185,7 +189,7 @@ wgrad_gemm_kernel(const __grid_constant__ CUtensorMap tmL, const __grid_constant
         if (live) {
 #pragma unroll
           for (int e = 0; e < 32; e += 4)
-            red_add_v4(dst + g * 32 + e, __uint_as_float(v[e]), __uint_as_float(v[e + 1]), __uint_as_float(v[e + 2]),
+            st_v4f(dst + g * 32 + e, __uint_as_float(v[e]), __uint_as_float(v[e + 1]), __uint_as_float(v[e + 2]),
                        __uint_as_float(v[e + 3]));
         }
       }
@@ -203,7 +207,7 @@ wgrad_gemm_kernel(const __grid_constant__ CUtensorMap tmL, const __grid_constant
 // workspace [rows][cols] fp32 -> PyTorch weight layout (optionally accumulating)
 __global__ void __launch_bounds__(256)
 wgrad_unpack_kernel(const float* __restrict__ ws, int kind, int swapped, int Cin, int Cout, int cols, long long total,
-                    float* __restrict__ dw, int accumulate) {
+                    float* __restrict__ dw, int accumulate, int splits, long long ws_slice) {
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
     size_t src;
@@ -225,7 +229,8 @@ wgrad_unpack_kernel(const float* __restrict__ ws, int kind, int swapped, int Cin
       const int t = static_cast<int>(i % 16), co = static_cast<int>((i / 16) % Cout), ci = static_cast<int>(i / (16LL * Cout));
       src = (static_cast<size_t>(t) * Cout + co) * cols + ci;
     }
-    const float v = ws[src];
+    float v = 0.f;
+    for (int sp = 0; sp < splits; ++sp) v += ws[static_cast<size_t>(sp) * ws_slice + src];      // fixed order: deterministic
     dw[i] = accumulate ? dw[i] + v : v;
   }
 }
@@ -307,7 +312,8 @@ extern "C" int hpe_wgrad_plan_create(const hpe_conv_desc* d, hpe_wgrad_plan** ou
   p.splits = (p.bricks + p.bricks_per_split - 1) / p.bricks_per_split;
   p.num_items = tiles * p.splits;
   pl->grid = p.num_items < num_sms() ? p.num_items : num_sms();
-  pl->ws_elems = (size_t)p.n_lblocks * 64 * p.out_cols;
+  p.ws_slice = (long long)p.n_lblocks * 64 * p.out_cols;
+  pl->ws_elems = (size_t)p.ws_slice * p.splits;
   WgKernelFn fn;
   switch (pl->block_n) {
     case 64:  fn = wgrad_gemm_kernel<64, 8>;  pl->smem = WgSmem<64, 8>::kDynamic; break;
@@ -376,8 +382,7 @@ extern "C" int hpe_wgrad_run(hpe_wgrad_plan* pl, const void* x, const void* dz, 
   int rc = wg_encode(pl, x, dz);
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
-  HPE_CUDA_OK(cudaMemsetAsync(workspace, 0, pl->ws_elems * sizeof(float), st));
-  WgradParams p = pl->p;
+  WgradParams p = pl->p;                       // (no memset: every slice element that is read is written by exactly one item)
   p.ws = workspace;
   void* args[3] = {&pl->tmL, &pl->tmR, &p};
   cudaError_t e = cudaLaunchKernel(pl->fn, dim3(pl->grid), dim3(kWgThreads), args, pl->smem, st);
@@ -385,6 +390,6 @@ extern "C" int hpe_wgrad_run(hpe_wgrad_plan* pl, const void* x, const void* dz, 
   const long long total = (long long)wg_weight_elems(&pl->d);
   const int grid = (int)((total + 255) / 256 > 2048 ? 2048 : (total + 255) / 256);
   wgrad_unpack_kernel<<<grid, 256, 0, st>>>(workspace, pl->d.kind, p.swapped, pl->d.Cin, pl->d.Cout, p.out_cols, total,
-                                           dw_torch, accumulate);
+                                           dw_torch, accumulate, p.splits, p.ws_slice);
   return launch_status("wgrad_unpack_kernel");
 }

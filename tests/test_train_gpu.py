@@ -367,3 +367,31 @@ def test_train_step_adamw_with_clipping_trains(hpe, cuda_dev):
     upd = (p1 - p0).abs().max().item()
     assert 0 < upd <= 4 * 1e-3 * 1.05 + 1e-3, upd              # |AdamW update| <= lr per step (+ decay)
     assert losses[-1] < losses[0]
+
+
+def test_train_step_bitwise_reproducible(hpe, cuda_dev):
+    """Two identical training steps from identical state give BIT-IDENTICAL gradients, losses and parameters: the wgrad split-K
+    partials go to per-split workspace slices added in a fixed order, BatchNorm / loss / bias reductions are two-stage with a
+    fixed order -- no floating-point atomics anywhere in the step."""
+    def run():
+        torch.manual_seed(3)
+        m = hpe.HeatmapPose(17, "resnet50", pretrained=False)
+        for n, mod in m.named_modules():
+            if isinstance(mod, torch.nn.BatchNorm2d):
+                mod.weight.data.uniform_(0.5, 1.5)
+                if n.endswith("bn3"):
+                    mod.weight.data.mul_(0.2)
+        m = m.to(cuda_dev).train()
+        step = hpe.TrainStep(m, lr=1e-2, momentum=0.9, weight_decay=1e-4, cuda_graph=False)
+        g = torch.Generator().manual_seed(4)
+        x = torch.rand(6, 3, 128, 96, generator=g).to(cuda_dev)
+        joints = (torch.rand(6, 17, 3, generator=g) * torch.tensor([96.0, 128.0, 1.0]) + torch.tensor([0.0, 0.0, 0.3])).to(cuda_dev)
+        losses = [step(x, joints).item() for _ in range(3)]
+        torch.cuda.synchronize()
+        return losses, step.flat_grad.clone(), step.flat_param.clone()
+    l1, g1, p1 = run()
+    l2, g2, p2 = run()
+    assert l1 == l2
+    assert torch.equal(g1, g2), f"gradients differ run to run: max {(g1 - g2).abs().max().item():.3g}"
+    assert torch.equal(p1, p2)
+    assert g1.abs().sum().item() > 0
