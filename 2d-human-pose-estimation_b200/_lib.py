@@ -59,6 +59,8 @@ SIGNATURES = {
     "hpe_bn_apply": (_i, [_vp, C.c_longlong, _i, _vp, _vp, _vp, _i, _vp, _vp]),
     "hpe_bn_scratch_elems": (_sz, [_i]),
     "hpe_bn_backward": (_i, [_vp, _vp, _vp, C.c_longlong, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "hpe_bn_apply_bits": (_i, [_vp, C.c_longlong, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp]),
+    "hpe_bn_backward_bits": (_i, [_vp, _vp, _vp, C.c_longlong, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "hpe_bn_backward_zmask": (_i, [_vp, _vp, _vp, C.c_longlong, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "hpe_maxpool3x3s2_train": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp]),
     "hpe_maxpool3x3s2_backward": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp]),

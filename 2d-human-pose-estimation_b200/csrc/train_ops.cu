@@ -4,6 +4,7 @@
 // All are plain vectorised (16-byte) grid-stride kernels: one pass over the tensor each, fp32 math.
 #include "hpe_common.cuh"
 #include <math.h>
+#include <cooperative_groups.h>
 
 namespace hpe {
 
@@ -28,7 +29,8 @@ __global__ void __launch_bounds__(256)
 bn_reduce_kernel(const __nv_bfloat16* __restrict__ z, const __nv_bfloat16* __restrict__ dy,
                  const __nv_bfloat16* __restrict__ y, const float* __restrict__ mean, const float* __restrict__ rstd,
                  int relu, long long M, int C, float* __restrict__ part,
-                 const float* __restrict__ msc = nullptr, const float* __restrict__ msh = nullptr) {
+                 const float* __restrict__ msc = nullptr, const float* __restrict__ msh = nullptr,
+                 const uint8_t* __restrict__ bits = nullptr) {
   __shared__ float red[256][17];
   const int cv = C >> 3, rpp = 256 / cv;
   const int vec = threadIdx.x % cv, r0 = threadIdx.x / cv;
@@ -36,7 +38,10 @@ bn_reduce_kernel(const __nv_bfloat16* __restrict__ z, const __nv_bfloat16* __res
 #pragma unroll
   for (int e = 0; e < 8; ++e) { a0[e] = 0.f; a1[e] = 0.f; mu[e] = 0.f; rs[e] = 1.f; }
   float ks[8], kh[8];
-  const bool zmask = MODE == 1 && relu && y == nullptr;
+  // ReLU mask source: `bits` (one byte per 16-byte vector, bit e = y[e] > 0, written by the forward's bn_apply: 1/16 of the
+  // bytes of y), else recomputed from z (units without a residual), else read from y
+  const bool bmask = MODE == 1 && relu && bits != nullptr;
+  const bool zmask = MODE == 1 && relu && !bmask && y == nullptr;
   if (MODE == 1) {
 #pragma unroll
     for (int e = 0; e < 8; ++e) { mu[e] = mean[vec * 8 + e]; rs[e] = rstd[vec * 8 + e]; }
@@ -48,6 +53,7 @@ bn_reduce_kernel(const __nv_bfloat16* __restrict__ z, const __nv_bfloat16* __res
     constexpr int U = MODE == 0 ? 8 : 4;
     for (long long row = static_cast<long long>(blockIdx.x) * rpp + r0; row < M; row += U * step) {
       uint4 vz[U], vd[U], vy[U];
+      uint32_t vb[U];
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const long long r = row + u * step;
@@ -56,7 +62,8 @@ bn_reduce_kernel(const __nv_bfloat16* __restrict__ z, const __nv_bfloat16* __res
           vz[u] = __ldg(reinterpret_cast<const uint4*>(z) + off);
           if (MODE == 1) {
             vd[u] = __ldg(reinterpret_cast<const uint4*>(dy) + off);
-            if (relu && !zmask) vy[u] = __ldg(reinterpret_cast<const uint4*>(y) + off);
+            if (bmask) vb[u] = __ldg(bits + off);
+            else if (relu && !zmask) vy[u] = __ldg(reinterpret_cast<const uint4*>(y) + off);
           }
         }
       }
@@ -69,7 +76,10 @@ bn_reduce_kernel(const __nv_bfloat16* __restrict__ z, const __nv_bfloat16* __res
             for (int e = 0; e < 8; ++e) { a0[e] += fz[e]; a1[e] = fmaf(fz[e], fz[e], a1[e]); }
           } else {
             float fd[8], fy[8]; unpack8(vd[u], fd);
-            if (relu && !zmask) unpack8(vy[u], fy);
+            if (bmask) {
+#pragma unroll
+              for (int e = 0; e < 8; ++e) fy[e] = ((vb[u] >> e) & 1u) ? 1.f : 0.f;
+            } else if (relu && !zmask) unpack8(vy[u], fy);
             if (zmask) {
 #pragma unroll
               for (int e = 0; e < 8; ++e) fy[e] = fmaf(fz[e], ks[e], kh[e]);
@@ -149,7 +159,8 @@ bn_collect_kernel(const float* __restrict__ part, int nparts, long long M, int C
 // 2 blocks/SM -> 49 KB in flight was slower although it read fewer bytes).  4 independent 16-byte loads per input per thread.
 __global__ void __launch_bounds__(256)
 bn_apply_kernel(const __nv_bfloat16* __restrict__ z, const float* __restrict__ scale, const float* __restrict__ shift,
-                const __nv_bfloat16* __restrict__ res, int relu, long long nvec, int cv, __nv_bfloat16* __restrict__ y) {
+                const __nv_bfloat16* __restrict__ res, int relu, long long nvec, int cv, __nv_bfloat16* __restrict__ y,
+                uint8_t* __restrict__ bits) {
   constexpr int U = 4;
   __shared__ __align__(16) float sk[2][2048];
   for (int c = threadIdx.x; c < cv * 8; c += 256) { sk[0][c] = __ldg(scale + c); sk[1][c] = __ldg(shift + c); }
@@ -183,6 +194,12 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ z, const float* __restrict__ s
 #pragma unroll
         for (int e = 0; e < 8; ++e) f[e] += r[e];
       }
+      if (bits) {                                  // ReLU mask of this vector for the backward pass (bit e = pre-activation > 0)
+        uint32_t m = 0;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) m |= (f[e] > 0.f ? 1u : 0u) << e;
+        bits[j] = static_cast<uint8_t>(m);
+      }
       if (relu) {
 #pragma unroll
         for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.f);
@@ -197,9 +214,10 @@ __global__ void __launch_bounds__(256)
 bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
                     const __nv_bfloat16* __restrict__ z, const float* __restrict__ coef, int C,
                     int relu, long long nvec, int cv, __nv_bfloat16* __restrict__ dz, __nv_bfloat16* __restrict__ g_out,
-                    const float* __restrict__ msc, const float* __restrict__ msh) {
+                    const float* __restrict__ msc, const float* __restrict__ msh, const uint8_t* __restrict__ bits) {
   constexpr int U = 2;
-  const bool zmask = relu && y == nullptr;      // ReLU mask recomputed from z (see bn_reduce_kernel)
+  const bool bmask = relu && bits != nullptr;   // ReLU mask from the forward's bit mask (see bn_reduce_kernel)
+  const bool zmask = relu && !bmask && y == nullptr;      // ... or recomputed from z
   __shared__ __align__(16) float sk[5][2048];   // A, Bz, C0, mask scale, mask shift
   for (int c = threadIdx.x; c < C; c += 256) {
     sk[0][c] = __ldg(coef + c); sk[1][c] = __ldg(coef + C + c); sk[2][c] = __ldg(coef + 2 * C + c);
@@ -211,14 +229,16 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
   const int c0 = static_cast<int>(threadIdx.x % cv) * 8;       // constant per thread: the stride is a multiple of cv
   for (long long i = tid; i < nvec; i += U * stride) {
     uint4 vd[U], vz[U], vy[U];
+    uint32_t vb[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const long long j = i + u * stride;
-      vy[u] = make_uint4(0, 0, 0, 0);
+      vy[u] = make_uint4(0, 0, 0, 0); vb[u] = 0;
       if (j < nvec) {
         vd[u] = __ldg(reinterpret_cast<const uint4*>(dy) + j);
         vz[u] = __ldg(reinterpret_cast<const uint4*>(z) + j);
-        if (relu && !zmask) vy[u] = __ldg(reinterpret_cast<const uint4*>(y) + j);
+        if (bmask) vb[u] = __ldg(bits + j);
+        else if (relu && !zmask) vy[u] = __ldg(reinterpret_cast<const uint4*>(y) + j);
       }
     }
 #pragma unroll
@@ -227,7 +247,10 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
       if (j >= nvec) break;
       float fd[8], fz[8], fy[8], o[8], k[8];
       unpack8(vd[u], fd); unpack8(vz[u], fz);
-      if (relu && !zmask) unpack8(vy[u], fy);
+      if (bmask) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) fy[e] = ((vb[u] >> e) & 1u) ? 1.f : 0.f;
+      } else if (relu && !zmask) unpack8(vy[u], fy);
       if (zmask) {
         float ks[8];
         *reinterpret_cast<float4*>(ks) = *reinterpret_cast<const float4*>(&sk[3][c0]);
@@ -370,23 +393,53 @@ hm_grad_nhwc_kernel(const void* __restrict__ dhm, int B, int K, int HW, __nv_bfl
 // tree), maps b = warp, warp + 8, ... added in order, the eight warps' sums added in order -> deterministic (round 1 used
 // shared + global fp32 atomics here, the last run-to-run varying reduction of the training step besides the wgrad split-K)
 template <bool BF16>
-__global__ void __launch_bounds__(256)
+__global__ void __cluster_dims__(8, 1, 1) __launch_bounds__(512)
 hm_dbias_kernel(const void* __restrict__ dhm, int B, int K, int HW, float* __restrict__ dbias) {
-  __shared__ float red[8];
-  const int k = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // one 8-CTA cluster per joint (8K CTAs ~ one per SM for K = 17): CTA r sums the maps b = r*16 + warp (mod 128), a warp per map
+  // with 16-byte loads; the cluster's eight totals are added by CTA 0 through distributed shared memory in rank order
+  __shared__ float red[16];
+  __shared__ float total;
+  cooperative_groups::cluster_group cl = cooperative_groups::this_cluster();
+  const unsigned r = cl.block_rank();
+  const int k = blockIdx.x >> 3, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr int EPV = BF16 ? 8 : 4;
+  const bool vec = HW % EPV == 0;
   float acc = 0.f;
-  for (int b = warp; b < B; b += 8) {
+  for (int b = static_cast<int>(r) * 16 + warp; b < B; b += 128) {
     const size_t off = (static_cast<size_t>(b) * K + k) * HW;
     float a = 0.f;
-    for (int i = lane; i < HW; i += 32)
-      a += BF16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(dhm)[off + i]) : reinterpret_cast<const float*>(dhm)[off + i];
+    if (vec) {
+      const uint4* src = reinterpret_cast<const uint4*>(BF16 ? static_cast<const void*>(reinterpret_cast<const __nv_bfloat16*>(dhm) + off)
+                                                             : static_cast<const void*>(reinterpret_cast<const float*>(dhm) + off));
+      const int nv = HW / EPV;
+      for (int i = lane; i < nv; i += 128) {
+        uint4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) v[u] = (i + u * 32 < nv) ? __ldg(src + i + u * 32) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          if (BF16) { float f[8]; unpack8(v[u], f); a += ((f[0] + f[1]) + (f[2] + f[3])) + ((f[4] + f[5]) + (f[6] + f[7])); }
+          else a += (__uint_as_float(v[u].x) + __uint_as_float(v[u].y)) + (__uint_as_float(v[u].z) + __uint_as_float(v[u].w));
+        }
+      }
+    } else {
+      for (int i = lane; i < HW; i += 32)
+        a += BF16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(dhm)[off + i]) : reinterpret_cast<const float*>(dhm)[off + i];
+    }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
     acc += a;
   }
   if (lane == 0) red[warp] = acc;
   __syncthreads();
-  if (threadIdx.x == 0) { float s = 0.f; for (int w = 0; w < 8; ++w) s += red[w]; dbias[k] = s; }
+  if (threadIdx.x == 0) { float s = 0.f; for (int w = 0; w < 16; ++w) s += red[w]; total = s; }
+  cl.sync();
+  if (r == 0 && threadIdx.x == 0) {
+    float s = 0.f;
+    for (unsigned j = 0; j < 8; ++j) s += *cl.map_shared_rank(&total, j);
+    dbias[k] = s;
+  }
+  cl.sync();                               // peers stay resident until CTA 0 has read their totals
 }
 
 // SGD with momentum (torch.optim.SGD, dampening 0, no nesterov):  g' = g*grad_scale + wd*p; m = mu*m + g'; p -= lr*m
@@ -494,16 +547,21 @@ extern "C" int hpe_bn_stats(const void* z, long long M, int C, const float* gamm
   return launch_status("bn_stats");
 }
 
-extern "C" int hpe_bn_apply(const void* z, long long M, int C, const float* scale, const float* shift, const void* residual,
-                            int relu, void* y, void* stream) {
+extern "C" int hpe_bn_apply_bits(const void* z, long long M, int C, const float* scale, const float* shift, const void* residual,
+                                 int relu, void* y, uint8_t* bits, void* stream) {
   int rc = bn_shape_ok(M, C, "hpe_bn_apply");
   if (rc) return rc;
   HPE_CHECK_ARG(z && scale && shift && y, "hpe_bn_apply: null pointer");
   const long long nvec = M * (C / 8);
   bn_apply_kernel<<<ew_grid(nvec), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)z, scale, shift,
                                                                   (const __nv_bfloat16*)residual, relu, nvec, C / 8,
-                                                                  (__nv_bfloat16*)y);
+                                                                  (__nv_bfloat16*)y, bits);
   return launch_status("bn_apply_kernel");
+}
+
+extern "C" int hpe_bn_apply(const void* z, long long M, int C, const float* scale, const float* shift, const void* residual,
+                            int relu, void* y, void* stream) {
+  return hpe_bn_apply_bits(z, M, C, scale, shift, residual, relu, y, nullptr, stream);
 }
 
 extern "C" int hpe_bn_backward(const void* dy, const void* y, const void* z, long long M, int C, const float* mean,
@@ -513,24 +571,37 @@ extern "C" int hpe_bn_backward(const void* dy, const void* y, const void* z, lon
   return hpe_bn_backward_zmask(dy, y, z, M, C, mean, rstd, gamma, relu, nullptr, nullptr, scratch, dbeta, dgamma, dz, g_out, stream);
 }
 
-extern "C" int hpe_bn_backward_zmask(const void* dy, const void* y, const void* z, long long M, int C, const float* mean,
-                                     const float* rstd, const float* gamma, int relu, const float* scale, const float* shift,
-                                     float* scratch, float* dbeta, float* dgamma, void* dz, void* g_out, void* stream) {
+static int bn_backward_impl(const void* dy, const void* y, const uint8_t* bits, const void* z, long long M, int C, const float* mean,
+                            const float* rstd, const float* gamma, int relu, const float* scale, const float* shift,
+                            float* scratch, float* dbeta, float* dgamma, void* dz, void* g_out, void* stream) {
   int rc = bn_shape_ok(M, C, "hpe_bn_backward");
   if (rc) return rc;
-  HPE_CHECK_ARG(dy && z && mean && rstd && gamma && scratch && dbeta && dgamma && dz && (y || !relu || (scale && shift)),
+  HPE_CHECK_ARG(dy && z && mean && rstd && gamma && scratch && dbeta && dgamma && dz && (y || bits || !relu || (scale && shift)),
                 "hpe_bn_backward: null pointer");
   cudaStream_t st = (cudaStream_t)stream;
   const int grid = reduce_grid(M, C);
   bn_reduce_kernel<1><<<grid, 256, 0, st>>>((const __nv_bfloat16*)z, (const __nv_bfloat16*)dy, (const __nv_bfloat16*)y, mean,
-                                            rstd, relu, M, C, scratch, scale, shift);
+                                            rstd, relu, M, C, scratch, scale, shift, bits);
   float* coef = scratch + (size_t)kBnMaxParts * 2 * C;
   bn_collect_kernel<1><<<(C + 31) / 32, 1024, 0, st>>>(scratch, grid, M, C, gamma, nullptr, 0.f, 0.f, nullptr, nullptr,
                                                        dbeta, dgamma, const_cast<float*>(mean), const_cast<float*>(rstd), coef);
   const long long nvec = M * (C / 8);
   bn_bwd_apply_kernel<<<ew_grid(nvec), 256, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)y, (const __nv_bfloat16*)z,
-                                                    coef, C, relu, nvec, C / 8, (__nv_bfloat16*)dz, (__nv_bfloat16*)g_out, scale, shift);
+                                                    coef, C, relu, nvec, C / 8, (__nv_bfloat16*)dz, (__nv_bfloat16*)g_out, scale, shift, bits);
   return launch_status("bn_backward");
+}
+
+extern "C" int hpe_bn_backward_zmask(const void* dy, const void* y, const void* z, long long M, int C, const float* mean,
+                                     const float* rstd, const float* gamma, int relu, const float* scale, const float* shift,
+                                     float* scratch, float* dbeta, float* dgamma, void* dz, void* g_out, void* stream) {
+  return bn_backward_impl(dy, y, nullptr, z, M, C, mean, rstd, gamma, relu, scale, shift, scratch, dbeta, dgamma, dz, g_out, stream);
+}
+
+extern "C" int hpe_bn_backward_bits(const void* dy, const uint8_t* bits, const void* z, long long M, int C, const float* mean,
+                                    const float* rstd, const float* gamma, float* scratch, float* dbeta, float* dgamma, void* dz,
+                                    void* g_out, void* stream) {
+  HPE_CHECK_ARG(bits, "hpe_bn_backward_bits: null mask");
+  return bn_backward_impl(dy, nullptr, bits, z, M, C, mean, rstd, gamma, 1, nullptr, nullptr, scratch, dbeta, dgamma, dz, g_out, stream);
 }
 
 extern "C" int hpe_maxpool3x3s2_train(const void* x, int B, int H, int W, int C, void* y, uint8_t* idx, void* stream) {
@@ -560,8 +631,8 @@ extern "C" int hpe_heatmap_grad_nhwc(const void* dhm, int dtype, int B, int K, i
   else                   hm_grad_nhwc_kernel<false><<<grid, 256, 0, st>>>(dhm, B, K, H * W, (__nv_bfloat16*)out);
   int rc = launch_status("hm_grad_nhwc_kernel");
   if (rc || !dbias) return rc;
-  if (dtype == HPE_BF16) hm_dbias_kernel<true><<<K, 256, 0, st>>>(dhm, B, K, H * W, dbias);
-  else                   hm_dbias_kernel<false><<<K, 256, 0, st>>>(dhm, B, K, H * W, dbias);
+  if (dtype == HPE_BF16) hm_dbias_kernel<true><<<K * 8, 512, 0, st>>>(dhm, B, K, H * W, dbias);
+  else                   hm_dbias_kernel<false><<<K * 8, 512, 0, st>>>(dhm, B, K, H * W, dbias);
   return launch_status("hm_dbias_kernel");
 }
 

@@ -44,11 +44,12 @@ def bn_stats(z, bn: nn.BatchNorm2d, u):
     _lib.check(rc, "hpe_bn_stats")
 
 
-def bn_apply(z, scale, shift, residual, relu, y):
+def bn_apply(z, scale, shift, residual, relu, y, bits=None):
+    """``bits`` (uint8 [M*C/8]): also write the ReLU mask, one byte per 8 channels, for ``bn_backward(..., bits=)``."""
     M, Cc = z.numel() // z.shape[-1], z.shape[-1]
     with torch.cuda.device(z.device):
-        rc = _lib.lib().hpe_bn_apply(_lib.ptr(z), M, Cc, _lib.ptr(scale), _lib.ptr(shift), _lib.ptr(residual), int(relu),
-                                     _lib.ptr(y), _lib.stream_ptr())
+        rc = _lib.lib().hpe_bn_apply_bits(_lib.ptr(z), M, Cc, _lib.ptr(scale), _lib.ptr(shift), _lib.ptr(residual), int(relu),
+                                          _lib.ptr(y), _lib.ptr(bits), _lib.stream_ptr())
     _lib.check(rc, "hpe_bn_apply")
 
 
@@ -65,10 +66,17 @@ def bn_scratch(device):
     return _bn_scratch[key]
 
 
-def bn_backward(dy, y, z, mean, rstd, gamma, relu, dbeta, dgamma, dz, g_out=None, scale=None, shift=None):
+def bn_backward(dy, y, z, mean, rstd, gamma, relu, dbeta, dgamma, dz, g_out=None, scale=None, shift=None, bits=None):
     """``y=None`` with ``relu`` and the forward's ``scale``/``shift``: the ReLU mask is recomputed from z (units without a
-    residual), so y is not read."""
+    residual), so y is not read.  ``bits``: the mask ``bn_apply`` wrote (units with a residual), read instead of y."""
     M, Cc = z.numel() // z.shape[-1], z.shape[-1]
+    if bits is not None:
+        with torch.cuda.device(z.device):
+            rc = _lib.lib().hpe_bn_backward_bits(_lib.ptr(dy), _lib.ptr(bits), _lib.ptr(z), M, Cc, _lib.ptr(mean), _lib.ptr(rstd),
+                                                 _lib.ptr(gamma), _lib.ptr(bn_scratch(z.device)), _lib.ptr(dbeta), _lib.ptr(dgamma),
+                                                 _lib.ptr(dz), _lib.ptr(g_out), _lib.stream_ptr())
+        _lib.check(rc, "hpe_bn_backward_bits")
+        return
     with torch.cuda.device(z.device):
         rc = _lib.lib().hpe_bn_backward_zmask(_lib.ptr(dy), _lib.ptr(y), _lib.ptr(z), M, Cc, _lib.ptr(mean), _lib.ptr(rstd),
                                               _lib.ptr(gamma), int(relu), _lib.ptr(scale), _lib.ptr(shift),
@@ -132,6 +140,9 @@ def adamw_step(param, grad, exp_avg, exp_avg_sq, step, lr, betas=(0.9, 0.999), e
     _lib.check(rc, "hpe_adamw_step")
 
 
+_BN_BITS = os.environ.get("HPE_B200_BN_BITS", "1") != "0"
+
+
 # ---- one conv + BatchNorm (+ReLU) (+residual) unit in training mode ------------------------------------------------
 class _Unit:
     def __init__(self, conv_name, bn_name, kind, B, H, W, Cin, Cout, stride, relu, dev, dgrad=True, dgrad_acc=False):
@@ -144,6 +155,7 @@ class _Unit:
         self.y = torch.empty(shape, dtype=torch.bfloat16, device=dev)
         f = lambda n: torch.empty(n, dtype=torch.float32, device=dev)  # noqa: E731
         self.scale, self.shift, self.mean, self.rstd = f(Cout), f(Cout), f(Cout), f(Cout)
+        self.bits = None         # ReLU mask of a residual unit (allocated on first use)
         self.x = None            # forward input (set by forward)
         self.bn = None           # nn.BatchNorm2d (set by load)
         self.in_shape = (B, H, W, Cin)
@@ -159,7 +171,9 @@ class _Unit:
         self.has_res = residual is not None
         self.fwd(x, None, self.z)
         bn_stats(self.z, self.bn, self)
-        bn_apply(self.z, self.scale, self.shift, residual, self.relu, self.y)
+        if self.has_res and self.relu and self.bits is None and _BN_BITS:   # residual units: keep the ReLU mask, 1 bit per element
+            self.bits = torch.empty(self.z.numel() // 8, dtype=torch.uint8, device=self.z.device)
+        bn_apply(self.z, self.scale, self.shift, residual, self.relu, self.y, self.bits if self.has_res else None)
         return self.y
 
     def backward(self, dy, grads, dz, g_out=None, dx_out=None, dx_res=None):
@@ -167,9 +181,10 @@ class _Unit:
         returns dx (or None when the unit has no dgrad)."""
         dzv = dz.narrow(0, 0, self.z.numel()).view(self.z.shape)
         zmask = self.relu and not getattr(self, "has_res", True)      # y = relu(z*scale + shift): mask recomputed from z
-        bn_backward(dy, self.y if (self.relu and not zmask) else None, self.z, self.mean, self.rstd, self.bn.weight, self.relu,
-                    grads[self.bn_name + ".bias"], grads[self.bn_name + ".weight"], dzv, g_out,
-                    self.scale if zmask else None, self.shift if zmask else None)
+        bits = self.bits if (self.relu and not zmask) else None       # residual unit: the mask bn_apply wrote
+        bn_backward(dy, self.y if (self.relu and not zmask and bits is None) else None, self.z, self.mean, self.rstd,
+                    self.bn.weight, self.relu, grads[self.bn_name + ".bias"], grads[self.bn_name + ".weight"], dzv, g_out,
+                    self.scale if zmask else None, self.shift if zmask else None, bits)
         self.wg(self.x, dzv, grads[self.conv_name + ".weight"])
         if self.dg is None:
             return None

@@ -247,6 +247,13 @@ int hpe_bn_backward(const void* dy, const void* y, const void* z, long long M, i
 int hpe_bn_backward_zmask(const void* dy, const void* y, const void* z, long long M, int C, const float* mean,
                           const float* rstd, const float* gamma, int relu, const float* scale, const float* shift,
                           float* scratch, float* dbeta, float* dgamma, void* dz, void* g_out, void* stream);
+/* ReLU units WITH a residual: the forward writes one mask byte per 8 channels (bit e = pre-activation of channel 8j+e > 0,
+ * bits[M*C/8]) next to y; the backward reads the mask instead of y (1/16 of the bytes). */
+int hpe_bn_apply_bits(const void* z, long long M, int C, const float* scale, const float* shift, const void* residual,
+                      int relu, void* y, uint8_t* bits, void* stream);
+int hpe_bn_backward_bits(const void* dy, const uint8_t* bits, const void* z, long long M, int C, const float* mean,
+                         const float* rstd, const float* gamma, float* scratch, float* dbeta, float* dgamma, void* dz,
+                         void* g_out, void* stream);
 /* MaxPool 3x3 s2 p1 that records the winning window position (first max, torch semantics) and its backward. */
 int hpe_maxpool3x3s2_train(const void* x, int B, int H, int W, int C, void* y, uint8_t* idx, void* stream);
 int hpe_maxpool3x3s2_backward(const void* dy, const uint8_t* idx, int B, int H, int W, int C, void* dx, void* stream);

@@ -89,6 +89,19 @@ def test_batchnorm_train_fwd_bwd(hpe, cuda_dev, B, H, W, C, relu, res):
     if res:
         bad = ((nchw(gout) - rr.grad).abs() > rr.grad.abs() * 2 ** -7 + 1e-6) & clear
         assert bad.float().mean() < 1e-3
+    if relu and res:
+        # residual unit: bn_apply also writes the ReLU mask (1 bit per element); the backward that reads the mask instead of y
+        # gives identical results wherever bf16(y) > 0 <=> pre-activation > 0 (i.e. everywhere but fp32 denormals)
+        y2 = torch.empty_like(zd); bits = torch.zeros(zd.numel() // 8, dtype=torch.uint8, device="cuda")
+        tr.bn_apply(zd, u.scale, u.shift, nhwc16(rs), relu, y2, bits)
+        torch.cuda.synchronize()
+        assert torch.equal(y2, y)
+        want = ((y.reshape(-1, 8) > 0).to(torch.int32) << torch.arange(8, device="cuda", dtype=torch.int32)).sum(1).to(torch.uint8)
+        assert torch.equal(bits, want)
+        dz2 = torch.empty_like(zd); g2 = torch.empty_like(zd); dbeta2, dgamma2 = f(C), f(C)
+        tr.bn_backward(nhwc16(dy), None, zd, u.mean, u.rstd, bn.weight, relu, dbeta2, dgamma2, dz2, g2, bits=bits)
+        torch.cuda.synchronize()
+        assert torch.equal(dz2, dz) and torch.equal(g2, gout) and torch.equal(dbeta2, dbeta) and torch.equal(dgamma2, dgamma)
     if relu and not res:
         # mask recomputed from z (y never read): identical results to the y-mask path
         dz2 = torch.empty_like(zd); dbeta2, dgamma2 = f(C), f(C)
@@ -129,6 +142,15 @@ def test_heatmap_grad_and_sgd(hpe, cuda_dev):
     assert torch.equal(out[..., :K].float().cpu(), r16(dhm).permute(0, 2, 3, 1))
     assert (out[..., K:] == 0).all()
     assert torch.allclose(db.cpu(), dhm.sum((0, 2, 3)), rtol=1e-4, atol=1e-4)
+    # dbias over more maps than one pass of the 8-CTA cluster (128), vector and scalar row lengths, fp32 and bf16, twice (bit-stable)
+    for (B2, H2, W2, dt) in ((131, 16, 12, torch.float32), (131, 16, 12, torch.bfloat16), (9, 5, 3, torch.float32), (9, 5, 3, torch.bfloat16)):
+        d2 = torch.randn(B2, K, H2, W2, generator=g).to(dt).cuda()
+        o2 = torch.empty(B2, H2, W2, 64, dtype=torch.bfloat16, device="cuda")
+        da, dbb = torch.empty(K, device="cuda"), torch.empty(K, device="cuda")
+        tr.heatmap_grad_nhwc(d2, o2, da); tr.heatmap_grad_nhwc(d2, o2, dbb)
+        torch.cuda.synchronize()
+        assert torch.equal(da, dbb)
+        assert torch.allclose(da.cpu(), d2.double().sum((0, 2, 3)).float().cpu(), rtol=1e-4, atol=2e-3)
     n = 100003
     p = torch.randn(n, generator=g); gr = torch.randn(n, generator=g); m = torch.randn(n, generator=g)
     pr = p.clone().requires_grad_(True); pr.grad = gr.clone() * 0.5
