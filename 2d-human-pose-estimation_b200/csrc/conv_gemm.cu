@@ -38,7 +38,8 @@ namespace hpe {
 using namespace ptx;
 
 constexpr int kConvThreads   = 352;                   // 3 control warps + 8 epilogue warps
-constexpr int kEpiThreads    = 256;
+constexpr int kConvThreads2  = 608;                   // EPI2: 3 control warps + two groups of 8 epilogue warps
+constexpr int kEpiThreads    = 256;                   // epilogue threads of ONE group
 constexpr int kEpiWarp0      = 3;
 constexpr int kMaxCout       = 2048;
 constexpr int kMaxBlockN     = 256;                   // scale/shift of ONE N tile staged in shared memory
@@ -62,9 +63,6 @@ struct ConvParams {
   float* hm_out;                // HPE_CONV_FINAL / fused head: fp32 NCHW heatmaps
   int head2_k;                  // fused head (HEAD2): number of joints K <= 32 of the second GEMM
   const float* bias2;           // fused head: conv bias [K]
-  // DIRECT epilogue: plain coalesced stores into y [B][out_up*Ho][out_up*Wo][out_pitch] (out_up = 2 for the parity-class kinds)
-  __nv_bfloat16* y_out;
-  int out_pitch, out_up;
 };
 
 struct TileCoord { int n_tile, cls, x0, y0, b0; };
@@ -103,7 +101,8 @@ __device__ __forceinline__ int kb_count(const ConvParams& p, int cls) {
 
 // NSB = epilogue staging buffers (16 KB each): 4 with a residual (they double as its prefetch ring), else 3 -- the bytes
 // saved go to a deeper operand ring, which is what bounds the deep-K layers (ring depth / hand-off round trip).
-template <int BLOCK_N, int STAGES, bool PAIR = false, int NSB = 4, bool HEAD2 = false, bool DIRECT = false>
+// EPI2 (two epilogue groups): NSB counts the buffers of BOTH groups and each group has its own scale/shift table.
+template <int BLOCK_N, int STAGES, bool PAIR = false, int NSB = 4, bool HEAD2 = false, bool EPI2 = false>
 struct SmemLayout {
   static constexpr int kW2Bytes    = HEAD2 ? 4 * 16 * 128 : 0;       // fused head: this CTA's 16 rows x 256 K of the joint weights
   static constexpr int kBBytes     = (PAIR ? BLOCK_N / 2 : BLOCK_N) * kKBlock * 2;    // a CTA of a pair holds half of B's rows
@@ -111,8 +110,8 @@ struct SmemLayout {
   static constexpr int kOffA   = 0;
   static constexpr int kOffB   = STAGES * kABytes;
   static constexpr int kOffSB  = kOffB + STAGES * kBBytes;
-  static constexpr int kOffSS  = kOffSB + NSB * kSBBytes;             // float scale[kMaxBlockN], shift[kMaxBlockN]
-  static constexpr int kOffW2  = kOffSS + (DIRECT ? 4 : 2) * kMaxBlockN * 4;   // the DIRECT epilogue double-buffers the table; 1024-byte aligned
+  static constexpr int kOffSS  = kOffSB + NSB * kSBBytes;             // float scale[kMaxBlockN], shift[kMaxBlockN] (x 2 groups with EPI2)
+  static constexpr int kOffW2  = kOffSS + (EPI2 ? 4 : 2) * kMaxBlockN * 4;     // 1024-byte aligned
   static constexpr int kOffBar = kOffW2 + kW2Bytes;
   static constexpr int kNumBar = 2 * STAGES + 4 + 2 * NSB + 3;       // + w2full, s2full, d2full (fused head)
   static constexpr int kTotal  = kOffBar + kNumBar * 8 + 16;
@@ -183,25 +182,28 @@ __device__ __forceinline__ float silu_fast(float x) {
 // exactly the SWIZZLE_128B K-major A operand of a second GEMM against the K-joint 1x1 weights (16 rows per CTA, resident in
 // smem), accumulated into the first 32 columns of the accumulator just drained, and written as fp32 NCHW heatmaps: deconv3 +
 // final_layer of the App. A.1 head in one kernel (saves writing and re-reading the 403 MB deconv3 output at B=256).
-// DIRECT: decoupled epilogue -- every epilogue warp stages its own 32 rows x 32 columns and writes them with plain coalesced
-// 16-byte stores: no 256-thread barrier, proxy fence, TMA store or bulk-group wait per 64-column chunk (in-kernel profile of the
-// lock-step TMA-store epilogue: 8.2 k cycles per residual tile against 2 k of MMA, the schedulers 26 % busy because all eight
-// warps waited at the same points).  The residual ring is released by an 8-arrival mbarrier.
-template <int BLOCK_N, int STAGES, int ACT, bool RES, bool FINAL, bool PAIR = false, bool HEAD2 = false, bool DIRECT = false>
-__global__ void __launch_bounds__(kConvThreads, 1)
+// EPI2: TWO independent epilogue groups of 8 warps (608 threads).  Group g drains accumulator g (the tiles with it & 1 == g) through
+// its own staging buffers, residual ring, scale/shift table, named barrier and TMA-store stream, so the tcgen05.ld -> residual
+// wait -> math -> fence -> barrier -> store chains of consecutive tiles overlap (in-kernel profile of the single lock-step group on
+// the residual 1x1 layers: 8.2 k cycles per tile against 2 k of MMA with the schedulers 26 % busy -- every warp waited at the same
+// points).  The group leader waits for ALL of its bulk stores to have left shared memory at the top of a chunk (wait_group.read 0),
+// which makes 3 buffers per group enough for a residual lead of 2 chunks (2 buffers without a residual).
+template <int BLOCK_N, int STAGES, int ACT, bool RES, bool FINAL, bool PAIR = false, bool HEAD2 = false, bool EPI2 = false>
+__global__ void __launch_bounds__(EPI2 ? kConvThreads2 : kConvThreads, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
                  const __grid_constant__ CUtensorMap tmW, const __grid_constant__ OutMaps tmOut,
                  const __grid_constant__ CUtensorMap tmRes, const ConvParams p) {
   // staging buffer q % kNumSB is rewritten by chunk q; the leader confirms "stores <= j-2 have left smem" at the start of
   // chunk j and everyone meets at chunk j's named barrier, so at the start of chunk q only stores <= q-3 are known done:
   // 3 buffers is the minimum.  With a residual the buffers double as its prefetch ring (4, lead 2).
+  // EPI2 (leader waits for stores <= j-1): a non-leader thread at chunk q knows stores <= q-2 are done -> 2 buffers; with a
+  // residual the buffer of chunk q-1 is handed to the producer at the top of chunk q -> 3 buffers give a lead of 2.
   static_assert(!HEAD2 || (PAIR && BLOCK_N == 256 && !RES && !FINAL), "fused head: pair kernel, 256 channels, no residual");
-  static_assert(!DIRECT || (!FINAL && !HEAD2), "the direct-store epilogue replaces the bf16 NHWC TMA-store path only");
-  // DIRECT without a residual: one 16 KB region holds the eight warps' private 2 KB staging tiles
-  // DIRECT with a residual: 3 chunk buffers (a buffer is free again as soon as the eight warps have read it back)
-  constexpr int kNumSB = FINAL ? 0 : (DIRECT ? (RES ? 3 : 1) : ((RES || HEAD2) ? 4 : 3));      // the fp32 heatmap epilogue stores from registers: all smem to the ring
+  static_assert(!EPI2 || (!FINAL && !HEAD2), "two epilogue groups: bf16 NHWC TMA-store path only");
+  constexpr int kGroups = EPI2 ? 2 : 1;
+  constexpr int kNumSB = FINAL ? 0 : (EPI2 ? (RES ? 3 : 2) : ((RES || HEAD2) ? 4 : 3));      // per group; the fp32 heatmap epilogue stores from registers: all smem to the ring
   constexpr int kResLead = 2;                   // the residual of chunk q + 2 is requested while chunk q is processed
-  using L = SmemLayout<BLOCK_N, STAGES, PAIR, kNumSB, HEAD2, DIRECT>;
+  using L = SmemLayout<BLOCK_N, STAGES, PAIR, kGroups * kNumSB, HEAD2, EPI2>;
   static_assert(!PAIR || (BLOCK_N % 32 == 0 && !FINAL), "pair kernels: N multiple of 32, bf16 NHWC epilogue");
   constexpr int kChunks   = BLOCK_N >= 64 ? BLOCK_N / 64 : 1;
   constexpr int kTmemCols = 2 * BLOCK_N <= 32 ? 32 : (2 * BLOCK_N <= 64 ? 64 : (2 * BLOCK_N <= 128 ? 128 : (2 * BLOCK_N <= 256 ? 256 : 512)));  // power of two
@@ -224,8 +226,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint64_t* tfull_bar  = bars + 2 * STAGES;
   uint64_t* tempty_bar = bars + 2 * STAGES + 2;
   uint64_t* sbfull_bar = bars + 2 * STAGES + 4;
-  uint64_t* sbempty_bar = bars + 2 * STAGES + 4 + kNumSB;
-  uint64_t* w2full_bar = bars + 2 * STAGES + 4 + 2 * kNumSB;       // fused head: joint weights landed (own CTA)
+  uint64_t* sbempty_bar = bars + 2 * STAGES + 4 + kGroups * kNumSB;
+  uint64_t* w2full_bar = bars + 2 * STAGES + 4 + 2 * kGroups * kNumSB;       // fused head: joint weights landed (own CTA)
   uint64_t* s2full_bar = w2full_bar + 1;                           // fused head: both CTAs staged their A' tile (leader's barrier)
   uint64_t* d2full_bar = w2full_bar + 2;                           // fused head: second GEMM done (multicast commit)
   uint8_t*  sW2 = smem + L::kOffW2;
@@ -241,7 +243,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // PAIR: the leader's full barrier collects both producers' arrivals, its tempty both CTAs' epilogue warps
     for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], PAIR ? 2 : 1); mbar_init(&empty_bar[s], 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], (PAIR ? 2 : 1) * kEpiThreads / 32); }
-    for (int b = 0; b < kNumSB; ++b) { mbar_init(&sbfull_bar[b], 1); mbar_init(&sbempty_bar[b], DIRECT ? kEpiThreads / 32 : 1); }
+    for (int b = 0; b < kGroups * kNumSB; ++b) { mbar_init(&sbfull_bar[b], 1); mbar_init(&sbempty_bar[b], 1); }
     mbar_init(w2full_bar, 1); mbar_init(s2full_bar, 2); mbar_init(d2full_bar, 1);
     fence_mbar_init();
   }
@@ -334,57 +336,67 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       for (int kb = 0; kb < 4; ++kb) tma_load_2d(sW2 + kb * 2048, &tmRes, w2full_bar, kb * kKBlock, rank * 16);
     }
     if (RES && lane == 0) {
-      int r = 0;
-      for (int work = work0; work < p.num_tiles; work += wstep) {
-        const TileCoord t = tile_coord(p, work_tile<PAIR>(p, work, rank));
-        for (int c = 0; c < kChunks; ++c, ++r) {
-          const int b = r % kNumSB;
-          // DIRECT: a buffer is free once the eight epilogue warps have read it back (fresh barrier: parity 1 passes at once);
-          // TMA-store path: the epilogue leader hands buffers over with a lead of kResLead chunks
-          mbar_wait(&sbempty_bar[b], DIRECT ? (((r / kNumSB) & 1) ^ 1) : ((r / kNumSB) & 1));
-          mbar_arrive_expect_tx(&sbfull_bar[b], kSBBytes);
-          tma_load_4d(sSB + b * kSBBytes, &tmRes, &sbfull_bar[b], t.n_tile * BLOCK_N + c * 64, t.x0, t.y0, t.b0);
+      if constexpr (EPI2) {
+        // two rings (one per epilogue group, tiles it & 1 == g): one thread serves both, polling so that neither ring waits
+        // behind the other's full buffers
+        int wk[2] = {work0, work0 + wstep}, ch[2] = {0, 0}, rr[2] = {0, 0};
+        TileCoord tg[2];
+#pragma unroll
+        for (int g = 0; g < 2; ++g) if (wk[g] < p.num_tiles) tg[g] = tile_coord(p, work_tile<PAIR>(p, wk[g], rank));
+        while (wk[0] < p.num_tiles || wk[1] < p.num_tiles) {
+#pragma unroll
+          for (int g = 0; g < 2; ++g) {
+            if (wk[g] >= p.num_tiles) continue;
+            const int b = g * kNumSB + rr[g] % kNumSB;
+            if (!mbar_test_wait(&sbempty_bar[b], (rr[g] / kNumSB) & 1)) continue;
+            mbar_arrive_expect_tx(&sbfull_bar[b], kSBBytes);
+            tma_load_4d(sSB + b * kSBBytes, &tmRes, &sbfull_bar[b], tg[g].n_tile * BLOCK_N + ch[g] * 64, tg[g].x0, tg[g].y0, tg[g].b0);
+            ++rr[g];
+            if (++ch[g] == kChunks) {
+              ch[g] = 0; wk[g] += 2 * wstep;
+              if (wk[g] < p.num_tiles) tg[g] = tile_coord(p, work_tile<PAIR>(p, wk[g], rank));
+            }
+          }
+        }
+      } else {
+        int r = 0;
+        for (int work = work0; work < p.num_tiles; work += wstep) {
+          const TileCoord t = tile_coord(p, work_tile<PAIR>(p, work, rank));
+          for (int c = 0; c < kChunks; ++c, ++r) {
+            const int b = r % kNumSB;
+            mbar_wait(&sbempty_bar[b], (r / kNumSB) & 1);   // the epilogue leader hands buffers over with a lead of kResLead chunks
+            mbar_arrive_expect_tx(&sbfull_bar[b], kSBBytes);
+            tma_load_4d(sSB + b * kSBBytes, &tmRes, &sbfull_bar[b], t.n_tile * BLOCK_N + c * 64, t.x0, t.y0, t.b0);
+          }
         }
       }
     }
   } else {
-    // ===================== epilogue (8 warps: TMEM lane quarter = warp & 3, column half = (warp - 3) >> 2) ====
+    // ===================== epilogue (8 warps per group: TMEM lane quarter = warp & 3, column half = ((warp - 3) >> 2) & 1) ====
+    const int grp = EPI2 ? (warp - kEpiWarp0) >> 3 : 0;          // EPI2: group g drains accumulator g (tiles it & 1 == g)
     const int ew = warp & 3;                      // TMEM lane quarter this warp may access
-    const int half = (warp - kEpiWarp0) >> 2;     // which 32 of the chunk's 64 columns
+    const int half = ((warp - kEpiWarp0) >> 2) & 1;     // which 32 of the chunk's 64 columns
     const int row = ew * 32 + lane;               // tile row = TMEM lane = pixel inside the brick
-    const bool leader = threadIdx.x == kEpiWarp0 * 32;
-    if (RES && !DIRECT && leader) for (int b = 0; b < kResLead; ++b) mbar_arrive(&sbempty_bar[b]);
-    const int etid = threadIdx.x - kEpiWarp0 * 32;
-    int q = 0, it = 0, staged_n = -1;
-    float* const sTab0 = sScale; int tab_par = 1;
-    // DIRECT store mapping: lane -> (pixel slot ps = lane & 7, 16-byte unit u4 = lane >> 3 of the warp's 64-byte column group);
-    // the lane stores pixels ps + 8 i (i < 4) of the warp's 32 rows.  A quarter-warp then reads 8 different rows of the staging
-    // tile at the same logical unit: conflict-free under the 128-byte swizzle (RES) and under the private tile's own XOR.
-    const int ps = lane & 7, u4 = lane >> 3;
-    int dxi[4], dyi[4], dbi[4];
-    if constexpr (DIRECT) {
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int r = ew * 32 + ps + 8 * i;
-        dxi[i] = r % p.tw; dyi[i] = (r / p.tw) % p.th; dbi[i] = r / (p.tw * p.th);
-      }
-    }
-    const uint32_t wstg = smem_u32(sSB) + (warp - kEpiWarp0) * 2048;      // DIRECT without a residual: this warp's 32 x 64 B tile
-    for (int work = work0; work < p.num_tiles; work += wstep, ++it) {
+    const int etid = threadIdx.x - kEpiWarp0 * 32 - grp * kEpiThreads;
+    const bool leader = etid == 0;
+    // per-group resources
+    sSB += grp * kNumSB * kSBBytes; sbfull_bar += grp * kNumSB; sbempty_bar += grp * kNumSB;
+    sScale += grp * 2 * kMaxBlockN; sShift += grp * 2 * kMaxBlockN;
+    const uint32_t bar_id = 1 + grp;
+    if (RES && leader) for (int b = 0; b < kResLead; ++b) mbar_arrive(&sbempty_bar[b]);
+    int q = 0, staged_n = -1;
+    for (int work = work0 + grp * wstep, it = grp; work < p.num_tiles; work += kGroups * wstep, it += kGroups) {
       const TileCoord t = tile_coord(p, work_tile<PAIR>(p, work, rank));
       const int acc = it & 1;
       if (t.n_tile != staged_n) {
-        // this N tile's folded-BN scale/shift -> smem (channels past Cout: 0).  Every thread finished reading the previous
-        // tile's values before the named barrier of its last chunk, so the table is free to overwrite here.  DIRECT (no
-        // per-chunk barrier): the tables alternate, and a warp that writes table `par` has passed the barrier that followed the
-        // staging of table `par ^ 1`, which every warp reached only after its last read of the old table `par`.
-        if constexpr (DIRECT) { tab_par ^= 1; sScale = sTab0 + tab_par * 2 * kMaxBlockN; sShift = sScale + kMaxBlockN; }
+        // this N tile's folded-BN scale/shift -> smem (channels past Cout: 0).  Every thread of the group finished reading the
+        // previous tile's values before the named barrier of its last chunk, so the table is free to overwrite here.
         if (etid < BLOCK_N) {
           const int n = t.n_tile * BLOCK_N + etid;
           sScale[etid] = n < p.Cout ? __ldg(p.scale + n) : 0.f; sShift[etid] = n < p.Cout ? __ldg(p.shift + n) : 0.f;
         }
         staged_n = t.n_tile;
-        named_bar_sync(1, kEpiThreads);
+        named_bar_sync(bar_id, kEpiThreads);
       }
       mbar_wait(&tfull_bar[acc], (it >> 1) & 1);
       tc_fence_after();
@@ -416,90 +428,12 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tempty_bar[acc]);
-      } else if constexpr (DIRECT) {
-        // ---- decoupled epilogue: no cross-warp synchronisation per chunk ----
-        const int up = p.out_up, cy = up == 2 ? (t.cls >> 1) : 0, cx = up == 2 ? (t.cls & 1) : 0;
-        __nv_bfloat16* dst[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int x = t.x0 + dxi[i], y = t.y0 + dyi[i], b = t.b0 + dbi[i];
-          const bool ok = x < p.Wo && y < p.Ho && b < p.B;
-          const size_t pix = (static_cast<size_t>(b) * (up * p.Ho) + (up * y + cy)) * (up * p.Wo) + (up * x + cx);
-          dst[i] = ok ? p.y_out + pix * p.out_pitch + t.n_tile * BLOCK_N + u4 * 8 : nullptr;
-        }
-        for (int c = 0; c < kChunks; ++c, ++q) {
-          const int sb = RES ? q % kNumSB : 0;
-          uint32_t v[32];
-          tmem_ld_x32(taddr + c * 64 + half * 32, v);
-          if (RES) mbar_wait(&sbfull_bar[sb], (q / kNumSB) & 1);
-          tmem_ld_wait();
-          if (c == kChunks - 1) {                                   // accumulator drained -> MMA may reuse it
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) {
-              if constexpr (PAIR) mbar_arrive_cluster(mapa_shared(smem_u32(&tempty_bar[acc]), 0));   // the leader's barrier
-              else                mbar_arrive(&tempty_bar[acc]);
-            }
-          }
-          const int n0 = c * 64 + half * 32;                        // first tile-local channel of this warp's 32 columns
-          const uint32_t ss = smem_u32(sScale + n0), sh = smem_u32(sShift + n0);
-          // RES: in place in the residual chunk buffer (128-byte rows, TMA's 128-byte swizzle); else the warp's private tile
-          // (64-byte rows, unit XOR (row >> 1) & 3: conflict-free for both the row-wise writes and the 8-row read-back)
-          const uint32_t rowp = RES ? smem_u32(sSB + sb * kSBBytes) + row * 128 : wstg + lane * 64;
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const float4 s0 = lds_f4(ss + j * 32), s1 = lds_f4(ss + j * 32 + 16);
-            const float4 h0 = lds_f4(sh + j * 32), h1 = lds_f4(sh + j * 32 + 16);
-            float2 o01 = __ffma2_rn(make_float2(__uint_as_float(v[j * 8 + 0]), __uint_as_float(v[j * 8 + 1])), make_float2(s0.x, s0.y), make_float2(h0.x, h0.y));
-            float2 o23 = __ffma2_rn(make_float2(__uint_as_float(v[j * 8 + 2]), __uint_as_float(v[j * 8 + 3])), make_float2(s0.z, s0.w), make_float2(h0.z, h0.w));
-            float2 o45 = __ffma2_rn(make_float2(__uint_as_float(v[j * 8 + 4]), __uint_as_float(v[j * 8 + 5])), make_float2(s1.x, s1.y), make_float2(h1.x, h1.y));
-            float2 o67 = __ffma2_rn(make_float2(__uint_as_float(v[j * 8 + 6]), __uint_as_float(v[j * 8 + 7])), make_float2(s1.z, s1.w), make_float2(h1.z, h1.w));
-            const uint32_t slot = RES ? rowp + (((half * 4 + j) ^ (row & 7)) << 4) : rowp + ((j ^ ((lane >> 1) & 3)) << 4);
-            if (RES) {
-              const uint4 rr = lds_v4(slot);
-              o01 = __fadd2_rn(o01, make_float2(bf16_lo(rr.x), bf16_hi(rr.x))); o23 = __fadd2_rn(o23, make_float2(bf16_lo(rr.y), bf16_hi(rr.y)));
-              o45 = __fadd2_rn(o45, make_float2(bf16_lo(rr.z), bf16_hi(rr.z))); o67 = __fadd2_rn(o67, make_float2(bf16_lo(rr.w), bf16_hi(rr.w)));
-            }
-            float o[8] = {o01.x, o01.y, o23.x, o23.y, o45.x, o45.y, o67.x, o67.y};
-            if (ACT == HPE_ACT_SILU) {
-#pragma unroll
-              for (int e = 0; e < 8; ++e) o[e] = silu_fast(o[e]);
-            }
-            if (ACT == HPE_ACT_GELU) {
-#pragma unroll
-              for (int e = 0; e < 8; ++e) o[e] = gelu_erf(o[e]);
-            }
-            uint4 pk = make_uint4(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]), pack_bf16(o[6], o[7]));
-            if (ACT == HPE_ACT_RELU) {
-              pk.x = relu_bf16x2(pk.x); pk.y = relu_bf16x2(pk.y); pk.z = relu_bf16x2(pk.z); pk.w = relu_bf16x2(pk.w);
-            }
-            sts_v4(slot, pk);
-          }
-          __syncwarp();                                             // the warp's 32 rows are staged
-          uint4 ov[4];
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const int r = ps + 8 * i;                               // row inside the warp's 32
-            ov[i] = RES ? lds_v4(smem_u32(sSB + sb * kSBBytes) + (ew * 32 + r) * 128 + (((half * 4 + u4) ^ (r & 7)) << 4))
-                        : lds_v4(wstg + r * 64 + ((u4 ^ ((r >> 1) & 3)) << 4));
-          }
-          __syncwarp();                                             // read back before the next chunk's writes / the buffer's release
-          if (RES) {
-            // generic-proxy accesses of the buffer are ordered before the TMA (async proxy) write that refills it
-            fence_proxy_async_smem();
-            if (lane == 0) mbar_arrive(&sbempty_bar[sb]);
-          }
-          const bool ch_ok = t.n_tile * BLOCK_N + n0 + u4 * 8 < p.Cout;      // channel clipping (Cout is a multiple of 8)
-#pragma unroll
-          for (int i = 0; i < 4; ++i)
-            if (dst[i] != nullptr && ch_ok) *reinterpret_cast<uint4*>(dst[i] + n0) = ov[i];
-        }
       } else {
         for (int c = 0; c < kChunks; ++c, ++q) {
           const int sb = HEAD2 ? c : q % kNumSB;                    // fused head: the tile's four chunks stay staged (A' operand)
           const uint32_t stg = smem_u32(sSB + sb * kSBBytes);
           if (!HEAD2 && leader) {
-            bulk_wait_read<1>();                                    // stores <= q-2 have left shared memory
+            bulk_wait_read<EPI2 ? 0 : 1>();                         // stores <= q-2 (EPI2: <= q-1) have left shared memory
             if (RES) mbar_arrive(&sbempty_bar[(q + kResLead) % kNumSB]);   // hand the buffer of chunk q+2 to warp 2
           }
           uint32_t v[32];
@@ -552,11 +486,11 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             if (c == kChunks - 1) {                                  // all four chunks staged: one fence + barrier per tile
               fence_proxy_async_smem();                              // generic-proxy writes -> visible to the tensor core
               tc_fence_before();                                     // our tcgen05.ld of this accumulator precede its reuse below
-              named_bar_sync(1, kEpiThreads);
+              named_bar_sync(bar_id, kEpiThreads);
             }
           } else {
             fence_proxy_async_smem();                                // generic-proxy writes -> visible to TMA
-            named_bar_sync(1, kEpiThreads);
+            named_bar_sync(bar_id, kEpiThreads);
             if (leader) {
               tma_store_4d(&tmOut.m[t.cls], sSB + sb * kSBBytes, t.n_tile * BLOCK_N + c * 64, t.x0, t.y0, t.b0);
               bulk_commit();
@@ -607,7 +541,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
       }
     }
-    if (!HEAD2 && !DIRECT && leader) bulk_wait_all();
+    if (!HEAD2 && leader) bulk_wait_all();
   }
 
   tc_fence_before();
@@ -748,10 +682,18 @@ struct hpe_conv_plan {
   void* y;
   CUtensorMap tmA2;
   const void* fn;
-  int direct;                         // direct-store epilogue (plain coalesced stores instead of TMA stores)
+  int epi2;                           // two epilogue groups (608-thread kernel)
   int halo_taps_y;                    // != 0: the layer runs on the y-halo variant (conv_halo.cu)
   HaloParams hp;
 };
+
+// CTAs a conv launch may use: all SMs, or fewer (HPE_B200_MAX_CTAS, read when the plan is created) so that two half-batch plans on
+// two streams occupy disjoint SM halves and an HBM-bound layer of one overlaps a tensor-bound layer of the other.
+static int cta_budget() {
+  const char* e = getenv("HPE_B200_MAX_CTAS");
+  const int n = e ? atoi(e) : 0;
+  return (n > 0 && n < num_sms()) ? n : num_sms();
+}
 
 // Layers whose generic kernel is operand-delivery bound and that fit the y-halo variant: the stem, and 3x3/s1 64->64.
 static bool halo_eligible(const hpe_conv_desc* d, int Ho, int Wo) {
@@ -1026,57 +968,57 @@ extern "C" int hpe_conv_pack_weight_dgrad(const hpe_conv_desc* f, const float* w
 
 typedef void (*ConvKernelFn)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const OutMaps, const CUtensorMap, const ConvParams);
 
-// ST_N / ST_R: operand-ring depth without / with a residual; D = direct-store epilogue (1 / 3 staging buffers instead of 3 / 4)
-template <int BN, int ST_N, int ST_R, int ST_F, bool D>
+// ST_N / ST_R / ST_F: operand-ring depth without / with a residual / for the fp32 heatmap epilogue
+template <int BN, int ST_N, int ST_R, int ST_F>
 static ConvKernelFn pick_kernel_bn(int act, bool res, bool fin, size_t* smem) {
-  *smem = res ? SmemLayout<BN, ST_R, false, D ? 3 : 4, false, D>::kDynamic : SmemLayout<BN, ST_N, false, D ? 1 : 3, false, D>::kDynamic;
+  *smem = res ? SmemLayout<BN, ST_R, false, 4>::kDynamic : SmemLayout<BN, ST_N, false, 3>::kDynamic;
   if (fin) { *smem = SmemLayout<BN, ST_F, false, 0>::kDynamic; return conv_gemm_kernel<BN, ST_F, HPE_ACT_NONE, false, true>; }
   if constexpr (BN >= 64) {
     switch (act) {
-      case HPE_ACT_RELU: return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_RELU, true, false, false, false, D> : conv_gemm_kernel<BN, ST_N, HPE_ACT_RELU, false, false, false, false, D>;
-      case HPE_ACT_SILU: return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_SILU, true, false, false, false, D> : conv_gemm_kernel<BN, ST_N, HPE_ACT_SILU, false, false, false, false, D>;
-      case HPE_ACT_GELU: return res ? nullptr : conv_gemm_kernel<BN, ST_N, HPE_ACT_GELU, false, false, false, false, D>;
-      default:           return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_NONE, true, false, false, false, D> : conv_gemm_kernel<BN, ST_N, HPE_ACT_NONE, false, false, false, false, D>;
+      case HPE_ACT_RELU: return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_RELU, true, false> : conv_gemm_kernel<BN, ST_N, HPE_ACT_RELU, false, false>;
+      case HPE_ACT_SILU: return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_SILU, true, false> : conv_gemm_kernel<BN, ST_N, HPE_ACT_SILU, false, false>;
+      case HPE_ACT_GELU: return res ? nullptr : conv_gemm_kernel<BN, ST_N, HPE_ACT_GELU, false, false>;
+      default:           return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_NONE, true, false> : conv_gemm_kernel<BN, ST_N, HPE_ACT_NONE, false, false>;
     }
   }
   return nullptr;
 }
 
-template <int BN, int ST_N, int ST_R, bool D>
+template <int BN, int ST_N, int ST_R>
 static ConvKernelFn pick_kernel_pair(int act, bool res, size_t* smem) {
-  *smem = res ? SmemLayout<BN, ST_R, true, D ? 3 : 4, false, D>::kDynamic : SmemLayout<BN, ST_N, true, D ? 1 : 3, false, D>::kDynamic;
+  *smem = res ? SmemLayout<BN, ST_R, true, 4>::kDynamic : SmemLayout<BN, ST_N, true, 3>::kDynamic;
   switch (act) {
-    case HPE_ACT_RELU: return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_RELU, true, false, true, false, D> : conv_gemm_kernel<BN, ST_N, HPE_ACT_RELU, false, false, true, false, D>;
-    case HPE_ACT_SILU: return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_SILU, true, false, true, false, D> : conv_gemm_kernel<BN, ST_N, HPE_ACT_SILU, false, false, true, false, D>;
-    case HPE_ACT_GELU: return res ? nullptr : conv_gemm_kernel<BN, ST_N, HPE_ACT_GELU, false, false, true, false, D>;
-    default:           return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_NONE, true, false, true, false, D> : conv_gemm_kernel<BN, ST_N, HPE_ACT_NONE, false, false, true, false, D>;
+    case HPE_ACT_RELU: return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_RELU, true, false, true> : conv_gemm_kernel<BN, ST_N, HPE_ACT_RELU, false, false, true>;
+    case HPE_ACT_SILU: return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_SILU, true, false, true> : conv_gemm_kernel<BN, ST_N, HPE_ACT_SILU, false, false, true>;
+    case HPE_ACT_GELU: return res ? nullptr : conv_gemm_kernel<BN, ST_N, HPE_ACT_GELU, false, false, true>;
+    default:           return res ? conv_gemm_kernel<BN, ST_R, HPE_ACT_NONE, true, false, true> : conv_gemm_kernel<BN, ST_N, HPE_ACT_NONE, false, false, true>;
+  }
+}
+
+// two epilogue groups (608 threads) on the 256-wide pair kernel with a residual: 3 ring stages + 2 x 3 staging buffers
+static ConvKernelFn pick_kernel_epi2(int act, size_t* smem) {
+  *smem = SmemLayout<256, 3, true, 6, false, true>::kDynamic;
+  switch (act) {
+    case HPE_ACT_RELU: return conv_gemm_kernel<256, 3, HPE_ACT_RELU, true, false, true, false, true>;
+    case HPE_ACT_SILU: return conv_gemm_kernel<256, 3, HPE_ACT_SILU, true, false, true, false, true>;
+    case HPE_ACT_GELU: return nullptr;
+    default:           return conv_gemm_kernel<256, 3, HPE_ACT_NONE, true, false, true, false, true>;
   }
 }
 
 // ring depths: as many stages as fit beside the staging buffers in the 227 KB a CTA may use
-static ConvKernelFn pick_kernel(int block_n, int act, bool res, bool fin, bool pair, bool head2, bool direct, size_t* smem) {
+static ConvKernelFn pick_kernel(int block_n, int act, bool res, bool fin, bool pair, bool head2, bool epi2, size_t* smem) {
   if (head2) { *smem = SmemLayout<256, 4, true, 4, true>::kDynamic; return conv_gemm_kernel<256, 4, HPE_ACT_RELU, false, false, true, true>; }
-  if (direct && !fin) {
-    // direct-store epilogue: 16 KB (no residual) / 48 KB (residual) of staging instead of 48 / 64 KB -> one more ring stage
-    if (pair && block_n == 256) return pick_kernel_pair<256, 6, 5, true>(act, res, smem);
-    if (pair && block_n == 192) return pick_kernel_pair<192, 7, 6, true>(act, res, smem);
-    if (pair) return pick_kernel_pair<128, 8, 7, true>(act, res, smem);
-    switch (block_n) {
-      case 64:  return pick_kernel_bn<64, 8, 7, 9, true>(act, res, fin, smem);
-      case 128: return pick_kernel_bn<128, 6, 5, 7, true>(act, res, fin, smem);
-      case 192: return pick_kernel_bn<192, 5, 4, 4, true>(act, res, fin, smem);
-      default:  return pick_kernel_bn<256, 4, 3, 4, true>(act, res, fin, smem);
-    }
-  }
-  if (pair && block_n == 256) return pick_kernel_pair<256, 5, 5, false>(act, res, smem);       // 32 KB stages (A + half of B)
-  if (pair && block_n == 192) return pick_kernel_pair<192, 6, 5, false>(act, res, smem);       // 28 KB stages (ConvNeXt C = 192/384/768)
-  if (pair) return pick_kernel_pair<128, 7, 6, false>(act, res, smem);                         // 24 KB stages
+  if (epi2) return pick_kernel_epi2(act, smem);
+  if (pair && block_n == 256) return pick_kernel_pair<256, 5, 5>(act, res, smem);       // 32 KB stages (A + half of B)
+  if (pair && block_n == 192) return pick_kernel_pair<192, 6, 5>(act, res, smem);       // 28 KB stages (ConvNeXt C = 192/384/768)
+  if (pair) return pick_kernel_pair<128, 7, 6>(act, res, smem);                         // 24 KB stages
   switch (block_n) {
-    case 32:  return pick_kernel_bn<32, 6, 6, 11, false>(act, res, fin, smem);     // 20 KB stages (FINAL only)
-    case 64:  return pick_kernel_bn<64, 7, 6, 9, false>(act, res, fin, smem);      // 24 KB stages
-    case 128: return pick_kernel_bn<128, 5, 5, 7, false>(act, res, fin, smem);     // 32 KB
-    case 192: return pick_kernel_bn<192, 4, 4, 4, false>(act, res, fin, smem);     // 40 KB
-    default:  return pick_kernel_bn<256, 3, 3, 4, false>(act, res, fin, smem);     // 48 KB
+    case 32:  return pick_kernel_bn<32, 6, 6, 11>(act, res, fin, smem);     // 20 KB stages (FINAL only)
+    case 64:  return pick_kernel_bn<64, 7, 6, 9>(act, res, fin, smem);      // 24 KB stages
+    case 128: return pick_kernel_bn<128, 5, 5, 7>(act, res, fin, smem);     // 32 KB
+    case 192: return pick_kernel_bn<192, 4, 4, 4>(act, res, fin, smem);     // 40 KB
+    default:  return pick_kernel_bn<256, 3, 3, 4>(act, res, fin, smem);     // 48 KB
   }
 }
 
@@ -1121,7 +1063,7 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
   const long long nt = (long long)p.tiles_x * p.tiles_y * p.tiles_b * p.n_tiles_n * p.n_classes;
   if (nt > 0x7fffffff) { delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: too many tiles"); }
   p.num_tiles = (int)nt;
-  pl->grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
+  pl->grid = p.num_tiles < cta_budget() ? p.num_tiles : cta_budget();
   {
     // cta_group::2 for the 256-wide tiles (HPE_B200_PAIR=0 disables): pairs of M tiles share one MMA stream
     const char* e = getenv("HPE_B200_PAIR");
@@ -1135,18 +1077,20 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
     if (pl->pair) {
       const long long np = (m_tiles + 1) / 2 * p.n_tiles_n * p.n_classes;
       p.num_tiles = (int)np;
-      const int max_clusters = num_sms() / 2;
+      const int max_clusters = cta_budget() / 2;
       pl->grid = 2 * (int)(np < max_clusters ? np : max_clusters);
     }
   }
   {
-    // direct-store epilogue: opt-in (HPE_B200_EPI_DIRECT=1).  Measured on B200 (profiles/r02_epilogue_direct_ab.log): parity-
-    // green but SLOWER than the lock-step TMA-store epilogue -- forward 3.37 -> 3.81 ms, the residual 1x1 layers +25...+80 us
-    // each -- so bulk TMA stores stay the default.
-    const char* e = getenv("HPE_B200_EPI_DIRECT");
-    pl->direct = (e && e[0] == '1') && d->kind != HPE_CONV_FINAL && !d->head2;
+    // two epilogue groups for the 256-wide pair kernel with a residual (HPE_B200_EPI2=0 disables, =2 also takes the deep-K
+    // layers): these layers are epilogue-bound (8.2 k cycles per tile against 0.5-4 k of MMA).  The second group's staging
+    // buffers cost two ring stages (3 instead of 5), so layers with more than 8 k-blocks per tile keep the single group.
+    const char* e = getenv("HPE_B200_EPI2");
+    const int mode = e ? atoi(e) : 1;
+    const int num_kb = p.taps * p.kc_per_tap + p.kc2;
+    pl->epi2 = mode != 0 && pl->pair && pl->block_n == 256 && p.has_res && !d->head2 && d->act != HPE_ACT_GELU && (mode == 2 || num_kb <= 8);
   }
-  pl->fn = (const void*)pick_kernel(pl->block_n, d->act, p.has_res != 0, d->kind == HPE_CONV_FINAL, pl->pair != 0, d->head2 != 0, pl->direct != 0, &pl->smem);
+  pl->fn = (const void*)pick_kernel(pl->block_n, d->act, p.has_res != 0, d->kind == HPE_CONV_FINAL, pl->pair != 0, d->head2 != 0, pl->epi2 != 0, &pl->smem);
   if (!pl->fn) { delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: no kernel for BLOCK_N=%d", pl->block_n); }
   {
     cudaError_t e = cudaFuncSetAttribute((const void*)pl->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem);
@@ -1159,7 +1103,7 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
     int max_clusters = -1;
     {
       cudaLaunchConfig_t cfg = {};
-      cfg.gridDim = dim3(num_sms() / 2 * 2); cfg.blockDim = dim3(kConvThreads); cfg.dynamicSmemBytes = pl->smem;
+      cfg.gridDim = dim3(num_sms() / 2 * 2); cfg.blockDim = dim3(pl->epi2 ? kConvThreads2 : kConvThreads); cfg.dynamicSmemBytes = pl->smem;
       cudaLaunchAttribute at[1];
       at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
       cfg.attrs = at; cfg.numAttrs = 1;
@@ -1168,6 +1112,7 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
       if (e != cudaSuccess || n <= 0) { delete pl; return fail(HPE_ECUDA, "cudaOccupancyMaxActiveClusters failed: %s", cudaGetErrorString(e)); }
       const char* ov = getenv("HPE_B200_PAIR_CLUSTERS");
       max_clusters = ov ? atoi(ov) : n;
+      if (max_clusters > cta_budget() / 2) max_clusters = cta_budget() / 2;
       if (getenv("HPE_B200_DEBUG")) fprintf(stderr, "[hpe] max active 2-CTA clusters: %d (using %d)\n", n, max_clusters);
     }
     pl->grid = 2 * (p.num_tiles < max_clusters ? p.num_tiles : max_clusters);
@@ -1188,7 +1133,7 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
       pl->hp.tiles_x = (pl->Wo + 2) / 3; pl->hp.tiles_y = (pl->Ho + 14) / 15;
     }
     pl->hp.num_tiles = pl->hp.tiles_x * pl->hp.tiles_y * d->B;
-    pl->grid = pl->hp.num_tiles < num_sms() ? pl->hp.num_tiles : num_sms();
+    pl->grid = pl->hp.num_tiles < cta_budget() ? pl->hp.num_tiles : cta_budget();
     p.tw = 8; p.th = kHaloRows; p.nb = 1;        // brick of the A map encoded below
   } else if (d->pool) {
     delete pl;
@@ -1336,15 +1281,12 @@ static int conv_launch(hpe_conv_plan* pl, const void* x, const void* x2, const v
   p.scale = scale; p.shift = shift;
   p.hm_out = (pl->d.kind == HPE_CONV_FINAL || pl->d.head2) ? (float*)y : nullptr;
   p.bias2 = bias2;
-  p.y_out = (__nv_bfloat16*)y;
-  p.out_pitch = pl->d.out_cstride ? pl->d.out_cstride : pl->d.Cout;
-  p.out_up = (is_class_strided(pl->d.kind) || pl->d.kind == HPE_CONV_DGRAD1x1S2) ? 2 : 1;
   if (!p.has_res && !pl->d.head2) pl->tmRes = pl->tmA;      // unused, but must be a valid object to copy
   if (pl->d.kind == HPE_CONV_FINAL || pl->d.head2) for (int c = 0; c < 4; ++c) pl->tmOut.m[c] = pl->tmA;
   if (!pl->d.Cin2) pl->tmA2 = pl->tmA;      // unused, but must be a valid object to copy
   void* args[6] = {&pl->tmA, &pl->tmA2, &pl->tmW, &pl->tmOut, &pl->tmRes, &p};
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(pl->grid); cfg.blockDim = dim3(kConvThreads);
+  cfg.gridDim = dim3(pl->grid); cfg.blockDim = dim3(pl->epi2 ? kConvThreads2 : kConvThreads);
   cfg.dynamicSmemBytes = pl->smem; cfg.stream = (cudaStream_t)stream;
   cudaLaunchAttribute attr[2];
   int na = 0;

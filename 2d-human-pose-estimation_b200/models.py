@@ -243,10 +243,29 @@ class _ForwardPlan:
         if H % 32 or W % 32:
             raise ValueError(f"input {H}x{W} must be a multiple of 32")
         self.B, self.H, self.W, self.device = B, H, W, device
-        self.ops = []            # (layer, src_key, res_key, dst_key, src2_key)
+        self.ops = []            # (layer, src_key, res_key, dst_key, src2_key), one per conv layer, in launch order
+        # DEPTH-FIRST SECTION (experiment, OFF by default: HPE_B200_DF_CHUNK images per pass, HPE_B200_DF_STAGES ResNet stages).
+        # Idea: the stem and the first stages move 403 MB tensors at B=256, but a chunk of 32 images keeps a bottleneck's working
+        # set inside the 126 MB L2, so the section's layers are planned for `chunk` images with chunk-sized buffers that every pass
+        # reuses; only the section's input (s2d image) and output are full-batch tensors, addressed per pass as batch slices.
+        # Measured on B200 (profiles/r02_experiments.md): SLOWER at every setting (3.21 ms -> 3.40 ms at 64 x 2 stages, 3.65 ms at
+        # 32 x 2): a conv launch has ~10-14 us of fixed cost (ramp, last-tile epilogue, wave tail), which the 66-150 extra launches
+        # pay many times over.  Per-image results do not depend on the chunking (same kernels, same bricks within an image).
+        chunk = int(os.environ.get("HPE_B200_DF_CHUNK", "0"))
+        self.df_stages = min(3, int(os.environ.get("HPE_B200_DF_STAGES", "2"))) if (chunk > 0 and B > chunk and B % chunk == 0) else 0
+        self.chunk = chunk if self.df_stages > 0 else B
+        self.n_chunks = B // self.chunk
+        self.n_section_ops = 0   # the first n_section_ops entries of self.ops run once per chunk
+        self.full_keys = set()   # full-batch buffers the section addresses by batch slice
         self.fused_shortcut = {}  # conv3 path -> downsample path folded into it
         # projection shortcut (downsample conv + BN) accumulated into conv3's TMEM tile: the shortcut tensor never exists
         fuse_sc = os.environ.get("HPE_B200_FUSE_SHORTCUT", "1") != "0"
+        # identity shortcut as extra k-blocks against an identity weight block (experiment, HPE_B200_RES_MMA=1, off by default): the
+        # residual add moves from the epilogue to the tensor pipe.  Measured (profiles/r02_experiments.md): layer1 conv3 -13 us
+        # each (its residual then streams through the 5-deep operand ring), every deeper layer slower (full-N identity k-blocks
+        # cost 4 x 512 MMA cycles and 64 KB of weight traffic per tile): forward 3.34 -> 3.77 ms.
+        res_mma = os.environ.get("HPE_B200_RES_MMA", "0") != "0"
+        self.identity_shortcut = set()
         self.bufs = {}
         self.named = {}          # module path -> ConvLayer (for load_weights)
         K = model.njoints
@@ -256,12 +275,20 @@ class _ForwardPlan:
             self.bufs[key] = torch.empty(shape, dtype=dtype, device=dev)
             return key
 
-        def add(name, layer, src, dst, res=None, src2=None):
+        def add(name, layer, src, dst, res=None, src2=None, full_out=False):
             self.named[name] = layer
-            buf(dst, layer.out_shape(), torch.float32 if (layer.kind == CONV_FINAL or layer.head2) else torch.bfloat16)
+            shape = layer.out_shape()
+            if full_out:                    # last layer of the depth-first section: writes its batch slice of a full tensor
+                shape = (Bf,) + tuple(shape[1:])
+                self.full_keys.add(dst)
+            buf(dst, shape, torch.float32 if (layer.kind == CONV_FINAL or layer.head2) else torch.bfloat16)
             self.ops.append((layer, src, res, dst, src2))
 
         self.s2d = preprocess(torch.zeros(B, 3, H, W, device=dev))
+        Bf = B                              # full batch
+        if self.df_stages > 0:
+            B = self.chunk                  # the section's layers are planned for one chunk
+            self.full_keys.add("s2d")
         # `x = self.maxpool(x)` (timm ResNet.forward_features) taken in the stem's epilogue: the H/2 x W/2 tensor never exists
         self.fused_pool = False
         h, w = H // 4, W // 4
@@ -276,7 +303,11 @@ class _ForwardPlan:
             buf("pool", (B, h, w, 64))
         cur, cin = "pool", 64
         for i, (n, p) in enumerate(zip(_LAYERS, _PLANES)):
+            if self.df_stages > 0 and i == self.df_stages:
+                self.n_section_ops = len(self.ops)
+                B = Bf
             for j in range(n):
+                last_of_section = self.df_stages > 0 and i == self.df_stages - 1 and j == n - 1
                 s = 2 if (i > 0 and j == 0) else 1
                 pre = f"backbone.layer{i + 1}.{j}"
                 add(pre + ".conv1", ConvLayer(CONV_1x1, B, h, w, cin, p, 1, ACT_RELU, False, dev), cur, pre + ".t1")
@@ -289,9 +320,14 @@ class _ForwardPlan:
                 if j == 0 and fuse_sc:
                     self.fused_shortcut[pre + ".conv3"] = pre + ".downsample"
                     add(pre + ".conv3", ConvLayer(CONV_1x1, B, h, w, p, 4 * p, 1, ACT_RELU, False, dev, Cin2=cin, stride2=s),
-                        pre + ".t2", pre + ".out", None, cur)
+                        pre + ".t2", pre + ".out", None, cur, full_out=last_of_section)
+                elif res_mma:
+                    self.identity_shortcut.add(pre + ".conv3")
+                    add(pre + ".conv3", ConvLayer(CONV_1x1, B, h, w, p, 4 * p, 1, ACT_RELU, False, dev, Cin2=4 * p, stride2=1),
+                        pre + ".t2", pre + ".out", None, sc, full_out=last_of_section)
                 else:
-                    add(pre + ".conv3", ConvLayer(CONV_1x1, B, h, w, p, 4 * p, 1, ACT_RELU, True, dev), pre + ".t2", pre + ".out", sc)
+                    add(pre + ".conv3", ConvLayer(CONV_1x1, B, h, w, p, 4 * p, 1, ACT_RELU, True, dev), pre + ".t2", pre + ".out", sc,
+                        full_out=last_of_section)
                 cur, cin = pre + ".out", 4 * p
         self.features_key = cur
         # last deconv stage + final_layer in one kernel (the 256-channel deconv3 output never leaves shared memory) when the
@@ -313,10 +349,12 @@ class _ForwardPlan:
             cur, cin, h, w = f"deconv{d}", 256, 2 * h, 2 * w
         if self.fused_head is None:
             add("final_layer", ConvLayer(CONV_FINAL, B, h, w, 256, K, 1, ACT_NONE, False, dev), cur, "heatmaps")
-        self.bufs["s2d"] = self.s2d
         self.weights_version = -1
         self.graph = None
-        self.n_launches = len(self.ops) + (1 if self.fused_pool else 2)          # + preprocess (+ maxpool)
+        self.bufs["s2d"] = self.s2d.view(Bf, -1)
+        self.B = Bf
+        extra = 0 if self.fused_pool else 1                                       # separate max-pool launch
+        self.n_launches = 1 + len(self.ops) + extra + (self.n_chunks - 1) * (self.n_section_ops + extra)      # 1 = preprocess
 
     @property
     def features(self):
@@ -343,6 +381,10 @@ class _ForwardPlan:
             scale, shift = fold_bn(bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps)
             if name == self.fused_head:
                 layer.load_head2(mods["final_layer"].weight, mods["final_layer"].bias)
+            if name in self.identity_shortcut:
+                c = m.out_channels
+                layer.load2(m.weight, scale, shift, torch.eye(c).view(c, c, 1, 1), torch.ones(c), torch.zeros(c))
+                continue
             if name in self.fused_shortcut:
                 ds = self.fused_shortcut[name]
                 bn2 = mods[ds + ".1"]
@@ -353,21 +395,39 @@ class _ForwardPlan:
         self.weights_version = model._weights_version
         self.graph = None         # packed buffers are updated in place, but be conservative
 
-    def _launch_all(self):
-        b = self.bufs
-        for layer, src, res, dst, src2 in self.ops:
+    def _view(self, key, c):
+        """Buffer `key` as pass `c` of the depth-first section sees it: full-batch tensors by batch slice, chunk buffers whole."""
+        if key is None:
+            return None
+        t = self.bufs[key]
+        return t[c * self.chunk:(c + 1) * self.chunk] if key in self.full_keys else t
+
+    def _launch_op(self, op, c=None):
+        layer, src, res, dst, src2 = op
+        if c is None:
+            b = self.bufs
             layer(b[src], b[res] if res else None, b[dst], b[src2] if src2 else None)
-            if dst == "stem":
-                maxpool3x3s2(b["stem"], b["pool"])
+        else:
+            layer(self._view(src, c), self._view(res, c), self._view(dst, c), self._view(src2, c))
+        if dst == "stem":
+            maxpool3x3s2(self.bufs["stem"], self.bufs["pool"])
+
+    def _launch_all(self):
+        ns = self.n_section_ops
+        for c in range(self.n_chunks if ns else 0):
+            for op in self.ops[:ns]:
+                self._launch_op(op, c)
+        for op in self.ops[ns:]:
+            self._launch_op(op)
 
     def layer_table(self):
         """(module path, family, algorithmic FLOPs, ConvLayer, buffers) per conv launch, in launch order.  FLOPs = 2 x MAC
         over the REAL filter taps / channels (no padding, no zero insertion); a fused projection shortcut
         or fused final 1x1 counts the work of both convolutions."""
         rows = []
-        for name, layer, src, res, dst, src2 in ((n, *op) for n, op in zip(self.named, self.ops)):
+        for k, (name, layer, src, res, dst, src2) in enumerate((n, *op) for n, op in zip(self.named, self.ops)):
             d = layer.desc
-            m = d.B * layer.Ho * layer.Wo
+            m = d.B * layer.Ho * layer.Wo * (self.n_chunks if k < self.n_section_ops else 1)      # per step
             taps = {CONV_1x1: 1, CONV_3x3: 9, CONV_STEM7x7: 49, CONV_DECONV4: 4, CONV_FINAL: 1}[d.kind]
             flops = 2.0 * m * d.Cin * d.Cout * taps + 2.0 * m * d.Cin2 * d.Cout + 2.0 * m * 256 * layer.head2
             if name.startswith("deconv") or name == "final_layer":
@@ -383,6 +443,10 @@ class _ForwardPlan:
         """NCHW fp32 CPU copies of every launch's stored inputs and output, keyed by module path: ``{"x", "res", "x2", "y"}``
         (the stem's ``x`` is omitted: its input is the image).  Teacher-forced parity tests feed these to the fp32 oracle
         layer by layer (tests/test_model_gpu.py)."""
+        if self.n_section_ops and self.n_chunks > 1:
+            raise RuntimeError("export_acts: the depth-first section reuses its chunk buffers (only the last pass is stored); "
+                               "use a batch <= HPE_B200_DF_CHUNK or HPE_B200_DF_CHUNK=0")
+
         def nchw(t):
             return t.float().cpu() if t.dtype == torch.float32 else t.float().cpu().permute(0, 3, 1, 2).contiguous()
         acts = {}
@@ -401,10 +465,14 @@ class _ForwardPlan:
         """CUDA-event time of every conv launch of the step, eagerly (no graph): per launch, one untimed call then ``reps``
         back-to-back calls between two events (the launch gap of all but the first is hidden behind the previous call).
         Returns [(name, family, flops, microseconds)].  Diagnostic / benchmark use."""
-        b = self.bufs
         out = []
-        for name, fam, flops, layer, (src, res, dst, src2) in self.layer_table():
-            call = lambda: layer(b[src], b[res] if res else None, b[dst], b[src2] if src2 else None)  # noqa: E731
+        for k, (name, fam, flops, layer, (src, res, dst, src2)) in enumerate(self.layer_table()):
+            passes = self.n_chunks if k < self.n_section_ops else 1            # a section layer is timed on pass 0, reported per step
+            c = 0 if k < self.n_section_ops else None
+            call = lambda: layer(self._view(src, c) if c is not None else self.bufs[src],          # noqa: E731
+                                 (self._view(res, c) if c is not None else self.bufs[res]) if res else None,
+                                 self._view(dst, c) if c is not None else self.bufs[dst],
+                                 (self._view(src2, c) if c is not None else self.bufs[src2]) if src2 else None)
             call()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
@@ -412,7 +480,7 @@ class _ForwardPlan:
                 call()
             e1.record()
             e1.synchronize()
-            out.append((name, fam, flops, e0.elapsed_time(e1) / reps * 1e3))
+            out.append((name, fam, flops, e0.elapsed_time(e1) / reps * 1e3 * passes))
         return out
 
     def run(self, x: torch.Tensor) -> torch.Tensor:

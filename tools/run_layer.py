@@ -30,9 +30,11 @@ r = torch.randn(layer.out_shape(), device=dev).to(torch.bfloat16) if res else No
 y = layer.alloc_out()
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 ts = []
+noflush = os.environ.get("RUN_LAYER_NOFLUSH", "0") == "1"      # inputs stay L2-resident between iterations (small B)
 for i in range(iters):
-    flush.zero_()
+    if not noflush:
+        flush.zero_()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(); layer(x, r, y); e1.record(); torch.cuda.synchronize()
     ts.append(e0.elapsed_time(e1))
-print(f"kind {kind} {Cin}->{Cout} s{stride} @{H}x{W} B={B}: min {min(ts)*1e3:.1f} us  median {sorted(ts)[len(ts)//2]*1e3:.1f} us")
+print(f"kind {kind} {Cin}->{Cout} s{stride} res{res} @{H}x{W} B={B} noflush={int(noflush)} EPI2={os.environ.get('HPE_B200_EPI2','-')}: min {min(ts)*1e3:.1f} us  median {sorted(ts)[len(ts)//2]*1e3:.1f} us")
