@@ -20,7 +20,7 @@ CONV_DGRAD3x3S2, CONV_DGRAD1x1S2, CONV_4x4S2, CONV_2x2S2 = 5, 6, 7, 8
 class ConvDesc(C.Structure):
     _fields_ = [("kind", C.c_int), ("B", C.c_int), ("H", C.c_int), ("W", C.c_int), ("Cin", C.c_int),
                 ("Cout", C.c_int), ("stride", C.c_int), ("act", C.c_int), ("has_residual", C.c_int),
-                ("in_cstride", C.c_int), ("out_cstride", C.c_int), ("Cin2", C.c_int), ("stride2", C.c_int), ("head2", C.c_int), ("pool", C.c_int)]
+                ("in_cstride", C.c_int), ("out_cstride", C.c_int), ("Cin2", C.c_int), ("stride2", C.c_int), ("head2", C.c_int), ("pool", C.c_int), ("chain", C.c_int)]
 
 
 _vp, _i, _f, _sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
@@ -45,6 +45,7 @@ SIGNATURES = {
     "hpe_conv_pack_weight2": (_i, [C.POINTER(ConvDesc), _vp, _vp, _vp, _vp]),
     "hpe_conv_run2": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "hpe_conv_run_head2": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "hpe_conv_run_chain": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "hpe_pack_job_bytes": (_sz, []),
     "hpe_conv_pack_job_fill": (_i, [C.POINTER(ConvDesc), _i, _vp, _vp, _i, _vp, C.POINTER(_i)]),
     "hpe_conv_pack_jobs_run": (_i, [_vp, _i, _i, _vp]),

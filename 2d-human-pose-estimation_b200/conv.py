@@ -26,10 +26,11 @@ def fold_bn(weight, bias, running_mean, running_var, eps):
 
 class ConvLayer:
     def __init__(self, kind, B, H, W, Cin, Cout, stride=1, act=ACT_RELU, has_residual=False, device="cuda", desc=None,
-                 in_cstride=0, out_cstride=0, Cin2=0, stride2=1, head2=0, pool=0):
+                 in_cstride=0, out_cstride=0, Cin2=0, stride2=1, head2=0, pool=0, chain=0):
         self.device = torch.device(device)
         self.desc = desc if desc is not None else ConvDesc(kind, B, H, W, Cin, Cout, stride, act, int(has_residual),
-                                                           in_cstride, out_cstride, Cin2, stride2 if Cin2 else 0, head2, int(pool))
+                                                           in_cstride, out_cstride, Cin2, stride2 if Cin2 else 0, head2, int(pool),
+                                                           int(chain))
         kind, B, Cout = self.desc.kind, self.desc.B, self.desc.Cout
         lib = _lib.lib()
         ho, wo = C.c_int(), C.c_int()
@@ -46,6 +47,11 @@ class ConvLayer:
         if self.head2:       # fused head: the final 1x1's weights (32 zero-padded rows x 256) and bias
             self.w2_packed = torch.zeros(32 * 256, dtype=torch.bfloat16, device=self.device)
             self.bias2 = torch.zeros(self.head2, dtype=torch.float32, device=self.device)
+        self.chain = int(self.desc.chain)
+        if self.chain:       # chained 1x1 conv 256 -> chain (the next layer): its packed weights and folded BN
+            self.w2_packed = torch.zeros(self.chain * 256, dtype=torch.bfloat16, device=self.device)
+            self.scale2 = torch.ones(self.chain, dtype=torch.float32, device=self.device)
+            self.shift2 = torch.zeros(self.chain, dtype=torch.float32, device=self.device)
         self.scale = torch.ones(Cout, dtype=torch.float32, device=self.device)
         self.shift = torch.zeros(Cout, dtype=torch.float32, device=self.device)
 
@@ -92,6 +98,18 @@ class ConvLayer:
         self.bias2.copy_(bias.detach().to(self.device, torch.float32))
         return self
 
+    def load_chain(self, weight: torch.Tensor, scale: torch.Tensor, shift: torch.Tensor):
+        """Chained layer (``chain = N2``): ``weight`` [N2,256,1,1] and folded BN ``scale``/``shift`` [N2] of the NEXT 1x1 conv
+        (timm ``Bottleneck.conv1``/``bn1``, resnet.py:247-251), applied to this layer's output tile while it is staged."""
+        w = weight.detach().to(self.device, torch.float32).contiguous()
+        cd = ConvDesc(CONV_1x1, self.B, self.Ho, self.Wo, 256, self.chain, 1, ACT_RELU, 0)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().hpe_conv_pack_weight(C.byref(cd), _lib.ptr(w), _lib.ptr(self.w2_packed), _lib.stream_ptr()),
+                       "hpe_conv_pack_weight")
+        self.scale2.copy_(scale.detach().to(self.device, torch.float32))
+        self.shift2.copy_(shift.detach().to(self.device, torch.float32))
+        return self
+
     def load2(self, weight: torch.Tensor, scale: torch.Tensor, shift: torch.Tensor, weight2: torch.Tensor, scale2: torch.Tensor,
               shift2: torch.Tensor):
         """Two-input layer (``Cin2``): ``y = act(bn(conv(x)) + bn2(conv2(x2)))`` -- conv3 + bn3 + the projection shortcut
@@ -108,7 +126,8 @@ class ConvLayer:
         self.shift.copy_(shift.detach().to(**f32) + shift2.detach().to(**f32))
         return self
 
-    def __call__(self, x: torch.Tensor, residual: torch.Tensor = None, out: torch.Tensor = None, x2: torch.Tensor = None):
+    def __call__(self, x: torch.Tensor, residual: torch.Tensor = None, out: torch.Tensor = None, x2: torch.Tensor = None,
+                 out2: torch.Tensor = None):
         if out is None:
             out = self.alloc_out()
         if self.desc.in_cstride or self.desc.out_cstride:
@@ -129,6 +148,16 @@ class ConvLayer:
                                                    _lib.ptr(out), _lib.stream_ptr())
             _lib.check(rc, "hpe_conv_run_head2")
             return out
+        if self.chain:
+            if out2 is None:
+                out2 = torch.empty((self.B, self.Ho, self.Wo, self.chain), dtype=torch.bfloat16, device=self.device)
+            _lib.require_cuda(out2)
+            with torch.cuda.device(self.device):
+                rc = _lib.lib().hpe_conv_run_chain(self.plan, _lib.ptr(x), _lib.ptr(x2), _lib.ptr(self.w_packed), _lib.ptr(self.scale),
+                                                   _lib.ptr(self.shift), _lib.ptr(residual), _lib.ptr(out), _lib.ptr(self.w2_packed),
+                                                   _lib.ptr(self.scale2), _lib.ptr(self.shift2), _lib.ptr(out2), _lib.stream_ptr())
+            _lib.check(rc, "hpe_conv_run_chain")
+            return out, out2
         with torch.cuda.device(self.device):
             rc = _lib.lib().hpe_conv_run2(self.plan, _lib.ptr(x), _lib.ptr(x2), _lib.ptr(self.w_packed), _lib.ptr(self.scale),
                                           _lib.ptr(self.shift), _lib.ptr(residual), _lib.ptr(out), _lib.stream_ptr())

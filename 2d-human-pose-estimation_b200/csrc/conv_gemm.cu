@@ -39,6 +39,7 @@ using namespace ptx;
 
 constexpr int kConvThreads   = 352;                   // 3 control warps + 8 epilogue warps
 constexpr int kConvThreads2  = 608;                   // EPI2: 3 control warps + two groups of 8 epilogue warps
+constexpr int kConvThreadsC  = 640;                   // CHAIN: 4 control warps (+ the second GEMM's issuer) + two groups of 8 epilogue warps
 constexpr int kEpiThreads    = 256;                   // epilogue threads of ONE group
 constexpr int kEpiWarp0      = 3;
 constexpr int kMaxCout       = 2048;
@@ -63,6 +64,8 @@ struct ConvParams {
   float* hm_out;                // HPE_CONV_FINAL / fused head: fp32 NCHW heatmaps
   int head2_k;                  // fused head (HEAD2): number of joints K <= 32 of the second GEMM
   const float* bias2;           // fused head: conv bias [K]
+  const float* scale2;          // CHAIN: folded-BN scale / shift [N2] of the chained 1x1 conv
+  const float* shift2;
 };
 
 struct TileCoord { int n_tile, cls, x0, y0, b0; };
@@ -102,18 +105,21 @@ __device__ __forceinline__ int kb_count(const ConvParams& p, int cls) {
 // NSB = epilogue staging buffers (16 KB each): 4 with a residual (they double as its prefetch ring), else 3 -- the bytes
 // saved go to a deeper operand ring, which is what bounds the deep-K layers (ring depth / hand-off round trip).
 // EPI2 (two epilogue groups): NSB counts the buffers of BOTH groups and each group has its own scale/shift table.
-template <int BLOCK_N, int STAGES, bool PAIR = false, int NSB = 4, bool HEAD2 = false, bool EPI2 = false>
+// KBR (CHAIN kernels): the layer's whole weight tile (KBR k-blocks of BLOCK_N x 64) stays RESIDENT and the ring carries A only.
+template <int BLOCK_N, int STAGES, bool PAIR = false, int NSB = 4, bool HEAD2 = false, bool EPI2 = false, int CHAIN = 0, int KBR = 0>
 struct SmemLayout {
-  static constexpr int kW2Bytes    = HEAD2 ? 4 * 16 * 128 : 0;       // fused head: this CTA's 16 rows x 256 K of the joint weights
+  // fused head: this CTA's 16 rows x 256 K of the joint weights; CHAIN: the chained 1x1 conv's [N2 rows][256 K] weights
+  static constexpr int kW2Bytes    = HEAD2 ? 4 * 16 * 128 : 4 * CHAIN * 128;
   static constexpr int kBBytes     = (PAIR ? BLOCK_N / 2 : BLOCK_N) * kKBlock * 2;    // a CTA of a pair holds half of B's rows
-  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStageBytes = kABytes + (KBR ? 0 : kBBytes);
   static constexpr int kOffA   = 0;
   static constexpr int kOffB   = STAGES * kABytes;
-  static constexpr int kOffSB  = kOffB + STAGES * kBBytes;
+  static constexpr int kOffSB  = kOffB + (KBR ? KBR : STAGES) * kBBytes;
   static constexpr int kOffSS  = kOffSB + NSB * kSBBytes;             // float scale[kMaxBlockN], shift[kMaxBlockN] (x 2 groups with EPI2)
-  static constexpr int kOffW2  = kOffSS + (EPI2 ? 4 : 2) * kMaxBlockN * 4;     // 1024-byte aligned
+  static constexpr int kOffSS2 = kOffSS + (EPI2 ? 4 : 2) * kMaxBlockN * 4;      // CHAIN: float scale2[128], shift2[128]
+  static constexpr int kOffW2  = kOffSS2 + (CHAIN ? 1024 : 0);                  // 1024-byte aligned
   static constexpr int kOffBar = kOffW2 + kW2Bytes;
-  static constexpr int kNumBar = 2 * STAGES + 4 + 2 * NSB + 3;       // + w2full, s2full, d2full (fused head)
+  static constexpr int kNumBar = 2 * STAGES + 4 + 4 * NSB + 7;       // + g2done[NSB], staged[NSB] (CHAIN) + w2full, s2full, d2full[2], a2empty[2], spare
   static constexpr int kTotal  = kOffBar + kNumBar * 8 + 16;
   static constexpr int kDynamic = kTotal;             // the dynamic segment starts 1024-byte aligned (checked in the kernel)
   static_assert(kTotal <= 232448, "exceeds the 227 KB of shared memory a CTA may use");
@@ -174,6 +180,36 @@ __device__ __forceinline__ float silu_fast(float x) {
   return x * r;
 }
 
+// One epilogue warp's share of a staged chunk: 32 accumulator columns of tile row `row` -> scale/shift (+ residual read back from
+// the chunk buffer) -> activation -> bf16 -> the chunk buffer's 128-byte-swizzled row.  (Same arithmetic as the generic epilogue
+// below; used by the chained kernel's two-group epilogue.)
+template <int ACT>
+__device__ __forceinline__ void epi_chunk_math(const uint32_t (&v)[32], uint32_t ss, uint32_t sh, uint32_t rowp, int half, int row, bool add_res) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float4 s0 = lds_f4(ss + j * 32), s1 = lds_f4(ss + j * 32 + 16);
+    const float4 h0 = lds_f4(sh + j * 32), h1 = lds_f4(sh + j * 32 + 16);
+    float2 o01 = __ffma2_rn(make_float2(__uint_as_float(v[j * 8 + 0]), __uint_as_float(v[j * 8 + 1])), make_float2(s0.x, s0.y), make_float2(h0.x, h0.y));
+    float2 o23 = __ffma2_rn(make_float2(__uint_as_float(v[j * 8 + 2]), __uint_as_float(v[j * 8 + 3])), make_float2(s0.z, s0.w), make_float2(h0.z, h0.w));
+    float2 o45 = __ffma2_rn(make_float2(__uint_as_float(v[j * 8 + 4]), __uint_as_float(v[j * 8 + 5])), make_float2(s1.x, s1.y), make_float2(h1.x, h1.y));
+    float2 o67 = __ffma2_rn(make_float2(__uint_as_float(v[j * 8 + 6]), __uint_as_float(v[j * 8 + 7])), make_float2(s1.z, s1.w), make_float2(h1.z, h1.w));
+    const uint32_t slot = rowp + (((half * 4 + j) ^ (row & 7)) << 4);     // 128-byte swizzle
+    if (add_res) {
+      const uint4 rr = lds_v4(slot);
+      o01 = __fadd2_rn(o01, make_float2(bf16_lo(rr.x), bf16_hi(rr.x))); o23 = __fadd2_rn(o23, make_float2(bf16_lo(rr.y), bf16_hi(rr.y)));
+      o45 = __fadd2_rn(o45, make_float2(bf16_lo(rr.z), bf16_hi(rr.z))); o67 = __fadd2_rn(o67, make_float2(bf16_lo(rr.w), bf16_hi(rr.w)));
+    }
+    float o[8] = {o01.x, o01.y, o23.x, o23.y, o45.x, o45.y, o67.x, o67.y};
+    if (ACT == HPE_ACT_SILU) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) o[e] = silu_fast(o[e]);
+    }
+    uint4 pk = make_uint4(pack_bf16(o[0], o[1]), pack_bf16(o[2], o[3]), pack_bf16(o[4], o[5]), pack_bf16(o[6], o[7]));
+    if (ACT == HPE_ACT_RELU) { pk.x = relu_bf16x2(pk.x); pk.y = relu_bf16x2(pk.y); pk.z = relu_bf16x2(pk.z); pk.w = relu_bf16x2(pk.w); }
+    sts_v4(slot, pk);
+  }
+}
+
 // ACT: HPE_ACT_*; RES: residual add; FINAL: fp32 NCHW heatmap epilogue (HPE_CONV_FINAL);
 // PAIR: cta_group::2 -- a 2-CTA cluster computes a 256 x BLOCK_N tile with ONE tcgen05.mma stream issued by the leader:
 // each CTA loads its own 128-pixel A brick and HALF of the weight tile, so a CTA ingests 32 KB instead of 48 KB per k-block
@@ -188,8 +224,18 @@ __device__ __forceinline__ float silu_fast(float x) {
 // the residual 1x1 layers: 8.2 k cycles per tile against 2 k of MMA with the schedulers 26 % busy -- every warp waited at the same
 // points).  The group leader waits for ALL of its bulk stores to have left shared memory at the top of a chunk (wait_group.read 0),
 // which makes 3 buffers per group enough for a residual lead of 2 chunks (2 buffers without a residual).
-template <int BLOCK_N, int STAGES, int ACT, bool RES, bool FINAL, bool PAIR = false, bool HEAD2 = false, bool EPI2 = false>
-__global__ void __launch_bounds__(EPI2 ? kConvThreads2 : kConvThreads, 1)
+// CHAIN = N2 (64 | 128; 256-wide single-CTA tiles of a 1x1 conv with Cout = 256): the NEXT layer's 1x1 conv (256 -> N2, folded BN,
+// same activation) runs on the output tile while it is staged for its own TMA store -- each 64-channel chunk the epilogue stages
+// is at once the source of the bulk store of y AND a K = 64 slice of the SWIZZLE_128B A operand of a second tcgen05 GEMM against the
+// resident [N2][256] weights, accumulated over the tile's four chunks into a separate TMEM accumulator and written as a second
+// bf16 NHWC tensor.  conv3 (+ shortcut + ReLU) of a Bottleneck and conv1 of the next one in one kernel: the 403 MB block output
+// of layer1 is written once and read once (as the next residual) instead of twice.  The main accumulator is single-buffered
+// (256 + N2 TMEM columns); with K = 64..128 its 4-8 MMAs are a small bubble in an HBM-bound tile.
+// KBR = the layer's k-blocks per tile (1 | 2, CHAIN only): its weight tile is loaded once and stays resident, the ring carries the A
+// bricks only, and the shared memory saved goes to a deeper chunk-buffer ring (the chained kernel was bound by the residual ring:
+// 4 buffers / (HBM latency + processing + drain) = one chunk per ~1.85 k cycles).
+template <int BLOCK_N, int STAGES, int ACT, bool RES, bool FINAL, bool PAIR = false, bool HEAD2 = false, bool EPI2 = false, int CHAIN = 0, int KBR = 0>
+__global__ void __launch_bounds__(CHAIN ? kConvThreadsC : (EPI2 ? kConvThreads2 : kConvThreads), 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
                  const __grid_constant__ CUtensorMap tmW, const __grid_constant__ OutMaps tmOut,
                  const __grid_constant__ CUtensorMap tmRes, const ConvParams p) {
@@ -200,13 +246,21 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   // residual the buffer of chunk q-1 is handed to the producer at the top of chunk q -> 3 buffers give a lead of 2.
   static_assert(!HEAD2 || (PAIR && BLOCK_N == 256 && !RES && !FINAL), "fused head: pair kernel, 256 channels, no residual");
   static_assert(!EPI2 || (!FINAL && !HEAD2), "two epilogue groups: bf16 NHWC TMA-store path only");
+  static_assert(!CHAIN || ((CHAIN == 64 || CHAIN == 128) && BLOCK_N == 256 && !PAIR && !HEAD2 && !EPI2 && !FINAL), "chained 1x1: single-CTA 256-wide tiles");
   constexpr int kGroups = EPI2 ? 2 : 1;
-  constexpr int kNumSB = FINAL ? 0 : (EPI2 ? (RES ? 3 : 2) : ((RES || HEAD2) ? 4 : 3));      // per group; the fp32 heatmap epilogue stores from registers: all smem to the ring
-  constexpr int kResLead = 2;                   // the residual of chunk q + 2 is requested while chunk q is processed
-  using L = SmemLayout<BLOCK_N, STAGES, PAIR, kGroups * kNumSB, HEAD2, EPI2>;
+  // per group; the fp32 heatmap epilogue stores from registers: all smem to the ring.  CHAIN = 128: its 64 KB of resident weights
+  // leave room for 3 buffers only (residual lead 1)
+  static_assert(!(CHAIN == 128 && !RES), "chained 128-wide conv: residual variant only (shared-memory budget)");
+  static_assert((KBR != 0) == (CHAIN != 0) && KBR <= 2, "resident weights: the chained kernels (1-2 k-blocks per tile)");
+  // CHAIN: one ring for both groups, as deep as fits (the residual rides it with a lead of kNumSB - 2 chunks)
+  constexpr int kNumSB = FINAL ? 0 : (CHAIN ? ((RES && CHAIN == 64) ? 6 : 4) : (EPI2 ? (RES ? 3 : 2) : ((RES || HEAD2) ? 4 : 3)));
+  constexpr int kResLead = 2;                     // the residual of chunk q + 2 is requested while chunk q is processed
+  constexpr int kLead = CHAIN ? kNumSB - 2 : kResLead;
+  constexpr int kChunks2 = CHAIN / 64;            // 64-column chunks of the chained conv's output
+  using L = SmemLayout<BLOCK_N, STAGES, PAIR, kGroups * kNumSB, HEAD2, EPI2, CHAIN, KBR>;
   static_assert(!PAIR || (BLOCK_N % 32 == 0 && !FINAL), "pair kernels: N multiple of 32, bf16 NHWC epilogue");
   constexpr int kChunks   = BLOCK_N >= 64 ? BLOCK_N / 64 : 1;
-  constexpr int kTmemCols = 2 * BLOCK_N <= 32 ? 32 : (2 * BLOCK_N <= 64 ? 64 : (2 * BLOCK_N <= 128 ? 128 : (2 * BLOCK_N <= 256 ? 256 : 512)));  // power of two
+  constexpr int kTmemCols = CHAIN ? 512 : 2 * BLOCK_N <= 32 ? 32 : (2 * BLOCK_N <= 64 ? 64 : (2 * BLOCK_N <= 128 ? 128 : (2 * BLOCK_N <= 256 ? 256 : 512)));  // power of two
   constexpr uint32_t kIdesc = PAIR ? make_idesc_bf16_m256(BLOCK_N) : make_idesc_bf16_m128(BLOCK_N);
   const int rank  = PAIR ? static_cast<int>(cluster_ctarank()) : 0;
   const int work0 = PAIR ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
@@ -227,10 +281,16 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint64_t* tempty_bar = bars + 2 * STAGES + 2;
   uint64_t* sbfull_bar = bars + 2 * STAGES + 4;
   uint64_t* sbempty_bar = bars + 2 * STAGES + 4 + kGroups * kNumSB;
-  uint64_t* w2full_bar = bars + 2 * STAGES + 4 + 2 * kGroups * kNumSB;       // fused head: joint weights landed (own CTA)
+  uint64_t* g2_bar     = bars + 2 * STAGES + 4 + 2 * kGroups * kNumSB;       // CHAIN: the second GEMM's MMAs on staging buffer b have completed
+  uint64_t* staged_bar = g2_bar + kGroups * kNumSB;                // CHAIN: chunk buffer b is staged (its group's leader, after the group barrier)
+  uint64_t* w2full_bar = staged_bar + kGroups * kNumSB;            // fused head / CHAIN: second-GEMM weights landed (own CTA)
   uint64_t* s2full_bar = w2full_bar + 1;                           // fused head: both CTAs staged their A' tile (leader's barrier)
-  uint64_t* d2full_bar = w2full_bar + 2;                           // fused head: second GEMM done (multicast commit)
+  uint64_t* d2full_bar = w2full_bar + 2;                           // fused head: second GEMM done (multicast commit); CHAIN: [2], per chained accumulator
+  uint64_t* a2empty_bar = w2full_bar + 4;                          // CHAIN: [2] chained accumulator drained
+  uint64_t* wres_bar   = w2full_bar + 6;                           // KBR: the resident weight tile has landed
   uint8_t*  sW2 = smem + L::kOffW2;
+  float*    sScale2 = reinterpret_cast<float*>(smem + L::kOffSS2);   // CHAIN
+  float*    sShift2 = sScale2 + 128;
   uint32_t* tmem_slot  = reinterpret_cast<uint32_t*>(bars + L::kNumBar);
 
   const int warp = threadIdx.x >> 5;
@@ -242,9 +302,13 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (RES) prefetch_tmap(&tmRes);
     // PAIR: the leader's full barrier collects both producers' arrivals, its tempty both CTAs' epilogue warps
     for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], PAIR ? 2 : 1); mbar_init(&empty_bar[s], 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], (PAIR ? 2 : 1) * kEpiThreads / 32); }
+    // CHAIN: both epilogue groups drain the one main accumulator
+    for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], (PAIR || CHAIN ? 2 : 1) * kEpiThreads / 32); }
     for (int b = 0; b < kGroups * kNumSB; ++b) { mbar_init(&sbfull_bar[b], 1); mbar_init(&sbempty_bar[b], 1); }
-    mbar_init(w2full_bar, 1); mbar_init(s2full_bar, 2); mbar_init(d2full_bar, 1);
+    for (int b = 0; b < kGroups * kNumSB; ++b) { mbar_init(&g2_bar[b], 1); mbar_init(&staged_bar[b], 1); }
+    mbar_init(w2full_bar, 1); mbar_init(s2full_bar, 2); mbar_init(d2full_bar, 1); mbar_init(d2full_bar + 1, 1);
+    mbar_init(&a2empty_bar[0], CHAIN ? 8 * kChunks2 : 1); mbar_init(&a2empty_bar[1], CHAIN ? 8 * kChunks2 : 1);
+    mbar_init(wres_bar, 1);
     fence_mbar_init();
   }
   if (warp == 1) {
@@ -269,6 +333,13 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // around each UTMALDG, an integer division and the tap switch) -- measured ~540 cycles per k-block with loads, MMAs and
     // epilogue all disabled, i.e. slower than the 512-cycle MMA work of a 128x256x64 block.
     int stage = 0; uint32_t phase = 0;
+    if constexpr (KBR != 0) {                     // the whole [BLOCK_N][64 KBR] weight tile, once
+      if (lane == 0) {
+        mbar_arrive_expect_tx(wres_bar, KBR * L::kBBytes);
+        for (int kb = 0; kb < KBR; ++kb) tma_load_2d(sB + kb * L::kBBytes, &tmW, wres_bar, kb * kKBlock, 0);
+      }
+      __syncwarp();
+    }
     for (int work = work0; work < p.num_tiles; work += wstep) {
       const TileCoord t = tile_coord(p, work_tile<PAIR>(p, work, rank));
       const int wrow = t.cls * p.Cout + t.n_tile * BLOCK_N + (PAIR ? rank * (BLOCK_N / 2) : 0);
@@ -291,6 +362,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           if (rank == 0) mbar_arrive_expect_tx_elect(fb, 2 * L::kStageBytes);
           else           mbar_arrive_cluster_elect(full0);
           tma_load_ab_2sm_elect(full0, dA, mA, c0, cx, cy, t.b0, dB, &tmW, kb * kKBlock, wrow);
+        } else if constexpr (KBR != 0) {
+          mbar_arrive_expect_tx_elect(fb, kABytes);
+          tma_load_4d_elect(dA, mA, fb, c0, cx, cy, t.b0);
         } else {
           tma_load_ab_elect(fb, L::kStageBytes, dA, mA, c0, cx, cy, t.b0, dB, &tmW, kb * kKBlock, wrow);
         }
@@ -305,9 +379,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (rank == 0) {
       constexpr uint32_t kDescHi = (1024u >> 4) | (1u << 14) | (2u << 29);     // SBO = 1024 B, version 1, SWIZZLE_128B
       int stage = 0; uint32_t phase = 0; int it = 0;
+      if constexpr (KBR != 0) mbar_wait(wres_bar, 0);
       for (int work = work0; work < p.num_tiles; work += wstep, ++it) {
-        const int acc = it & 1;
-        mbar_wait(&tempty_bar[acc], ((it >> 1) & 1) ^ 1);
+        const int acc = CHAIN ? 0 : (it & 1);     // CHAIN: one main accumulator (columns 256.. hold the chained conv's)
+        mbar_wait(&tempty_bar[acc], (CHAIN ? (it & 1) : ((it >> 1) & 1)) ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
         const int num_kb = kb_count(p, tile_coord(p, work_tile<PAIR>(p, work, 0)).cls);
@@ -315,7 +390,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           const uint32_t a_lo = ((smem_u32(sA + stage * kABytes) & 0x3FFFFu) >> 4) | (1u << 16);
-          const uint32_t b_lo = ((smem_u32(sB + stage * L::kBBytes) & 0x3FFFFu) >> 4) | (1u << 16);
+          const uint32_t b_lo = ((smem_u32(sB + (KBR ? kb : stage) * L::kBBytes) & 0x3FFFFu) >> 4) | (1u << 16);
 #pragma unroll
           for (int k = 0; k < kKBlock / 16; ++k) {    // UMMA_K = 16 bf16 = 32 B -> +2 in the (addr>>4) field
             if constexpr (PAIR) umma_bf16_2sm_elect_lo(tmem_d, a_lo + 2 * k, kDescHi, b_lo + 2 * k, kDescHi, kIdesc, (kb | k) != 0);
@@ -334,6 +409,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (HEAD2 && lane == 0) {        // fused head: this CTA's 16 joint-weight rows (4 k-blocks of 16 x 128 B), loaded once
       mbar_arrive_expect_tx(w2full_bar, L::kW2Bytes);
       for (int kb = 0; kb < 4; ++kb) tma_load_2d(sW2 + kb * 2048, &tmRes, w2full_bar, kb * kKBlock, rank * 16);
+    }
+    if (CHAIN && lane == 0) {        // chained 1x1: [N2 rows][256 K] as 4 k-blocks of N2 x 128 B, loaded once (map in tmOut.m[2])
+      mbar_arrive_expect_tx(w2full_bar, L::kW2Bytes);
+      for (int kb = 0; kb < 4; ++kb) tma_load_2d(sW2 + kb * (CHAIN * 128), &tmOut.m[2], w2full_bar, kb * kKBlock, 0);
     }
     if (RES && lane == 0) {
       if constexpr (EPI2) {
@@ -362,14 +441,100 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         int r = 0;
         for (int work = work0; work < p.num_tiles; work += wstep) {
           const TileCoord t = tile_coord(p, work_tile<PAIR>(p, work, rank));
-          for (int c = 0; c < kChunks; ++c, ++r) {
+          for (int c = 0; c < kChunks + kChunks2; ++c, ++r) {
             const int b = r % kNumSB;
             mbar_wait(&sbempty_bar[b], (r / kNumSB) & 1);   // the epilogue leader hands buffers over with a lead of kResLead chunks
+            if (c >= kChunks) { mbar_arrive(&sbfull_bar[b]); continue; }     // CHAIN: the chained conv's output chunk has no residual
             mbar_arrive_expect_tx(&sbfull_bar[b], kSBBytes);
             tma_load_4d(sSB + b * kSBBytes, &tmRes, &sbfull_bar[b], t.n_tile * BLOCK_N + c * 64, t.x0, t.y0, t.b0);
           }
         }
       }
+    }
+  } else if (CHAIN != 0 && warp == 3) {
+    // ===================== CHAIN: issuer of the second GEMM =====================
+    // One thread issues every chunk's K = 64 slice in chunk order (so the accumulation order over the 256 input channels is
+    // the separate conv1 launch's), as soon as the chunk's group has staged it.
+    if constexpr (CHAIN != 0) {
+      if (lane == 0) {
+        constexpr int kCPT = kChunks + kChunks2;                 // chunks per tile: 4 of y, then 1-2 of the chained output
+        constexpr uint32_t kIdesc2 = make_idesc_bf16_m128(CHAIN);
+        mbar_wait(w2full_bar, 0);
+        int q = 0, it = 0;
+        for (int work = work0; work < p.num_tiles; work += wstep, ++it) {
+          const int a2 = it & 1;
+          mbar_wait(&a2empty_bar[a2], ((it >> 1) & 1) ^ 1);      // tile it-2's chained output has left accumulator a2
+          for (int c = 0; c < kCPT; ++c, ++q) {
+            const int sb = q % kNumSB;
+            mbar_wait(&staged_bar[sb], (q / kNumSB) & 1);
+            if (c < kChunks) {
+              tc_fence_after();
+              const uint64_t adesc = make_sw128_kmajor_desc(sSB + sb * kSBBytes);
+              const uint64_t bdesc = make_sw128_kmajor_desc(sW2 + c * (CHAIN * 128));
+#pragma unroll
+              for (int k = 0; k < 4; ++k) umma_bf16(tmem_base + BLOCK_N + a2 * CHAIN, adesc + 2 * k, bdesc + 2 * k, kIdesc2, (c | k) != 0);
+            }
+            umma_commit(&g2_bar[sb]);                            // every chunk commits: a buffer's phase sequence stays uniform
+            if (c == kChunks - 1) umma_commit(&d2full_bar[a2]);
+          }
+        }
+      }
+    }
+  } else if (CHAIN != 0) {
+    // ===================== CHAIN: two epilogue groups, chunk-interleaved =====================
+    // Chunk q = it * kCPT + c of this CTA's chunk sequence goes to group q & 1 (warps 4-11 / 12-19): both groups drain the SAME
+    // tile, so two tcgen05.ld -> residual wait -> math -> fence -> barrier -> store chains are in flight (a single group ran the
+    // chained kernel at 11.6 k cycles per tile against ~7.9 k of HBM time).  The buffers form ONE ring in chunk order; with an
+    // even buffer count, or the residual hand-over two chunks back, a buffer is always recycled by the group that stored it.
+    if constexpr (CHAIN != 0) {
+      constexpr int kCPT = kChunks + kChunks2;
+      const int grp = (warp - 4) >> 3, ew = warp & 3, half = ((warp - 4) >> 2) & 1, row = ew * 32 + lane;
+      const int atid = threadIdx.x - 128, etid = atid - grp * kEpiThreads;
+      const bool leader = etid == 0;
+      const uint32_t bar_id = 1 + grp;
+      if (atid < BLOCK_N) { sScale[atid] = atid < p.Cout ? __ldg(p.scale + atid) : 0.f; sShift[atid] = atid < p.Cout ? __ldg(p.shift + atid) : 0.f; }
+      else if (atid < BLOCK_N + CHAIN) { sScale2[atid - BLOCK_N] = __ldg(p.scale2 + atid - BLOCK_N); sShift2[atid - BLOCK_N] = __ldg(p.shift2 + atid - BLOCK_N); }
+      named_bar_sync(3, 2 * kEpiThreads);
+      if (RES && atid == 0) for (int b = 0; b < kLead; ++b) mbar_arrive(&sbempty_bar[b]);
+      const uint32_t taddr0 = tmem_base + (static_cast<uint32_t>(ew * 32) << 16);
+      int it_cur = -1;
+      TileCoord t = {};
+      for (int q = grp; ; q += 2) {
+        const int it = q / kCPT, c = q - it * kCPT;
+        const int work = work0 + it * wstep;
+        if (work >= p.num_tiles) break;
+        if (it != it_cur) { t = tile_coord(p, work); it_cur = it; }
+        const bool e2 = c >= kChunks;
+        const int sb = q % kNumSB, a2 = it & 1;
+        if (leader) {
+          bulk_wait_read<0>();                                   // this group's stores (chunks q-2, q-4, ...) have left shared memory
+          if (q >= 2) mbar_wait(&g2_bar[(q - 2) % kNumSB], ((q - 2) / kNumSB) & 1);     // ... and the second GEMM has read chunk q-2
+          if (RES) mbar_arrive(&sbempty_bar[(q + kLead) % kNumSB]);                     // = chunk q-2's buffer: to the residual producer
+        }
+        if (e2) mbar_wait(&d2full_bar[a2], (it >> 1) & 1); else mbar_wait(&tfull_bar[0], it & 1);
+        tc_fence_after();
+        uint32_t v[32];
+        tmem_ld_x32(e2 ? taddr0 + BLOCK_N + a2 * CHAIN + (c - kChunks) * 64 + half * 32 : taddr0 + c * 64 + half * 32, v);
+        if (RES) mbar_wait(&sbfull_bar[sb], (q / kNumSB) & 1);
+        tmem_ld_wait();
+        if (e2 || c + 2 >= kChunks) {                            // this group's last read of the main / of the chained accumulator
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(e2 ? &a2empty_bar[a2] : &tempty_bar[0]);
+        }
+        const int n0 = (e2 ? c - kChunks : c) * 64 + half * 32;
+        epi_chunk_math<ACT>(v, smem_u32((e2 ? sScale2 : sScale) + n0), smem_u32((e2 ? sShift2 : sShift) + n0),
+                            smem_u32(sSB + sb * kSBBytes) + row * 128, half, row, RES && !e2);
+        fence_proxy_async_smem();                                // generic-proxy writes -> visible to TMA and to the tensor core
+        named_bar_sync(bar_id, kEpiThreads);
+        if (leader) {
+          if (e2) tma_store_4d(&tmOut.m[1], sSB + sb * kSBBytes, (c - kChunks) * 64, t.x0, t.y0, t.b0);
+          else    tma_store_4d(&tmOut.m[0], sSB + sb * kSBBytes, c * 64, t.x0, t.y0, t.b0);
+          bulk_commit();
+          mbar_arrive(&staged_bar[sb]);
+        }
+      }
+      if (leader) bulk_wait_all();
     }
   } else {
     // ===================== epilogue (8 warps per group: TMEM lane quarter = warp & 3, column half = ((warp - 3) >> 2) & 1) ====
@@ -383,7 +548,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     sSB += grp * kNumSB * kSBBytes; sbfull_bar += grp * kNumSB; sbempty_bar += grp * kNumSB;
     sScale += grp * 2 * kMaxBlockN; sShift += grp * 2 * kMaxBlockN;
     const uint32_t bar_id = 1 + grp;
-    if (RES && leader) for (int b = 0; b < kResLead; ++b) mbar_arrive(&sbempty_bar[b]);
+    if (RES && leader) for (int b = 0; b < kLead; ++b) mbar_arrive(&sbempty_bar[b]);
     int q = 0, staged_n = -1;
     for (int work = work0 + grp * wstep, it = grp; work < p.num_tiles; work += kGroups * wstep, it += kGroups) {
       const TileCoord t = tile_coord(p, work_tile<PAIR>(p, work, rank));
@@ -434,7 +599,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const uint32_t stg = smem_u32(sSB + sb * kSBBytes);
           if (!HEAD2 && leader) {
             bulk_wait_read<EPI2 ? 0 : 1>();                         // stores <= q-2 (EPI2: <= q-1) have left shared memory
-            if (RES) mbar_arrive(&sbempty_bar[(q + kResLead) % kNumSB]);   // hand the buffer of chunk q+2 to warp 2
+            if (RES) mbar_arrive(&sbempty_bar[(q + kLead) % kNumSB]);   // hand the buffer of chunk q + lead to warp 2
           }
           uint32_t v[32];
           tmem_ld_x32(taddr + c * 64 + half * 32, v);
@@ -679,7 +844,7 @@ struct hpe_conv_plan {
   CUtensorMap tmA, tmW, tmRes;
   OutMaps tmOut;
   const void *x, *x2, *w, *res, *w2;
-  void* y;
+  void *y, *y2;                       // y2: CHAIN, the chained conv's output
   CUtensorMap tmA2;
   const void* fn;
   int epi2;                           // two epilogue groups (608-thread kernel)
@@ -724,6 +889,11 @@ static int desc_check(const hpe_conv_desc* d, const char* fn) {
     const bool kind_ok = d->kind == HPE_CONV_DECONV4 || ((d->kind == HPE_CONV_1x1 || d->kind == HPE_CONV_3x3) && d->stride == 1);
     if (!kind_ok || d->Cout != 256 || d->has_residual || d->out_cstride || d->Cin2 || d->act != HPE_ACT_RELU)
       return fail(HPE_EUNSUPPORTED, "%s: the fused head needs a ReLU deconv / stride-1 conv with Cout = 256, no residual, no second input", fn);
+  }
+  if (d->chain) {
+    if ((d->chain != 64 && d->chain != 128) || d->kind != HPE_CONV_1x1 || d->stride != 1 || d->Cout != 256 || d->head2 || d->out_cstride ||
+        d->act != HPE_ACT_RELU)
+      return fail(HPE_EUNSUPPORTED, "%s: a chained 1x1 conv (64 or 128 outputs) needs a dense ReLU 1x1 stride-1 layer with Cout = 256", fn);
   }
   if (d->Cin2) {
     if (d->kind != HPE_CONV_1x1 || d->stride != 1) return fail(HPE_EUNSUPPORTED, "%s: a second input needs a 1x1 stride-1 main conv", fn);
@@ -942,7 +1112,7 @@ extern "C" int hpe_conv_dgrad_desc(const hpe_conv_desc* f, hpe_conv_desc* g) {
   if (rc) return rc;
   *g = *f;
   g->H = Ho; g->W = Wo; g->Cin = f->Cout; g->Cout = f->Cin; g->stride = 1; g->act = HPE_ACT_NONE; g->has_residual = 0;
-  g->Cin2 = 0; g->stride2 = 0; g->head2 = 0; g->pool = 0;
+  g->Cin2 = 0; g->stride2 = 0; g->head2 = 0; g->pool = 0; g->chain = 0;
   if (f->Cin2) return fail(HPE_EUNSUPPORTED, "hpe_conv_dgrad_desc: fused two-input layers are inference-only");
   switch (f->kind) {
     case HPE_CONV_1x1:     g->kind = f->stride == 2 ? HPE_CONV_DGRAD1x1S2 : HPE_CONV_1x1; break;
@@ -1004,6 +1174,26 @@ static ConvKernelFn pick_kernel_epi2(int act, size_t* smem) {
     case HPE_ACT_GELU: return nullptr;
     default:           return conv_gemm_kernel<256, 3, HPE_ACT_NONE, true, false, true, false, true>;
   }
+}
+
+// chained 1x1 (N2 = 64 | 128) behind a 256-wide single-CTA ReLU tile: 2 ring stages of 48 KB, 4 (N2 = 128 with a residual: 3)
+// staging buffers, the chained weights resident
+static ConvKernelFn pick_kernel_chain(int n2, bool res, int num_kb, size_t* smem) {
+  // (N2, residual, k-blocks per tile) of the three layer1 cases: conv3 (K = 64) + identity shortcut -> conv1 64 | 128, and the
+  // first block's two-source conv3 (K = 64 + 64, projection shortcut folded in) -> conv1 64
+  if (n2 == 64 && res && num_kb == 1) {
+    *smem = SmemLayout<256, 3, false, 6, false, false, 64, 1>::kDynamic;
+    return conv_gemm_kernel<256, 3, HPE_ACT_RELU, true, false, false, false, false, 64, 1>;
+  }
+  if (n2 == 128 && res && num_kb == 1) {
+    *smem = SmemLayout<256, 3, false, 4, false, false, 128, 1>::kDynamic;
+    return conv_gemm_kernel<256, 3, HPE_ACT_RELU, true, false, false, false, false, 128, 1>;
+  }
+  if (n2 == 64 && !res && num_kb == 2) {
+    *smem = SmemLayout<256, 3, false, 4, false, false, 64, 2>::kDynamic;
+    return conv_gemm_kernel<256, 3, HPE_ACT_RELU, false, false, false, false, false, 64, 2>;
+  }
+  return nullptr;
 }
 
 // ring depths: as many stages as fit beside the staging buffers in the 227 KB a CTA may use
@@ -1072,8 +1262,9 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
     const char* e128 = getenv("HPE_B200_PAIR128");
     const char* e192 = getenv("HPE_B200_PAIR192");
     const long long m_tiles = (long long)p.tiles_x * p.tiles_y * p.tiles_b;
-    pl->pair = !(e && e[0] == '0') && (pl->block_n == 256 || (pl->block_n == 192 && !(e192 && e192[0] == '0')) || (pl->block_n == 128 && e128 && e128[0] == '1')) && d->kind != HPE_CONV_FINAL && m_tiles >= 2 && !halo_eligible(d, pl->Ho, pl->Wo);
-    if (d->head2 && !pl->pair) { delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: the fused head runs on the cta_group::2 kernel only (needs >= 2 M tiles, HPE_B200_PAIR != 0)"); }
+    pl->pair = !d->chain && !(e && e[0] == '0') && (pl->block_n == 256 || (pl->block_n == 192 && !(e192 && e192[0] == '0')) || (pl->block_n == 128 && e128 && e128[0] == '1')) && d->kind != HPE_CONV_FINAL && m_tiles >= 2 && !halo_eligible(d, pl->Ho, pl->Wo);
+    if (d->chain && halo_eligible(d, pl->Ho, pl->Wo)) { delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: chained layer on the halo kernel"); }
+  if (d->head2 && !pl->pair) { delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: the fused head runs on the cta_group::2 kernel only (needs >= 2 M tiles, HPE_B200_PAIR != 0)"); }
     if (pl->pair) {
       const long long np = (m_tiles + 1) / 2 * p.n_tiles_n * p.n_classes;
       p.num_tiles = (int)np;
@@ -1090,8 +1281,9 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
     const int num_kb = p.taps * p.kc_per_tap + p.kc2;
     pl->epi2 = mode != 0 && pl->pair && pl->block_n == 256 && p.has_res && !d->head2 && d->act != HPE_ACT_GELU && (mode == 2 || num_kb <= 8);
   }
-  pl->fn = (const void*)pick_kernel(pl->block_n, d->act, p.has_res != 0, d->kind == HPE_CONV_FINAL, pl->pair != 0, d->head2 != 0, pl->epi2 != 0, &pl->smem);
-  if (!pl->fn) { delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: no kernel for BLOCK_N=%d", pl->block_n); }
+  pl->fn = d->chain ? (const void*)pick_kernel_chain(d->chain, p.has_res != 0, p.taps * p.kc_per_tap + p.kc2, &pl->smem)
+                    : (const void*)pick_kernel(pl->block_n, d->act, p.has_res != 0, d->kind == HPE_CONV_FINAL, pl->pair != 0, d->head2 != 0, pl->epi2 != 0, &pl->smem);
+  if (!pl->fn) { const int bn = pl->block_n; delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: no kernel for BLOCK_N=%d%s", bn, d->chain ? " (chained layers: Cin = 64 with a residual, or Cin = Cin2 = 64 without)" : ""); }
   {
     cudaError_t e = cudaFuncSetAttribute((const void*)pl->fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem);
     if (e != cudaSuccess) { delete pl; return fail(HPE_ECUDA, "cudaFuncSetAttribute(smem=%zu) failed: %s", pl->smem, cudaGetErrorString(e)); }
@@ -1117,7 +1309,7 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
     }
     pl->grid = 2 * (p.num_tiles < max_clusters ? p.num_tiles : max_clusters);
   }
-  pl->x = pl->x2 = pl->w = pl->res = pl->w2 = nullptr; pl->y = nullptr;
+  pl->x = pl->x2 = pl->w = pl->res = pl->w2 = nullptr; pl->y = pl->y2 = nullptr;
   pl->halo_taps_y = 0;
   if (halo_eligible(d, pl->Ho, pl->Wo)) {
     // 8-wide x 32-tall bricks; the 3x3 reads ONE 10-pixel-wide halo'd box per brick whose column taps are 128-byte shifts of
@@ -1146,7 +1338,7 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
 extern "C" void hpe_conv_plan_destroy(hpe_conv_plan* plan) { delete plan; }
 
 static int encode_plan_maps(hpe_conv_plan* pl, const void* x, const void* x2, const void* w, const void* res, void* y,
-                            const void* w2 = nullptr) {
+                            const void* w2 = nullptr, void* y2 = nullptr) {
   const hpe_conv_desc& d = pl->d;
   const ConvParams& p = pl->p;
   int rc;
@@ -1224,9 +1416,29 @@ static int encode_plan_maps(hpe_conv_plan* pl, const void* x, const void* x2, co
       const uint64_t str[3] = {P * 2, (uint64_t)pl->Wo * P * 2, (uint64_t)pl->Ho * pl->Wo * P * 2};
       rc = encode_map(&pl->tmOut.m[0], y, 4, dims, str, box, ones, "out");
       if (rc) return rc;
-      pl->tmOut.m[1] = pl->tmOut.m[2] = pl->tmOut.m[3] = pl->tmOut.m[0];
+      if (d.chain) pl->tmOut.m[3] = pl->tmOut.m[0];             // m[1], m[2]: the chained conv's output / weights
+      else pl->tmOut.m[1] = pl->tmOut.m[2] = pl->tmOut.m[3] = pl->tmOut.m[0];
     }
     pl->y = y;
+  }
+  if (d.chain && (w2 != pl->w2 || y2 != pl->y2)) {       // chained 1x1: weights [N2][256] -> tmOut.m[2], dense output [B,Ho,Wo,N2] -> tmOut.m[1]
+    HPE_CHECK_ARG(w2 && y2 && (((uintptr_t)w2 | (uintptr_t)y2) & 15) == 0, "hpe_conv_run_chain: w2 / y2 must be non-null and 16-byte aligned");
+    {
+      const uint64_t dims[2] = {256, (uint64_t)d.chain};
+      const uint64_t str[1] = {256 * 2};
+      const uint32_t box[2] = {64, (uint32_t)d.chain};
+      rc = encode_map(&pl->tmOut.m[2], w2, 2, dims, str, box, ones, "chain W");
+      if (rc) return rc;
+    }
+    {
+      const uint64_t C = d.chain;
+      const uint64_t dims[4] = {C, (uint64_t)pl->Wo, (uint64_t)pl->Ho, (uint64_t)d.B};
+      const uint64_t str[3] = {C * 2, (uint64_t)pl->Wo * C * 2, (uint64_t)pl->Ho * pl->Wo * C * 2};
+      const uint32_t box[4] = {64, (uint32_t)p.tw, (uint32_t)p.th, (uint32_t)p.nb};
+      rc = encode_map(&pl->tmOut.m[1], y2, 4, dims, str, box, ones, "chain out");
+      if (rc) return rc;
+    }
+    pl->w2 = w2; pl->y2 = y2;
   }
   if (p.has_res && res != pl->res) {
     HPE_CHECK_ARG(res && ((uintptr_t)res & 15) == 0, "hpe_conv_run: residual must be non-null and 16-byte aligned");
@@ -1249,10 +1461,23 @@ extern "C" int hpe_conv_run(hpe_conv_plan* pl, const void* x, const void* w_pack
 static int conv_launch(hpe_conv_plan* pl, const void* x, const void* x2, const void* w_packed, const float* scale,
                        const float* shift, const void* residual, void* y, const void* w2, const float* bias2, void* stream);
 
+static int conv_launch(hpe_conv_plan* pl, const void* x, const void* x2, const void* w_packed, const float* scale,
+                       const float* shift, const void* residual, void* y, const void* w2, const float* bias2, void* stream,
+                       const float* scale2, const float* shift2, void* y2);
+
 extern "C" int hpe_conv_run2(hpe_conv_plan* pl, const void* x, const void* x2, const void* w_packed, const float* scale,
                              const float* shift, const void* residual, void* y, void* stream) {
   HPE_CHECK_ARG(pl && !pl->d.head2, "hpe_conv_run: the plan has a fused head; use hpe_conv_run_head2");
+  HPE_CHECK_ARG(!pl->d.chain, "hpe_conv_run: the plan has a chained 1x1 conv; use hpe_conv_run_chain");
   return conv_launch(pl, x, x2, w_packed, scale, shift, residual, y, nullptr, nullptr, stream);
+}
+
+extern "C" int hpe_conv_run_chain(hpe_conv_plan* pl, const void* x, const void* x2, const void* w_packed, const float* scale,
+                                  const float* shift, const void* residual, void* y, const void* w2_packed, const float* scale2,
+                                  const float* shift2, void* y2, void* stream) {
+  HPE_CHECK_ARG(pl && pl->d.chain, "hpe_conv_run_chain: the plan has no chained conv (desc.chain = 0)");
+  HPE_CHECK_ARG(w2_packed && scale2 && shift2 && y2, "hpe_conv_run_chain: null pointer");
+  return conv_launch(pl, x, x2, w_packed, scale, shift, residual, y, w2_packed, nullptr, stream, scale2, shift2, y2);
 }
 
 extern "C" int hpe_conv_run_head2(hpe_conv_plan* pl, const void* x, const void* w_packed, const float* scale, const float* shift,
@@ -1264,6 +1489,12 @@ extern "C" int hpe_conv_run_head2(hpe_conv_plan* pl, const void* x, const void* 
 
 static int conv_launch(hpe_conv_plan* pl, const void* x, const void* x2, const void* w_packed, const float* scale,
                        const float* shift, const void* residual, void* y, const void* w2, const float* bias2, void* stream) {
+  return conv_launch(pl, x, x2, w_packed, scale, shift, residual, y, w2, bias2, stream, nullptr, nullptr, nullptr);
+}
+
+static int conv_launch(hpe_conv_plan* pl, const void* x, const void* x2, const void* w_packed, const float* scale,
+                       const float* shift, const void* residual, void* y, const void* w2, const float* bias2, void* stream,
+                       const float* scale2, const float* shift2, void* y2) {
   HPE_CHECK_ARG(pl && x && w_packed && scale && shift && y, "hpe_conv_run: null pointer");
   HPE_CHECK_ARG((pl->d.Cin2 != 0) == (x2 != nullptr), "hpe_conv_run2: x2 must be given exactly when the plan has a second input (Cin2=%d)", pl->d.Cin2);
   HPE_CHECK_ARG((((uintptr_t)scale | (uintptr_t)shift) & 15) == 0, "hpe_conv_run: scale/shift must be 16-byte aligned");
@@ -1271,7 +1502,7 @@ static int conv_launch(hpe_conv_plan* pl, const void* x, const void* x2, const v
     return fail(HPE_EUNSUPPORTED, "hpe_conv_run: the strided-store kinds have no residual input");
   if (pl->d.kind == HPE_CONV_DGRAD1x1S2)      // odd rows/columns of dx receive no gradient
     HPE_CUDA_OK(cudaMemsetAsync(y, 0, (size_t)pl->d.B * pl->Ho * pl->Wo * pl->d.Cout * 2, (cudaStream_t)stream));
-  int rc = encode_plan_maps(pl, x, x2, w_packed, residual, y, w2);
+  int rc = encode_plan_maps(pl, x, x2, w_packed, residual, y, w2, y2);
   if (rc) return rc;
   if (pl->halo_taps_y) {
     pl->hp.scale = scale; pl->hp.shift = shift; pl->hp.out = y;
@@ -1281,12 +1512,13 @@ static int conv_launch(hpe_conv_plan* pl, const void* x, const void* x2, const v
   p.scale = scale; p.shift = shift;
   p.hm_out = (pl->d.kind == HPE_CONV_FINAL || pl->d.head2) ? (float*)y : nullptr;
   p.bias2 = bias2;
+  p.scale2 = scale2; p.shift2 = shift2;
   if (!p.has_res && !pl->d.head2) pl->tmRes = pl->tmA;      // unused, but must be a valid object to copy
   if (pl->d.kind == HPE_CONV_FINAL || pl->d.head2) for (int c = 0; c < 4; ++c) pl->tmOut.m[c] = pl->tmA;
   if (!pl->d.Cin2) pl->tmA2 = pl->tmA;      // unused, but must be a valid object to copy
   void* args[6] = {&pl->tmA, &pl->tmA2, &pl->tmW, &pl->tmOut, &pl->tmRes, &p};
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(pl->grid); cfg.blockDim = dim3(pl->epi2 ? kConvThreads2 : kConvThreads);
+  cfg.gridDim = dim3(pl->grid); cfg.blockDim = dim3(pl->d.chain ? kConvThreadsC : (pl->epi2 ? kConvThreads2 : kConvThreads));
   cfg.dynamicSmemBytes = pl->smem; cfg.stream = (cudaStream_t)stream;
   cudaLaunchAttribute attr[2];
   int na = 0;

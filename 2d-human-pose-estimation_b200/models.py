@@ -243,7 +243,7 @@ class _ForwardPlan:
         if H % 32 or W % 32:
             raise ValueError(f"input {H}x{W} must be a multiple of 32")
         self.B, self.H, self.W, self.device = B, H, W, device
-        self.ops = []            # (layer, src_key, res_key, dst_key, src2_key), one per conv layer, in launch order
+        self.ops = []            # (layer, src_key, res_key, dst_key, src2_key, dst2_key), one per conv launch, in launch order
         # DEPTH-FIRST SECTION (experiment, OFF by default: HPE_B200_DF_CHUNK images per pass, HPE_B200_DF_STAGES ResNet stages).
         # Idea: the stem and the first stages move 403 MB tensors at B=256, but a chunk of 32 images keeps a bottleneck's working
         # set inside the 126 MB L2, so the section's layers are planned for `chunk` images with chunk-sized buffers that every pass
@@ -266,6 +266,11 @@ class _ForwardPlan:
         # cost 4 x 512 MMA cycles and 64 KB of weight traffic per tile): forward 3.34 -> 3.77 ms.
         res_mma = os.environ.get("HPE_B200_RES_MMA", "0") != "0"
         self.identity_shortcut = set()
+        # conv3 (+ shortcut + ReLU) of a layer1 Bottleneck and conv1 (+ BN + ReLU) of the NEXT block in one kernel (desc.chain): the
+        # 256-channel block output is read once (as the next shortcut) instead of twice, and one launch per block disappears
+        fuse_chain = os.environ.get("HPE_B200_FUSE_CHAIN", "1") != "0"
+        self.chained = {}        # conv1 path -> the conv3 path whose kernel computes it
+        pending_chain = None     # (conv3 name, t1 buffer key) while the next block's conv1 is still to be declared
         self.bufs = {}
         self.named = {}          # module path -> ConvLayer (for load_weights)
         K = model.njoints
@@ -275,14 +280,16 @@ class _ForwardPlan:
             self.bufs[key] = torch.empty(shape, dtype=dtype, device=dev)
             return key
 
-        def add(name, layer, src, dst, res=None, src2=None, full_out=False):
+        def add(name, layer, src, dst, res=None, src2=None, full_out=False, dst2=None):
             self.named[name] = layer
             shape = layer.out_shape()
             if full_out:                    # last layer of the depth-first section: writes its batch slice of a full tensor
                 shape = (Bf,) + tuple(shape[1:])
                 self.full_keys.add(dst)
             buf(dst, shape, torch.float32 if (layer.kind == CONV_FINAL or layer.head2) else torch.bfloat16)
-            self.ops.append((layer, src, res, dst, src2))
+            if dst2:
+                buf(dst2, (layer.B, layer.Ho, layer.Wo, layer.chain))
+            self.ops.append((layer, src, res, dst, src2, dst2))
 
         self.s2d = preprocess(torch.zeros(B, 3, H, W, device=dev))
         Bf = B                              # full batch
@@ -310,24 +317,34 @@ class _ForwardPlan:
                 last_of_section = self.df_stages > 0 and i == self.df_stages - 1 and j == n - 1
                 s = 2 if (i > 0 and j == 0) else 1
                 pre = f"backbone.layer{i + 1}.{j}"
-                add(pre + ".conv1", ConvLayer(CONV_1x1, B, h, w, cin, p, 1, ACT_RELU, False, dev), cur, pre + ".t1")
+                if pending_chain is not None:         # conv1 runs inside the previous block's conv3 kernel, which writes .t1
+                    self.chained[pre + ".conv1"] = pending_chain
+                    pending_chain = None
+                else:
+                    add(pre + ".conv1", ConvLayer(CONV_1x1, B, h, w, cin, p, 1, ACT_RELU, False, dev), cur, pre + ".t1")
                 add(pre + ".conv2", ConvLayer(CONV_3x3, B, h, w, p, p, s, ACT_RELU, False, dev), pre + ".t1", pre + ".t2")
                 sc = cur
+                # chain the next block's conv1 (256 -> 64 | 128) behind this conv3 when the block output has 256 channels (layer1)
+                nxt = (f"backbone.layer{i + 1}.{j + 1}", p) if j + 1 < n else ((f"backbone.layer{i + 2}.0", _PLANES[i + 1]) if i + 1 < 4 else None)
+                n2 = nxt[1] if (fuse_chain and nxt and 4 * p == 256 and nxt[1] in (64, 128) and not res_mma and self.df_stages == 0) else 0
+                d2 = nxt[0] + ".t1" if n2 else None
                 if j == 0 and not fuse_sc:
                     add(pre + ".downsample.0", ConvLayer(CONV_1x1, B, h, w, cin, 4 * p, s, ACT_NONE, False, dev), cur, pre + ".sc")
                     sc = pre + ".sc"
                 h, w = h // s, w // s
                 if j == 0 and fuse_sc:
                     self.fused_shortcut[pre + ".conv3"] = pre + ".downsample"
-                    add(pre + ".conv3", ConvLayer(CONV_1x1, B, h, w, p, 4 * p, 1, ACT_RELU, False, dev, Cin2=cin, stride2=s),
-                        pre + ".t2", pre + ".out", None, cur, full_out=last_of_section)
+                    add(pre + ".conv3", ConvLayer(CONV_1x1, B, h, w, p, 4 * p, 1, ACT_RELU, False, dev, Cin2=cin, stride2=s, chain=n2),
+                        pre + ".t2", pre + ".out", None, cur, full_out=last_of_section, dst2=d2)
                 elif res_mma:
                     self.identity_shortcut.add(pre + ".conv3")
                     add(pre + ".conv3", ConvLayer(CONV_1x1, B, h, w, p, 4 * p, 1, ACT_RELU, False, dev, Cin2=4 * p, stride2=1),
                         pre + ".t2", pre + ".out", None, sc, full_out=last_of_section)
                 else:
-                    add(pre + ".conv3", ConvLayer(CONV_1x1, B, h, w, p, 4 * p, 1, ACT_RELU, True, dev), pre + ".t2", pre + ".out", sc,
-                        full_out=last_of_section)
+                    add(pre + ".conv3", ConvLayer(CONV_1x1, B, h, w, p, 4 * p, 1, ACT_RELU, True, dev, chain=n2), pre + ".t2", pre + ".out", sc,
+                        full_out=last_of_section, dst2=d2)
+                if n2:
+                    pending_chain = pre + ".conv3"
                 cur, cin = pre + ".out", 4 * p
         self.features_key = cur
         # last deconv stage + final_layer in one kernel (the 256-channel deconv3 output never leaves shared memory) when the
@@ -379,6 +396,10 @@ class _ForwardPlan:
             else:
                 bn = mods[name.replace("conv", "bn")]
             scale, shift = fold_bn(bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.eps)
+            if layer.chain:
+                c1 = next(k for k, v in self.chained.items() if v == name)
+                bn1 = mods[c1.replace("conv", "bn")]
+                layer.load_chain(mods[c1].weight, *fold_bn(bn1.weight, bn1.bias, bn1.running_mean, bn1.running_var, bn1.eps))
             if name == self.fused_head:
                 layer.load_head2(mods["final_layer"].weight, mods["final_layer"].bias)
             if name in self.identity_shortcut:
@@ -403,10 +424,10 @@ class _ForwardPlan:
         return t[c * self.chunk:(c + 1) * self.chunk] if key in self.full_keys else t
 
     def _launch_op(self, op, c=None):
-        layer, src, res, dst, src2 = op
+        layer, src, res, dst, src2, dst2 = op
         if c is None:
             b = self.bufs
-            layer(b[src], b[res] if res else None, b[dst], b[src2] if src2 else None)
+            layer(b[src], b[res] if res else None, b[dst], b[src2] if src2 else None, *((b[dst2],) if dst2 else ()))
         else:
             layer(self._view(src, c), self._view(res, c), self._view(dst, c), self._view(src2, c))
         if dst == "stem":
@@ -425,18 +446,18 @@ class _ForwardPlan:
         over the REAL filter taps / channels (no padding, no zero insertion); a fused projection shortcut
         or fused final 1x1 counts the work of both convolutions."""
         rows = []
-        for k, (name, layer, src, res, dst, src2) in enumerate((n, *op) for n, op in zip(self.named, self.ops)):
+        for k, (name, layer, src, res, dst, src2, dst2) in enumerate((n, *op) for n, op in zip(self.named, self.ops)):
             d = layer.desc
             m = d.B * layer.Ho * layer.Wo * (self.n_chunks if k < self.n_section_ops else 1)      # per step
             taps = {CONV_1x1: 1, CONV_3x3: 9, CONV_STEM7x7: 49, CONV_DECONV4: 4, CONV_FINAL: 1}[d.kind]
-            flops = 2.0 * m * d.Cin * d.Cout * taps + 2.0 * m * d.Cin2 * d.Cout + 2.0 * m * 256 * layer.head2
+            flops = 2.0 * m * d.Cin * d.Cout * taps + 2.0 * m * d.Cin2 * d.Cout + 2.0 * m * 256 * (layer.head2 + layer.chain)
             if name.startswith("deconv") or name == "final_layer":
                 fam = "deconv_head"
             elif name == "backbone.conv1":
                 fam = "stem"
             else:
                 fam = name.split(".")[1] + (".3x3" if d.kind == CONV_3x3 else ".1x1")
-            rows.append((name, fam, flops, layer, (src, res, dst, src2)))
+            rows.append((name, fam, flops, layer, (src, res, dst, src2, dst2)))
         return rows
 
     def export_acts(self):
@@ -450,7 +471,10 @@ class _ForwardPlan:
         def nchw(t):
             return t.float().cpu() if t.dtype == torch.float32 else t.float().cpu().permute(0, 3, 1, 2).contiguous()
         acts = {}
-        for name, (layer, src, res, dst, src2) in zip(self.named, self.ops):
+        for c1, c3 in self.chained.items():              # a chained conv1: input = the block output its conv3 kernel staged
+            op = self.ops[list(self.named).index(c3)]
+            acts[c1] = {"x": nchw(self.bufs[op[3]]), "y": nchw(self.bufs[op[5]])}
+        for name, (layer, src, res, dst, src2, dst2) in zip(self.named, self.ops):
             a = {"y": nchw(self.bufs[dst])}
             if src != "s2d":
                 a["x"] = nchw(self.bufs[src])
@@ -466,13 +490,14 @@ class _ForwardPlan:
         back-to-back calls between two events (the launch gap of all but the first is hidden behind the previous call).
         Returns [(name, family, flops, microseconds)].  Diagnostic / benchmark use."""
         out = []
-        for k, (name, fam, flops, layer, (src, res, dst, src2)) in enumerate(self.layer_table()):
+        for k, (name, fam, flops, layer, (src, res, dst, src2, dst2)) in enumerate(self.layer_table()):
             passes = self.n_chunks if k < self.n_section_ops else 1            # a section layer is timed on pass 0, reported per step
             c = 0 if k < self.n_section_ops else None
             call = lambda: layer(self._view(src, c) if c is not None else self.bufs[src],          # noqa: E731
                                  (self._view(res, c) if c is not None else self.bufs[res]) if res else None,
                                  self._view(dst, c) if c is not None else self.bufs[dst],
-                                 (self._view(src2, c) if c is not None else self.bufs[src2]) if src2 else None)
+                                 (self._view(src2, c) if c is not None else self.bufs[src2]) if src2 else None,
+                                 *((self.bufs[dst2],) if dst2 else ()))
             call()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()

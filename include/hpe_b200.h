@@ -155,6 +155,12 @@ typedef struct hpe_conv_desc {
                                (MaxPool2d(3, 2, 1) after conv1/bn1/act1) is taken in the stem's epilogue; y is the POOLED
                                [B, Hp, Wp, 64] tensor and the H/2 x W/2 stem output is never written.  Bit-identical to
                                hpe_conv_run followed by hpe_maxpool3x3s2. */
+  int chain;                /* N2 = 64 | 128 (dense ReLU HPE_CONV_1x1, stride 1, Cout = 256): the NEXT layer's 1x1 conv 256 -> N2 (+ folded
+                               BN + ReLU) runs on every output tile while it is staged for its store -- `x = self.act3(x)` of one timm
+                               Bottleneck and `x = self.conv1(x); x = self.bn1(x); x = self.act1(x)` of the next (resnet.py:247-270) in
+                               one kernel.  y is written as usual (it is the next block's shortcut); the chained output y2
+                               [B,Ho,Wo,N2] is bit-identical to running the second conv as its own layer.  Run with
+                               hpe_conv_run_chain. */
 } hpe_conv_desc;
 /* Channel counts: Cin and Cout must be multiples of 8 (16-byte pixels); partial 64-channel blocks are zero-filled by TMA. */
 
@@ -176,6 +182,11 @@ int  hpe_conv_run2(hpe_conv_plan* plan, const void* x, const void* x2, const voi
  * Cin 256, Cout K) into a ZERO-initialised buffer of 32*256 bf16; bias2 [K] f32; heatmaps [B,K,Ho,Wo] f32 NCHW */
 int  hpe_conv_run_head2(hpe_conv_plan* plan, const void* x, const void* w_packed, const float* scale, const float* shift,
                         const void* w2_packed, const float* bias2, float* heatmaps, void* stream);
+/* chained variant (desc.chain = N2): w2_packed = the next 1x1 conv's weights packed with hpe_conv_pack_weight (kind HPE_CONV_1x1,
+ * Cin 256, Cout N2); scale2 / shift2 [N2] its folded BN; y2 [B,Ho,Wo,N2] bf16 NHWC.  x2 as in hpe_conv_run2 (NULL without Cin2). */
+int  hpe_conv_run_chain(hpe_conv_plan* plan, const void* x, const void* x2, const void* w_packed, const float* scale,
+                        const float* shift, const void* residual, void* y, const void* w2_packed, const float* scale2,
+                        const float* shift2, void* y2, void* stream);
 /* Batched packing (training re-packs every layer's forward and backward-data operands each step): fill one job record per
  * (layer, direction) on the HOST (hpe_pack_job_bytes() bytes each, consecutive block ranges: pass the running sum of
  * *n_blocks as block_begin), copy the records to the device once, then ONE launch re-packs everything. */

@@ -86,7 +86,7 @@ def test_fused_paths_equal_unfused_layers(pair, cuda_dev, monkeypatch, B):
     hm1 = m(x).clone()
     hm2 = m(x).clone()
     assert torch.equal(hm1, hm2)
-    for k in ("HPE_B200_FUSE_SHORTCUT", "HPE_B200_FUSE_HEAD", "HPE_B200_PAIR", "HPE_B200_FUSE_POOL"):
+    for k in ("HPE_B200_FUSE_SHORTCUT", "HPE_B200_FUSE_HEAD", "HPE_B200_PAIR", "HPE_B200_FUSE_POOL", "HPE_B200_FUSE_CHAIN"):
         monkeypatch.setenv(k, "0")
     plain = models.HeatmapPose(17, "resnet50", pretrained=False)
     plain.load_state_dict(ref.state_dict())
@@ -98,6 +98,32 @@ def test_fused_paths_equal_unfused_layers(pair, cuda_dev, monkeypatch, B):
     scale = want.abs().max().item()
     assert (hm1 - want).abs().max().item() <= 2e-2 * scale, (hm1 - want).abs().max().item() / scale
     assert ((hm1 - want) ** 2).mean().sqrt().item() <= 3e-3 * scale
+
+
+@pytest.mark.parametrize("B", [2, 5, 32])
+def test_chained_conv1_is_bit_identical(pair, cuda_dev, monkeypatch, B):
+    """desc.chain: conv3 (+ shortcut + ReLU) of a layer1 Bottleneck and conv1 + BN + ReLU of the next block in one kernel (the
+    second GEMM reads the staged output chunks).  Same bf16 A operand, same k order, same epilogue arithmetic as the separate
+    conv1 launch: every activation of the chained convs and the heatmaps are bit-identical with the fusion switched off."""
+    from importlib import import_module
+    models = import_module("2d-human-pose-estimation_b200.models")
+    m, ref = pair
+    x = torch.rand(B, 3, 256, 192, generator=torch.Generator().manual_seed(90 + B)).to(cuda_dev)
+    hm = m(x).clone()
+    plan = m._plans[(tuple(x.shape), cuda_dev.index)]
+    assert len(plan.chained) == 3, plan.chained          # layer1.1.conv1, layer1.2.conv1, layer2.0.conv1
+    t1 = {k: plan.bufs[k.replace("conv1", "t1")].clone() for k in plan.chained}
+    monkeypatch.setenv("HPE_B200_FUSE_CHAIN", "0")
+    plain = models.HeatmapPose(17, "resnet50", pretrained=False)
+    plain.load_state_dict(ref.state_dict())
+    plain = plain.to(cuda_dev).eval()
+    want = plain(x)
+    torch.cuda.synchronize()
+    pplan = next(iter(plain._plans.values()))
+    assert not pplan.chained
+    for k, got in t1.items():
+        assert torch.equal(got, pplan.bufs[k.replace("conv1", "t1")]), k
+    assert torch.equal(hm, want)
 
 
 def test_full_size_batch_equals_small_batches(pair, cuda_dev):

@@ -82,7 +82,7 @@ def forward():
     plan = next(iter(m._plans.values()))
     # per-layer eager timing (L2 not flushed between layers: this is how they run in the step)
     rows = []
-    for layer, src, res, dst, src2 in plan.ops:
+    for layer, src, res, dst, src2, _dst2 in plan.ops:
         name = [k for k, v in plan.named.items() if v is layer][0]
         fn = lambda: layer(plan.bufs[src], plan.bufs[res] if res else None, plan.bufs[dst], plan.bufs[src2] if src2 else None)
         med, best = timeit(fn, iters=5, warm=1)
