@@ -761,6 +761,45 @@ preprocess_kernel(const T* __restrict__ img, int B, int H, int W, __nv_bfloat16*
   }
 }
 
+// uint8 image, W % 8 == 0: one thread = FOUR adjacent space-to-depth pixels (xp = 4g .. 4g+3, i.e. source columns 8g-4 .. 8g+3 of two
+// image rows) from 4-byte loads; same values as preprocess_kernel<unsigned char> (x / 255 in fp32, rounded to bf16).
+__global__ void __launch_bounds__(256)
+preprocess_u8x4_kernel(const unsigned char* __restrict__ img, int B, int H, int W, __nv_bfloat16* __restrict__ out) {
+  const int Hs = H / 2, Ws = W / 2, Wp = Ws + kS2DPad, G = Wp / 4;         // W % 8 == 0 -> Wp % 4 == 0
+  const long long total = static_cast<long long>(B) * Hs * G;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int g  = static_cast<int>(i % G);
+    const int ys = static_cast<int>((i / G) % Hs);
+    const int b  = static_cast<int>(i / (static_cast<long long>(G) * Hs));
+    const int sx0 = 8 * g - 4;                                             // first source column of the group (multiple of 4)
+    float v[3][2][8];                                                      // [c][py][8 source columns]
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+#pragma unroll
+      for (int py = 0; py < 2; ++py) {
+        const unsigned char* row = img + ((static_cast<size_t>(b) * 3 + c) * H + (2 * ys + py)) * W;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int sx = sx0 + 4 * h;
+          uchar4 u = make_uchar4(0, 0, 0, 0);
+          if (sx >= 0 && sx < W) u = __ldg(reinterpret_cast<const uchar4*>(row + sx));
+          v[c][py][4 * h + 0] = __fdiv_rn(static_cast<float>(u.x), 255.f); v[c][py][4 * h + 1] = __fdiv_rn(static_cast<float>(u.y), 255.f);
+          v[c][py][4 * h + 2] = __fdiv_rn(static_cast<float>(u.z), 255.f); v[c][py][4 * h + 3] = __fdiv_rn(static_cast<float>(u.w), 255.f);
+        }
+      }
+    uint4* o = reinterpret_cast<uint4*>(out + ((static_cast<size_t>(b) * Hs + ys) * Wp + 4 * g) * 16);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {                                          // s2d pixel xp = 4g + k = source columns 2k, 2k+1 of the group
+      // channel = (py*2+px)*4 + c (c == 3 -> 0); columns outside the image were loaded as 0 (the physical x padding)
+      o[2 * k]     = make_uint4(pack_bf16(v[0][0][2 * k], v[1][0][2 * k]), pack_bf16(v[2][0][2 * k], 0.f),
+                                pack_bf16(v[0][0][2 * k + 1], v[1][0][2 * k + 1]), pack_bf16(v[2][0][2 * k + 1], 0.f));
+      o[2 * k + 1] = make_uint4(pack_bf16(v[0][1][2 * k], v[1][1][2 * k]), pack_bf16(v[2][1][2 * k], 0.f),
+                                pack_bf16(v[0][1][2 * k + 1], v[1][1][2 * k + 1]), pack_bf16(v[2][1][2 * k + 1], 0.f));
+    }
+  }
+}
+
 __device__ __forceinline__ uint32_t bf16x2_max(uint32_t a, uint32_t b) {
   __nv_bfloat162 r = __hmax2(*reinterpret_cast<__nv_bfloat162*>(&a), *reinterpret_cast<__nv_bfloat162*>(&b));
   return *reinterpret_cast<uint32_t*>(&r);
@@ -1557,6 +1596,14 @@ extern "C" int hpe_preprocess_u8(const unsigned char* img, int B, int H, int W, 
   HPE_CHECK_ARG(img && out, "hpe_preprocess_u8: null pointer");
   HPE_CHECK_ARG(B > 0 && H > 0 && W > 0 && H % 2 == 0 && W % 2 == 0, "hpe_preprocess_u8: H and W must be positive and even");
   HPE_CHECK_ARG((((uintptr_t)img & 1) | ((uintptr_t)out & 15)) == 0, "hpe_preprocess_u8: misaligned pointer");
+  if (W % 8 == 0 && ((uintptr_t)img & 3) == 0) {
+    // four space-to-depth pixels per thread from 4-byte loads (the 2-byte loads of the generic kernel made the uint8 path
+    // SLOWER than the fp32 one -- 68 vs 40 us at B = 256 -- although it reads a quarter of the bytes)
+    const long long total = (long long)B * (H / 2) * ((W / 2 + kS2DPad) / 4);
+    const int grid = (int)((total + 255) / 256 > (long long)num_sms() * 16 ? (long long)num_sms() * 16 : (total + 255) / 256);
+    preprocess_u8x4_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(img, B, H, W, (__nv_bfloat16*)out);
+    return launch_status("preprocess_u8x4_kernel");
+  }
   const long long total = (long long)B * (H / 2) * (W / 2 + kS2DPad);
   const int grid = (int)((total + 255) / 256 > (long long)num_sms() * 16 ? (long long)num_sms() * 16 : (total + 255) / 256);
   preprocess_kernel<unsigned char><<<grid, 256, 0, (cudaStream_t)stream>>>(img, B, H, W, (__nv_bfloat16*)out);
