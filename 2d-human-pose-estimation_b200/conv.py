@@ -49,7 +49,7 @@ class ConvLayer:
             self.bias2 = torch.zeros(self.head2, dtype=torch.float32, device=self.device)
         self.chain = int(self.desc.chain)
         if self.chain:       # chained 1x1 conv 256 -> chain (the next layer): its packed weights and folded BN
-            self.w2_packed = torch.zeros(self.chain * 256, dtype=torch.bfloat16, device=self.device)
+            self.w2_packed = torch.zeros(self.chain * Cout, dtype=torch.bfloat16, device=self.device)
             self.scale2 = torch.ones(self.chain, dtype=torch.float32, device=self.device)
             self.shift2 = torch.zeros(self.chain, dtype=torch.float32, device=self.device)
         self.scale = torch.ones(Cout, dtype=torch.float32, device=self.device)
@@ -99,10 +99,10 @@ class ConvLayer:
         return self
 
     def load_chain(self, weight: torch.Tensor, scale: torch.Tensor, shift: torch.Tensor):
-        """Chained layer (``chain = N2``): ``weight`` [N2,256,1,1] and folded BN ``scale``/``shift`` [N2] of the NEXT 1x1 conv
+        """Chained layer (``chain = N2``): ``weight`` [N2,Cout,1,1] and folded BN ``scale``/``shift`` [N2] of the NEXT 1x1 conv
         (timm ``Bottleneck.conv1``/``bn1``, resnet.py:247-251), applied to this layer's output tile while it is staged."""
         w = weight.detach().to(self.device, torch.float32).contiguous()
-        cd = ConvDesc(CONV_1x1, self.B, self.Ho, self.Wo, 256, self.chain, 1, ACT_RELU, 0)
+        cd = ConvDesc(CONV_1x1, self.B, self.Ho, self.Wo, self.Cout, self.chain, 1, ACT_RELU, 0)
         with torch.cuda.device(self.device):
             _lib.check(_lib.lib().hpe_conv_pack_weight(C.byref(cd), _lib.ptr(w), _lib.ptr(self.w2_packed), _lib.stream_ptr()),
                        "hpe_conv_pack_weight")

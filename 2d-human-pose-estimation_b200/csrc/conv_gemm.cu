@@ -106,20 +106,23 @@ __device__ __forceinline__ int kb_count(const ConvParams& p, int cls) {
 // saved go to a deeper operand ring, which is what bounds the deep-K layers (ring depth / hand-off round trip).
 // EPI2 (two epilogue groups): NSB counts the buffers of BOTH groups and each group has its own scale/shift table.
 // KBR (CHAIN kernels): the layer's whole weight tile (KBR k-blocks of BLOCK_N x 64) stays RESIDENT and the ring carries A only.
-template <int BLOCK_N, int STAGES, bool PAIR = false, int NSB = 4, bool HEAD2 = false, bool EPI2 = false, int CHAIN = 0, int KBR = 0>
+// NH (CHAIN kernels): 256-wide halves of the layer's output a CTA computes per pixel tile (2 = Cout 512); then the chained conv's
+// [N2][256 NH] weights do not fit and their 64-wide K slices stream through a ring of kW2Slots buffers instead.
+constexpr int kW2Slots = 3;
+template <int BLOCK_N, int STAGES, bool PAIR = false, int NSB = 4, bool HEAD2 = false, bool EPI2 = false, int CHAIN = 0, int KBR = 0, int NH = 1>
 struct SmemLayout {
   // fused head: this CTA's 16 rows x 256 K of the joint weights; CHAIN: the chained 1x1 conv's [N2 rows][256 K] weights
-  static constexpr int kW2Bytes    = HEAD2 ? 4 * 16 * 128 : 4 * CHAIN * 128;
+  static constexpr int kW2Bytes    = HEAD2 ? 4 * 16 * 128 : (NH == 1 ? 4 : kW2Slots) * CHAIN * 128;
   static constexpr int kBBytes     = (PAIR ? BLOCK_N / 2 : BLOCK_N) * kKBlock * 2;    // a CTA of a pair holds half of B's rows
   static constexpr int kStageBytes = kABytes + (KBR ? 0 : kBBytes);
   static constexpr int kOffA   = 0;
   static constexpr int kOffB   = STAGES * kABytes;
   static constexpr int kOffSB  = kOffB + (KBR ? KBR : STAGES) * kBBytes;
   static constexpr int kOffSS  = kOffSB + NSB * kSBBytes;             // float scale[kMaxBlockN], shift[kMaxBlockN] (x 2 groups with EPI2)
-  static constexpr int kOffSS2 = kOffSS + (EPI2 ? 4 : 2) * kMaxBlockN * 4;      // CHAIN: float scale2[128], shift2[128]
+  static constexpr int kOffSS2 = kOffSS + ((EPI2 || NH == 2) ? 4 : 2) * kMaxBlockN * 4;      // CHAIN: float scale2[128], shift2[128]
   static constexpr int kOffW2  = kOffSS2 + (CHAIN ? 1024 : 0);                  // 1024-byte aligned
   static constexpr int kOffBar = kOffW2 + kW2Bytes;
-  static constexpr int kNumBar = 2 * STAGES + 4 + 4 * NSB + 7;       // + g2done[NSB], staged[NSB] (CHAIN) + w2full, s2full, d2full[2], a2empty[2], spare
+  static constexpr int kNumBar = 2 * STAGES + 4 + 4 * NSB + 7 + 2 * kW2Slots;       // + g2done[NSB], staged[NSB] (CHAIN) + w2full, s2full, d2full[2], a2empty[2], wres + w2 ring full/empty
   static constexpr int kTotal  = kOffBar + kNumBar * 8 + 16;
   static constexpr int kDynamic = kTotal;             // the dynamic segment starts 1024-byte aligned (checked in the kernel)
   static_assert(kTotal <= 232448, "exceeds the 227 KB of shared memory a CTA may use");
@@ -234,7 +237,10 @@ __device__ __forceinline__ void epi_chunk_math(const uint32_t (&v)[32], uint32_t
 // KBR = the layer's k-blocks per tile (1 | 2, CHAIN only): its weight tile is loaded once and stays resident, the ring carries the A
 // bricks only, and the shared memory saved goes to a deeper chunk-buffer ring (the chained kernel was bound by the residual ring:
 // 4 buffers / (HBM latency + processing + drain) = one chunk per ~1.85 k cycles).
-template <int BLOCK_N, int STAGES, int ACT, bool RES, bool FINAL, bool PAIR = false, bool HEAD2 = false, bool EPI2 = false, int CHAIN = 0, int KBR = 0>
+// NH = 2 (CHAIN = 128, Cout = 512: layer2): the CTA computes BOTH 256-wide halves of a pixel tile one after the other through the
+// single main accumulator (weights streamed as usual), eight real chunks feed the chained GEMM (K = 512), whose weight slices
+// [128][64] stream through a small ring loaded by the issuer warp itself.
+template <int BLOCK_N, int STAGES, int ACT, bool RES, bool FINAL, bool PAIR = false, bool HEAD2 = false, bool EPI2 = false, int CHAIN = 0, int KBR = 0, int NH = 1>
 __global__ void __launch_bounds__(CHAIN ? kConvThreadsC : (EPI2 ? kConvThreads2 : kConvThreads), 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
                  const __grid_constant__ CUtensorMap tmW, const __grid_constant__ OutMaps tmOut,
@@ -250,14 +256,15 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   constexpr int kGroups = EPI2 ? 2 : 1;
   // per group; the fp32 heatmap epilogue stores from registers: all smem to the ring.  CHAIN = 128: its 64 KB of resident weights
   // leave room for 3 buffers only (residual lead 1)
-  static_assert(!(CHAIN == 128 && !RES), "chained 128-wide conv: residual variant only (shared-memory budget)");
-  static_assert((KBR != 0) == (CHAIN != 0) && KBR <= 2, "resident weights: the chained kernels (1-2 k-blocks per tile)");
+  static_assert(!(CHAIN == 128 && NH == 1 && !RES), "chained 128-wide conv behind 256 channels: residual variant only (shared-memory budget)");
+  static_assert((KBR != 0) == (CHAIN != 0 && NH == 1) && KBR <= 2, "resident weights: the 256-channel chained kernels (1-2 k-blocks per tile)");
+  static_assert(NH == 1 || (NH == 2 && CHAIN == 128), "two halves per pixel tile: the 512 -> 128 chain of layer2");
   // CHAIN: one ring for both groups, as deep as fits (the residual rides it with a lead of kNumSB - 2 chunks)
   constexpr int kNumSB = FINAL ? 0 : (CHAIN ? ((RES && CHAIN == 64) ? 6 : 4) : (EPI2 ? (RES ? 3 : 2) : ((RES || HEAD2) ? 4 : 3)));
   constexpr int kResLead = 2;                     // the residual of chunk q + 2 is requested while chunk q is processed
   constexpr int kLead = CHAIN ? kNumSB - 2 : kResLead;
   constexpr int kChunks2 = CHAIN / 64;            // 64-column chunks of the chained conv's output
-  using L = SmemLayout<BLOCK_N, STAGES, PAIR, kGroups * kNumSB, HEAD2, EPI2, CHAIN, KBR>;
+  using L = SmemLayout<BLOCK_N, STAGES, PAIR, kGroups * kNumSB, HEAD2, EPI2, CHAIN, KBR, NH>;
   static_assert(!PAIR || (BLOCK_N % 32 == 0 && !FINAL), "pair kernels: N multiple of 32, bf16 NHWC epilogue");
   constexpr int kChunks   = BLOCK_N >= 64 ? BLOCK_N / 64 : 1;
   constexpr int kTmemCols = CHAIN ? 512 : 2 * BLOCK_N <= 32 ? 32 : (2 * BLOCK_N <= 64 ? 64 : (2 * BLOCK_N <= 128 ? 128 : (2 * BLOCK_N <= 256 ? 256 : 512)));  // power of two
@@ -288,6 +295,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint64_t* d2full_bar = w2full_bar + 2;                           // fused head: second GEMM done (multicast commit); CHAIN: [2], per chained accumulator
   uint64_t* a2empty_bar = w2full_bar + 4;                          // CHAIN: [2] chained accumulator drained
   uint64_t* wres_bar   = w2full_bar + 6;                           // KBR: the resident weight tile has landed
+  uint64_t* w2rfull_bar = w2full_bar + 7;                          // NH = 2: [kW2Slots] a chained-weight K slice has landed
+  uint64_t* w2rempty_bar = w2rfull_bar + kW2Slots;                 // NH = 2: [kW2Slots] ... has been consumed by its MMAs
   uint8_t*  sW2 = smem + L::kOffW2;
   float*    sScale2 = reinterpret_cast<float*>(smem + L::kOffSS2);   // CHAIN
   float*    sShift2 = sScale2 + 128;
@@ -309,6 +318,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     mbar_init(w2full_bar, 1); mbar_init(s2full_bar, 2); mbar_init(d2full_bar, 1); mbar_init(d2full_bar + 1, 1);
     mbar_init(&a2empty_bar[0], CHAIN ? 8 * kChunks2 : 1); mbar_init(&a2empty_bar[1], CHAIN ? 8 * kChunks2 : 1);
     mbar_init(wres_bar, 1);
+    for (int b = 0; b < kW2Slots; ++b) { mbar_init(&w2rfull_bar[b], 1); mbar_init(&w2rempty_bar[b], 1); }
     fence_mbar_init();
   }
   if (warp == 1) {
@@ -342,7 +352,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     for (int work = work0; work < p.num_tiles; work += wstep) {
       const TileCoord t = tile_coord(p, work_tile<PAIR>(p, work, rank));
-      const int wrow = t.cls * p.Cout + t.n_tile * BLOCK_N + (PAIR ? rank * (BLOCK_N / 2) : 0);
+     for (int nh = 0; nh < NH; ++nh) {              // NH = 2: both 256-wide halves of the pixel tile (A is loaded again for the second)
+      const int wrow = t.cls * p.Cout + (t.n_tile * NH + nh) * BLOCK_N + (PAIR ? rank * (BLOCK_N / 2) : 0);
       const int num_kb = kb_count(p, t.cls), num_kb1 = num_kb - p.kc2;
       const int bx = t.x0 * p.in_stride, by = t.y0 * p.in_stride;
       int tap = 0, kc = 0, dx, dy;
@@ -371,6 +382,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (++kc == p.kc_per_tap) { kc = 0; ++tap; tap_offset(p, tap, t.cls, dx, dy); }
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
+     }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
@@ -380,7 +392,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       constexpr uint32_t kDescHi = (1024u >> 4) | (1u << 14) | (2u << 29);     // SBO = 1024 B, version 1, SWIZZLE_128B
       int stage = 0; uint32_t phase = 0; int it = 0;
       if constexpr (KBR != 0) mbar_wait(wres_bar, 0);
-      for (int work = work0; work < p.num_tiles; work += wstep, ++it) {
+      for (int work = work0; work < p.num_tiles; work += wstep) for (int nh = 0; nh < NH; ++nh, ++it) {     // it counts (tile, half)
         const int acc = CHAIN ? 0 : (it & 1);     // CHAIN: one main accumulator (columns 256.. hold the chained conv's)
         mbar_wait(&tempty_bar[acc], (CHAIN ? (it & 1) : ((it >> 1) & 1)) ^ 1);
         tc_fence_after();
@@ -410,7 +422,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       mbar_arrive_expect_tx(w2full_bar, L::kW2Bytes);
       for (int kb = 0; kb < 4; ++kb) tma_load_2d(sW2 + kb * 2048, &tmRes, w2full_bar, kb * kKBlock, rank * 16);
     }
-    if (CHAIN && lane == 0) {        // chained 1x1: [N2 rows][256 K] as 4 k-blocks of N2 x 128 B, loaded once (map in tmOut.m[2])
+    if (CHAIN && NH == 1 && lane == 0) {        // chained 1x1: [N2 rows][256 K] as 4 k-blocks of N2 x 128 B, loaded once (map in tmOut.m[2])
       mbar_arrive_expect_tx(w2full_bar, L::kW2Bytes);
       for (int kb = 0; kb < 4; ++kb) tma_load_2d(sW2 + kb * (CHAIN * 128), &tmOut.m[2], w2full_bar, kb * kKBlock, 0);
     }
@@ -441,12 +453,12 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         int r = 0;
         for (int work = work0; work < p.num_tiles; work += wstep) {
           const TileCoord t = tile_coord(p, work_tile<PAIR>(p, work, rank));
-          for (int c = 0; c < kChunks + kChunks2; ++c, ++r) {
+          for (int c = 0; c < NH * kChunks + kChunks2; ++c, ++r) {
             const int b = r % kNumSB;
             mbar_wait(&sbempty_bar[b], (r / kNumSB) & 1);   // the epilogue leader hands buffers over with a lead of kResLead chunks
-            if (c >= kChunks) { mbar_arrive(&sbfull_bar[b]); continue; }     // CHAIN: the chained conv's output chunk has no residual
+            if (c >= NH * kChunks) { mbar_arrive(&sbfull_bar[b]); continue; }     // CHAIN: the chained conv's output chunk has no residual
             mbar_arrive_expect_tx(&sbfull_bar[b], kSBBytes);
-            tma_load_4d(sSB + b * kSBBytes, &tmRes, &sbfull_bar[b], t.n_tile * BLOCK_N + c * 64, t.x0, t.y0, t.b0);
+            tma_load_4d(sSB + b * kSBBytes, &tmRes, &sbfull_bar[b], t.n_tile * NH * BLOCK_N + c * 64, t.x0, t.y0, t.b0);
           }
         }
       }
@@ -457,25 +469,47 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // the separate conv1 launch's), as soon as the chunk's group has staged it.
     if constexpr (CHAIN != 0) {
       if (lane == 0) {
-        constexpr int kCPT = kChunks + kChunks2;                 // chunks per tile: 4 of y, then 1-2 of the chained output
+        constexpr int kCT = NH * kChunks;                        // real chunks per tile (4 of y per 256-wide half)
+        constexpr int kCPT = kCT + kChunks2;                     // ... then 1-2 of the chained output
         constexpr uint32_t kIdesc2 = make_idesc_bf16_m128(CHAIN);
-        mbar_wait(w2full_bar, 0);
+        constexpr int kSlice = CHAIN * 128;                      // bytes of one [N2][64] K slice of the chained weights
+        if constexpr (NH == 1) mbar_wait(w2full_bar, 0);
         int q = 0, it = 0;
+        // NH = 2: the K slices stream through kW2Slots buffers, requested kW2Slots - 1 real chunks ahead
+        int w_req = 0, w_use = 0;                                // slices requested / consumed so far (over the whole kernel)
+        const int my_tiles = work0 < p.num_tiles ? (p.num_tiles - 1 - work0) / wstep + 1 : 0;
+        const int w_total = my_tiles * kCT;
+        auto request = [&]() {
+          const int slot = w_req % kW2Slots;
+          mbar_wait(&w2rempty_bar[slot], ((w_req / kW2Slots) & 1) ^ 1);
+          mbar_arrive_expect_tx(&w2rfull_bar[slot], kSlice);
+          tma_load_2d(sW2 + slot * kSlice, &tmOut.m[2], &w2rfull_bar[slot], (w_req % kCT) * kKBlock, 0);
+          ++w_req;
+        };
+        if constexpr (NH == 2) { while (w_req < kW2Slots - 1 && w_req < w_total) request(); }
         for (int work = work0; work < p.num_tiles; work += wstep, ++it) {
           const int a2 = it & 1;
           mbar_wait(&a2empty_bar[a2], ((it >> 1) & 1) ^ 1);      // tile it-2's chained output has left accumulator a2
           for (int c = 0; c < kCPT; ++c, ++q) {
             const int sb = q % kNumSB;
+            if (NH == 2 && c < kCT && w_req < w_total) request();
             mbar_wait(&staged_bar[sb], (q / kNumSB) & 1);
-            if (c < kChunks) {
+            if (c < kCT) {
+              const uint8_t* wsl = sW2 + c * kSlice;
+              if constexpr (NH == 2) {
+                const int slot = w_use % kW2Slots;
+                mbar_wait(&w2rfull_bar[slot], (w_use / kW2Slots) & 1);
+                wsl = sW2 + slot * kSlice;
+              }
               tc_fence_after();
               const uint64_t adesc = make_sw128_kmajor_desc(sSB + sb * kSBBytes);
-              const uint64_t bdesc = make_sw128_kmajor_desc(sW2 + c * (CHAIN * 128));
+              const uint64_t bdesc = make_sw128_kmajor_desc(wsl);
 #pragma unroll
               for (int k = 0; k < 4; ++k) umma_bf16(tmem_base + BLOCK_N + a2 * CHAIN, adesc + 2 * k, bdesc + 2 * k, kIdesc2, (c | k) != 0);
+              if constexpr (NH == 2) { umma_commit(&w2rempty_bar[w_use % kW2Slots]); ++w_use; }
             }
             umma_commit(&g2_bar[sb]);                            // every chunk commits: a buffer's phase sequence stays uniform
-            if (c == kChunks - 1) umma_commit(&d2full_bar[a2]);
+            if (c == kCT - 1) umma_commit(&d2full_bar[a2]);
           }
         }
       }
@@ -487,13 +521,14 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // chained kernel at 11.6 k cycles per tile against ~7.9 k of HBM time).  The buffers form ONE ring in chunk order; with an
     // even buffer count, or the residual hand-over two chunks back, a buffer is always recycled by the group that stored it.
     if constexpr (CHAIN != 0) {
-      constexpr int kCPT = kChunks + kChunks2;
+      constexpr int kCT = NH * kChunks, kCPT = kCT + kChunks2;
       const int grp = (warp - 4) >> 3, ew = warp & 3, half = ((warp - 4) >> 2) & 1, row = ew * 32 + lane;
       const int atid = threadIdx.x - 128, etid = atid - grp * kEpiThreads;
       const bool leader = etid == 0;
       const uint32_t bar_id = 1 + grp;
-      if (atid < BLOCK_N) { sScale[atid] = atid < p.Cout ? __ldg(p.scale + atid) : 0.f; sShift[atid] = atid < p.Cout ? __ldg(p.shift + atid) : 0.f; }
-      else if (atid < BLOCK_N + CHAIN) { sScale2[atid - BLOCK_N] = __ldg(p.scale2 + atid - BLOCK_N); sShift2[atid - BLOCK_N] = __ldg(p.shift2 + atid - BLOCK_N); }
+      float* const scl = sScale; float* const shf = sScale + NH * BLOCK_N;      // (NH = 2: a 4 KB table region)
+      for (int n = atid; n < NH * BLOCK_N; n += 2 * kEpiThreads) { scl[n] = n < p.Cout ? __ldg(p.scale + n) : 0.f; shf[n] = n < p.Cout ? __ldg(p.shift + n) : 0.f; }
+      if (atid < CHAIN) { sScale2[atid] = __ldg(p.scale2 + atid); sShift2[atid] = __ldg(p.shift2 + atid); }
       named_bar_sync(3, 2 * kEpiThreads);
       if (RES && atid == 0) for (int b = 0; b < kLead; ++b) mbar_arrive(&sbempty_bar[b]);
       const uint32_t taddr0 = tmem_base + (static_cast<uint32_t>(ew * 32) << 16);
@@ -504,31 +539,32 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int work = work0 + it * wstep;
         if (work >= p.num_tiles) break;
         if (it != it_cur) { t = tile_coord(p, work); it_cur = it; }
-        const bool e2 = c >= kChunks;
+        const bool e2 = c >= kCT;
         const int sb = q % kNumSB, a2 = it & 1;
+        const int nh = e2 ? 0 : c / kChunks, cc = e2 ? c - kCT : c - nh * kChunks;     // 256-wide half, chunk inside it
         if (leader) {
           bulk_wait_read<0>();                                   // this group's stores (chunks q-2, q-4, ...) have left shared memory
           if (q >= 2) mbar_wait(&g2_bar[(q - 2) % kNumSB], ((q - 2) / kNumSB) & 1);     // ... and the second GEMM has read chunk q-2
           if (RES) mbar_arrive(&sbempty_bar[(q + kLead) % kNumSB]);                     // = chunk q-2's buffer: to the residual producer
         }
-        if (e2) mbar_wait(&d2full_bar[a2], (it >> 1) & 1); else mbar_wait(&tfull_bar[0], it & 1);
+        if (e2) mbar_wait(&d2full_bar[a2], (it >> 1) & 1); else mbar_wait(&tfull_bar[0], (it * NH + nh) & 1);
         tc_fence_after();
         uint32_t v[32];
-        tmem_ld_x32(e2 ? taddr0 + BLOCK_N + a2 * CHAIN + (c - kChunks) * 64 + half * 32 : taddr0 + c * 64 + half * 32, v);
+        tmem_ld_x32(e2 ? taddr0 + BLOCK_N + a2 * CHAIN + cc * 64 + half * 32 : taddr0 + cc * 64 + half * 32, v);
         if (RES) mbar_wait(&sbfull_bar[sb], (q / kNumSB) & 1);
         tmem_ld_wait();
-        if (e2 || c + 2 >= kChunks) {                            // this group's last read of the main / of the chained accumulator
+        if (e2 || cc + 2 >= kChunks) {                           // this group's last read of the main (half) / of the chained accumulator
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(e2 ? &a2empty_bar[a2] : &tempty_bar[0]);
         }
-        const int n0 = (e2 ? c - kChunks : c) * 64 + half * 32;
-        epi_chunk_math<ACT>(v, smem_u32((e2 ? sScale2 : sScale) + n0), smem_u32((e2 ? sShift2 : sShift) + n0),
+        const int n0 = (e2 ? cc : c) * 64 + half * 32;
+        epi_chunk_math<ACT>(v, smem_u32((e2 ? sScale2 : scl) + n0), smem_u32((e2 ? sShift2 : shf) + n0),
                             smem_u32(sSB + sb * kSBBytes) + row * 128, half, row, RES && !e2);
         fence_proxy_async_smem();                                // generic-proxy writes -> visible to TMA and to the tensor core
         named_bar_sync(bar_id, kEpiThreads);
         if (leader) {
-          if (e2) tma_store_4d(&tmOut.m[1], sSB + sb * kSBBytes, (c - kChunks) * 64, t.x0, t.y0, t.b0);
+          if (e2) tma_store_4d(&tmOut.m[1], sSB + sb * kSBBytes, cc * 64, t.x0, t.y0, t.b0);
           else    tma_store_4d(&tmOut.m[0], sSB + sb * kSBBytes, c * 64, t.x0, t.y0, t.b0);
           bulk_commit();
           mbar_arrive(&staged_bar[sb]);
@@ -930,9 +966,9 @@ static int desc_check(const hpe_conv_desc* d, const char* fn) {
       return fail(HPE_EUNSUPPORTED, "%s: the fused head needs a ReLU deconv / stride-1 conv with Cout = 256, no residual, no second input", fn);
   }
   if (d->chain) {
-    if ((d->chain != 64 && d->chain != 128) || d->kind != HPE_CONV_1x1 || d->stride != 1 || d->Cout != 256 || d->head2 || d->out_cstride ||
-        d->act != HPE_ACT_RELU)
-      return fail(HPE_EUNSUPPORTED, "%s: a chained 1x1 conv (64 or 128 outputs) needs a dense ReLU 1x1 stride-1 layer with Cout = 256", fn);
+    const bool shape_ok = (d->Cout == 256 && (d->chain == 64 || d->chain == 128)) || (d->Cout == 512 && d->chain == 128);
+    if (!shape_ok || d->kind != HPE_CONV_1x1 || d->stride != 1 || d->head2 || d->out_cstride || d->act != HPE_ACT_RELU)
+      return fail(HPE_EUNSUPPORTED, "%s: a chained 1x1 conv needs a dense ReLU 1x1 stride-1 layer with Cout = 256 (64 | 128 chained outputs) or 512 (128)", fn);
   }
   if (d->Cin2) {
     if (d->kind != HPE_CONV_1x1 || d->stride != 1) return fail(HPE_EUNSUPPORTED, "%s: a second input needs a 1x1 stride-1 main conv", fn);
@@ -1217,7 +1253,13 @@ static ConvKernelFn pick_kernel_epi2(int act, size_t* smem) {
 
 // chained 1x1 (N2 = 64 | 128) behind a 256-wide single-CTA ReLU tile: 2 ring stages of 48 KB, 4 (N2 = 128 with a residual: 3)
 // staging buffers, the chained weights resident
-static ConvKernelFn pick_kernel_chain(int n2, bool res, int num_kb, size_t* smem) {
+static ConvKernelFn pick_kernel_chain(int cout, int n2, bool res, int num_kb, size_t* smem) {
+  if (cout == 512) {       // layer2: two 256-wide halves per pixel tile, streamed weights (main ring 2 x 48 KB, 3 chained K slices)
+    if (n2 != 128) return nullptr;
+    *smem = SmemLayout<256, 2, false, 4, false, false, 128, 0, 2>::kDynamic;
+    return res ? conv_gemm_kernel<256, 2, HPE_ACT_RELU, true, false, false, false, false, 128, 0, 2>
+               : conv_gemm_kernel<256, 2, HPE_ACT_RELU, false, false, false, false, false, 128, 0, 2>;
+  }
   // (N2, residual, k-blocks per tile) of the three layer1 cases: conv3 (K = 64) + identity shortcut -> conv1 64 | 128, and the
   // first block's two-source conv3 (K = 64 + 64, projection shortcut folded in) -> conv1 64
   if (n2 == 64 && res && num_kb == 1) {
@@ -1285,7 +1327,7 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
   p.tw = tw; p.th = th; p.nb = nb;
   p.tiles_x = (p.Wo + tw - 1) / tw; p.tiles_y = (p.Ho + th - 1) / th; p.tiles_b = (p.B + nb - 1) / nb;
   pl->block_n = pick_block_n(d, (long long)p.tiles_x * p.tiles_y * p.tiles_b * p.n_classes);
-  p.n_tiles_n = d->kind == HPE_CONV_FINAL ? 1 : (d->Cout + pl->block_n - 1) / pl->block_n;
+  p.n_tiles_n = (d->kind == HPE_CONV_FINAL || d->chain) ? 1 : (d->Cout + pl->block_n - 1) / pl->block_n;   // chain: all of Cout in one CTA
   p.cout_total = d->out_cstride ? d->out_cstride : d->Cout;
   if (is_class_strided(d->kind) && d->Cout % pl->block_n) { delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: parity-class kinds need Cout %% %d == 0", pl->block_n); }
   if (p.n_tiles_n * pl->block_n > kMaxCout) { delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: padded Cout exceeds %d", kMaxCout); }
@@ -1320,7 +1362,7 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
     const int num_kb = p.taps * p.kc_per_tap + p.kc2;
     pl->epi2 = mode != 0 && pl->pair && pl->block_n == 256 && p.has_res && !d->head2 && d->act != HPE_ACT_GELU && (mode == 2 || num_kb <= 8);
   }
-  pl->fn = d->chain ? (const void*)pick_kernel_chain(d->chain, p.has_res != 0, p.taps * p.kc_per_tap + p.kc2, &pl->smem)
+  pl->fn = d->chain ? (const void*)pick_kernel_chain(d->Cout, d->chain, p.has_res != 0, p.taps * p.kc_per_tap + p.kc2, &pl->smem)
                     : (const void*)pick_kernel(pl->block_n, d->act, p.has_res != 0, d->kind == HPE_CONV_FINAL, pl->pair != 0, d->head2 != 0, pl->epi2 != 0, &pl->smem);
   if (!pl->fn) { const int bn = pl->block_n; delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: no kernel for BLOCK_N=%d%s", bn, d->chain ? " (chained layers: Cin = 64 with a residual, or Cin = Cin2 = 64 without)" : ""); }
   {
@@ -1463,8 +1505,8 @@ static int encode_plan_maps(hpe_conv_plan* pl, const void* x, const void* x2, co
   if (d.chain && (w2 != pl->w2 || y2 != pl->y2)) {       // chained 1x1: weights [N2][256] -> tmOut.m[2], dense output [B,Ho,Wo,N2] -> tmOut.m[1]
     HPE_CHECK_ARG(w2 && y2 && (((uintptr_t)w2 | (uintptr_t)y2) & 15) == 0, "hpe_conv_run_chain: w2 / y2 must be non-null and 16-byte aligned");
     {
-      const uint64_t dims[2] = {256, (uint64_t)d.chain};
-      const uint64_t str[1] = {256 * 2};
+      const uint64_t dims[2] = {(uint64_t)d.Cout, (uint64_t)d.chain};      // [N2 rows][K = Cout]
+      const uint64_t str[1] = {(uint64_t)d.Cout * 2};
       const uint32_t box[2] = {64, (uint32_t)d.chain};
       rc = encode_map(&pl->tmOut.m[2], w2, 2, dims, str, box, ones, "chain W");
       if (rc) return rc;

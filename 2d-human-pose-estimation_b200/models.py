@@ -269,6 +269,7 @@ class _ForwardPlan:
         # conv3 (+ shortcut + ReLU) of a layer1 Bottleneck and conv1 (+ BN + ReLU) of the NEXT block in one kernel (desc.chain): the
         # 256-channel block output is read once (as the next shortcut) instead of twice, and one launch per block disappears
         fuse_chain = os.environ.get("HPE_B200_FUSE_CHAIN", "1") != "0"
+        fuse_chain2 = int(os.environ.get("HPE_B200_FUSE_CHAIN2", "1"))         # ... and the 512 -> 128 chains inside layer2 (2: also behind its first block)
         self.chained = {}        # conv1 path -> the conv3 path whose kernel computes it
         pending_chain = None     # (conv3 name, t1 buffer key) while the next block's conv1 is still to be declared
         self.bufs = {}
@@ -326,7 +327,10 @@ class _ForwardPlan:
                 sc = cur
                 # chain the next block's conv1 (256 -> 64 | 128) behind this conv3 when the block output has 256 channels (layer1)
                 nxt = (f"backbone.layer{i + 1}.{j + 1}", p) if j + 1 < n else ((f"backbone.layer{i + 2}.0", _PLANES[i + 1]) if i + 1 < 4 else None)
-                n2 = nxt[1] if (fuse_chain and nxt and 4 * p == 256 and nxt[1] in (64, 128) and not res_mma and self.df_stages == 0) else 0
+                # (layer2: identity blocks only -- the first block's two-source conv3 runs 6 k-blocks per 256-wide half through a
+                #  2-stage ring and a single accumulator: measured 165 us chained against 81 + 45 us as two launches)
+                ok = nxt and ((4 * p == 256 and nxt[1] in (64, 128)) or (4 * p == 512 and nxt[1] == 128 and fuse_chain2 and (j > 0 or fuse_chain2 == 2)))
+                n2 = nxt[1] if (fuse_chain and ok and not res_mma and self.df_stages == 0) else 0
                 d2 = nxt[0] + ".t1" if n2 else None
                 if j == 0 and not fuse_sc:
                     add(pre + ".downsample.0", ConvLayer(CONV_1x1, B, h, w, cin, 4 * p, s, ACT_NONE, False, dev), cur, pre + ".sc")
@@ -450,7 +454,7 @@ class _ForwardPlan:
             d = layer.desc
             m = d.B * layer.Ho * layer.Wo * (self.n_chunks if k < self.n_section_ops else 1)      # per step
             taps = {CONV_1x1: 1, CONV_3x3: 9, CONV_STEM7x7: 49, CONV_DECONV4: 4, CONV_FINAL: 1}[d.kind]
-            flops = 2.0 * m * d.Cin * d.Cout * taps + 2.0 * m * d.Cin2 * d.Cout + 2.0 * m * 256 * (layer.head2 + layer.chain)
+            flops = 2.0 * m * d.Cin * d.Cout * taps + 2.0 * m * d.Cin2 * d.Cout + 2.0 * m * 256 * layer.head2 + 2.0 * m * d.Cout * layer.chain
             if name.startswith("deconv") or name == "final_layer":
                 fam = "deconv_head"
             elif name == "backbone.conv1":

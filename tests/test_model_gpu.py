@@ -111,7 +111,7 @@ def test_chained_conv1_is_bit_identical(pair, cuda_dev, monkeypatch, B):
     x = torch.rand(B, 3, 256, 192, generator=torch.Generator().manual_seed(90 + B)).to(cuda_dev)
     hm = m(x).clone()
     plan = m._plans[(tuple(x.shape), cuda_dev.index)]
-    assert len(plan.chained) == 3, plan.chained          # layer1.1.conv1, layer1.2.conv1, layer2.0.conv1
+    assert len(plan.chained) == 5, plan.chained          # layer1.{1,2}.conv1, layer2.{0,2,3}.conv1
     t1 = {k: plan.bufs[k.replace("conv1", "t1")].clone() for k in plan.chained}
     monkeypatch.setenv("HPE_B200_FUSE_CHAIN", "0")
     plain = models.HeatmapPose(17, "resnet50", pretrained=False)
