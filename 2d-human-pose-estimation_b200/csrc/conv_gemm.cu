@@ -66,6 +66,7 @@ struct ConvParams {
   const float* bias2;           // fused head: conv bias [K]
   const float* scale2;          // CHAIN: folded-BN scale / shift [N2] of the chained 1x1 conv
   const float* shift2;
+  int res_prefetch;             // != 0: the residual producer prefetches the NEXT tile's residual boxes into L2 while it serves this one
 };
 
 struct TileCoord { int n_tile, cls, x0, y0, b0; };
@@ -119,7 +120,7 @@ struct SmemLayout {
   static constexpr int kOffB   = STAGES * kABytes;
   static constexpr int kOffSB  = kOffB + (KBR ? KBR : STAGES) * kBBytes;
   static constexpr int kOffSS  = kOffSB + NSB * kSBBytes;             // float scale[kMaxBlockN], shift[kMaxBlockN] (x 2 groups with EPI2)
-  static constexpr int kOffSS2 = kOffSS + ((EPI2 || NH == 2) ? 4 : 2) * kMaxBlockN * 4;      // CHAIN: float scale2[128], shift2[128]
+  static constexpr int kOffSS2 = kOffSS + ((EPI2 || NH >= 2) ? 4 : 2) * kMaxBlockN * 4;      // CHAIN: float scale2[128], shift2[128]
   static constexpr int kOffW2  = kOffSS2 + (CHAIN ? 1024 : 0);                  // 1024-byte aligned
   static constexpr int kOffBar = kOffW2 + kW2Bytes;
   static constexpr int kNumBar = 2 * STAGES + 4 + 4 * NSB + 7 + 2 * kW2Slots;       // + g2done[NSB], staged[NSB] (CHAIN) + w2full, s2full, d2full[2], a2empty[2], wres + w2 ring full/empty
@@ -252,13 +253,16 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   // residual the buffer of chunk q-1 is handed to the producer at the top of chunk q -> 3 buffers give a lead of 2.
   static_assert(!HEAD2 || (PAIR && BLOCK_N == 256 && !RES && !FINAL), "fused head: pair kernel, 256 channels, no residual");
   static_assert(!EPI2 || (!FINAL && !HEAD2), "two epilogue groups: bf16 NHWC TMA-store path only");
-  static_assert(!CHAIN || ((CHAIN == 64 || CHAIN == 128) && BLOCK_N == 256 && !PAIR && !HEAD2 && !EPI2 && !FINAL), "chained 1x1: single-CTA 256-wide tiles");
+  static_assert(!CHAIN || ((CHAIN == 64 || CHAIN == 128) && (BLOCK_N == 256 || BLOCK_N == 128) && !PAIR && !HEAD2 && !EPI2 && !FINAL), "chained 1x1: single-CTA tiles");
+  // CHAIN with 128-wide tiles (Cout 512 as FOUR quarters per pixel tile): the main accumulator is double-buffered again (2 x 128 +
+  // 2 x 128 chained columns), so the MMAs of quarter i+1 overlap the epilogue of quarter i, and a 32 KB ring stage is one k-block
+  constexpr bool kAcc2x = CHAIN != 0 && BLOCK_N == 128;
   constexpr int kGroups = EPI2 ? 2 : 1;
   // per group; the fp32 heatmap epilogue stores from registers: all smem to the ring.  CHAIN = 128: its 64 KB of resident weights
   // leave room for 3 buffers only (residual lead 1)
   static_assert(!(CHAIN == 128 && NH == 1 && !RES), "chained 128-wide conv behind 256 channels: residual variant only (shared-memory budget)");
   static_assert((KBR != 0) == (CHAIN != 0 && NH == 1) && KBR <= 2, "resident weights: the 256-channel chained kernels (1-2 k-blocks per tile)");
-  static_assert(NH == 1 || (NH == 2 && CHAIN == 128), "two halves per pixel tile: the 512 -> 128 chain of layer2");
+  static_assert(NH == 1 || ((NH == 2 || NH == 4) && CHAIN == 128 && NH * BLOCK_N == 512), "several N tiles per pixel tile: the 512 -> 128 chain of layer2");
   // CHAIN: one ring for both groups, as deep as fits (the residual rides it with a lead of kNumSB - 2 chunks)
   constexpr int kNumSB = FINAL ? 0 : (CHAIN ? ((RES && CHAIN == 64) ? 6 : 4) : (EPI2 ? (RES ? 3 : 2) : ((RES || HEAD2) ? 4 : 3)));
   constexpr int kResLead = 2;                     // the residual of chunk q + 2 is requested while chunk q is processed
@@ -393,8 +397,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       int stage = 0; uint32_t phase = 0; int it = 0;
       if constexpr (KBR != 0) mbar_wait(wres_bar, 0);
       for (int work = work0; work < p.num_tiles; work += wstep) for (int nh = 0; nh < NH; ++nh, ++it) {     // it counts (tile, half)
-        const int acc = CHAIN ? 0 : (it & 1);     // CHAIN: one main accumulator (columns 256.. hold the chained conv's)
-        mbar_wait(&tempty_bar[acc], (CHAIN ? (it & 1) : ((it >> 1) & 1)) ^ 1);
+        const int acc = (CHAIN && !kAcc2x) ? 0 : (it & 1);     // CHAIN (256-wide): one main accumulator (columns 256.. hold the chained conv's)
+        mbar_wait(&tempty_bar[acc], ((CHAIN && !kAcc2x) ? (it & 1) : ((it >> 1) & 1)) ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
         const int num_kb = kb_count(p, tile_coord(p, work_tile<PAIR>(p, work, 0)).cls);
@@ -453,6 +457,12 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         int r = 0;
         for (int work = work0; work < p.num_tiles; work += wstep) {
           const TileCoord t = tile_coord(p, work_tile<PAIR>(p, work, rank));
+          if (p.res_prefetch && work + wstep < p.num_tiles) {
+            // the ring's lead (2-4 chunks) is shorter than the HBM latency once two epilogue groups drain it: pull the next tile's
+            // residual into L2 a whole tile ahead, so the ring's own loads are L2 hits
+            const TileCoord tn = tile_coord(p, work_tile<PAIR>(p, work + wstep, rank));
+            for (int c = 0; c < NH * kChunks; ++c) tma_prefetch_l2_4d(&tmRes, tn.n_tile * NH * BLOCK_N + c * 64, tn.x0, tn.y0, tn.b0);
+          }
           for (int c = 0; c < NH * kChunks + kChunks2; ++c, ++r) {
             const int b = r % kNumSB;
             mbar_wait(&sbempty_bar[b], (r / kNumSB) & 1);   // the epilogue leader hands buffers over with a lead of kResLead chunks
@@ -474,6 +484,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         constexpr uint32_t kIdesc2 = make_idesc_bf16_m128(CHAIN);
         constexpr int kSlice = CHAIN * 128;                      // bytes of one [N2][64] K slice of the chained weights
         if constexpr (NH == 1) mbar_wait(w2full_bar, 0);
+        static_assert(NH == 1 || BLOCK_N * NH == 512, "");
         int q = 0, it = 0;
         // NH = 2: the K slices stream through kW2Slots buffers, requested kW2Slots - 1 real chunks ahead
         int w_req = 0, w_use = 0;                                // slices requested / consumed so far (over the whole kernel)
@@ -486,17 +497,17 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           tma_load_2d(sW2 + slot * kSlice, &tmOut.m[2], &w2rfull_bar[slot], (w_req % kCT) * kKBlock, 0);
           ++w_req;
         };
-        if constexpr (NH == 2) { while (w_req < kW2Slots - 1 && w_req < w_total) request(); }
+        if constexpr (NH >= 2) { while (w_req < kW2Slots - 1 && w_req < w_total) request(); }
         for (int work = work0; work < p.num_tiles; work += wstep, ++it) {
           const int a2 = it & 1;
           mbar_wait(&a2empty_bar[a2], ((it >> 1) & 1) ^ 1);      // tile it-2's chained output has left accumulator a2
           for (int c = 0; c < kCPT; ++c, ++q) {
             const int sb = q % kNumSB;
-            if (NH == 2 && c < kCT && w_req < w_total) request();
+            if (NH >= 2 && c < kCT && w_req < w_total) request();
             mbar_wait(&staged_bar[sb], (q / kNumSB) & 1);
             if (c < kCT) {
               const uint8_t* wsl = sW2 + c * kSlice;
-              if constexpr (NH == 2) {
+              if constexpr (NH >= 2) {
                 const int slot = w_use % kW2Slots;
                 mbar_wait(&w2rfull_bar[slot], (w_use / kW2Slots) & 1);
                 wsl = sW2 + slot * kSlice;
@@ -505,8 +516,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               const uint64_t adesc = make_sw128_kmajor_desc(sSB + sb * kSBBytes);
               const uint64_t bdesc = make_sw128_kmajor_desc(wsl);
 #pragma unroll
-              for (int k = 0; k < 4; ++k) umma_bf16(tmem_base + BLOCK_N + a2 * CHAIN, adesc + 2 * k, bdesc + 2 * k, kIdesc2, (c | k) != 0);
-              if constexpr (NH == 2) { umma_commit(&w2rempty_bar[w_use % kW2Slots]); ++w_use; }
+              for (int k = 0; k < 4; ++k) umma_bf16(tmem_base + 256 + a2 * CHAIN, adesc + 2 * k, bdesc + 2 * k, kIdesc2, (c | k) != 0);
+              if constexpr (NH >= 2) { umma_commit(&w2rempty_bar[w_use % kW2Slots]); ++w_use; }
             }
             umma_commit(&g2_bar[sb]);                            // every chunk commits: a buffer's phase sequence stays uniform
             if (c == kCT - 1) umma_commit(&d2full_bar[a2]);
@@ -547,16 +558,17 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           if (q >= 2) mbar_wait(&g2_bar[(q - 2) % kNumSB], ((q - 2) / kNumSB) & 1);     // ... and the second GEMM has read chunk q-2
           if (RES) mbar_arrive(&sbempty_bar[(q + kLead) % kNumSB]);                     // = chunk q-2's buffer: to the residual producer
         }
-        if (e2) mbar_wait(&d2full_bar[a2], (it >> 1) & 1); else mbar_wait(&tfull_bar[0], (it * NH + nh) & 1);
+        const int ih = it * NH + nh, a1 = kAcc2x ? (ih & 1) : 0;              // main-accumulator use number / buffer
+        if (e2) mbar_wait(&d2full_bar[a2], (it >> 1) & 1); else mbar_wait(&tfull_bar[a1], kAcc2x ? ((ih >> 1) & 1) : (ih & 1));
         tc_fence_after();
         uint32_t v[32];
-        tmem_ld_x32(e2 ? taddr0 + BLOCK_N + a2 * CHAIN + cc * 64 + half * 32 : taddr0 + cc * 64 + half * 32, v);
+        tmem_ld_x32(e2 ? taddr0 + 256 + a2 * CHAIN + cc * 64 + half * 32 : taddr0 + a1 * BLOCK_N + cc * 64 + half * 32, v);
         if (RES) mbar_wait(&sbfull_bar[sb], (q / kNumSB) & 1);
         tmem_ld_wait();
         if (e2 || cc + 2 >= kChunks) {                           // this group's last read of the main (half) / of the chained accumulator
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(e2 ? &a2empty_bar[a2] : &tempty_bar[0]);
+          if (lane == 0) mbar_arrive(e2 ? &a2empty_bar[a2] : &tempty_bar[a1]);
         }
         const int n0 = (e2 ? cc : c) * 64 + half * 32;
         epi_chunk_math<ACT>(v, smem_u32((e2 ? sScale2 : scl) + n0), smem_u32((e2 ? sShift2 : shf) + n0),
@@ -1254,11 +1266,11 @@ static ConvKernelFn pick_kernel_epi2(int act, size_t* smem) {
 // chained 1x1 (N2 = 64 | 128) behind a 256-wide single-CTA ReLU tile: 2 ring stages of 48 KB, 4 (N2 = 128 with a residual: 3)
 // staging buffers, the chained weights resident
 static ConvKernelFn pick_kernel_chain(int cout, int n2, bool res, int num_kb, size_t* smem) {
-  if (cout == 512) {       // layer2: two 256-wide halves per pixel tile, streamed weights (main ring 2 x 48 KB, 3 chained K slices)
+  if (cout == 512) {       // layer2: four 128-wide quarters per pixel tile, streamed weights (ring 3 x 32 KB, 3 chained K slices)
     if (n2 != 128) return nullptr;
-    *smem = SmemLayout<256, 2, false, 4, false, false, 128, 0, 2>::kDynamic;
-    return res ? conv_gemm_kernel<256, 2, HPE_ACT_RELU, true, false, false, false, false, 128, 0, 2>
-               : conv_gemm_kernel<256, 2, HPE_ACT_RELU, false, false, false, false, false, 128, 0, 2>;
+    *smem = SmemLayout<128, 3, false, 4, false, false, 128, 0, 4>::kDynamic;
+    return res ? conv_gemm_kernel<128, 3, HPE_ACT_RELU, true, false, false, false, false, 128, 0, 4>
+               : conv_gemm_kernel<128, 3, HPE_ACT_RELU, false, false, false, false, false, 128, 0, 4>;
   }
   // (N2, residual, k-blocks per tile) of the three layer1 cases: conv3 (K = 64) + identity shortcut -> conv1 64 | 128, and the
   // first block's two-source conv3 (K = 64 + 64, projection shortcut folded in) -> conv1 64
@@ -1327,6 +1339,7 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
   p.tw = tw; p.th = th; p.nb = nb;
   p.tiles_x = (p.Wo + tw - 1) / tw; p.tiles_y = (p.Ho + th - 1) / th; p.tiles_b = (p.B + nb - 1) / nb;
   pl->block_n = pick_block_n(d, (long long)p.tiles_x * p.tiles_y * p.tiles_b * p.n_classes);
+  if (d->chain && d->Cout == 512) pl->block_n = 128;       // four quarters per pixel tile inside one CTA
   p.n_tiles_n = (d->kind == HPE_CONV_FINAL || d->chain) ? 1 : (d->Cout + pl->block_n - 1) / pl->block_n;   // chain: all of Cout in one CTA
   p.cout_total = d->out_cstride ? d->out_cstride : d->Cout;
   if (is_class_strided(d->kind) && d->Cout % pl->block_n) { delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: parity-class kinds need Cout %% %d == 0", pl->block_n); }
@@ -1594,6 +1607,14 @@ static int conv_launch(hpe_conv_plan* pl, const void* x, const void* x2, const v
   p.hm_out = (pl->d.kind == HPE_CONV_FINAL || pl->d.head2) ? (float*)y : nullptr;
   p.bias2 = bias2;
   p.scale2 = scale2; p.shift2 = shift2;
+  {
+    // residual L2 prefetch one tile ahead (experiment, OFF: measured slower -- forward 3.12 / 3.20 ms off, 3.20 / 3.23 ms on the
+    // chained kernels, 3.23 ms on every residual layer; like the A-stream prefetch of round 1, the prefetches only compete with
+    // the demand loads of an HBM-bound kernel): HPE_B200_RES_PREFETCH = 1 chained kernels, 2 every residual layer
+    static int mode = -1;
+    if (mode < 0) { const char* e = getenv("HPE_B200_RES_PREFETCH"); mode = e ? atoi(e) : 0; }
+    p.res_prefetch = p.has_res && (mode == 2 || (mode == 1 && pl->d.chain)) ? 1 : 0;
+  }
   if (!p.has_res && !pl->d.head2) pl->tmRes = pl->tmA;      // unused, but must be a valid object to copy
   if (pl->d.kind == HPE_CONV_FINAL || pl->d.head2) for (int c = 0; c < 4; ++c) pl->tmOut.m[c] = pl->tmA;
   if (!pl->d.Cin2) pl->tmA2 = pl->tmA;      // unused, but must be a valid object to copy
