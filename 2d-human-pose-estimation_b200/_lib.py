@@ -77,6 +77,14 @@ SIGNATURES = {
     "hpe_dwconv": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _f, _vp, _i, _vp]),
     "hpe_dwconv7_bias": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _i, _vp]),
     "hpe_layernorm_nhwc": (_i, [_vp, _i, C.c_longlong, _i, _vp, _vp, _f, _vp, _i, _vp]),
+    "hpe_bnact_scratch_elems": (_sz, [_i]),
+    "hpe_bnact_stats": (_i, [_vp, C.c_longlong, _i, _vp, _vp, _f, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "hpe_bnact_apply": (_i, [_vp, C.c_longlong, _i, _vp, _vp, _i, _vp, _vp]),
+    "hpe_bnact_backward": (_i, [_vp, _vp, C.c_longlong, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp]),
+    "hpe_dwconv3_wgrad_scratch_elems": (_sz, [_i]),
+    "hpe_dwconv3_wgrad": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp]),
+    "hpe_maxpool5_backward": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp]),
+    "hpe_upsample_bilinear_backward": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp]),
     "hpe_patchify4": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "hpe_patchify4_u8": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "hpe_maxpool5": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _i, _vp]),

@@ -97,7 +97,7 @@ dwconv_kernel(const __nv_bfloat16* __restrict__ x, int in_pitch, const float* __
       if (ox0 + r < W) {
         float o[8];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) { const float t = fmaf(acc[r][e], sc[e], sh[e]); o[e] = t / (1.f + __expf(-t)); }
+        for (int e = 0; e < 8; ++e) { const float t = fmaf(acc[r][e], sc[e], sh[e]); o[e] = eps < 0.f ? t : t / (1.f + __expf(-t)); }   // eps < 0: no activation (training: raw conv output)
         *reinterpret_cast<uint4*>(yo + static_cast<size_t>(r) * out_pitch) = pack8(o);
       }
     }

@@ -194,7 +194,7 @@ class _PosePlan:
     ``heatmap_head=True``: ``model`` is a ``HeatmapPose`` with a ConvNeXt backbone -- the four ConvNeXt stages feed the App. A.1
     deconv heatmap head instead of adaptor + SPPF + PAN + PoseHead."""
 
-    def __init__(self, model, B, H, W, device, heatmap_head=False):
+    def __init__(self, model, B, H, W, device, heatmap_head=False, backbone_only=False):
         if H % 32 or W % 32:
             raise ValueError(f"input {H}x{W} must be a multiple of 32")
         self.B, self.H, self.W, self.dev = B, H, W, device
@@ -202,6 +202,7 @@ class _PosePlan:
         self.keep = []                    # device tensors owned by the plan (packed weights live in the ConvLayers)
         self.n_launches = 0
         self.graph = None
+        self.levels = None                # backbone_only plans have no head outputs
         dims, depths = model.dims, model.depths
         bf = lambda *shape: torch.zeros(shape, dtype=torch.bfloat16, device=device)      # noqa: E731
         f32 = lambda t: t.detach().to(device, torch.float32).contiguous()               # noqa: E731
@@ -282,6 +283,9 @@ class _PosePlan:
                 cur, other = other, cur
             if i > 0:                                # later stages own fresh buffers, so `cur` survives as a pyramid level
                 feats.append((cur, h, w, C))
+        self.feats = [f for f, _, _, _ in feats]      # stage 1-3 outputs (NHWC bf16): the pyramid the neck reads
+        if backbone_only:                                # training: the frozen backbone only; the neck and head run in posetrain.py
+            return
         if heatmap_head:
             self._build_heatmap_head(model, feats[-1], B, device)
             return
@@ -478,8 +482,16 @@ class DINOv3Pose(nn.Module):
         plan.run(x.contiguous() if x.dtype == torch.uint8 else x.float().contiguous())
         return [f.float().permute(0, 3, 1, 2) for f in plan.features]
 
-    @torch.no_grad()
     def forward(self, x):
+        if self.training and torch.is_grad_enabled():
+            # model.train() under autograd (HPE/train.py:116-139): frozen backbone on the inference kernels, the neck and head with
+            # BatchNorm batch statistics and a backward pass through the dgrad / wgrad kernels (posetrain.py)
+            from .posetrain import train_forward
+            return train_forward(self, x)
+        with torch.no_grad():
+            return self._forward_nograd(x)
+
+    def _forward_nograd(self, x):
         plan = self._plan(x)
         levels = plan.run(x.contiguous() if x.dtype == torch.uint8 else x.float().contiguous())   # uint8 = x.float()/255 (train.py:120)
         if self.training:

@@ -1,0 +1,363 @@
+"""Training-mode forward + backward of the reference's real pose model on the sm_100a kernels.
+
+The reference trains ``DINOv3Pose`` with its backbone frozen (``finetuning=True`` -> ``requires_grad = False`` on every ConvNeXt
+parameter, /root/reference/HPE/models/pose.py:47-49; training loop HPE/train.py:116-139: ``preds = model(imgs)`` under
+``model.train()``, ``loss = criterion(preds, targets)``, ``loss.backward()``, ``clip_grad_norm_``, ``AdamW.step()``).  What needs
+gradients is the FeatureAdaptor, SPPF, PAN and PoseHead: 70-odd ``ConvBlock`` units (Conv2d without bias + BatchNorm2d with batch
+statistics + SiLU, block.py:20-45), two plain 1x1 convs and a BatchNorm over a concat per BottleneckCSP (block.py:74-100), a
+depthwise 3x3 ConvBlock per level, three 5x5 max-pools, two bilinear up-samplings, six biased 1x1 output convs.
+
+Here every one of those ops is a ``torch.autograd.Function`` whose forward AND backward are launches of this library:
+
+* convolutions: the tcgen05 implicit-GEMM kernel for the forward (raw output, ``ACT_NONE``), for the backward-data pass
+  (``DgradLayer``: transposed / rotated / parity-class weights) and the tcgen05 wgrad GEMM (``WgradLayer``) -- the kernels the
+  ResNet training step uses (train.py);
+* BatchNorm + SiLU, depthwise 3x3, max-pool, up-sampling and their backward passes: csrc/neck_train_ops.cu, convnext_ops.cu;
+* the frozen backbone: the inference launch plan (posemodel._PosePlan, CUDA-graph replay), no autograd.
+
+PyTorch's autograd only does the bookkeeping of the graph (which Function feeds which, summing the gradients of a tensor with
+several consumers, splitting the gradient of ``torch.cat``); activations are NHWC bf16, parameters and their gradients fp32, exactly
+the tensors ``model.parameters()`` exposes, so ``torch.optim.AdamW`` / ``clip_grad_norm_`` -- or ``hpe_adamw_step`` -- work unchanged.
+Channel counts that are not multiples of 64 (96 inside ``fpn_conv4``, 51 in the keypoint branch) run zero-padded to the next
+multiple of 64; the padding stays exactly zero through BN (beta_pad = 0) and SiLU and is sliced off before a concat.
+There is no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+import torch.nn.functional as F
+
+from . import _lib
+from ._lib import ACT_NONE, CONV_1x1, CONV_3x3, CONV_FINAL
+from .conv import ConvLayer, DgradLayer, WgradLayer
+from .posemodel import _PosePlan, _dwconv, _maxpool5, _upsample
+
+ACT_SILU_BN = 2          # act code of the hpe_bnact_* kernels: 0 none, 1 ReLU, 2 SiLU
+
+
+def _cp(c: int) -> int:
+    return (c + 63) // 64 * 64
+
+
+def _plans(model):
+    if not hasattr(model, "_tplans"):
+        model._tplans = {}
+    return model._tplans
+
+
+def _f32(n, dev, fill=None):
+    t = torch.empty(n, dtype=torch.float32, device=dev)
+    if fill is not None:
+        t.fill_(fill)
+    return t
+
+
+# ------------------------------------------------------------------------------------------------- convolution
+class _ConvSpec:
+    """Forward / backward-data / weight-gradient plans of one conv at one input shape (channels padded to multiples of 64)."""
+
+    def __init__(self, kind, B, H, W, cin, cout, stride, dev, need_dx):
+        self.cin, self.cout, self.cinp, self.coutp = cin, cout, _cp(cin), _cp(cout)
+        self.k = 3 if kind == CONV_3x3 else 1
+        self.fwd = ConvLayer(kind, B, H, W, self.cinp, self.coutp, stride, ACT_NONE, False, dev)
+        self.dgrad = DgradLayer(kind, B, H, W, self.cinp, self.coutp, stride, device=dev) if need_dx else None
+        self.wgrad = WgradLayer(kind, B, H, W, self.cinp, self.coutp, stride, dev)
+
+    def pad_weight(self, w):
+        if self.cinp == self.cin and self.coutp == self.cout:
+            return w.detach().float().contiguous()
+        wp = torch.zeros((self.coutp, self.cinp, self.k, self.k), dtype=torch.float32, device=w.device)
+        wp[:self.cout, :self.cin] = w.detach()
+        return wp
+
+
+class ConvFn(torch.autograd.Function):
+    """``z = conv(x, w)`` (no bias): Conv2d of a ConvBlock / BottleneckCSP.cv2 / cv3 (block.py:24, 82-83)."""
+
+    @staticmethod
+    def forward(ctx, x, w, spec):
+        wp = spec.pad_weight(w)
+        spec.fwd.load(wp)
+        z = spec.fwd(x)
+        ctx.save_for_backward(x, wp)
+        ctx.spec = spec
+        return z
+
+    @staticmethod
+    def backward(ctx, dz):
+        x, wp = ctx.saved_tensors
+        spec = ctx.spec
+        dz = dz.contiguous()
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            spec.dgrad.load(wp)
+            dx = spec.dgrad(dz)
+        if ctx.needs_input_grad[1]:
+            dwp = torch.empty_like(wp)
+            spec.wgrad(x, dz, dwp)
+            dw = dwp[:spec.cout, :spec.cin].contiguous() if dwp.shape[:2] != (spec.cout, spec.cin) else dwp
+        return dx, dw, None
+
+
+def conv(model, mod, x, kind, stride=1, need_dx=True):
+    """``mod``: the nn.Conv2d parameter container; x NHWC bf16 with ceil64(Cin) channels."""
+    B, H, W, _ = x.shape
+    key = ("conv", id(mod), B, H, W, need_dx)
+    spec = _plans(model).get(key)
+    if spec is None:
+        spec = _plans(model)[key] = _ConvSpec(kind, B, H, W, mod.in_channels, mod.out_channels, stride, x.device, need_dx)
+    return ConvFn.apply(x.contiguous(), mod.weight, spec)
+
+
+# ------------------------------------------------------------------------------------------------- BatchNorm + activation
+class BNActFn(torch.autograd.Function):
+    """``y = act(BatchNorm2d(z))`` with BATCH statistics (model.train()); running statistics updated as torch does."""
+
+    @staticmethod
+    def forward(ctx, z, gamma, beta, bn, act):
+        Cp, Cr = z.shape[-1], gamma.numel()
+        M = z.numel() // Cp
+        dev = z.device
+        g, b = gamma.detach().float(), beta.detach().float()
+        rm, rv = bn.running_mean, bn.running_var
+        if Cp != Cr:                                  # zero-padded channels: gamma 1, beta 0 keep them exactly zero
+            g = torch.cat([g, torch.ones(Cp - Cr, device=dev)]); b = torch.cat([b, torch.zeros(Cp - Cr, device=dev)])
+            rm = torch.cat([rm, torch.zeros(Cp - Cr, device=dev)]); rv = torch.cat([rv, torch.ones(Cp - Cr, device=dev)])
+        g, b = g.contiguous(), b.contiguous()
+        scale, shift, mean, rstd = (_f32(Cp, dev) for _ in range(4))
+        scratch = _f32(_lib.lib().hpe_bnact_scratch_elems(Cp), dev)
+        mom = bn.momentum if bn.momentum is not None else 0.1
+        with torch.cuda.device(dev):
+            _lib.check(_lib.lib().hpe_bnact_stats(_lib.ptr(z), M, Cp, _lib.ptr(g), _lib.ptr(b), float(bn.eps), float(mom), _lib.ptr(rm),
+                                                  _lib.ptr(rv), _lib.ptr(scratch), _lib.ptr(scale), _lib.ptr(shift), _lib.ptr(mean),
+                                                  _lib.ptr(rstd), _lib.stream_ptr()), "hpe_bnact_stats")
+            y = torch.empty_like(z)
+            _lib.check(_lib.lib().hpe_bnact_apply(_lib.ptr(z), M, Cp, _lib.ptr(scale), _lib.ptr(shift), int(act), _lib.ptr(y),
+                                                  _lib.stream_ptr()), "hpe_bnact_apply")
+        if Cp != Cr:
+            bn.running_mean.copy_(rm[:Cr]); bn.running_var.copy_(rv[:Cr])
+        if bn.num_batches_tracked is not None:
+            bn.num_batches_tracked += 1
+        ctx.save_for_backward(z, g, scale, shift, mean, rstd)
+        ctx.act, ctx.Cr = int(act), Cr
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        z, g, scale, shift, mean, rstd = ctx.saved_tensors
+        Cp = z.shape[-1]
+        M = z.numel() // Cp
+        dev = z.device
+        dy = dy.contiguous()
+        dz = torch.empty_like(z)
+        dbeta, dgamma = _f32(Cp, dev), _f32(Cp, dev)
+        scratch = _f32(_lib.lib().hpe_bnact_scratch_elems(Cp), dev)
+        with torch.cuda.device(dev):
+            _lib.check(_lib.lib().hpe_bnact_backward(_lib.ptr(dy), _lib.ptr(z), M, Cp, _lib.ptr(mean), _lib.ptr(rstd), _lib.ptr(g),
+                                                     _lib.ptr(scale), _lib.ptr(shift), ctx.act, _lib.ptr(scratch), _lib.ptr(dbeta),
+                                                     _lib.ptr(dgamma), _lib.ptr(dz), _lib.stream_ptr()), "hpe_bnact_backward")
+        return dz, dgamma[:ctx.Cr].contiguous(), dbeta[:ctx.Cr].contiguous(), None, None
+
+
+def bn_act(bn, z, act=ACT_SILU_BN):
+    return BNActFn.apply(z.contiguous(), bn.weight, bn.bias, bn, act)
+
+
+def conv_block(model, cb, x, need_dx=True):
+    """ConvBlock.forward (block.py:41-42): act(bn(conv(x))), 1x1 / 3x3, stride 1 | 2, SiLU."""
+    z = conv(model, cb.conv, x, CONV_3x3 if cb.k == 3 else CONV_1x1, cb.s, need_dx)
+    return bn_act(cb.bn, z)
+
+
+# ------------------------------------------------------------------------------------------------- depthwise 3x3, pool, up-sampling
+class DwConv3Fn(torch.autograd.Function):
+    """Depthwise 3x3 conv (groups = C, pad 1): the head's class branch opens with ConvBlock(x, x, 3, g=x) (head.py:143-144)."""
+
+    @staticmethod
+    def forward(ctx, x, w):
+        Cc = x.shape[-1]
+        wt = w.detach().float().reshape(Cc, 9).t().contiguous()                 # [9][C]
+        one, zero = _f32(Cc, x.device, 1.0), _f32(Cc, x.device, 0.0)
+        y = torch.empty_like(x)
+        _dwconv(x, wt, one, zero, None, -1.0, 3, 0, y)                            # eps < 0: raw output (BN + SiLU follow as their own op)
+        ctx.save_for_backward(x, wt, one, zero)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, wt, one, zero = ctx.saved_tensors
+        B, H, W, Cc = x.shape
+        dy = dy.contiguous()
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(x)
+            _dwconv(dy, wt.flip(0).contiguous(), one, zero, None, -1.0, 3, 0, dx)  # correlation with the 180-degree rotated taps
+        if ctx.needs_input_grad[1]:
+            dw = torch.empty((Cc, 1, 3, 3), dtype=torch.float32, device=x.device)
+            scratch = _f32(_lib.lib().hpe_dwconv3_wgrad_scratch_elems(Cc), x.device)
+            with torch.cuda.device(x.device):
+                _lib.check(_lib.lib().hpe_dwconv3_wgrad(_lib.ptr(x), _lib.ptr(dy), B, H, W, Cc, _lib.ptr(scratch), _lib.ptr(dw),
+                                                        _lib.stream_ptr()), "hpe_dwconv3_wgrad")
+        return dx, dw
+
+
+class MaxPool5Fn(torch.autograd.Function):
+    """MaxPool2d(5, 1, 2) of SPPF (block.py:108, 111-113)."""
+
+    @staticmethod
+    def forward(ctx, x):
+        y = torch.empty_like(x)
+        _maxpool5(x, y)
+        ctx.save_for_backward(x)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x,) = ctx.saved_tensors
+        B, H, W, Cc = x.shape
+        dx = torch.empty_like(x)
+        with torch.cuda.device(x.device):
+            _lib.check(_lib.lib().hpe_maxpool5_backward(_lib.ptr(x), _lib.ptr(dy.contiguous()), B, H, W, Cc, _lib.ptr(dx),
+                                                        _lib.stream_ptr()), "hpe_maxpool5_backward")
+        return dx
+
+
+class UpsampleFn(torch.autograd.Function):
+    """F.interpolate(size=(Ho, Wo), mode='bilinear', align_corners=False) of PAN (block.py:138, 141)."""
+
+    @staticmethod
+    def forward(ctx, x, Ho, Wo):
+        B, Hi, Wi, Cc = x.shape
+        y = torch.empty((B, Ho, Wo, Cc), dtype=x.dtype, device=x.device)
+        _upsample(x, y)
+        ctx.shape = (B, Hi, Wi, Cc, Ho, Wo)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        B, Hi, Wi, Cc, Ho, Wo = ctx.shape
+        dx = torch.empty((B, Hi, Wi, Cc), dtype=dy.dtype, device=dy.device)
+        with torch.cuda.device(dy.device):
+            _lib.check(_lib.lib().hpe_upsample_bilinear_backward(_lib.ptr(dy.contiguous()), B, Hi, Wi, Cc, Ho, Wo, _lib.ptr(dx),
+                                                                 _lib.stream_ptr()), "hpe_upsample_bilinear_backward")
+        return dx, None, None
+
+
+# ------------------------------------------------------------------------------------------------- biased 1x1 output conv
+class _FinalSpec:
+    def __init__(self, B, H, W, cin, K, dev):
+        self.cin, self.cinp, self.K = cin, _cp(cin), K
+        self.fwd = ConvLayer(CONV_FINAL, B, H, W, self.cinp, K, 1, ACT_NONE, False, dev)
+        self.dgrad = DgradLayer(CONV_FINAL, B, H, W, self.cinp, K, 1, device=dev)
+        self.wgrad = WgradLayer(CONV_FINAL, B, H, W, self.cinp, K, 1, dev)
+
+
+class FinalConvFn(torch.autograd.Function):
+    """``nn.Conv2d(c, K, 1)`` with bias -> fp32 NCHW maps: the last layer of the head's class / keypoint branches
+    (head.py:154-160)."""
+
+    @staticmethod
+    def forward(ctx, x, w, b, spec):
+        wp = w.detach().float()
+        if spec.cinp != spec.cin:
+            wp = F.pad(wp, (0, 0, 0, 0, 0, spec.cinp - spec.cin))
+        wp = wp.contiguous()
+        spec.fwd.load(wp, torch.ones(spec.K), b.detach())
+        out = spec.fwd(x)                                   # [B, K, H, W] fp32
+        ctx.save_for_backward(x, wp)
+        ctx.spec = spec
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        from .train import heatmap_grad_nhwc
+        x, wp = ctx.saved_tensors
+        spec = ctx.spec
+        B, H, W, _ = x.shape
+        dout = dout.contiguous().float()
+        g = torch.empty((B, H, W, 64), dtype=torch.bfloat16, device=x.device)       # joints zero-padded to 64
+        db = _f32(spec.K, x.device)
+        heatmap_grad_nhwc(dout, g, db)
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            spec.dgrad.load(wp)
+            dx = spec.dgrad(g)
+        if ctx.needs_input_grad[1]:
+            dwp = torch.empty_like(wp)
+            spec.wgrad(x, g, dwp)
+            dw = dwp[:, :spec.cin].contiguous()
+        return dx, dw, db, None
+
+
+def final_conv(model, mod, x):
+    B, H, W, _ = x.shape
+    key = ("final", id(mod), B, H, W)
+    spec = _plans(model).get(key)
+    if spec is None:
+        spec = _plans(model)[key] = _FinalSpec(B, H, W, mod.in_channels, mod.out_channels, x.device)
+    return FinalConvFn.apply(x.contiguous(), mod.weight, mod.bias, spec)
+
+
+# ------------------------------------------------------------------------------------------------- the model
+def _csp(model, m, x):
+    """BottleneckCSP.forward (block.py:96-100), shortcut=False."""
+    c_ = m.c_
+    y1 = conv_block(model, m.cv1, x)
+    for b in m.m:
+        y1 = conv_block(model, b.cv2, conv_block(model, b.cv1, y1))
+    y1 = conv(model, m.cv3, y1, CONV_1x1)
+    y2 = conv(model, m.cv2, x, CONV_1x1)
+    cat = torch.cat([y1[..., :c_], y2[..., :c_]], -1)            # the zero padding of a 96-channel half is dropped here
+    return conv_block(model, m.cv4, bn_act(m.bn, cat))
+
+
+def train_forward(model, x):
+    """``DINOv3Pose.forward`` under ``model.train()`` with autograd on: the list of raw per-level maps
+    ``[B, nc + nk, H_l, W_l]`` fp32 (head.py:176-181), differentiable w.r.t. every adaptor / SPPF / PAN / head parameter."""
+    if x.dim() != 4 or x.shape[1] != 3:
+        raise ValueError(f"expected [B,3,H,W] input, got {tuple(x.shape)}")
+    if not x.is_cuda:
+        raise RuntimeError("libhpe_b200 has no CPU path: input must live on a CUDA (sm_100a) device")
+    if any(p.requires_grad for p in model.backbone.parameters()):
+        raise RuntimeError("training is built for the reference's configuration: frozen backbone (finetuning=True, pose.py:47-49)")
+    B, _, H, W = x.shape
+    key = ("backbone", B, H, W, x.device.index)
+    plans = _plans(model)
+    plan = plans.get(key)
+    if plan is None:
+        with torch.no_grad():
+            plan = plans[key] = _PosePlan(model, B, H, W, x.device, backbone_only=True)
+    with torch.no_grad():
+        plan.run(x.contiguous() if x.dtype == torch.uint8 else x.float().contiguous())
+        f1, f2, f3 = (f.clone() for f in plan.feats)             # the plan's buffers are overwritten by the next step
+    # ---- FeatureAdaptor (block.py:236-254), SPPF (block.py:102-114)
+    ad = model.adaptor.adapters
+    c1 = conv_block(model, ad[0][1], conv_block(model, ad[0][0], f1, need_dx=False))
+    c2 = conv_block(model, ad[1][1], conv_block(model, ad[1][0], f2, need_dx=False))
+    c3 = conv_block(model, ad[2][1], conv_block(model, ad[2][0], f3, need_dx=False))
+    y = [conv_block(model, model.sppf.conv1, c3)]
+    for _ in range(3):
+        y.append(MaxPool5Fn.apply(y[-1]))
+    c3 = conv_block(model, model.sppf.conv2, torch.cat(y, -1))
+    # ---- PAN (block.py:132-157); F.interpolate to an unchanged size (after down1 / down2) is the identity
+    pan = model.pan
+    up = lambda t, ref: UpsampleFn.apply(t, ref.shape[1], ref.shape[2])          # noqa: E731
+    c2f = _csp(model, pan.fpn_conv2, torch.cat([c2, up(conv_block(model, pan.fpn_conv1, c3), c2)], -1))
+    c1f = _csp(model, pan.fpn_conv4, torch.cat([c1, up(conv_block(model, pan.fpn_conv3, c2f), c1)], -1))
+    c2p = _csp(model, pan.pan_conv1, torch.cat([conv_block(model, pan.down1, c1f), c2f], -1))
+    c3p = _csp(model, pan.pan_conv2, torch.cat([conv_block(model, pan.down2, c2p), c3], -1))
+    # ---- PoseHead (head.py:173-181)
+    hd = model.head
+    outs = []
+    for i, f in enumerate((c1f, c2p, c3p)):
+        dw = hd.cv3[i][0][0]
+        t = bn_act(dw.bn, DwConv3Fn.apply(f.contiguous(), dw.conv.weight))
+        t = conv_block(model, hd.cv3[i][0][1], t)
+        t = conv_block(model, hd.cv3[i][1][1], conv_block(model, hd.cv3[i][1][0], t))
+        cls = final_conv(model, hd.cv3[i][2], t)
+        k = conv_block(model, hd.cv4[i][1], conv_block(model, hd.cv4[i][0], f))
+        kpt = final_conv(model, hd.cv4[i][2], k)
+        outs.append(torch.cat([cls, kpt], 1))
+    return outs

@@ -362,6 +362,33 @@ int hpe_maxpool5(const void* x, int in_pitch, int B, int H, int W, int C, void* 
 int hpe_upsample_bilinear(const void* x, int in_pitch, int B, int Hi, int Wi, int C, int Ho, int Wo, void* y, int out_pitch,
                           void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Training-mode pieces of the reference's real pose model beyond its (frozen) backbone: the neck and head of DINOv3Pose are
+ * trained by HPE/train.py:116-139 (`finetuning=True` freezes the ConvNeXt, HPE/models/pose.py:47-49); they are built from
+ * ConvBlock = Conv2d + BatchNorm2d (batch statistics under model.train()) + SiLU (HPE/models/nn/modules/block.py:20-45).
+ * The convolutions use hpe_conv_run / hpe_conv_dgrad_desc / hpe_wgrad_*; these are the bandwidth-bound rest, for any channel
+ * count that is a multiple of 8.  act: 0 none, 1 ReLU, 2 SiLU.  All reductions are two-stage in a fixed order (no atomics).
+ *   hpe_bnact_stats     as hpe_bn_stats (scale/shift/mean/rstd + running statistics); scratch = hpe_bnact_scratch_elems(C) floats
+ *   hpe_bnact_apply     y = act(z*scale + shift)
+ *   hpe_bnact_backward  g = dy * act'(z*scale + shift); dbeta = sum g; dgamma = sum g*xhat; dz = gamma*rstd*(g - dbeta/M - xhat*dgamma/M)
+ *   hpe_dwconv3_wgrad   weight gradient [C][1][3][3] of a depthwise 3x3 conv (pad 1, stride 1); its forward and backward-data
+ *                       passes are hpe_dwconv (mode 0 with scale 1, shift 0 and eps < 0 = no activation; flipped taps for dgrad)
+ *   hpe_maxpool5_backward           backward of MaxPool2d(5, 1, 2) (SPPF, block.py:102-114), arg-max recomputed from the input x
+ *   hpe_upsample_bilinear_backward  backward of F.interpolate(mode='bilinear', align_corners=False) (PAN, block.py:132-151)
+ * ---------------------------------------------------------------------------------------------- */
+size_t hpe_bnact_scratch_elems(int C);
+int hpe_bnact_stats(const void* z, long long M, int C, const float* gamma, const float* beta, float eps, float momentum,
+                    float* running_mean, float* running_var, float* scratch, float* scale, float* shift, float* mean,
+                    float* rstd, void* stream);
+int hpe_bnact_apply(const void* z, long long M, int C, const float* scale, const float* shift, int act, void* y, void* stream);
+int hpe_bnact_backward(const void* dy, const void* z, long long M, int C, const float* mean, const float* rstd,
+                       const float* gamma, const float* scale, const float* shift, int act, float* scratch, float* dbeta,
+                       float* dgamma, void* dz, void* stream);
+size_t hpe_dwconv3_wgrad_scratch_elems(int C);
+int hpe_dwconv3_wgrad(const void* x, const void* dz, int B, int H, int W, int C, float* scratch, float* dw_torch, void* stream);
+int hpe_maxpool5_backward(const void* x, const void* dy, int B, int H, int W, int C, void* dx, void* stream);
+int hpe_upsample_bilinear_backward(const void* dy, int B, int Hi, int Wi, int C, int Ho, int Wo, void* dx, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
