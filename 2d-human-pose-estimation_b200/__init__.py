@@ -20,6 +20,7 @@ from .train import TrainPlan, TrainStep, adamw_step, grad_sumsq
 from .detpose import (OKS, OKS_SIGMAS, PCK, ComputeLoss, KeypointLoss, non_max_suppression_pose, pose_decode,
                       pose_nms_raw)
 from .posemodel import DINOv3Pose
+from .posetrain import PoseTrainStep
 from .pipeline import PoseEstimator, ResultGather, gather_keypoints, gather_keypoints_equal, shard_range
 
 __version__ = "0.1.0"

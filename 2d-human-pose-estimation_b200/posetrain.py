@@ -361,3 +361,70 @@ def train_forward(model, x):
         kpt = final_conv(model, hd.cv4[i][2], k)
         outs.append(torch.cat([cls, kpt], 1))
     return outs
+
+
+# ------------------------------------------------------------------------------------------------- the training step
+class PoseTrainStep:
+    """The reference's training step for its real model (HPE/train.py:116-139) as one call, data-parallel:
+
+        step = PoseTrainStep(model, lr=1e-4, weight_decay=1e-4, max_grad_norm=10.0)     # AdamW + clip_grad_norm_(10), train.py:52-55, 136
+        loss, (cls, kpt, vis) = step(images, targets)
+
+    ``images`` [B,3,H,W] uint8 or fp32 on the device (uint8 = ``imgs.float() / 255``, train.py:117-120, fused into the stem);
+    ``targets`` rows ``[b, cls, cx, cy, w, h, (x, y, v) * K]`` normalised (HPE/dataset.py:23-37).  Forward (frozen backbone +
+    batch-statistics neck / head), ``ComputeLoss`` with its analytic gradient, backward through the dgrad / wgrad kernels into ONE
+    flat fp32 gradient buffer (the parameters' ``.grad`` are views of it), ONE NCCL all-reduce of that buffer under
+    ``torch.distributed`` (per-rank BatchNorm statistics, averaged gradients: what the reference's DDP wrap does,
+    pose/pose/core/builder.py:92-123), then the gradient-norm kernel and ONE AdamW kernel over the flat parameter buffer."""
+
+    def __init__(self, model, lr=1e-4, weight_decay=1e-4, betas=(0.9, 0.999), eps=1e-8, max_grad_norm=10.0, group=None):
+        import torch.distributed as dist
+        from .detpose import ComputeLoss
+        from .train import ParamLayout
+        self.model = model.train()
+        self.criterion = ComputeLoss(model, items=False)
+        self.lr, self.weight_decay, self.betas, self.eps, self.max_grad_norm = lr, weight_decay, tuple(betas), eps, float(max_grad_norm)
+        self.group, self._t = group, 0
+        self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+        self.layout = ParamLayout(model)                       # trainable parameters first
+        dev = next(model.parameters()).device
+        self.device = dev
+        self.flat_param = torch.zeros(self.layout.total, dtype=torch.float32, device=dev)
+        nt = self.layout.trainable_total
+        self.flat_grad = torch.zeros(nt, dtype=torch.float32, device=dev)
+        self.exp_avg, self.exp_avg_sq = torch.zeros_like(self.flat_grad), torch.zeros_like(self.flat_grad)
+        self.grad_sumsq = torch.zeros(1, dtype=torch.float32, device=dev)
+        pv = self.layout.views(self.flat_param)
+        with torch.no_grad():
+            for n, p in model.named_parameters():              # re-point the parameters at the flat buffer
+                pv[n].copy_(p.data)
+                p.data = pv[n]
+        self._trainable = [(n, p) for n, p in model.named_parameters() if p.requires_grad]
+        self._grad_views = {n: self.flat_grad.narrow(0, self.layout.offsets[n], p.numel()).view(p.shape) for n, p in self._trainable}
+
+    def broadcast_parameters(self, src=0):
+        import torch.distributed as dist
+        if self.world > 1:
+            dist.broadcast(self.flat_param, src, group=self.group)
+            for b in self.model.buffers():
+                if b.dtype.is_floating_point:
+                    dist.broadcast(b, src, group=self.group)
+
+    def __call__(self, images, targets):
+        import torch.distributed as dist
+        from .train import adamw_step, grad_sumsq
+        self.flat_grad.zero_()
+        for n, p in self._trainable:                           # autograd accumulates in place into the flat buffer
+            p.grad = self._grad_views[n]
+        loss, items = self.criterion(train_forward(self.model, images), targets)
+        loss.backward()
+        if self.world > 1:
+            dist.all_reduce(self.flat_grad, op=dist.ReduceOp.SUM, group=self.group)
+        self._t += 1
+        clip = self.max_grad_norm > 0
+        if clip:                                               # norm of the summed gradient; the kernel applies 1 / world to both
+            grad_sumsq(self.flat_grad, self.grad_sumsq)
+        nt = self.layout.trainable_total
+        adamw_step(self.flat_param[:nt], self.flat_grad, self.exp_avg, self.exp_avg_sq, self._t, self.lr, self.betas, self.eps,
+                   self.weight_decay, 1.0 / self.world, self.grad_sumsq if clip else None, self.max_grad_norm)
+        return loss.detach(), items

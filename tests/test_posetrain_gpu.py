@@ -259,3 +259,40 @@ def test_dinov3pose_training_with_compute_loss_and_adamw(hpe, cuda_dev):
         opt.step()
         losses.append(float(loss.detach()))
     assert all(torch.isfinite(torch.tensor(losses))) and losses[-1] < losses[0], losses
+
+
+def test_pose_train_step_flat_buffers(hpe, cuda_dev):
+    """PoseTrainStep: the parameters and gradients live in flat buffers, one gradient-norm + one AdamW kernel per step; the frozen
+    backbone does not move, the trainable parameters do, the loss falls, and the first step equals torch.optim.AdamW +
+    clip_grad_norm_ on the same gradients."""
+    torch.manual_seed(0)
+    m = hpe.DINOv3Pose("dinov3_convnext_tiny", nkpts=(17, 3), ncls=1, device=cuda_dev)
+    twin = hpe.DINOv3Pose("dinov3_convnext_tiny", nkpts=(17, 3), ncls=1, device=cuda_dev)
+    twin.load_state_dict(m.state_dict())
+    B = 4
+    gen = torch.Generator().manual_seed(1)
+    x = torch.randint(0, 256, (B, 3, 128, 96), generator=gen, dtype=torch.uint8).to(cuda_dev)
+    tg = torch.zeros(B, 6 + 17 * 3)
+    tg[:, 0] = torch.arange(B); tg[:, 2:4] = 0.3 + 0.4 * torch.rand(B, 2, generator=gen); tg[:, 4:6] = 0.3
+    kp = torch.rand(B, 17, 3, generator=gen); kp[..., :2] = 0.2 + 0.6 * kp[..., :2]; kp[..., 2] = 2.0
+    tg[:, 6:] = kp.reshape(B, -1)
+    tg = tg.to(cuda_dev)
+    step = hpe.PoseTrainStep(m, lr=2e-3, weight_decay=1e-2, max_grad_norm=10.0)
+    bb0 = [p.detach().clone() for p in m.backbone.parameters()]
+    # reference for the FIRST step: same forward/backward kernels, torch's optimizer and clipping
+    twin.train()
+    crit = hpe.ComputeLoss(twin)
+    tp = [p for p in twin.parameters() if p.requires_grad]
+    opt = torch.optim.AdamW(tp, lr=2e-3, weight_decay=1e-2)
+    crit(twin(x), tg)[0].backward()
+    torch.nn.utils.clip_grad_norm_(tp, 10.0)
+    opt.step()
+    losses = [float(step(x, tg)[0])]
+    for (n, p), (_, q) in zip(m.named_parameters(), twin.named_parameters()):
+        if p.requires_grad:
+            assert torch.allclose(p, q, rtol=1e-4, atol=2e-6), n
+    for _ in range(5):
+        losses.append(float(step(x, tg)[0]))
+    assert all(torch.isfinite(torch.tensor(losses))) and losses[-1] < losses[0], losses
+    assert all(torch.equal(a, b) for a, b in zip(bb0, m.backbone.parameters()))
+    assert all(p.data_ptr() >= step.flat_param.data_ptr() for p in m.parameters())
