@@ -83,6 +83,7 @@ SIGNATURES = {
     "hpe_bnact_backward": (_i, [_vp, _vp, C.c_longlong, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp]),
     "hpe_dwconv3_wgrad_scratch_elems": (_sz, [_i]),
     "hpe_dwconv3_wgrad": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp]),
+    "hpe_maxpool5_train": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp]),
     "hpe_maxpool5_backward": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp]),
     "hpe_upsample_bilinear_backward": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp]),
     "hpe_patchify4": (_i, [_vp, _i, _i, _i, _vp, _vp]),

@@ -6,7 +6,7 @@
 // (the neck's 192 / 384 / 576 / 768 / 1152 / 1536 are not the powers of two train_ops.cu is specialised for):
 //   bnact_*            BatchNorm2d forward statistics / apply / backward with act in {none, ReLU, SiLU}
 //   dwconv3_wgrad_*    weight gradient of a depthwise 3x3 convolution
-//   maxpool5_bwd       backward of MaxPool2d(5, 1, 2) (first-max tie rule, recomputed from the forward input)
+//   maxpool5_idx / bwd  MaxPool2d(5, 1, 2) with the recorded arg-max (first-max tie rule) and its backward
 //   upsample2x_bwd     backward of F.interpolate(mode='bilinear', align_corners=False)
 // Every reduction is two-stage with a fixed order (no atomics): gradients are bit-reproducible run to run.
 #include "hpe_common.cuh"
@@ -33,7 +33,7 @@ __device__ __forceinline__ float nt_dact(float u, int act) {
   return 1.f;
 }
 
-constexpr int kNtSlices = 64;            // row slices of the two-stage reductions (partials [slice][2][C])
+constexpr int kNtSlices = 256;           // max row slices of the two-stage reductions (partials [slice][2][C])
 
 // Stage 1 of a per-channel reduction over the M rows of an [M][C] bf16 tensor.  Block = 8 rows x 32 channel vectors (a warp
 // reads 512 contiguous bytes of one row); grid = (ceil(Cv / 32), kNtSlices).
@@ -226,10 +226,49 @@ __device__ __forceinline__ bool nt_bf16_gt(uint16_t a, uint16_t b) {
   return __uint_as_float(static_cast<uint32_t>(a) << 16) > __uint_as_float(static_cast<uint32_t>(b) << 16);
 }
 
-// ---- MaxPool2d(5, 1, 2) backward: dx[p] = sum of dy[q] over the windows q (|q - p| <= 2) whose FIRST maximum (row-major scan of
-// the window, strict >, as ATen's max_pool2d) is p.  The arg-max is recomputed from the forward input (the tensors are small).
+// ---- MaxPool2d(5, 1, 2) in training mode: the forward also records, per output element, which window position (wy * 5 + wx)
+// holds the FIRST maximum (row-major scan of the window, strict >, as ATen's max_pool2d); the backward gathers
+// dx[p] = sum of dy[q] over the <= 25 windows q around p whose recorded arg-max is p (fixed order, no atomics).
 __global__ void __launch_bounds__(256)
-maxpool5_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy, int B, int H, int W, int C,
+maxpool5_idx_kernel(const __nv_bfloat16* __restrict__ x, int B, int H, int W, int C, __nv_bfloat16* __restrict__ y,
+                    uint8_t* __restrict__ idx) {
+  const int Cv = C / 8;
+  const long long total = static_cast<long long>(B) * H * W * Cv;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int cv = static_cast<int>(i % Cv);
+    const int qx = static_cast<int>((i / Cv) % W);
+    const int qy = static_cast<int>((i / (static_cast<long long>(Cv) * W)) % H);
+    const long long b = i / (static_cast<long long>(Cv) * W * H);
+    const uint4* xb = reinterpret_cast<const uint4*>(x) + b * H * W * Cv + cv;
+    uint16_t best[8]; uint8_t bi[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) { best[e] = 0xFF80; bi[e] = 255; }
+#pragma unroll
+    for (int wy = 0; wy < 5; ++wy) {
+      const int iy = qy + wy - 2;
+      if (iy < 0 || iy >= H) continue;
+#pragma unroll
+      for (int wx = 0; wx < 5; ++wx) {
+        const int ix = qx + wx - 2;
+        if (ix < 0 || ix >= W) continue;
+        const uint4 v = __ldg(xb + (static_cast<long long>(iy) * W + ix) * Cv);
+        const uint16_t* h = reinterpret_cast<const uint16_t*>(&v);
+#pragma unroll
+        for (int e = 0; e < 8; ++e)
+          if (bi[e] == 255 || nt_bf16_gt(h[e], best[e])) { best[e] = h[e]; bi[e] = static_cast<uint8_t>(wy * 5 + wx); }
+      }
+    }
+    uint4 o; uint16_t* oh = reinterpret_cast<uint16_t*>(&o);
+    uint2 oi; uint8_t* ob = reinterpret_cast<uint8_t*>(&oi);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) { oh[e] = best[e]; ob[e] = bi[e]; }
+    reinterpret_cast<uint4*>(y)[i] = o;
+    reinterpret_cast<uint2*>(idx)[i] = oi;
+  }
+}
+__global__ void __launch_bounds__(256)
+maxpool5_bwd_kernel(const uint8_t* __restrict__ idx, const __nv_bfloat16* __restrict__ dy, int B, int H, int W, int C,
                     __nv_bfloat16* __restrict__ dx) {
   const int Cv = C / 8;
   const long long total = static_cast<long long>(B) * H * W * Cv;
@@ -239,34 +278,26 @@ maxpool5_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
     const int px = static_cast<int>((i / Cv) % W);
     const int py = static_cast<int>((i / (static_cast<long long>(Cv) * W)) % H);
     const long long b = i / (static_cast<long long>(Cv) * W * H);
-    const uint4* xb = reinterpret_cast<const uint4*>(x) + b * H * W * Cv + cv;
+    const uint2* ib = reinterpret_cast<const uint2*>(idx) + b * H * W * Cv + cv;
     const uint4* gb = reinterpret_cast<const uint4*>(dy) + b * H * W * Cv + cv;
     float acc[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-    for (int qy = py - 2; qy <= py + 2; ++qy) {
+#pragma unroll
+    for (int wy = 0; wy < 5; ++wy) {
+      const int qy = py - (wy - 2);                      // window q whose position (wy, wx) is p
       if (qy < 0 || qy >= H) continue;
-      for (int qx = px - 2; qx <= px + 2; ++qx) {
+#pragma unroll
+      for (int wx = 0; wx < 5; ++wx) {
+        const int qx = px - (wx - 2);
         if (qx < 0 || qx >= W) continue;
-        // first maximum of window q per channel; does it sit at p?
-        uint16_t best[8]; int by[8], bx[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) { best[e] = 0xFF80; by[e] = -1; bx[e] = -1; }
-        for (int wy = qy - 2; wy <= qy + 2; ++wy) {
-          if (wy < 0 || wy >= H) continue;
-          for (int wx = qx - 2; wx <= qx + 2; ++wx) {
-            if (wx < 0 || wx >= W) continue;
-            const uint4 v = __ldg(xb + (static_cast<long long>(wy) * W + wx) * Cv);
-            const uint16_t* h = reinterpret_cast<const uint16_t*>(&v);
-#pragma unroll
-            for (int e = 0; e < 8; ++e)
-              if (by[e] < 0 || nt_bf16_gt(h[e], best[e])) { best[e] = h[e]; by[e] = wy; bx[e] = wx; }
-          }
-        }
+        const long long o = (static_cast<long long>(qy) * W + qx) * Cv;
+        const uint2 k = __ldg(ib + o);
+        const uint8_t* kb = reinterpret_cast<const uint8_t*>(&k);
         float g[8];
-        nt_unpack8(__ldg(gb + (static_cast<long long>(qy) * W + qx) * Cv), g);
+        nt_unpack8(__ldg(gb + o), g);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) if (by[e] == py && bx[e] == px) acc[e] += g[e];
+        for (int e = 0; e < 8; ++e) if (kb[e] == wy * 5 + wx) acc[e] += g[e];
       }
     }
     reinterpret_cast<uint4*>(dx)[i] = nt_pack8(acc);
@@ -330,6 +361,12 @@ static inline int nt_grid(long long n) {
 
 using namespace hpe;
 
+// row slices of a reduction over M rows: ~128 rows per block, at least 16 (small maps) and at most kNtSlices
+static int nt_slices(long long M) {
+  long long n = (M + 127) / 128;
+  return (int)(n < 16 ? 16 : (n > kNtSlices ? kNtSlices : n));
+}
+
 static int nt_shape_ok(long long M, int C, const char* fn) {
   HPE_CHECK_ARG(M > 0 && C >= 8 && C % 8 == 0 && C <= 4096, "%s: C=%d must be a multiple of 8 in [8, 4096] and M > 0", fn, C);
   return HPE_OK;
@@ -345,11 +382,12 @@ extern "C" int hpe_bnact_stats(const void* z, long long M, int C, const float* g
   HPE_CHECK_ARG(z && gamma && beta && scratch && scale && shift && mean && rstd, "hpe_bnact_stats: null pointer");
   HPE_CHECK_ARG(((uintptr_t)z & 15) == 0, "hpe_bnact_stats: misaligned pointer");
   cudaStream_t st = (cudaStream_t)stream;
-  const dim3 grid((C / 8 + 31) / 32, kNtSlices);
+  const int ns = nt_slices(M);
+  const dim3 grid((C / 8 + 31) / 32, ns);
   bnact_reduce_kernel<0><<<grid, 256, 0, st>>>((const __nv_bfloat16*)z, nullptr, M, C, 0, nullptr, nullptr, nullptr, nullptr, scratch);
   rc = launch_status("bnact_reduce_kernel<0>");
   if (rc) return rc;
-  bnact_finish_kernel<0><<<(C + 255) / 256, 256, 0, st>>>(scratch, kNtSlices, M, C, gamma, beta, eps, momentum, running_mean, running_var,
+  bnact_finish_kernel<0><<<(C + 255) / 256, 256, 0, st>>>(scratch, ns, M, C, gamma, beta, eps, momentum, running_mean, running_var,
                                                         scale, shift, mean, rstd, nullptr);
   return launch_status("bnact_finish_kernel<0>");
 }
@@ -374,11 +412,12 @@ extern "C" int hpe_bnact_backward(const void* dy, const void* z, long long M, in
   HPE_CHECK_ARG((((uintptr_t)dy | (uintptr_t)z | (uintptr_t)dz) & 15) == 0, "hpe_bnact_backward: misaligned pointer");
   cudaStream_t st = (cudaStream_t)stream;
   float* coef = scratch + (size_t)kNtSlices * 2 * C;
-  const dim3 grid((C / 8 + 31) / 32, kNtSlices);
+  const int ns = nt_slices(M);
+  const dim3 grid((C / 8 + 31) / 32, ns);
   bnact_reduce_kernel<1><<<grid, 256, 0, st>>>((const __nv_bfloat16*)z, (const __nv_bfloat16*)dy, M, C, act, scale, shift, mean, rstd, scratch);
   rc = launch_status("bnact_reduce_kernel<1>");
   if (rc) return rc;
-  bnact_finish_kernel<1><<<(C + 255) / 256, 256, 0, st>>>(scratch, kNtSlices, M, C, gamma, nullptr, 0.f, 0.f, nullptr, nullptr, dbeta, dgamma,
+  bnact_finish_kernel<1><<<(C + 255) / 256, 256, 0, st>>>(scratch, ns, M, C, gamma, nullptr, 0.f, 0.f, nullptr, nullptr, dbeta, dgamma,
                                                         const_cast<float*>(mean), const_cast<float*>(rstd), coef);
   rc = launch_status("bnact_finish_kernel<1>");
   if (rc) return rc;
@@ -394,19 +433,28 @@ extern "C" int hpe_dwconv3_wgrad(const void* x, const void* dz, int B, int H, in
   HPE_CHECK_ARG(x && dz && scratch && dw_torch && B > 0 && H > 0 && W > 0 && C > 0 && C % 8 == 0, "hpe_dwconv3_wgrad: bad argument");
   HPE_CHECK_ARG((((uintptr_t)x | (uintptr_t)dz) & 15) == 0, "hpe_dwconv3_wgrad: misaligned pointer");
   cudaStream_t st = (cudaStream_t)stream;
-  const dim3 grid((C / 8 + 31) / 32, kNtSlices);
+  const int ns = nt_slices((long long)B * H);
+  const dim3 grid((C / 8 + 31) / 32, ns);
   dwconv3_wgrad_kernel<<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)dz, B, H, W, C, scratch);
   int rc = launch_status("dwconv3_wgrad_kernel");
   if (rc) return rc;
-  dwconv3_wgrad_finish_kernel<<<(C * 9 + 255) / 256, 256, 0, st>>>(scratch, kNtSlices, C, dw_torch);
+  dwconv3_wgrad_finish_kernel<<<(C * 9 + 255) / 256, 256, 0, st>>>(scratch, ns, C, dw_torch);
   return launch_status("dwconv3_wgrad_finish_kernel");
 }
 
-extern "C" int hpe_maxpool5_backward(const void* x, const void* dy, int B, int H, int W, int C, void* dx, void* stream) {
-  HPE_CHECK_ARG(x && dy && dx && B > 0 && H > 0 && W > 0 && C > 0 && C % 8 == 0, "hpe_maxpool5_backward: bad argument");
-  HPE_CHECK_ARG((((uintptr_t)x | (uintptr_t)dy | (uintptr_t)dx) & 15) == 0, "hpe_maxpool5_backward: misaligned pointer");
-  maxpool5_bwd_kernel<<<nt_grid((long long)B * H * W * (C / 8)), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)dy,
-                                                                                               B, H, W, C, (__nv_bfloat16*)dx);
+extern "C" int hpe_maxpool5_train(const void* x, int B, int H, int W, int C, void* y, uint8_t* idx, void* stream) {
+  HPE_CHECK_ARG(x && y && idx && B > 0 && H > 0 && W > 0 && C > 0 && C % 8 == 0, "hpe_maxpool5_train: bad argument");
+  HPE_CHECK_ARG((((uintptr_t)x | (uintptr_t)y) & 15) == 0 && ((uintptr_t)idx & 7) == 0, "hpe_maxpool5_train: misaligned pointer");
+  maxpool5_idx_kernel<<<nt_grid((long long)B * H * W * (C / 8)), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, B, H, W, C,
+                                                                                               (__nv_bfloat16*)y, idx);
+  return launch_status("maxpool5_idx_kernel");
+}
+
+extern "C" int hpe_maxpool5_backward(const uint8_t* idx, const void* dy, int B, int H, int W, int C, void* dx, void* stream) {
+  HPE_CHECK_ARG(idx && dy && dx && B > 0 && H > 0 && W > 0 && C > 0 && C % 8 == 0, "hpe_maxpool5_backward: bad argument");
+  HPE_CHECK_ARG((((uintptr_t)dy | (uintptr_t)dx) & 15) == 0 && ((uintptr_t)idx & 7) == 0, "hpe_maxpool5_backward: misaligned pointer");
+  maxpool5_bwd_kernel<<<nt_grid((long long)B * H * W * (C / 8)), 256, 0, (cudaStream_t)stream>>>(idx, (const __nv_bfloat16*)dy, B, H, W, C,
+                                                                                               (__nv_bfloat16*)dx);
   return launch_status("maxpool5_bwd_kernel");
 }
 

@@ -123,7 +123,9 @@ class ComputeLoss:
         B = preds[0].shape[0]
         Hs, Ws = _int_array([p.shape[2] for p in preds]), _int_array([p.shape[3] for p in preds])
         n = targets.shape[0]
-        sig = self.sigmas.to(dev)
+        if self.sigmas.device != dev:                 # moved once (a host->device copy per call would also break CUDA-graph capture)
+            self.sigmas = self.sigmas.to(dev)
+        sig = self.sigmas
         lib = _lib.lib()
         need = lib.hpe_compute_loss_workspace_bytes(len(preds), B, Hs, Ws, self.nc, n)
         if self._ws is None or self._ws.numel() < need or self._ws.device != dev:

@@ -404,7 +404,8 @@ class _PosePlan:
 
     def run(self, x):
         _patchify4(x, self.patches)
-        if os.environ.get("HPE_B200_CUDA_GRAPH", "1") == "0":
+        # (inside an outer capture -- PoseTrainStep(cuda_graph=True) -- the launches are recorded into THAT graph)
+        if os.environ.get("HPE_B200_CUDA_GRAPH", "1") == "0" or torch.cuda.is_current_stream_capturing():
             self._launch_all()
             return self.levels
         if self.graph is None:

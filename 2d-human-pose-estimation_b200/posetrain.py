@@ -32,7 +32,7 @@ import torch.nn.functional as F
 from . import _lib
 from ._lib import ACT_NONE, CONV_1x1, CONV_3x3, CONV_FINAL
 from .conv import ConvLayer, DgradLayer, WgradLayer
-from .posemodel import _PosePlan, _dwconv, _maxpool5, _upsample
+from .posemodel import _PosePlan, _dwconv, _upsample
 
 ACT_SILU_BN = 2          # act code of the hpe_bnact_* kernels: 0 none, 1 ReLU, 2 SiLU
 
@@ -208,18 +208,22 @@ class MaxPool5Fn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x):
+        B, H, W, Cc = x.shape
         y = torch.empty_like(x)
-        _maxpool5(x, y)
-        ctx.save_for_backward(x)
+        idx = torch.empty(x.shape, dtype=torch.uint8, device=x.device)          # window position of the first maximum
+        with torch.cuda.device(x.device):
+            _lib.check(_lib.lib().hpe_maxpool5_train(_lib.ptr(x), B, H, W, Cc, _lib.ptr(y), _lib.ptr(idx), _lib.stream_ptr()),
+                       "hpe_maxpool5_train")
+        ctx.save_for_backward(idx)
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        (x,) = ctx.saved_tensors
-        B, H, W, Cc = x.shape
-        dx = torch.empty_like(x)
-        with torch.cuda.device(x.device):
-            _lib.check(_lib.lib().hpe_maxpool5_backward(_lib.ptr(x), _lib.ptr(dy.contiguous()), B, H, W, Cc, _lib.ptr(dx),
+        (idx,) = ctx.saved_tensors
+        B, H, W, Cc = idx.shape
+        dx = torch.empty(idx.shape, dtype=dy.dtype, device=dy.device)
+        with torch.cuda.device(dy.device):
+            _lib.check(_lib.lib().hpe_maxpool5_backward(_lib.ptr(idx), _lib.ptr(dy.contiguous()), B, H, W, Cc, _lib.ptr(dx),
                                                         _lib.stream_ptr()), "hpe_maxpool5_backward")
         return dx
 
@@ -252,6 +256,7 @@ class _FinalSpec:
         self.fwd = ConvLayer(CONV_FINAL, B, H, W, self.cinp, K, 1, ACT_NONE, False, dev)
         self.dgrad = DgradLayer(CONV_FINAL, B, H, W, self.cinp, K, 1, device=dev)
         self.wgrad = WgradLayer(CONV_FINAL, B, H, W, self.cinp, K, 1, dev)
+        self.ones = torch.ones(K, dtype=torch.float32, device=dev)
 
 
 class FinalConvFn(torch.autograd.Function):
@@ -264,7 +269,7 @@ class FinalConvFn(torch.autograd.Function):
         if spec.cinp != spec.cin:
             wp = F.pad(wp, (0, 0, 0, 0, 0, spec.cinp - spec.cin))
         wp = wp.contiguous()
-        spec.fwd.load(wp, torch.ones(spec.K), b.detach())
+        spec.fwd.load(wp, spec.ones, b.detach())
         out = spec.fwd(x)                                   # [B, K, H, W] fp32
         ctx.save_for_backward(x, wp)
         ctx.spec = spec
@@ -377,7 +382,7 @@ class PoseTrainStep:
     ``torch.distributed`` (per-rank BatchNorm statistics, averaged gradients: what the reference's DDP wrap does,
     pose/pose/core/builder.py:92-123), then the gradient-norm kernel and ONE AdamW kernel over the flat parameter buffer."""
 
-    def __init__(self, model, lr=1e-4, weight_decay=1e-4, betas=(0.9, 0.999), eps=1e-8, max_grad_norm=10.0, group=None):
+    def __init__(self, model, lr=1e-4, weight_decay=1e-4, betas=(0.9, 0.999), eps=1e-8, max_grad_norm=10.0, group=None, cuda_graph=False):
         import torch.distributed as dist
         from .detpose import ComputeLoss
         from .train import ParamLayout
@@ -385,6 +390,9 @@ class PoseTrainStep:
         self.criterion = ComputeLoss(model, items=False)
         self.lr, self.weight_decay, self.betas, self.eps, self.max_grad_norm = lr, weight_decay, tuple(betas), eps, float(max_grad_norm)
         self.group, self._t = group, 0
+        # cuda_graph: capture forward + loss + backward (~2700 launches) once per (image shape, target shape) and replay it; the
+        # all-reduce and the optimizer kernels follow the replay.  Needs a fixed number of target rows per step.
+        self.use_graph, self.graph, self._key, self._warm = bool(cuda_graph), None, None, 0
         self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
         self.layout = ParamLayout(model)                       # trainable parameters first
         dev = next(model.parameters()).device
@@ -410,14 +418,18 @@ class PoseTrainStep:
                 if b.dtype.is_floating_point:
                     dist.broadcast(b, src, group=self.group)
 
-    def __call__(self, images, targets):
-        import torch.distributed as dist
-        from .train import adamw_step, grad_sumsq
+    def _compute(self, images, targets):
+        """forward -> ComputeLoss -> backward into the flat gradient buffer (this rank's shard)."""
         self.flat_grad.zero_()
         for n, p in self._trainable:                           # autograd accumulates in place into the flat buffer
             p.grad = self._grad_views[n]
         loss, items = self.criterion(train_forward(self.model, images), targets)
         loss.backward()
+        self.loss, self.items = loss.detach(), items
+
+    def _update(self):
+        import torch.distributed as dist
+        from .train import adamw_step, grad_sumsq
         if self.world > 1:
             dist.all_reduce(self.flat_grad, op=dist.ReduceOp.SUM, group=self.group)
         self._t += 1
@@ -427,4 +439,28 @@ class PoseTrainStep:
         nt = self.layout.trainable_total
         adamw_step(self.flat_param[:nt], self.flat_grad, self.exp_avg, self.exp_avg_sq, self._t, self.lr, self.betas, self.eps,
                    self.weight_decay, 1.0 / self.world, self.grad_sumsq if clip else None, self.max_grad_norm)
-        return loss.detach(), items
+
+    def __call__(self, images, targets):
+        if not self.use_graph:
+            self._compute(images, targets)
+            self._update()
+            return self.loss, self.items
+        key = (tuple(images.shape), images.dtype, tuple(targets.shape))
+        if key != self._key:
+            self._key, self.graph, self._warm = key, None, 0
+            self.x_static, self.t_static = torch.empty_like(images), torch.empty_like(targets, dtype=torch.float32)
+        self.x_static.copy_(images)
+        self.t_static.copy_(targets)
+        if self.graph is None and self._warm < 2:              # eager warm-up: plans, TMA descriptors, workspaces
+            self._compute(self.x_static, self.t_static)
+            self._warm += 1
+        else:
+            if self.graph is None:
+                torch.cuda.synchronize(self.device)
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    self._compute(self.x_static, self.t_static)
+                self.graph = g
+            self.graph.replay()
+        self._update()
+        return self.loss, self.items

@@ -373,7 +373,8 @@ int hpe_upsample_bilinear(const void* x, int in_pitch, int B, int Hi, int Wi, in
  *   hpe_bnact_backward  g = dy * act'(z*scale + shift); dbeta = sum g; dgamma = sum g*xhat; dz = gamma*rstd*(g - dbeta/M - xhat*dgamma/M)
  *   hpe_dwconv3_wgrad   weight gradient [C][1][3][3] of a depthwise 3x3 conv (pad 1, stride 1); its forward and backward-data
  *                       passes are hpe_dwconv (mode 0 with scale 1, shift 0 and eps < 0 = no activation; flipped taps for dgrad)
- *   hpe_maxpool5_backward           backward of MaxPool2d(5, 1, 2) (SPPF, block.py:102-114), arg-max recomputed from the input x
+ *   hpe_maxpool5_train / _backward  MaxPool2d(5, 1, 2) (SPPF, block.py:102-114) that also records the window position of the first
+ *                                   maximum (idx: one byte per element) / its backward from that record
  *   hpe_upsample_bilinear_backward  backward of F.interpolate(mode='bilinear', align_corners=False) (PAN, block.py:132-151)
  * ---------------------------------------------------------------------------------------------- */
 size_t hpe_bnact_scratch_elems(int C);
@@ -386,7 +387,8 @@ int hpe_bnact_backward(const void* dy, const void* z, long long M, int C, const 
                        float* dgamma, void* dz, void* stream);
 size_t hpe_dwconv3_wgrad_scratch_elems(int C);
 int hpe_dwconv3_wgrad(const void* x, const void* dz, int B, int H, int W, int C, float* scratch, float* dw_torch, void* stream);
-int hpe_maxpool5_backward(const void* x, const void* dy, int B, int H, int W, int C, void* dx, void* stream);
+int hpe_maxpool5_train(const void* x, int B, int H, int W, int C, void* y, unsigned char* idx, void* stream);
+int hpe_maxpool5_backward(const unsigned char* idx, const void* dy, int B, int H, int W, int C, void* dx, void* stream);
 int hpe_upsample_bilinear_backward(const void* dy, int B, int Hi, int Wi, int C, int Ho, int Wo, void* dx, void* stream);
 
 #ifdef __cplusplus

@@ -23,6 +23,12 @@ def test_data_parallel_training_step():
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+def test_data_parallel_pose_training_step():
+    r = _torchrun([os.path.join(ROOT, "tests", "dist_posetrain_check.py")], 2)
+    assert r.returncode == 0 and "DIST_POSETRAIN_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
 def test_bench_two_gpus_prints_one_json_line():
     import json
     r = _torchrun([os.path.join(ROOT, "bench.py"), "--gpus", "2", "--steps", "3", "--warmup", "3", "--batch", "64", "--sustain-s", "0.2",

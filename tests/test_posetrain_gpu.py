@@ -296,3 +296,26 @@ def test_pose_train_step_flat_buffers(hpe, cuda_dev):
     assert all(torch.isfinite(torch.tensor(losses))) and losses[-1] < losses[0], losses
     assert all(torch.equal(a, b) for a, b in zip(bb0, m.backbone.parameters()))
     assert all(p.data_ptr() >= step.flat_param.data_ptr() for p in m.parameters())
+
+
+def test_pose_train_step_cuda_graph_equals_eager(hpe, cuda_dev):
+    """cuda_graph=True replays the captured forward + loss + backward (the frozen backbone's launches recorded into the same graph):
+    the same kernels in the same order as the eager step, so losses and parameters agree bit for bit."""
+    def run(graph):
+        torch.manual_seed(0)
+        m = hpe.DINOv3Pose("dinov3_convnext_tiny", nkpts=(17, 3), ncls=1, device=cuda_dev)
+        gen = torch.Generator().manual_seed(1)
+        B = 4
+        x = torch.randint(0, 256, (B, 3, 128, 96), generator=gen, dtype=torch.uint8).to(cuda_dev)
+        tg = torch.zeros(B, 6 + 17 * 3)
+        tg[:, 0] = torch.arange(B); tg[:, 2:4] = 0.3 + 0.4 * torch.rand(B, 2, generator=gen); tg[:, 4:6] = 0.3
+        kp = torch.rand(B, 17, 3, generator=gen); kp[..., :2] = 0.2 + 0.6 * kp[..., :2]; kp[..., 2] = 2.0
+        tg[:, 6:] = kp.reshape(B, -1)
+        tg = tg.to(cuda_dev)
+        step = hpe.PoseTrainStep(m, lr=1e-3, weight_decay=1e-2, max_grad_norm=10.0, cuda_graph=graph)
+        losses = [float(step(x, tg)[0]) for _ in range(5)]
+        return losses, step.flat_param.clone()
+    le, pe = run(False)
+    lg, pg = run(True)
+    assert le == lg, (le, lg)
+    assert torch.equal(pe, pg)
