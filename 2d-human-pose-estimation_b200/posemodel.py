@@ -13,7 +13,8 @@ load with ``load_state_dict``.  The ``torch.nn`` modules below are parameter con
   * depthwise 7x7 + LayerNorm, depthwise 3x3 + BN + SiLU, LayerNorm, 5x5 max-pool, bilinear upsampling as NHWC bf16
     bandwidth kernels (csrc/convnext_ops.cu),
   * ``torch.cat`` along channels as nothing at all: producers write into channel slices of one buffer.
-There is no CPU path.  Not built: the ViT backbones (pose.py:34-46) and the backward pass of this model.
+There is no CPU path.  ``model.train()`` under autograd runs posetrain.py (batch-statistics BatchNorm in the neck / head and their
+backward pass behind the frozen backbone, HPE/train.py:116-139).  Not built: the ViT backbones (pose.py:34-46).
 """
 from __future__ import annotations
 
