@@ -436,6 +436,39 @@ def train_subbench(hpe, ctx, args, peaks):
     return out
 
 
+def pose_train_subbench(hpe, ctx, args):
+    """The reference's REAL training step (HPE/train.py:116-139) at N GPUs: DINOv3Pose(small) with its frozen ConvNeXt backbone,
+    batch-statistics neck / head, ComputeLoss, backward through the dgrad / wgrad kernels, ONE NCCL all-reduce of the flat gradient
+    buffer, gradient-norm clipping + AdamW kernels (hpe_b200.PoseTrainStep, forward + loss + backward replayed as a CUDA graph)."""
+    B, H, W = args.pose_train_batch, args.height, args.width
+    torch.manual_seed(0)
+    m = hpe.DINOv3Pose("dinov3_convnext_small", nkpts=(17, 3), ncls=1, device=ctx.dev)
+    gen = torch.Generator().manual_seed(300 + ctx.rank)
+    x = [torch.randint(0, 256, (B, 3, H, W), generator=gen, dtype=torch.uint8).to(ctx.dev) for _ in range(2)]
+    tg = torch.zeros(B, 6 + 17 * 3)
+    tg[:, 0] = torch.arange(B); tg[:, 2:4] = 0.3 + 0.4 * torch.rand(B, 2, generator=gen); tg[:, 4:6] = 0.3
+    kp = torch.rand(B, 17, 3, generator=gen); kp[..., :2] = 0.2 + 0.6 * kp[..., :2]; kp[..., 2] = 2.0
+    tg[:, 6:] = kp.reshape(B, -1)
+    tg = tg.to(ctx.dev)
+    step = hpe.PoseTrainStep(m, lr=1e-4, weight_decay=1e-4, max_grad_norm=10.0, cuda_graph=not args.no_graph)
+    step.broadcast_parameters(0)
+    for i in range(4):
+        step(x[i & 1], tg)
+    steps = max(args.steps, 10)
+    ms_total, clocks = timed(ctx, lambda i: step(x[i & 1], tg), steps)
+    loss = float(step.loss)
+    nbytes = step.flat_grad.numel() * 4
+    out = {"workload": f"DINOv3Pose(dinov3_convnext_small) training step, {H}x{W}, K=17, batch {B}/GPU: frozen backbone, batch-statistics "
+                       "neck + head, ComputeLoss, backward, all-reduce, clip_grad_norm_(10) + AdamW (HPE/train.py:116-139)",
+           "value": round(ctx.world * B * steps / ms_total * 1e3, 1), "unit": "images/s", "ms_per_step": round(ms_total / steps, 4), "steps": steps,
+           "trainable_params": int(step.layout.trainable_total),
+           "allreduce_bytes_per_step": nbytes if ctx.world > 1 else 0, "loss": loss, "clocks": clocks}
+    step.graph = None
+    del step, m
+    torch.cuda.empty_cache()
+    return out
+
+
 def run_b200(args):
     import hpe_b200 as hpe
     ctx = Ctx("(B200 arm)")
@@ -499,6 +532,9 @@ def run_b200(args):
     torch.cuda.empty_cache()
     if not args.quick and not args.no_train:
         train = train_subbench(hpe, ctx, args, peaks)
+    pose_train = None
+    if not args.quick and not args.no_train and not args.no_pose_train:
+        pose_train = pose_train_subbench(hpe, ctx, args)
 
     if rank == 0:
         img_scale = (H * W) / (256 * 192)
@@ -553,6 +589,8 @@ def run_b200(args):
             line["hires"] = hires
         if train:
             line["train"] = train
+        if pose_train:
+            line["pose_train"] = pose_train
         if world == 1 and not args.no_cpu_baseline:
             ips, mean, nthr = cpu_forward_decode(args.cpu_batch, H, W, K, 3, 1)
             line["cpu_baseline"] = {"value": round(ips, 3), "unit": "images/s", "cores": nthr, "kind": "port",
@@ -659,6 +697,8 @@ def main():
     ap.add_argument("--quick", action="store_true", help="headline + e2e only (no sweep / per-kernel / hires / train sub-benchmarks)")
     ap.add_argument("--no-hires", action="store_true")
     ap.add_argument("--no-train", action="store_true")
+    ap.add_argument("--no-pose-train", action="store_true")
+    ap.add_argument("--pose-train-batch", type=int, default=64, help="images per GPU of the DINOv3Pose training sub-benchmark")
     ap.add_argument("--hires-batch", type=int, default=64, help="images per GPU of the 384x288 sub-benchmark (configs[3])")
     ap.add_argument("--sustain-s", type=float, default=2.0, help="length of the second (sustained) timed region; 0 = skip")
     ap.add_argument("--layers-log", default="", help="write the per-launch timings behind roofline.per_kernel to this file")
