@@ -80,7 +80,7 @@ SIGNATURES = {
     "hpe_bnact_scratch_elems": (_sz, [_i]),
     "hpe_bnact_stats": (_i, [_vp, C.c_longlong, _i, _vp, _vp, _f, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "hpe_bnact_apply": (_i, [_vp, C.c_longlong, _i, _vp, _vp, _i, _vp, _vp]),
-    "hpe_bnact_backward": (_i, [_vp, _vp, C.c_longlong, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp]),
+    "hpe_bnact_backward": (_i, [_vp, _vp, C.c_longlong, _i, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "hpe_dwconv3_wgrad_scratch_elems": (_sz, [_i]),
     "hpe_dwconv3_wgrad": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp]),
     "hpe_maxpool5_train": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _vp]),

@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(256)
 bnact_finish_kernel(const float* __restrict__ part, int nslices, long long M, int C, const float* __restrict__ gamma,
                     const float* __restrict__ beta, float eps, float momentum, float* running_mean, float* running_var,
                     float* __restrict__ o0, float* __restrict__ o1, float* __restrict__ o2, float* __restrict__ o3,
-                    float* __restrict__ coef) {
+                    float* __restrict__ coef, int frozen) {
   const int c = blockIdx.x * 256 + threadIdx.x;
   if (c >= C) return;
   float s0 = 0.f, s1 = 0.f;
@@ -104,7 +104,8 @@ bnact_finish_kernel(const float* __restrict__ part, int nslices, long long M, in
   if (MODE == 1) {
     o0[c] = s0; o1[c] = s1;                                    // dbeta, dgamma
     const float rs = o3[c], mu = o2[c], A = gamma[c] * rs;     // saved rstd, mean
-    coef[c] = A; coef[C + c] = -A * rs * s1 * inv; coef[2 * C + c] = A * (mu * rs * s1 - s0) * inv;
+    // frozen statistics (the module is in eval mode: running mean / variance are constants): dz = gamma * rstd * g
+    coef[c] = A; coef[C + c] = frozen ? 0.f : -A * rs * s1 * inv; coef[2 * C + c] = frozen ? 0.f : A * (mu * rs * s1 - s0) * inv;
     return;
   }
   const float mu = s0 * inv, var = fmaxf(s1 * inv - mu * mu, 0.f), rs = rsqrtf(var + eps), sc = gamma[c] * rs;
@@ -388,7 +389,7 @@ extern "C" int hpe_bnact_stats(const void* z, long long M, int C, const float* g
   rc = launch_status("bnact_reduce_kernel<0>");
   if (rc) return rc;
   bnact_finish_kernel<0><<<(C + 255) / 256, 256, 0, st>>>(scratch, ns, M, C, gamma, beta, eps, momentum, running_mean, running_var,
-                                                        scale, shift, mean, rstd, nullptr);
+                                                        scale, shift, mean, rstd, nullptr, 0);
   return launch_status("bnact_finish_kernel<0>");
 }
 
@@ -403,8 +404,8 @@ extern "C" int hpe_bnact_apply(const void* z, long long M, int C, const float* s
 }
 
 extern "C" int hpe_bnact_backward(const void* dy, const void* z, long long M, int C, const float* mean, const float* rstd,
-                                  const float* gamma, const float* scale, const float* shift, int act, float* scratch, float* dbeta,
-                                  float* dgamma, void* dz, void* stream) {
+                                  const float* gamma, const float* scale, const float* shift, int act, int frozen_stats, float* scratch,
+                                  float* dbeta, float* dgamma, void* dz, void* stream) {
   int rc = nt_shape_ok(M, C, "hpe_bnact_backward");
   if (rc) return rc;
   HPE_CHECK_ARG(dy && z && mean && rstd && gamma && scale && shift && scratch && dbeta && dgamma && dz && act >= 0 && act <= 2,
@@ -418,7 +419,7 @@ extern "C" int hpe_bnact_backward(const void* dy, const void* z, long long M, in
   rc = launch_status("bnact_reduce_kernel<1>");
   if (rc) return rc;
   bnact_finish_kernel<1><<<(C + 255) / 256, 256, 0, st>>>(scratch, ns, M, C, gamma, nullptr, 0.f, 0.f, nullptr, nullptr, dbeta, dgamma,
-                                                        const_cast<float*>(mean), const_cast<float*>(rstd), coef);
+                                                        const_cast<float*>(mean), const_cast<float*>(rstd), coef, frozen_stats ? 1 : 0);
   rc = launch_status("bnact_finish_kernel<1>");
   if (rc) return rc;
   const long long nvec = M * (C / 8);

@@ -113,7 +113,8 @@ def conv(model, mod, x, kind, stride=1, need_dx=True):
 
 # ------------------------------------------------------------------------------------------------- BatchNorm + activation
 class BNActFn(torch.autograd.Function):
-    """``y = act(BatchNorm2d(z))`` with BATCH statistics (model.train()); running statistics updated as torch does."""
+    """``y = act(BatchNorm2d(z))``: BATCH statistics when the module is in training mode (running statistics updated as torch
+    does), its running statistics as constants when it is in eval mode (``bn.eval()`` inside a training model)."""
 
     @staticmethod
     def forward(ctx, z, gamma, beta, bn, act):
@@ -126,22 +127,29 @@ class BNActFn(torch.autograd.Function):
             g = torch.cat([g, torch.ones(Cp - Cr, device=dev)]); b = torch.cat([b, torch.zeros(Cp - Cr, device=dev)])
             rm = torch.cat([rm, torch.zeros(Cp - Cr, device=dev)]); rv = torch.cat([rv, torch.ones(Cp - Cr, device=dev)])
         g, b = g.contiguous(), b.contiguous()
-        scale, shift, mean, rstd = (_f32(Cp, dev) for _ in range(4))
-        scratch = _f32(_lib.lib().hpe_bnact_scratch_elems(Cp), dev)
-        mom = bn.momentum if bn.momentum is not None else 0.1
+        frozen = not bn.training
+        if frozen:                                    # eval-mode BatchNorm: y = z * gamma / sqrt(running_var + eps) + (beta - ...)
+            mean, rstd = rm.detach().float().contiguous(), torch.rsqrt(rv.detach().float() + bn.eps)
+            scale = (g * rstd).contiguous(); shift = (b - mean * scale).contiguous()
+        else:
+            scale, shift, mean, rstd = (_f32(Cp, dev) for _ in range(4))
+            scratch = _f32(_lib.lib().hpe_bnact_scratch_elems(Cp), dev)
+            mom = bn.momentum if bn.momentum is not None else 0.1
+            with torch.cuda.device(dev):
+                _lib.check(_lib.lib().hpe_bnact_stats(_lib.ptr(z), M, Cp, _lib.ptr(g), _lib.ptr(b), float(bn.eps), float(mom), _lib.ptr(rm),
+                                                      _lib.ptr(rv), _lib.ptr(scratch), _lib.ptr(scale), _lib.ptr(shift), _lib.ptr(mean),
+                                                      _lib.ptr(rstd), _lib.stream_ptr()), "hpe_bnact_stats")
         with torch.cuda.device(dev):
-            _lib.check(_lib.lib().hpe_bnact_stats(_lib.ptr(z), M, Cp, _lib.ptr(g), _lib.ptr(b), float(bn.eps), float(mom), _lib.ptr(rm),
-                                                  _lib.ptr(rv), _lib.ptr(scratch), _lib.ptr(scale), _lib.ptr(shift), _lib.ptr(mean),
-                                                  _lib.ptr(rstd), _lib.stream_ptr()), "hpe_bnact_stats")
             y = torch.empty_like(z)
             _lib.check(_lib.lib().hpe_bnact_apply(_lib.ptr(z), M, Cp, _lib.ptr(scale), _lib.ptr(shift), int(act), _lib.ptr(y),
                                                   _lib.stream_ptr()), "hpe_bnact_apply")
-        if Cp != Cr:
-            bn.running_mean.copy_(rm[:Cr]); bn.running_var.copy_(rv[:Cr])
-        if bn.num_batches_tracked is not None:
-            bn.num_batches_tracked += 1
+        if not frozen:
+            if Cp != Cr:
+                bn.running_mean.copy_(rm[:Cr]); bn.running_var.copy_(rv[:Cr])
+            if bn.num_batches_tracked is not None:
+                bn.num_batches_tracked += 1
         ctx.save_for_backward(z, g, scale, shift, mean, rstd)
-        ctx.act, ctx.Cr = int(act), Cr
+        ctx.act, ctx.Cr, ctx.frozen = int(act), Cr, frozen
         return y
 
     @staticmethod
@@ -156,7 +164,7 @@ class BNActFn(torch.autograd.Function):
         scratch = _f32(_lib.lib().hpe_bnact_scratch_elems(Cp), dev)
         with torch.cuda.device(dev):
             _lib.check(_lib.lib().hpe_bnact_backward(_lib.ptr(dy), _lib.ptr(z), M, Cp, _lib.ptr(mean), _lib.ptr(rstd), _lib.ptr(g),
-                                                     _lib.ptr(scale), _lib.ptr(shift), ctx.act, _lib.ptr(scratch), _lib.ptr(dbeta),
+                                                     _lib.ptr(scale), _lib.ptr(shift), ctx.act, int(ctx.frozen), _lib.ptr(scratch), _lib.ptr(dbeta),
                                                      _lib.ptr(dgamma), _lib.ptr(dz), _lib.stream_ptr()), "hpe_bnact_backward")
         return dz, dgamma[:ctx.Cr].contiguous(), dbeta[:ctx.Cr].contiguous(), None, None
 

@@ -370,7 +370,8 @@ int hpe_upsample_bilinear(const void* x, int in_pitch, int B, int Hi, int Wi, in
  * count that is a multiple of 8.  act: 0 none, 1 ReLU, 2 SiLU.  All reductions are two-stage in a fixed order (no atomics).
  *   hpe_bnact_stats     as hpe_bn_stats (scale/shift/mean/rstd + running statistics); scratch = hpe_bnact_scratch_elems(C) floats
  *   hpe_bnact_apply     y = act(z*scale + shift)
- *   hpe_bnact_backward  g = dy * act'(z*scale + shift); dbeta = sum g; dgamma = sum g*xhat; dz = gamma*rstd*(g - dbeta/M - xhat*dgamma/M)
+ *   hpe_bnact_backward  g = dy * act'(z*scale + shift); dbeta = sum g; dgamma = sum g*xhat; dz = gamma*rstd*(g - dbeta/M - xhat*dgamma/M);
+ *                       frozen_stats != 0 (the module is in eval mode, mean / rstd are its running statistics): dz = gamma*rstd*g
  *   hpe_dwconv3_wgrad   weight gradient [C][1][3][3] of a depthwise 3x3 conv (pad 1, stride 1); its forward and backward-data
  *                       passes are hpe_dwconv (mode 0 with scale 1, shift 0 and eps < 0 = no activation; flipped taps for dgrad)
  *   hpe_maxpool5_train / _backward  MaxPool2d(5, 1, 2) (SPPF, block.py:102-114) that also records the window position of the first
@@ -383,8 +384,8 @@ int hpe_bnact_stats(const void* z, long long M, int C, const float* gamma, const
                     float* rstd, void* stream);
 int hpe_bnact_apply(const void* z, long long M, int C, const float* scale, const float* shift, int act, void* y, void* stream);
 int hpe_bnact_backward(const void* dy, const void* z, long long M, int C, const float* mean, const float* rstd,
-                       const float* gamma, const float* scale, const float* shift, int act, float* scratch, float* dbeta,
-                       float* dgamma, void* dz, void* stream);
+                       const float* gamma, const float* scale, const float* shift, int act, int frozen_stats, float* scratch,
+                       float* dbeta, float* dgamma, void* dz, void* stream);
 size_t hpe_dwconv3_wgrad_scratch_elems(int C);
 int hpe_dwconv3_wgrad(const void* x, const void* dz, int B, int H, int W, int C, float* scratch, float* dw_torch, void* stream);
 int hpe_maxpool5_train(const void* x, int B, int H, int W, int C, void* y, unsigned char* idx, void* stream);

@@ -319,3 +319,30 @@ def test_pose_train_step_cuda_graph_equals_eager(hpe, cuda_dev):
     lg, pg = run(True)
     assert le == lg, (le, lg)
     assert torch.equal(pe, pg)
+
+
+def test_training_path_with_eval_mode_batchnorm_matches_reference_golden(hpe, cuda_dev):
+    """``bn.eval()`` inside a training model (how tests/golden/make_golden_dinov3pose.py ran the reference's DINOv3Pose to get
+    deterministic train-format outputs): the autograd path then normalises with the RUNNING statistics, and its raw level maps
+    agree with the reference's own outputs; the backward treats those statistics as constants (dz = gamma * rstd * g)."""
+    import numpy as np
+    import os
+    from oracle import dinov3pose_ref as dr
+    gold = np.load(os.path.join(os.path.dirname(__file__), "golden", "dinov3pose_golden.npz"))
+    oracle = dr.build_synthetic("tiny", (17, 3), 1, seed=0)
+    m = hpe.DINOv3Pose("dinov3_convnext_tiny", nkpts=(17, 3), ncls=1, device=cuda_dev)
+    m.load_state_dict(oracle.state_dict())
+    m.train()
+    for mod in m.modules():
+        if isinstance(mod, torch.nn.BatchNorm2d):
+            mod.eval()
+    x = torch.rand(2, 3, 128, 96, generator=torch.Generator().manual_seed(0))
+    lv = m(x.to(cuda_dev))
+    assert all(l.requires_grad for l in lv)
+    for i, l in enumerate(lv):
+        g = gold[f"level{i}"]
+        err = np.abs(l.detach().cpu().numpy() - g)
+        assert err.max() <= 1.5e-2 * np.abs(g).max() and np.sqrt((err ** 2).mean()) <= 5e-3 * np.sqrt((g ** 2).mean()), (i, err.max())
+    sum(l.square().mean() for l in lv).backward()
+    bn = m.sppf.conv1.bn
+    assert bn.weight.grad is not None and torch.isfinite(bn.weight.grad).all() and int(bn.num_batches_tracked) == 0
