@@ -13,6 +13,8 @@
 // All tensors are NHWC bf16 with an explicit channel pitch (elements between consecutive pixels), so torch.cat along
 // channels never materialises: producers write into their slice.
 #include "hpe_common.cuh"
+#include "ptx_sm100.cuh"
+#include "tma_host.cuh"
 
 namespace hpe {
 
@@ -264,6 +266,94 @@ dwconv7_tiled_kernel(const __nv_bfloat16* __restrict__ x, int in_pitch, const fl
   }
 }
 
+// ---- The same, fed by TMA and software-pipelined (round 2).  ncu of the kernel above (C = 384 @16x12, B = 256): fp32 FMA pipe
+// active 42 % of the time, the rest staging (global load -> bf16->fp32 convert -> st.shared, `long_scoreboard` / `barrier`
+// stalls) that two co-resident CTAs overlap only by chance.  Here a PERSISTENT CTA owns one 64-channel slice (its 49 x 2 filter
+// weights stay in registers across tiles) and walks spatial tiles; the halo'd bf16 tile {64 ch, tw+6, th+6} arrives as ONE TMA
+// box (zero padding = out-of-bounds fill, no staging instructions at all) into a two-deep ring, so tile i+1 loads while tile i
+// computes; the inner loop converts bf16 pairs on the ALU pipe (two shifts per 8-byte... per 4-byte load) beside the packed FMAs.
+__global__ void __launch_bounds__(kDtMaxWarps * 32, 2)
+dwconv7_tma_kernel(const __grid_constant__ CUtensorMap tmX, const float* __restrict__ wt /* [49][C] */, const float* __restrict__ bias,
+                   int H, int W, int C, int th, int tw, int tiles_x, int tiles_y, int n_slices, int n_spatial, int tile_bytes,
+                   __nv_bfloat16* __restrict__ y, int out_pitch) {
+  using namespace ptx;
+  extern __shared__ uint8_t dsm_raw[];
+  uint8_t* dsm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(dsm_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ uint64_t full_bar[2];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const int slice = blockIdx.x % n_slices, sp0 = blockIdx.x / n_slices, sp_step = gridDim.x / n_slices;
+  const int c0 = slice * kDtSlice, ch = c0 + 2 * lane;
+  const bool chok = ch < C;
+  if (threadIdx.x == 0) { prefetch_tmap(&tmX); mbar_init(&full_bar[0], 1); mbar_init(&full_bar[1], 1); fence_mbar_init(); }
+  float2 w[49];
+#pragma unroll
+  for (int k = 0; k < 49; ++k) w[k] = chok ? __ldg(reinterpret_cast<const float2*>(wt + static_cast<size_t>(k) * C + ch)) : make_float2(0.f, 0.f);
+  const float2 bs = chok ? __ldg(reinterpret_cast<const float2*>(bias + ch)) : make_float2(0.f, 0.f);
+  __syncthreads();
+  const int pw = tw + 6;
+  auto issue = [&](int sp, int buf) {                 // one elected thread: the halo'd tile of spatial tile `sp`
+    const int tx = sp % tiles_x, ty = (sp / tiles_x) % tiles_y, b = sp / (tiles_x * tiles_y);
+    mbar_arrive_expect_tx(&full_bar[buf], tile_bytes);
+    tma_load_4d(dsm + buf * ((tile_bytes + 1023) & ~1023), &tmX, &full_bar[buf], c0, tx * tw - 3, ty * th - 3, b);
+  };
+  if (threadIdx.x == 0 && sp0 < n_spatial) issue(sp0, 0);
+  const int nbx = tw / kDtRX, nblk = (th / kDtTY) * nbx;
+  int it = 0;
+  for (int sp = sp0; sp < n_spatial; sp += sp_step, ++it) {
+    const int buf = it & 1;
+    if (threadIdx.x == 0 && sp + sp_step < n_spatial) issue(sp + sp_step, buf ^ 1);     // that buffer was drained before the last __syncthreads
+    mbar_wait(&full_bar[buf], (it >> 1) & 1);
+    const int tx = sp % tiles_x, ty = (sp / tiles_x) % tiles_y, b = sp / (tiles_x * tiles_y);
+    const int x0 = tx * tw, y0 = ty * th;
+    const uint32_t tbase = smem_u32(dsm + buf * ((tile_bytes + 1023) & ~1023));
+    for (int blk = warp; blk < nblk; blk += nwarps) {
+      const int by = (blk / nbx) * kDtTY, bx = (blk % nbx) * kDtRX;
+      float2 acc[kDtTY][kDtRX];
+#pragma unroll
+      for (int ry = 0; ry < kDtTY; ++ry)
+#pragma unroll
+        for (int rx = 0; rx < kDtRX; ++rx) acc[ry][rx] = bs;
+#pragma unroll
+      for (int iy = 0; iy < kDtTY + 6; ++iy) {
+#pragma unroll
+        for (int ix = 0; ix < kDtRX + 6; ++ix) {
+          // pixel row p of the box = 128 B (64 bf16), 16-byte chunks XOR-swizzled with (p & 7) by TMA (SWIZZLE_128B); a warp reads the
+          // whole row (lane -> channel pair 2 lane), i.e. every chunk once: conflict-free
+          const int pix = (by + iy) * pw + bx + ix;
+          uint32_t u;
+          asm volatile("ld.shared.u32 %0, [%1];" : "=r"(u) : "r"(tbase + pix * 128 + ((((lane >> 2) ^ (pix & 7)) << 4) | ((lane & 3) << 2))));
+          const float2 v = make_float2(__uint_as_float(u << 16), __uint_as_float(u & 0xffff0000u));
+#pragma unroll
+          for (int ry = 0; ry < kDtTY; ++ry) {
+            const int ky = iy - ry;
+            if (ky < 0 || ky > 6) continue;
+#pragma unroll
+            for (int rx = 0; rx < kDtRX; ++rx) {
+              const int kx = ix - rx;
+              if (kx < 0 || kx > 6) continue;
+              acc[ry][rx] = __ffma2_rn(v, w[ky * 7 + kx], acc[ry][rx]);
+            }
+          }
+        }
+      }
+      if (chok) {
+#pragma unroll
+        for (int ry = 0; ry < kDtTY; ++ry) {
+          const int oy = y0 + by + ry;
+          if (oy >= H) continue;
+#pragma unroll
+          for (int rx = 0; rx < kDtRX; ++rx) {
+            const int ox = x0 + bx + rx;
+            if (ox < W)
+              *reinterpret_cast<uint32_t*>(y + ((static_cast<size_t>(b) * H + oy) * W + ox) * out_pitch + ch) = pack_bf16(acc[ry][rx].x, acc[ry][rx].y);
+          }
+        }
+      }
+    }
+    __syncthreads();                                  // every warp is done with this buffer: it may be refilled two tiles later
+  }
+}
+
 // A pixel is normalised by a group of `gsz` lanes (power of two >= C/8, at most 32; narrow tensors put 2-8 pixels in a
 // warp); the pixel's channels stay in registers (C <= 1024: 4 x 16 B per lane), so the kernel is one read + one write and
 // in-place safe.
@@ -456,6 +546,33 @@ extern "C" int hpe_dwconv7_bias(const void* x, int in_pitch, int B, int H, int W
   const int tiles_y = (H + th - 1) / th, tiles_x = (W + tw - 1) / tw, n_slices = (C + kDtSlice - 1) / kDtSlice;
   const int nblk = (th / kDtTY) * (tw / kDtRX);
   const int warps = nblk <= kDtMaxWarps ? nblk : kDtMaxWarps;
+  {
+    // TMA-fed persistent variant (default; HPE_B200_DWCONV_TMA=0 keeps the staged kernel): x must be 16-byte aligned with a pitch
+    // that is a multiple of 8 channels (checked above)
+    static int use_tma = -1;
+    if (use_tma < 0) { const char* e = getenv("HPE_B200_DWCONV_TMA"); use_tma = (e && e[0] == '0') ? 0 : 1; }
+    const long long n_spatial = (long long)B * tiles_y * tiles_x;
+    if (use_tma && n_spatial < 0x7fffffffLL) {
+      CUtensorMap tm;
+      const uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)B};
+      const uint64_t str[3] = {(uint64_t)in_pitch * 2, (uint64_t)W * in_pitch * 2, (uint64_t)H * W * in_pitch * 2};
+      const uint32_t box[4] = {64, (uint32_t)(tw + 6), (uint32_t)(th + 6), 1};
+      const uint32_t ones[4] = {1, 1, 1, 1};
+      int rc = encode_map(&tm, x, 4, dims, str, box, ones, "dwconv7 x");
+      if (rc) return rc;
+      const int tile_bytes = (th + 6) * (tw + 6) * 128;
+      const size_t smem = 2 * (size_t)((tile_bytes + 1023) & ~1023) + 1024;
+      HPE_CUDA_OK(cudaFuncSetAttribute((const void*)dwconv7_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      // persistent grid: 2 CTAs per SM, a multiple of the slice count, every CTA at least one spatial tile
+      long long per_slice = (long long)num_sms() * 2 / n_slices;
+      if (per_slice < 1) per_slice = 1;
+      if (per_slice > n_spatial) per_slice = n_spatial;
+      const int grid = (int)(per_slice * n_slices);
+      dwconv7_tma_kernel<<<grid, warps * 32, smem, (cudaStream_t)stream>>>(tm, w_taps, bias, H, W, C, th, tw, tiles_x, tiles_y, n_slices,
+                                                                         (int)n_spatial, tile_bytes, (__nv_bfloat16*)y, out_pitch);
+      return launch_status("dwconv7_tma_kernel");
+    }
+  }
   const size_t smem = (size_t)(th + 6) * (tw + 6) * kDtSlice * 4;
   // per-DEVICE function attribute: set on every call that needs it
   if (smem > 48 * 1024)
