@@ -96,10 +96,15 @@ bnact_finish_kernel(const float* __restrict__ part, int nslices, long long M, in
                     const float* __restrict__ beta, float eps, float momentum, float* running_mean, float* running_var,
                     float* __restrict__ o0, float* __restrict__ o1, float* __restrict__ o2, float* __restrict__ o3,
                     float* __restrict__ coef, int frozen) {
-  const int c = blockIdx.x * 256 + threadIdx.x;
+  // a warp per channel: lane l adds slices l, l + 32, ... in order, then a fixed shuffle tree (deterministic; one thread walking
+  // up to 256 dependent loads per channel made these 116 tiny launches ~9 us each)
+  const int lane = threadIdx.x & 31, c = blockIdx.x * 8 + (threadIdx.x >> 5);
   if (c >= C) return;
   float s0 = 0.f, s1 = 0.f;
-  for (int s = 0; s < nslices; ++s) { s0 += part[(static_cast<size_t>(s) * 2) * C + c]; s1 += part[(static_cast<size_t>(s) * 2 + 1) * C + c]; }
+  for (int s = lane; s < nslices; s += 32) { s0 += part[(static_cast<size_t>(s) * 2) * C + c]; s1 += part[(static_cast<size_t>(s) * 2 + 1) * C + c]; }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { s0 += __shfl_xor_sync(0xffffffffu, s0, o); s1 += __shfl_xor_sync(0xffffffffu, s1, o); }
+  if (lane != 0) return;
   const float inv = 1.f / static_cast<float>(M);
   if (MODE == 1) {
     o0[c] = s0; o1[c] = s1;                                    // dbeta, dgamma
@@ -388,7 +393,7 @@ extern "C" int hpe_bnact_stats(const void* z, long long M, int C, const float* g
   bnact_reduce_kernel<0><<<grid, 256, 0, st>>>((const __nv_bfloat16*)z, nullptr, M, C, 0, nullptr, nullptr, nullptr, nullptr, scratch);
   rc = launch_status("bnact_reduce_kernel<0>");
   if (rc) return rc;
-  bnact_finish_kernel<0><<<(C + 255) / 256, 256, 0, st>>>(scratch, ns, M, C, gamma, beta, eps, momentum, running_mean, running_var,
+  bnact_finish_kernel<0><<<(C + 7) / 8, 256, 0, st>>>(scratch, ns, M, C, gamma, beta, eps, momentum, running_mean, running_var,
                                                         scale, shift, mean, rstd, nullptr, 0);
   return launch_status("bnact_finish_kernel<0>");
 }
@@ -418,7 +423,7 @@ extern "C" int hpe_bnact_backward(const void* dy, const void* z, long long M, in
   bnact_reduce_kernel<1><<<grid, 256, 0, st>>>((const __nv_bfloat16*)z, (const __nv_bfloat16*)dy, M, C, act, scale, shift, mean, rstd, scratch);
   rc = launch_status("bnact_reduce_kernel<1>");
   if (rc) return rc;
-  bnact_finish_kernel<1><<<(C + 255) / 256, 256, 0, st>>>(scratch, ns, M, C, gamma, nullptr, 0.f, 0.f, nullptr, nullptr, dbeta, dgamma,
+  bnact_finish_kernel<1><<<(C + 7) / 8, 256, 0, st>>>(scratch, ns, M, C, gamma, nullptr, 0.f, 0.f, nullptr, nullptr, dbeta, dgamma,
                                                         const_cast<float*>(mean), const_cast<float*>(rstd), coef, frozen_stats ? 1 : 0);
   rc = launch_status("bnact_finish_kernel<1>");
   if (rc) return rc;
@@ -434,7 +439,7 @@ extern "C" int hpe_dwconv3_wgrad(const void* x, const void* dz, int B, int H, in
   HPE_CHECK_ARG(x && dz && scratch && dw_torch && B > 0 && H > 0 && W > 0 && C > 0 && C % 8 == 0, "hpe_dwconv3_wgrad: bad argument");
   HPE_CHECK_ARG((((uintptr_t)x | (uintptr_t)dz) & 15) == 0, "hpe_dwconv3_wgrad: misaligned pointer");
   cudaStream_t st = (cudaStream_t)stream;
-  const int ns = nt_slices((long long)B * H);
+  const int ns = nt_slices((long long)B * H * 32);          // ~4 image rows per block (the channel groups alone are 1-3 blocks)
   const dim3 grid((C / 8 + 31) / 32, ns);
   dwconv3_wgrad_kernel<<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)dz, B, H, W, C, scratch);
   int rc = launch_status("dwconv3_wgrad_kernel");
