@@ -1252,8 +1252,13 @@ static ConvKernelFn pick_kernel_pair(int act, bool res, size_t* smem) {
   }
 }
 
-// two epilogue groups (608 threads) on the 256-wide pair kernel with a residual: 3 ring stages + 2 x 3 staging buffers
-static ConvKernelFn pick_kernel_epi2(int act, size_t* smem) {
+// two epilogue groups (608 threads) on the 256-wide pair kernel: with a residual 3 ring stages + 2 x 3 staging buffers; without
+// one (the GELU epilogue of ConvNeXt's pwconv1: 5 FMAs + 2 MUFUs per element over 4C channels) 4 stages + 2 x 2 buffers
+static ConvKernelFn pick_kernel_epi2(int act, bool res, size_t* smem) {
+  if (!res) {
+    *smem = SmemLayout<256, 4, true, 4, false, true>::kDynamic;
+    return act == HPE_ACT_GELU ? conv_gemm_kernel<256, 4, HPE_ACT_GELU, false, false, true, false, true> : nullptr;
+  }
   *smem = SmemLayout<256, 3, true, 6, false, true>::kDynamic;
   switch (act) {
     case HPE_ACT_RELU: return conv_gemm_kernel<256, 3, HPE_ACT_RELU, true, false, true, false, true>;
@@ -1292,7 +1297,7 @@ static ConvKernelFn pick_kernel_chain(int cout, int n2, bool res, int num_kb, si
 // ring depths: as many stages as fit beside the staging buffers in the 227 KB a CTA may use
 static ConvKernelFn pick_kernel(int block_n, int act, bool res, bool fin, bool pair, bool head2, bool epi2, size_t* smem) {
   if (head2) { *smem = SmemLayout<256, 4, true, 4, true>::kDynamic; return conv_gemm_kernel<256, 4, HPE_ACT_RELU, false, false, true, true>; }
-  if (epi2) return pick_kernel_epi2(act, smem);
+  if (epi2) return pick_kernel_epi2(act, res, smem);
   if (pair && block_n == 256) return pick_kernel_pair<256, 5, 5>(act, res, smem);       // 32 KB stages (A + half of B)
   if (pair && block_n == 192) return pick_kernel_pair<192, 6, 5>(act, res, smem);       // 28 KB stages (ConvNeXt C = 192/384/768)
   if (pair) return pick_kernel_pair<128, 7, 6>(act, res, smem);                         // 24 KB stages
@@ -1373,7 +1378,10 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
     const char* e = getenv("HPE_B200_EPI2");
     const int mode = e ? atoi(e) : 1;
     const int num_kb = p.taps * p.kc_per_tap + p.kc2;
-    pl->epi2 = mode != 0 && pl->pair && pl->block_n == 256 && p.has_res && !d->head2 && d->act != HPE_ACT_GELU && (mode == 2 || num_kb <= 8);
+    const char* eg = getenv("HPE_B200_EPI2_GELU");
+    const bool gelu2 = d->act == HPE_ACT_GELU && !p.has_res && !(eg && eg[0] == '0');        // epilogue-bound GELU layers (pwconv1)
+    pl->epi2 = mode != 0 && pl->pair && pl->block_n == 256 && !d->head2 &&
+               ((p.has_res && d->act != HPE_ACT_GELU && (mode == 2 || num_kb <= 8)) || gelu2);
   }
   pl->fn = d->chain ? (const void*)pick_kernel_chain(d->Cout, d->chain, p.has_res != 0, p.taps * p.kc_per_tap + p.kc2, &pl->smem)
                     : (const void*)pick_kernel(pl->block_n, d->act, p.has_res != 0, d->kind == HPE_CONV_FINAL, pl->pair != 0, d->head2 != 0, pl->epi2 != 0, &pl->smem);
