@@ -264,7 +264,11 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   static_assert((KBR != 0) == (CHAIN != 0 && NH == 1) && KBR <= 2, "resident weights: the 256-channel chained kernels (1-2 k-blocks per tile)");
   static_assert(NH == 1 || ((NH == 2 || NH == 4) && CHAIN == 128 && NH * BLOCK_N == 512), "several N tiles per pixel tile: the 512 -> 128 chain of layer2");
   // CHAIN: one ring for both groups, as deep as fits (the residual rides it with a lead of kNumSB - 2 chunks)
-  constexpr int kNumSB = FINAL ? 0 : (CHAIN ? ((RES && CHAIN == 64) ? 6 : 4) : (EPI2 ? (RES ? 3 : 2) : ((RES || HEAD2) ? 4 : 3)));
+  // RING6: the 256-wide pair kernel without a residual with SIX ring stages -- the deep-K layers are bound by bytes in flight per
+  // SM -- paid for by a 2-buffer staging ring under the `wait_group.read 0` protocol (the leader waits for the previous chunk's
+  // store to have left shared memory; these layers' epilogues have slack)
+  constexpr bool kRing6 = PAIR && !RES && !HEAD2 && !EPI2 && CHAIN == 0 && BLOCK_N == 256 && STAGES == 6;
+  constexpr int kNumSB = FINAL ? 0 : (CHAIN ? ((RES && CHAIN == 64) ? 6 : 4) : ((EPI2 || kRing6) ? (RES ? 3 : 2) : ((RES || HEAD2) ? 4 : 3)));
   constexpr int kResLead = 2;                     // the residual of chunk q + 2 is requested while chunk q is processed
   constexpr int kLead = CHAIN ? kNumSB - 2 : kResLead;
   constexpr int kChunks2 = CHAIN / 64;            // 64-column chunks of the chained conv's output
@@ -646,7 +650,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const int sb = HEAD2 ? c : q % kNumSB;                    // fused head: the tile's four chunks stay staged (A' operand)
           const uint32_t stg = smem_u32(sSB + sb * kSBBytes);
           if (!HEAD2 && leader) {
-            bulk_wait_read<EPI2 ? 0 : 1>();                         // stores <= q-2 (EPI2: <= q-1) have left shared memory
+            bulk_wait_read<(EPI2 || kRing6) ? 0 : 1>();             // stores <= q-2 (EPI2 / RING6: <= q-1) have left shared memory
             if (RES) mbar_arrive(&sbempty_bar[(q + kLead) % kNumSB]);   // hand the buffer of chunk q + lead to warp 2
           }
           uint32_t v[32];
@@ -1241,6 +1245,16 @@ static ConvKernelFn pick_kernel_bn(int act, bool res, bool fin, size_t* smem) {
   return nullptr;
 }
 
+static ConvKernelFn pick_kernel_ring6(int act, size_t* smem) {
+  *smem = SmemLayout<256, 6, true, 2>::kDynamic;
+  switch (act) {
+    case HPE_ACT_RELU: return conv_gemm_kernel<256, 6, HPE_ACT_RELU, false, false, true>;
+    case HPE_ACT_SILU: return conv_gemm_kernel<256, 6, HPE_ACT_SILU, false, false, true>;
+    case HPE_ACT_NONE: return conv_gemm_kernel<256, 6, HPE_ACT_NONE, false, false, true>;
+    default:           return nullptr;
+  }
+}
+
 template <int BN, int ST_N, int ST_R>
 static ConvKernelFn pick_kernel_pair(int act, bool res, size_t* smem) {
   *smem = res ? SmemLayout<BN, ST_R, true, 4>::kDynamic : SmemLayout<BN, ST_N, true, 3>::kDynamic;
@@ -1298,6 +1312,11 @@ static ConvKernelFn pick_kernel_chain(int cout, int n2, bool res, int num_kb, si
 static ConvKernelFn pick_kernel(int block_n, int act, bool res, bool fin, bool pair, bool head2, bool epi2, size_t* smem) {
   if (head2) { *smem = SmemLayout<256, 4, true, 4, true>::kDynamic; return conv_gemm_kernel<256, 4, HPE_ACT_RELU, false, false, true, true>; }
   if (epi2) return pick_kernel_epi2(act, res, smem);
+  if (pair && block_n == 256 && !res && act != HPE_ACT_GELU) {
+    static int ring6 = -1;
+    if (ring6 < 0) { const char* e = getenv("HPE_B200_RING6"); ring6 = (e && e[0] == '0') ? 0 : 1; }       // default on: forward 3.228 -> 3.214 ms (two A/B pairs)
+    if (ring6) return pick_kernel_ring6(act, smem);
+  }
   if (pair && block_n == 256) return pick_kernel_pair<256, 5, 5>(act, res, smem);       // 32 KB stages (A + half of B)
   if (pair && block_n == 192) return pick_kernel_pair<192, 6, 5>(act, res, smem);       // 28 KB stages (ConvNeXt C = 192/384/768)
   if (pair) return pick_kernel_pair<128, 7, 6>(act, res, smem);                         // 24 KB stages
