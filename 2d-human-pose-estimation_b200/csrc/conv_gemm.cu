@@ -267,7 +267,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   // RING6: the 256-wide pair kernel without a residual with SIX ring stages -- the deep-K layers are bound by bytes in flight per
   // SM -- paid for by a 2-buffer staging ring under the `wait_group.read 0` protocol (the leader waits for the previous chunk's
   // store to have left shared memory; these layers' epilogues have slack)
-  constexpr bool kRing6 = PAIR && !RES && !HEAD2 && !EPI2 && CHAIN == 0 && BLOCK_N == 256 && STAGES == 6;
+  constexpr bool kRing6 = !RES && !HEAD2 && !EPI2 && !FINAL && CHAIN == 0 && STAGES == 6 && ((PAIR && BLOCK_N == 256) || (!PAIR && BLOCK_N == 128));
   constexpr int kNumSB = FINAL ? 0 : (CHAIN ? ((RES && CHAIN == 64) ? 6 : 4) : ((EPI2 || kRing6) ? (RES ? 3 : 2) : ((RES || HEAD2) ? 4 : 3)));
   constexpr int kResLead = 2;                     // the residual of chunk q + 2 is requested while chunk q is processed
   constexpr int kLead = CHAIN ? kNumSB - 2 : kResLead;
@@ -1255,6 +1255,16 @@ static ConvKernelFn pick_kernel_ring6(int act, size_t* smem) {
   }
 }
 
+static ConvKernelFn pick_kernel_ring6_128(int act, size_t* smem) {       // single-CTA 128-wide tiles (layer2's 3x3, 256 -> 128 1x1)
+  *smem = SmemLayout<128, 6, false, 2>::kDynamic;
+  switch (act) {
+    case HPE_ACT_RELU: return conv_gemm_kernel<128, 6, HPE_ACT_RELU, false, false>;
+    case HPE_ACT_SILU: return conv_gemm_kernel<128, 6, HPE_ACT_SILU, false, false>;
+    case HPE_ACT_NONE: return conv_gemm_kernel<128, 6, HPE_ACT_NONE, false, false>;
+    default:           return nullptr;
+  }
+}
+
 template <int BN, int ST_N, int ST_R>
 static ConvKernelFn pick_kernel_pair(int act, bool res, size_t* smem) {
   *smem = res ? SmemLayout<BN, ST_R, true, 4>::kDynamic : SmemLayout<BN, ST_N, true, 3>::kDynamic;
@@ -1320,6 +1330,11 @@ static ConvKernelFn pick_kernel(int block_n, int act, bool res, bool fin, bool p
   if (pair && block_n == 256) return pick_kernel_pair<256, 5, 5>(act, res, smem);       // 32 KB stages (A + half of B)
   if (pair && block_n == 192) return pick_kernel_pair<192, 6, 5>(act, res, smem);       // 28 KB stages (ConvNeXt C = 192/384/768)
   if (pair) return pick_kernel_pair<128, 7, 6>(act, res, smem);                         // 24 KB stages
+  if (!pair && block_n == 128 && !res && !fin && act != HPE_ACT_GELU) {
+    static int r128 = -1;
+    if (r128 < 0) { const char* e = getenv("HPE_B200_RING6_128"); r128 = (e && e[0] == '1') ? 1 : 0; }
+    if (r128) return pick_kernel_ring6_128(act, smem);
+  }
   switch (block_n) {
     case 32:  return pick_kernel_bn<32, 6, 6, 11>(act, res, fin, smem);     // 20 KB stages (FINAL only)
     case 64:  return pick_kernel_bn<64, 7, 6, 9>(act, res, fin, smem);      // 24 KB stages
