@@ -67,9 +67,26 @@ struct ConvParams {
   const float* scale2;          // CHAIN: folded-BN scale / shift [N2] of the chained 1x1 conv
   const float* shift2;
   int res_prefetch;             // != 0: the residual producer prefetches the NEXT tile's residual boxes into L2 while it serves this one
+  int chain_defer;              // CHAIN: the chained conv's output chunks of tile i are drained after this many chunks of tile i+1 (0 = right behind tile i)
 };
 
 struct TileCoord { int n_tile, cls, x0, y0, b0; };
+
+// CHAIN kernels: entry q of a CTA's chunk sequence.  Tile i contributes kCT chunks of the layer's own output and kC2 chunks of the
+// chained conv's output (c >= kCT); the latter need the second GEMM over ALL of tile i's chunks, so they are walked `defer` chunks
+// into tile i+1 (right behind the last tile's chunks for the last tile) -- by then their accumulator has long been committed and
+// no epilogue group waits for it.  defer = 0 is the plain order [tile i | its chained chunks].  The residual producer, the second
+// GEMM's issuer and both epilogue groups all walk this one sequence; false = past the end.
+template <int kCT, int kC2>
+__device__ __forceinline__ bool chain_seq(int q, int my_tiles, int defer, int& it, int& c) {
+  if (q < kCT) { it = 0; c = q; return my_tiles > 0; }
+  const int q2 = q - kCT, j = q2 / (kCT + kC2), pos = q2 - j * (kCT + kC2);
+  if (j + 1 >= my_tiles) { it = my_tiles - 1; c = kCT + pos; return pos < kC2; }        // behind the last tile: its chained chunks
+  if (pos < defer) { it = j + 1; c = pos; }
+  else if (pos < defer + kC2) { it = j; c = kCT + pos - defer; }
+  else { it = j + 1; c = pos - kC2; }
+  return true;
+}
 
 __device__ __forceinline__ TileCoord tile_coord(const ConvParams& p, int tile) {
   TileCoord t;
@@ -457,6 +474,25 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
           }
         }
+      } else if constexpr (CHAIN != 0) {
+        // one ring in the order of chain_seq: the chained conv's output chunks take a buffer too, but carry no residual
+        const int my_tiles = work0 < p.num_tiles ? (p.num_tiles - 1 - work0) / wstep + 1 : 0;
+        TileCoord t = {};
+        int it = 0, c = 0, it_cur = -1;
+        for (int r = 0; chain_seq<NH * kChunks, kChunks2>(r, my_tiles, p.chain_defer, it, c); ++r) {
+          const int b = r % kNumSB;
+          mbar_wait(&sbempty_bar[b], (r / kNumSB) & 1);     // the epilogue leaders hand buffers over with a lead of kLead chunks
+          if (c >= NH * kChunks) { mbar_arrive(&sbfull_bar[b]); continue; }
+          if (it != it_cur) {
+            it_cur = it; t = tile_coord(p, work0 + it * wstep);
+            if (p.res_prefetch && it + 1 < my_tiles) {       // (experiment, off) the next tile's residual boxes into L2 a tile ahead
+              const TileCoord tn = tile_coord(p, work0 + (it + 1) * wstep);
+              for (int cn = 0; cn < NH * kChunks; ++cn) tma_prefetch_l2_4d(&tmRes, tn.n_tile * NH * BLOCK_N + cn * 64, tn.x0, tn.y0, tn.b0);
+            }
+          }
+          mbar_arrive_expect_tx(&sbfull_bar[b], kSBBytes);
+          tma_load_4d(sSB + b * kSBBytes, &tmRes, &sbfull_bar[b], t.n_tile * NH * BLOCK_N + c * 64, t.x0, t.y0, t.b0);
+        }
       } else {
         int r = 0;
         for (int work = work0; work < p.num_tiles; work += wstep) {
@@ -465,14 +501,13 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             // the ring's lead (2-4 chunks) is shorter than the HBM latency once two epilogue groups drain it: pull the next tile's
             // residual into L2 a whole tile ahead, so the ring's own loads are L2 hits
             const TileCoord tn = tile_coord(p, work_tile<PAIR>(p, work + wstep, rank));
-            for (int c = 0; c < NH * kChunks; ++c) tma_prefetch_l2_4d(&tmRes, tn.n_tile * NH * BLOCK_N + c * 64, tn.x0, tn.y0, tn.b0);
+            for (int c = 0; c < kChunks; ++c) tma_prefetch_l2_4d(&tmRes, tn.n_tile * BLOCK_N + c * 64, tn.x0, tn.y0, tn.b0);
           }
-          for (int c = 0; c < NH * kChunks + kChunks2; ++c, ++r) {
+          for (int c = 0; c < kChunks; ++c, ++r) {
             const int b = r % kNumSB;
             mbar_wait(&sbempty_bar[b], (r / kNumSB) & 1);   // the epilogue leader hands buffers over with a lead of kResLead chunks
-            if (c >= NH * kChunks) { mbar_arrive(&sbfull_bar[b]); continue; }     // CHAIN: the chained conv's output chunk has no residual
             mbar_arrive_expect_tx(&sbfull_bar[b], kSBBytes);
-            tma_load_4d(sSB + b * kSBBytes, &tmRes, &sbfull_bar[b], t.n_tile * NH * BLOCK_N + c * 64, t.x0, t.y0, t.b0);
+            tma_load_4d(sSB + b * kSBBytes, &tmRes, &sbfull_bar[b], t.n_tile * BLOCK_N + c * 64, t.x0, t.y0, t.b0);
           }
         }
       }
@@ -484,7 +519,6 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if constexpr (CHAIN != 0) {
       if (lane == 0) {
         constexpr int kCT = NH * kChunks;                        // real chunks per tile (4 of y per 256-wide half)
-        constexpr int kCPT = kCT + kChunks2;                     // ... then 1-2 of the chained output
         constexpr uint32_t kIdesc2 = make_idesc_bf16_m128(CHAIN);
         constexpr int kSlice = CHAIN * 128;                      // bytes of one [N2][64] K slice of the chained weights
         if constexpr (NH == 1) mbar_wait(w2full_bar, 0);
@@ -502,41 +536,39 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           ++w_req;
         };
         if constexpr (NH >= 2) { while (w_req < kW2Slots - 1 && w_req < w_total) request(); }
-        for (int work = work0; work < p.num_tiles; work += wstep, ++it) {
-          const int a2 = it & 1;
-          mbar_wait(&a2empty_bar[a2], ((it >> 1) & 1) ^ 1);      // tile it-2's chained output has left accumulator a2
-          for (int c = 0; c < kCPT; ++c, ++q) {
-            const int sb = q % kNumSB;
-            if (NH >= 2 && c < kCT && w_req < w_total) request();
-            mbar_wait(&staged_bar[sb], (q / kNumSB) & 1);
-            if (c < kCT) {
-              const uint8_t* wsl = sW2 + c * kSlice;
-              if constexpr (NH >= 2) {
-                const int slot = w_use % kW2Slots;
-                mbar_wait(&w2rfull_bar[slot], (w_use / kW2Slots) & 1);
-                wsl = sW2 + slot * kSlice;
-              }
-              tc_fence_after();
-              const uint64_t adesc = make_sw128_kmajor_desc(sSB + sb * kSBBytes);
-              const uint64_t bdesc = make_sw128_kmajor_desc(wsl);
-#pragma unroll
-              for (int k = 0; k < 4; ++k) umma_bf16(tmem_base + 256 + a2 * CHAIN, adesc + 2 * k, bdesc + 2 * k, kIdesc2, (c | k) != 0);
-              if constexpr (NH >= 2) { umma_commit(&w2rempty_bar[w_use % kW2Slots]); ++w_use; }
+        int c = 0;
+        for (; chain_seq<kCT, kChunks2>(q, my_tiles, p.chain_defer, it, c); ++q) {
+          const int sb = q % kNumSB, a2 = it & 1;
+          if (c == 0) mbar_wait(&a2empty_bar[a2], ((it >> 1) & 1) ^ 1);      // tile it-2's chained output has left accumulator a2
+          if (NH >= 2 && c < kCT && w_req < w_total) request();
+          mbar_wait(&staged_bar[sb], (q / kNumSB) & 1);
+          if (c < kCT) {
+            const uint8_t* wsl = sW2 + c * kSlice;
+            if constexpr (NH >= 2) {
+              const int slot = w_use % kW2Slots;
+              mbar_wait(&w2rfull_bar[slot], (w_use / kW2Slots) & 1);
+              wsl = sW2 + slot * kSlice;
             }
-            umma_commit(&g2_bar[sb]);                            // every chunk commits: a buffer's phase sequence stays uniform
-            if (c == kCT - 1) umma_commit(&d2full_bar[a2]);
+            tc_fence_after();
+            const uint64_t adesc = make_sw128_kmajor_desc(sSB + sb * kSBBytes);
+            const uint64_t bdesc = make_sw128_kmajor_desc(wsl);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) umma_bf16(tmem_base + 256 + a2 * CHAIN, adesc + 2 * k, bdesc + 2 * k, kIdesc2, (c | k) != 0);
+            if constexpr (NH >= 2) { umma_commit(&w2rempty_bar[w_use % kW2Slots]); ++w_use; }
           }
+          umma_commit(&g2_bar[sb]);                              // every chunk commits: a buffer's phase sequence stays uniform
+          if (c == kCT - 1) umma_commit(&d2full_bar[a2]);
         }
       }
     }
   } else if (CHAIN != 0) {
     // ===================== CHAIN: two epilogue groups, chunk-interleaved =====================
-    // Chunk q = it * kCPT + c of this CTA's chunk sequence goes to group q & 1 (warps 4-11 / 12-19): both groups drain the SAME
+    // Entry q of this CTA's chunk sequence (chain_seq) goes to group q & 1 (warps 4-11 / 12-19): both groups drain the SAME
     // tile, so two tcgen05.ld -> residual wait -> math -> fence -> barrier -> store chains are in flight (a single group ran the
     // chained kernel at 11.6 k cycles per tile against ~7.9 k of HBM time).  The buffers form ONE ring in chunk order; with an
     // even buffer count, or the residual hand-over two chunks back, a buffer is always recycled by the group that stored it.
     if constexpr (CHAIN != 0) {
-      constexpr int kCT = NH * kChunks, kCPT = kCT + kChunks2;
+      constexpr int kCT = NH * kChunks;
       const int grp = (warp - 4) >> 3, ew = warp & 3, half = ((warp - 4) >> 2) & 1, row = ew * 32 + lane;
       const int atid = threadIdx.x - 128, etid = atid - grp * kEpiThreads;
       const bool leader = etid == 0;
@@ -547,13 +579,13 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       named_bar_sync(3, 2 * kEpiThreads);
       if (RES && atid == 0) for (int b = 0; b < kLead; ++b) mbar_arrive(&sbempty_bar[b]);
       const uint32_t taddr0 = tmem_base + (static_cast<uint32_t>(ew * 32) << 16);
-      int it_cur = -1;
-      TileCoord t = {};
-      for (int q = grp; ; q += 2) {
-        const int it = q / kCPT, c = q - it * kCPT;
-        const int work = work0 + it * wstep;
-        if (work >= p.num_tiles) break;
-        if (it != it_cur) { t = tile_coord(p, work); it_cur = it; }
+      const int my_tiles = work0 < p.num_tiles ? (p.num_tiles - 1 - work0) / wstep + 1 : 0;
+      TileCoord tce = {}, tco = {};                              // coordinates of the even / odd tile in flight (a deferred chained chunk
+      int ite = -1, ito = -1, it = 0, c = 0;                     // belongs to the tile BEFORE the one whose chunks surround it)
+      for (int q = grp; chain_seq<kCT, kChunks2>(q, my_tiles, p.chain_defer, it, c); q += 2) {
+        if (it & 1) { if (ito != it) { tco = tile_coord(p, work0 + it * wstep); ito = it; } }
+        else        { if (ite != it) { tce = tile_coord(p, work0 + it * wstep); ite = it; } }
+        const TileCoord t = (it & 1) ? tco : tce;
         const bool e2 = c >= kCT;
         const int sb = q % kNumSB, a2 = it & 1;
         const int nh = e2 ? 0 : c / kChunks, cc = e2 ? c - kCT : c - nh * kChunks;     // 256-wide half, chunk inside it
@@ -1656,6 +1688,11 @@ static int conv_launch(hpe_conv_plan* pl, const void* x, const void* x2, const v
     static int mode = -1;
     if (mode < 0) { const char* e = getenv("HPE_B200_RES_PREFETCH"); mode = e ? atoi(e) : 0; }
     p.res_prefetch = p.has_res && (mode == 2 || (mode == 1 && pl->d.chain)) ? 1 : 0;
+    // chained kernels: drain tile i's chained-conv output two chunks into tile i+1 (chain_seq); HPE_B200_CHAIN_DEFER=0 = right behind
+    // tile i, where the group that gets it waits for the second GEMM over the chunk the OTHER group has only just staged
+    static int defer = -1;
+    if (defer < 0) { const char* e = getenv("HPE_B200_CHAIN_DEFER"); defer = (e && atoi(e) == 0) ? 0 : 2; }
+    p.chain_defer = pl->d.chain ? defer : 0;
   }
   if (!p.has_res && !pl->d.head2) pl->tmRes = pl->tmA;      // unused, but must be a valid object to copy
   if (pl->d.kind == HPE_CONV_FINAL || pl->d.head2) for (int c = 0; c < 4; ++c) pl->tmOut.m[c] = pl->tmA;
