@@ -68,6 +68,8 @@ struct ConvParams {
   const float* shift2;
   int res_prefetch;             // != 0: the residual producer prefetches the NEXT tile's residual boxes into L2 while it serves this one
   int chain_defer;              // CHAIN: the chained conv's output chunks of tile i are drained after this many chunks of tile i+1 (0 = right behind tile i)
+  int reverse;                  // != 0: the work items are walked from the last to the first (hpe_conv_set_schedule)
+  unsigned long long l2_out, l2_res;     // != 0: L2 eviction-priority policy word of the output stores / the residual loads
 };
 
 struct TileCoord { int n_tile, cls, x0, y0, b0; };
@@ -170,6 +172,7 @@ __device__ __forceinline__ uint32_t relu_bf16x2(uint32_t v) {
 // stores are clipped.
 template <bool PAIR>
 __device__ __forceinline__ int work_tile(const ConvParams& p, int work, int rank) {
+  if (p.reverse) work = p.num_tiles - 1 - work;
   if (!PAIR) return work;
   const int per_m = p.n_tiles_n * p.n_classes;
   return ((work / per_m) * 2 + rank) * per_m + work % per_m;
@@ -451,6 +454,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       mbar_arrive_expect_tx(w2full_bar, L::kW2Bytes);
       for (int kb = 0; kb < 4; ++kb) tma_load_2d(sW2 + kb * (CHAIN * 128), &tmOut.m[2], w2full_bar, kb * kKBlock, 0);
     }
+    auto res_load = [&](void* dst, uint64_t* bar, int c0, int c1, int c2, int c3) {
+      if (p.l2_res) tma_load_4d_hint(dst, &tmRes, bar, c0, c1, c2, c3, p.l2_res); else tma_load_4d(dst, &tmRes, bar, c0, c1, c2, c3);
+    };
     if (RES && lane == 0) {
       if constexpr (EPI2) {
         // two rings (one per epilogue group, tiles it & 1 == g): one thread serves both, polling so that neither ring waits
@@ -466,7 +472,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const int b = g * kNumSB + rr[g] % kNumSB;
             if (!mbar_test_wait(&sbempty_bar[b], (rr[g] / kNumSB) & 1)) continue;
             mbar_arrive_expect_tx(&sbfull_bar[b], kSBBytes);
-            tma_load_4d(sSB + b * kSBBytes, &tmRes, &sbfull_bar[b], tg[g].n_tile * BLOCK_N + ch[g] * 64, tg[g].x0, tg[g].y0, tg[g].b0);
+            res_load(sSB + b * kSBBytes, &sbfull_bar[b], tg[g].n_tile * BLOCK_N + ch[g] * 64, tg[g].x0, tg[g].y0, tg[g].b0);
             ++rr[g];
             if (++ch[g] == kChunks) {
               ch[g] = 0; wk[g] += 2 * wstep;
@@ -484,14 +490,14 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           mbar_wait(&sbempty_bar[b], (r / kNumSB) & 1);     // the epilogue leaders hand buffers over with a lead of kLead chunks
           if (c >= NH * kChunks) { mbar_arrive(&sbfull_bar[b]); continue; }
           if (it != it_cur) {
-            it_cur = it; t = tile_coord(p, work0 + it * wstep);
+            it_cur = it; t = tile_coord(p, work_tile<false>(p, work0 + it * wstep, 0));
             if (p.res_prefetch && it + 1 < my_tiles) {       // (experiment, off) the next tile's residual boxes into L2 a tile ahead
-              const TileCoord tn = tile_coord(p, work0 + (it + 1) * wstep);
+              const TileCoord tn = tile_coord(p, work_tile<false>(p, work0 + (it + 1) * wstep, 0));
               for (int cn = 0; cn < NH * kChunks; ++cn) tma_prefetch_l2_4d(&tmRes, tn.n_tile * NH * BLOCK_N + cn * 64, tn.x0, tn.y0, tn.b0);
             }
           }
           mbar_arrive_expect_tx(&sbfull_bar[b], kSBBytes);
-          tma_load_4d(sSB + b * kSBBytes, &tmRes, &sbfull_bar[b], t.n_tile * NH * BLOCK_N + c * 64, t.x0, t.y0, t.b0);
+          res_load(sSB + b * kSBBytes, &sbfull_bar[b], t.n_tile * NH * BLOCK_N + c * 64, t.x0, t.y0, t.b0);
         }
       } else {
         int r = 0;
@@ -507,7 +513,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const int b = r % kNumSB;
             mbar_wait(&sbempty_bar[b], (r / kNumSB) & 1);   // the epilogue leader hands buffers over with a lead of kResLead chunks
             mbar_arrive_expect_tx(&sbfull_bar[b], kSBBytes);
-            tma_load_4d(sSB + b * kSBBytes, &tmRes, &sbfull_bar[b], t.n_tile * BLOCK_N + c * 64, t.x0, t.y0, t.b0);
+            res_load(sSB + b * kSBBytes, &sbfull_bar[b], t.n_tile * BLOCK_N + c * 64, t.x0, t.y0, t.b0);
           }
         }
       }
@@ -583,8 +589,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       TileCoord tce = {}, tco = {};                              // coordinates of the even / odd tile in flight (a deferred chained chunk
       int ite = -1, ito = -1, it = 0, c = 0;                     // belongs to the tile BEFORE the one whose chunks surround it)
       for (int q = grp; chain_seq<kCT, kChunks2>(q, my_tiles, p.chain_defer, it, c); q += 2) {
-        if (it & 1) { if (ito != it) { tco = tile_coord(p, work0 + it * wstep); ito = it; } }
-        else        { if (ite != it) { tce = tile_coord(p, work0 + it * wstep); ite = it; } }
+        if (it & 1) { if (ito != it) { tco = tile_coord(p, work_tile<false>(p, work0 + it * wstep, 0)); ito = it; } }
+        else        { if (ite != it) { tce = tile_coord(p, work_tile<false>(p, work0 + it * wstep, 0)); ite = it; } }
         const TileCoord t = (it & 1) ? tco : tce;
         const bool e2 = c >= kCT;
         const int sb = q % kNumSB, a2 = it & 1;
@@ -612,8 +618,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         fence_proxy_async_smem();                                // generic-proxy writes -> visible to TMA and to the tensor core
         named_bar_sync(bar_id, kEpiThreads);
         if (leader) {
-          if (e2) tma_store_4d(&tmOut.m[1], sSB + sb * kSBBytes, cc * 64, t.x0, t.y0, t.b0);
-          else    tma_store_4d(&tmOut.m[0], sSB + sb * kSBBytes, c * 64, t.x0, t.y0, t.b0);
+          if (e2)            tma_store_4d(&tmOut.m[1], sSB + sb * kSBBytes, cc * 64, t.x0, t.y0, t.b0);
+          else if (p.l2_out) tma_store_4d_hint(&tmOut.m[0], sSB + sb * kSBBytes, c * 64, t.x0, t.y0, t.b0, p.l2_out);
+          else               tma_store_4d(&tmOut.m[0], sSB + sb * kSBBytes, c * 64, t.x0, t.y0, t.b0);
           bulk_commit();
           mbar_arrive(&staged_bar[sb]);
         }
@@ -741,7 +748,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             fence_proxy_async_smem();                                // generic-proxy writes -> visible to TMA
             named_bar_sync(bar_id, kEpiThreads);
             if (leader) {
-              tma_store_4d(&tmOut.m[t.cls], sSB + sb * kSBBytes, t.n_tile * BLOCK_N + c * 64, t.x0, t.y0, t.b0);
+              if (p.l2_out) tma_store_4d_hint(&tmOut.m[t.cls], sSB + sb * kSBBytes, t.n_tile * BLOCK_N + c * 64, t.x0, t.y0, t.b0, p.l2_out);
+              else          tma_store_4d(&tmOut.m[t.cls], sSB + sb * kSBBytes, t.n_tile * BLOCK_N + c * 64, t.x0, t.y0, t.b0);
               bulk_commit();
             }
           }
@@ -1061,6 +1069,23 @@ static int pick_block_n(const hpe_conv_desc* d, long long /*m_tiles*/) {
     if (waste < best_waste) { best_waste = waste; best = bn; }
   }
   return best;
+}
+
+// Launch-order / L2 hints of a plan (performance only; results are bit-identical).  Consecutive layers walk their tiles in the same
+// order, so a layer starts by reading the part of its input that its producer wrote FIRST -- with tensors near the size of the
+// 126 MB L2 exactly the part that has been evicted.  reverse_tiles walks the work items last to first; l2_out / l2_res = 0 (none),
+// 1 (evict first), 2 (evict last) put an eviction priority on the output stores / the residual loads.  Returns the reverse flag in
+// effect (0 for plans on the y-halo kernel, which ignore the call), negative on error.
+extern "C" int hpe_conv_set_schedule(hpe_conv_plan* pl, int reverse_tiles, int l2_out, int l2_res) {
+  if (!pl) return fail(HPE_EINVAL, "hpe_conv_set_schedule: null plan");
+  if (l2_out < 0 || l2_out > 2 || l2_res < 0 || l2_res > 2)
+    return fail(HPE_EINVAL, "hpe_conv_set_schedule: hints are 0 (none), 1 (evict first), 2 (evict last)");
+  if (pl->halo_taps_y) return 0;
+  static const unsigned long long pol[3] = {0ull, kL2EvictFirst, kL2EvictLast};
+  pl->p.reverse = reverse_tiles ? 1 : 0;
+  pl->p.l2_out = pol[l2_out];
+  pl->p.l2_res = pol[l2_res];
+  return pl->p.reverse;
 }
 
 extern "C" int hpe_conv_out_hw(const hpe_conv_desc* d, int* Ho, int* Wo) {

@@ -80,6 +80,23 @@ __device__ __forceinline__ void tma_load_4d(void* smem, const CUtensorMap* m, ui
       ::"r"(smem_u32(smem)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)),
         "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
 }
+// ... with an L2 eviction-priority hint (64-bit policy word; kL2EvictFirst / kL2EvictLast below, the encodings createpolicy
+// .fractional.L2::evict_first / evict_last produce for fraction 1.0)
+constexpr unsigned long long kL2EvictFirst = 0x12F0000000000000ull;
+constexpr unsigned long long kL2EvictLast  = 0x14F0000000000000ull;
+__device__ __forceinline__ void tma_load_4d_hint(void* smem, const CUtensorMap* m, uint64_t* bar,
+                                                 int c0, int c1, int c2, int c3, unsigned long long policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4, %5, %6}], [%2], %7;"
+      ::"r"(smem_u32(smem)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)),
+        "r"(c0), "r"(c1), "r"(c2), "r"(c3), "l"(policy) : "memory");
+}
+__device__ __forceinline__ void tma_store_4d_hint(const CUtensorMap* m, const void* smem, int c0, int c1, int c2, int c3,
+                                                  unsigned long long policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.global.shared::cta.bulk_group.L2::cache_hint [%0, {%2, %3, %4, %5}], [%1], %6;"
+      ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(smem)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "l"(policy) : "memory");
+}
 // L2 prefetch of a 4-D box (no shared-memory destination, no completion to wait for)
 __device__ __forceinline__ void tma_prefetch_l2_4d(const CUtensorMap* m, int c0, int c1, int c2, int c3) {
   asm volatile("cp.async.bulk.prefetch.tensor.4d.L2.global.tile [%0, {%1, %2, %3, %4}];"

@@ -100,6 +100,28 @@ def test_fused_paths_equal_unfused_layers(pair, cuda_dev, monkeypatch, B):
     assert ((hm1 - want) ** 2).mean().sqrt().item() <= 3e-3 * scale
 
 
+@pytest.mark.parametrize("B", [3, 32])
+def test_tile_schedule_is_bit_identical(pair, cuda_dev, monkeypatch, B):
+    """hpe_conv_set_schedule (reversed tile walk, L2 eviction hints on stores / shortcut loads) changes WHEN a tile is computed and
+    how long its lines stay in L2, never its bits: heatmaps with the default schedule == heatmaps with HPE_B200_L2_SCHED=0, and the
+    default plan really reverses some launches."""
+    from importlib import import_module
+    models = import_module("2d-human-pose-estimation_b200.models")
+    m, ref = pair
+    x = torch.rand(B, 3, 256, 192, generator=torch.Generator().manual_seed(70 + B)).to(cuda_dev)
+    hm = m(x).clone()
+    plan = m._plans[(tuple(x.shape), cuda_dev.index)]
+    assert any(rev for rev, _, _ in plan.schedule.values()) and any(o for _, o, _ in plan.schedule.values())
+    monkeypatch.setenv("HPE_B200_L2_SCHED", "0")
+    plain = models.HeatmapPose(17, "resnet50", pretrained=False)
+    plain.load_state_dict(ref.state_dict())
+    plain = plain.to(cuda_dev).eval()
+    want = plain(x)
+    torch.cuda.synchronize()
+    assert not next(iter(plain._plans.values())).schedule
+    assert torch.equal(hm, want)
+
+
 @pytest.mark.parametrize("B", [2, 5, 32])
 def test_chained_conv1_is_bit_identical(pair, cuda_dev, monkeypatch, B):
     """desc.chain: conv3 (+ shortcut + ReLU) of a layer1 Bottleneck and conv1 + BN + ReLU of the next block in one kernel (the
