@@ -35,6 +35,8 @@ SIGNATURES = {
     "hpe_decode_host_scratch_bytes": (_sz, [_i, _i, _i, _i, _i]),
     "hpe_decode_heatmaps_host": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
     "hpe_joints_mse_fused": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _f, _f, _f, _vp, _vp, _vp, _f, _vp, _vp]),
+    "hpe_static_loss_max_maps": (_i, []),
+    "hpe_joints_mse_fused_noalloc": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _f, _f, _f, _vp, _vp, _f, _vp, _vp]),
     "hpe_joints_mse_dense": (_i, [_vp, _i, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _f, _vp]),
     "hpe_generate_target": (_i, [_vp, _i, _i, _i, _i, _f, _f, _f, _vp, _vp, _vp]),
     "hpe_conv_plan_create": (_i, [C.POINTER(ConvDesc), C.POINTER(_vp)]),

@@ -6,6 +6,7 @@
 // xor-shuffle tree) and optionally writes dL/dpred in the same pass.  Maps whose weight is 0 are not
 // read at all (their gradient is written as zeros).  A second single-CTA kernel sums the per-map
 // partials in a fixed order, so the loss is run-to-run bit-stable.
+#include <mutex>
 #include "hpe_common.cuh"
 #include <limits.h>
 
@@ -330,6 +331,55 @@ extern "C" int hpe_joints_mse_fused(const void* pred, int dtype, const float* jo
   if (rc) return rc;
   reduce_partials_kernel<<<1, 1024, 0, st>>>(partials, n_maps, 0.5 / n, loss);
   return launch_status("reduce_partials_kernel");
+}
+
+// ---- allocation-free variant (no counterpart in the reference) -------------------
+// The per-map partial sums live in a file-scope device array instead of caller-provided scratch, so a caller that may not call
+// cudaMalloc (graph capture, serving loops) needs device memory for inputs and outputs only.  Every GPU that loads the library
+// holds the array (kStaticLossMaps = 131072 floats = 512 KB) until exit.  The kernels overwrite partials[0 .. B*K) completely
+// (maps with weight 0 store 0) and stage 2 reads exactly that range, so nothing has to be cleared between calls; all calls share
+// the array: calls that overlap on one GPU (two streams, two threads) race on it.
+namespace hpe {
+constexpr int kStaticLossMaps = 1 << 17;
+static __device__ __align__(256) float g_static_partials[kStaticLossMaps];
+}  // namespace hpe
+
+// Device address of g_static_partials on the CURRENT device.  In host code the array's name is only a handle for
+// cudaGetSymbolAddress, never a pointer a kernel may dereference; the address differs per device, so it is looked up once per
+// device, with that device current.
+static int static_partials_ptr(float** out) {
+  constexpr int kMaxDev = 64;
+  static std::mutex mu;
+  static float* addr[kMaxDev] = {};
+  int dev = 0;
+  HPE_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDev) return fail(HPE_EUNSUPPORTED, "hpe_joints_mse_fused_noalloc: device ordinal %d >= %d", dev, kMaxDev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[dev]) {
+    float* ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void**)&ptr, hpe::g_static_partials);
+    if (e != cudaSuccess || !ptr)
+      return fail(HPE_ECUDA, "hpe_joints_mse_fused_noalloc: cudaGetSymbolAddress on device %d: %s", dev, cudaGetErrorString(e));
+    addr[dev] = ptr;
+  }
+  *out = addr[dev];
+  return HPE_OK;
+}
+
+extern "C" int hpe_static_loss_max_maps(void) { return hpe::kStaticLossMaps; }
+
+extern "C" int hpe_joints_mse_fused_noalloc(const void* pred, int dtype, const float* joints,
+                                            int B, int K, int H, int W, float sigma, float stride_x, float stride_y,
+                                            float* loss, void* grad, float grad_scale, float* weight_out, void* stream) {
+  HPE_CHECK_ARG(B > 0 && K > 0, "hpe_joints_mse_fused_noalloc: non-positive size B=%d K=%d", B, K);
+  if ((long long)B * K > hpe::kStaticLossMaps)
+    return fail(HPE_EUNSUPPORTED, "hpe_joints_mse_fused_noalloc: B*K = %lld maps exceed the built-in scratch of %d maps; use "
+                "hpe_joints_mse_fused with caller-provided partials", (long long)B * K, hpe::kStaticLossMaps);
+  float* partials = nullptr;
+  const int rc = static_partials_ptr(&partials);
+  if (rc) return rc;
+  return hpe_joints_mse_fused(pred, dtype, joints, B, K, H, W, sigma, stride_x, stride_y, partials, loss, grad, grad_scale,
+                              weight_out, stream);
 }
 
 extern "C" int hpe_joints_mse_dense(const void* pred, int dtype, const float* target, const float* weight,

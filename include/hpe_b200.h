@@ -93,6 +93,19 @@ int hpe_joints_mse_fused(const void* pred, int dtype, const float* joints,
                          float* partials, float* loss, void* grad, float grad_scale,
                          float* weight_out, void* stream);
 
+/* Allocation-free variant of hpe_joints_mse_fused.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same arguments and results (bit-identical) minus `partials`: the per-map partial sums live in a 512 KB array
+ * built into the library (every GPU that loads it holds the array until exit), so B*K <= hpe_static_loss_max_maps() = 131072;
+ * larger problems are rejected with HPE_EUNSUPPORTED.  The call allocates nothing (no cudaMalloc / cudaFree / allocating
+ * library routine).  All calls share the array: calls that overlap on one GPU (different streams or threads) race on it --
+ * serialise them or use hpe_joints_mse_fused with separate scratch.  Nothing needs clearing between calls (each call rewrites
+ * the B*K entries it reads).  The device the pointers live on must be current. */
+int hpe_static_loss_max_maps(void);
+int hpe_joints_mse_fused_noalloc(const void* pred, int dtype, const float* joints,
+                                 int B, int K, int H, int W, float sigma, float stride_x, float stride_y,
+                                 float* loss, void* grad, float grad_scale, float* weight_out, void* stream);
+
 /* Drop-in mode: materialised target [B,K,H,W] f32 and weight [B,K] f32 (the trainer's call shape). */
 int hpe_joints_mse_dense(const void* pred, int dtype, const float* target, const float* weight,
                          int B, int K, int H, int W,
