@@ -48,7 +48,7 @@ SIGNATURES = {
     "hpe_conv_run2": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "hpe_conv_run_head2": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "hpe_conv_run_chain": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
-    "hpe_conv_set_schedule": (_i, [_vp, _i, _i, _i]),
+    "hpe_conv_set_schedule": (_i, [_vp, _i, _i, _i, _i]),
     "hpe_pack_job_bytes": (_sz, []),
     "hpe_conv_pack_job_fill": (_i, [C.POINTER(ConvDesc), _i, _vp, _vp, _i, _vp, C.POINTER(_i)]),
     "hpe_conv_pack_jobs_run": (_i, [_vp, _i, _i, _vp]),

@@ -63,10 +63,10 @@ class ConvLayer:
         except Exception:
             pass
 
-    def set_schedule(self, reverse=False, l2_out=0, l2_res=0) -> bool:
+    def set_schedule(self, reverse=False, l2_out=0, l2_res=0, l2_in=0) -> bool:
         """Tile order / L2 eviction hints of this layer's launches (hpe_conv_set_schedule; performance only).  Returns the tile
         direction in effect (True = reversed)."""
-        rc = _lib.lib().hpe_conv_set_schedule(self.plan, int(bool(reverse)), int(l2_out), int(l2_res))
+        rc = _lib.lib().hpe_conv_set_schedule(self.plan, int(bool(reverse)), int(l2_out), int(l2_res), int(l2_in))
         if rc < 0:
             _lib.check(rc, "hpe_conv_set_schedule")
         return bool(rc)

@@ -70,6 +70,7 @@ struct ConvParams {
   int chain_defer;              // CHAIN: the chained conv's output chunks of tile i are drained after this many chunks of tile i+1 (0 = right behind tile i)
   int reverse;                  // != 0: the work items are walked from the last to the first (hpe_conv_set_schedule)
   unsigned long long l2_out, l2_res;     // != 0: L2 eviction-priority policy word of the output stores / the residual loads
+  unsigned long long l2_in;              // policy word of the A-operand loads (kL2EvictNormal unless hpe_conv_set_schedule says otherwise)
 };
 
 struct TileCoord { int n_tile, cls, x0, y0, b0; };
@@ -400,12 +401,12 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const uint32_t full0 = mapa_shared(fb, 0);
           if (rank == 0) mbar_arrive_expect_tx_elect(fb, 2 * L::kStageBytes);
           else           mbar_arrive_cluster_elect(full0);
-          tma_load_ab_2sm_elect(full0, dA, mA, c0, cx, cy, t.b0, dB, &tmW, kb * kKBlock, wrow);
+          tma_load_ab_2sm_elect(full0, dA, mA, c0, cx, cy, t.b0, dB, &tmW, kb * kKBlock, wrow, p.l2_in);
         } else if constexpr (KBR != 0) {
           mbar_arrive_expect_tx_elect(fb, kABytes);
-          tma_load_4d_elect(dA, mA, fb, c0, cx, cy, t.b0);
+          tma_load_4d_elect(dA, mA, fb, c0, cx, cy, t.b0, p.l2_in);
         } else {
-          tma_load_ab_elect(fb, L::kStageBytes, dA, mA, c0, cx, cy, t.b0, dB, &tmW, kb * kKBlock, wrow);
+          tma_load_ab_elect(fb, L::kStageBytes, dA, mA, c0, cx, cy, t.b0, dB, &tmW, kb * kKBlock, wrow, p.l2_in);
         }
         if (++kc == p.kc_per_tap) { kc = 0; ++tap; tap_offset(p, tap, t.cls, dx, dy); }
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -1059,8 +1060,24 @@ static int desc_check(const hpe_conv_desc* d, const char* fn) {
 // BLOCK_N: the widest tile dividing Cout.  (Measured on B200: narrower tiles that fill the last wave of the
 // persistent grid better are still slower -- layer4 3x3 66 -> 78 us -- because every extra N tile re-reads
 // the A operand through the L2->SM fabric, which is what bounds these kernels; see profiles/.)
-static int pick_block_n(const hpe_conv_desc* d, long long /*m_tiles*/) {
+static bool is_class_strided(int kind);
+static int pick_block_n(const hpe_conv_desc* d, long long m_tiles) {
   if (d->kind == HPE_CONV_FINAL) return d->Cout <= 32 ? 32 : (d->Cout <= 64 ? 64 : (d->Cout <= 128 ? 128 : 256));
+  {
+    // Wave quantisation of the cta_group::2 kernels: layer4's conv1 / conv2 (Cout 512 over 96 M tiles) are 96 work items of 256
+    // columns on 74 clusters = 2 waves at 65 %; as 144 items of 192 columns (the third N tile a third full) they are 2 waves of
+    // 3/4 the length.  Measured (per-layer log, three boxes): layer4 3x3 176 / 169 / 175 -> 157 / 143 / 130 us, layer4 1x1
+    // 246 / 235 / 245 -> 244 / 224 / 209 us.  HPE_B200_WAVE192=0 keeps the widest tile that divides Cout.
+    static int wave = -1;
+    if (wave < 0) { const char* e = getenv("HPE_B200_WAVE192"); wave = e ? atoi(e) : 1; }
+    if (wave && d->Cout % 256 == 0 && d->Cout >= 512 && !d->chain && !d->has_residual && !is_class_strided(d->kind) && m_tiles >= 2 &&
+        (d->Cout + 191) / 192 * 192 <= kMaxCout) {
+      const long long clusters = cta_budget() / 2, pairs = (m_tiles + 1) / 2;
+      const long long w256 = (pairs * (d->Cout / 256) + clusters - 1) / clusters * 256;
+      const long long w192 = (pairs * ((d->Cout + 191) / 192) + clusters - 1) / clusters * 192;
+      if (w192 < w256) return 192;
+    }
+  }
   // the tile width wasting the fewest padded columns; ties -> the wider tile (fewer re-reads of A)
   const int cand[4] = {256, 192, 128, 64};
   int best = 64, best_waste = 1 << 30;
@@ -1073,18 +1090,19 @@ static int pick_block_n(const hpe_conv_desc* d, long long /*m_tiles*/) {
 
 // Launch-order / L2 hints of a plan (performance only; results are bit-identical).  Consecutive layers walk their tiles in the same
 // order, so a layer starts by reading the part of its input that its producer wrote FIRST -- with tensors near the size of the
-// 126 MB L2 exactly the part that has been evicted.  reverse_tiles walks the work items last to first; l2_out / l2_res = 0 (none),
-// 1 (evict first), 2 (evict last) put an eviction priority on the output stores / the residual loads.  Returns the reverse flag in
-// effect (0 for plans on the y-halo kernel, which ignore the call), negative on error.
-extern "C" int hpe_conv_set_schedule(hpe_conv_plan* pl, int reverse_tiles, int l2_out, int l2_res) {
+// 126 MB L2 exactly the part that has been evicted.  reverse_tiles walks the work items last to first; l2_out / l2_res / l2_in =
+// 0 (none), 1 (evict first), 2 (evict last) put an eviction priority on the output stores / the residual loads / the input
+// (A operand) loads.  Plans on the y-halo kernel take the direction only.  Returns the reverse flag in effect, negative on error.
+extern "C" int hpe_conv_set_schedule(hpe_conv_plan* pl, int reverse_tiles, int l2_out, int l2_res, int l2_in) {
   if (!pl) return fail(HPE_EINVAL, "hpe_conv_set_schedule: null plan");
-  if (l2_out < 0 || l2_out > 2 || l2_res < 0 || l2_res > 2)
+  if (l2_out < 0 || l2_out > 2 || l2_res < 0 || l2_res > 2 || l2_in < 0 || l2_in > 2)
     return fail(HPE_EINVAL, "hpe_conv_set_schedule: hints are 0 (none), 1 (evict first), 2 (evict last)");
-  if (pl->halo_taps_y) return 0;
+  if (pl->halo_taps_y) { pl->hp.reverse = reverse_tiles ? 1 : 0; return pl->hp.reverse; }
   static const unsigned long long pol[3] = {0ull, kL2EvictFirst, kL2EvictLast};
   pl->p.reverse = reverse_tiles ? 1 : 0;
   pl->p.l2_out = pol[l2_out];
   pl->p.l2_res = pol[l2_res];
+  pl->p.l2_in = l2_in ? pol[l2_in] : kL2EvictNormal;
   return pl->p.reverse;
 }
 
@@ -1412,6 +1430,7 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
   hpe_conv_out_hw(d, &pl->Ho, &pl->Wo);
   ConvParams& p = pl->p;
   p.kind = d->kind;
+  p.l2_in = kL2EvictNormal;
   p.in_stride = (d->kind == HPE_CONV_1x1 || d->kind == HPE_CONV_3x3) ? d->stride
                 : ((d->kind == HPE_CONV_4x4S2 || d->kind == HPE_CONV_2x2S2) ? 2 : 1);
   switch (d->kind) {
@@ -1518,6 +1537,7 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
       pl->hp.tiles_x = (pl->Wo + 2) / 3; pl->hp.tiles_y = (pl->Ho + 14) / 15;
     }
     pl->hp.num_tiles = pl->hp.tiles_x * pl->hp.tiles_y * d->B;
+    pl->hp.nbatch = d->B; pl->hp.reverse = 0;
     pl->grid = pl->hp.num_tiles < cta_budget() ? pl->hp.num_tiles : cta_budget();
     p.tw = 8; p.th = kHaloRows; p.nb = 1;        // brick of the A map encoded below
   } else if (d->pool) {

@@ -134,10 +134,13 @@ conv_yhalo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       int stage = 0; uint32_t phase = 0;
       TileWalk w(blockIdx.x, gridDim.x, p.tiles_x, p.tiles_y);
       for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-        const int x0 = POOL ? 6 * w.tx - 1 : w.tx * 8, y0 = POOL ? 30 * w.ty - 1 : w.ty * kHRows;
+        // reversed walk: mirroring every coordinate of the mixed-radix tile index = walking the index backwards
+        const int wtx = p.reverse ? p.tiles_x - 1 - w.tx : w.tx, wty = p.reverse ? p.tiles_y - 1 - w.ty : w.ty;
+        const int wb = p.reverse ? p.nbatch - 1 - w.b : w.b;
+        const int x0 = POOL ? 6 * wtx - 1 : wtx * 8, y0 = POOL ? 30 * wty - 1 : wty * kHRows;
         mbar_wait(&empty_bar[stage], phase ^ 1);
         mbar_arrive_expect_tx(&full_bar[stage], kBoxRows * 128);      // bytes the box delivers (a stage is padded to 1 KB)
-        tma_load_4d(sA + stage * kABytes, &tmA, &full_bar[stage], 0, x0 - p.x_lo, y0 - p.y_lo, w.b);
+        tma_load_4d(sA + stage * kABytes, &tmA, &full_bar[stage], 0, x0 - p.x_lo, y0 - p.y_lo, wb);
         if (++stage == kHStages) { stage = 0; phase ^= 1; }
         w.next(p.tiles_x, p.tiles_y);
       }
@@ -214,7 +217,9 @@ conv_yhalo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     TileWalk w(blockIdx.x + grp * gridDim.x, 2 * gridDim.x, p.tiles_x, p.tiles_y);
     int it = 0;
     for (int tile = blockIdx.x + grp * gridDim.x; tile < p.num_tiles; tile += 2 * gridDim.x, ++it) {
-      const int x0 = POOL ? 6 * w.tx - 1 : w.tx * 8, y0 = POOL ? 30 * w.ty - 1 : w.ty * kHRows;
+      const int wtx = p.reverse ? p.tiles_x - 1 - w.tx : w.tx, wty = p.reverse ? p.tiles_y - 1 - w.ty : w.ty;
+      const int wb = p.reverse ? p.nbatch - 1 - w.b : w.b;
+      const int x0 = POOL ? 6 * wtx - 1 : wtx * 8, y0 = POOL ? 30 * wty - 1 : wty * kHRows;
       mbar_wait(&tfull_bar[grp], it & 1);
       tc_fence_after();
 #pragma unroll
@@ -280,15 +285,15 @@ conv_yhalo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               const uint4 q = h_lds_v4(sb + r * 128 + ((j ^ (r & 7)) << 4));
               mx.x = h_max2(mx.x, q.x); mx.y = h_max2(mx.y, q.y); mx.z = h_max2(mx.z, q.z); mx.w = h_max2(mx.w, q.w);
             }
-          const int oy = 15 * w.ty + ppy, ox = 3 * w.tx + ppx;
-          if (oy < p.Ho && ox < p.Wo) out[((static_cast<size_t>(w.b) * p.Ho + oy) * p.Wo + ox) * 8 + j] = mx;
+          const int oy = 15 * wty + ppy, ox = 3 * wtx + ppx;
+          if (oy < p.Ho && ox < p.Wo) out[((static_cast<size_t>(wb) * p.Ho + oy) * p.Wo + ox) * 8 + j] = mx;
         }
       } else {
         // Staging buffer -> global memory with plain 16-byte stores, 4 pixels (512 contiguous bytes of an image row) per
         // instruction: no proxy fence, no bulk-store wait, no block barrier -- the warp staged image rows 8 ew .. 8 ew + 7 itself.
         __syncwarp();
         const int ox = x0 + (lane >> 3), oy = y0 + 8 * ew, c = lane & 7;
-        uint4* const o0 = out + ((static_cast<size_t>(w.b) * p.Ho + oy) * p.Wo + ox) * 8 + c;
+        uint4* const o0 = out + ((static_cast<size_t>(wb) * p.Ho + oy) * p.Wo + ox) * 8 + c;
         const uint32_t s0 = sb + (ew * 64 + (lane >> 3)) * 128;
 #pragma unroll
         for (int i = 0; i < 16; ++i) {                               // brick row 8 ew + (i >> 1), columns 4 (i & 1) .. + 3

@@ -17,6 +17,7 @@ struct HaloParams {
   int pool;                            // != 0 (stem only): MaxPool 3x3/s2/p1 of the ReLU output is taken in the epilogue; bricks are then
                                        // OVERLAPPING, at (6*tx - 1, 30*ty - 1), and produce 3 x 15 pooled pixels each
   int Wc, Hc;                          // pool: extent of the (never written) convolution output
+  int reverse, nbatch;                 // reverse != 0: the bricks are walked from the last to the first (hpe_conv_set_schedule); nbatch = B
 };
 
 int halo_launch(int taps_y, int act, const CUtensorMap* tmA, const CUtensorMap* tmW, const HaloParams& p, int grid, cudaStream_t stream);

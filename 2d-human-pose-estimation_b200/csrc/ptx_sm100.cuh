@@ -84,6 +84,7 @@ __device__ __forceinline__ void tma_load_4d(void* smem, const CUtensorMap* m, ui
 // .fractional.L2::evict_first / evict_last produce for fraction 1.0)
 constexpr unsigned long long kL2EvictFirst = 0x12F0000000000000ull;
 constexpr unsigned long long kL2EvictLast  = 0x14F0000000000000ull;
+constexpr unsigned long long kL2EvictNormal = 0x1000000000000000ull;
 __device__ __forceinline__ void tma_load_4d_hint(void* smem, const CUtensorMap* m, uint64_t* bar,
                                                  int c0, int c1, int c2, int c3, unsigned long long policy) {
   asm volatile(
@@ -248,32 +249,35 @@ __device__ __forceinline__ void mbar_arrive_cluster_elect(uint32_t cluster_addr)
   asm volatile("{\n\t.reg .pred e;\n\telect.sync _|e, 0xffffffff;\n\t"
                "@e mbarrier.arrive.shared::cluster.b64 _, [%0];\n\t}" ::"r"(cluster_addr) : "memory");
 }
-__device__ __forceinline__ void tma_load_4d_elect(uint32_t dst, const CUtensorMap* m, uint32_t bar, int c0, int c1, int c2, int c3) {
+__device__ __forceinline__ void tma_load_4d_elect(uint32_t dst, const CUtensorMap* m, uint32_t bar, int c0, int c1, int c2, int c3,
+                                                  unsigned long long pol = kL2EvictNormal) {
   asm volatile(
       "{\n\t.reg .pred e;\n\telect.sync _|e, 0xffffffff;\n\t"
-      "@e cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];\n\t}"
-      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+      "@e cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4, %5, %6}], [%2], %7;\n\t}"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "l"(pol) : "memory");
 }
-// expect_tx + the A box (4-D) + the W box (2-D) of one ring stage, one election
+// expect_tx + the A box (4-D, L2 policy `pol`) + the W box (2-D) of one ring stage, one election
 __device__ __forceinline__ void tma_load_ab_elect(uint32_t bar, uint32_t bytes, uint32_t dA, const CUtensorMap* mA,
-                                                  int c0, int c1, int c2, int c3, uint32_t dB, const CUtensorMap* mW, int k, int row) {
+                                                  int c0, int c1, int c2, int c3, uint32_t dB, const CUtensorMap* mW, int k, int row,
+                                                  unsigned long long pol) {
   asm volatile(
       "{\n\t.reg .pred e;\n\telect.sync _|e, 0xffffffff;\n\t"
       "@e mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n\t"
-      "@e cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%2], [%3, {%4, %5, %6, %7}], [%0];\n\t"
+      "@e cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%2], [%3, {%4, %5, %6, %7}], [%0], %12;\n\t"
       "@e cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%8], [%9, {%10, %11}], [%0];\n\t}"
       ::"r"(bar), "r"(bytes), "r"(dA), "l"(reinterpret_cast<uint64_t>(mA)), "r"(c0), "r"(c1), "r"(c2), "r"(c3),
-        "r"(dB), "l"(reinterpret_cast<uint64_t>(mW)), "r"(k), "r"(row) : "memory");
+        "r"(dB), "l"(reinterpret_cast<uint64_t>(mW)), "r"(k), "r"(row), "l"(pol) : "memory");
 }
 // pair form: both boxes complete on `bar_cluster` (the leader's full barrier); the arrival is issued separately
 __device__ __forceinline__ void tma_load_ab_2sm_elect(uint32_t bar_cluster, uint32_t dA, const CUtensorMap* mA,
-                                                      int c0, int c1, int c2, int c3, uint32_t dB, const CUtensorMap* mW, int k, int row) {
+                                                      int c0, int c1, int c2, int c3, uint32_t dB, const CUtensorMap* mW, int k, int row,
+                                                      unsigned long long pol) {
   asm volatile(
       "{\n\t.reg .pred e;\n\telect.sync _|e, 0xffffffff;\n\t"
-      "@e cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%1], [%2, {%3, %4, %5, %6}], [%0];\n\t"
+      "@e cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%1], [%2, {%3, %4, %5, %6}], [%0], %11;\n\t"
       "@e cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%7], [%8, {%9, %10}], [%0];\n\t}"
       ::"r"(bar_cluster), "r"(dA), "l"(reinterpret_cast<uint64_t>(mA)), "r"(c0), "r"(c1), "r"(c2), "r"(c3),
-        "r"(dB), "l"(reinterpret_cast<uint64_t>(mW)), "r"(k), "r"(row) : "memory");
+        "r"(dB), "l"(reinterpret_cast<uint64_t>(mW)), "r"(k), "r"(row), "l"(pol) : "memory");
 }
 __device__ __forceinline__ void umma_bf16_2sm_elect_lo(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
                                                        uint32_t idesc, uint32_t accumulate) {

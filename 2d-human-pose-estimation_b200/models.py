@@ -370,7 +370,7 @@ class _ForwardPlan:
             cur, cin, h, w = f"deconv{d}", 256, 2 * h, 2 * w
         if self.fused_head is None:
             add("final_layer", ConvLayer(CONV_FINAL, B, h, w, 256, K, 1, ACT_NONE, False, dev), cur, "heatmaps")
-        self._schedule(int(os.environ.get("HPE_B200_L2_SCHED", "3")))
+        self._schedule(int(os.environ.get("HPE_B200_L2_SCHED", "2")))
         self.weights_version = -1
         self.graph = None
         self.bufs["s2d"] = self.s2d.view(Bf, -1)
@@ -421,29 +421,35 @@ class _ForwardPlan:
         self.weights_version = model._weights_version
         self.graph = None         # packed buffers are updated in place, but be conservative
 
-    def _schedule(self, mode, l2_keep_bytes=104 << 20):
+    def _schedule(self, mode):
         """Tile order and L2 eviction hints per launch (hpe_conv_set_schedule; results are bit-identical).  Every launch walks its
         tiles batch-major, so by default a layer starts on the part of its input that was written FIRST -- for tensors around
         the size of the 126 MB L2 (layer3: 100 MB) exactly the part already evicted.  mode & 2: a launch runs in the direction
         opposite to the one in which its largest input was last touched (it starts where that pass ended).  mode & 1: outputs
-        that fit L2 are stored evict-last, the shortcut (read for the last time) is loaded evict-first.  HPE_B200_L2_SCHED,
-        default 3 (measured: forward 3.154 / 3.164 ms at 0, 3.141 / 3.118 ms at 3)."""
+        up to HPE_B200_L2_KEEP_MB (104) are stored evict-last, the shortcut (read for the last time) is loaded evict-first.
+        mode & 4: an input that no later launch reads is loaded evict-first.  HPE_B200_L2_SCHED, default 2.  Measured forward,
+        five runs on two boxes: mode 0 3.151 ms, mode 2 3.107, mode 3 3.123, mode 7 3.175 (two runs); keep = 60 / 512 MB no better:
+        the direction is what helps, the hints do not."""
         self.schedule = {}
         if not mode:
             return
+        keep = int(os.environ.get("HPE_B200_L2_KEEP_MB", "104")) << 20
         last_dir = {}                       # buffer key -> direction (True = reversed) of the last launch that touched it
-        for name, (layer, src, res, dst, src2, dst2) in zip(self.named, self.ops):
-            ins = [k for k in (src, res, src2) if k is not None and k in self.bufs]
-            big = max(ins, key=lambda k: self.bufs[k].numel() * self.bufs[k].element_size(), default=None)
+        ops = list(zip(self.named, self.ops))
+        for k, (name, (layer, src, res, dst, src2, dst2)) in enumerate(ops):
+            ins = [b for b in (src, res, src2) if b is not None and b in self.bufs]
+            big = max(ins, key=lambda b: self.bufs[b].numel() * self.bufs[b].element_size(), default=None)
             rev = (not last_dir.get(big, False)) if (mode & 2 and big is not None and big in last_dir) else False
             out_bytes = self.bufs[dst].numel() * self.bufs[dst].element_size()
-            l2_out = 2 if (mode & 1 and out_bytes <= l2_keep_bytes and self.bufs[dst].dtype == torch.bfloat16) else 0
+            l2_out = 2 if (mode & 1 and out_bytes <= keep and self.bufs[dst].dtype == torch.bfloat16) else 0
             l2_res = 1 if (mode & 1 and res is not None) else 0
-            rev = layer.set_schedule(rev, l2_out, l2_res)
-            self.schedule[name] = (rev, l2_out, l2_res)
-            for k in (src, res, src2, dst, dst2):
-                if k is not None:
-                    last_dir[k] = rev
+            read_later = any(src in (o[1], o[2], o[4]) for _, o in ops[k + 1:])
+            l2_in = 1 if (mode & 4 and not read_later and src2 is None) else 0
+            rev = layer.set_schedule(rev, l2_out, l2_res, l2_in)
+            self.schedule[name] = (rev, l2_out, l2_res, l2_in)
+            for b in (src, res, src2, dst, dst2):
+                if b is not None:
+                    last_dir[b] = rev
 
     def _view(self, key, c):
         """Buffer `key` as pass `c` of the depth-first section sees it: full-batch tensors by batch slice, chunk buffers whole."""

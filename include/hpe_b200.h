@@ -209,9 +209,10 @@ int  hpe_conv_pack_job_fill(const hpe_conv_desc* fwd_desc, int dgrad, const floa
 int  hpe_conv_pack_jobs_run(const void* jobs_device, int n_jobs, int total_blocks, void* stream);
 /* Launch order / L2 eviction hints of a plan (performance only, results bit-identical; no counterpart in the reference, whose
  * cuDNN calls schedule themselves).  reverse_tiles != 0 walks the tiles last to first: layer n+1 then starts on the part of its
- * input that layer n wrote last, which is still in L2.  l2_out / l2_res: 0 none, 1 evict-first, 2 evict-last on the output
- * stores / the residual loads.  Returns the reverse flag in effect (plans on the y-halo kernel ignore the call: 0), < 0 on error. */
-int  hpe_conv_set_schedule(hpe_conv_plan* plan, int reverse_tiles, int l2_out, int l2_res);
+ * input that layer n wrote last, which is still in L2.  l2_out / l2_res / l2_in: 0 none, 1 evict-first, 2 evict-last on the
+ * output stores / the residual loads / the input (A operand) loads.  Plans on the y-halo kernel take the direction only.
+ * Returns the reverse flag in effect, < 0 on error. */
+int  hpe_conv_set_schedule(hpe_conv_plan* plan, int reverse_tiles, int l2_out, int l2_res, int l2_in);
 /* output spatial size of the layer */
 int  hpe_conv_out_hw(const hpe_conv_desc* desc, int* Ho, int* Wo);
 

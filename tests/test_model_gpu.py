@@ -109,9 +109,15 @@ def test_tile_schedule_is_bit_identical(pair, cuda_dev, monkeypatch, B):
     models = import_module("2d-human-pose-estimation_b200.models")
     m, ref = pair
     x = torch.rand(B, 3, 256, 192, generator=torch.Generator().manual_seed(70 + B)).to(cuda_dev)
-    hm = m(x).clone()
-    plan = m._plans[(tuple(x.shape), cuda_dev.index)]
-    assert any(rev for rev, _, _ in plan.schedule.values()) and any(o for _, o, _ in plan.schedule.values())
+    monkeypatch.setenv("HPE_B200_L2_SCHED", "7")          # direction + store / shortcut / input hints
+    hinted = models.HeatmapPose(17, "resnet50", pretrained=False)
+    hinted.load_state_dict(ref.state_dict())
+    hinted = hinted.to(cuda_dev).eval()
+    hm = hinted(x).clone()
+    plan = next(iter(hinted._plans.values()))
+    assert all(any(s[i] for s in plan.schedule.values()) for i in range(4))
+    assert torch.equal(hm, m(x))                          # the default schedule (direction only)
+    assert any(s[0] for s in m._plans[(tuple(x.shape), cuda_dev.index)].schedule.values())
     monkeypatch.setenv("HPE_B200_L2_SCHED", "0")
     plain = models.HeatmapPose(17, "resnet50", pretrained=False)
     plain.load_state_dict(ref.state_dict())
