@@ -12,7 +12,7 @@ _PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_PKG, "lib", "libhpe_b200.so")
 
 HPE_F32, HPE_BF16 = 0, 1
-ACT_NONE, ACT_RELU, ACT_SILU, ACT_GELU = 0, 1, 2, 3
+ACT_NONE, ACT_RELU, ACT_SILU, ACT_GELU, ACT_GELU_LN = 0, 1, 2, 3, 4
 CONV_1x1, CONV_3x3, CONV_STEM7x7, CONV_DECONV4, CONV_FINAL = 0, 1, 2, 3, 4
 CONV_DGRAD3x3S2, CONV_DGRAD1x1S2, CONV_4x4S2, CONV_2x2S2 = 5, 6, 7, 8
 
@@ -49,6 +49,7 @@ SIGNATURES = {
     "hpe_conv_run_head2": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "hpe_conv_run_chain": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "hpe_conv_set_schedule": (_i, [_vp, _i, _i, _i, _i]),
+    "hpe_conv_run_ln": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _f, _vp, _vp]),
     "hpe_pack_job_bytes": (_sz, []),
     "hpe_conv_pack_job_fill": (_i, [C.POINTER(ConvDesc), _i, _vp, _vp, _i, _vp, C.POINTER(_i)]),
     "hpe_conv_pack_jobs_run": (_i, [_vp, _i, _i, _vp]),
@@ -79,6 +80,8 @@ SIGNATURES = {
     "hpe_wgrad_run": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp]),
     "hpe_dwconv": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _f, _vp, _i, _vp]),
     "hpe_dwconv7_bias": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _i, _vp]),
+    "hpe_dwconv7_stats_elems": (_sz, [_i, _i, _i, _i]),
+    "hpe_dwconv7_bias_stats": (_i, [_vp, _i, _i, _i, _i, _i, _vp, _vp, _vp, _i, _vp, _vp]),
     "hpe_layernorm_nhwc": (_i, [_vp, _i, C.c_longlong, _i, _vp, _vp, _f, _vp, _i, _vp]),
     "hpe_bnact_scratch_elems": (_sz, [_i]),
     "hpe_bnact_stats": (_i, [_vp, C.c_longlong, _i, _vp, _vp, _f, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -13,7 +13,7 @@ import ctypes as C
 import torch
 
 from . import _lib
-from ._lib import (ACT_GELU, ACT_NONE, ACT_RELU, ACT_SILU, CONV_1x1, CONV_2x2S2, CONV_3x3, CONV_4x4S2, CONV_DECONV4,
+from ._lib import (ACT_GELU, ACT_GELU_LN, ACT_NONE, ACT_RELU, ACT_SILU, CONV_1x1, CONV_2x2S2, CONV_3x3, CONV_4x4S2, CONV_DECONV4,
                    CONV_DGRAD1x1S2, CONV_DGRAD3x3S2, CONV_FINAL, CONV_STEM7x7, ConvDesc)
 
 
@@ -62,6 +62,23 @@ class ConvLayer:
                 self.plan = None
         except Exception:
             pass
+
+    def run_ln(self, x: torch.Tensor, rowstats: torch.Tensor, n_slices: int, channels: int, eps: float, out: torch.Tensor):
+        """``act = ACT_GELU_LN``: ``gelu(pwconv1(norm(x)))`` of the ConvNeXt block (dinov3 convnext.py:74-77) on the RAW ``x`` --
+        the LayerNorm is folded into the weights (``load`` them as ``gamma * W``), the column table (``scale`` = column sums of
+        the bf16 folded weights, ``shift`` = ``b + W beta``) and a per-row (mean, rstd) the epilogue derives from ``rowstats``
+        ([pixels][n_slices][2] fp32 partial sums written by ``hpe_dwconv7_bias_stats``)."""
+        _lib.require_cuda(x, rowstats)
+        if self.desc.out_cstride:          # a channel slice of a wider NHWC buffer
+            if not out.is_cuda or out.stride(-1) != 1 or out.stride(-2) != self.desc.out_cstride:
+                raise RuntimeError("libhpe_b200: channel-slice tensor does not match the plan's channel pitch")
+        else:
+            _lib.require_cuda(out)
+        with torch.cuda.device(self.device):
+            rc = _lib.lib().hpe_conv_run_ln(self.plan, _lib.ptr(x), _lib.ptr(self.w_packed), _lib.ptr(self.scale), _lib.ptr(self.shift),
+                                            _lib.ptr(rowstats), int(n_slices), int(channels), float(eps), _lib.ptr(out), _lib.stream_ptr())
+        _lib.check(rc, "hpe_conv_run_ln")
+        return out
 
     def set_schedule(self, reverse=False, l2_out=0, l2_res=0, l2_in=0) -> bool:
         """Tile order / L2 eviction hints of this layer's launches (hpe_conv_set_schedule; performance only).  Returns the tile

@@ -71,6 +71,9 @@ struct ConvParams {
   int reverse;                  // != 0: the work items are walked from the last to the first (hpe_conv_set_schedule)
   unsigned long long l2_out, l2_res;     // != 0: L2 eviction-priority policy word of the output stores / the residual loads
   unsigned long long l2_in;              // policy word of the A-operand loads (kL2EvictNormal unless hpe_conv_set_schedule says otherwise)
+  const float2* rowstats;       // HPE_ACT_GELU_LN: per input pixel and 64-channel slice (sum, sum of squares) of the stored input
+  int ln_slices;                //   slices per pixel;  ln_inv_c = 1 / channels, ln_eps: the LayerNorm folded into this 1x1 conv
+  float ln_inv_c, ln_eps;
 };
 
 struct TileCoord { int n_tile, cls, x0, y0, b0; };
@@ -642,6 +645,25 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const uint32_t bar_id = 1 + grp;
     if (RES && leader) for (int b = 0; b < kLead; ++b) mbar_arrive(&sbempty_bar[b]);
     int q = 0, staged_n = -1;
+    // HPE_ACT_GELU_LN: this row's LayerNorm partial sums of the tile `w` (first kLnPf slices into registers; ln_st = null: no pixel)
+    constexpr int kLnPf = 8;
+    float2 ln_pf[kLnPf];
+    const float2* ln_st = nullptr;
+    auto ln_fetch = [&](int w) {
+      ln_st = nullptr;
+#pragma unroll
+      for (int i = 0; i < kLnPf; ++i) ln_pf[i] = make_float2(0.f, 0.f);
+      if (w >= p.num_tiles) return;
+      const TileCoord tn = tile_coord(p, work_tile<PAIR>(p, w, rank));
+      const int xi = row % p.tw, yi = (row / p.tw) % p.th, bi = row / (p.tw * p.th);
+      const int x = tn.x0 + xi, y = tn.y0 + yi, b = tn.b0 + bi;
+      if (x < p.Wo && y < p.Ho && b < p.B) {
+        ln_st = p.rowstats + (static_cast<size_t>(b * p.Ho + y) * p.Wo + x) * p.ln_slices;
+#pragma unroll
+        for (int i = 0; i < kLnPf; ++i) if (i < p.ln_slices) ln_pf[i] = __ldg(ln_st + i);
+      }
+    };
+    if constexpr (ACT == HPE_ACT_GELU_LN) ln_fetch(work0 + grp * wstep);
     for (int work = work0 + grp * wstep, it = grp; work < p.num_tiles; work += kGroups * wstep, it += kGroups) {
       const TileCoord t = tile_coord(p, work_tile<PAIR>(p, work, rank));
       const int acc = it & 1;
@@ -654,6 +676,24 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
         staged_n = t.n_tile;
         named_bar_sync(bar_id, kEpiThreads);
+      }
+      // HPE_ACT_GELU_LN: LayerNorm over the INPUT channels folded into this 1x1 conv.  With W' = gamma * W the layer computes
+      //   gelu( LN(x) W^T + b ) = gelu( rstd_r * (x W'^T - mu_r * colsum(W')) + (b + W beta) ),
+      // so the A operand is the raw tensor and the epilogue applies a per-ROW (mu, rstd) beside the per-column tables
+      // (scale = colsum(W'), shift = b + W beta).  The row's statistics come from the producer's partial sums.
+      // The partial sums of a tile are requested one tile ahead (ln_fetch below) and consumed here, so their latency hides
+      // behind a whole tile of epilogue work (fetched at the point of use they cost the single-group 192-wide kernel +33 %).
+      float2 ln_nmu = make_float2(0.f, 0.f), ln_rstd = make_float2(1.f, 1.f);
+      if constexpr (ACT == HPE_ACT_GELU_LN) {
+        if (ln_st != nullptr) {
+          float s = 0.f, q = 0.f;
+#pragma unroll
+          for (int i = 0; i < kLnPf; ++i) { s += ln_pf[i].x; q += ln_pf[i].y; }
+          for (int i = kLnPf; i < p.ln_slices; ++i) { const float2 v2 = __ldg(ln_st + i); s += v2.x; q += v2.y; }
+          const float mu = s * p.ln_inv_c, rs = rsqrtf(fmaxf(fmaf(-mu, mu, q * p.ln_inv_c), 0.f) + p.ln_eps);
+          ln_nmu = make_float2(-mu, -mu); ln_rstd = make_float2(rs, rs);
+        }
+        ln_fetch(work + kGroups * wstep);
       }
       mbar_wait(&tfull_bar[acc], (it >> 1) & 1);
       tc_fence_after();
@@ -718,6 +758,12 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             float2 o23 = __ffma2_rn(make_float2(__uint_as_float(v[j * 8 + 2]), __uint_as_float(v[j * 8 + 3])), make_float2(s0.z, s0.w), make_float2(h0.z, h0.w));
             float2 o45 = __ffma2_rn(make_float2(__uint_as_float(v[j * 8 + 4]), __uint_as_float(v[j * 8 + 5])), make_float2(s1.x, s1.y), make_float2(h1.x, h1.y));
             float2 o67 = __ffma2_rn(make_float2(__uint_as_float(v[j * 8 + 6]), __uint_as_float(v[j * 8 + 7])), make_float2(s1.z, s1.w), make_float2(h1.z, h1.w));
+            if constexpr (ACT == HPE_ACT_GELU_LN) {     // rstd * (acc - mu * colsum) + shift
+              o01 = __ffma2_rn(__ffma2_rn(make_float2(s0.x, s0.y), ln_nmu, make_float2(__uint_as_float(v[j * 8 + 0]), __uint_as_float(v[j * 8 + 1]))), ln_rstd, make_float2(h0.x, h0.y));
+              o23 = __ffma2_rn(__ffma2_rn(make_float2(s0.z, s0.w), ln_nmu, make_float2(__uint_as_float(v[j * 8 + 2]), __uint_as_float(v[j * 8 + 3]))), ln_rstd, make_float2(h0.z, h0.w));
+              o45 = __ffma2_rn(__ffma2_rn(make_float2(s1.x, s1.y), ln_nmu, make_float2(__uint_as_float(v[j * 8 + 4]), __uint_as_float(v[j * 8 + 5]))), ln_rstd, make_float2(h1.x, h1.y));
+              o67 = __ffma2_rn(__ffma2_rn(make_float2(s1.z, s1.w), ln_nmu, make_float2(__uint_as_float(v[j * 8 + 6]), __uint_as_float(v[j * 8 + 7]))), ln_rstd, make_float2(h1.z, h1.w));
+            }
             const uint32_t slot = rowp + (((half * 4 + j) ^ (row & 7)) << 4);     // 128-byte swizzle
             if (RES) {
               const uint4 rr = lds_v4(slot);
@@ -729,7 +775,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
               for (int e = 0; e < 8; ++e) o[e] = silu_fast(o[e]);
             }
-            if (ACT == HPE_ACT_GELU) {         // exact (erf) GELU = nn.GELU() default (dinov3 convnext.py:60)
+            if (ACT == HPE_ACT_GELU || ACT == HPE_ACT_GELU_LN) {         // exact (erf) GELU = nn.GELU() default (dinov3 convnext.py:60)
 #pragma unroll
               for (int e = 0; e < 8; ++e) o[e] = gelu_erf(o[e]);
             }
@@ -1044,7 +1090,9 @@ static int desc_check(const hpe_conv_desc* d, const char* fn) {
   if (d->out_cstride && (d->out_cstride % 8 || d->out_cstride < d->Cout))
     return fail(HPE_EINVAL, "%s: out_cstride=%d must be a multiple of 8 and >= Cout", fn, d->out_cstride);
   if (d->Cout > kMaxCout) return fail(HPE_EUNSUPPORTED, "%s: Cout=%d exceeds %d", fn, d->Cout, kMaxCout);
-  if (d->act < HPE_ACT_NONE || d->act > HPE_ACT_GELU) return fail(HPE_EINVAL, "%s: bad act %d", fn, d->act);
+  if (d->act < HPE_ACT_NONE || d->act > HPE_ACT_GELU_LN) return fail(HPE_EINVAL, "%s: bad act %d", fn, d->act);
+  if (d->act == HPE_ACT_GELU_LN && (d->kind != HPE_CONV_1x1 || d->stride != 1 || d->Cin2 || d->chain || d->head2 || d->has_residual))
+    return fail(HPE_EUNSUPPORTED, "%s: the LayerNorm-folded GELU epilogue is for plain 1x1 / stride 1 layers", fn);
   if (d->act == HPE_ACT_GELU && d->has_residual) return fail(HPE_EUNSUPPORTED, "%s: GELU epilogue has no residual variant", fn);
   if (d->kind == HPE_CONV_1x1 || d->kind == HPE_CONV_3x3) {
     if (d->stride != 1 && d->stride != 2) return fail(HPE_EUNSUPPORTED, "%s: stride %d not in {1,2}", fn, d->stride);
@@ -1070,7 +1118,8 @@ static int pick_block_n(const hpe_conv_desc* d, long long m_tiles) {
     // 246 / 235 / 245 -> 244 / 224 / 209 us.  HPE_B200_WAVE192=0 keeps the widest tile that divides Cout.
     static int wave = -1;
     if (wave < 0) { const char* e = getenv("HPE_B200_WAVE192"); wave = e ? atoi(e) : 1; }
-    if (wave && d->Cout % 256 == 0 && d->Cout >= 512 && !d->chain && !d->has_residual && !is_class_strided(d->kind) && m_tiles >= 2 &&
+    // (not for the GELU layers: their 256-wide tiles run two epilogue groups, which the 192-wide kernel does not have)
+    if (wave && d->Cout % 256 == 0 && d->Cout >= 512 && !d->chain && !d->has_residual && d->act != HPE_ACT_GELU && d->act != HPE_ACT_GELU_LN && !is_class_strided(d->kind) && m_tiles >= 2 &&
         (d->Cout + 191) / 192 * 192 <= kMaxCout) {
       const long long clusters = cta_budget() / 2, pairs = (m_tiles + 1) / 2;
       const long long w256 = (pairs * (d->Cout / 256) + clusters - 1) / clusters * 256;
@@ -1356,6 +1405,7 @@ static ConvKernelFn pick_kernel_pair(int act, bool res, size_t* smem) {
 static ConvKernelFn pick_kernel_epi2(int act, bool res, size_t* smem) {
   if (!res) {
     *smem = SmemLayout<256, 4, true, 4, false, true>::kDynamic;
+    if (act == HPE_ACT_GELU_LN) return conv_gemm_kernel<256, 4, HPE_ACT_GELU_LN, false, false, true, false, true>;
     return act == HPE_ACT_GELU ? conv_gemm_kernel<256, 4, HPE_ACT_GELU, false, false, true, false, true> : nullptr;
   }
   *smem = SmemLayout<256, 3, true, 6, false, true>::kDynamic;
@@ -1403,6 +1453,10 @@ static ConvKernelFn pick_kernel(int block_n, int act, bool res, bool fin, bool p
     if (ring6) return pick_kernel_ring6(act, smem);
   }
   if (pair && block_n == 256) return pick_kernel_pair<256, 5, 5>(act, res, smem);       // 32 KB stages (A + half of B)
+  if (pair && block_n == 192 && act == HPE_ACT_GELU_LN) {
+    *smem = SmemLayout<192, 6, true, 3>::kDynamic;
+    return conv_gemm_kernel<192, 6, HPE_ACT_GELU_LN, false, false, true>;
+  }
   if (pair && block_n == 192) return pick_kernel_pair<192, 6, 5>(act, res, smem);       // 28 KB stages (ConvNeXt C = 192/384/768)
   if (pair) return pick_kernel_pair<128, 7, 6>(act, res, smem);                         // 24 KB stages
   if (!pair && block_n == 128 && !res && !fin && act != HPE_ACT_GELU) {
@@ -1489,9 +1543,13 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
     const int mode = e ? atoi(e) : 1;
     const int num_kb = p.taps * p.kc_per_tap + p.kc2;
     const char* eg = getenv("HPE_B200_EPI2_GELU");
-    const bool gelu2 = d->act == HPE_ACT_GELU && !p.has_res && !(eg && eg[0] == '0');        // epilogue-bound GELU layers (pwconv1)
+    const bool gelu2 = ((d->act == HPE_ACT_GELU && !(eg && eg[0] == '0')) || d->act == HPE_ACT_GELU_LN) && !p.has_res;   // epilogue-bound GELU layers (pwconv1)
     pl->epi2 = mode != 0 && pl->pair && pl->block_n == 256 && !d->head2 &&
                ((p.has_res && d->act != HPE_ACT_GELU && (mode == 2 || num_kb <= 8)) || gelu2);
+  }
+  if (d->act == HPE_ACT_GELU_LN && !pl->epi2 && !(pl->pair && pl->block_n == 192)) {
+    delete pl;
+    return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: the LayerNorm-folded GELU layer runs on the cta_group::2 kernels only (>= 2 pixel tiles; 256-wide tiles with two epilogue groups or 192-wide tiles; HPE_B200_PAIR / HPE_B200_EPI2 != 0)");
   }
   pl->fn = d->chain ? (const void*)pick_kernel_chain(d->Cout, d->chain, p.has_res != 0, p.taps * p.kc_per_tap + p.kc2, &pl->smem)
                     : (const void*)pick_kernel(pl->block_n, d->act, p.has_res != 0, d->kind == HPE_CONV_FINAL, pl->pair != 0, d->head2 != 0, pl->epi2 != 0, &pl->smem);
@@ -1682,7 +1740,17 @@ extern "C" int hpe_conv_run2(hpe_conv_plan* pl, const void* x, const void* x2, c
                              const float* shift, const void* residual, void* y, void* stream) {
   HPE_CHECK_ARG(pl && !pl->d.head2, "hpe_conv_run: the plan has a fused head; use hpe_conv_run_head2");
   HPE_CHECK_ARG(!pl->d.chain, "hpe_conv_run: the plan has a chained 1x1 conv; use hpe_conv_run_chain");
+  HPE_CHECK_ARG(pl->d.act != HPE_ACT_GELU_LN, "hpe_conv_run: the plan folds a LayerNorm; use hpe_conv_run_ln");
   return conv_launch(pl, x, x2, w_packed, scale, shift, residual, y, nullptr, nullptr, stream);
+}
+
+extern "C" int hpe_conv_run_ln(hpe_conv_plan* pl, const void* x, const void* w_packed, const float* colsum, const float* shift,
+                               const float* rowstats, int n_slices, int ln_channels, float eps, void* y, void* stream) {
+  HPE_CHECK_ARG(pl && pl->d.act == HPE_ACT_GELU_LN, "hpe_conv_run_ln: the plan's activation is not HPE_ACT_GELU_LN");
+  HPE_CHECK_ARG(rowstats && ((uintptr_t)rowstats & 7) == 0 && n_slices > 0 && ln_channels > 0 && eps > 0.f, "hpe_conv_run_ln: bad LayerNorm arguments");
+  pl->p.rowstats = reinterpret_cast<const float2*>(rowstats);
+  pl->p.ln_slices = n_slices; pl->p.ln_inv_c = 1.f / (float)ln_channels; pl->p.ln_eps = eps;
+  return conv_launch(pl, x, nullptr, w_packed, colsum, shift, nullptr, y, nullptr, nullptr, stream);
 }
 
 extern "C" int hpe_conv_run_chain(hpe_conv_plan* pl, const void* x, const void* x2, const void* w_packed, const float* scale,

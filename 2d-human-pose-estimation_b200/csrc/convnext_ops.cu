@@ -275,7 +275,7 @@ dwconv7_tiled_kernel(const __nv_bfloat16* __restrict__ x, int in_pitch, const fl
 __global__ void __launch_bounds__(kDtMaxWarps * 32, 2)
 dwconv7_tma_kernel(const __grid_constant__ CUtensorMap tmX, const float* __restrict__ wt /* [49][C] */, const float* __restrict__ bias,
                    int H, int W, int C, int th, int tw, int tiles_x, int tiles_y, int n_slices, int n_spatial, int tile_bytes,
-                   __nv_bfloat16* __restrict__ y, int out_pitch) {
+                   __nv_bfloat16* __restrict__ y, int out_pitch, float2* __restrict__ stats) {
   using namespace ptx;
   extern __shared__ uint8_t dsm_raw[];
   uint8_t* dsm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(dsm_raw) + 1023) & ~uintptr_t(1023));
@@ -348,6 +348,35 @@ dwconv7_tma_kernel(const __grid_constant__ CUtensorMap tmX, const float* __restr
               *reinterpret_cast<uint32_t*>(y + ((static_cast<size_t>(b) * H + oy) * W + ox) * out_pitch + ch) = pack_bf16(acc[ry][rx].x, acc[ry][rx].y);
           }
         }
+      }
+      if (stats != nullptr) {
+        // LayerNorm statistics of the STORED (bf16-rounded) values: per pixel the sum and the sum of squares over this slice's 64
+        // channels, i.e. over the warp's 32 lanes.  Reduce-scatter: at offset 16 / 8 / 4 / 2 a lane keeps one half of its
+        // pixels and trades the other, so after four steps it holds ONE pixel (index lane >> 1), then one plain butterfly step:
+        // 16 shuffles per quantity for the block's 16 pixels instead of 80.
+        float sv[kDtTY * kDtRX], qv[kDtTY * kDtRX];
+#pragma unroll
+        for (int i = 0; i < kDtTY * kDtRX; ++i) {
+          const uint32_t pk = pack_bf16(acc[i / kDtRX][i % kDtRX].x, acc[i / kDtRX][i % kDtRX].y);
+          const float a = chok ? bf16_lo(pk) : 0.f, c2 = chok ? bf16_hi(pk) : 0.f;
+          sv[i] = a + c2; qv[i] = fmaf(a, a, c2 * c2);
+        }
+#pragma unroll
+        for (int off = 16, n = kDtTY * kDtRX; n > 1; off >>= 1, n >>= 1) {
+          const bool hi = (lane & off) != 0;
+#pragma unroll
+          for (int i = 0; i < n / 2; ++i) {
+            const float ks = hi ? sv[i + n / 2] : sv[i], ts = hi ? sv[i] : sv[i + n / 2];
+            const float kq = hi ? qv[i + n / 2] : qv[i], tq = hi ? qv[i] : qv[i + n / 2];
+            sv[i] = ks + __shfl_xor_sync(0xffffffffu, ts, off);
+            qv[i] = kq + __shfl_xor_sync(0xffffffffu, tq, off);
+          }
+        }
+        sv[0] += __shfl_xor_sync(0xffffffffu, sv[0], 1);
+        qv[0] += __shfl_xor_sync(0xffffffffu, qv[0], 1);
+        const int pi = lane >> 1, oy = y0 + by + pi / kDtRX, ox = x0 + bx + pi % kDtRX;
+        if ((lane & 1) == 0 && oy < H && ox < W)
+          stats[((static_cast<size_t>(b) * H + oy) * W + ox) * n_slices + slice] = make_float2(sv[0], qv[0]);
       }
     }
     __syncthreads();                                  // every warp is done with this buffer: it may be refilled two tiles later
@@ -532,8 +561,8 @@ extern "C" int hpe_dwconv(const void* x, int in_pitch, int B, int H, int W, int 
   return launch_status("dwconv_kernel");
 }
 
-extern "C" int hpe_dwconv7_bias(const void* x, int in_pitch, int B, int H, int W, int C, const float* w_taps, const float* bias,
-                               void* y, int out_pitch, void* stream) {
+static int dwconv7_bias_impl(const void* x, int in_pitch, int B, int H, int W, int C, const float* w_taps, const float* bias,
+                            void* y, int out_pitch, float* rowstats, void* stream) {
   HPE_CHECK_ARG(x && y && w_taps && bias, "hpe_dwconv7_bias: null pointer");
   HPE_CHECK_ARG(B > 0 && H > 0 && W > 0 && C > 0 && C % 8 == 0, "hpe_dwconv7_bias: C must be a positive multiple of 8");
   HPE_CHECK_ARG(HPE_PITCH_OK(in_pitch, C) && HPE_PITCH_OK(out_pitch, C), "hpe_dwconv7_bias: bad channel pitch");
@@ -569,10 +598,12 @@ extern "C" int hpe_dwconv7_bias(const void* x, int in_pitch, int B, int H, int W
       if (per_slice > n_spatial) per_slice = n_spatial;
       const int grid = (int)(per_slice * n_slices);
       dwconv7_tma_kernel<<<grid, warps * 32, smem, (cudaStream_t)stream>>>(tm, w_taps, bias, H, W, C, th, tw, tiles_x, tiles_y, n_slices,
-                                                                         (int)n_spatial, tile_bytes, (__nv_bfloat16*)y, out_pitch);
+                                                                         (int)n_spatial, tile_bytes, (__nv_bfloat16*)y, out_pitch,
+                                                                         reinterpret_cast<float2*>(rowstats));
       return launch_status("dwconv7_tma_kernel");
     }
   }
+  if (rowstats) return fail(HPE_EUNSUPPORTED, "hpe_dwconv7_bias_stats: LayerNorm statistics come from the TMA-fed kernel only (HPE_B200_DWCONV_TMA=0 is set)");
   const size_t smem = (size_t)(th + 6) * (tw + 6) * kDtSlice * 4;
   // per-DEVICE function attribute: set on every call that needs it
   if (smem > 48 * 1024)
@@ -582,6 +613,21 @@ extern "C" int hpe_dwconv7_bias(const void* x, int in_pitch, int B, int H, int W
   dwconv7_tiled_kernel<<<(unsigned)grid, warps * 32, smem, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, in_pitch, w_taps, bias, H, W, C, th, tw,
                                                                                  tiles_x, tiles_y, n_slices, (__nv_bfloat16*)y, out_pitch);
   return launch_status("dwconv7_tiled_kernel");
+}
+
+extern "C" int hpe_dwconv7_bias(const void* x, int in_pitch, int B, int H, int W, int C, const float* w_taps, const float* bias,
+                               void* y, int out_pitch, void* stream) {
+  return dwconv7_bias_impl(x, in_pitch, B, H, W, C, w_taps, bias, y, out_pitch, nullptr, stream);
+}
+
+extern "C" size_t hpe_dwconv7_stats_elems(int B, int H, int W, int C) {
+  return (B > 0 && H > 0 && W > 0 && C > 0) ? (size_t)B * H * W * ((C + kDtSlice - 1) / kDtSlice) * 2 : 0;
+}
+
+extern "C" int hpe_dwconv7_bias_stats(const void* x, int in_pitch, int B, int H, int W, int C, const float* w_taps, const float* bias,
+                                     void* y, int out_pitch, float* rowstats, void* stream) {
+  HPE_CHECK_ARG(rowstats && ((uintptr_t)rowstats & 7) == 0, "hpe_dwconv7_bias_stats: rowstats must be a non-null, 8-byte aligned pointer");
+  return dwconv7_bias_impl(x, in_pitch, B, H, W, C, w_taps, bias, y, out_pitch, rowstats, stream);
 }
 
 extern "C" int hpe_layernorm_nhwc(const void* x, int in_pitch, long long M, int C, const float* gamma, const float* beta,

@@ -25,7 +25,7 @@ import torch
 import torch.nn as nn
 
 from . import _lib
-from ._lib import ACT_GELU, ACT_NONE, ACT_RELU, ACT_SILU, CONV_1x1, CONV_2x2S2, CONV_3x3, CONV_DECONV4, CONV_FINAL, ConvDesc
+from ._lib import ACT_GELU, ACT_GELU_LN, ACT_NONE, ACT_RELU, ACT_SILU, CONV_1x1, CONV_2x2S2, CONV_3x3, CONV_DECONV4, CONV_FINAL, ConvDesc
 from .conv import ConvLayer, fold_bn
 from .detpose import pose_decode
 
@@ -152,6 +152,14 @@ def _dwconv7_bias(x, w_taps, bias, y):
     _lib.check(rc, "hpe_dwconv7_bias")
 
 
+def _dwconv7_bias_stats(x, w_taps, bias, y, rowstats):
+    B, H, W, C = x.shape
+    with torch.cuda.device(x.device):
+        rc = _lib.lib().hpe_dwconv7_bias_stats(_lib.ptr(x), _pitch(x), B, H, W, C, _lib.ptr(w_taps), _lib.ptr(bias), _lib.ptr(y), _pitch(y),
+                                               _lib.ptr(rowstats), _lib.stream_ptr())
+    _lib.check(rc, "hpe_dwconv7_bias_stats")
+
+
 def _layernorm(x, gamma, beta, eps, y):
     B, H, W, C = x.shape
     with torch.cuda.device(x.device):
@@ -204,6 +212,7 @@ class _PosePlan:
         self.n_launches = 0
         self.graph = None
         self.levels = None                # backbone_only plans have no head outputs
+        self.ln_folded = 0                # ConvNeXt blocks whose LayerNorm runs inside pwconv1's epilogue
         dims, depths = model.dims, model.depths
         bf = lambda *shape: torch.zeros(shape, dtype=torch.bfloat16, device=device)      # noqa: E731
         f32 = lambda t: t.detach().to(device, torch.float32).contiguous()               # noqa: E731
@@ -232,6 +241,35 @@ class _PosePlan:
             self.steps.append(lambda: layer(src, residual, out_t))
             self.n_launches += 1
             return layer
+
+        def pwconv1_ln(blk, src, dst, rowstats):
+            """`x = self.act(self.pwconv1(self.norm(x)))` (convnext.py:74-77) with the LayerNorm folded into the GEMM (conv.run_ln);
+            False when the layer has no kernel for it (tiny batch: no cta_group::2 tiles) -- the caller keeps the separate pass."""
+            Bx, Hx, Wx, Cx = src.shape
+            W1 = blk.pwconv1.weight.detach().to(device, torch.float32)                         # [4C, C]
+            g, beta = blk.norm.weight.detach().to(device, torch.float32), blk.norm.bias.detach().to(device, torch.float32)
+            Wf = W1 * g[None, :]
+            colsum = Wf.to(torch.bfloat16).float().sum(1)                                       # of the weights the GEMM really uses
+            shift = blk.pwconv1.bias.detach().to(device, torch.float32) + W1 @ beta
+            n_out = W1.shape[0]
+            pieces = -(-n_out // 2048)
+            step_c = -(-n_out // pieces // 64) * 64
+            layers = []
+            try:
+                for c0 in range(0, n_out, step_c):
+                    c1 = min(c0 + step_c, n_out)
+                    d = dst[..., c0:c1]
+                    layer = ConvLayer(CONV_1x1, Bx, Hx, Wx, Cx, c1 - c0, 1, ACT_GELU_LN, False, device,
+                                      out_cstride=0 if d.is_contiguous() else _pitch(d))
+                    layer.load(Wf[c0:c1].reshape(c1 - c0, Cx, 1, 1).contiguous(), colsum[c0:c1].contiguous(), shift[c0:c1].contiguous())
+                    layers.append((layer, d))
+            except RuntimeError:
+                return False
+            ns = -(-Cx // 64)
+            for layer, d in layers:
+                self.steps.append(lambda layer=layer, d=d: layer.run_ln(src, rowstats, ns, Cx, blk.norm.eps, d))
+                self.n_launches += 1
+            return True
 
         def convblock(cb, src, dst, extra_bn=None, pad_out=None, pad_in=None):
             """ConvBlock (block.py:20-45) with its BatchNorm folded; 1x1 / 3x3, stride 1|2, SiLU."""
@@ -269,15 +307,30 @@ class _PosePlan:
                 conv(CONV_2x2S2, other, nxt, cv.weight, ones(C), cv.bias, ACT_NONE, 2)
                 cur, other = nxt, nxt2
             t1, t2 = bf(B, h, w, C), bf(B, h, w, 4 * C)
+            # LayerNorm folded into pwconv1 (HPE_B200_LN_FOLD=0: separate LayerNorm pass): the depthwise conv emits the per-pixel
+            # statistics, pwconv1 normalises in its epilogue
+            ln_fold = os.environ.get("HPE_B200_LN_FOLD", "1") != "0" and os.environ.get("HPE_B200_DWCONV", "tiled") != "fused" \
+                and os.environ.get("HPE_B200_DWCONV_TMA", "1") != "0"
+            rowstats = torch.zeros(B * h * w * (-(-C // 64)) * 2, dtype=torch.float32, device=device) if ln_fold else None
             for blk in bb.stages[i]:
                 wt = f32(blk.dwconv.weight.detach().reshape(C, 49).t())             # [49][C]
                 p0, p1, p2 = f32(blk.dwconv.bias), f32(blk.norm.weight), f32(blk.norm.bias); self.keep += [wt, p0, p1, p2]
+                folded = False
                 if os.environ.get("HPE_B200_DWCONV", "tiled") == "fused":      # one kernel: dwconv + bias + LayerNorm
                     step(lambda x=cur, y=t1, wt=wt, p0=p0, p1=p1, p2=p2, e=blk.norm.eps: _dwconv(x, wt, p0, p1, p2, e, 7, 1, y))
-                else:                                                          # FMA-bound tiled dwconv, then LayerNorm in place
-                    step(lambda x=cur, y=t1, wt=wt, p0=p0: _dwconv7_bias(x, wt, p0, y))
+                elif ln_fold:                                                  # dwconv (+ LayerNorm statistics), LayerNorm inside pwconv1
+                    n_before = len(self.steps)
+                    step(lambda x=cur, y=t1, wt=wt, p0=p0, rs=rowstats: _dwconv7_bias_stats(x, wt, p0, y, rs))
+                    folded = pwconv1_ln(blk, t1, t2, rowstats)
+                    if not folded:
+                        del self.steps[n_before:]
+                        self.n_launches -= 1
+                if not folded and os.environ.get("HPE_B200_DWCONV", "tiled") != "fused":
+                    step(lambda x=cur, y=t1, wt=wt, p0=p0: _dwconv7_bias(x, wt, p0, y))      # FMA-bound tiled dwconv, then LayerNorm in place
                     step(lambda y=t1, p1=p1, p2=p2, e=blk.norm.eps: _layernorm(y, p1, p2, e, y))
-                conv(CONV_1x1, t1, t2, blk.pwconv1.weight.detach().reshape(4 * C, C, 1, 1), ones(4 * C), blk.pwconv1.bias, ACT_GELU)
+                if not folded:
+                    conv(CONV_1x1, t1, t2, blk.pwconv1.weight.detach().reshape(4 * C, C, 1, 1), ones(4 * C), blk.pwconv1.bias, ACT_GELU)
+                self.ln_folded += int(folded)
                 gam = blk.gamma.detach().float()
                 conv(CONV_1x1, t2, other, blk.pwconv2.weight.detach().reshape(C, 4 * C, 1, 1), gam, gam * blk.pwconv2.bias.detach().float(),
                      ACT_NONE, residual=cur)

@@ -40,6 +40,7 @@ extern "C" {
 #define HPE_ACT_RELU 1        /* timm Bottleneck act (resnet.py:244-270)                               */
 #define HPE_ACT_SILU 2        /* first-party ConvBlock default act (HPE/models/nn/modules/block.py:20-45) */
 #define HPE_ACT_GELU 3        /* exact erf GELU of the ConvNeXt block MLP (HPE/thirdparty/dinov3/dinov3/models/convnext.py:60) */
+#define HPE_ACT_GELU_LN 4     /* GELU of a 1x1 conv with the LayerNorm in front of it folded in (convnext.py:74-77: norm -> pwconv1 -> act); run with hpe_conv_run_ln */
 
 int         hpe_abi_version(void);
 const char* hpe_last_error(void);
@@ -195,6 +196,13 @@ int  hpe_conv_run2(hpe_conv_plan* plan, const void* x, const void* x2, const voi
  * Cin 256, Cout K) into a ZERO-initialised buffer of 32*256 bf16; bias2 [K] f32; heatmaps [B,K,Ho,Wo] f32 NCHW */
 int  hpe_conv_run_head2(hpe_conv_plan* plan, const void* x, const void* w_packed, const float* scale, const float* shift,
                         const void* w2_packed, const float* bias2, float* heatmaps, void* stream);
+/* LayerNorm-folded variant (desc.act = HPE_ACT_GELU_LN; plain 1x1 / stride 1 layers on the cta_group::2 kernels): computes
+ * `x = self.act(self.pwconv1(self.norm(x)))` of the ConvNeXt block (HPE/thirdparty/dinov3/dinov3/models/convnext.py:74-77) from
+ * the RAW x: w_packed = pwconv1's weights times the LayerNorm gamma (per input channel), colsum[n] = sum over the input
+ * channels of the bf16-rounded folded weights, shift[n] = b[n] + sum_c W[n][c] beta[c]; rowstats / n_slices as written by
+ * hpe_dwconv7_bias_stats, ln_channels = C, eps = the LayerNorm's.  y = gelu(rstd_r (x W'^T - mu_r colsum) + shift). */
+int  hpe_conv_run_ln(hpe_conv_plan* plan, const void* x, const void* w_packed, const float* colsum, const float* shift,
+                     const float* rowstats, int n_slices, int ln_channels, float eps, void* y, void* stream);
 /* chained variant (desc.chain = N2): w2_packed = the next 1x1 conv's weights packed with hpe_conv_pack_weight (kind HPE_CONV_1x1,
  * Cin 256, Cout N2); scale2 / shift2 [N2] its folded BN; y2 [B,Ho,Wo,N2] bf16 NHWC.  x2 as in hpe_conv_run2 (NULL without Cin2). */
 int  hpe_conv_run_chain(hpe_conv_plan* plan, const void* x, const void* x2, const void* w_packed, const float* scale,
@@ -373,6 +381,12 @@ int hpe_dwconv(const void* x, int in_pitch, int B, int H, int W, int C, int ksiz
 /* depthwise 7x7 + bias only (FMA-bound tiled formulation; the LayerNorm that follows is hpe_layernorm_nhwc) */
 int hpe_dwconv7_bias(const void* x, int in_pitch, int B, int H, int W, int C, const float* w_taps, const float* bias,
                      void* y, int out_pitch, void* stream);
+/* ... that also writes, per output pixel and 64-channel slice, (sum, sum of squares) of the STORED bf16 values:
+ * rowstats [B*H*W][ceil(C/64)][2] fp32 = hpe_dwconv7_stats_elems(B,H,W,C) floats -- the statistics of the block's LayerNorm
+ * (convnext.py:73-74), consumed by hpe_conv_run_ln, so that the LayerNorm pass itself disappears. */
+size_t hpe_dwconv7_stats_elems(int B, int H, int W, int C);
+int hpe_dwconv7_bias_stats(const void* x, int in_pitch, int B, int H, int W, int C, const float* w_taps, const float* bias,
+                           void* y, int out_pitch, float* rowstats, void* stream);
 int hpe_layernorm_nhwc(const void* x, int in_pitch, long long M, int C, const float* gamma, const float* beta, float eps,
                        void* y, int out_pitch, void* stream);
 int hpe_patchify4(const float* img_nchw, int B, int H, int W, void* out, void* stream);

@@ -152,6 +152,83 @@ def _rel_err(a, b):
     return float(np.abs(a - b).max() / np.abs(b).max()), float(np.sqrt(((a - b) ** 2).mean()) / np.sqrt((b ** 2).mean()))
 
 
+@pytest.mark.parametrize("C,B,H,W", [(96, 3, 64, 48), (192, 5, 32, 24), (384, 16, 16, 12), (768, 40, 8, 6), (1024, 33, 8, 6)])
+def test_layernorm_folded_into_pwconv1(hpe, cuda_dev, C, B, H, W):
+    """ConvNeXt block front half `act(pwconv1(norm(dwconv(x))))` (dinov3 convnext.py:72-77) with the LayerNorm folded into the GEMM:
+    hpe_dwconv7_bias_stats writes the raw dwconv output + per-pixel partial (sum, sum of squares), hpe_conv_run_ln normalises in
+    its epilogue.  Checked (a) the statistics against the stored bf16 tensor, (b) the output against fp32 PyTorch on that tensor
+    at one bf16 rounding, (c) against the unfolded kernel pair (LayerNorm pass + GELU conv)."""
+    lib, pm = _mods()
+    conv = __import__("importlib").import_module("2d-human-pose-estimation_b200.conv")
+    g = torch.Generator().manual_seed(C + B)
+    x = make(g, B, C, H, W) + 0.7                          # a common mode, so that mean != 0 matters
+    w = torch.randn(C, 1, 7, 7, generator=g) * 0.1; bias = torch.randn(C, generator=g) * 0.1
+    gam = torch.rand(C, generator=g) + 0.5; bet = torch.randn(C, generator=g) * 0.1
+    W1 = torch.randn(4 * C, C, generator=g) * C ** -0.5; b1 = torch.randn(4 * C, generator=g) * 0.1
+    d = lambda t: t.cuda().contiguous()                                            # noqa: E731
+    ns = -(-C // 64)
+    y = torch.empty((B, H, W, C), dtype=torch.bfloat16, device="cuda")
+    stats = torch.full((B * H * W, ns, 2), float("nan"), device="cuda")
+    pm._dwconv7_bias_stats(nhwc(x), d(w.reshape(C, 49).t()), d(bias), y, stats)
+    y_plain = torch.empty_like(y)
+    pm._dwconv7_bias(nhwc(x), d(w.reshape(C, 49).t()), d(bias), y_plain)
+    torch.cuda.synchronize()
+    assert torch.equal(y, y_plain)
+    yf = y.float().reshape(-1, C)
+    pad = torch.zeros(yf.shape[0], ns * 64 - C, device="cuda")
+    ysl = torch.cat([yf, pad], 1).reshape(-1, ns, 64)
+    assert torch.allclose(stats[..., 0], ysl.sum(-1), rtol=1e-5, atol=1e-4)
+    assert torch.allclose(stats[..., 1], (ysl * ysl).sum(-1), rtol=1e-5, atol=1e-4)
+    # (b) fp32 reference on the stored tensor
+    ref = F.gelu(F.linear(F.layer_norm(yf.cpu(), (C,), gam, bet, 1e-6), W1, b1)).reshape(B, H, W, 4 * C)
+    Wf = (W1 * gam[None, :]).cuda()
+    out = torch.empty((B, H, W, 4 * C), dtype=torch.bfloat16, device="cuda")
+    n_out, pieces = 4 * C, -(-4 * C // 2048)
+    step_c = -(-n_out // pieces // 64) * 64
+    for c0 in range(0, n_out, step_c):
+        c1 = min(c0 + step_c, n_out)
+        layer = conv.ConvLayer(lib.CONV_1x1, B, H, W, C, c1 - c0, 1, lib.ACT_GELU_LN, False, cuda_dev,
+                               out_cstride=0 if pieces == 1 else 4 * C)
+        layer.load(Wf[c0:c1].reshape(c1 - c0, C, 1, 1).contiguous(), Wf[c0:c1].to(torch.bfloat16).float().sum(1).contiguous(),
+                   (b1 + W1 @ bet)[c0:c1].cuda().contiguous())
+        layer.run_ln(y, stats, ns, C, 1e-6, out[..., c0:c1])
+    torch.cuda.synchronize()
+    check(out.float().cpu(), ref, "LN-folded pwconv1 + GELU", k=2.0)
+    # (c) the unfolded pair on the same tensor
+    t = torch.empty_like(y)
+    pm._layernorm(y, d(gam), d(bet), 1e-6, t)
+    out2 = torch.empty_like(out)
+    for c0 in range(0, n_out, step_c):
+        c1 = min(c0 + step_c, n_out)
+        layer = conv.ConvLayer(lib.CONV_1x1, B, H, W, C, c1 - c0, 1, lib.ACT_GELU, False, cuda_dev,
+                               out_cstride=0 if pieces == 1 else 4 * C)
+        layer.load(W1[c0:c1].reshape(c1 - c0, C, 1, 1).cuda().contiguous(), torch.ones(c1 - c0, device="cuda"), b1[c0:c1].cuda().contiguous())
+        layer(t, None, out2[..., c0:c1])
+    torch.cuda.synchronize()
+    check(out2.float().cpu(), ref, "LayerNorm pass + pwconv1 + GELU", k=2.0)
+    check(out.float().cpu(), out2.float().cpu(), "folded vs unfolded", k=3.0)
+
+
+def test_dinov3pose_layernorm_fold_switch(hpe, cuda_dev, monkeypatch):
+    """The plan folds the blocks' LayerNorms by default (ln_folded counts them) and the level maps stay within the
+    golden test's bar of the HPE_B200_LN_FOLD=0 plan."""
+    oracle = dp.build_synthetic("tiny", (17, 3), 1, seed=0)
+    x = torch.rand(4, 3, 128, 96, generator=torch.Generator().manual_seed(1)).to(cuda_dev)
+    outs = []
+    for fold in ("1", "0"):
+        monkeypatch.setenv("HPE_B200_LN_FOLD", fold)
+        m = hpe.DINOv3Pose("dinov3_convnext_tiny", nkpts=(17, 3), ncls=1, device=cuda_dev)
+        m.load_state_dict(oracle.state_dict())
+        with torch.no_grad():
+            outs.append([l.clone() for l in m.train()(x)])
+        plan = next(iter(m._plans.values()))
+        # (the last stage of this small input is a single pixel tile: no cta_group::2 kernel, its 3 blocks keep the separate pass)
+        assert plan.ln_folded == (sum(m.depths) - 3 if fold == "1" else 0), plan.ln_folded
+    for a, b in zip(*outs):
+        mx, rms = _rel_err(a.cpu().numpy(), b.cpu().numpy())
+        assert mx <= 1e-2 and rms <= 5e-3, (mx, rms)
+
+
 def test_dinov3pose_forward_vs_reference_golden(hpe, cuda_dev):
     oracle = dp.build_synthetic("tiny", (17, 3), 1, seed=0)
     m = hpe.DINOv3Pose("dinov3_convnext_tiny", nkpts=(17, 3), ncls=1, device=cuda_dev)
