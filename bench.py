@@ -152,8 +152,9 @@ def workload_config(args, world):
     return {"workload": f"resnet50+deconv-head heatmap fwd+decode, {H}x{W}, K={K}, batch {B}/GPU, random-init weights "
                         "(BASELINE configs[1])",
             "global_batch": world * B, "parallelism": f"dp{world}",
-            "l2": f"inputs ({B * 3 * H * W / 1e6:.0f} MB uint8 / {B * 3 * H * W * 4 / 1e6:.0f} MB fp32 per step, 2 alternating batches) and "
-                  "every activation exceed the 126 MB L2; no flush needed"}
+            "input": "uint8 NCHW images resident in HBM, /255 on the device (HPE/train.py:117-120: imgs.to(device); imgs.float() / 255.0)",
+            "l2": f"two alternating input batches ({B * 3 * H * W / 1e6:.0f} MB uint8 each) and every activation of a step (3.4 GB in total) "
+                  "exceed the 126 MB L2; no flush needed"}
 
 
 # --------------------------------------------------------------------------------------------- CPU arm
@@ -166,13 +167,13 @@ def cpu_forward_decode(batch, H, W, K, steps, warmup, threads=None):
     n = threads or os.cpu_count() or 1
     torch.set_num_threads(n)
     model = rr.build_synthetic(K, seed=0)
-    x = torch.rand(batch, 3, H, W, generator=torch.Generator().manual_seed(0))
+    x = torch.randint(0, 256, (batch, 3, H, W), generator=torch.Generator().manual_seed(0), dtype=torch.uint8)   # the reference's input format
     center, scale = hr.synth_center_scale(batch)
     times = []
     with torch.no_grad():
         for i in range(warmup + steps):
             t0 = time.perf_counter()
-            hm = model(x).numpy()
+            hm = model(x.float() / 255.0).numpy()                 # HPE/train.py:120: imgs = imgs.float() / 255.0
             preds, maxvals = hr.get_final_preds(hm, center, scale)
             dt = time.perf_counter() - t0
             if i >= warmup:
@@ -285,13 +286,14 @@ def make_model(hpe, K, dev, train=False):
 
 def infer_setup(hpe, ctx, model, B, H, W, K, seed=100):
     """Synthetic inputs of one rank: two alternating uint8 host batches (the reference's host format, HPE/train.py:117-120),
-    their fp32 twins (= u8 / 255, what the reference uploads after `.float() / 255`), device copies, per-sample affines."""
+    device copies of them (the reference's device-resident input too: `imgs.to(device)` and THEN `imgs.float() / 255.0`,
+    HPE/train.py:117-120 -- here the /255 is fused into the stem's layout kernel), their fp32 twins, per-sample affines."""
     gen = torch.Generator().manual_seed(seed + ctx.rank)
     h_u8 = [torch.randint(0, 256, (B, 3, H, W), generator=gen, dtype=torch.uint8).pin_memory() for _ in range(2)]
     center = torch.rand(B, 2, generator=gen) * torch.tensor([640.0, 480.0])
     sw = torch.rand(B, 1, generator=gen) * 2 + 0.5
     h_aff = hpe.affine_from_center_scale(center, torch.cat([sw, sw * 4 / 3], 1), (H // 4, W // 4)).pin_memory()
-    return {"h_u8": h_u8, "h_aff": h_aff, "x": [t.to(ctx.dev).float().div_(255.0) for t in h_u8], "aff": h_aff.to(ctx.dev),
+    return {"h_u8": h_u8, "h_aff": h_aff, "x": [t.to(ctx.dev).float().div_(255.0) for t in h_u8], "xu": [t.to(ctx.dev) for t in h_u8], "aff": h_aff.to(ctx.dev),
             "rg": hpe.ResultGather(B, K, ctx.dev)}
 
 
@@ -303,7 +305,7 @@ def infer_step_fn(hpe, model, s, marks=None):
     def step(i):
         if marks is not None:
             e0 = ev(); e0.record()
-        hm = model.forward_static(s["x"][i & 1])
+        hm = model.forward_static(s["xu"][i & 1])
         if marks is not None:
             e1 = ev(); e1.record()
         hpe.get_final_preds_xyv(hm, s["aff"], rg.slot())

@@ -136,3 +136,14 @@ def test_bf16_emulated_forward_close_to_fp32():
     b = rr.forward_bf16_emulated(m, x)
     assert a.shape == b.shape == (1, 17, 16, 16)
     assert (a - b).abs().max().item() < 0.05 * a.abs().max().item() + 1e-3
+
+
+def test_uint8_scale_by_reciprocal_equals_division_in_bf16():
+    """`imgs.float() / 255.0` (HPE/train.py:120) followed by the bf16 rounding of the stem's input: the uint8 layout kernel
+    multiplies by fp32(1/255) instead of dividing.  The fp32 values differ in the last bit for about half of the 256 inputs, the
+    bf16 values for none -- checked here for every possible byte."""
+    import torch
+    b = torch.arange(256, dtype=torch.float32)
+    want = (b / 255.0).to(torch.bfloat16)
+    got = (b * torch.tensor(1.0 / 255.0, dtype=torch.float32)).to(torch.bfloat16)
+    assert torch.equal(want, got)
