@@ -874,14 +874,17 @@ __global__ void __launch_bounds__(256)
 preprocess_kernel(const T* __restrict__ img, int B, int H, int W, __nv_bfloat16* __restrict__ out) {
   const int Hs = H / 2, Ws = W / 2, Wp = Ws + kS2DPad;
   const long long total = static_cast<long long>(B) * Hs * Wp;
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+  const int lane = threadIdx.x & 31;
+  // whole warps walk the loop: the output is linear in i (32 bytes per thread), and the warp trades its 16-byte pieces by shuffle
+  // so that each of its two store instructions covers 512 contiguous bytes (not 32 half-written sectors)
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i - lane < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
     const int xp = static_cast<int>(i % Wp);
     const int ys = static_cast<int>((i / Wp) % Hs);
     const int b  = static_cast<int>(i / (static_cast<long long>(Wp) * Hs));
     const int xs = xp - 2;
     uint4 lo = make_uint4(0, 0, 0, 0), hi = make_uint4(0, 0, 0, 0);
-    if (xs >= 0 && xs < Ws) {
+    if (i < total && xs >= 0 && xs < Ws) {
       float v[2][2][3];
 #pragma unroll
       for (int c = 0; c < 3; ++c)
@@ -895,8 +898,17 @@ preprocess_kernel(const T* __restrict__ img, int B, int H, int W, __nv_bfloat16*
       hi = make_uint4(pack_bf16(v[1][0][0], v[1][0][1]), pack_bf16(v[1][0][2], 0.f),
                       pack_bf16(v[1][1][0], v[1][1][1]), pack_bf16(v[1][1][2], 0.f));
     }
-    uint4* o = reinterpret_cast<uint4*>(out + static_cast<size_t>(i) * 16);
-    o[0] = lo; o[1] = hi;
+    uint4* o = reinterpret_cast<uint4*>(out) + (i - lane) * 2;            // the warp's first pixel
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int src = j * 16 + (lane >> 1);                                // piece j * 32 + lane = half (lane & 1) of that lane's pixel
+      uint4 a, c2;
+      a.x = __shfl_sync(0xffffffffu, lo.x, src); a.y = __shfl_sync(0xffffffffu, lo.y, src);
+      a.z = __shfl_sync(0xffffffffu, lo.z, src); a.w = __shfl_sync(0xffffffffu, lo.w, src);
+      c2.x = __shfl_sync(0xffffffffu, hi.x, src); c2.y = __shfl_sync(0xffffffffu, hi.y, src);
+      c2.z = __shfl_sync(0xffffffffu, hi.z, src); c2.w = __shfl_sync(0xffffffffu, hi.w, src);
+      if (i - lane + src < total) o[j * 32 + lane] = (lane & 1) ? c2 : a;
+    }
   }
 }
 

@@ -29,7 +29,9 @@ __device__ __forceinline__ float nt_act(float u, int act) {
 }
 __device__ __forceinline__ float nt_dact(float u, int act) {
   if (act == 1) return u > 0.f ? 1.f : 0.f;
-  if (act == 2) { const float s = 1.f / (1.f + __expf(-u)); return s * fmaf(u, 1.f - s, 1.f); }
+  // SiLU'(u) = s (1 + u (1 - s)), s = sigmoid(u); the reciprocal is the 1-ulp MUFU approximation: the IEEE division cost ~8 issue
+  // slots per element and made the backward reduction compute-bound at the 1-2 blocks per SM these small tensors give
+  if (act == 2) { const float s = __fdividef(1.f, 1.f + __expf(-u)); return s * fmaf(u, 1.f - s, 1.f); }
   return 1.f;
 }
 
@@ -56,19 +58,36 @@ bnact_reduce_kernel(const __nv_bfloat16* __restrict__ z, const __nv_bfloat16* __
     }
     const long long per = (M + gridDim.y - 1) / gridDim.y;
     const long long r0 = static_cast<long long>(blockIdx.y) * per, r1 = r0 + per < M ? r0 + per : M;
-    for (long long r = r0 + ty; r < r1; r += 8) {
-      float fz[8];
-      nt_unpack8(__ldg(reinterpret_cast<const uint4*>(z) + r * Cv + vec), fz);
-      if (MODE == 0) {
+    // four rows per pass, every load issued before the first use (with one row in flight per thread and 1-2 blocks per SM the
+    // kernel ran at the latency of a single load: 58 launches of the backward reduction took 1.33 ms at B = 64); the rows are
+    // still added in the order r0 + ty, + 8, + 16, ...: same bits as before
+    constexpr int U = 4;
+    for (long long r = r0 + ty; r < r1; r += 8 * U) {
+      uint4 vz[U], vd[U];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) { a0[e] += fz[e]; a1[e] = fmaf(fz[e], fz[e], a1[e]); }
-      } else {
-        float fd[8];
-        nt_unpack8(__ldg(reinterpret_cast<const uint4*>(dy) + r * Cv + vec), fd);
+      for (int u = 0; u < U; ++u) {
+        const long long rr = r + 8 * u;
+        if (rr < r1) {
+          vz[u] = __ldg(reinterpret_cast<const uint4*>(z) + rr * Cv + vec);
+          if (MODE == 1) vd[u] = __ldg(reinterpret_cast<const uint4*>(dy) + rr * Cv + vec);
+        }
+      }
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const float g = fd[e] * nt_dact(fmaf(fz[e], sc[e], sh[e]), act);
-          a0[e] += g; a1[e] = fmaf(g, (fz[e] - mu[e]) * rs[e], a1[e]);
+      for (int u = 0; u < U; ++u) {
+        if (r + 8 * u >= r1) break;
+        float fz[8];
+        nt_unpack8(vz[u], fz);
+        if (MODE == 0) {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) { a0[e] += fz[e]; a1[e] = fmaf(fz[e], fz[e], a1[e]); }
+        } else {
+          float fd[8];
+          nt_unpack8(vd[u], fd);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const float g = fd[e] * nt_dact(fmaf(fz[e], sc[e], sh[e]), act);
+            a0[e] += g; a1[e] = fmaf(g, (fz[e] - mu[e]) * rs[e], a1[e]);
+          }
         }
       }
     }
@@ -145,19 +164,37 @@ __global__ void __launch_bounds__(256)
 bnact_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ z, const float* __restrict__ coef,
                        const float* __restrict__ scale, const float* __restrict__ shift, int act, int C, long long nvec, int Cv,
                        __nv_bfloat16* __restrict__ dz) {
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int c0 = static_cast<int>(i % Cv) * 8;
-    float fd[8], fz[8], o[8];
-    nt_unpack8(__ldg(reinterpret_cast<const uint4*>(dy) + i), fd);
-    nt_unpack8(__ldg(reinterpret_cast<const uint4*>(z) + i), fz);
+  // two vectors per pass (four 16-byte loads in flight per thread), per-channel coefficients as 16-byte loads (C % 8 == 0 and the
+  // arrays are 16-byte aligned: torch allocations / scratch + a multiple of 4 floats); same arithmetic per element as before
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i0 = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i0 < nvec; i0 += 2 * stride) {
+    uint4 vd[2], vz[2];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      const int c = c0 + e;
-      const float g = fd[e] * nt_dact(fmaf(fz[e], __ldg(scale + c), __ldg(shift + c)), act);
-      o[e] = fmaf(__ldg(coef + c), g, fmaf(__ldg(coef + C + c), fz[e], __ldg(coef + 2 * C + c)));
+    for (int u = 0; u < 2; ++u) {
+      const long long i = i0 + u * stride;
+      if (i < nvec) { vd[u] = __ldg(reinterpret_cast<const uint4*>(dy) + i); vz[u] = __ldg(reinterpret_cast<const uint4*>(z) + i); }
     }
-    reinterpret_cast<uint4*>(dz)[i] = nt_pack8(o);
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const long long i = i0 + u * stride;
+      if (i >= nvec) break;
+      const int c0 = static_cast<int>(i % Cv) * 8;
+      float fd[8], fz[8], o[8], k[5][8];
+      nt_unpack8(vd[u], fd);
+      nt_unpack8(vz[u], fz);
+      const float* src[5] = {scale + c0, shift + c0, coef + c0, coef + C + c0, coef + 2 * C + c0};
+#pragma unroll
+      for (int a = 0; a < 5; ++a) {
+        const float4 lo = __ldg(reinterpret_cast<const float4*>(src[a])), hi = __ldg(reinterpret_cast<const float4*>(src[a]) + 1);
+        k[a][0] = lo.x; k[a][1] = lo.y; k[a][2] = lo.z; k[a][3] = lo.w; k[a][4] = hi.x; k[a][5] = hi.y; k[a][6] = hi.z; k[a][7] = hi.w;
+      }
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const float g = fd[e] * nt_dact(fmaf(fz[e], k[0][e], k[1][e]), act);
+        o[e] = fmaf(k[2][e], g, fmaf(k[3][e], fz[e], k[4][e]));
+      }
+      reinterpret_cast<uint4*>(dz)[i] = nt_pack8(o);
+    }
   }
 }
 
@@ -415,7 +452,8 @@ extern "C" int hpe_bnact_backward(const void* dy, const void* z, long long M, in
   if (rc) return rc;
   HPE_CHECK_ARG(dy && z && mean && rstd && gamma && scale && shift && scratch && dbeta && dgamma && dz && act >= 0 && act <= 2,
                 "hpe_bnact_backward: bad argument");
-  HPE_CHECK_ARG((((uintptr_t)dy | (uintptr_t)z | (uintptr_t)dz) & 15) == 0, "hpe_bnact_backward: misaligned pointer");
+  HPE_CHECK_ARG((((uintptr_t)dy | (uintptr_t)z | (uintptr_t)dz | (uintptr_t)scale | (uintptr_t)shift | (uintptr_t)scratch) & 15) == 0,
+                "hpe_bnact_backward: misaligned pointer (tensors, scale / shift and scratch must be 16-byte aligned)");
   cudaStream_t st = (cudaStream_t)stream;
   float* coef = scratch + (size_t)kNtSlices * 2 * C;
   const int ns = nt_slices(M);
