@@ -1151,8 +1151,8 @@ static int pick_block_n(const hpe_conv_desc* d, long long m_tiles) {
     // columns on 74 clusters = 2 waves at 65 %; as 144 items of 192 columns (the third N tile a third full) they are 2 waves of
     // 3/4 the length.  Measured (per-layer log, three boxes): layer4 3x3 176 / 169 / 175 -> 157 / 143 / 130 us, layer4 1x1
     // 246 / 235 / 245 -> 244 / 224 / 209 us.  HPE_B200_WAVE192=0 keeps the widest tile that divides Cout.
-    static int wave = -1;
-    if (wave < 0) { const char* e = getenv("HPE_B200_WAVE192"); wave = e ? atoi(e) : 1; }
+    const char* ew = getenv("HPE_B200_WAVE192");            // read per plan (plans are created once per layer and shape)
+    const int wave = ew ? atoi(ew) : 1;
     // (not for the GELU layers: their 256-wide tiles run two epilogue groups, which the 192-wide kernel does not have)
     if (wave && d->Cout % 256 == 0 && d->Cout >= 512 && !d->chain && !d->has_residual && d->act != HPE_ACT_GELU && d->act != HPE_ACT_GELU_LN && !is_class_strided(d->kind) && m_tiles >= 2 &&
         (d->Cout + 191) / 192 * 192 <= kMaxCout) {

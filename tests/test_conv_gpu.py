@@ -109,6 +109,36 @@ def test_conv3x3(hpe, cuda_dev, B, H, W, C, Cout, stride):
     check(nchw(y), ref, "conv3x3")
 
 
+@pytest.mark.parametrize("kind,B,H,W,Cin,Cout", [("3x3", 256, 8, 6, 512, 512), ("1x1", 256, 8, 6, 2048, 512), ("3x3", 9, 8, 6, 512, 512)])
+def test_wave_quantisation_tiles_and_schedule_are_bit_identical(hpe, cuda_dev, monkeypatch, kind, B, H, W, Cin, Cout):
+    """Layer4's conv1 / conv2 at the benchmark batch: 96 cta_group::2 work items of 256 columns on 74 clusters, run as 144 items of
+    192 columns instead (HPE_B200_WAVE192, the third N tile a third full) -- and any layer walked last tile to first with L2
+    hints (hpe_conv_set_schedule): the same MMAs per output element, so the same bits as the 256-wide forward walk; parity
+    against fp32 PyTorch on top."""
+    from importlib import import_module
+    conv = import_module("2d-human-pose-estimation_b200.conv")
+    g = torch.Generator().manual_seed(11)
+    k = 3 if kind == "3x3" else 1
+    x = make(g, B, Cin, H, W); w = make(g, Cout, Cin, k, k, s=(k * k * Cin) ** -0.5)
+    scale = torch.rand(Cout, generator=g) + 0.5; shift = torch.randn(Cout, generator=g) * 0.1
+    xin = nhwc(x)
+    outs = []
+    for wave in ("1", "0"):
+        monkeypatch.setenv("HPE_B200_WAVE192", wave)
+        layer = conv.ConvLayer(conv.CONV_3x3 if k == 3 else conv.CONV_1x1, B, H, W, Cin, Cout, 1, 1, False).load(w, scale, shift)
+        outs.append(layer(xin).clone())
+        assert layer.set_schedule(True, 2, 0, 1) is True                 # reversed walk, evict-last stores, evict-first input loads
+        outs.append(layer(xin).clone())
+    torch.cuda.synchronize()
+    for o in outs[1:]:
+        assert torch.equal(outs[0], o)
+    if B <= 16:
+        ref = torch.relu(F.conv2d(x, w, padding=k // 2) * scale[None, :, None, None] + shift[None, :, None, None])
+        check(nchw(outs[0]), ref, "wave192 conv")
+    with pytest.raises(RuntimeError):
+        layer.set_schedule(False, 3, 0, 0)                               # hints are 0 | 1 | 2
+
+
 @pytest.mark.parametrize("B,H,W", [(4, 64, 48), (2, 256, 192), (3, 36, 20), (3, 96, 80), (2, 240, 112), (1, 248, 90), (200, 64, 32)])
 def test_stem_and_maxpool(hpe, cuda_dev, B, H, W):
     from importlib import import_module
