@@ -495,6 +495,23 @@ class _ForwardPlan:
             rows.append((name, fam, flops, layer, (src, res, dst, src2, dst2)))
         return rows
 
+    def layer_bytes(self):
+        """Algorithmic HBM bytes of every conv launch of a step, keyed by module path: the tensors it must read (input -- for a
+        stride-2 1x1 conv only the pixels it samples --, shortcut, second source) and write (output, chained output), plus its
+        packed weights once.  The other half of the per-layer roofline next to ``layer_table``'s FLOPs."""
+        out = {}
+        for k, (name, layer, src, res, dst, src2, dst2) in enumerate((n, *op) for n, op in zip(self.named, self.ops)):
+            d = layer.desc
+            passes = self.n_chunks if k < self.n_section_ops else 1
+            nb = lambda key: self.bufs[key].numel() * self.bufs[key].element_size() if key in self.bufs else 0      # noqa: E731
+            src_b = nb(src) if k >= self.n_section_ops or src not in self.full_keys else nb(src) / self.n_chunks
+            if d.kind == CONV_1x1 and d.stride == 2:
+                src_b /= 4
+            src2_b = (nb(src2) / (4 if d.stride2 == 2 else 1)) if src2 else 0
+            total = src_b + src2_b + (nb(res) if res else 0) + nb(dst) + (nb(dst2) if dst2 else 0)
+            out[name] = total * passes + layer.w_packed.numel() * layer.w_packed.element_size()
+        return out
+
     def export_acts(self):
         """NCHW fp32 CPU copies of every launch's stored inputs and output, keyed by module path: ``{"x", "res", "x2", "y"}``
         (the stem's ``x`` is omitted: its input is the image).  Teacher-forced parity tests feed these to the fp32 oracle

@@ -376,15 +376,21 @@ def per_kernel_table(model, x, peaks):
     model.forward_static(x)
     plan = model._plans[(tuple(x.shape), x.device.index)]
     rows = plan.time_layers(reps=3)
+    nbytes = plan.layer_bytes()
     fam = {}
     for name, f, flops, us in rows:
-        d = fam.setdefault(f, {"launches": 0, "us": 0.0, "gflop": 0.0})
-        d["launches"] += 1; d["us"] += us; d["gflop"] += flops / 1e9
+        d = fam.setdefault(f, {"launches": 0, "us": 0.0, "gflop": 0.0, "mb": 0.0, "bound_us": 0.0, "hbm_bound": 0})
+        t_tensor, t_hbm = flops / (peaks["tflops_burst"] * 1e12) * 1e6, nbytes[name] / (peaks["hbm"] * 1e9) * 1e6
+        d["launches"] += 1; d["us"] += us; d["gflop"] += flops / 1e9; d["mb"] += nbytes[name] / 1e6
+        d["bound_us"] += max(t_tensor, t_hbm); d["hbm_bound"] += int(t_hbm > t_tensor)
     out = {}
     for f, d in fam.items():
         tf = d["gflop"] / 1e3 / (d["us"] * 1e-6) if d["us"] > 0 else 0.0
         out[f] = {"launches": d["launches"], "us_per_step": round(d["us"], 1), "tflops": round(tf, 1),
-                  "frac_burst": round(tf / peaks["tflops_burst"], 3)}
+                  "frac_burst": round(tf / peaks["tflops_burst"], 3),
+                  # the per-launch roofline: max(FLOPs / tensor peak, algorithmic bytes / measured HBM copy bandwidth), summed
+                  "mb_per_step": round(d["mb"], 1), "bound_us": round(d["bound_us"], 1), "hbm_bound_launches": d["hbm_bound"],
+                  "frac_of_bound": round(d["bound_us"] / d["us"], 3) if d["us"] > 0 else 0.0}
     return out, rows
 
 
@@ -555,6 +561,18 @@ def run_b200(args):
                 "ms_forward": round(fwd_ms, 4),
                 "note": "algorithmic FLOPs of the step (10.854 GFLOP/image, SURVEY §8d) / CUDA-event time of the forward graph (incl. preprocess)",
                 "per_kernel": per_kernel}
+        if per_kernel:
+            # Two-resource view of the same step: every launch bounded by the slower of its tensor time and its HBM time.  The
+            # whole-step tensor fraction above cannot reach 1 because the 1x1 layers of layer1 / layer2 (and the identity blocks
+            # of layer3) are HBM-bound at bf16 activations; this is the fraction of the step's own per-launch roofline.
+            b_us = sum(v["bound_us"] for v in per_kernel.values())
+            roof["layerwise"] = {"bound_ms": round(b_us / 1e3, 4), "frac": round(b_us / 1e3 / fwd_ms, 4),
+                                 "gb_per_step": round(sum(v["mb_per_step"] for v in per_kernel.values()) / 1e3, 3),
+                                 "hbm_bound_launches": sum(v["hbm_bound_launches"] for v in per_kernel.values()),
+                                 "launches": sum(v["launches"] for v in per_kernel.values()),
+                                 "peaks": {"tensor_tflops": peaks["tflops_burst"], "hbm_gbs": peaks["hbm"]},
+                                 "note": "sum over the conv launches of max(algorithmic FLOPs / burst bf16 peak, algorithmic bytes / measured HBM "
+                                         "copy bandwidth) / ms_forward"}
         if sus:
             tfs = flops_step / (sus["ms_forward"] * 1e-3) / 1e12
             roof["frac_sustained"] = round(tfs / peaks["tflops"], 4)
