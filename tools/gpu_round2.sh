@@ -13,3 +13,8 @@ grep "bn_" gpurun_out/profile_train_bits1.log | cut -c1-90; grep "bn_" gpurun_ou
 HPE_B200_CUDA_GRAPH=0 timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none \
     -k regex:'conv_gemm|yhalo|preprocess|decode' -c 400 --csv --log-file gpurun_out/launches.csv \
     python bench.py --quick --steps 2 --warmup 3 --no-cpu-baseline --sustain-s 0 > gpurun_out/ncu_list.log 2>&1; echo "ncu rc=$?"; tail -2 gpurun_out/ncu_list.log | cut -c1-300
+# DINOv3Pose inference / training profiles and the ncu --set full capture of the chained kernel (scratch .ncu-rep, summary in profiles/)
+timeout 600 python tools/bench_pose.py small 256 > gpurun_out/pose_profile.log 2>&1; head -3 gpurun_out/pose_profile.log | cut -c1-160
+timeout 600 python tools/bench_posetrain.py > gpurun_out/posetrain_profile.log 2>&1; head -2 gpurun_out/posetrain_profile.log | cut -c1-160
+timeout 300 python tools/time_preprocess.py > gpurun_out/preprocess_timing.log 2>&1; cat gpurun_out/preprocess_timing.log
+bash tools/profile_chain.sh
