@@ -133,14 +133,18 @@ __device__ __forceinline__ int kb_count(const ConvParams& p, int cls) {
 // NH (CHAIN kernels): 256-wide halves of the layer's output a CTA computes per pixel tile (2 = Cout 512); then the chained conv's
 // [N2][256 NH] weights do not fit and their 64-wide K slices stream through a ring of kW2Slots buffers instead.
 constexpr int kW2Slots = 3;
-template <int BLOCK_N, int STAGES, bool PAIR = false, int NSB = 4, bool HEAD2 = false, bool EPI2 = false, int CHAIN = 0, int KBR = 0, int NH = 1>
+// AH (3x3 / stride 1, Cin = 128): the A operand is NOT ringed.  Per pixel tile (8 x 16 brick of one image) two halo'd boxes
+// {64 ch, 10 px, 18 rows} (one per 64-channel block) land in a double-buffered region and every filter tap reads them through a
+// shifted descriptor start (conv_halo.cu's trick); the ring carries the weight tiles only.
+constexpr int kAHBoxBytes = (18 * 10 * 128 + 1023) / 1024 * 1024;      // one halo box, padded to the 1024-byte swizzle atom
+template <int BLOCK_N, int STAGES, bool PAIR = false, int NSB = 4, bool HEAD2 = false, bool EPI2 = false, int CHAIN = 0, int KBR = 0, int NH = 1, bool AH = false>
 struct SmemLayout {
   // fused head: this CTA's 16 rows x 256 K of the joint weights; CHAIN: the chained 1x1 conv's [N2 rows][256 K] weights
   static constexpr int kW2Bytes    = HEAD2 ? 4 * 16 * 128 : (NH == 1 ? 4 : kW2Slots) * CHAIN * 128;
   static constexpr int kBBytes     = (PAIR ? BLOCK_N / 2 : BLOCK_N) * kKBlock * 2;    // a CTA of a pair holds half of B's rows
-  static constexpr int kStageBytes = kABytes + (KBR ? 0 : kBBytes);
+  static constexpr int kStageBytes = (AH ? 0 : kABytes) + (KBR ? 0 : kBBytes);
   static constexpr int kOffA   = 0;
-  static constexpr int kOffB   = STAGES * kABytes;
+  static constexpr int kOffB   = AH ? 4 * kAHBoxBytes : STAGES * kABytes;
   static constexpr int kOffSB  = kOffB + (KBR ? KBR : STAGES) * kBBytes;
   static constexpr int kOffSS  = kOffSB + NSB * kSBBytes;             // float scale[kMaxBlockN], shift[kMaxBlockN] (x 2 groups with EPI2)
   static constexpr int kOffSS2 = kOffSS + ((EPI2 || NH >= 2) ? 4 : 2) * kMaxBlockN * 4;      // CHAIN: float scale2[128], shift2[128]
@@ -265,7 +269,7 @@ __device__ __forceinline__ void epi_chunk_math(const uint32_t (&v)[32], uint32_t
 // NH = 2 (CHAIN = 128, Cout = 512: layer2): the CTA computes BOTH 256-wide halves of a pixel tile one after the other through the
 // single main accumulator (weights streamed as usual), eight real chunks feed the chained GEMM (K = 512), whose weight slices
 // [128][64] stream through a small ring loaded by the issuer warp itself.
-template <int BLOCK_N, int STAGES, int ACT, bool RES, bool FINAL, bool PAIR = false, bool HEAD2 = false, bool EPI2 = false, int CHAIN = 0, int KBR = 0, int NH = 1>
+template <int BLOCK_N, int STAGES, int ACT, bool RES, bool FINAL, bool PAIR = false, bool HEAD2 = false, bool EPI2 = false, int CHAIN = 0, int KBR = 0, int NH = 1, bool AH = false>
 __global__ void __launch_bounds__(CHAIN ? kConvThreadsC : (EPI2 ? kConvThreads2 : kConvThreads), 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
                  const __grid_constant__ CUtensorMap tmW, const __grid_constant__ OutMaps tmOut,
@@ -296,7 +300,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   constexpr int kResLead = 2;                     // the residual of chunk q + 2 is requested while chunk q is processed
   constexpr int kLead = CHAIN ? kNumSB - 2 : kResLead;
   constexpr int kChunks2 = CHAIN / 64;            // 64-column chunks of the chained conv's output
-  using L = SmemLayout<BLOCK_N, STAGES, PAIR, kGroups * kNumSB, HEAD2, EPI2, CHAIN, KBR, NH>;
+  static_assert(!AH || (BLOCK_N == 128 && !PAIR && !RES && !FINAL && !HEAD2 && !EPI2 && CHAIN == 0), "halo'd A operand: 128-wide single-CTA tiles of a plain 3x3");
+  using L = SmemLayout<BLOCK_N, STAGES, PAIR, kGroups * kNumSB, HEAD2, EPI2, CHAIN, KBR, NH, AH>;
   static_assert(!PAIR || (BLOCK_N % 32 == 0 && !FINAL), "pair kernels: N multiple of 32, bf16 NHWC epilogue");
   constexpr int kChunks   = BLOCK_N >= 64 ? BLOCK_N / 64 : 1;
   constexpr int kTmemCols = CHAIN ? 512 : 2 * BLOCK_N <= 32 ? 32 : (2 * BLOCK_N <= 64 ? 64 : (2 * BLOCK_N <= 128 ? 128 : (2 * BLOCK_N <= 256 ? 256 : 512)));  // power of two
@@ -375,6 +380,28 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // around each UTMALDG, an integer division and the tap switch) -- measured ~540 cycles per k-block with loads, MMAs and
     // epilogue all disabled, i.e. slower than the 512-cycle MMA work of a 128x256x64 block.
     int stage = 0; uint32_t phase = 0;
+    if constexpr (AH) {
+      // halo'd A: two boxes per tile into buffer it & 1 (barriers: w2rfull = landed, w2rempty = its MMAs have retired), then the
+      // tile's 18 weight tiles through the ring
+      int it = 0;
+      for (int work = work0; work < p.num_tiles; work += wstep, ++it) {
+        const TileCoord t = tile_coord(p, work_tile<false>(p, work, 0));
+        const int buf = it & 1;
+        const int wrow = t.n_tile * BLOCK_N;
+        mbar_wait(&w2rempty_bar[buf], ((it >> 1) & 1) ^ 1);
+        if (lane == 0) {
+          mbar_arrive_expect_tx(&w2rfull_bar[buf], 2 * 18 * 10 * 128);
+          tma_load_4d(sA + (buf * 2 + 0) * kAHBoxBytes, &tmA, &w2rfull_bar[buf], 0, t.x0 - 1, t.y0 - 1, t.b0);
+          tma_load_4d(sA + (buf * 2 + 1) * kAHBoxBytes, &tmA, &w2rfull_bar[buf], 64, t.x0 - 1, t.y0 - 1, t.b0);
+        }
+        __syncwarp();
+        for (int kb = 0; kb < 18; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          tma_load_b_elect(smem_u32(&full_bar[stage]), L::kBBytes, smem_u32(sB + stage * L::kBBytes), &tmW, kb * kKBlock, wrow);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    } else {
     if constexpr (KBR != 0) {                     // the whole [BLOCK_N][64 KBR] weight tile, once
       if (lane == 0) {
         mbar_arrive_expect_tx(wres_bar, KBR * L::kBBytes);
@@ -416,6 +443,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
      }
     }
+    }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     // whole warp converged, one elected lane issues; descriptors as 32-bit halves (constant high word, low word = stage
@@ -424,6 +452,33 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       constexpr uint32_t kDescHi = (1024u >> 4) | (1u << 14) | (2u << 29);     // SBO = 1024 B, version 1, SWIZZLE_128B
       int stage = 0; uint32_t phase = 0; int it = 0;
       if constexpr (KBR != 0) mbar_wait(wres_bar, 0);
+      if constexpr (AH) {
+        // k-block kb = tap * 2 + channel block: the A rows of tap (ky, kx) are the box rows (y + ky) * 10 + x + kx, i.e. the box
+        // read from row offset ky * 10 + kx with a 10-row (1280-byte) stride between the 8-row groups
+        constexpr uint32_t kDescHiA = (1280u >> 4) | (1u << 14) | (2u << 29);
+        for (int work = work0; work < p.num_tiles; work += wstep, ++it) {
+          const int acc = it & 1, buf = it & 1;
+          mbar_wait(&tempty_bar[acc], ((it >> 1) & 1) ^ 1);
+          mbar_wait(&w2rfull_bar[buf], (it >> 1) & 1);
+          tc_fence_after();
+          const uint32_t tmem_d = tmem_base + acc * BLOCK_N;
+          for (int kb = 0; kb < 18; ++kb) {
+            mbar_wait(&full_bar[stage], phase);
+            tc_fence_after();
+            const int tap = kb >> 1, ky = tap / 3, kx = tap - 3 * ky;
+            const uint32_t a_addr = smem_u32(sA + (buf * 2 + (kb & 1)) * kAHBoxBytes) + (ky * 10 + kx) * 128;
+            const uint32_t a_lo = ((a_addr & 0x3FFFFu) >> 4) | (1u << 16);
+            const uint32_t b_lo = ((smem_u32(sB + stage * L::kBBytes) & 0x3FFFFu) >> 4) | (1u << 16);
+#pragma unroll
+            for (int k = 0; k < kKBlock / 16; ++k)
+              umma_bf16_elect_lo(tmem_d, a_lo + 2 * k, kDescHiA, b_lo + 2 * k, kDescHi, kIdesc, (kb | k) != 0);
+            umma_commit_elect(&empty_bar[stage]);
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          }
+          umma_commit_elect(&w2rempty_bar[buf]);      // the boxes may be overwritten once these MMAs retire
+          umma_commit_elect(&tfull_bar[acc]);
+        }
+      } else
       for (int work = work0; work < p.num_tiles; work += wstep) for (int nh = 0; nh < NH; ++nh, ++it) {     // it counts (tile, half)
         const int acc = (CHAIN && !kAcc2x) ? 0 : (it & 1);     // CHAIN (256-wide): one main accumulator (columns 256.. hold the chained conv's)
         mbar_wait(&tempty_bar[acc], ((CHAIN && !kAcc2x) ? (it & 1) : ((it >> 1) & 1)) ^ 1);
@@ -1062,6 +1117,7 @@ struct hpe_conv_plan {
   const void* fn;
   int epi2;                           // two epilogue groups (608-thread kernel)
   int halo_taps_y;                    // != 0: the layer runs on the y-halo variant (conv_halo.cu)
+  int ah;                             // != 0: halo'd A operand inside conv_gemm_kernel (3x3 / stride 1, 128 -> 128; AH template flag)
   HaloParams hp;
 };
 
@@ -1143,6 +1199,16 @@ static int desc_check(const hpe_conv_desc* d, const char* fn) {
 // BLOCK_N: the widest tile dividing Cout.  (Measured on B200: narrower tiles that fill the last wave of the
 // persistent grid better are still slower -- layer4 3x3 66 -> 78 us -- because every extra N tile re-reads
 // the A operand through the L2->SM fabric, which is what bounds these kernels; see profiles/.)
+// 3x3 / stride 1 / 128 -> 128 (ResNet layer2 conv2): the generic kernel re-reads the A brick for each of the 9 taps through the
+// L2 -> SM fabric (576 KB of operands per 128-pixel tile, 125 B per cycle of MMA work: the layer ran at 0.53 of the tensor peak);
+// with two halo'd boxes per tile it is 334 KB.  HPE_B200_HALO128=0 keeps the generic kernel.
+static bool halo128_eligible(const hpe_conv_desc* d) {
+  const char* e = getenv("HPE_B200_HALO128");
+  if (!(e ? atoi(e) : 1)) return false;
+  return d->kind == HPE_CONV_3x3 && d->stride == 1 && d->Cin == 128 && d->Cout == 128 && d->act == HPE_ACT_RELU && !d->has_residual &&
+         !d->in_cstride && !d->out_cstride && !d->Cin2 && !d->chain && !d->head2 && !d->pool && d->W % 8 == 0;
+}
+
 static bool is_class_strided(int kind);
 static int pick_block_n(const hpe_conv_desc* d, long long m_tiles) {
   if (d->kind == HPE_CONV_FINAL) return d->Cout <= 32 ? 32 : (d->Cout <= 64 ? 64 : (d->Cout <= 128 ? 128 : 256));
@@ -1540,6 +1606,8 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
   p.act = d->act; p.has_res = d->has_residual ? 1 : 0;
   int tw = 1, th = 1, nb = 128;
   pick_brick(128, p.Wo, p.Ho, p.B, (p.in_stride == 2 || p.in_stride2 == 2) ? 128 : 256, &tw, &th, &nb);
+  pl->ah = halo128_eligible(d) ? 1 : 0;
+  if (pl->ah) { tw = 8; th = 16; nb = 1; }         // the brick the two halo'd boxes {64, 10, 18, 1} cover
   p.tw = tw; p.th = th; p.nb = nb;
   p.tiles_x = (p.Wo + tw - 1) / tw; p.tiles_y = (p.Ho + th - 1) / th; p.tiles_b = (p.B + nb - 1) / nb;
   pl->block_n = pick_block_n(d, (long long)p.tiles_x * p.tiles_y * p.tiles_b * p.n_classes);
@@ -1586,6 +1654,12 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
     delete pl;
     return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: the LayerNorm-folded GELU layer runs on the cta_group::2 kernels only (>= 2 pixel tiles; 256-wide tiles with two epilogue groups or 192-wide tiles; HPE_B200_PAIR / HPE_B200_EPI2 != 0)");
   }
+  if (pl->ah) {
+    // 6 weight stages of 16 KB + 2 staging buffers (the `wait_group.read 0` protocol of the 6-stage kernels): 5 stages hold
+    // 1800 cycles of MMA work, less than the L2 round trip
+    pl->smem = SmemLayout<128, 6, false, 2, false, false, 0, 0, 1, true>::kDynamic;
+    pl->fn = (const void*)conv_gemm_kernel<128, 6, HPE_ACT_RELU, false, false, false, false, false, 0, 0, 1, true>;
+  } else
   pl->fn = d->chain ? (const void*)pick_kernel_chain(d->Cout, d->chain, p.has_res != 0, p.taps * p.kc_per_tap + p.kc2, &pl->smem)
                     : (const void*)pick_kernel(pl->block_n, d->act, p.has_res != 0, d->kind == HPE_CONV_FINAL, pl->pair != 0, d->head2 != 0, pl->epi2 != 0, &pl->smem);
   if (!pl->fn) { const int bn = pl->block_n; delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: no kernel for BLOCK_N=%d%s", bn, d->chain ? " (chained layers: Cin = 64 with a residual, or Cin = Cin2 = 64 without)" : ""); }
@@ -1662,8 +1736,8 @@ static int encode_plan_maps(hpe_conv_plan* pl, const void* x, const void* x2, co
       const uint64_t dims[4] = {C, (uint64_t)d.W, (uint64_t)d.H, (uint64_t)d.B};
       const uint64_t str[3] = {P * 2, (uint64_t)d.W * P * 2, (uint64_t)d.H * d.W * P * 2};
       const uint32_t s = (uint32_t)p.in_stride;
-      const uint32_t box[4] = {64, (uint32_t)(pl->halo_taps_y ? 10 : p.tw * s),
-                               (uint32_t)(pl->halo_taps_y ? kHaloRows + pl->halo_taps_y - 1 : p.th * s), (uint32_t)p.nb};
+      const uint32_t box[4] = {64, (uint32_t)((pl->halo_taps_y || pl->ah) ? 10 : p.tw * s),
+                               (uint32_t)(pl->halo_taps_y ? kHaloRows + pl->halo_taps_y - 1 : (pl->ah ? 18 : p.th * s)), (uint32_t)p.nb};
       const uint32_t es[4] = {1, s, s, 1};
       rc = encode_map(&pl->tmA, x, 4, dims, str, box, es, "A");
     }

@@ -268,6 +268,14 @@ __device__ __forceinline__ void tma_load_ab_elect(uint32_t bar, uint32_t bytes, 
       ::"r"(bar), "r"(bytes), "r"(dA), "l"(reinterpret_cast<uint64_t>(mA)), "r"(c0), "r"(c1), "r"(c2), "r"(c3),
         "r"(dB), "l"(reinterpret_cast<uint64_t>(mW)), "r"(k), "r"(row), "l"(pol) : "memory");
 }
+// expect_tx + the W box only (the A operand is resident: halo'd boxes)
+__device__ __forceinline__ void tma_load_b_elect(uint32_t bar, uint32_t bytes, uint32_t dB, const CUtensorMap* mW, int k, int row) {
+  asm volatile(
+      "{\n\t.reg .pred e;\n\telect.sync _|e, 0xffffffff;\n\t"
+      "@e mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n\t"
+      "@e cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%2], [%3, {%4, %5}], [%0];\n\t}"
+      ::"r"(bar), "r"(bytes), "r"(dB), "l"(reinterpret_cast<uint64_t>(mW)), "r"(k), "r"(row) : "memory");
+}
 // pair form: both boxes complete on `bar_cluster` (the leader's full barrier); the arrival is issued separately
 __device__ __forceinline__ void tma_load_ab_2sm_elect(uint32_t bar_cluster, uint32_t dA, const CUtensorMap* mA,
                                                       int c0, int c1, int c2, int c3, uint32_t dB, const CUtensorMap* mW, int k, int row,

@@ -95,8 +95,9 @@ def test_conv1x1_fused_projection_shortcut(hpe, cuda_dev, B, H, W, Cin, Cin2, Co
     (3, 10, 6, 64, 64, 1), (2, 8, 6, 512, 512, 1),
     (3, 32, 24, 64, 64, 1), (2, 16, 8, 64, 64, 1), (2, 64, 48, 64, 64, 1), (5, 48, 40, 64, 64, 1),   # y-halo variant (conv_halo.cu)
     (1, 120, 56, 64, 64, 1), (2, 124, 44, 64, 64, 1), (160, 32, 8, 64, 64, 1),                        # ... bricks hanging over the bottom / right edge
+    (4, 32, 24, 128, 128, 1), (3, 20, 16, 128, 128, 1), (2, 8, 8, 128, 128, 1), (37, 32, 24, 128, 128, 1), (1, 50, 40, 128, 128, 1),   # halo'd A operand (AH)
 ])
-def test_conv3x3(hpe, cuda_dev, B, H, W, C, Cout, stride):
+def test_conv3x3(hpe, cuda_dev, monkeypatch, B, H, W, C, Cout, stride):
     from importlib import import_module
     conv = import_module("2d-human-pose-estimation_b200.conv")
     g = torch.Generator().manual_seed(2)
@@ -107,6 +108,13 @@ def test_conv3x3(hpe, cuda_dev, B, H, W, C, Cout, stride):
     y = layer(nhwc(x))
     torch.cuda.synchronize()
     check(nchw(y), ref, "conv3x3")
+    if C == 128 and Cout == 128 and stride == 1 and W % 8 == 0:
+        # the halo'd-A variant (two {64, 10, 18} boxes per 8 x 16 brick, taps through shifted descriptors) adds the same products
+        # in the same order as the generic kernel (one A brick per tap through the ring): bit-identical
+        monkeypatch.setenv("HPE_B200_HALO128", "0")
+        plain = conv.ConvLayer(conv.CONV_3x3, B, H, W, C, Cout, stride, 1, False).load(w, scale, shift)
+        assert torch.equal(y, plain(nhwc(x)))
+        assert layer.set_schedule(True, 0, 0, 0) is True and torch.equal(y, layer(nhwc(x)))
 
 
 @pytest.mark.parametrize("kind,B,H,W,Cin,Cout", [("3x3", 256, 8, 6, 512, 512), ("1x1", 256, 8, 6, 2048, 512), ("3x3", 9, 8, 6, 512, 512)])
