@@ -300,7 +300,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   constexpr int kResLead = 2;                     // the residual of chunk q + 2 is requested while chunk q is processed
   constexpr int kLead = CHAIN ? kNumSB - 2 : kResLead;
   constexpr int kChunks2 = CHAIN / 64;            // 64-column chunks of the chained conv's output
-  static_assert(!AH || (BLOCK_N == 128 && !PAIR && !RES && !FINAL && !HEAD2 && !EPI2 && CHAIN == 0), "halo'd A operand: 128-wide single-CTA tiles of a plain 3x3");
+  static_assert(!AH || (BLOCK_N == 128 && !RES && !FINAL && !HEAD2 && !EPI2 && CHAIN == 0), "halo'd A operand: 128-wide tiles of a plain 3x3 (single CTA or cta_group::2)");
   using L = SmemLayout<BLOCK_N, STAGES, PAIR, kGroups * kNumSB, HEAD2, EPI2, CHAIN, KBR, NH, AH>;
   static_assert(!PAIR || (BLOCK_N % 32 == 0 && !FINAL), "pair kernels: N multiple of 32, bf16 NHWC epilogue");
   constexpr int kChunks   = BLOCK_N >= 64 ? BLOCK_N / 64 : 1;
@@ -355,7 +355,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     mbar_init(w2full_bar, 1); mbar_init(s2full_bar, 2); mbar_init(d2full_bar, 1); mbar_init(d2full_bar + 1, 1);
     mbar_init(&a2empty_bar[0], CHAIN ? 8 * kChunks2 : 1); mbar_init(&a2empty_bar[1], CHAIN ? 8 * kChunks2 : 1);
     mbar_init(wres_bar, 1);
-    for (int b = 0; b < kW2Slots; ++b) { mbar_init(&w2rfull_bar[b], 1); mbar_init(&w2rempty_bar[b], 1); }
+    for (int b = 0; b < kW2Slots; ++b) { mbar_init(&w2rfull_bar[b], (AH && PAIR) ? 2 : 1); mbar_init(&w2rempty_bar[b], 1); }   // AH: the leader's barrier collects both CTAs' boxes
     fence_mbar_init();
   }
   if (warp == 1) {
@@ -383,21 +383,39 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if constexpr (AH) {
       // halo'd A: two boxes per tile into buffer it & 1 (barriers: w2rfull = landed, w2rempty = its MMAs have retired), then the
       // tile's 18 weight tiles through the ring
+      // cta_group::2: each CTA loads the boxes of ITS M tile and half of every weight tile; all bytes are accounted on the
+      // leader's barriers (the ones its MMA warp waits on), the peer adds a remote arrival
       int it = 0;
       for (int work = work0; work < p.num_tiles; work += wstep, ++it) {
-        const TileCoord t = tile_coord(p, work_tile<false>(p, work, 0));
+        const TileCoord t = tile_coord(p, work_tile<PAIR>(p, work, rank));
         const int buf = it & 1;
-        const int wrow = t.n_tile * BLOCK_N;
+        const int wrow = t.n_tile * BLOCK_N + (PAIR ? rank * (BLOCK_N / 2) : 0);
         mbar_wait(&w2rempty_bar[buf], ((it >> 1) & 1) ^ 1);
         if (lane == 0) {
-          mbar_arrive_expect_tx(&w2rfull_bar[buf], 2 * 18 * 10 * 128);
-          tma_load_4d(sA + (buf * 2 + 0) * kAHBoxBytes, &tmA, &w2rfull_bar[buf], 0, t.x0 - 1, t.y0 - 1, t.b0);
-          tma_load_4d(sA + (buf * 2 + 1) * kAHBoxBytes, &tmA, &w2rfull_bar[buf], 64, t.x0 - 1, t.y0 - 1, t.b0);
+          if constexpr (PAIR) {
+            const uint32_t afull0 = mapa_shared(smem_u32(&w2rfull_bar[buf]), 0);
+            if (rank == 0) mbar_arrive_expect_tx(&w2rfull_bar[buf], 2 * 2 * 18 * 10 * 128);
+            else           mbar_arrive_cluster(afull0);
+            tma_load_4d_2sm(sA + (buf * 2 + 0) * kAHBoxBytes, &tmA, afull0, 0, t.x0 - 1, t.y0 - 1, t.b0);
+            tma_load_4d_2sm(sA + (buf * 2 + 1) * kAHBoxBytes, &tmA, afull0, 64, t.x0 - 1, t.y0 - 1, t.b0);
+          } else {
+            mbar_arrive_expect_tx(&w2rfull_bar[buf], 2 * 18 * 10 * 128);
+            tma_load_4d(sA + (buf * 2 + 0) * kAHBoxBytes, &tmA, &w2rfull_bar[buf], 0, t.x0 - 1, t.y0 - 1, t.b0);
+            tma_load_4d(sA + (buf * 2 + 1) * kAHBoxBytes, &tmA, &w2rfull_bar[buf], 64, t.x0 - 1, t.y0 - 1, t.b0);
+          }
         }
         __syncwarp();
         for (int kb = 0; kb < 18; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          tma_load_b_elect(smem_u32(&full_bar[stage]), L::kBBytes, smem_u32(sB + stage * L::kBBytes), &tmW, kb * kKBlock, wrow);
+          const uint32_t fb = smem_u32(&full_bar[stage]);
+          if constexpr (PAIR) {
+            const uint32_t full0 = mapa_shared(fb, 0);
+            if (rank == 0) mbar_arrive_expect_tx_elect(fb, 2 * L::kBBytes);
+            else           mbar_arrive_cluster_elect(full0);
+            tma_load_b_2sm_elect(full0, smem_u32(sB + stage * L::kBBytes), &tmW, kb * kKBlock, wrow);
+          } else {
+            tma_load_b_elect(fb, L::kBBytes, smem_u32(sB + stage * L::kBBytes), &tmW, kb * kKBlock, wrow);
+          }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -470,13 +488,16 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const uint32_t a_lo = ((a_addr & 0x3FFFFu) >> 4) | (1u << 16);
             const uint32_t b_lo = ((smem_u32(sB + stage * L::kBBytes) & 0x3FFFFu) >> 4) | (1u << 16);
 #pragma unroll
-            for (int k = 0; k < kKBlock / 16; ++k)
-              umma_bf16_elect_lo(tmem_d, a_lo + 2 * k, kDescHiA, b_lo + 2 * k, kDescHi, kIdesc, (kb | k) != 0);
-            umma_commit_elect(&empty_bar[stage]);
+            for (int k = 0; k < kKBlock / 16; ++k) {
+              if constexpr (PAIR) umma_bf16_2sm_elect_lo(tmem_d, a_lo + 2 * k, kDescHiA, b_lo + 2 * k, kDescHi, kIdesc, (kb | k) != 0);
+              else                umma_bf16_elect_lo(tmem_d, a_lo + 2 * k, kDescHiA, b_lo + 2 * k, kDescHi, kIdesc, (kb | k) != 0);
+            }
+            if constexpr (PAIR) umma_commit_2sm_elect(&empty_bar[stage], 3); else umma_commit_elect(&empty_bar[stage]);
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
           }
-          umma_commit_elect(&w2rempty_bar[buf]);      // the boxes may be overwritten once these MMAs retire
-          umma_commit_elect(&tfull_bar[acc]);
+          // the boxes (of both CTAs) may be overwritten once these MMAs retire; the accumulator is ready
+          if constexpr (PAIR) { umma_commit_2sm_elect(&w2rempty_bar[buf], 3); umma_commit_2sm_elect(&tfull_bar[acc], 3); }
+          else                { umma_commit_elect(&w2rempty_bar[buf]); umma_commit_elect(&tfull_bar[acc]); }
         }
       } else
       for (int work = work0; work < p.num_tiles; work += wstep) for (int nh = 0; nh < NH; ++nh, ++it) {     // it counts (tile, half)
@@ -1201,10 +1222,10 @@ static int desc_check(const hpe_conv_desc* d, const char* fn) {
 // the A operand through the L2->SM fabric, which is what bounds these kernels; see profiles/.)
 // 3x3 / stride 1 / 128 -> 128 (ResNet layer2 conv2): the generic kernel re-reads the A brick for each of the 9 taps through the
 // L2 -> SM fabric (576 KB of operands per 128-pixel tile, 125 B per cycle of MMA work: the layer ran at 0.53 of the tensor peak);
-// with two halo'd boxes per tile it is 334 KB.  HPE_B200_HALO128=0 keeps the generic kernel.
+// with two halo'd boxes per tile it is 334 KB.  HPE_B200_HALO128=0 keeps the generic kernel (1: single CTAs, 2: CTA pairs, default).
 static bool halo128_eligible(const hpe_conv_desc* d) {
   const char* e = getenv("HPE_B200_HALO128");
-  if (!(e ? atoi(e) : 1)) return false;
+  if (!(e ? atoi(e) : 2)) return false;
   return d->kind == HPE_CONV_3x3 && d->stride == 1 && d->Cin == 128 && d->Cout == 128 && d->act == HPE_ACT_RELU && !d->has_residual &&
          !d->in_cstride && !d->out_cstride && !d->Cin2 && !d->chain && !d->head2 && !d->pool && d->W % 8 == 0;
 }
@@ -1627,8 +1648,12 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
     // stages hold only 256 cycles of MMA work, so the longer cross-CTA hand-off outweighs the two extra ring stages
     const char* e128 = getenv("HPE_B200_PAIR128");
     const char* e192 = getenv("HPE_B200_PAIR192");
+    const char* eah = getenv("HPE_B200_HALO128");
+    // HPE_B200_HALO128 = 2 (default): the halo'd-A kernel as a cta_group::2 pair (8 KB weight half-tiles, ten stages: layer 55.4 ->
+    // 53.2 us, forward 3.285 -> 3.275 ms); 1: single CTAs
+    const bool ah_pair = (eah ? atoi(eah) : 2) == 2;
     const long long m_tiles = (long long)p.tiles_x * p.tiles_y * p.tiles_b;
-    pl->pair = !d->chain && !(e && e[0] == '0') && (pl->block_n == 256 || (pl->block_n == 192 && !(e192 && e192[0] == '0')) || (pl->block_n == 128 && e128 && e128[0] == '1')) && d->kind != HPE_CONV_FINAL && m_tiles >= 2 && !halo_eligible(d, pl->Ho, pl->Wo);
+    pl->pair = !d->chain && !(e && e[0] == '0') && (pl->block_n == 256 || (pl->block_n == 192 && !(e192 && e192[0] == '0')) || (pl->block_n == 128 && ((e128 && e128[0] == '1') || (pl->ah && ah_pair)))) && d->kind != HPE_CONV_FINAL && m_tiles >= 2 && !halo_eligible(d, pl->Ho, pl->Wo);
     if (d->chain && halo_eligible(d, pl->Ho, pl->Wo)) { delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: chained layer on the halo kernel"); }
   if (d->head2 && !pl->pair) { delete pl; return fail(HPE_EUNSUPPORTED, "hpe_conv_plan_create: the fused head runs on the cta_group::2 kernel only (needs >= 2 M tiles, HPE_B200_PAIR != 0)"); }
     if (pl->pair) {
@@ -1659,6 +1684,10 @@ extern "C" int hpe_conv_plan_create(const hpe_conv_desc* d, hpe_conv_plan** out)
     // 1800 cycles of MMA work, less than the L2 round trip
     pl->smem = SmemLayout<128, 6, false, 2, false, false, 0, 0, 1, true>::kDynamic;
     pl->fn = (const void*)conv_gemm_kernel<128, 6, HPE_ACT_RELU, false, false, false, false, false, 0, 0, 1, true>;
+    if (pl->pair) {       // cta_group::2: 8 KB weight half-tiles, ten stages
+      pl->smem = SmemLayout<128, 10, true, 3, false, false, 0, 0, 1, true>::kDynamic;
+      pl->fn = (const void*)conv_gemm_kernel<128, 10, HPE_ACT_RELU, false, false, true, false, false, 0, 0, 1, true>;
+    }
   } else
   pl->fn = d->chain ? (const void*)pick_kernel_chain(d->Cout, d->chain, p.has_res != 0, p.taps * p.kc_per_tap + p.kc2, &pl->smem)
                     : (const void*)pick_kernel(pl->block_n, d->act, p.has_res != 0, d->kind == HPE_CONV_FINAL, pl->pair != 0, d->head2 != 0, pl->epi2 != 0, &pl->smem);

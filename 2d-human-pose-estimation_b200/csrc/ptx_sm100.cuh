@@ -276,6 +276,13 @@ __device__ __forceinline__ void tma_load_b_elect(uint32_t bar, uint32_t bytes, u
       "@e cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%2], [%3, {%4, %5}], [%0];\n\t}"
       ::"r"(bar), "r"(bytes), "r"(dB), "l"(reinterpret_cast<uint64_t>(mW)), "r"(k), "r"(row) : "memory");
 }
+// ... its pair form: this CTA's half of the W tile, completing on `bar_cluster` (the leader's full barrier)
+__device__ __forceinline__ void tma_load_b_2sm_elect(uint32_t bar_cluster, uint32_t dB, const CUtensorMap* mW, int k, int row) {
+  asm volatile(
+      "{\n\t.reg .pred e;\n\telect.sync _|e, 0xffffffff;\n\t"
+      "@e cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%1], [%2, {%3, %4}], [%0];\n\t}"
+      ::"r"(bar_cluster), "r"(dB), "l"(reinterpret_cast<uint64_t>(mW)), "r"(k), "r"(row) : "memory");
+}
 // pair form: both boxes complete on `bar_cluster` (the leader's full barrier); the arrival is issued separately
 __device__ __forceinline__ void tma_load_ab_2sm_elect(uint32_t bar_cluster, uint32_t dA, const CUtensorMap* mA,
                                                       int c0, int c1, int c2, int c3, uint32_t dB, const CUtensorMap* mW, int k, int row,

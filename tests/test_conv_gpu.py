@@ -111,9 +111,10 @@ def test_conv3x3(hpe, cuda_dev, monkeypatch, B, H, W, C, Cout, stride):
     if C == 128 and Cout == 128 and stride == 1 and W % 8 == 0:
         # the halo'd-A variant (two {64, 10, 18} boxes per 8 x 16 brick, taps through shifted descriptors) adds the same products
         # in the same order as the generic kernel (one A brick per tap through the ring): bit-identical
-        monkeypatch.setenv("HPE_B200_HALO128", "0")
-        plain = conv.ConvLayer(conv.CONV_3x3, B, H, W, C, Cout, stride, 1, False).load(w, scale, shift)
-        assert torch.equal(y, plain(nhwc(x)))
+        for mode in ("0", "1"):           # generic kernel / single-CTA form of the halo'd-A kernel (the default is its cta_group::2 form)
+            monkeypatch.setenv("HPE_B200_HALO128", mode)
+            plain = conv.ConvLayer(conv.CONV_3x3, B, H, W, C, Cout, stride, 1, False).load(w, scale, shift)
+            assert torch.equal(y, plain(nhwc(x))), mode
         assert layer.set_schedule(True, 0, 0, 0) is True and torch.equal(y, layer(nhwc(x)))
 
 
