@@ -25,6 +25,7 @@ There is no CPU path.
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 import torch.nn.functional as F
@@ -64,6 +65,9 @@ class _ConvSpec:
         self.fwd = ConvLayer(kind, B, H, W, self.cinp, self.coutp, stride, ACT_NONE, False, dev)
         self.dgrad = DgradLayer(kind, B, H, W, self.cinp, self.coutp, stride, device=dev) if need_dx else None
         self.wgrad = WgradLayer(kind, B, H, W, self.cinp, self.coutp, stride, dev)
+        self.mod = None              # the nn.Conv2d whose weight this spec packs (set by conv())
+        self.wsrc = None             # persistent zero-padded fp32 copy of the weight (layers with padded channels), see prepack()
+        self.prepacked = False       # True while a PoseTrainStep has packed both operands for the step in flight
 
     def pad_weight(self, w):
         if self.cinp == self.cin and self.coutp == self.cout:
@@ -78,8 +82,11 @@ class ConvFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, w, spec):
-        wp = spec.pad_weight(w)
-        spec.fwd.load(wp)
+        if spec.prepacked:           # operands packed by prepack() in one launch for the whole step
+            wp = spec.wsrc if spec.wsrc is not None else w.detach()
+        else:
+            wp = spec.pad_weight(w)
+            spec.fwd.load(wp)
         z = spec.fwd(x)
         ctx.save_for_backward(x, wp)
         ctx.spec = spec
@@ -92,7 +99,8 @@ class ConvFn(torch.autograd.Function):
         dz = dz.contiguous()
         dx = dw = None
         if ctx.needs_input_grad[0]:
-            spec.dgrad.load(wp)
+            if not spec.prepacked:
+                spec.dgrad.load(wp)
             dx = spec.dgrad(dz)
         if ctx.needs_input_grad[1]:
             dwp = torch.empty_like(wp)
@@ -108,7 +116,58 @@ def conv(model, mod, x, kind, stride=1, need_dx=True):
     spec = _plans(model).get(key)
     if spec is None:
         spec = _plans(model)[key] = _ConvSpec(kind, B, H, W, mod.in_channels, mod.out_channels, stride, x.device, need_dx)
+        spec.mod = mod
     return ConvFn.apply(x.contiguous(), mod.weight, spec)
+
+
+def prepack(model):
+    """Pack the forward and backward-data operands of EVERY ConvFn layer of the model's training plans in ONE launch
+    (hpe_conv_pack_jobs_run, as ``TrainPlan.repack`` does for the ResNet step) instead of two launches per layer per step, and
+    mark the specs so that ConvFn skips its own packing.  Layers with padded channels pack from a persistent zero-padded fp32
+    copy of the weight (one strided copy per step).  Returns the specs it marked (``release`` un-marks them); [] before the
+    first forward has created the plans."""
+    specs = [sp for k, sp in _plans(model).items() if k[0] == "conv" and sp.mod is not None]
+    if not specs:
+        return []
+    items = []
+    for sp in specs:
+        w = sp.mod.weight
+        if sp.cinp != sp.cin or sp.coutp != sp.cout:
+            if sp.wsrc is None:
+                sp.wsrc = torch.zeros((sp.coutp, sp.cinp, sp.k, sp.k), dtype=torch.float32, device=w.device)
+            sp.wsrc[:sp.cout, :sp.cin].copy_(w.detach())
+            src = sp.wsrc
+        else:
+            src = w.detach()
+            if not (src.dtype == torch.float32 and src.is_contiguous()):
+                return []
+        items.append((sp.fwd.desc, 0, src, sp.fwd.w_packed))
+        if sp.dgrad is not None:
+            items.append((sp.dgrad.fwd_desc, 1, src, sp.dgrad.w_packed))
+    cache = _plans(model).setdefault(("prepack",), {})
+    key = tuple((w.data_ptr(), wp.data_ptr()) for _, _, w, wp in items)
+    lib = _lib.lib()
+    if cache.get("key") != key:
+        jb = lib.hpe_pack_job_bytes()
+        host = (C.c_char * (jb * len(items)))()
+        begin = 0
+        for k, (desc, dg, w, wp) in enumerate(items):
+            nb = C.c_int()
+            _lib.check(lib.hpe_conv_pack_job_fill(C.byref(desc), dg, w.data_ptr(), wp.data_ptr(), begin,
+                                                  C.addressof(host) + k * jb, C.byref(nb)), "hpe_conv_pack_job_fill")
+            begin += nb.value
+        cache.update(key=key, jobs=torch.frombuffer(bytearray(host.raw), dtype=torch.uint8).to(items[0][2].device), n=len(items), blocks=begin)
+    with torch.cuda.device(items[0][2].device):
+        _lib.check(lib.hpe_conv_pack_jobs_run(_lib.ptr(cache["jobs"]), cache["n"], cache["blocks"], _lib.stream_ptr()),
+                   "hpe_conv_pack_jobs_run")
+    for sp in specs:
+        sp.prepacked = True
+    return specs
+
+
+def release(specs):
+    for sp in specs:
+        sp.prepacked = False
 
 
 # ------------------------------------------------------------------------------------------------- BatchNorm + activation
@@ -431,8 +490,12 @@ class PoseTrainStep:
         self.flat_grad.zero_()
         for n, p in self._trainable:                           # autograd accumulates in place into the flat buffer
             p.grad = self._grad_views[n]
-        loss, items = self.criterion(train_forward(self.model, images), targets)
-        loss.backward()
+        packed = prepack(self.model) if os.environ.get("HPE_B200_POSE_PREPACK", "1") != "0" else []
+        try:
+            loss, items = self.criterion(train_forward(self.model, images), targets)
+            loss.backward()
+        finally:
+            release(packed)
         self.loss, self.items = loss.detach(), items
 
     def _update(self):
