@@ -103,9 +103,16 @@ class ConvFn(torch.autograd.Function):
                 spec.dgrad.load(wp)
             dx = spec.dgrad(dz)
         if ctx.needs_input_grad[1]:
-            dwp = torch.empty_like(wp)
-            spec.wgrad(x, dz, dwp)
-            dw = dwp[:spec.cout, :spec.cin].contiguous() if dwp.shape[:2] != (spec.cout, spec.cin) else dwp
+            tgt = _direct_target(spec.mod, "weight") if spec.mod is not None else None
+            if tgt is not None and tuple(wp.shape) == tuple(tgt.shape):
+                spec.wgrad(x, dz, tgt)                       # straight into the flat gradient buffer
+            else:
+                dwp = torch.empty_like(wp)
+                spec.wgrad(x, dz, dwp)
+                if tgt is not None:
+                    tgt.copy_(dwp[:spec.cout, :spec.cin])
+                else:
+                    dw = dwp[:spec.cout, :spec.cin].contiguous() if dwp.shape[:2] != (spec.cout, spec.cin) else dwp
         return dx, dw, None
 
 
@@ -170,6 +177,27 @@ def release(specs):
         sp.prepacked = False
 
 
+# Direct gradient targets (PoseTrainStep): a parameter whose gradient is produced by exactly one kernel per step (conv weight:
+# wgrad; BatchNorm gamma / beta: hpe_bnact_backward) can have that kernel write straight into the parameter's slice of the flat
+# gradient buffer -- no temporary, no slice copy, no autograd accumulation kernel (181 elementwise adds per step otherwise).
+# `_DIRECT[0]` is the current step's token (0 = off); a module remembers the token of its last direct write in `_hpe_grad_step`,
+# so a module that runs twice in one step (shared weights) falls back to the accumulating autograd path on its second use.
+_DIRECT = [0]
+
+
+def _direct_target(mod, name):
+    """The flat-buffer view registered for `mod.<name>` if this use may write it directly, else None."""
+    tok = _DIRECT[0]
+    tgt = getattr(mod, "_hpe_grad", None) if tok else None
+    if tgt is None or name not in tgt:
+        return None
+    seen = mod.__dict__.setdefault("_hpe_grad_step", {})
+    if seen.get(name) == tok:
+        return None
+    seen[name] = tok
+    return tgt[name]
+
+
 # ------------------------------------------------------------------------------------------------- BatchNorm + activation
 class BNActFn(torch.autograd.Function):
     """``y = act(BatchNorm2d(z))``: BATCH statistics when the module is in training mode (running statistics updated as torch
@@ -208,7 +236,7 @@ class BNActFn(torch.autograd.Function):
             if bn.num_batches_tracked is not None:
                 bn.num_batches_tracked += 1
         ctx.save_for_backward(z, g, scale, shift, mean, rstd)
-        ctx.act, ctx.Cr, ctx.frozen = int(act), Cr, frozen
+        ctx.act, ctx.Cr, ctx.frozen, ctx.bn = int(act), Cr, frozen, bn
         return y
 
     @staticmethod
@@ -219,12 +247,18 @@ class BNActFn(torch.autograd.Function):
         dev = z.device
         dy = dy.contiguous()
         dz = torch.empty_like(z)
-        dbeta, dgamma = _f32(Cp, dev), _f32(Cp, dev)
+        direct = False
+        if Cp == ctx.Cr and ctx.needs_input_grad[1] and ctx.needs_input_grad[2]:
+            tg, tb = _direct_target(ctx.bn, "weight"), _direct_target(ctx.bn, "bias")
+            direct = tg is not None and tb is not None
+        dbeta, dgamma = (tb, tg) if direct else (_f32(Cp, dev), _f32(Cp, dev))
         scratch = _f32(_lib.lib().hpe_bnact_scratch_elems(Cp), dev)
         with torch.cuda.device(dev):
             _lib.check(_lib.lib().hpe_bnact_backward(_lib.ptr(dy), _lib.ptr(z), M, Cp, _lib.ptr(mean), _lib.ptr(rstd), _lib.ptr(g),
                                                      _lib.ptr(scale), _lib.ptr(shift), ctx.act, int(ctx.frozen), _lib.ptr(scratch), _lib.ptr(dbeta),
                                                      _lib.ptr(dgamma), _lib.ptr(dz), _lib.stream_ptr()), "hpe_bnact_backward")
+        if direct:
+            return dz, None, None, None, None
         return dz, dgamma[:ctx.Cr].contiguous(), dbeta[:ctx.Cr].contiguous(), None, None
 
 
@@ -476,6 +510,15 @@ class PoseTrainStep:
                 p.data = pv[n]
         self._trainable = [(n, p) for n, p in model.named_parameters() if p.requires_grad]
         self._grad_views = {n: self.flat_grad.narrow(0, self.layout.offsets[n], p.numel()).view(p.shape) for n, p in self._trainable}
+        # direct gradient targets of the conv weights and BatchNorm affine parameters (see _direct_target)
+        mods = dict(model.named_modules())
+        for n, p in self._trainable:
+            mname, _, pname = n.rpartition(".")
+            m = mods.get(mname)
+            if isinstance(m, (torch.nn.Conv2d, torch.nn.BatchNorm2d)) and pname in ("weight", "bias") and \
+                    not (isinstance(m, torch.nn.Conv2d) and pname == "bias"):
+                m.__dict__.setdefault("_hpe_grad", {})[pname] = self._grad_views[n]
+        self._step_token = 0
 
     def broadcast_parameters(self, src=0):
         import torch.distributed as dist
@@ -491,11 +534,14 @@ class PoseTrainStep:
         for n, p in self._trainable:                           # autograd accumulates in place into the flat buffer
             p.grad = self._grad_views[n]
         packed = prepack(self.model) if os.environ.get("HPE_B200_POSE_PREPACK", "1") != "0" else []
+        self._step_token += 1
+        _DIRECT[0] = (id(self), self._step_token) if os.environ.get("HPE_B200_POSE_DIRECT_GRAD", "1") != "0" else 0
         try:
             loss, items = self.criterion(train_forward(self.model, images), targets)
             loss.backward()
         finally:
             release(packed)
+            _DIRECT[0] = 0
         self.loss, self.items = loss.detach(), items
 
     def _update(self):

@@ -59,3 +59,26 @@ def test_config_reference_keys(hpe, tmp_path):
     assert cfg.train.optimizer == "RMSprop" and cfg.train.lr == 2.5e-4
     with pytest.raises(AttributeError):
         cfg.seed = 1
+
+
+def test_direct_gradient_target_is_granted_once_per_step():
+    """posetrain._direct_target: a module's parameter may be written straight into the flat gradient buffer by the ONE kernel that
+    produces its gradient; a second use of the same module in the same step (shared weights) must fall back to autograd's
+    accumulation, and nothing is granted outside a PoseTrainStep."""
+    from importlib import import_module
+    import torch
+    pt = import_module("2d-human-pose-estimation_b200.posetrain")
+    m = torch.nn.Conv2d(8, 8, 1)
+    view = torch.zeros_like(m.weight)
+    assert pt._direct_target(m, "weight") is None                 # no step in flight, nothing registered
+    m.__dict__["_hpe_grad"] = {"weight": view}
+    assert pt._direct_target(m, "weight") is None                 # registered, but no step in flight
+    pt._DIRECT[0] = ("step", 1)
+    try:
+        assert pt._direct_target(m, "weight") is view
+        assert pt._direct_target(m, "weight") is None             # second use in the same step
+        assert pt._direct_target(m, "bias") is None               # never registered
+        pt._DIRECT[0] = ("step", 2)
+        assert pt._direct_target(m, "weight") is view             # next step
+    finally:
+        pt._DIRECT[0] = 0
