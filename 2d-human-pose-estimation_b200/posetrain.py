@@ -183,6 +183,7 @@ def release(specs):
 # `_DIRECT[0]` is the current step's token (0 = off); a module remembers the token of its last direct write in `_hpe_grad_step`,
 # so a module that runs twice in one step (shared weights) falls back to the accumulating autograd path on its second use.
 _DIRECT = [0]
+_NBT = [None]        # PoseTrainStep: set of id(bn) of the training-mode BatchNorm modules the forward in flight ran (else None)
 
 
 def _direct_target(mod, name):
@@ -234,7 +235,10 @@ class BNActFn(torch.autograd.Function):
             if Cp != Cr:
                 bn.running_mean.copy_(rm[:Cr]); bn.running_var.copy_(rv[:Cr])
             if bn.num_batches_tracked is not None:
-                bn.num_batches_tracked += 1
+                if _NBT[0] is not None:
+                    _NBT[0].add(id(bn))              # PoseTrainStep adds 1 to all of them with ONE launch after the forward
+                else:
+                    bn.num_batches_tracked += 1
         ctx.save_for_backward(z, g, scale, shift, mean, rstd)
         ctx.act, ctx.Cr, ctx.frozen, ctx.bn = int(act), Cr, frozen, bn
         return y
@@ -519,6 +523,15 @@ class PoseTrainStep:
                     not (isinstance(m, torch.nn.Conv2d) and pname == "bias"):
                 m.__dict__.setdefault("_hpe_grad", {})[pname] = self._grad_views[n]
         self._step_token = 0
+        # `num_batches_tracked` of every BatchNorm re-pointed at one flat int64 buffer: one masked add per step instead of one
+        # tiny kernel per module (the mask = the modules that ran in training mode; torch increments only those)
+        self._bns = [m for m in model.modules() if isinstance(m, torch.nn.BatchNorm2d) and m.num_batches_tracked is not None]
+        self.flat_nbt = torch.zeros(max(len(self._bns), 1), dtype=torch.int64, device=dev)
+        with torch.no_grad():
+            for i, m in enumerate(self._bns):
+                self.flat_nbt[i] = m.num_batches_tracked.to(dev)
+                m.num_batches_tracked.data = self.flat_nbt[i]
+        self._nbt_mask, self._nbt_key = None, None
 
     def broadcast_parameters(self, src=0):
         import torch.distributed as dist
@@ -536,12 +549,22 @@ class PoseTrainStep:
         packed = prepack(self.model) if os.environ.get("HPE_B200_POSE_PREPACK", "1") != "0" else []
         self._step_token += 1
         _DIRECT[0] = (id(self), self._step_token) if os.environ.get("HPE_B200_POSE_DIRECT_GRAD", "1") != "0" else 0
+        _NBT[0] = set()
         try:
-            loss, items = self.criterion(train_forward(self.model, images), targets)
+            levels = train_forward(self.model, images)
+            ran = _NBT[0]
+            _NBT[0] = None
+            key = tuple(id(m) in ran for m in self._bns)
+            if key != self._nbt_key:                      # (re)built outside any graph capture: the eager warm-up steps come first
+                self._nbt_key = key
+                self._nbt_mask = torch.tensor([int(k) for k in key] or [0], dtype=torch.int64).to(self.device)
+            self.flat_nbt.add_(self._nbt_mask)
+            loss, items = self.criterion(levels, targets)
             loss.backward()
         finally:
             release(packed)
             _DIRECT[0] = 0
+            _NBT[0] = None
         self.loss, self.items = loss.detach(), items
 
     def _update(self):
